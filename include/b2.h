@@ -1,0 +1,216 @@
+/*
+ * b2.h -- C ABI of the B200-native GGUF inference path (libb2.so).
+ *
+ * The reference (graz-dev/llms-on-kubernetes) has no in-process plugin / FFI for this path: its
+ * boundary is the process `llama-server --host --port --model --alias`
+ * (ramalama-models/helm-chart/templates/model-deployments.yaml:26-35) speaking OpenAI-style HTTP to
+ * the API gateway (ramalama-models/helm-chart/templates/api-gateway.yaml:63-104).  This header is the
+ * "thin C-ABI layer" BASELINE.json's north_star asks for underneath that process: the llama-server
+ * binary in this repo (llms-on-kubernetes_b200/csrc/server) and the pytest/ctypes harness both call
+ * exactly these symbols.  Each entry point cites the stage of the reference's hot path it replaces
+ * (the reference-side implementation of rows a8-a16 is the un-vendored
+ * llama-server launched at model-deployments.yaml:26-35).
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types; every function returns 0 on success and
+ * a negative B2_E* code on failure, with b2_last_error() giving a thread-local message; the caller
+ * owns host buffers, the library owns device buffers it allocates; every kernel-launching entry point
+ * takes an explicit cudaStream_t (passed as void*; NULL = the legacy default stream); no exceptions
+ * cross the boundary; there is NO CPU fallback -- without a CUDA device the compute entry points fail
+ * with B2_ECUDA.
+ */
+#ifndef B2_H
+#define B2_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_ABI_VERSION 1
+
+enum {
+    B2_OK = 0,
+    B2_EINVAL = -1,   /* bad argument (shape, type, NULL)            */
+    B2_EIO = -2,      /* file cannot be opened / read                */
+    B2_EFORMAT = -3,  /* not a GGUF file, or malformed               */
+    B2_EUNSUP = -4,   /* valid GGUF, but arch / tensor type unsupported */
+    B2_ECUDA = -5,    /* CUDA runtime error (no device, OOM, launch) */
+    B2_ERANGE = -6,   /* position / token / size outside limits      */
+    B2_ENOTFOUND = -7
+};
+
+/* ggml tensor type ids as stored in GGUF (gguf-py constants.py:4059-4093) */
+enum {
+    B2_TYPE_F32 = 0, B2_TYPE_F16 = 1, B2_TYPE_Q8_0 = 8, B2_TYPE_Q4_K = 12,
+    B2_TYPE_Q5_K = 13, B2_TYPE_Q6_K = 14, B2_TYPE_BF16 = 30
+};
+
+/* GGUF metadata value types (gguf-py constants.py:4157-4170) */
+enum {
+    B2_KV_U8 = 0, B2_KV_I8, B2_KV_U16, B2_KV_I16, B2_KV_U32, B2_KV_I32, B2_KV_F32, B2_KV_BOOL,
+    B2_KV_STRING, B2_KV_ARRAY, B2_KV_U64, B2_KV_I64, B2_KV_F64
+};
+
+typedef struct b2_gguf b2_gguf;    /* a parsed GGUF file (host side, mmap'd)          */
+typedef struct b2_model b2_model;  /* weights resident in HBM, raw blocks as on disk  */
+typedef struct b2_ctx b2_ctx;      /* one decode context: KV cache, scratch, CUDA graph */
+
+const char* b2_last_error(void);
+int b2_abi_version(void);
+/* number of CUDA devices visible, or a negative error (used by the server to fail loudly) */
+int b2_device_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * GGUF container  ("GGUF load"; layout = gguf-py gguf_reader.py:132-185,259-287)
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+    const char* name;      /* NUL-terminated copy owned by the b2_gguf */
+    uint32_t n_dims;
+    uint64_t dims[4];      /* fastest-varying first, as on disk */
+    uint32_t type;         /* ggml type id */
+    uint64_t offset;       /* relative to the data section */
+    uint64_t n_bytes;
+} b2_tensor_info;
+
+int b2_gguf_open(const char* path, b2_gguf** out);
+void b2_gguf_close(b2_gguf* g);
+uint32_t b2_gguf_version(const b2_gguf* g);
+uint32_t b2_gguf_alignment(const b2_gguf* g);
+uint64_t b2_gguf_data_offset(const b2_gguf* g);      /* absolute file offset of the tensor data */
+int64_t b2_gguf_n_kv(const b2_gguf* g);
+int64_t b2_gguf_n_tensors(const b2_gguf* g);
+const char* b2_gguf_kv_key(const b2_gguf* g, int64_t i);
+int b2_gguf_kv_type(const b2_gguf* g, int64_t i);        /* B2_KV_* */
+int b2_gguf_kv_array_type(const b2_gguf* g, int64_t i);  /* element type when B2_KV_ARRAY */
+int64_t b2_gguf_kv_array_len(const b2_gguf* g, int64_t i);
+int64_t b2_gguf_find_kv(const b2_gguf* g, const char* key);  /* index or B2_ENOTFOUND */
+/* scalar accessors convert between integer widths / float widths; strings return a pointer into
+ * the mapping plus a length (not NUL-terminated) */
+int b2_gguf_kv_u64(const b2_gguf* g, int64_t i, uint64_t* out);
+int b2_gguf_kv_i64(const b2_gguf* g, int64_t i, int64_t* out);
+int b2_gguf_kv_f64(const b2_gguf* g, int64_t i, double* out);
+int b2_gguf_kv_str(const b2_gguf* g, int64_t i, const char** s, uint64_t* len);
+/* array element accessors (element j of array-valued KV i) */
+int b2_gguf_kv_arr_str(const b2_gguf* g, int64_t i, int64_t j, const char** s, uint64_t* len);
+int b2_gguf_kv_arr_f64(const b2_gguf* g, int64_t i, int64_t j, double* out);
+int b2_gguf_kv_arr_i64(const b2_gguf* g, int64_t i, int64_t j, int64_t* out);
+int b2_gguf_tensor_info(const b2_gguf* g, int64_t i, b2_tensor_info* out);
+int64_t b2_gguf_find_tensor(const b2_gguf* g, const char* name);
+/* host pointer to the raw bytes of tensor i inside the mapping */
+const void* b2_gguf_tensor_data(const b2_gguf* g, int64_t i);
+
+/* ---------------------------------------------------------------------------------------------
+ * Device memory helpers for FFI callers without a CUDA binding of their own
+ * ------------------------------------------------------------------------------------------- */
+int b2_dev_malloc(void** out, size_t bytes);
+int b2_dev_free(void* p);
+int b2_dev_memset(void* p, int value, size_t bytes, void* stream);
+int b2_memcpy_h2d(void* dst_dev, const void* src_host, size_t bytes, void* stream);
+int b2_memcpy_d2h(void* dst_host, const void* src_dev, size_t bytes, void* stream);
+int b2_stream_sync(void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Block-level operators on DEVICE pointers
+ * ------------------------------------------------------------------------------------------- */
+/* bytes of one row of k elements of `type`, or negative if k is not a whole number of blocks */
+int64_t b2_row_bytes(int type, int64_t k);
+
+/* Dequantise n elements to fp32, bit-exact with ggml's dequantize_row_* (SURVEY 8a rows a8/a10;
+ * block math gguf-py quants.py:395-401,475-522,525-549,552-572).  src_dev needs 2-byte alignment only. */
+int b2_dequantize(int type, const void* src_dev, float* dst_dev, int64_t n, void* stream);
+/* same, host buffers in and out (upload, kernel, download) */
+int b2_dequantize_host(int type, const void* src_host, float* dst_host, int64_t n);
+
+/* y[N] = W[N x K] . x[K]   ("quantised matmul"; ggml_compute_forward_mul_mat with
+ * n_tokens = 1).  W: N rows of K elements in `type` blocks, exactly as in the GGUF.  x, y fp32.  The
+ * activation row is quantised on the fly to Q8_K (K-quants) or Q8_0 (Q8_0 weights) and the dot product
+ * is integer, as on ggml's CPU path.  B > 1 runs B independent columns: x is [B][K], y is [B][N]. */
+int b2_gemv(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int B, void* stream);
+
+/* y = x * rsqrt(mean(x^2) + eps) * w  over rows of length n   (row a11, ggml rms_norm + mul) */
+int b2_rmsnorm(const float* x_dev, const float* w_dev, float* y_dev, int64_t n, int64_t rows, float eps, void* stream);
+
+/* Rotary embedding in place on x[n_heads][head_dim] for one position (row a13, ggml rope).
+ * mode 0 = adjacent pairs (`llama`), 2 = NEOX pairs (`qwen2`).  freq_factors_dev may be NULL. */
+int b2_rope(float* x_dev, int n_heads, int head_dim, int n_dims, int mode, int pos, float freq_base,
+            const float* freq_factors_dev, void* stream);
+
+/* Single-query attention over an fp16 KV cache (row a14).  q: [n_head][head_dim] fp32;
+ * k_cache, v_cache: [n_kv][n_ctx][head_dim] fp16; attends positions [0, n_tokens).  out: [n_head][head_dim].
+ * scratch_dev: b2_attn_scratch_bytes(n_head, head_dim, n_tokens) bytes of device memory, zeroed once by the caller. */
+size_t b2_attn_scratch_bytes(int n_head, int head_dim, int n_tokens);
+int b2_attn_decode(const float* q_dev, const void* k_cache_dev, const void* v_cache_dev, float* out_dev,
+                   int n_head, int n_kv, int head_dim, int n_ctx, int n_tokens, void* scratch_dev, void* stream);
+
+/* argmax over n logits, lowest index wins ties (row a16 greedy).  scratch_dev: b2_argmax_scratch_bytes(n),
+ * zeroed once by the caller. */
+size_t b2_argmax_scratch_bytes(int64_t n);
+int b2_sample_greedy(const float* logits_dev, int64_t n, int32_t* token_out_dev, void* scratch_dev, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Model + decode context  (rows a8-a16 end to end; replaces llama_model_load / llama_decode inside
+ * the llama-server the chart launches)
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+    int32_t arch;       /* 0 = llama, 1 = qwen2 */
+    int32_t n_layer, d_model, d_ff, n_head, n_kv, head_dim, vocab, n_ctx_train, rope_dim;
+    float eps, rope_base;
+    int32_t bos_id, eos_id, eot_id;
+    int32_t tied;           /* output.weight absent -> token_embd used as lm_head */
+    uint64_t weight_bytes;  /* bytes resident in HBM */
+    uint64_t stream_bytes;  /* bytes one decode step reads (SURVEY 8d W_stream) */
+} b2_model_info;
+
+/* Upload the GGUF's tensor data to `device` unmodified.  tp_rank/tp_size: 0/1 for a full replica. */
+int b2_model_load(const char* path, int device, int tp_rank, int tp_size, b2_model** out);
+void b2_model_free(b2_model* m);
+int b2_model_get_info(const b2_model* m, b2_model_info* out);
+const b2_gguf* b2_model_gguf(const b2_model* m);
+/* device pointer + info of a named tensor (for tests that check the upload is byte-identical) */
+int b2_model_tensor(const b2_model* m, const char* name, const void** dev_ptr, b2_tensor_info* info);
+
+/* n_ctx: KV-cache capacity in tokens (0 = min(model training context, 8192)). */
+int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out);
+void b2_ctx_free(b2_ctx* c);
+int b2_ctx_n_ctx(const b2_ctx* c);
+/* forget the sequence (positions restart at 0) */
+int b2_ctx_reset(b2_ctx* c);
+
+/* Feed n tokens at positions pos0 .. pos0+n-1 (host array).  If logits_out_host != NULL it receives the
+ * vocab-sized fp32 logits after the LAST token.  If next_token_out != NULL it receives the greedy
+ * continuation.  Host buffers; the H2D / D2H copies are part of the call. */
+int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, float* logits_out_host, int32_t* next_token_out);
+
+/* Greedy generation entirely on the device: starting from the state left by b2_ctx_decode (whose greedy
+ * token t0 the caller already has), run n_steps decode steps, each consuming the previous argmax without a
+ * host round trip, then copy the n_steps newly produced token ids t1..tn to tokens_out_host. */
+int b2_ctx_generate_greedy(b2_ctx* c, int n_steps, int32_t* tokens_out_host);
+
+/* Same loop without the final copy or synchronisation, for device-side timing: enqueue n_steps steps on
+ * the context's stream.  b2_ctx_stream() returns that cudaStream_t so callers can record events on it. */
+int b2_ctx_enqueue_steps(b2_ctx* c, int n_steps);
+void* b2_ctx_stream(b2_ctx* c);
+int b2_ctx_sync(b2_ctx* c);
+/* read back state for parity tests: hidden state after the last layer [d_model], last logits [vocab] */
+int b2_ctx_get_hidden(b2_ctx* c, float* out_host);
+int b2_ctx_get_logits(b2_ctx* c, float* out_host);
+int b2_ctx_pos(const b2_ctx* c);
+/* kernels launched per decode step (for bench.py's gpu_launches) */
+int b2_ctx_launches_per_step(const b2_ctx* c);
+
+/* ---------------------------------------------------------------------------------------------
+ * Measurement helpers (no counterpart on the reference's request path; the reference's own tool for
+ * this is llama-bench).  Both time with CUDA events recorded on the context's stream.
+ * ------------------------------------------------------------------------------------------- */
+/* n_steps greedy decode steps (as b2_ctx_enqueue_steps) -> elapsed milliseconds */
+int b2_ctx_time_steps(b2_ctx* c, int n_steps, float* ms_out);
+/* only the mat-vec launches of a decode step, `reps` times back to back: elapsed milliseconds, the weight
+ * bytes those launches read per repetition and their number.  Leaves the context reset to position 0. */
+int b2_ctx_time_matvec_only(b2_ctx* c, int reps, float* ms_out, uint64_t* bytes_per_rep_out, int* launches_per_rep_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2_H */

@@ -1,0 +1,103 @@
+// device_utils.cuh -- sm_100a device helpers: mbarrier, 1-D bulk async copy (TMA unit), programmatic
+// dependent launch, packed-int8 dot, alignment-tolerant shared-memory loads.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2 {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- mbarrier (shared::cta) ---------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    // make barrier initialisation visible to the async proxy (the TMA unit completes transactions on it)
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug must not hang the GPU (a hung box is a lost box).  ~2^26 probes of a
+// HW-sleeping try_wait is seconds; on expiry the kernel traps and the launch reports an error.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    for (uint32_t i = 0; i < (1u << 26); i++)
+        if (mbar_try_wait(bar, parity)) return;
+    asm volatile("trap;");
+}
+
+// ---- 1-D bulk async copy global -> shared, completion on an mbarrier (SASS: UBLKCP) ---------------
+// dst and src 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// ---- programmatic dependent launch ---------------------------------------------------------------
+// wait: block until every grid this launch depends on has completed and its writes are visible
+// (no-op for an ordinary launch).  launch_dependents: allow the next grid in the stream to start
+// its pre-wait part (weight prefetch) while this one is still running.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// ---- named barrier for a subset of the CTA's warps ----------------------------------------------
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// ---- arithmetic ---------------------------------------------------------------------------------
+__device__ __forceinline__ int dp4a_ss(uint32_t a, uint32_t b, int c) { return __dp4a((int)a, (int)b, c); }
+
+__device__ __forceinline__ float h2f_bits(uint32_t h16) { return __half2float(__ushort_as_half((unsigned short)h16)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// 16 bytes from shared memory at an address that is only 2-byte aligned: five aligned words and a
+// funnel shift by 0 or 16 bits.  (Q6_K blocks are 210 bytes and Q8_0 blocks 34, so inside a row they
+// sit at every even offset.)
+__device__ __forceinline__ uint4 lds16_a2(const uint8_t* p) {
+    const uint32_t a = smem_u32(p);
+    const uint32_t sh = (a & 2u) << 3;
+    const uint32_t* w = (const uint32_t*)(p - (a & 3u));
+    const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = w[4];
+    uint4 r;
+    r.x = __funnelshift_r(w0, w1, sh);
+    r.y = __funnelshift_r(w1, w2, sh);
+    r.z = __funnelshift_r(w2, w3, sh);
+    r.w = __funnelshift_r(w3, w4, sh);
+    return r;
+}
+// same for global memory (used by the dequantise kernels, which read blocks in place)
+__device__ __forceinline__ uint32_t ldg32_a2(const uint8_t* p) {
+    const uint16_t* h = (const uint16_t*)p;
+    return (uint32_t)h[0] | ((uint32_t)h[1] << 16);
+}
+
+}  // namespace b2

@@ -1,0 +1,720 @@
+// model.cu -- GGUF -> HBM upload and the decode step (SURVEY 8a rows a8-a16 end to end).
+//
+// Replaces, inside the process the chart launches (`llama-server --model P`,
+// ramalama-models/helm-chart/templates/model-deployments.yaml:26-35), llama.cpp's model load and
+// llama_decode for one token: embedding row -> L x {RMSNorm+QKV+RoPE+KV-write, attention,
+// O-proj+residual, RMSNorm+gate/up+SwiGLU, down-proj+residual} -> RMSNorm+lm_head -> argmax.
+//
+// HBM layout: the GGUF data section is uploaded as ONE allocation, byte for byte, at the same
+// relative offsets (so every tensor keeps its 32-byte file alignment and nothing is repacked); the
+// KV cache is fp16 [layer][kv head][position][head_dim]; activations are a handful of fp32 vectors.
+// A decode step is 5 kernels per layer + 3, captured once into a CUDA graph with programmatic
+// dependent launch edges so each mat-vec prefetches its weights under the previous kernel's tail.
+// Token id, position and step counter live on the device: greedy generation replays the graph with
+// no host round trip.
+#include "model.h"
+
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+
+#include "gemv.cuh"
+#include "ops.h"
+
+using namespace b2;
+
+namespace {
+
+bool env_flag(const char* name) {
+    const char* v = getenv(name);
+    return v && *v && strcmp(v, "0") != 0;
+}
+
+int find_w(b2_model* m, const std::string& name, b2_model::W* w, bool required) {
+    const int64_t i = m->g->find_tensor(name);
+    if (i < 0) {
+        if (!required) return 1;
+        set_error("model: tensor '%s' missing from '%s'", name.c_str(), m->g->path.c_str());
+        return B2_EFORMAT;
+    }
+    const auto& t = m->g->tensors[i];
+    w->p = m->d_data + t.offset;
+    w->type = (int)t.type;
+    w->cols = (int64_t)t.dims[0];
+    w->rows = t.n_dims > 1 ? (int64_t)t.dims[1] : 1;
+    return 0;
+}
+
+int check_matrix(const b2_model::W& w, const char* what, int64_t rows, int64_t cols) {
+    if (w.rows != rows || w.cols != cols) {
+        set_error("model: %s has shape [%lld x %lld], expected [%lld x %lld]", what, (long long)w.rows, (long long)w.cols,
+                  (long long)rows, (long long)cols);
+        return B2_EFORMAT;
+    }
+    if (gemv_act_for_type(w.type) < 0) {
+        const TypeTraits* t = type_traits(w.type);
+        set_error("model: %s is stored as ggml type %d (%s); this build computes Q4_K, Q5_K, Q6_K and Q8_0 matrices", what, w.type,
+                  t ? t->name : "unknown");
+        return B2_EUNSUP;
+    }
+    return 0;
+}
+
+int check_vec(const b2_model::W& w, const char* what, int64_t n) {
+    if (w.type != B2_TYPE_F32 || w.cols * w.rows != n) {
+        set_error("model: %s must be F32[%lld]", what, (long long)n);
+        return B2_EFORMAT;
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int b2_model_load(const char* path, int device, int tp_rank, int tp_size, b2_model** out) {
+    if (!out || !path) {
+        set_error("b2_model_load: NULL argument");
+        return B2_EINVAL;
+    }
+    *out = nullptr;
+    if (tp_size != 1 || tp_rank != 0) {
+        set_error("b2_model_load: tensor parallelism (tp_size=%d) is not built yet; load a full replica (tp 0/1)", tp_size);
+        return B2_EUNSUP;
+    }
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
+        cudaGetLastError();
+        set_error("b2_model_load: no CUDA device visible; this library has no CPU fallback");
+        return B2_ECUDA;
+    }
+    if (device < 0 || device >= n_dev) {
+        set_error("b2_model_load: device %d out of range (0..%d)", device, n_dev - 1);
+        return B2_EINVAL;
+    }
+    B2_CUDA_CHECK(cudaSetDevice(device));
+    Gguf* gp = nullptr;
+    int rc = Gguf::open(path, &gp);
+    if (rc) return rc;
+    std::unique_ptr<b2_model> m(new b2_model());
+    m->g.reset(gp);
+    m->gguf_handle.g = gp;
+    m->gguf_handle.owned = false;
+    m->device = device;
+    Gguf& g = *gp;
+
+    std::string arch;
+    if (!g.get_str("general.architecture", &arch)) {
+        set_error("model: general.architecture missing");
+        return B2_EFORMAT;
+    }
+    b2_model_info& I = m->info;
+    if (arch == "llama") I.arch = 0;
+    else if (arch == "qwen2") I.arch = 1;
+    else {
+        set_error("model: architecture '%s' is not supported (llama, qwen2)", arch.c_str());
+        return B2_EUNSUP;
+    }
+    uint32_t u;
+    auto need_u32 = [&](const std::string& k, int32_t* dst) -> int {
+        if (!g.get_u32(arch + "." + k, &u)) {
+            set_error("model: key %s.%s missing", arch.c_str(), k.c_str());
+            return B2_EFORMAT;
+        }
+        *dst = (int32_t)u;
+        return 0;
+    };
+    if ((rc = need_u32("block_count", &I.n_layer))) return rc;
+    if ((rc = need_u32("embedding_length", &I.d_model))) return rc;
+    if ((rc = need_u32("feed_forward_length", &I.d_ff))) return rc;
+    if ((rc = need_u32("attention.head_count", &I.n_head))) return rc;
+    I.n_kv = g.get_u32(arch + ".attention.head_count_kv", &u) ? (int32_t)u : I.n_head;
+    if (I.n_head <= 0 || I.n_kv <= 0 || I.n_layer <= 0 || I.d_model <= 0 || I.d_ff <= 0) {
+        set_error("model: non-positive hyper-parameter");
+        return B2_EFORMAT;
+    }
+    I.head_dim = g.get_u32(arch + ".attention.key_length", &u) ? (int32_t)u : I.d_model / I.n_head;
+    I.rope_dim = g.get_u32(arch + ".rope.dimension_count", &u) ? (int32_t)u : I.head_dim;
+    I.n_ctx_train = g.get_u32(arch + ".context_length", &u) ? (int32_t)u : 2048;
+    if (!g.get_f32(arch + ".attention.layer_norm_rms_epsilon", &I.eps)) I.eps = 1e-5f;
+    if (!g.get_f32(arch + ".rope.freq_base", &I.rope_base)) I.rope_base = 10000.0f;
+    I.bos_id = g.get_u32("tokenizer.ggml.bos_token_id", &u) ? (int32_t)u : -1;
+    I.eos_id = g.get_u32("tokenizer.ggml.eos_token_id", &u) ? (int32_t)u : -1;
+    I.eot_id = g.get_u32("tokenizer.ggml.eot_token_id", &u) ? (int32_t)u : -1;
+    if (I.n_head % I.n_kv || I.rope_dim > I.head_dim || (I.rope_dim & 1)) {
+        set_error("model: inconsistent head configuration");
+        return B2_EFORMAT;
+    }
+
+    // ---- upload the data section as-is: pinned double-buffered staging from the mmap ----
+    const size_t guard = 256;
+    B2_CUDA_CHECK(cudaMalloc((void**)&m->d_alloc, g.data_size + 2 * guard));
+    m->d_data = m->d_alloc + guard;
+    B2_CUDA_CHECK(cudaMemset(m->d_alloc, 0, guard));
+    B2_CUDA_CHECK(cudaMemset(m->d_data + g.data_size, 0, guard));
+    {
+        const size_t CH = 64u << 20;
+        uint8_t* pin[2] = {nullptr, nullptr};
+        cudaEvent_t ev[2];
+        cudaStream_t st;
+        B2_CUDA_CHECK(cudaStreamCreate(&st));
+        for (int i = 0; i < 2; i++) {
+            B2_CUDA_CHECK(cudaMallocHost((void**)&pin[i], CH));
+            B2_CUDA_CHECK(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+        }
+        const uint8_t* src = g.map + g.data_offset;
+        int b = 0;
+        for (size_t off = 0; off < g.data_size; off += CH, b ^= 1) {
+            const size_t n = std::min(CH, (size_t)g.data_size - off);
+            B2_CUDA_CHECK(cudaEventSynchronize(ev[b]));
+            memcpy(pin[b], src + off, n);
+            B2_CUDA_CHECK(cudaMemcpyAsync(m->d_data + off, pin[b], n, cudaMemcpyHostToDevice, st));
+            B2_CUDA_CHECK(cudaEventRecord(ev[b], st));
+        }
+        B2_CUDA_CHECK(cudaStreamSynchronize(st));
+        for (int i = 0; i < 2; i++) {
+            cudaFreeHost(pin[i]);
+            cudaEventDestroy(ev[i]);
+        }
+        cudaStreamDestroy(st);
+    }
+    I.weight_bytes = g.data_size;
+
+    // ---- tensor table ----
+    if ((rc = find_w(m.get(), "token_embd.weight", &m->tok_embd, true)) < 0) return rc;
+    if ((rc = find_w(m.get(), "output_norm.weight", &m->output_norm, true)) < 0) return rc;
+    rc = find_w(m.get(), "output.weight", &m->output, false);
+    if (rc < 0) return rc;
+    I.tied = rc == 1;
+    if (I.tied) m->output = m->tok_embd;
+    I.vocab = (int32_t)m->tok_embd.rows;
+    if (m->tok_embd.cols != I.d_model || !type_traits(m->tok_embd.type)) {
+        set_error("model: token_embd.weight has an unsupported shape or type");
+        return B2_EUNSUP;
+    }
+    if ((rc = check_matrix(m->output, "output.weight", I.vocab, I.d_model))) return rc;
+    if ((rc = check_vec(m->output_norm, "output_norm.weight", I.d_model))) return rc;
+    {
+        b2_model::W rf;
+        rc = find_w(m.get(), "rope_freqs.weight", &rf, false);
+        if (rc < 0) return rc;
+        if (rc == 0) {
+            if ((rc = check_vec(rf, "rope_freqs.weight", I.rope_dim / 2))) return rc;
+            m->rope_freqs = (const float*)rf.p;
+            const int64_t ti = g.find_tensor("rope_freqs.weight");
+            const float* hp = (const float*)g.tensor_data(ti);
+            m->rope_freqs_host.assign(hp, hp + I.rope_dim / 2);
+        }
+    }
+    const int64_t qd = (int64_t)I.n_head * I.head_dim, kvd = (int64_t)I.n_kv * I.head_dim;
+    uint64_t stream = m->output.rows * (uint64_t)row_bytes(m->output.type, m->output.cols) + (uint64_t)I.d_model * 4;
+    m->layers.resize(I.n_layer);
+    for (int il = 0; il < I.n_layer; il++) {
+        auto& L = m->layers[il];
+        const std::string p = "blk." + std::to_string(il) + ".";
+        struct { const char* n; b2_model::W* w; int64_t r, c; } mats[] = {
+            {"attn_q.weight", &L.wq, qd, I.d_model},   {"attn_k.weight", &L.wk, kvd, I.d_model},
+            {"attn_v.weight", &L.wv, kvd, I.d_model},  {"attn_output.weight", &L.wo, I.d_model, qd},
+            {"ffn_gate.weight", &L.gate, I.d_ff, I.d_model}, {"ffn_up.weight", &L.up, I.d_ff, I.d_model},
+            {"ffn_down.weight", &L.down, I.d_model, I.d_ff}};
+        for (auto& e : mats) {
+            if ((rc = find_w(m.get(), p + e.n, e.w, true)) < 0) return rc;
+            if ((rc = check_matrix(*e.w, (p + e.n).c_str(), e.r, e.c))) return rc;
+            stream += (uint64_t)e.w->rows * row_bytes(e.w->type, e.w->cols);
+        }
+        if ((rc = find_w(m.get(), p + "attn_norm.weight", &L.attn_norm, true)) < 0) return rc;
+        if ((rc = find_w(m.get(), p + "ffn_norm.weight", &L.ffn_norm, true)) < 0) return rc;
+        if ((rc = check_vec(L.attn_norm, "attn_norm.weight", I.d_model))) return rc;
+        if ((rc = check_vec(L.ffn_norm, "ffn_norm.weight", I.d_model))) return rc;
+        stream += 2ull * I.d_model * 4;
+        struct { const char* n; const float** b; int64_t len; } biases[] = {
+            {"attn_q.bias", &L.bq, qd}, {"attn_k.bias", &L.bk, kvd}, {"attn_v.bias", &L.bv, kvd}};
+        for (auto& e : biases) {
+            b2_model::W bw;
+            rc = find_w(m.get(), p + e.n, &bw, false);
+            if (rc < 0) return rc;
+            if (rc == 0) {
+                if ((rc = check_vec(bw, e.n, e.len))) return rc;
+                *e.b = (const float*)bw.p;
+                stream += (uint64_t)e.len * 4;
+            }
+        }
+    }
+    I.stream_bytes = stream;
+    *out = m.release();
+    return 0;
+}
+
+extern "C" void b2_model_free(b2_model* m) {
+    if (!m) return;
+    if (m->d_alloc) cudaFree(m->d_alloc);
+    delete m;
+}
+
+extern "C" int b2_model_get_info(const b2_model* m, b2_model_info* out) {
+    if (!m || !out) return B2_EINVAL;
+    *out = m->info;
+    return 0;
+}
+extern "C" const b2_gguf* b2_model_gguf(const b2_model* m) { return m ? &m->gguf_handle : nullptr; }
+
+extern "C" int b2_model_tensor(const b2_model* m, const char* name, const void** dev_ptr, b2_tensor_info* info) {
+    if (!m || !name) return B2_EINVAL;
+    const int64_t i = m->g->find_tensor(name);
+    if (i < 0) {
+        set_error("b2_model_tensor: no tensor '%s'", name);
+        return B2_ENOTFOUND;
+    }
+    const auto& t = m->g->tensors[i];
+    if (dev_ptr) *dev_ptr = m->d_data + t.offset;
+    if (info) {
+        info->name = t.name.c_str();
+        info->n_dims = t.n_dims;
+        for (int d = 0; d < 4; d++) info->dims[d] = t.dims[d];
+        info->type = t.type;
+        info->offset = t.offset;
+        info->n_bytes = t.n_bytes;
+    }
+    return 0;
+}
+
+// -------------------------------------------------------------------------------------------------
+// decode context
+// -------------------------------------------------------------------------------------------------
+namespace {
+
+template <typename T>
+int dmalloc(T** p, size_t n) {
+    B2_CUDA_CHECK(cudaMalloc((void**)p, n * sizeof(T)));
+    return 0;
+}
+
+void seg_matrix(GemvSeg& s, const b2_model::W& w, int pairing, int epi) {
+    s = GemvSeg{};
+    s.wa = w.p;
+    s.type = w.type;
+    s.pairing = pairing;
+    s.epi = epi;
+    s.n_rows = (int)w.rows;
+    s.n_pairs = pairing == PAIR_SPLIT ? (int)w.rows : (int)((w.rows + 1) / 2);
+}
+
+// enqueue one decode step (token and position are read from device memory)
+int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false) {
+    b2_model* m = c->m;
+    const b2_model_info& I = m->info;
+    int rc;
+    int launches = 0;
+    const int64_t kv_layer = (int64_t)I.n_kv * c->n_ctx * I.head_dim;
+    const int rope_pairing = I.arch == 1 ? PAIR_NEOX : PAIR_ADJ;
+    auto common = [&](GemvArgs& a, const float* x, const float* norm_w, int K) {
+        a = GemvArgs{};
+        a.x = x;
+        a.norm_w = norm_w;
+        a.prologue = norm_w ? PRO_NORM : PRO_PLAIN;
+        a.eps = I.eps;
+        a.K = K;
+        a.pos_ptr = c->d_pos;
+        a.rope_tab = c->rope_tab;
+        a.rope_half = I.rope_dim / 2;
+    };
+    auto run = [&](GemvArgs& a, int act) -> int {
+        if ((rc = gemv_finalize(a, act))) return rc;
+        if ((rc = launch_gemv(a, act, st, pdl))) return rc;
+        launches++;
+        return 0;
+    };
+    // the first kernel of a step depends on a memcpy / the previous graph launch: ordinary dependency
+    if (!matvec_only) {
+        if ((rc = launch_embed(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, c->d_tok, c->x,
+                               st, false)))
+            return rc;
+        launches++;
+    }
+    for (int il = 0; il < I.n_layer; il++) {
+        const auto& L = m->layers[il];
+        __half* kc = c->k_cache + il * kv_layer;
+        __half* vc = c->v_cache + il * kv_layer;
+        // --- attention block: RMSNorm -> Q,K,V (+bias) -> RoPE -> cache ---
+        GemvSeg sq, sk, sv;
+        seg_matrix(sq, L.wq, rope_pairing, EPI_ROPE_Q);
+        sq.out = c->q;
+        sq.bias = L.bq;
+        sq.head_dim = I.head_dim;
+        seg_matrix(sk, L.wk, rope_pairing, EPI_ROPE_K);
+        sk.cache = kc;
+        sk.bias = L.bk;
+        sk.head_dim = I.head_dim;
+        sk.n_ctx = c->n_ctx;
+        seg_matrix(sv, L.wv, PAIR_ADJ, EPI_V);
+        sv.cache = vc;
+        sv.bias = L.bv;
+        sv.head_dim = I.head_dim;
+        sv.n_ctx = c->n_ctx;
+        const int aq = gemv_act_for_type(L.wq.type), ak = gemv_act_for_type(L.wk.type), av = gemv_act_for_type(L.wv.type);
+        GemvArgs a;
+        if (aq == ak && ak == av) {
+            common(a, c->x, (const float*)L.attn_norm.p, I.d_model);
+            a.seg[0] = sq; a.seg[1] = sk; a.seg[2] = sv;
+            a.n_seg = 3;
+            if ((rc = run(a, aq))) return rc;
+        } else {
+            const GemvSeg* segs[3] = {&sq, &sk, &sv};
+            const int acts[3] = {aq, ak, av};
+            for (int i = 0; i < 3; i++) {
+                common(a, c->x, (const float*)L.attn_norm.p, I.d_model);
+                a.seg[0] = *segs[i];
+                a.n_seg = 1;
+                if ((rc = run(a, acts[i]))) return rc;
+            }
+        }
+        if (!matvec_only) {
+            if ((rc = launch_attn_decode(c->q, kc, vc, c->attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, c->d_pos, 0, c->max_splits,
+                                         c->attn_scratch, st, pdl)))
+                return rc;
+            launches++;
+        }
+        // --- attention output projection + residual ---
+        common(a, c->attn_out, nullptr, I.n_head * I.head_dim);
+        seg_matrix(a.seg[0], L.wo, PAIR_ADJ, EPI_RESID);
+        a.seg[0].out = c->x;
+        a.n_seg = 1;
+        if ((rc = run(a, gemv_act_for_type(L.wo.type)))) return rc;
+        // --- FFN: RMSNorm -> gate, up -> SwiGLU ---
+        const int ag = gemv_act_for_type(L.gate.type), au = gemv_act_for_type(L.up.type);
+        if (ag == au && L.gate.type == L.up.type) {
+            common(a, c->x, (const float*)L.ffn_norm.p, I.d_model);
+            seg_matrix(a.seg[0], L.gate, PAIR_SPLIT, EPI_SWIGLU);
+            a.seg[0].wb = L.up.p;
+            a.seg[0].out = c->h;
+            a.n_seg = 1;
+            if ((rc = run(a, ag))) return rc;
+        } else {
+            set_error("model: ffn_gate and ffn_up of layer %d have different types (%d, %d): unsupported", il, L.gate.type, L.up.type);
+            return B2_EUNSUP;
+        }
+        // --- FFN down projection + residual ---
+        common(a, c->h, nullptr, I.d_ff);
+        seg_matrix(a.seg[0], L.down, PAIR_ADJ, EPI_RESID);
+        a.seg[0].out = c->x;
+        a.n_seg = 1;
+        if ((rc = run(a, gemv_act_for_type(L.down.type)))) return rc;
+    }
+    // --- final norm + lm_head ---
+    GemvArgs a;
+    common(a, c->x, (const float*)m->output_norm.p, I.d_model);
+    seg_matrix(a.seg[0], m->output, PAIR_ADJ, EPI_STORE);
+    a.seg[0].out = c->logits;
+    a.n_seg = 1;
+    if ((rc = run(a, gemv_act_for_type(m->output.type)))) return rc;
+    if (matvec_only) {
+        c->matvec_launches = launches;
+        return 0;
+    }
+    if ((rc = launch_argmax(c->logits, I.vocab, c->d_tok, c->argmax_scratch, c->d_pos, c->d_step, c->d_out, c->out_cap, st, pdl))) return rc;
+    launches++;
+    c->launches_per_step = launches;
+    return 0;
+}
+
+int build_graph(b2_ctx* c) {
+    if (!c->use_graph) return 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        const bool pdl = c->use_pdl && attempt == 0;
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        cudaError_t e = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal);
+        int rc = 0;
+        if (e == cudaSuccess) {
+            rc = enqueue_step(c, c->stream, pdl);
+            e = cudaStreamEndCapture(c->stream, &graph);
+        }
+        if (e == cudaSuccess && rc == 0) e = cudaGraphInstantiate(&exec, graph, 0);
+        if (e == cudaSuccess && rc == 0) {
+            c->graph = graph;
+            c->exec = exec;
+            c->use_pdl = pdl;
+            return 0;
+        }
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        if (rc) return rc;  // argument errors do not go away without PDL
+        if (!pdl) {
+            set_error("ctx: CUDA graph capture failed: %s", cudaGetErrorString(e));
+            return B2_ECUDA;
+        }
+        fprintf(stderr, "b2: graph capture with programmatic dependent launch failed (%s); retrying without\n", cudaGetErrorString(e));
+    }
+    return B2_ECUDA;
+}
+
+int run_step(b2_ctx* c) {
+    if (c->exec) {
+        B2_CUDA_CHECK(cudaGraphLaunch(c->exec, c->stream));
+        return 0;
+    }
+    return enqueue_step(c, c->stream, c->use_pdl);
+}
+
+}  // namespace
+
+extern "C" int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out) {
+    if (!m || !out) {
+        set_error("b2_ctx_create: NULL argument");
+        return B2_EINVAL;
+    }
+    *out = nullptr;
+    const b2_model_info& I = m->info;
+    if (n_ctx <= 0) {
+        const char* e = getenv("B2_CTX_SIZE");
+        n_ctx = e ? atoi(e) : 0;
+        if (n_ctx <= 0) n_ctx = I.n_ctx_train < 8192 ? I.n_ctx_train : 8192;
+    }
+    if (n_ctx > I.n_ctx_train && I.n_ctx_train > 0 && !env_flag("B2_ALLOW_CTX_EXTEND")) n_ctx = I.n_ctx_train;
+    B2_CUDA_CHECK(cudaSetDevice(m->device));
+    std::unique_ptr<b2_ctx> c(new b2_ctx());
+    c->m = m;
+    c->n_ctx = n_ctx;
+    c->use_graph = !env_flag("B2_NO_GRAPH");
+    c->use_pdl = !env_flag("B2_NO_PDL");
+    B2_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    int rc;
+    const size_t kv_elems = (size_t)I.n_layer * I.n_kv * n_ctx * I.head_dim;
+    if ((rc = dmalloc(&c->k_cache, kv_elems))) return rc;
+    if ((rc = dmalloc(&c->v_cache, kv_elems))) return rc;
+    B2_CUDA_CHECK(cudaMemsetAsync(c->k_cache, 0, kv_elems * sizeof(__half), c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->v_cache, 0, kv_elems * sizeof(__half), c->stream));
+    if ((rc = dmalloc(&c->x, I.d_model))) return rc;
+    if ((rc = dmalloc(&c->q, (size_t)I.n_head * I.head_dim))) return rc;
+    if ((rc = dmalloc(&c->attn_out, (size_t)I.n_head * I.head_dim))) return rc;
+    if ((rc = dmalloc(&c->h, I.d_ff))) return rc;
+    if ((rc = dmalloc(&c->logits, I.vocab))) return rc;
+    c->out_cap = 4096;
+    c->prompt_cap = 4096;
+    if ((rc = dmalloc(&c->d_tok, 1))) return rc;
+    if ((rc = dmalloc(&c->d_pos, 1))) return rc;
+    if ((rc = dmalloc(&c->d_step, 1))) return rc;
+    if ((rc = dmalloc(&c->d_out, c->out_cap))) return rc;
+    if ((rc = dmalloc(&c->d_prompt, c->prompt_cap))) return rc;
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_tok, 0, 4, c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_pos, 0, 4, c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_step, 0, 4, c->stream));
+    c->h_pin_cap = 4096;
+    B2_CUDA_CHECK(cudaMallocHost((void**)&c->h_pin, c->h_pin_cap * sizeof(int32_t)));
+    c->max_splits = attn_max_splits(n_ctx);
+    const size_t asz = attn_scratch_bytes(I.n_head, I.head_dim, c->max_splits);
+    B2_CUDA_CHECK(cudaMalloc(&c->attn_scratch, asz));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->attn_scratch, 0, asz, c->stream));
+    B2_CUDA_CHECK(cudaMalloc(&c->argmax_scratch, argmax_scratch_bytes()));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->argmax_scratch, 0, argmax_scratch_bytes(), c->stream));
+    // RoPE table built on the host the way ggml builds its per-position cache (ggml_rope_cache_init):
+    // theta_0 = pos, theta_{i+1} = theta_i * base^(-2/n_dims) in fp32, angle = theta / freq_factor,
+    // cosf/sinf from the host libm -- the same libm the CPU reference would call.
+    {
+        const int half = I.rope_dim / 2;
+        std::vector<float2> tab((size_t)n_ctx * half);
+        const float theta_scale = powf(I.rope_base, -2.0f / (float)I.rope_dim);
+        for (int p = 0; p < n_ctx; p++) {
+            float theta = (float)p;
+            for (int i = 0; i < half; i++) {
+                const float ff = m->rope_freqs_host.empty() ? 1.0f : m->rope_freqs_host[i];
+                const float t = theta / ff;
+                tab[(size_t)p * half + i] = make_float2(cosf(t), sinf(t));
+                theta *= theta_scale;
+            }
+        }
+        if ((rc = dmalloc(&c->rope_tab, tab.size()))) return rc;
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->rope_tab, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
+        B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    }
+    // run one eager step so lazy module loading and attribute setting happen outside capture
+    if ((rc = enqueue_step(c.get(), c->stream, false))) return rc;
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_pos, 0, 4, c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_step, 0, 4, c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_tok, 0, 4, c->stream));
+    if ((rc = build_graph(c.get()))) return rc;
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    c->pos = 0;
+    *out = c.release();
+    return 0;
+}
+
+extern "C" void b2_ctx_free(b2_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->m->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->exec) cudaGraphExecDestroy(c->exec);
+    if (c->graph) cudaGraphDestroy(c->graph);
+    void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
+                    c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (c->h_pin) cudaFreeHost(c->h_pin);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+extern "C" int b2_ctx_n_ctx(const b2_ctx* c) { return c ? c->n_ctx : B2_EINVAL; }
+extern "C" int b2_ctx_pos(const b2_ctx* c) { return c ? c->pos : B2_EINVAL; }
+extern "C" int b2_ctx_launches_per_step(const b2_ctx* c) { return c ? c->launches_per_step : B2_EINVAL; }
+extern "C" void* b2_ctx_stream(b2_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+extern "C" int b2_ctx_sync(b2_ctx* c) {
+    if (!c) return B2_EINVAL;
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+extern "C" int b2_ctx_reset(b2_ctx* c) {
+    if (!c) return B2_EINVAL;
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_pos, 0, 4, c->stream));
+    c->pos = 0;
+    return 0;
+}
+
+extern "C" int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, float* logits_out_host, int32_t* next_token_out) {
+    if (!c || !tokens || n <= 0) {
+        set_error("b2_ctx_decode: bad arguments");
+        return B2_EINVAL;
+    }
+    const b2_model_info& I = c->m->info;
+    if (pos0 < 0 || (int64_t)pos0 + n > c->n_ctx) {
+        set_error("b2_ctx_decode: positions %d..%d exceed the context size %d", pos0, pos0 + n - 1, c->n_ctx);
+        return B2_ERANGE;
+    }
+    for (int i = 0; i < n; i++)
+        if (tokens[i] < 0 || tokens[i] >= I.vocab) {
+            set_error("b2_ctx_decode: token %d at index %d is outside the vocabulary (%d)", tokens[i], i, I.vocab);
+            return B2_ERANGE;
+        }
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    int rc;
+    for (int done = 0; done < n;) {
+        const int chunk = std::min(n - done, std::min(c->prompt_cap, c->h_pin_cap - 2));
+        // pinned staging: [0] = position, [1..] = token ids
+        B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));  // staging buffer reuse
+        c->h_pin[0] = pos0 + done;
+        memcpy(c->h_pin + 1, tokens + done, (size_t)chunk * sizeof(int32_t));
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->d_pos, c->h_pin, 4, cudaMemcpyHostToDevice, c->stream));
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->d_prompt, c->h_pin + 1, (size_t)chunk * 4, cudaMemcpyHostToDevice, c->stream));
+        for (int i = 0; i < chunk; i++) {
+            B2_CUDA_CHECK(cudaMemcpyAsync(c->d_tok, c->d_prompt + i, 4, cudaMemcpyDeviceToDevice, c->stream));
+            if ((rc = run_step(c))) return rc;
+        }
+        done += chunk;
+    }
+    c->pos = pos0 + n;
+    if (logits_out_host)
+        B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->logits, (size_t)I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (next_token_out) {
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->h_pin, c->d_tok, 4, cudaMemcpyDeviceToHost, c->stream));
+        B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        *next_token_out = c->h_pin[0];
+    } else {
+        B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    }
+    return 0;
+}
+
+extern "C" int b2_ctx_enqueue_steps(b2_ctx* c, int n_steps) {
+    if (!c || n_steps < 0) return B2_EINVAL;
+    if ((int64_t)c->pos + n_steps > c->n_ctx) {
+        set_error("b2_ctx_enqueue_steps: %d steps from position %d exceed the context size %d", n_steps, c->pos, c->n_ctx);
+        return B2_ERANGE;
+    }
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    int rc;
+    for (int i = 0; i < n_steps; i++)
+        if ((rc = run_step(c))) return rc;
+    c->pos += n_steps;
+    return 0;
+}
+
+extern "C" int b2_ctx_generate_greedy(b2_ctx* c, int n_steps, int32_t* tokens_out_host) {
+    if (!c || n_steps < 0 || (n_steps && !tokens_out_host)) return B2_EINVAL;
+    int rc;
+    for (int done = 0; done < n_steps;) {
+        const int chunk = std::min(n_steps - done, std::min(c->out_cap, c->h_pin_cap));
+        B2_CUDA_CHECK(cudaMemsetAsync(c->d_step, 0, 4, c->stream));
+        if ((rc = b2_ctx_enqueue_steps(c, chunk))) return rc;
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->h_pin, c->d_out, (size_t)chunk * 4, cudaMemcpyDeviceToHost, c->stream));
+        B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        memcpy(tokens_out_host + done, c->h_pin, (size_t)chunk * 4);
+        done += chunk;
+    }
+    return 0;
+}
+
+extern "C" int b2_ctx_get_hidden(b2_ctx* c, float* out_host) {
+    if (!c || !out_host) return B2_EINVAL;
+    B2_CUDA_CHECK(cudaMemcpyAsync(out_host, c->x, (size_t)c->m->info.d_model * 4, cudaMemcpyDeviceToHost, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+extern "C" int b2_ctx_get_logits(b2_ctx* c, float* out_host) {
+    if (!c || !out_host) return B2_EINVAL;
+    B2_CUDA_CHECK(cudaMemcpyAsync(out_host, c->logits, (size_t)c->m->info.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+// ---- measurement helpers (bench.py): CUDA events on the context's own stream ----------------------
+extern "C" int b2_ctx_time_steps(b2_ctx* c, int n_steps, float* ms_out) {
+    if (!c || !ms_out || n_steps <= 0) return B2_EINVAL;
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    cudaEvent_t e0, e1;
+    B2_CUDA_CHECK(cudaEventCreate(&e0));
+    B2_CUDA_CHECK(cudaEventCreate(&e1));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    B2_CUDA_CHECK(cudaEventRecord(e0, c->stream));
+    int rc = b2_ctx_enqueue_steps(c, n_steps);
+    if (rc == 0) {
+        cudaError_t e = cudaEventRecord(e1, c->stream);
+        if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(ms_out, e0, e1);
+        if (e != cudaSuccess) {
+            set_error("b2_ctx_time_steps: %s", cudaGetErrorString(e));
+            rc = B2_ECUDA;
+        }
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return rc;
+}
+
+extern "C" int b2_ctx_time_matvec_only(b2_ctx* c, int reps, float* ms_out, uint64_t* bytes_per_rep_out, int* launches_per_rep_out) {
+    if (!c || !ms_out || reps <= 0) return B2_EINVAL;
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    cudaEvent_t e0, e1;
+    B2_CUDA_CHECK(cudaEventCreate(&e0));
+    B2_CUDA_CHECK(cudaEventCreate(&e1));
+    int rc = enqueue_step(c, c->stream, false, true);  // warm
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    B2_CUDA_CHECK(cudaEventRecord(e0, c->stream));
+    for (int i = 0; i < reps && rc == 0; i++) rc = enqueue_step(c, c->stream, false, true);
+    if (rc == 0) {
+        cudaError_t e = cudaEventRecord(e1, c->stream);
+        if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(ms_out, e0, e1);
+        if (e != cudaSuccess) {
+            set_error("b2_ctx_time_matvec_only: %s", cudaGetErrorString(e));
+            rc = B2_ECUDA;
+        }
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    // weight bytes the mat-vec launches of one step read: every matrix once (norm vectors and biases excluded)
+    if (bytes_per_rep_out) {
+        const b2_model_info& I = c->m->info;
+        uint64_t b = c->m->output.rows * (uint64_t)row_bytes(c->m->output.type, c->m->output.cols);
+        for (auto& L : c->m->layers)
+            for (const b2_model::W* w : {&L.wq, &L.wk, &L.wv, &L.wo, &L.gate, &L.up, &L.down}) b += (uint64_t)w->rows * row_bytes(w->type, w->cols);
+        (void)I;
+        *bytes_per_rep_out = b;
+    }
+    if (launches_per_rep_out) *launches_per_rep_out = c->matvec_launches;
+    // the residual epilogues ran on stale activations: put the context back to a clean sequence start
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_pos, 0, 4, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    c->pos = 0;
+    return rc;
+}

@@ -1,0 +1,51 @@
+// model.h -- weights in HBM + one decode context (internal; public surface is include/b2.h)
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <memory>
+#include <vector>
+
+#include "gguf.h"
+
+struct b2_model {
+    struct W {
+        const uint8_t* p = nullptr;  // device pointer to the raw blocks
+        int type = 0;
+        int64_t rows = 0, cols = 0;
+    };
+    struct Layer {
+        W attn_norm, wq, wk, wv, wo, ffn_norm, gate, up, down;
+        const float *bq = nullptr, *bk = nullptr, *bv = nullptr;
+    };
+    std::unique_ptr<b2::Gguf> g;
+    b2_gguf gguf_handle;   // non-owning view handed out by b2_model_gguf()
+    int device = 0;
+    uint8_t* d_alloc = nullptr;  // allocation (guard bytes both sides)
+    uint8_t* d_data = nullptr;   // image of the GGUF data section, byte for byte
+    b2_model_info info{};
+    W tok_embd, output, output_norm;
+    const float* rope_freqs = nullptr;
+    std::vector<float> rope_freqs_host;
+    std::vector<Layer> layers;
+};
+
+struct b2_ctx {
+    b2_model* m = nullptr;
+    int n_ctx = 0;
+    cudaStream_t stream = nullptr;
+    __half *k_cache = nullptr, *v_cache = nullptr;  // [layer][n_kv][n_ctx][head_dim]
+    float *x = nullptr, *q = nullptr, *attn_out = nullptr, *h = nullptr, *logits = nullptr;
+    int32_t *d_tok = nullptr, *d_pos = nullptr, *d_step = nullptr, *d_out = nullptr, *d_prompt = nullptr;
+    int out_cap = 0, prompt_cap = 0;
+    float2* rope_tab = nullptr;
+    void *attn_scratch = nullptr, *argmax_scratch = nullptr;
+    int max_splits = 1;
+    int32_t* h_pin = nullptr;  // pinned host staging (token ids in / out)
+    int h_pin_cap = 0;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    bool use_graph = true, use_pdl = true;
+    int launches_per_step = 0, matvec_launches = 0;
+    int pos = 0;
+};

@@ -1,0 +1,37 @@
+// ops.h -- host-side launchers of the CUDA kernels (internal; the public surface is include/b2.h)
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include "common.h"
+
+namespace b2 {
+
+// dequant.cu
+int launch_dequantize(int type, const void* src, float* dst, int64_t n, cudaStream_t st);
+
+// attn.cu
+constexpr int ATTN_SPLIT_TOKENS = 1024;  // tokens one CTA handles per pass (shared-memory score buffer)
+constexpr int ATTN_MAX_SPLITS = 16;
+int attn_max_splits(int n_ctx);
+size_t attn_scratch_bytes(int n_head, int head_dim, int max_splits);
+// pos_ptr != NULL: attend positions [0, *pos_ptr] (device-resident position, graph-replayable);
+// otherwise attend [0, n_tokens_imm).
+int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim,
+                       int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl);
+
+// misc.cu
+// x[d] = dequantised row *token_ptr of the embedding table (row a10)
+int launch_embed(int type, const void* table, int64_t row_bytes, int d_model, int vocab, const int32_t* token_ptr, float* x,
+                 cudaStream_t st, bool pdl);
+constexpr int ARGMAX_BLOCKS = 64;
+size_t argmax_scratch_bytes();
+// argmax over logits -> *token_out; if step_out != NULL also appends the token to step_out[*step_ptr]
+// and advances *pos_ptr / *step_ptr (the device-resident decode loop's bookkeeping)
+int launch_argmax(const float* logits, int64_t n, int32_t* token_out, void* scratch, int32_t* pos_ptr, int32_t* step_ptr,
+                  int32_t* step_out, int step_cap, cudaStream_t st, bool pdl);
+int launch_rmsnorm(const float* x, const float* w, float* y, int64_t n, int64_t rows, float eps, cudaStream_t st);
+int launch_rope(float* x, int n_heads, int head_dim, int n_dims, int mode, int pos, float freq_base, const float* freq_factors,
+                cudaStream_t st);
+
+}  // namespace b2
