@@ -193,9 +193,13 @@ int b2_ctx_generate_greedy(b2_ctx* c, int n_steps, int32_t* tokens_out_host);
 int b2_ctx_enqueue_steps(b2_ctx* c, int n_steps);
 void* b2_ctx_stream(b2_ctx* c);
 int b2_ctx_sync(b2_ctx* c);
-/* read back state for parity tests: hidden state after the last layer [d_model], last logits [vocab] */
-int b2_ctx_get_hidden(b2_ctx* c, float* out_host);
-int b2_ctx_get_logits(b2_ctx* c, float* out_host);
+/* Read back state for parity tests.  Activation buffers as the last decode step left them: the residual
+ * stream after the last layer, and the last layer's rotated query, attention output and SwiGLU output.
+ * Returns the number of floats written (cap = capacity of out_host in floats). */
+enum { B2_ACT_HIDDEN = 0, B2_ACT_Q = 1, B2_ACT_ATTN_OUT = 2, B2_ACT_FFN_H = 3, B2_ACT_LOGITS = 4 };
+int b2_ctx_get_activation(b2_ctx* c, int which, float* out_host, int64_t cap);
+/* fp16 K and V rows [n_kv * head_dim] of one layer at one position */
+int b2_ctx_get_kv(b2_ctx* c, int layer, int pos, uint16_t* k_out_host, uint16_t* v_out_host);
 int b2_ctx_pos(const b2_ctx* c);
 /* kernels launched per decode step (for bench.py's gpu_launches) */
 int b2_ctx_launches_per_step(const b2_ctx* c);

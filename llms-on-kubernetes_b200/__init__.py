@@ -97,8 +97,8 @@ SYMBOLS = {
     "b2_ctx_enqueue_steps": (_I, [_P, _I]),
     "b2_ctx_stream": (_P, [_P]),
     "b2_ctx_sync": (_I, [_P]),
-    "b2_ctx_get_hidden": (_I, [_P, _P]),
-    "b2_ctx_get_logits": (_I, [_P, _P]),
+    "b2_ctx_get_activation": (_I, [_P, _I, _P, _I64]),
+    "b2_ctx_get_kv": (_I, [_P, _I, _I, _P, _P]),
     "b2_ctx_pos": (_I, [_P]),
     "b2_ctx_launches_per_step": (_I, [_P]),
     "b2_ctx_time_steps": (_I, [_P, _I, C.POINTER(C.c_float)]),
@@ -342,10 +342,24 @@ class Context:
         rest = self.generate_greedy(n_new - 1) if n_new > 1 else []
         return [first] + rest, logits
 
+    ACT = {"hidden": 0, "q": 1, "attn_out": 2, "ffn_h": 3, "logits": 4}
+
+    def activation(self, which: str) -> np.ndarray:
+        i = self.model.info
+        cap = max(i.vocab, i.d_ff, i.n_head * i.head_dim, i.d_model)
+        out = np.empty(cap, np.float32)
+        n = check(lib.b2_ctx_get_activation(self.h, self.ACT[which], out.ctypes.data, cap))
+        return out[:n].copy()
+
     def hidden(self) -> np.ndarray:
-        out = np.empty(self.model.info.d_model, np.float32)
-        check(lib.b2_ctx_get_hidden(self.h, out.ctypes.data))
-        return out
+        return self.activation("hidden")
+
+    def kv(self, layer: int, pos: int) -> tuple[np.ndarray, np.ndarray]:
+        i = self.model.info
+        k = np.empty(i.n_kv * i.head_dim, np.float16)
+        v = np.empty_like(k)
+        check(lib.b2_ctx_get_kv(self.h, layer, pos, k.ctypes.data, v.ctypes.data))
+        return k, v
 
     def enqueue_steps(self, n: int):
         check(lib.b2_ctx_enqueue_steps(self.h, n))

@@ -644,15 +644,41 @@ extern "C" int b2_ctx_generate_greedy(b2_ctx* c, int n_steps, int32_t* tokens_ou
     return 0;
 }
 
-extern "C" int b2_ctx_get_hidden(b2_ctx* c, float* out_host) {
+extern "C" int b2_ctx_get_activation(b2_ctx* c, int which, float* out_host, int64_t cap) {
     if (!c || !out_host) return B2_EINVAL;
-    B2_CUDA_CHECK(cudaMemcpyAsync(out_host, c->x, (size_t)c->m->info.d_model * 4, cudaMemcpyDeviceToHost, c->stream));
+    const b2_model_info& I = c->m->info;
+    const float* src = nullptr;
+    int64_t n = 0;
+    switch (which) {
+        case B2_ACT_HIDDEN: src = c->x; n = I.d_model; break;
+        case B2_ACT_Q: src = c->q; n = (int64_t)I.n_head * I.head_dim; break;
+        case B2_ACT_ATTN_OUT: src = c->attn_out; n = (int64_t)I.n_head * I.head_dim; break;
+        case B2_ACT_FFN_H: src = c->h; n = I.d_ff; break;
+        case B2_ACT_LOGITS: src = c->logits; n = I.vocab; break;
+        default: set_error("b2_ctx_get_activation: unknown buffer %d", which); return B2_EINVAL;
+    }
+    if (cap < n) {
+        set_error("b2_ctx_get_activation: buffer %d holds %lld floats, caller provided %lld", which, (long long)n, (long long)cap);
+        return B2_ERANGE;
+    }
+    B2_CUDA_CHECK(cudaMemcpyAsync(out_host, src, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
-    return 0;
+    return (int)n;
 }
-extern "C" int b2_ctx_get_logits(b2_ctx* c, float* out_host) {
-    if (!c || !out_host) return B2_EINVAL;
-    B2_CUDA_CHECK(cudaMemcpyAsync(out_host, c->logits, (size_t)c->m->info.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
+
+extern "C" int b2_ctx_get_kv(b2_ctx* c, int layer, int pos, uint16_t* k_out_host, uint16_t* v_out_host) {
+    if (!c || !k_out_host || !v_out_host) return B2_EINVAL;
+    const b2_model_info& I = c->m->info;
+    if (layer < 0 || layer >= I.n_layer || pos < 0 || pos >= c->n_ctx) {
+        set_error("b2_ctx_get_kv: layer %d / position %d out of range", layer, pos);
+        return B2_ERANGE;
+    }
+    const size_t kv_layer = (size_t)I.n_kv * c->n_ctx * I.head_dim;
+    for (int h = 0; h < I.n_kv; h++) {
+        const size_t off = layer * kv_layer + ((size_t)h * c->n_ctx + pos) * I.head_dim;
+        B2_CUDA_CHECK(cudaMemcpyAsync(k_out_host + (size_t)h * I.head_dim, c->k_cache + off, I.head_dim * 2, cudaMemcpyDeviceToHost, c->stream));
+        B2_CUDA_CHECK(cudaMemcpyAsync(v_out_host + (size_t)h * I.head_dim, c->v_cache + off, I.head_dim * 2, cudaMemcpyDeviceToHost, c->stream));
+    }
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     return 0;
 }

@@ -610,8 +610,24 @@ int32_t ref_decode(ref_ctx* c, int32_t token, int32_t pos, float* logits_out) {
     return best;
 }
 
-/* expose the hidden state after the last layer (before output_norm) for debugging parity */
+/* expose the hidden state after the last layer (before output_norm) and the last layer's intermediates */
 const float* ref_ctx_hidden(const ref_ctx* c) { return c->x; }
+const float* ref_ctx_buffer(const ref_ctx* c, int which) {
+    switch (which) {
+        case 0: return c->x;
+        case 1: return c->q;
+        case 2: return c->attn_out;
+        case 3: return c->h;
+    }
+    return 0;
+}
+/* fp16 K / V rows [n_kv*head_dim] of a layer at a position */
+const uint16_t* ref_ctx_k(const ref_ctx* c, int layer, int pos) {
+    return c->k_cache + ((int64_t)layer * c->m->n_ctx + pos) * c->m->n_kv * c->m->head_dim;
+}
+const uint16_t* ref_ctx_v(const ref_ctx* c, int layer, int pos) {
+    return c->v_cache + ((int64_t)layer * c->m->n_ctx + pos) * c->m->n_kv * c->m->head_dim;
+}
 
 /* dot of one weight row with an fp32 activation row (quantises the activation first) */
 float ref_vec_dot(int wtype, const void* wrow, const float* x, int64_t K) {

@@ -61,6 +61,11 @@ def lib() -> C.CDLL:
         L.ref_decode.restype = C.c_int32
         L.ref_ctx_hidden.argtypes = [C.c_void_p]
         L.ref_ctx_hidden.restype = C.POINTER(C.c_float)
+        L.ref_ctx_buffer.argtypes = [C.c_void_p, C.c_int]
+        L.ref_ctx_buffer.restype = C.POINTER(C.c_float)
+        for f in (L.ref_ctx_k, L.ref_ctx_v):
+            f.argtypes = [C.c_void_p, C.c_int, C.c_int]
+            f.restype = C.POINTER(C.c_uint16)
         L.ref_row_bytes.argtypes = [C.c_int, C.c_int64]
         L.ref_row_bytes.restype = C.c_int64
         L.ref_num_threads.restype = C.c_int
@@ -201,6 +206,18 @@ class RefGGUFModel:
 
     def hidden(self) -> np.ndarray:
         return np.ctypeslib.as_array(lib().ref_ctx_hidden(self.ctx), shape=(self.d_model,)).copy()
+
+    def activation(self, which: str) -> np.ndarray:
+        m = self.m
+        idx, n = {"hidden": (0, m.d_model), "q": (1, m.n_head * m.head_dim), "attn_out": (2, m.n_head * m.head_dim),
+                  "ffn_h": (3, m.d_ff)}[which]
+        return np.ctypeslib.as_array(lib().ref_ctx_buffer(self.ctx, idx), shape=(n,)).copy()
+
+    def kv(self, layer: int, pos: int) -> tuple[np.ndarray, np.ndarray]:
+        n = self.m.n_kv * self.m.head_dim
+        k = np.ctypeslib.as_array(lib().ref_ctx_k(self.ctx, layer, pos), shape=(n,)).copy().view(np.float16)
+        v = np.ctypeslib.as_array(lib().ref_ctx_v(self.ctx, layer, pos), shape=(n,)).copy().view(np.float16)
+        return k, v
 
     def greedy(self, prompt: list[int], n_new: int) -> tuple[list[int], np.ndarray]:
         """Feed the prompt token by token, then generate n_new greedy tokens.
