@@ -9,8 +9,8 @@
 //
 // Data movement (HBM-bound byte work; no tensor cores on purpose):
 //   * weights stay in HBM exactly as in the GGUF.  A producer warp streams row segments into a
-//     4-stage shared-memory ring with 1-D bulk async copies (cp.async.bulk, SASS UBLKCP) that
-//     complete on mbarriers; 4 consumer warps read the ring with aligned 16-byte LDS.  Because the
+//     3-stage shared-memory ring with 1-D bulk async copies (cp.async.bulk, SASS UBLKCP) that
+//     complete on mbarriers; 8 consumer warps read the ring with aligned 16-byte LDS.  Because the
 //     copy engine moves raw bytes, the 2-byte-aligned 210-byte Q6_K and 34-byte Q8_0 blocks need no
 //     repacking: consumers read them with aligned words + funnel shifts.
 //   * the producer never touches activations, so under programmatic dependent launch it starts
@@ -18,8 +18,9 @@
 //     griddepcontrol.wait until their input exists.
 //   * each CTA rebuilds the (tiny) quantised activation vector in shared memory from the fp32 vector
 //     in L2, which removes separate norm / quantise launches from the dependency chain.
-//   * a tile is 4 row pairs (one per consumer warp) x one K-chunk of 2048 weights; tiles are dealt
-//     round-robin to a grid of at most 3 CTAs per SM.
+//   * a tile is 4 row pairs x one K-chunk of 4096 weights; each pair is worked on by two consumer
+//     warps that split the chunk's blocks between them (8 consumer warps per CTA, 2 CTAs per SM);
+//     tiles are dealt round-robin over the grid.
 #include "gemv.cuh"
 
 #include "common.h"
@@ -35,9 +36,8 @@ constexpr int NCT = NCW * 32;  // consumer threads
 template <int ACT>
 struct Geo {
     // blocks per K-chunk, bytes of a ring row slot (largest row segment + 16 bytes of alignment slack)
-    static constexpr int CHUNK_BLOCKS = ACT == ACT_Q8K ? 8 : 32;
-    static constexpr int CHUNK_ELEMS = ACT == ACT_Q8K ? 2048 : 1024;
-    static constexpr int ROW_SLOT = ACT == ACT_Q8K ? (8 * 210 + 16) : (32 * 34 + 16);
+    static constexpr int CHUNK_BLOCKS = ACT == ACT_Q8K ? 16 : 64;
+    static constexpr int ROW_SLOT = ACT == ACT_Q8K ? (16 * 210 + 16) : (64 * 34 + 16);
     static constexpr int STAGE_BYTES = 2 * GEMV_TILE_PAIRS * ROW_SLOT;
 };
 
@@ -100,10 +100,10 @@ __device__ __forceinline__ float q4k_block(const uint8_t* blk, int j, int c, con
 
 // Q4_K: 8 lanes per 144-byte block (lane j takes qs[16j..16j+15]: low nibbles -> sub-block 2c,
 // high nibbles -> sub-block 2c+1, c = j/2), 4 blocks per warp pass.
-__device__ __forceinline__ void dot_chunk_q4k(const uint8_t* ra, const uint8_t* rb, int nb, int kb0, const ActView& x,
+__device__ __forceinline__ void dot_chunk_q4k(const uint8_t* ra, const uint8_t* rb, int b0, int b1, int kb0, const ActView& x,
                                               int lane, float& acc0, float& acc1) {
     const int j = lane & 7, c = j >> 1, hb = j & 1;
-    for (int b = lane >> 3; b < nb; b += 4) {
+    for (int b = b0 + (lane >> 3); b < b1; b += 4) {
         const int kb = kb0 + b;
         const int8_t* xb = x.q + kb * 256 + 64 * c + 16 * hb;
         const uint4 xl = *(const uint4*)xb, xh = *(const uint4*)(xb + 32);
@@ -136,10 +136,10 @@ __device__ __forceinline__ float q5k_block(const uint8_t* blk, int j, int c, int
     return d * (float)(sc0 * dlo + sc1 * dhi) - dmin * (float)(mj * bs);
 }
 
-__device__ __forceinline__ void dot_chunk_q5k(const uint8_t* ra, const uint8_t* rb, int nb, int kb0, const ActView& x,
+__device__ __forceinline__ void dot_chunk_q5k(const uint8_t* ra, const uint8_t* rb, int b0, int b1, int kb0, const ActView& x,
                                               int lane, float& acc0, float& acc1) {
     const int j = lane & 7, c = j >> 1, hb = j & 1;
-    for (int b = lane >> 3; b < nb; b += 4) {
+    for (int b = b0 + (lane >> 3); b < b1; b += 4) {
         const int kb = kb0 + b;
         const int8_t* xb = x.q + kb * 256 + 64 * c + 16 * hb;
         const uint4 xl = *(const uint4*)xb, xh = *(const uint4*)(xb + 32);
@@ -173,10 +173,10 @@ __device__ __forceinline__ float q6k_unit(const uint8_t* blk, int h, int p, cons
     return d * (float)isum;
 }
 
-__device__ __forceinline__ void dot_chunk_q6k(const uint8_t* ra, const uint8_t* rb, int nb, int kb0, const ActView& x,
+__device__ __forceinline__ void dot_chunk_q6k(const uint8_t* ra, const uint8_t* rb, int b0, int b1, int kb0, const ActView& x,
                                               int lane, float& acc0, float& acc1) {
-    const int b = lane >> 2, h = (lane >> 1) & 1, p = lane & 1;
-    if (b < nb) {
+    const int h = (lane >> 1) & 1, p = lane & 1;
+    for (int b = b0 + (lane >> 2); b < b1; b += 8) {
         const int kb = kb0 + b;
         const int8_t* xb = x.q + kb * 256 + 128 * h + 16 * p;
         uint4 xv[4];
@@ -205,32 +205,115 @@ __device__ __forceinline__ float q80_block(const uint8_t* blk, const uint4& x0, 
     s = dp4a_ss(b.w, x1.w, s);
     return (float)s * h2f_bits(*(const uint16_t*)blk);
 }
-__device__ __forceinline__ void dot_chunk_q80(const uint8_t* ra, const uint8_t* rb, int nb, int kb0, const ActView& x,
+__device__ __forceinline__ void dot_chunk_q80(const uint8_t* ra, const uint8_t* rb, int b0, int b1, int kb0, const ActView& x,
                                               int lane, float& acc0, float& acc1) {
-    if (lane < nb) {
-        const int kb = kb0 + lane;
+    for (int b = b0 + lane; b < b1; b += 32) {
+        const int kb = kb0 + b;
         const uint4 x0 = *(const uint4*)(x.q + kb * 32), x1 = *(const uint4*)(x.q + kb * 32 + 16);
         const float dx = x.d[kb];
         // ggml: sumi * (d_w * d_x); keep that association
-        acc0 += q80_block(ra + lane * 34, x0, x1) * dx;
-        acc1 += q80_block(rb + lane * 34, x0, x1) * dx;
+        acc0 += q80_block(ra + b * 34, x0, x1) * dx;
+        acc1 += q80_block(rb + b * 34, x0, x1) * dx;
     }
 }
 
 // ------------------------------------------------------------------------------------------------
-// prologue: fp32 activation (optionally RMS-normalised) -> quantised copy in shared memory
+// prologue: fp32 activation (optionally RMS-normalised) -> quantised copy in shared memory.
+// Latency-bound (one small vector out of L2), so every load a warp needs is issued before the first
+// use: warp w owns the 256-element spans w, w+8, ...; a lane holds 8 consecutive values of each.
 // ------------------------------------------------------------------------------------------------
+template <int ACT>
+__device__ __forceinline__ void quantise_span(const float (&v)[8], int base, int lane, int K, int8_t* xq, float* xd, int16_t* xbs) {
+    const int i0 = base + lane * 8;
+    int q[8];
+    if (ACT == ACT_Q8K) {
+        // first element with the largest magnitude (strict '>' scan in quantize_row_q8_K_ref)
+        float amax = 0.0f, mval = 0.0f;
+        int midx = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const float ax = fabsf(v[i]);
+            if (ax > amax) { amax = ax; mval = v[i]; midx = lane * 8 + i; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
+            const float ov = __shfl_xor_sync(0xffffffffu, mval, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, midx, o);
+            if (oa > amax || (oa == amax && oi < midx)) { amax = oa; mval = ov; midx = oi; }
+        }
+        float d = 0.0f;
+        if (amax != 0.0f) {
+            const float iscale = -127.0f / mval;
+#pragma unroll
+            for (int i = 0; i < 8; i++) q[i] = min(127, __float2int_rn(iscale * v[i]));
+            d = 1.0f / iscale;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) q[i] = 0;
+        }
+        int s8 = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) s8 += q[i];
+        s8 += __shfl_xor_sync(0xffffffffu, s8, 1);
+        if (i0 < K) {
+            if ((lane & 1) == 0) xbs[(base >> 4) + (lane >> 1)] = (int16_t)s8;
+            if (lane == 0) xd[base >> 8] = d;
+        }
+    } else {
+        // Q8_0: 32-element blocks = 4 lanes
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+        const float d = amax / 127.0f;
+        const float id = d != 0.0f ? 1.0f / d : 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) q[i] = (int)roundf(v[i] * id);
+        if (i0 < K && (lane & 3) == 0) xd[i0 >> 5] = __half2float(__float2half_rn(d));
+    }
+    if (i0 < K) {
+        uint2 pk;
+        pk.x = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
+        pk.y = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
+        *(uint2*)(xq + i0) = pk;
+    }
+}
+
+__device__ __forceinline__ void load8(const float* p, int i0, int K, float (&v)[8]) {
+    if (i0 < K) {
+        const float4 p0 = *(const float4*)(p + i0), p1 = *(const float4*)(p + i0 + 4);
+        v[0] = p0.x; v[1] = p0.y; v[2] = p0.z; v[3] = p0.w;
+        v[4] = p1.x; v[5] = p1.y; v[6] = p1.z; v[7] = p1.w;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = 0.0f;
+    }
+}
+
 template <int ACT>
 __device__ void build_activation(const GemvArgs& a, int8_t* xq, float* xd, int16_t* xbs, double* red, int tid) {
     const int K = a.K;
     const int lane = tid & 31, warp = tid >> 5;
-    float scale = 1.0f;
+    const int nspans = (K + 255) >> 8;
     if (a.prologue == PRO_NORM) {
-        // ggml rms_norm: sum of fp32 squares accumulated in double, mean, 1/sqrtf(mean + eps)
+        // ggml rms_norm: sum of fp32 squares accumulated in double, mean, 1/sqrtf(mean + eps); then (x*scale)*w
+        constexpr int MB = 4;   // spans per warp kept in registers (d_model <= 8192); larger vectors are re-read
+        const bool resident = nspans <= NCW * MB;
+        float v[MB][8], w[MB][8];
         double ss = 0.0;
-        for (int i = tid * 4; i < K; i += NCT * 4) {
-            const float4 v = *(const float4*)(a.x + i);
-            ss += (double)(v.x * v.x) + (double)(v.y * v.y) + (double)(v.z * v.z) + (double)(v.w * v.w);
+        for (int s0 = 0; s0 < nspans; s0 += NCW * MB) {
+#pragma unroll
+            for (int m = 0; m < MB; m++) {
+                const int base = (s0 + warp + m * NCW) << 8;
+                load8(a.x, base < K ? base + lane * 8 : K, K, v[m]);
+                if (resident) load8(a.norm_w, base < K ? base + lane * 8 : K, K, w[m]);
+            }
+#pragma unroll
+            for (int m = 0; m < MB; m++)
+#pragma unroll
+                for (int i = 0; i < 8; i++) ss += (double)(v[m][i] * v[m][i]);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
@@ -238,82 +321,42 @@ __device__ void build_activation(const GemvArgs& a, int8_t* xq, float* xd, int16
         named_bar_sync(1, NCT);
         double tot = 0.0;
 #pragma unroll
-        for (int w = 0; w < NCW; w++) tot += red[w];
+        for (int k = 0; k < NCW; k++) tot += red[k];
         const float mean = (float)(tot / (double)K);
-        scale = 1.0f / sqrtf(mean + a.eps);
-    }
-    // each warp quantises 256-element spans: lane holds 8 consecutive values
-    for (int base = warp * 256; base < K; base += NCW * 256) {
-        const int i0 = base + lane * 8;
-        float v[8];
-        if (i0 < K) {
-            const float4 p0 = *(const float4*)(a.x + i0), p1 = *(const float4*)(a.x + i0 + 4);
-            v[0] = p0.x; v[1] = p0.y; v[2] = p0.z; v[3] = p0.w;
-            v[4] = p1.x; v[5] = p1.y; v[6] = p1.z; v[7] = p1.w;
-            if (a.prologue == PRO_NORM) {
-                const float4 w0 = *(const float4*)(a.norm_w + i0), w1 = *(const float4*)(a.norm_w + i0 + 4);
-                v[0] = (v[0] * scale) * w0.x; v[1] = (v[1] * scale) * w0.y;
-                v[2] = (v[2] * scale) * w0.z; v[3] = (v[3] * scale) * w0.w;
-                v[4] = (v[4] * scale) * w1.x; v[5] = (v[5] * scale) * w1.y;
-                v[6] = (v[6] * scale) * w1.z; v[7] = (v[7] * scale) * w1.w;
-            }
-        } else {
+        const float scale = 1.0f / sqrtf(mean + a.eps);
+        for (int s0 = 0; s0 < nspans; s0 += NCW * MB) {
 #pragma unroll
-            for (int i = 0; i < 8; i++) v[i] = 0.0f;
+            for (int m = 0; m < MB; m++) {
+                const int base = (s0 + warp + m * NCW) << 8;
+                if (!resident) {
+                    load8(a.x, base < K ? base + lane * 8 : K, K, v[m]);
+                    load8(a.norm_w, base < K ? base + lane * 8 : K, K, w[m]);
+                }
+            }
+#pragma unroll
+            for (int m = 0; m < MB; m++) {
+                const int base = (s0 + warp + m * NCW) << 8;
+                if (base < K) {   // warp-uniform
+#pragma unroll
+                    for (int i = 0; i < 8; i++) v[m][i] = (v[m][i] * scale) * w[m][i];
+                    quantise_span<ACT>(v[m], base, lane, K, xq, xd, xbs);
+                }
+            }
         }
-        int q[8];
-        if (ACT == ACT_Q8K) {
-            // first element with the largest magnitude (strict '>' scan in quantize_row_q8_K_ref)
-            float amax = 0.0f, mval = 0.0f;
-            int midx = 0;
+    } else {
+        constexpr int MB = 8;
+        float v[MB][8];
+        for (int s0 = 0; s0 < nspans; s0 += NCW * MB) {
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const float ax = fabsf(v[i]);
-                if (ax > amax) { amax = ax; mval = v[i]; midx = lane * 8 + i; }
+            for (int m = 0; m < MB; m++) {
+                const int base = (s0 + warp + m * NCW) << 8;
+                load8(a.x, base < K ? base + lane * 8 : K, K, v[m]);
             }
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
-                const float ov = __shfl_xor_sync(0xffffffffu, mval, o);
-                const int oi = __shfl_xor_sync(0xffffffffu, midx, o);
-                if (oa > amax || (oa == amax && oi < midx)) { amax = oa; mval = ov; midx = oi; }
+            for (int m = 0; m < MB; m++) {
+                const int base = (s0 + warp + m * NCW) << 8;
+                if (base < K) quantise_span<ACT>(v[m], base, lane, K, xq, xd, xbs);
             }
-            float d = 0.0f;
-            if (amax != 0.0f) {
-                const float iscale = -127.0f / mval;
-#pragma unroll
-                for (int i = 0; i < 8; i++) q[i] = min(127, __float2int_rn(iscale * v[i]));
-                d = 1.0f / iscale;
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; i++) q[i] = 0;
-            }
-            int s8 = 0;
-#pragma unroll
-            for (int i = 0; i < 8; i++) s8 += q[i];
-            s8 += __shfl_xor_sync(0xffffffffu, s8, 1);
-            if (i0 < K) {
-                if ((lane & 1) == 0) xbs[(base >> 4) + (lane >> 1)] = (int16_t)s8;
-                if (lane == 0) xd[base >> 8] = d;
-            }
-        } else {
-            // Q8_0: 32-element blocks = 4 lanes
-            float amax = 0.0f;
-#pragma unroll
-            for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-            const float d = amax / 127.0f;
-            const float id = d != 0.0f ? 1.0f / d : 0.0f;
-#pragma unroll
-            for (int i = 0; i < 8; i++) q[i] = (int)roundf(v[i] * id);
-            if (i0 < K && (lane & 3) == 0) xd[i0 >> 5] = __half2float(__float2half_rn(d));
-        }
-        if (i0 < K) {
-            uint2 pk;
-            pk.x = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
-            pk.y = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
-            *(uint2*)(xq + i0) = pk;
         }
     }
     named_bar_sync(1, NCT);
@@ -375,14 +418,15 @@ __device__ __forceinline__ void epilogue(const GemvArgs& a, const GemvSeg& s, in
 }
 
 template <int ACT>
-__global__ void __launch_bounds__(GEMV_THREADS, 3) gemv_kernel(const __grid_constant__ GemvArgs a) {
+__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_constant__ GemvArgs a) {
     using G = Geo<ACT>;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* ring = smem;
     uint64_t* full = (uint64_t*)(smem + GEMV_STAGES * G::STAGE_BYTES);
     uint64_t* empty = full + GEMV_STAGES;
     double* red = (double*)(empty + GEMV_STAGES);
-    int8_t* xq = (int8_t*)(red + NCW);
+    float* part = (float*)(red + NCW);                 // [2 parities][pairs][2 rows] partial sums of the odd warps
+    int8_t* xq = (int8_t*)(part + 2 * GEMV_TILE_PAIRS * 2);
     const int K = a.K;
     float* xd = (float*)(xq + K);
     int16_t* xbs = (int16_t*)(xd + (ACT == ACT_Q8K ? K / 256 : K / 32));
@@ -452,13 +496,15 @@ __global__ void __launch_bounds__(GEMV_THREADS, 3) gemv_kernel(const __grid_cons
     build_activation<ACT>(a, xq, xd, xbs, red, tid);
     const ActView xv{xq, xd, xbs};
 
-    int stage = 0, phase = 0;
-    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+    // warps 2p and 2p+1 share row pair p of the tile and split each chunk's blocks between them
+    const int pw = warp >> 1, half = warp & 1;
+    int stage = 0, phase = 0, parity = 0;
+    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
         int si = 0;
         while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
         const GemvSeg& s = a.seg[si];
         const int bb = block_bytes_of(s.type);
-        const int p = (tile - s.tile0) * GEMV_TILE_PAIRS + warp;
+        const int p = (tile - s.tile0) * GEMV_TILE_PAIRS + pw;
         const bool valid = p < s.n_pairs;
         int ra = 0, rb = -1;
         uint32_t offa = 0, offb = 0;
@@ -473,30 +519,35 @@ __global__ void __launch_bounds__(GEMV_THREADS, 3) gemv_kernel(const __grid_cons
         float acc0 = 0.0f, acc1 = 0.0f;
         for (int c = 0; c < n_chunks; c++) {
             const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
+            // split in whole warp passes (4 blocks for Q4_K/Q5_K, 8 for Q6_K, 32 for Q8_0)
+            constexpr int GRAN = ACT == ACT_Q8K ? 8 : 32;
+            const int h0 = min(nb, ((nb + 2 * GRAN - 1) / (2 * GRAN)) * GRAN);
+            const int b0 = half ? h0 : 0, b1 = half ? nb : h0;
             mbar_wait(&full[stage], phase);
-            if (valid) {
-                const uint8_t* slot = ring + stage * G::STAGE_BYTES + (2 * warp) * G::ROW_SLOT;
+            if (valid && b0 < b1) {
+                const uint8_t* slot = ring + stage * G::STAGE_BYTES + (2 * pw) * G::ROW_SLOT;
                 const uint8_t* pa = slot + ((offa + c * chunk_step) & 15);
                 const uint8_t* pb = slot + G::ROW_SLOT + ((offb + c * chunk_step) & 15);
                 if (rb < 0) pb = pa;
                 const int kb0 = c * G::CHUNK_BLOCKS;
                 if (ACT == ACT_Q8K) {
-                    if (s.type == B2_TYPE_Q4_K) dot_chunk_q4k(pa, pb, nb, kb0, xv, lane, acc0, acc1);
-                    else if (s.type == B2_TYPE_Q6_K) dot_chunk_q6k(pa, pb, nb, kb0, xv, lane, acc0, acc1);
-                    else dot_chunk_q5k(pa, pb, nb, kb0, xv, lane, acc0, acc1);
+                    if (s.type == B2_TYPE_Q4_K) dot_chunk_q4k(pa, pb, b0, b1, kb0, xv, lane, acc0, acc1);
+                    else if (s.type == B2_TYPE_Q6_K) dot_chunk_q6k(pa, pb, b0, b1, kb0, xv, lane, acc0, acc1);
+                    else dot_chunk_q5k(pa, pb, b0, b1, kb0, xv, lane, acc0, acc1);
                 } else {
-                    dot_chunk_q80(pa, pb, nb, kb0, xv, lane, acc0, acc1);
+                    dot_chunk_q80(pa, pb, b0, b1, kb0, xv, lane, acc0, acc1);
                 }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
         }
-        if (valid) {
-            acc0 = warp_sum(acc0);
-            acc1 = warp_sum(acc1);
-            if (lane == 0) epilogue(a, s, p, ra, rb, acc0, acc1);
-        }
+        acc0 = warp_sum(acc0);
+        acc1 = warp_sum(acc1);
+        float* pp = part + (parity * GEMV_TILE_PAIRS + pw) * 2;
+        if (half && lane == 0) { pp[0] = acc0; pp[1] = acc1; }
+        named_bar_sync(2 + pw, 64);   // the pair's two warps
+        if (!half && lane == 0 && valid) epilogue(a, s, p, ra, rb, acc0 + pp[0], acc1 + pp[1]);
     }
 }
 
@@ -512,7 +563,7 @@ int gemv_act_for_type(int type) {
 
 size_t gemv_smem_bytes(int act, int K) {
     const size_t stage = act == ACT_Q8K ? Geo<ACT_Q8K>::STAGE_BYTES : Geo<ACT_Q80>::STAGE_BYTES;
-    size_t n = GEMV_STAGES * stage + 2 * GEMV_STAGES * sizeof(uint64_t) + NCW * sizeof(double);
+    size_t n = GEMV_STAGES * stage + 2 * GEMV_STAGES * sizeof(uint64_t) + NCW * sizeof(double) + 2 * GEMV_TILE_PAIRS * 2 * sizeof(float);
     n += (size_t)K;                                           // int8 activations
     n += (act == ACT_Q8K ? K / 256 : K / 32) * sizeof(float);  // block scales
     if (act == ACT_Q8K) n += (size_t)K / 16 * sizeof(int16_t);
@@ -580,7 +631,7 @@ int launch_gemv(const GemvArgs& a, int act, cudaStream_t st, bool pdl) {
         configured[act] = smem;
     }
     int ctas_per_sm = (int)((227 * 1024) / (smem + 1024));
-    if (ctas_per_sm > 3) ctas_per_sm = 3;
+    if (ctas_per_sm > 2) ctas_per_sm = 2;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     int grid = g_num_sms * ctas_per_sm;
     if (grid > a.n_tiles) grid = a.n_tiles;

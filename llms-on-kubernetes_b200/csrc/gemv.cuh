@@ -47,10 +47,10 @@ struct GemvArgs {
     int rope_half;
 };
 
-constexpr int GEMV_CONSUMER_WARPS = 4;
+constexpr int GEMV_CONSUMER_WARPS = 8;
 constexpr int GEMV_THREADS = (GEMV_CONSUMER_WARPS + 1) * 32;
-constexpr int GEMV_TILE_PAIRS = GEMV_CONSUMER_WARPS;  // one row pair per consumer warp
-constexpr int GEMV_STAGES = 4;
+constexpr int GEMV_TILE_PAIRS = GEMV_CONSUMER_WARPS / 2;  // two consumer warps per row pair (K split)
+constexpr int GEMV_STAGES = 3;
 
 // fills tile0 / n_tiles from n_pairs; returns 0 or a negative B2_E* code after validating shapes
 int gemv_finalize(GemvArgs& a, int act);

@@ -66,8 +66,9 @@ def test_attention_single_split(b2, n_head, n_kv, hd, T):
     b2.check(b2.lib.b2_attn_decode(dq.ptr, dk.ptr, dv.ptr, do.ptr, n_head, n_kv, hd, n_ctx, T, sc.ptr, None))
     got = do.to_numpy(np.float32).reshape(n_head, hd)
     want = _attn_ref(q, K, V, n_head, n_kv, hd, T)
-    # same fp16 roundings; fp32 summation order differs
-    assert np.abs(got - want).max() < 2e-5 * max(1.0, np.abs(want).max()) + 1e-3 * (T > 1) * 2.0 ** -10
+    # same fp16 roundings; fp32 summation order differs, and a probability that lands on an fp16 rounding
+    # boundary may flip by one fp16 ulp (2^-11 relative) times |v| <= ~4
+    assert np.abs(got - want).max() < 2e-4 * max(1.0, np.abs(want).max())
 
 
 @pytest.mark.parametrize("T", [1025, 3000, 8192])
