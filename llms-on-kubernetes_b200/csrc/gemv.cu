@@ -7,20 +7,25 @@
 // dot products are integer (dp4a) with one fp32 scale per (super-)block.  See oracle/ggml_ref.c for
 // the CPU restatement these kernels are tested against.
 //
-// Data movement (HBM-bound byte work; no tensor cores on purpose):
+// The kernel is HBM-bound byte work, and at B200 bandwidth it is the *instruction issue rate* that
+// threatens the roofline (11.6e12 4.5-bit weights per second), so the design is about instructions
+// per weight as much as about bytes:
 //   * weights stay in HBM exactly as in the GGUF.  A producer warp streams row segments into a
-//     3-stage shared-memory ring with 1-D bulk async copies (cp.async.bulk, SASS UBLKCP) that
-//     complete on mbarriers; 8 consumer warps read the ring with aligned 16-byte LDS.  Because the
-//     copy engine moves raw bytes, the 2-byte-aligned 210-byte Q6_K and 34-byte Q8_0 blocks need no
-//     repacking: consumers read them with aligned words + funnel shifts.
-//   * the producer never touches activations, so under programmatic dependent launch it starts
-//     filling the ring while the previous kernel in the stream is still running; consumers block in
-//     griddepcontrol.wait until their input exists.
-//   * each CTA rebuilds the (tiny) quantised activation vector in shared memory from the fp32 vector
-//     in L2, which removes separate norm / quantise launches from the dependency chain.
-//   * a tile is 4 row pairs x one K-chunk of 4096 weights; each pair is worked on by two consumer
-//     warps that split the chunk's blocks between them (8 consumer warps per CTA, 2 CTAs per SM);
-//     tiles are dealt round-robin over the grid.
+//     3-stage shared-memory ring with 1-D bulk async copies (cp.async.bulk, SASS UBLKCP) completing
+//     on mbarriers; it never touches activations, so under programmatic dependent launch it fills the
+//     ring while the previous kernel in the stream is still running.  Because the copy engine moves
+//     raw bytes, the 2-byte-aligned 210-byte Q6_K / 34-byte Q8_0 blocks need no repacking.
+//   * a tile is 8 weight rows x one K-chunk (16 super-blocks).  Each of the 8 consumer warps takes
+//     two super-blocks of the chunk for all 8 rows: 4 lanes per (row, super-block), 64 weights per
+//     lane, so the 6-bit scale unpack, the fp16 scale converts and the activation loads are amortised
+//     over 64 weights, and the activation bytes are broadcast-read once for 8 rows.  High nibbles are
+//     multiplied in place (dp4a.u32.s32 on q & 0xF0F0F0F0, exact shift by 4 afterwards).
+//   * the quantised activation vector is built ONCE PER THREAD-BLOCK CLUSTER, not once per CTA: the
+//     8 CTAs of a cluster each quantise 1/8 of the 256-element spans and store the result into every
+//     peer's shared memory through DSMEM, signalling per-span on the peers' mbarriers.  (Done per CTA
+//     this prologue was 39% of all issued instructions.)
+//   * per tile the warps' partial sums meet in shared memory; warp 0 adds them in a fixed order and
+//     runs the fused epilogue on row pairs (RoPE pairs, gate/up pairs).
 #include "gemv.cuh"
 
 #include "common.h"
@@ -31,14 +36,16 @@ namespace b2 {
 namespace {
 
 constexpr int NCW = GEMV_CONSUMER_WARPS;
-constexpr int NCT = NCW * 32;  // consumer threads
+constexpr int NCT = NCW * 32;   // consumer threads
+constexpr int TILE_ROWS = 8;
+constexpr int MAX_SPANS = 128;  // K <= 32768
 
 template <int ACT>
 struct Geo {
     // blocks per K-chunk, bytes of a ring row slot (largest row segment + 16 bytes of alignment slack)
     static constexpr int CHUNK_BLOCKS = ACT == ACT_Q8K ? 16 : 64;
     static constexpr int ROW_SLOT = ACT == ACT_Q8K ? (16 * 210 + 16) : (64 * 34 + 16);
-    static constexpr int STAGE_BYTES = 2 * GEMV_TILE_PAIRS * ROW_SLOT;
+    static constexpr int STAGE_BYTES = TILE_ROWS * ROW_SLOT;
 };
 
 __host__ __device__ inline int block_bytes_of(int type) {
@@ -67,94 +74,101 @@ __device__ __forceinline__ void pair_rows(const GemvSeg& s, int p, int* ra, int*
     }
 }
 
-// ------------------------------------------------------------------------------------------------
-// per-type inner products of one K-chunk of a row pair held in the ring
-// ------------------------------------------------------------------------------------------------
+// source pointer of tile slot `slot` (0..7: pair slot/2, row slot&1) or nullptr if it does not exist
+__device__ __forceinline__ const uint8_t* slot_row_ptr(const GemvSeg& s, int ptile, int slot, int row_bytes) {
+    const int p = ptile * GEMV_TILE_PAIRS + (slot >> 1);
+    if (p >= s.n_pairs) return nullptr;
+    int ra, rb;
+    pair_rows(s, p, &ra, &rb);
+    const int r = (slot & 1) ? rb : ra;
+    if (r < 0) return nullptr;
+    const uint8_t* w = (s.pairing == PAIR_SPLIT && (slot & 1)) ? s.wb : s.wa;
+    return w + (size_t)r * row_bytes;
+}
+
+// quantised activation vector in shared memory
 struct ActView {
-    const int8_t* q;     // [K]
-    const float* d;      // [K/256] (Q8_K) or [K/32] (Q8_0, fp16-rounded)
-    const int16_t* bs;   // [K/16] (Q8_K only)
+    const int8_t* q;      // [K]
+    const float* d;       // [K/256] (Q8_K) or [K/32] (Q8_0, fp16-rounded)
+    const int16_t* bs16;  // [K/16] sums of 16 (Q8_K)
+    const int16_t* bs32;  // [K/32] sums of 32 (Q8_K)
 };
 
-__device__ __forceinline__ float q4k_block(const uint8_t* blk, int j, int c, const uint4& xl, const uint4& xh, int bs) {
+// ------------------------------------------------------------------------------------------------
+// inner products: one lane = one quarter of a (row, super-block)
+// ------------------------------------------------------------------------------------------------
+// Q4_K quarter c: qs[32c .. 32c+31]; low nibbles are sub-block 2c, high nibbles sub-block 2c+1.
+__device__ __forceinline__ float q4k_quarter(const uint8_t* blk, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
     const uint4 hdr = *(const uint4*)blk;
-    const uint4 q = *(const uint4*)(blk + 16 + 16 * j);
-    int dlo = dp4a_ss(q.x & 0x0F0F0F0Fu, xl.x, 0);
-    int dhi = dp4a_ss((q.x >> 4) & 0x0F0F0F0Fu, xh.x, 0);
-    dlo = dp4a_ss(q.y & 0x0F0F0F0Fu, xl.y, dlo);
-    dhi = dp4a_ss((q.y >> 4) & 0x0F0F0F0Fu, xh.y, dhi);
-    dlo = dp4a_ss(q.z & 0x0F0F0F0Fu, xl.z, dlo);
-    dhi = dp4a_ss((q.z >> 4) & 0x0F0F0F0Fu, xh.z, dhi);
-    dlo = dp4a_ss(q.w & 0x0F0F0F0Fu, xl.w, dlo);
-    dhi = dp4a_ss((q.w >> 4) & 0x0F0F0F0Fu, xh.w, dhi);
-    // 6-bit scales/mins, four at a time (get_scale_min_k4 on packed words)
-    const uint32_t sc_lo = hdr.y & 0x3f3f3f3fu, m_lo = hdr.z & 0x3f3f3f3fu;
-    const uint32_t sc_hi = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
-    const uint32_t m_hi = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
-    const uint32_t scw = (c < 2 ? sc_lo : sc_hi) >> (16 * (c & 1));
-    const int sc0 = scw & 0xff, sc1 = (scw >> 8) & 0xff;
-    const int mj = ((j < 4 ? m_lo : m_hi) >> (8 * (j & 3))) & 0xff;
-    const float d = h2f_bits(hdr.x & 0xffffu), dmin = h2f_bits(hdr.x >> 16);
-    return d * (float)(sc0 * dlo + sc1 * dhi) - dmin * (float)(mj * bs);
-}
-
-// Q4_K: 8 lanes per 144-byte block (lane j takes qs[16j..16j+15]: low nibbles -> sub-block 2c,
-// high nibbles -> sub-block 2c+1, c = j/2), 4 blocks per warp pass.
-__device__ __forceinline__ void dot_chunk_q4k(const uint8_t* ra, const uint8_t* rb, int b0, int b1, int kb0, const ActView& x,
-                                              int lane, float& acc0, float& acc1) {
-    const int j = lane & 7, c = j >> 1, hb = j & 1;
-    for (int b = b0 + (lane >> 3); b < b1; b += 4) {
-        const int kb = kb0 + b;
-        const int8_t* xb = x.q + kb * 256 + 64 * c + 16 * hb;
-        const uint4 xl = *(const uint4*)xb, xh = *(const uint4*)(xb + 32);
-        const uint32_t bsw = *(const uint32_t*)(x.bs + kb * 16 + 2 * j);
-        const int bs = (int)(int16_t)(bsw & 0xffff) + (int)(int16_t)(bsw >> 16);
-        const float dx = x.d[kb];
-        acc0 += dx * q4k_block(ra + b * 144, j, c, xl, xh, bs);
-        acc1 += dx * q4k_block(rb + b * 144, j, c, xl, xh, bs);
+    const uint4 q0 = *(const uint4*)(blk + 16 + 32 * c), q1 = *(const uint4*)(blk + 32 + 32 * c);
+    int dlo = dp4a_ss(q0.x & 0x0F0F0F0Fu, xv[0].x, 0);
+    int dhi = dp4a_us(q0.x & 0xF0F0F0F0u, xv[2].x, 0);
+    dlo = dp4a_ss(q0.y & 0x0F0F0F0Fu, xv[0].y, dlo);
+    dhi = dp4a_us(q0.y & 0xF0F0F0F0u, xv[2].y, dhi);
+    dlo = dp4a_ss(q0.z & 0x0F0F0F0Fu, xv[0].z, dlo);
+    dhi = dp4a_us(q0.z & 0xF0F0F0F0u, xv[2].z, dhi);
+    dlo = dp4a_ss(q0.w & 0x0F0F0F0Fu, xv[0].w, dlo);
+    dhi = dp4a_us(q0.w & 0xF0F0F0F0u, xv[2].w, dhi);
+    dlo = dp4a_ss(q1.x & 0x0F0F0F0Fu, xv[1].x, dlo);
+    dhi = dp4a_us(q1.x & 0xF0F0F0F0u, xv[3].x, dhi);
+    dlo = dp4a_ss(q1.y & 0x0F0F0F0Fu, xv[1].y, dlo);
+    dhi = dp4a_us(q1.y & 0xF0F0F0F0u, xv[3].y, dhi);
+    dlo = dp4a_ss(q1.z & 0x0F0F0F0Fu, xv[1].z, dlo);
+    dhi = dp4a_us(q1.z & 0xF0F0F0F0u, xv[3].z, dhi);
+    dlo = dp4a_ss(q1.w & 0x0F0F0F0Fu, xv[1].w, dlo);
+    dhi = dp4a_us(q1.w & 0xF0F0F0F0u, xv[3].w, dhi);
+    // 6-bit scale / min pairs (2c, 2c+1) of get_scale_min_k4, as two packed bytes each
+    const int sh = (c & 1) * 16;
+    const uint32_t A = hdr.y >> sh, Z = hdr.z >> sh, W = hdr.w >> sh;
+    uint32_t scp, mp;
+    if (c < 2) {
+        scp = A & 0x3f3fu;
+        mp = Z & 0x3f3fu;
+    } else {
+        scp = (W & 0x0f0fu) | ((A >> 2) & 0x3030u);
+        mp = ((W >> 4) & 0x0f0fu) | ((Z >> 2) & 0x3030u);
     }
+    const int isum = (int)(scp & 0xffu) * dlo + (int)(scp >> 8) * (dhi >> 4);   // dhi is an exact multiple of 16
+    const int msum = (int)(mp & 0xffu) * (int)(int16_t)(bs2 & 0xffffu) + (int)(mp >> 8) * ((int)bs2 >> 16);
+    const float d = h2f_bits(hdr.x & 0xffffu), dmin = h2f_bits(hdr.x >> 16);
+    return dx * (d * (float)isum - dmin * (float)msum);
 }
 
-__device__ __forceinline__ float q5k_block(const uint8_t* blk, int j, int c, int hb, const uint4& xl, const uint4& xh, int bs) {
+// Q5_K quarter c: as Q4_K plus bit 2c / 2c+1 of qh[0..31] as the fifth bit.
+__device__ __forceinline__ float q5k_quarter(const uint8_t* blk, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
     const uint4 hdr = *(const uint4*)blk;
-    const uint4 qh = *(const uint4*)(blk + 16 + 16 * hb);
-    const uint4 q = *(const uint4*)(blk + 48 + 16 * j);
+    const uint4 h0 = *(const uint4*)(blk + 16), h1 = *(const uint4*)(blk + 32);
+    const uint4 q0 = *(const uint4*)(blk + 48 + 32 * c), q1 = *(const uint4*)(blk + 64 + 32 * c);
     const int s0 = 2 * c, s1 = 2 * c + 1;
     int dlo = 0, dhi = 0;
-#define B2_Q5_STEP(W)                                                                               \
-    dlo = dp4a_ss((q.W & 0x0F0F0F0Fu) | (((qh.W >> s0) & 0x01010101u) << 4), xl.W, dlo);            \
-    dhi = dp4a_ss(((q.W >> 4) & 0x0F0F0F0Fu) | (((qh.W >> s1) & 0x01010101u) << 4), xh.W, dhi);
-    B2_Q5_STEP(x) B2_Q5_STEP(y) B2_Q5_STEP(z) B2_Q5_STEP(w)
+#define B2_Q5_STEP(Q, H, XL, XH, W)                                                                  \
+    dlo = dp4a_ss((Q.W & 0x0F0F0F0Fu) | (((H.W >> s0) & 0x01010101u) << 4), XL.W, dlo);              \
+    dhi = dp4a_ss(((Q.W >> 4) & 0x0F0F0F0Fu) | (((H.W >> s1) & 0x01010101u) << 4), XH.W, dhi);
+    B2_Q5_STEP(q0, h0, xv[0], xv[2], x) B2_Q5_STEP(q0, h0, xv[0], xv[2], y)
+    B2_Q5_STEP(q0, h0, xv[0], xv[2], z) B2_Q5_STEP(q0, h0, xv[0], xv[2], w)
+    B2_Q5_STEP(q1, h1, xv[1], xv[3], x) B2_Q5_STEP(q1, h1, xv[1], xv[3], y)
+    B2_Q5_STEP(q1, h1, xv[1], xv[3], z) B2_Q5_STEP(q1, h1, xv[1], xv[3], w)
 #undef B2_Q5_STEP
-    const uint32_t sc_lo = hdr.y & 0x3f3f3f3fu, m_lo = hdr.z & 0x3f3f3f3fu;
-    const uint32_t sc_hi = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
-    const uint32_t m_hi = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
-    const uint32_t scw = (c < 2 ? sc_lo : sc_hi) >> (16 * (c & 1));
-    const int sc0 = scw & 0xff, sc1 = (scw >> 8) & 0xff;
-    const int mj = ((j < 4 ? m_lo : m_hi) >> (8 * (j & 3))) & 0xff;
-    const float d = h2f_bits(hdr.x & 0xffffu), dmin = h2f_bits(hdr.x >> 16);
-    return d * (float)(sc0 * dlo + sc1 * dhi) - dmin * (float)(mj * bs);
-}
-
-__device__ __forceinline__ void dot_chunk_q5k(const uint8_t* ra, const uint8_t* rb, int b0, int b1, int kb0, const ActView& x,
-                                              int lane, float& acc0, float& acc1) {
-    const int j = lane & 7, c = j >> 1, hb = j & 1;
-    for (int b = b0 + (lane >> 3); b < b1; b += 4) {
-        const int kb = kb0 + b;
-        const int8_t* xb = x.q + kb * 256 + 64 * c + 16 * hb;
-        const uint4 xl = *(const uint4*)xb, xh = *(const uint4*)(xb + 32);
-        const uint32_t bsw = *(const uint32_t*)(x.bs + kb * 16 + 2 * j);
-        const int bs = (int)(int16_t)(bsw & 0xffff) + (int)(int16_t)(bsw >> 16);
-        const float dx = x.d[kb];
-        acc0 += dx * q5k_block(ra + b * 176, j, c, hb, xl, xh, bs);
-        acc1 += dx * q5k_block(rb + b * 176, j, c, hb, xl, xh, bs);
+    const int sh = (c & 1) * 16;
+    const uint32_t A = hdr.y >> sh, Z = hdr.z >> sh, W = hdr.w >> sh;
+    uint32_t scp, mp;
+    if (c < 2) {
+        scp = A & 0x3f3fu;
+        mp = Z & 0x3f3fu;
+    } else {
+        scp = (W & 0x0f0fu) | ((A >> 2) & 0x3030u);
+        mp = ((W >> 4) & 0x0f0fu) | ((Z >> 2) & 0x3030u);
     }
+    const int isum = (int)(scp & 0xffu) * dlo + (int)(scp >> 8) * dhi;
+    const int msum = (int)(mp & 0xffu) * (int)(int16_t)(bs2 & 0xffffu) + (int)(mp >> 8) * ((int)bs2 >> 16);
+    const float d = h2f_bits(hdr.x & 0xffffu), dmin = h2f_bits(hdr.x >> 16);
+    return dx * (d * (float)isum - dmin * (float)msum);
 }
 
-// Q6_K: one "unit" per lane = half h, 16-column group p of a block: 16 bytes of ql (A), 16 of ql+32 (B),
-// 16 of qh give 64 weights in four scale groups 8h+2j+p, j = 0..3 (elements 128h + 32j + 16p + 0..15).
-// The -32 offset is taken out through the activation's 16-element sums instead of per byte.
-__device__ __forceinline__ float q6k_unit(const uint8_t* blk, int h, int p, const uint4* xv, const int* bsv) {
+// Q6_K quarter (h, p): half h, 16-column group p: 16 bytes of ql (A), 16 of ql+32 (B), 16 of qh give 64
+// weights in the four scale groups 8h+2j+p, j = 0..3 (elements 128h + 32j + 16p + 0..15).  The -32
+// offset is taken out through the activation's 16-element sums instead of per byte.
+__device__ __forceinline__ float q6k_quarter(const uint8_t* blk, int h, int p, const uint4 (&xv)[4], const int (&bsv)[4], float dx) {
     const uint4 A = lds16_a2(blk + 64 * h + 16 * p);
     const uint4 B = lds16_a2(blk + 64 * h + 32 + 16 * p);
     const uint4 H = lds16_a2(blk + 128 + 32 * h + 16 * p);
@@ -170,30 +184,11 @@ __device__ __forceinline__ float q6k_unit(const uint8_t* blk, int h, int p, cons
     const int isum = (int)sc[0] * (d0 - 32 * bsv[0]) + (int)sc[2] * (d1 - 32 * bsv[1]) +
                      (int)sc[4] * (d2 - 32 * bsv[2]) + (int)sc[6] * (d3 - 32 * bsv[3]);
     const float d = h2f_bits(*(const uint16_t*)(blk + 208));
-    return d * (float)isum;
+    return dx * (d * (float)isum);
 }
 
-__device__ __forceinline__ void dot_chunk_q6k(const uint8_t* ra, const uint8_t* rb, int b0, int b1, int kb0, const ActView& x,
-                                              int lane, float& acc0, float& acc1) {
-    const int h = (lane >> 1) & 1, p = lane & 1;
-    for (int b = b0 + (lane >> 2); b < b1; b += 8) {
-        const int kb = kb0 + b;
-        const int8_t* xb = x.q + kb * 256 + 128 * h + 16 * p;
-        uint4 xv[4];
-        int bsv[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            xv[j] = *(const uint4*)(xb + 32 * j);
-            bsv[j] = x.bs[kb * 16 + 8 * h + 2 * j + p];
-        }
-        const float dx = x.d[kb];
-        acc0 += dx * q6k_unit(ra + b * 210, h, p, xv, bsv);
-        acc1 += dx * q6k_unit(rb + b * 210, h, p, xv, bsv);
-    }
-}
-
-// Q8_0: one 34-byte block per lane.
-__device__ __forceinline__ float q80_block(const uint8_t* blk, const uint4& x0, const uint4& x1) {
+// Q8_0: one 34-byte block per lane per step
+__device__ __forceinline__ float q80_block(const uint8_t* blk, const uint4& x0, const uint4& x1, float dx) {
     const uint4 a = lds16_a2(blk + 2), b = lds16_a2(blk + 18);
     int s = dp4a_ss(a.x, x0.x, 0);
     s = dp4a_ss(a.y, x0.y, s);
@@ -203,83 +198,68 @@ __device__ __forceinline__ float q80_block(const uint8_t* blk, const uint4& x0, 
     s = dp4a_ss(b.y, x1.y, s);
     s = dp4a_ss(b.z, x1.z, s);
     s = dp4a_ss(b.w, x1.w, s);
-    return (float)s * h2f_bits(*(const uint16_t*)blk);
+    // ggml: sumi * (d_w * d_x); keep that association
+    return (float)s * (h2f_bits(*(const uint16_t*)blk) * dx);
 }
-__device__ __forceinline__ void dot_chunk_q80(const uint8_t* ra, const uint8_t* rb, int b0, int b1, int kb0, const ActView& x,
-                                              int lane, float& acc0, float& acc1) {
-    for (int b = b0 + lane; b < b1; b += 32) {
-        const int kb = kb0 + b;
-        const uint4 x0 = *(const uint4*)(x.q + kb * 32), x1 = *(const uint4*)(x.q + kb * 32 + 16);
-        const float dx = x.d[kb];
-        // ggml: sumi * (d_w * d_x); keep that association
-        acc0 += q80_block(ra + b * 34, x0, x1) * dx;
-        acc1 += q80_block(rb + b * 34, x0, x1) * dx;
+
+// one warp's share of a K-chunk for the tile's 8 rows; `row` = this lane's row segment in the ring
+template <int ACT>
+__device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, int nb, int kb0, const ActView& x, int warp, int lane) {
+    float acc = 0.0f;
+    if (ACT == ACT_Q8K) {
+        const int c = lane & 3;
+        for (int b = warp; b < nb; b += NCW) {
+            const int kb = kb0 + b;
+            const float dx = x.d[kb];
+            if (type == B2_TYPE_Q6_K) {
+                const int h = c >> 1, p = c & 1;
+                const int8_t* xb = x.q + kb * 256 + 128 * h + 16 * p;
+                uint4 xv[4];
+                int bsv[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    xv[j] = *(const uint4*)(xb + 32 * j);
+                    bsv[j] = x.bs16[kb * 16 + 8 * h + 2 * j + p];
+                }
+                acc += q6k_quarter(row + b * 210, h, p, xv, bsv, dx);
+            } else {
+                const int8_t* xb = x.q + kb * 256 + 64 * c;
+                uint4 xv[4];
+                xv[0] = *(const uint4*)xb;          // sub-block 2c, elements 0..15
+                xv[1] = *(const uint4*)(xb + 16);   //               elements 16..31
+                xv[2] = *(const uint4*)(xb + 32);   // sub-block 2c+1
+                xv[3] = *(const uint4*)(xb + 48);
+                const uint32_t bs2 = *(const uint32_t*)(x.bs32 + kb * 8 + 2 * c);
+                if (type == B2_TYPE_Q4_K) acc += q4k_quarter(row + b * 144, c, xv, bs2, dx);
+                else acc += q5k_quarter(row + b * 176, c, xv, bs2, dx);
+            }
+        }
+    } else {
+        // 64-block chunk: warp w owns blocks [8w, 8w+8); lane (row, i) takes blocks 8w+i and 8w+i+4
+        const int i = lane & 3;
+        for (int b = warp * 8 + i; b < min(nb, warp * 8 + 8); b += 4) {
+            const int kb = kb0 + b;
+            const uint4 x0 = *(const uint4*)(x.q + kb * 32), x1 = *(const uint4*)(x.q + kb * 32 + 16);
+            acc += q80_block(row + b * 34, x0, x1, x.d[kb]);
+        }
     }
+    return acc;
 }
 
 // ------------------------------------------------------------------------------------------------
-// prologue: fp32 activation (optionally RMS-normalised) -> quantised copy in shared memory.
-// Latency-bound (one small vector out of L2), so every load a warp needs is issued before the first
-// use: warp w owns the 256-element spans w, w+8, ...; a lane holds 8 consecutive values of each.
+// prologue: fp32 activation (optionally RMS-normalised) -> quantised copy in the shared memory of
+// every CTA of the cluster.  Span s (256 elements) is quantised by warp (s / csize) % 8 of CTA
+// s % csize; lane l holds its 8 consecutive values.
 // ------------------------------------------------------------------------------------------------
-template <int ACT>
-__device__ __forceinline__ void quantise_span(const float (&v)[8], int base, int lane, int K, int8_t* xq, float* xd, int16_t* xbs) {
-    const int i0 = base + lane * 8;
-    int q[8];
-    if (ACT == ACT_Q8K) {
-        // first element with the largest magnitude (strict '>' scan in quantize_row_q8_K_ref)
-        float amax = 0.0f, mval = 0.0f;
-        int midx = 0;
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const float ax = fabsf(v[i]);
-            if (ax > amax) { amax = ax; mval = v[i]; midx = lane * 8 + i; }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
-            const float ov = __shfl_xor_sync(0xffffffffu, mval, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, midx, o);
-            if (oa > amax || (oa == amax && oi < midx)) { amax = oa; mval = ov; midx = oi; }
-        }
-        float d = 0.0f;
-        if (amax != 0.0f) {
-            const float iscale = -127.0f / mval;
-#pragma unroll
-            for (int i = 0; i < 8; i++) q[i] = min(127, __float2int_rn(iscale * v[i]));
-            d = 1.0f / iscale;
-        } else {
-#pragma unroll
-            for (int i = 0; i < 8; i++) q[i] = 0;
-        }
-        int s8 = 0;
-#pragma unroll
-        for (int i = 0; i < 8; i++) s8 += q[i];
-        s8 += __shfl_xor_sync(0xffffffffu, s8, 1);
-        if (i0 < K) {
-            if ((lane & 1) == 0) xbs[(base >> 4) + (lane >> 1)] = (int16_t)s8;
-            if (lane == 0) xd[base >> 8] = d;
-        }
-    } else {
-        // Q8_0: 32-element blocks = 4 lanes
-        float amax = 0.0f;
-#pragma unroll
-        for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
-        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-        const float d = amax / 127.0f;
-        const float id = d != 0.0f ? 1.0f / d : 0.0f;
-#pragma unroll
-        for (int i = 0; i < 8; i++) q[i] = (int)roundf(v[i] * id);
-        if (i0 < K && (lane & 3) == 0) xd[i0 >> 5] = __half2float(__float2half_rn(d));
-    }
-    if (i0 < K) {
-        uint2 pk;
-        pk.x = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
-        pk.y = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
-        *(uint2*)(xq + i0) = pk;
-    }
-}
+struct ActSmem {
+    int8_t* xq;
+    float* xd;
+    int16_t* bs16;
+    int16_t* bs32;
+    double* ss_span;   // [MAX_SPANS] per-span sum of squares (PRO_NORM)
+    uint64_t* xbar;    // completes when every span has arrived
+    uint64_t* ssbar;
+};
 
 __device__ __forceinline__ void load8(const float* p, int i0, int K, float (&v)[8]) {
     if (i0 < K) {
@@ -292,78 +272,157 @@ __device__ __forceinline__ void load8(const float* p, int i0, int K, float (&v)[
     }
 }
 
+// quantise one span held in v[] and store it into the shared memory of all `csize` CTAs
 template <int ACT>
-__device__ void build_activation(const GemvArgs& a, int8_t* xq, float* xd, int16_t* xbs, double* red, int tid) {
-    const int K = a.K;
-    const int lane = tid & 31, warp = tid >> 5;
-    const int nspans = (K + 255) >> 8;
-    if (a.prologue == PRO_NORM) {
-        // ggml rms_norm: sum of fp32 squares accumulated in double, mean, 1/sqrtf(mean + eps); then (x*scale)*w
-        constexpr int MB = 4;   // spans per warp kept in registers (d_model <= 8192); larger vectors are re-read
-        const bool resident = nspans <= NCW * MB;
-        float v[MB][8], w[MB][8];
-        double ss = 0.0;
-        for (int s0 = 0; s0 < nspans; s0 += NCW * MB) {
+__device__ __forceinline__ void quantise_span(const float (&v)[8], int base, int lane, int K, const ActSmem& sm,
+                                              const uint8_t* smem_base, uint32_t csize) {
+    const int i0 = base + lane * 8;
+    int q[8];
+    float d = 0.0f;
+    int s8 = 0, s16 = 0, s32 = 0;
+    if (ACT == ACT_Q8K) {
+        // the first element with the largest magnitude decides the sign of the scale
+        // (strict '>' scan in quantize_row_q8_K_ref)
+        float amax = 0.0f;
 #pragma unroll
-            for (int m = 0; m < MB; m++) {
-                const int base = (s0 + warp + m * NCW) << 8;
-                load8(a.x, base < K ? base + lane * 8 : K, K, v[m]);
-                if (resident) load8(a.norm_w, base < K ? base + lane * 8 : K, K, w[m]);
-            }
+        for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+        const float wmax = warp_max(amax);
+        int first = 8;
 #pragma unroll
-            for (int m = 0; m < MB; m++)
+        for (int i = 7; i >= 0; i--)
+            if (fabsf(v[i]) == wmax) first = i;
+        const uint32_t owners = __ballot_sync(0xffffffffu, first < 8);
+        float mval = 0.0f;
 #pragma unroll
-                for (int i = 0; i < 8; i++) ss += (double)(v[m][i] * v[m][i]);
+        for (int i = 0; i < 8; i++)
+            if (i == first) mval = v[i];
+        mval = __shfl_sync(0xffffffffu, mval, owners ? __ffs(owners) - 1 : 0);
+        if (wmax != 0.0f) {
+            const float iscale = -127.0f / mval;
+#pragma unroll
+            for (int i = 0; i < 8; i++) q[i] = min(127, __float2int_rn(iscale * v[i]));
+            d = 1.0f / iscale;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) q[i] = 0;
         }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-        if (lane == 0) red[warp] = ss;
-        named_bar_sync(1, NCT);
-        double tot = 0.0;
-#pragma unroll
-        for (int k = 0; k < NCW; k++) tot += red[k];
-        const float mean = (float)(tot / (double)K);
-        const float scale = 1.0f / sqrtf(mean + a.eps);
-        for (int s0 = 0; s0 < nspans; s0 += NCW * MB) {
-#pragma unroll
-            for (int m = 0; m < MB; m++) {
-                const int base = (s0 + warp + m * NCW) << 8;
-                if (!resident) {
-                    load8(a.x, base < K ? base + lane * 8 : K, K, v[m]);
-                    load8(a.norm_w, base < K ? base + lane * 8 : K, K, w[m]);
-                }
-            }
-#pragma unroll
-            for (int m = 0; m < MB; m++) {
-                const int base = (s0 + warp + m * NCW) << 8;
-                if (base < K) {   // warp-uniform
-#pragma unroll
-                    for (int i = 0; i < 8; i++) v[m][i] = (v[m][i] * scale) * w[m][i];
-                    quantise_span<ACT>(v[m], base, lane, K, xq, xd, xbs);
-                }
-            }
-        }
+        for (int i = 0; i < 8; i++) s8 += q[i];
+        s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
+        s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
     } else {
-        constexpr int MB = 8;
-        float v[MB][8];
-        for (int s0 = 0; s0 < nspans; s0 += NCW * MB) {
+        // Q8_0: 32-element blocks = 4 lanes
+        float amax = 0.0f;
 #pragma unroll
-            for (int m = 0; m < MB; m++) {
-                const int base = (s0 + warp + m * NCW) << 8;
-                load8(a.x, base < K ? base + lane * 8 : K, K, v[m]);
-            }
+        for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+        d = amax / 127.0f;
+        const float id = d != 0.0f ? 1.0f / d : 0.0f;
 #pragma unroll
-            for (int m = 0; m < MB; m++) {
-                const int base = (s0 + warp + m * NCW) << 8;
-                if (base < K) quantise_span<ACT>(v[m], base, lane, K, xq, xd, xbs);
+        for (int i = 0; i < 8; i++) q[i] = (int)roundf(v[i] * id);
+        d = __half2float(__float2half_rn(d));
+    }
+    const uint32_t pk0 = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
+    const uint32_t pk1 = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
+    if (i0 < K) {
+        const uint32_t o_q = (uint32_t)((const uint8_t*)(sm.xq + i0) - smem_base);
+        const uint32_t o_d = (uint32_t)((const uint8_t*)(sm.xd + (ACT == ACT_Q8K ? (base >> 8) : (i0 >> 5))) - smem_base);
+        const uint32_t o_16 = (uint32_t)((const uint8_t*)(sm.bs16 + (i0 >> 4)) - smem_base);
+        const uint32_t o_32 = (uint32_t)((const uint8_t*)(sm.bs32 + (i0 >> 5)) - smem_base);
+        for (uint32_t r = 0; r < csize; r++) {
+            const uint32_t pb = dsmem_addr(smem_base, r);
+            dsmem_st_v2(pb + o_q, pk0, pk1);
+            if (ACT == ACT_Q8K) {
+                if ((lane & 1) == 0) dsmem_st_u16(pb + o_16, (uint16_t)(int16_t)s16);
+                if ((lane & 3) == 0) dsmem_st_u16(pb + o_32, (uint16_t)(int16_t)s32);
+                if (lane == 0) dsmem_st_u32(pb + o_d, __float_as_uint(d));
+            } else {
+                if ((lane & 3) == 0) dsmem_st_u32(pb + o_d, __float_as_uint(d));
             }
         }
     }
-    named_bar_sync(1, NCT);
+    // publish: every lane's stores, then one arrival per peer
+    fence_cluster();
+    __syncwarp();
+    if (lane < (int)csize) mbar_arrive_remote(dsmem_addr(sm.xbar, (uint32_t)lane));
+}
+
+template <int ACT>
+__device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uint8_t* smem_base, int tid, uint32_t rank, uint32_t csize) {
+    const int K = a.K;
+    const int lane = tid & 31, warp = tid >> 5;
+    const int nspans = (K + 255) >> 8;
+    const int first = (int)rank + (int)csize * warp, stride = (int)csize * NCW;   // this warp's spans
+    float scale = 1.0f;
+    // the first two spans of a warp stay in registers across the norm reduction (with 8 CTAs sharing the
+    // work a warp rarely owns more); further spans are re-read
+    float v0[8], v1[8];
+    if (a.prologue == PRO_NORM) {
+        // ggml rms_norm: sum of fp32 squares accumulated in double, mean, 1/sqrtf(mean + eps); then (x*scale)*w
+        auto publish_ss = [&](const float (&t)[8], int s) {
+            double ss = 0.0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) ss += (double)(t[i] * t[i]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            const uint32_t off = (uint32_t)((const uint8_t*)(sm.ss_span + s) - smem_base);
+            if (lane < (int)csize) {
+                dsmem_st_f64(dsmem_addr(smem_base, (uint32_t)lane) + off, ss);
+                fence_cluster();
+                mbar_arrive_remote(dsmem_addr(sm.ssbar, (uint32_t)lane));
+            }
+        };
+        if (first < nspans) load8(a.x, (first << 8) + lane * 8, K, v0);
+        if (first + stride < nspans) load8(a.x, ((first + stride) << 8) + lane * 8, K, v1);
+        if (first < nspans) publish_ss(v0, first);
+        if (first + stride < nspans) publish_ss(v1, first + stride);
+        for (int s = first + 2 * stride; s < nspans; s += stride) {
+            float t[8];
+            load8(a.x, (s << 8) + lane * 8, K, t);
+            publish_ss(t, s);
+        }
+        mbar_wait_cluster(sm.ssbar, 0);
+        // every CTA adds the per-span sums in the same order: lane-strided, then a butterfly
+        double tot = 0.0;
+        for (int s = lane; s < nspans; s += 32) tot += sm.ss_span[s];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+        const float mean = (float)(tot / (double)K);
+        scale = 1.0f / sqrtf(mean + a.eps);
+    }
+    if (a.prologue == PRO_NORM) {
+        auto norm_quant = [&](float (&t)[8], int s) {
+            float w[8];
+            load8(a.norm_w, (s << 8) + lane * 8, K, w);
+#pragma unroll
+            for (int i = 0; i < 8; i++) t[i] = (t[i] * scale) * w[i];
+            quantise_span<ACT>(t, s << 8, lane, K, sm, smem_base, csize);
+        };
+        if (first < nspans) norm_quant(v0, first);
+        if (first + stride < nspans) norm_quant(v1, first + stride);
+        for (int s = first + 2 * stride; s < nspans; s += stride) {
+            float t[8];
+            load8(a.x, (s << 8) + lane * 8, K, t);
+            norm_quant(t, s);
+        }
+    } else {
+        // issue the loads of two spans before the first use
+        if (first < nspans) load8(a.x, (first << 8) + lane * 8, K, v0);
+        if (first + stride < nspans) load8(a.x, ((first + stride) << 8) + lane * 8, K, v1);
+        if (first < nspans) quantise_span<ACT>(v0, first << 8, lane, K, sm, smem_base, csize);
+        if (first + stride < nspans) quantise_span<ACT>(v1, (first + stride) << 8, lane, K, sm, smem_base, csize);
+        for (int s = first + 2 * stride; s < nspans; s += stride) {
+            float t[8];
+            load8(a.x, (s << 8) + lane * 8, K, t);
+            quantise_span<ACT>(t, s << 8, lane, K, sm, smem_base, csize);
+        }
+    }
+    mbar_wait_cluster(sm.xbar, 0);
 }
 
 // ------------------------------------------------------------------------------------------------
-// epilogue for one row pair (lane 0 of the consumer warp)
+// epilogue for one row pair
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void epilogue(const GemvArgs& a, const GemvSeg& s, int p, int ra, int rb, float va, float vb) {
     if (s.bias) {
@@ -424,23 +483,32 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
     uint8_t* ring = smem;
     uint64_t* full = (uint64_t*)(smem + GEMV_STAGES * G::STAGE_BYTES);
     uint64_t* empty = full + GEMV_STAGES;
-    double* red = (double*)(empty + GEMV_STAGES);
-    float* part = (float*)(red + NCW);                 // [2 parities][pairs][2 rows] partial sums of the odd warps
-    int8_t* xq = (int8_t*)(part + 2 * GEMV_TILE_PAIRS * 2);
+    ActSmem sm;
+    sm.xbar = empty + GEMV_STAGES;
+    sm.ssbar = sm.xbar + 1;
+    sm.ss_span = (double*)(sm.ssbar + 1);
+    float* red = (float*)(sm.ss_span + MAX_SPANS);   // [2 parities][NCW warps][TILE_ROWS]
     const int K = a.K;
-    float* xd = (float*)(xq + K);
-    int16_t* xbs = (int16_t*)(xd + (ACT == ACT_Q8K ? K / 256 : K / 32));
+    sm.xq = (int8_t*)(red + 2 * NCW * TILE_ROWS);
+    sm.xd = (float*)(sm.xq + K);
+    sm.bs16 = (int16_t*)(sm.xd + (ACT == ACT_Q8K ? K / 256 : K / 32));
+    sm.bs32 = sm.bs16 + K / 16;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = cluster_ctarank(), csize = cluster_nctarank();
+    const int nspans = (K + 255) >> 8;
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < GEMV_STAGES; s++) {
             mbar_init(&full[s], 1);
             mbar_init(&empty[s], NCW);
         }
+        mbar_init(sm.xbar, nspans);
+        mbar_init(sm.ssbar, nspans);
         mbar_fence_init();
     }
-    __syncthreads();
+    // peers store into this CTA's shared memory and arrive on its barriers: they must be initialised first
+    cluster_sync_all();
     // let the next kernel in the stream begin its own weight prefetch as early as possible
     pdl_launch_dependents();
 
@@ -455,17 +523,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
             while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
             const GemvSeg& s = a.seg[si];
             const int bb = block_bytes_of(s.type);
-            const uint8_t* rowp = nullptr;
-            if (lane < 2 * GEMV_TILE_PAIRS) {
-                const int p = (tile - s.tile0) * GEMV_TILE_PAIRS + (lane >> 1);
-                if (p < s.n_pairs) {
-                    int ra, rb;
-                    pair_rows(s, p, &ra, &rb);
-                    const int r = (lane & 1) ? rb : ra;
-                    const uint8_t* w = (s.pairing == PAIR_SPLIT && (lane & 1)) ? s.wb : s.wa;
-                    if (r >= 0) rowp = w + (size_t)r * nblk_row * bb;
-                }
-            }
+            const uint8_t* rowp = lane < TILE_ROWS ? slot_row_ptr(s, tile - s.tile0, lane, nblk_row * bb) : nullptr;
             for (int c = 0; c < n_chunks; c++) {
                 const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
                 const uint8_t* src = nullptr;
@@ -493,61 +551,54 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
 
     // ===== consumers =====
     pdl_wait();  // the activation vector is written by the previous kernel
-    build_activation<ACT>(a, xq, xd, xbs, red, tid);
-    const ActView xv{xq, xd, xbs};
+    build_activation<ACT>(a, sm, smem, tid, rank, csize);
+    const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};
 
-    // warps 2p and 2p+1 share row pair p of the tile and split each chunk's blocks between them
-    const int pw = warp >> 1, half = warp & 1;
+    const int r = lane >> 2;   // this lane's row slot in the tile
     int stage = 0, phase = 0, parity = 0;
     for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
         int si = 0;
         while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
         const GemvSeg& s = a.seg[si];
         const int bb = block_bytes_of(s.type);
-        const int p = (tile - s.tile0) * GEMV_TILE_PAIRS + pw;
-        const bool valid = p < s.n_pairs;
-        int ra = 0, rb = -1;
-        uint32_t offa = 0, offb = 0;
-        if (valid) {
-            pair_rows(s, p, &ra, &rb);
-            // byte offset of the row segment inside its ring slot = source address mod 16
-            const uint8_t* wb = s.pairing == PAIR_SPLIT ? s.wb : s.wa;
-            offa = (uint32_t)((uintptr_t)(s.wa + (size_t)ra * nblk_row * bb) & 15);
-            offb = (uint32_t)((uintptr_t)(wb + (size_t)(rb < 0 ? ra : rb) * nblk_row * bb) & 15);
-        }
-        const uint32_t chunk_step = (uint32_t)(G::CHUNK_BLOCKS * bb) & 15;  // alignment drift per chunk
-        float acc0 = 0.0f, acc1 = 0.0f;
+        const int ptile = tile - s.tile0;
+        const uint8_t* src = slot_row_ptr(s, ptile, r, nblk_row * bb);
+        const uint32_t off0 = (uint32_t)((uintptr_t)src & 15);               // row segment offset inside its slot
+        const uint32_t chunk_step = (uint32_t)(G::CHUNK_BLOCKS * bb) & 15;   // alignment drift per chunk
+        float acc = 0.0f;
         for (int c = 0; c < n_chunks; c++) {
             const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
-            // split in whole warp passes (4 blocks for Q4_K/Q5_K, 8 for Q6_K, 32 for Q8_0)
-            constexpr int GRAN = ACT == ACT_Q8K ? 8 : 32;
-            const int h0 = min(nb, ((nb + 2 * GRAN - 1) / (2 * GRAN)) * GRAN);
-            const int b0 = half ? h0 : 0, b1 = half ? nb : h0;
             mbar_wait(&full[stage], phase);
-            if (valid && b0 < b1) {
-                const uint8_t* slot = ring + stage * G::STAGE_BYTES + (2 * pw) * G::ROW_SLOT;
-                const uint8_t* pa = slot + ((offa + c * chunk_step) & 15);
-                const uint8_t* pb = slot + G::ROW_SLOT + ((offb + c * chunk_step) & 15);
-                if (rb < 0) pb = pa;
-                const int kb0 = c * G::CHUNK_BLOCKS;
-                if (ACT == ACT_Q8K) {
-                    if (s.type == B2_TYPE_Q4_K) dot_chunk_q4k(pa, pb, b0, b1, kb0, xv, lane, acc0, acc1);
-                    else if (s.type == B2_TYPE_Q6_K) dot_chunk_q6k(pa, pb, b0, b1, kb0, xv, lane, acc0, acc1);
-                    else dot_chunk_q5k(pa, pb, b0, b1, kb0, xv, lane, acc0, acc1);
-                } else {
-                    dot_chunk_q80(pa, pb, b0, b1, kb0, xv, lane, acc0, acc1);
-                }
+            if (src) {
+                const uint8_t* row = ring + stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
+                acc += dot_chunk<ACT>(s.type, row, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
         }
-        acc0 = warp_sum(acc0);
-        acc1 = warp_sum(acc1);
-        float* pp = part + (parity * GEMV_TILE_PAIRS + pw) * 2;
-        if (half && lane == 0) { pp[0] = acc0; pp[1] = acc1; }
-        named_bar_sync(2 + pw, 64);   // the pair's two warps
-        if (!half && lane == 0 && valid) epilogue(a, s, p, ra, rb, acc0 + pp[0], acc1 + pp[1]);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        float* rp = red + parity * NCW * TILE_ROWS;
+        if ((lane & 3) == 0) rp[warp * TILE_ROWS + r] = acc;
+        named_bar_sync(1, NCT);
+        if (warp == 0) {
+            // lane l < 8 owns row slot l: add the 8 warps' shares in a fixed order, then pair up
+            float v = 0.0f;
+            if (lane < TILE_ROWS) {
+#pragma unroll
+                for (int w = 0; w < NCW; w++) v += rp[w * TILE_ROWS + lane];
+            }
+            const float vo = __shfl_xor_sync(0xffffffffu, v, 1);
+            if (lane < TILE_ROWS && (lane & 1) == 0) {
+                const int p = ptile * GEMV_TILE_PAIRS + (lane >> 1);
+                if (p < s.n_pairs) {
+                    int ra, rb;
+                    pair_rows(s, p, &ra, &rb);
+                    epilogue(a, s, p, ra, rb, v, vo);
+                }
+            }
+        }
     }
 }
 
@@ -563,10 +614,11 @@ int gemv_act_for_type(int type) {
 
 size_t gemv_smem_bytes(int act, int K) {
     const size_t stage = act == ACT_Q8K ? Geo<ACT_Q8K>::STAGE_BYTES : Geo<ACT_Q80>::STAGE_BYTES;
-    size_t n = GEMV_STAGES * stage + 2 * GEMV_STAGES * sizeof(uint64_t) + NCW * sizeof(double) + 2 * GEMV_TILE_PAIRS * 2 * sizeof(float);
-    n += (size_t)K;                                           // int8 activations
+    size_t n = GEMV_STAGES * stage + (2 * GEMV_STAGES + 2) * sizeof(uint64_t) + MAX_SPANS * sizeof(double) +
+               2 * NCW * TILE_ROWS * sizeof(float);
+    n += (size_t)K;                                            // int8 activations
     n += (act == ACT_Q8K ? K / 256 : K / 32) * sizeof(float);  // block scales
-    if (act == ACT_Q8K) n += (size_t)K / 16 * sizeof(int16_t);
+    n += (size_t)K / 16 * sizeof(int16_t) + (size_t)K / 32 * sizeof(int16_t);
     return (n + 127) & ~(size_t)127;
 }
 
@@ -576,8 +628,8 @@ int gemv_finalize(GemvArgs& a, int act) {
         return B2_EINVAL;
     }
     const int kmult = act == ACT_Q8K ? 256 : 32;
-    if (a.K <= 0 || a.K % kmult || a.K % 8) {
-        set_error("gemv: K=%d is not a multiple of %d", a.K, kmult);
+    if (a.K <= 0 || a.K % kmult || a.K % 8 || a.K > MAX_SPANS * 256) {
+        set_error("gemv: K=%d must be a multiple of %d and at most %d", a.K, kmult, MAX_SPANS * 256);
         return B2_EINVAL;
     }
     if (((uintptr_t)a.x & 15) || (a.prologue == PRO_NORM && ((uintptr_t)a.norm_w & 15))) {
@@ -635,16 +687,31 @@ int launch_gemv(const GemvArgs& a, int act, cudaStream_t st, bool pdl) {
     if (ctas_per_sm < 1) ctas_per_sm = 1;
     int grid = g_num_sms * ctas_per_sm;
     if (grid > a.n_tiles) grid = a.n_tiles;
+    // the activation prologue is shared across a cluster of up to 8 CTAs
+    int cluster = 8;
+    while (cluster > 1 && grid < cluster) cluster >>= 1;
+    grid -= grid % cluster;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(GEMV_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (cluster > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = cluster;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        na++;
+    }
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    cfg.numAttrs = na;
     B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, a));
     return 0;
 }
