@@ -24,8 +24,11 @@
 //     8 CTAs of a cluster each quantise 1/8 of the 256-element spans and store the result into every
 //     peer's shared memory through DSMEM, signalling per-span on the peers' mbarriers.  (Done per CTA
 //     this prologue was 39% of all issued instructions.)
-//   * per tile the warps' partial sums meet in shared memory; warp 0 adds them in a fixed order and
-//     runs the fused epilogue on row pairs (RoPE pairs, gate/up pairs).
+//   * a decoder warp unpacks the 6-bit scale/min headers of a freshly landed stage once (128 headers)
+//     into ready-to-use records, instead of every lane of every compute warp doing it per quarter.
+//   * per tile the compute warps' partial sums are handed through shared memory + mbarriers to an
+//     epilogue warp that adds them in a fixed order and runs the fused epilogue on row pairs (RoPE
+//     pairs, gate/up pairs); compute warps never meet at a CTA barrier and never wait on a global load.
 #include "gemv.cuh"
 
 #include "common.h"
@@ -46,7 +49,24 @@ struct Geo {
     static constexpr int CHUNK_BLOCKS = ACT == ACT_Q8K ? 16 : 64;
     static constexpr int ROW_SLOT = ACT == ACT_Q8K ? (16 * 210 + 16) : (64 * 34 + 16);
     static constexpr int STAGE_BYTES = TILE_ROWS * ROW_SLOT;
+    // decoded Q4_K/Q5_K headers of one stage: 32 bytes per (row, block)
+    static constexpr int DEC_BYTES = ACT == ACT_Q8K ? TILE_ROWS * CHUNK_BLOCKS * 32 : 0;
 };
+
+// decoded header record: {float d, float dmin, pad, pad, w[4]} with w[c] = bytes (sc[2c], sc[2c+1], m[2c], m[2c+1])
+__device__ __forceinline__ void decode_k4_header(const uint8_t* blk, uint8_t* rec) {
+    const uint4 hdr = *(const uint4*)blk;
+    const uint32_t sc_lo = hdr.y & 0x3f3f3f3fu, m_lo = hdr.z & 0x3f3f3f3fu;
+    const uint32_t sc_hi = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+    const uint32_t m_hi = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+    uint4 w;
+    w.x = __byte_perm(sc_lo, m_lo, 0x5410);
+    w.y = __byte_perm(sc_lo, m_lo, 0x7632);
+    w.z = __byte_perm(sc_hi, m_hi, 0x5410);
+    w.w = __byte_perm(sc_hi, m_hi, 0x7632);
+    *(float2*)rec = make_float2(h2f_bits(hdr.x & 0xffffu), h2f_bits(hdr.x >> 16));
+    *(uint4*)(rec + 16) = w;
+}
 
 __host__ __device__ inline int block_bytes_of(int type) {
     switch (type) {
@@ -98,45 +118,32 @@ struct ActView {
 // inner products: one lane = one quarter of a (row, super-block)
 // ------------------------------------------------------------------------------------------------
 // Q4_K quarter c: qs[32c .. 32c+31]; low nibbles are sub-block 2c, high nibbles sub-block 2c+1.
-__device__ __forceinline__ float q4k_quarter(const uint8_t* blk, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
-    const uint4 hdr = *(const uint4*)blk;
+// rec = the decoded header record of this (row, block).
+__device__ __forceinline__ float k4_finish(const uint8_t* rec, int c, int dlo, int dhi, uint32_t bs2, float dx) {
+    const float2 dd = *(const float2*)rec;
+    const uint32_t w = *(const uint32_t*)(rec + 16 + 4 * c);
+    const int isum = (int)(w & 0xffu) * dlo + (int)((w >> 8) & 0xffu) * dhi;
+    const int msum = (int)((w >> 16) & 0xffu) * (int)(int16_t)(bs2 & 0xffffu) + (int)(w >> 24) * ((int)bs2 >> 16);
+    return dx * (dd.x * (float)isum - dd.y * (float)msum);
+}
+
+__device__ __forceinline__ float q4k_quarter(const uint8_t* blk, const uint8_t* rec, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
     const uint4 q0 = *(const uint4*)(blk + 16 + 32 * c), q1 = *(const uint4*)(blk + 32 + 32 * c);
-    int dlo = dp4a_ss(q0.x & 0x0F0F0F0Fu, xv[0].x, 0);
-    int dhi = dp4a_us(q0.x & 0xF0F0F0F0u, xv[2].x, 0);
-    dlo = dp4a_ss(q0.y & 0x0F0F0F0Fu, xv[0].y, dlo);
-    dhi = dp4a_us(q0.y & 0xF0F0F0F0u, xv[2].y, dhi);
-    dlo = dp4a_ss(q0.z & 0x0F0F0F0Fu, xv[0].z, dlo);
-    dhi = dp4a_us(q0.z & 0xF0F0F0F0u, xv[2].z, dhi);
-    dlo = dp4a_ss(q0.w & 0x0F0F0F0Fu, xv[0].w, dlo);
-    dhi = dp4a_us(q0.w & 0xF0F0F0F0u, xv[2].w, dhi);
-    dlo = dp4a_ss(q1.x & 0x0F0F0F0Fu, xv[1].x, dlo);
-    dhi = dp4a_us(q1.x & 0xF0F0F0F0u, xv[3].x, dhi);
-    dlo = dp4a_ss(q1.y & 0x0F0F0F0Fu, xv[1].y, dlo);
-    dhi = dp4a_us(q1.y & 0xF0F0F0F0u, xv[3].y, dhi);
-    dlo = dp4a_ss(q1.z & 0x0F0F0F0Fu, xv[1].z, dlo);
-    dhi = dp4a_us(q1.z & 0xF0F0F0F0u, xv[3].z, dhi);
-    dlo = dp4a_ss(q1.w & 0x0F0F0F0Fu, xv[1].w, dlo);
-    dhi = dp4a_us(q1.w & 0xF0F0F0F0u, xv[3].w, dhi);
-    // 6-bit scale / min pairs (2c, 2c+1) of get_scale_min_k4, as two packed bytes each
-    const int sh = (c & 1) * 16;
-    const uint32_t A = hdr.y >> sh, Z = hdr.z >> sh, W = hdr.w >> sh;
-    uint32_t scp, mp;
-    if (c < 2) {
-        scp = A & 0x3f3fu;
-        mp = Z & 0x3f3fu;
-    } else {
-        scp = (W & 0x0f0fu) | ((A >> 2) & 0x3030u);
-        mp = ((W >> 4) & 0x0f0fu) | ((Z >> 2) & 0x3030u);
-    }
-    const int isum = (int)(scp & 0xffu) * dlo + (int)(scp >> 8) * (dhi >> 4);   // dhi is an exact multiple of 16
-    const int msum = (int)(mp & 0xffu) * (int)(int16_t)(bs2 & 0xffffu) + (int)(mp >> 8) * ((int)bs2 >> 16);
-    const float d = h2f_bits(hdr.x & 0xffffu), dmin = h2f_bits(hdr.x >> 16);
-    return dx * (d * (float)isum - dmin * (float)msum);
+    // four independent accumulation chains
+    int l0 = dp4a_ss(q0.x & 0x0F0F0F0Fu, xv[0].x, 0), h0 = dp4a_us(q0.x & 0xF0F0F0F0u, xv[2].x, 0);
+    int l1 = dp4a_ss(q1.x & 0x0F0F0F0Fu, xv[1].x, 0), h1 = dp4a_us(q1.x & 0xF0F0F0F0u, xv[3].x, 0);
+    l0 = dp4a_ss(q0.y & 0x0F0F0F0Fu, xv[0].y, l0); h0 = dp4a_us(q0.y & 0xF0F0F0F0u, xv[2].y, h0);
+    l1 = dp4a_ss(q1.y & 0x0F0F0F0Fu, xv[1].y, l1); h1 = dp4a_us(q1.y & 0xF0F0F0F0u, xv[3].y, h1);
+    l0 = dp4a_ss(q0.z & 0x0F0F0F0Fu, xv[0].z, l0); h0 = dp4a_us(q0.z & 0xF0F0F0F0u, xv[2].z, h0);
+    l1 = dp4a_ss(q1.z & 0x0F0F0F0Fu, xv[1].z, l1); h1 = dp4a_us(q1.z & 0xF0F0F0F0u, xv[3].z, h1);
+    l0 = dp4a_ss(q0.w & 0x0F0F0F0Fu, xv[0].w, l0); h0 = dp4a_us(q0.w & 0xF0F0F0F0u, xv[2].w, h0);
+    l1 = dp4a_ss(q1.w & 0x0F0F0F0Fu, xv[1].w, l1); h1 = dp4a_us(q1.w & 0xF0F0F0F0u, xv[3].w, h1);
+    // the high-nibble dot is an exact multiple of 16
+    return k4_finish(rec, c, l0 + l1, (h0 + h1) >> 4, bs2, dx);
 }
 
 // Q5_K quarter c: as Q4_K plus bit 2c / 2c+1 of qh[0..31] as the fifth bit.
-__device__ __forceinline__ float q5k_quarter(const uint8_t* blk, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
-    const uint4 hdr = *(const uint4*)blk;
+__device__ __forceinline__ float q5k_quarter(const uint8_t* blk, const uint8_t* rec, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
     const uint4 h0 = *(const uint4*)(blk + 16), h1 = *(const uint4*)(blk + 32);
     const uint4 q0 = *(const uint4*)(blk + 48 + 32 * c), q1 = *(const uint4*)(blk + 64 + 32 * c);
     const int s0 = 2 * c, s1 = 2 * c + 1;
@@ -149,20 +156,7 @@ __device__ __forceinline__ float q5k_quarter(const uint8_t* blk, int c, const ui
     B2_Q5_STEP(q1, h1, xv[1], xv[3], x) B2_Q5_STEP(q1, h1, xv[1], xv[3], y)
     B2_Q5_STEP(q1, h1, xv[1], xv[3], z) B2_Q5_STEP(q1, h1, xv[1], xv[3], w)
 #undef B2_Q5_STEP
-    const int sh = (c & 1) * 16;
-    const uint32_t A = hdr.y >> sh, Z = hdr.z >> sh, W = hdr.w >> sh;
-    uint32_t scp, mp;
-    if (c < 2) {
-        scp = A & 0x3f3fu;
-        mp = Z & 0x3f3fu;
-    } else {
-        scp = (W & 0x0f0fu) | ((A >> 2) & 0x3030u);
-        mp = ((W >> 4) & 0x0f0fu) | ((Z >> 2) & 0x3030u);
-    }
-    const int isum = (int)(scp & 0xffu) * dlo + (int)(scp >> 8) * dhi;
-    const int msum = (int)(mp & 0xffu) * (int)(int16_t)(bs2 & 0xffffu) + (int)(mp >> 8) * ((int)bs2 >> 16);
-    const float d = h2f_bits(hdr.x & 0xffffu), dmin = h2f_bits(hdr.x >> 16);
-    return dx * (d * (float)isum - dmin * (float)msum);
+    return k4_finish(rec, c, dlo, dhi, bs2, dx);
 }
 
 // Q6_K quarter (h, p): half h, 16-column group p: 16 bytes of ql (A), 16 of ql+32 (B), 16 of qh give 64
@@ -204,7 +198,8 @@ __device__ __forceinline__ float q80_block(const uint8_t* blk, const uint4& x0, 
 
 // one warp's share of a K-chunk for the tile's 8 rows; `row` = this lane's row segment in the ring
 template <int ACT>
-__device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, int nb, int kb0, const ActView& x, int warp, int lane) {
+__device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, const uint8_t* dec_row, int nb, int kb0, const ActView& x,
+                                           int warp, int lane) {
     float acc = 0.0f;
     if (ACT == ACT_Q8K) {
         const int c = lane & 3;
@@ -230,8 +225,8 @@ __device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, int nb,
                 xv[2] = *(const uint4*)(xb + 32);   // sub-block 2c+1
                 xv[3] = *(const uint4*)(xb + 48);
                 const uint32_t bs2 = *(const uint32_t*)(x.bs32 + kb * 8 + 2 * c);
-                if (type == B2_TYPE_Q4_K) acc += q4k_quarter(row + b * 144, c, xv, bs2, dx);
-                else acc += q5k_quarter(row + b * 176, c, xv, bs2, dx);
+                if (type == B2_TYPE_Q4_K) acc += q4k_quarter(row + b * 144, dec_row + b * 32, c, xv, bs2, dx);
+                else acc += q5k_quarter(row + b * 176, dec_row + b * 32, c, xv, bs2, dx);
             }
         }
     } else {
@@ -476,15 +471,22 @@ __device__ __forceinline__ void epilogue(const GemvArgs& a, const GemvSeg& s, in
     }
 }
 
+// warp roles
+constexpr int W_PRODUCER = NCW, W_DECODER = NCW + 1, W_EPILOGUE = NCW + 2;
+
 template <int ACT>
 __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_constant__ GemvArgs a) {
     using G = Geo<ACT>;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* ring = smem;
-    uint64_t* full = (uint64_t*)(smem + GEMV_STAGES * G::STAGE_BYTES);
-    uint64_t* empty = full + GEMV_STAGES;
+    uint8_t* dec = smem + GEMV_STAGES * G::STAGE_BYTES;
+    uint64_t* full = (uint64_t*)(dec + GEMV_STAGES * G::DEC_BYTES);   // data landed            (producer -> decoder)
+    uint64_t* ready = full + GEMV_STAGES;                             // headers decoded        (decoder -> compute)
+    uint64_t* empty = ready + GEMV_STAGES;                            // stage consumed         (compute -> producer)
+    uint64_t* part_full = empty + GEMV_STAGES;                        // [2] partial sums written (compute -> epilogue)
+    uint64_t* part_free = part_full + 2;                              // [2] partial sums read    (epilogue -> compute)
     ActSmem sm;
-    sm.xbar = empty + GEMV_STAGES;
+    sm.xbar = part_free + 2;
     sm.ssbar = sm.xbar + 1;
     sm.ss_span = (double*)(sm.ssbar + 1);
     float* red = (float*)(sm.ss_span + MAX_SPANS);   // [2 parities][NCW warps][TILE_ROWS]
@@ -501,8 +503,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
 #pragma unroll
         for (int s = 0; s < GEMV_STAGES; s++) {
             mbar_init(&full[s], 1);
+            mbar_init(&ready[s], 1);
             mbar_init(&empty[s], NCW);
         }
+        mbar_init(&part_full[0], NCW);
+        mbar_init(&part_full[1], NCW);
+        mbar_init(&part_free[0], 1);
+        mbar_init(&part_free[1], 1);
         mbar_init(sm.xbar, nspans);
         mbar_init(sm.ssbar, nspans);
         mbar_fence_init();
@@ -515,11 +522,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
     const int nblk_row = K / (ACT == ACT_Q8K ? 256 : 32);
     const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
 
-    if (warp == NCW) {
+    if (warp == W_PRODUCER) {
         // ===== producer: weights only, independent of the previous kernel's output =====
-        int stage = 0, phase = 0;
+        int stage = 0, phase = 0, si = 0;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
-            int si = 0;
             while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
             const GemvSeg& s = a.seg[si];
             const int bb = block_bytes_of(s.type);
@@ -549,49 +555,52 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
         return;
     }
 
-    // ===== consumers =====
-    pdl_wait();  // the activation vector is written by the previous kernel
-    build_activation<ACT>(a, sm, smem, tid, rank, csize);
-    const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};
-
-    const int r = lane >> 2;   // this lane's row slot in the tile
-    int stage = 0, phase = 0, parity = 0;
-    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
-        int si = 0;
-        while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
-        const GemvSeg& s = a.seg[si];
-        const int bb = block_bytes_of(s.type);
-        const int ptile = tile - s.tile0;
-        const uint8_t* src = slot_row_ptr(s, ptile, r, nblk_row * bb);
-        const uint32_t off0 = (uint32_t)((uintptr_t)src & 15);               // row segment offset inside its slot
-        const uint32_t chunk_step = (uint32_t)(G::CHUNK_BLOCKS * bb) & 15;   // alignment drift per chunk
-        float acc = 0.0f;
-        for (int c = 0; c < n_chunks; c++) {
-            const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
-            mbar_wait(&full[stage], phase);
-            if (src) {
-                const uint8_t* row = ring + stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
-                acc += dot_chunk<ACT>(s.type, row, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
+    if (warp == W_DECODER) {
+        // ===== decoder: unpack the Q4_K / Q5_K scale headers of each landed stage once =====
+        int stage = 0, phase = 0, si = 0;
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
+            const int type = a.seg[si].type;
+            const int bb = block_bytes_of(type);
+            for (int c = 0; c < n_chunks; c++) {
+                const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
+                mbar_wait(&full[stage], phase);
+                if (ACT == ACT_Q8K && (type == B2_TYPE_Q4_K || type == B2_TYPE_Q5_K)) {
+                    // Q4_K / Q5_K rows are 16-byte aligned in their slots
+                    for (int i = lane; i < TILE_ROWS * nb; i += 32) {
+                        const int rr = i / nb, b = i - rr * nb;
+                        decode_k4_header(ring + stage * G::STAGE_BYTES + rr * G::ROW_SLOT + b * bb,
+                                         dec + stage * G::DEC_BYTES + (rr * G::CHUNK_BLOCKS + b) * 32);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ready[stage]);
+                if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[stage]);
-            if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
         }
-        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-        float* rp = red + parity * NCW * TILE_ROWS;
-        if ((lane & 3) == 0) rp[warp * TILE_ROWS + r] = acc;
-        named_bar_sync(1, NCT);
-        if (warp == 0) {
-            // lane l < 8 owns row slot l: add the 8 warps' shares in a fixed order, then pair up
+        return;
+    }
+
+    if (warp == W_EPILOGUE) {
+        // ===== epilogue: add the compute warps' shares in a fixed order, finish row pairs =====
+        pdl_wait();   // the epilogue reads and writes activations of the previous kernel
+        int parity = 0, ph = 0, si = 0;   // ph: bit p = phase of part_full[p]
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
+            while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
+            const GemvSeg& s = a.seg[si];
+            mbar_wait(&part_full[parity], (ph >> parity) & 1);
+            const float* rp = red + parity * NCW * TILE_ROWS;
             float v = 0.0f;
             if (lane < TILE_ROWS) {
 #pragma unroll
                 for (int w = 0; w < NCW; w++) v += rp[w * TILE_ROWS + lane];
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&part_free[parity]);
+            ph ^= 1 << parity;
             const float vo = __shfl_xor_sync(0xffffffffu, v, 1);
             if (lane < TILE_ROWS && (lane & 1) == 0) {
-                const int p = ptile * GEMV_TILE_PAIRS + (lane >> 1);
+                const int p = (tile - s.tile0) * GEMV_TILE_PAIRS + (lane >> 1);
                 if (p < s.n_pairs) {
                     int ra, rb;
                     pair_rows(s, p, &ra, &rb);
@@ -599,6 +608,45 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
                 }
             }
         }
+        return;
+    }
+
+    // ===== compute warps =====
+    pdl_wait();  // the activation vector is written by the previous kernel
+    build_activation<ACT>(a, sm, smem, tid, rank, csize);
+    const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};
+
+    const int r = lane >> 2;   // this lane's row slot in the tile
+    int stage = 0, phase = 0, parity = 0, fph = 3, si = 0;   // fph: bit p = phase of part_free[p]
+    for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
+        while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
+        const GemvSeg& s = a.seg[si];
+        const int type = s.type;
+        const int bb = block_bytes_of(type);
+        // row segment offset inside its ring slot (source address mod 16): zero for the 16-byte-multiple
+        // Q4_K / Q5_K blocks, row dependent for Q6_K / Q8_0.  Rows that do not exist (last tile of a
+        // segment) are computed on whatever the slot holds and ignored by the epilogue.
+        uint32_t off0 = 0;
+        if (ACT != ACT_Q8K || type == B2_TYPE_Q6_K) off0 = (uint32_t)((uintptr_t)slot_row_ptr(s, tile - s.tile0, r, nblk_row * bb) & 15);
+        const uint32_t chunk_step = (uint32_t)(G::CHUNK_BLOCKS * bb) & 15;   // alignment drift per chunk
+        float acc = 0.0f;
+        for (int c = 0; c < n_chunks; c++) {
+            const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
+            mbar_wait(&ready[stage], phase);
+            const uint8_t* row = ring + stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
+            acc += dot_chunk<ACT>(type, row, dec + stage * G::DEC_BYTES + r * G::CHUNK_BLOCKS * 32, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[stage]);
+            if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        // hand the 8 row sums of this warp's K share to the epilogue warp
+        mbar_wait(&part_free[parity], (fph >> parity) & 1);
+        fph ^= 1 << parity;
+        if ((lane & 3) == 0) red[(parity * NCW + warp) * TILE_ROWS + r] = acc;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&part_full[parity]);
     }
 }
 
@@ -614,7 +662,8 @@ int gemv_act_for_type(int type) {
 
 size_t gemv_smem_bytes(int act, int K) {
     const size_t stage = act == ACT_Q8K ? Geo<ACT_Q8K>::STAGE_BYTES : Geo<ACT_Q80>::STAGE_BYTES;
-    size_t n = GEMV_STAGES * stage + (2 * GEMV_STAGES + 2) * sizeof(uint64_t) + MAX_SPANS * sizeof(double) +
+    const size_t decb = act == ACT_Q8K ? Geo<ACT_Q8K>::DEC_BYTES : Geo<ACT_Q80>::DEC_BYTES;
+    size_t n = GEMV_STAGES * (stage + decb) + (3 * GEMV_STAGES + 6) * sizeof(uint64_t) + MAX_SPANS * sizeof(double) +
                2 * NCW * TILE_ROWS * sizeof(float);
     n += (size_t)K;                                            // int8 activations
     n += (act == ACT_Q8K ? K / 256 : K / 32) * sizeof(float);  // block scales

@@ -48,7 +48,7 @@ struct GemvArgs {
 };
 
 constexpr int GEMV_CONSUMER_WARPS = 8;
-constexpr int GEMV_THREADS = (GEMV_CONSUMER_WARPS + 1) * 32;
+constexpr int GEMV_THREADS = (GEMV_CONSUMER_WARPS + 3) * 32;  // + producer, header decoder, epilogue warps
 constexpr int GEMV_TILE_PAIRS = GEMV_CONSUMER_WARPS / 2;  // two consumer warps per row pair (K split)
 constexpr int GEMV_STAGES = 3;
 
