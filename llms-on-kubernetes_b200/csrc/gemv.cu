@@ -486,9 +486,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
     uint64_t* part_full = empty + GEMV_STAGES;                        // [2] partial sums written (compute -> epilogue)
     uint64_t* part_free = part_full + 2;                              // [2] partial sums read    (epilogue -> compute)
     ActSmem sm;
-    sm.xbar = part_free + 2;
+    sm.xbar = part_free + 2;   // 15 barriers so far; ss_span starts after a pad to keep 16-byte alignment below
     sm.ssbar = sm.xbar + 1;
-    sm.ss_span = (double*)(sm.ssbar + 1);
+    sm.ss_span = (double*)(sm.ssbar + 2);
     float* red = (float*)(sm.ss_span + MAX_SPANS);   // [2 parities][NCW warps][TILE_ROWS]
     const int K = a.K;
     sm.xq = (int8_t*)(red + 2 * NCW * TILE_ROWS);
@@ -663,7 +663,7 @@ int gemv_act_for_type(int type) {
 size_t gemv_smem_bytes(int act, int K) {
     const size_t stage = act == ACT_Q8K ? Geo<ACT_Q8K>::STAGE_BYTES : Geo<ACT_Q80>::STAGE_BYTES;
     const size_t decb = act == ACT_Q8K ? Geo<ACT_Q8K>::DEC_BYTES : Geo<ACT_Q80>::DEC_BYTES;
-    size_t n = GEMV_STAGES * (stage + decb) + (3 * GEMV_STAGES + 6) * sizeof(uint64_t) + MAX_SPANS * sizeof(double) +
+    size_t n = GEMV_STAGES * (stage + decb) + (3 * GEMV_STAGES + 7) * sizeof(uint64_t) + MAX_SPANS * sizeof(double) +
                2 * NCW * TILE_ROWS * sizeof(float);
     n += (size_t)K;                                            // int8 activations
     n += (act == ACT_Q8K ? K / 256 : K / 32) * sizeof(float);  // block scales
