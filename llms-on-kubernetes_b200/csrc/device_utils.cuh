@@ -92,10 +92,14 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t pa
         : "memory");
     return ok != 0;
 }
+// poll with CTA-scope probes (a cluster-scope acquire invalidates L1 on every probe), then acquire once
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
 #pragma unroll 1
     for (uint32_t i = 0; i < (1u << 22); i++)
-        if (mbar_try_wait_cluster(bar, parity)) return;
+        if (mbar_try_wait(bar, parity)) {
+            mbar_try_wait_cluster(bar, parity);
+            return;
+        }
     asm volatile("trap;");
 }
 

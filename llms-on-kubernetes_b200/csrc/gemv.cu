@@ -50,8 +50,15 @@ struct Geo {
     static constexpr int ROW_SLOT = ACT == ACT_Q8K ? (16 * 210 + 16) : (64 * 34 + 16);
     static constexpr int STAGE_BYTES = TILE_ROWS * ROW_SLOT;
     // decoded Q4_K/Q5_K headers of one stage: 32 bytes per (row, block)
-    static constexpr int DEC_BYTES = ACT == ACT_Q8K ? TILE_ROWS * CHUNK_BLOCKS * 32 : 0;
+    // (row stride padded by 16 bytes so the 8 rows a warp reads at once fall into different banks)
+    static constexpr int DEC_ROW = CHUNK_BLOCKS * 32 + 16;
+    static constexpr int DEC_BYTES = ACT == ACT_Q8K ? TILE_ROWS * DEC_ROW : 0;
 };
+
+// The int8 activations are stored with a bank swizzle inside every 256-byte span: 16-byte granule g
+// lives at granule g ^ ((g & 8) >> 2).  A warp reads four granules 64 bytes apart (Q4_K/Q5_K quarters)
+// or two pairs 128 bytes apart (Q6_K quarters) in one LDS.128; unswizzled, those alias two-way.
+__device__ __forceinline__ int xswz(int g) { return g ^ ((g & 8) >> 2); }
 
 // decoded header record: {float d, float dmin, pad, pad, w[4]} with w[c] = bytes (sc[2c], sc[2c+1], m[2c], m[2c+1])
 __device__ __forceinline__ void decode_k4_header(const uint8_t* blk, uint8_t* rec) {
@@ -208,22 +215,22 @@ __device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, const u
             const float dx = x.d[kb];
             if (type == B2_TYPE_Q6_K) {
                 const int h = c >> 1, p = c & 1;
-                const int8_t* xb = x.q + kb * 256 + 128 * h + 16 * p;
+                const int8_t* xb = x.q + kb * 256;
                 uint4 xv[4];
                 int bsv[4];
 #pragma unroll
                 for (int j = 0; j < 4; j++) {
-                    xv[j] = *(const uint4*)(xb + 32 * j);
+                    xv[j] = *(const uint4*)(xb + 16 * xswz(8 * h + p + 2 * j));
                     bsv[j] = x.bs16[kb * 16 + 8 * h + 2 * j + p];
                 }
                 acc += q6k_quarter(row + b * 210, h, p, xv, bsv, dx);
             } else {
-                const int8_t* xb = x.q + kb * 256 + 64 * c;
+                const int8_t* xb = x.q + kb * 256;
                 uint4 xv[4];
-                xv[0] = *(const uint4*)xb;          // sub-block 2c, elements 0..15
-                xv[1] = *(const uint4*)(xb + 16);   //               elements 16..31
-                xv[2] = *(const uint4*)(xb + 32);   // sub-block 2c+1
-                xv[3] = *(const uint4*)(xb + 48);
+                xv[0] = *(const uint4*)(xb + 16 * xswz(4 * c));       // sub-block 2c, elements 0..15
+                xv[1] = *(const uint4*)(xb + 16 * xswz(4 * c + 1));   //               elements 16..31
+                xv[2] = *(const uint4*)(xb + 16 * xswz(4 * c + 2));   // sub-block 2c+1
+                xv[3] = *(const uint4*)(xb + 16 * xswz(4 * c + 3));
                 const uint32_t bs2 = *(const uint32_t*)(x.bs32 + kb * 8 + 2 * c);
                 if (type == B2_TYPE_Q4_K) acc += q4k_quarter(row + b * 144, dec_row + b * 32, c, xv, bs2, dx);
                 else acc += q5k_quarter(row + b * 176, dec_row + b * 32, c, xv, bs2, dx);
@@ -321,7 +328,8 @@ __device__ __forceinline__ void quantise_span(const float (&v)[8], int base, int
     const uint32_t pk0 = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
     const uint32_t pk1 = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
     if (i0 < K) {
-        const uint32_t o_q = (uint32_t)((const uint8_t*)(sm.xq + i0) - smem_base);
+        const int qpos = ACT == ACT_Q8K ? base + 16 * xswz(lane >> 1) + 8 * (lane & 1) : i0;
+        const uint32_t o_q = (uint32_t)((const uint8_t*)(sm.xq + qpos) - smem_base);
         const uint32_t o_d = (uint32_t)((const uint8_t*)(sm.xd + (ACT == ACT_Q8K ? (base >> 8) : (i0 >> 5))) - smem_base);
         const uint32_t o_16 = (uint32_t)((const uint8_t*)(sm.bs16 + (i0 >> 4)) - smem_base);
         const uint32_t o_32 = (uint32_t)((const uint8_t*)(sm.bs32 + (i0 >> 5)) - smem_base);
@@ -570,7 +578,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
                     for (int i = lane; i < TILE_ROWS * nb; i += 32) {
                         const int rr = i / nb, b = i - rr * nb;
                         decode_k4_header(ring + stage * G::STAGE_BYTES + rr * G::ROW_SLOT + b * bb,
-                                         dec + stage * G::DEC_BYTES + (rr * G::CHUNK_BLOCKS + b) * 32);
+                                         dec + stage * G::DEC_BYTES + rr * G::DEC_ROW + b * 32);
                     }
                 }
                 __syncwarp();
@@ -634,7 +642,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
             const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
             mbar_wait(&ready[stage], phase);
             const uint8_t* row = ring + stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
-            acc += dot_chunk<ACT>(type, row, dec + stage * G::DEC_BYTES + r * G::CHUNK_BLOCKS * 32, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
+            acc += dot_chunk<ACT>(type, row, dec + stage * G::DEC_BYTES + r * G::DEC_ROW, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
