@@ -31,6 +31,8 @@
 //     pairs, gate/up pairs); compute warps never meet at a CTA barrier and never wait on a global load.
 #include "gemv.cuh"
 
+#include <cstdlib>
+
 #include "common.h"
 #include "device_utils.cuh"
 
@@ -742,14 +744,20 @@ int launch_gemv(const GemvArgs& a, int act, cudaStream_t st, bool pdl) {
     int ctas_per_sm = (int)((227 * 1024) / (smem + 1024));
     if (ctas_per_sm > 2) ctas_per_sm = 2;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
-    int grid = g_num_sms * ctas_per_sm;
-    if (grid > a.n_tiles) grid = a.n_tiles;
-    // the activation prologue is shared across a cluster of up to 8 CTAs
-    int cluster = 8;
-    while (cluster > 1 && grid < cluster) cluster >>= 1;
-    grid -= grid % cluster;
+    // The activation prologue is shared across a thread-block cluster.  A cluster must sit inside one
+    // GPC, so fewer CTAs are co-resident than SMs x CTAs/SM; a grid larger than that runs a nearly
+    // empty second wave (measured: SMs idle half the kernel).  Ask the driver how many clusters fit.
+    static int g_cluster_size = 0;
+    if (!g_cluster_size) {
+        const char* e = getenv("B2_GEMV_CLUSTER");
+        g_cluster_size = e ? atoi(e) : 8;
+        if (g_cluster_size != 1 && g_cluster_size != 2 && g_cluster_size != 4 && g_cluster_size != 8) g_cluster_size = 8;
+    }
+    int cluster = g_cluster_size;
+    int want = g_num_sms * ctas_per_sm;
+    if (want > a.n_tiles) want = a.n_tiles;
+    while (cluster > 1 && want < cluster) cluster >>= 1;
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(GEMV_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
@@ -762,6 +770,27 @@ int launch_gemv(const GemvArgs& a, int act, cudaStream_t st, bool pdl) {
         attr[na].val.clusterDim.z = 1;
         na++;
     }
+    int max_clusters = want / cluster;
+    if (cluster > 1) {
+        // cached per (activation format, cluster size, shared-memory size)
+        static int cached[2][9] = {};
+        static size_t cached_smem[2][9] = {};
+        if (!cached[act][cluster] || cached_smem[act][cluster] != smem) {
+            cudaLaunchConfig_t q = cfg;
+            q.gridDim = dim3(g_num_sms * ctas_per_sm / cluster * cluster);
+            q.attrs = attr;
+            q.numAttrs = na;
+            int n = 0;
+            B2_CUDA_CHECK(cudaOccupancyMaxActiveClusters(&n, kern, &q));
+            if (n < 1) n = 1;
+            cached[act][cluster] = n;
+            cached_smem[act][cluster] = smem;
+        }
+        if (max_clusters > cached[act][cluster]) max_clusters = cached[act][cluster];
+    }
+    if (max_clusters < 1) max_clusters = 1;
+    const int grid = max_clusters * cluster;
+    cfg.gridDim = dim3(grid);
     if (pdl) {
         attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         attr[na].val.programmaticStreamSerializationAllowed = 1;
