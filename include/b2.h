@@ -144,6 +144,17 @@ size_t b2_attn_scratch_bytes(int n_head, int head_dim, int n_tokens);
 int b2_attn_decode(const float* q_dev, const void* k_cache_dev, const void* v_cache_dev, float* out_dev,
                    int n_head, int n_kv, int head_dim, int n_ctx, int n_tokens, void* scratch_dev, void* stream);
 
+/* The same attention for callers that cannot allocate device memory (code inside a CUDA-graph capture or a
+ * latency-critical loop where cudaMalloc would synchronise the device, plugins running under a fixed memory
+ * budget, hosts whose own allocator owns all of HBM).  No counterpart in the reference: its scratch is a
+ * fixed array inside libb2.so (about 133 KiB on every GPU that loads the library), so there is no
+ * scratch argument.  Limits: n_head <= 64, head_dim <= 128, n_tokens <= 4096 -- larger requests fail with
+ * B2_ERANGE; use b2_attn_decode for those.  The first call on each device looks up the array's device
+ * address; make that first call outside any stream capture.  All calls on a device share the array: calls
+ * whose kernels overlap on the GPU race.  Calls no cudaMalloc / cudaFree. */
+int b2_attn_decode_static(const float* q_dev, const void* k_cache_dev, const void* v_cache_dev, float* out_dev,
+                          int n_head, int n_kv, int head_dim, int n_ctx, int n_tokens, void* stream);
+
 /* argmax over n logits, lowest index wins ties (row a16 greedy).  scratch_dev: b2_argmax_scratch_bytes(n),
  * zeroed once by the caller. */
 size_t b2_argmax_scratch_bytes(int64_t n);

@@ -81,6 +81,7 @@ SYMBOLS = {
     "b2_rope": (_I, [_P, _I, _I, _I, _I, _I, C.c_float, _P, _P]),
     "b2_attn_scratch_bytes": (_SZ, [_I, _I, _I]),
     "b2_attn_decode": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    "b2_attn_decode_static": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "b2_argmax_scratch_bytes": (_SZ, [_I64]),
     "b2_sample_greedy": (_I, [_P, _I64, _P, _P, _P]),
     "b2_model_load": (_I, [C.c_char_p, _I, _I, _I, C.POINTER(_P)]),

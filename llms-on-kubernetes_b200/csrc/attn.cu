@@ -19,6 +19,8 @@
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include "common.h"
 #include "device_utils.cuh"
 #include "ops.h"
@@ -339,3 +341,77 @@ int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float
 }
 
 }  // namespace b2
+
+// -------------------------------------------------------------------------------------------------
+// b2_attn_decode_static: the same split-sequence attention, for callers that must not allocate.
+//
+// Some hosts of this library cannot call cudaMalloc when they need attention: code running inside
+// a CUDA-graph capture or a latency-critical serving loop where an allocation would synchronise
+// the device, a sandboxed plugin that was handed a fixed memory budget at start-up, or an
+// embedder whose allocator owns all of HBM and gives none to third-party libraries.  For them the
+// split-merge scratch lives in the library image itself: a file-scope __device__ array of a fixed,
+// modest size that every GPU loading libb2.so carries until the process exits.
+//
+// The array's name is only a host-side handle; the device address is looked up once per device with
+// cudaGetSymbolAddress (with that device current) and cached.  That look-up happens on the FIRST call
+// on a device, so make that first call outside of any stream capture.  The entry point calls no
+// cudaMalloc / cudaFree and no allocating library routine.
+//
+// Limits (rejected with B2_ERANGE beyond them): n_head <= 64, head_dim <= 128, n_tokens <= 4096.
+// All calls on a device share the one array: the partial records are fully rewritten by every call
+// that uses them and the arrival counters are cleared on the caller's stream before each launch, but
+// two calls whose kernels overlap on the GPU (different streams, no ordering) race on it.
+// -------------------------------------------------------------------------------------------------
+namespace b2 {
+namespace {
+constexpr int STATIC_MAX_HEADS = 64, STATIC_MAX_HD = 128, STATIC_MAX_TOKENS = 4096;
+constexpr int STATIC_MAX_SPLITS = STATIC_MAX_TOKENS / ATTN_SPLIT_TOKENS;
+constexpr size_t STATIC_PART_BYTES = ((size_t)STATIC_MAX_HEADS * STATIC_MAX_SPLITS * (STATIC_MAX_HD + 2) * sizeof(float) + 255) & ~(size_t)255;
+constexpr size_t STATIC_SCRATCH_BYTES = STATIC_PART_BYTES + 256;   // + arrival counters (one per kv head)
+static __device__ __align__(256) unsigned char g_attn_static_scratch[STATIC_SCRATCH_BYTES];
+
+constexpr int MAX_DEVICES = 64;
+void* g_static_ptr[MAX_DEVICES];   // device address of the array, per device, filled on first use
+std::mutex g_static_mu;
+}  // namespace
+}  // namespace b2
+
+extern "C" int b2_attn_decode_static(const float* q_dev, const void* k_cache_dev, const void* v_cache_dev, float* out_dev, int n_head,
+                                     int n_kv, int head_dim, int n_ctx, int n_tokens, void* stream) {
+    using namespace b2;
+    if (!q_dev || !k_cache_dev || !v_cache_dev || !out_dev) {
+        set_error("b2_attn_decode_static: NULL pointer");
+        return B2_EINVAL;
+    }
+    if (n_head > STATIC_MAX_HEADS || head_dim > STATIC_MAX_HD || n_tokens > STATIC_MAX_TOKENS) {
+        set_error("b2_attn_decode_static: n_head=%d head_dim=%d n_tokens=%d exceed the built-in scratch (max %d heads, head_dim %d, %d tokens); "
+                  "use b2_attn_decode with caller-provided scratch",
+                  n_head, head_dim, n_tokens, STATIC_MAX_HEADS, STATIC_MAX_HD, STATIC_MAX_TOKENS);
+        return B2_ERANGE;
+    }
+    int dev = 0;
+    B2_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) {
+        set_error("b2_attn_decode_static: device ordinal %d not supported", dev);
+        return B2_ERANGE;
+    }
+    void* scratch;
+    {
+        // first call on this device: resolve the symbol's device address (the current device is `dev`)
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (!g_static_ptr[dev]) {
+            void* p = nullptr;
+            B2_CUDA_CHECK(cudaGetSymbolAddress(&p, g_attn_static_scratch));
+            g_static_ptr[dev] = p;
+        }
+        scratch = g_static_ptr[dev];
+    }
+    const int max_splits = attn_max_splits(n_tokens);
+    // same layout launch_attn_decode derives from (n_head, head_dim, max_splits): partial records, then counters
+    size_t part = (size_t)n_head * max_splits * ((size_t)head_dim + 2) * sizeof(float);
+    part = (part + 255) & ~(size_t)255;
+    // the counters must start at zero even if an earlier call on this array was interrupted
+    B2_CUDA_CHECK(cudaMemsetAsync((unsigned char*)scratch + part, 0, 256, (cudaStream_t)stream));
+    return launch_attn_decode(q_dev, (const __half*)k_cache_dev, (const __half*)v_cache_dev, out_dev, n_head, n_kv, head_dim, n_ctx,
+                              nullptr, n_tokens, max_splits, scratch, (cudaStream_t)stream, false);
+}
