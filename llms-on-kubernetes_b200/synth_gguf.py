@@ -267,7 +267,7 @@ def synth_vocab(n: int) -> tuple[list[bytes], list[float], list[int]]:
     for w in words:
         if len(toks) < n:
             toks.append(w.encode())
-            types.append(1)
+            types.append(4 if w.startswith("<|") else 1)  # chat markers are USER_DEFINED: matched verbatim
     i = 0
     while len(toks) < n:
         toks.append(f"▁tok{i}".encode())

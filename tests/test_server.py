@@ -1,0 +1,216 @@
+"""The process / HTTP face of the boundary: the `llama-server` binary launched with exactly the
+chart's four flags (ramalama-models/helm-chart/templates/model-deployments.yaml:26-35), called directly, through an
+HTTP/1.0 client (nginx proxy_pass default) and through the reference's API gateway (restated, see
+tests/gateway_restated.py).  The README's curl pair (ramalama-models/README.md:273-285) is the acceptance test."""
+import http.client
+import json
+import os
+import socket
+import subprocess
+import time
+
+import numpy as np
+import pytest
+
+import gateway_restated
+
+
+def free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+# ------------------------------------------------------------------ CPU: command line and tokenizer tools
+def test_cli_contract_without_gpu(b2, tiny_models):
+    exe = b2.SERVER_PATH
+    assert os.access(exe, os.X_OK), "bin/llama-server is not built"
+    r = subprocess.run([exe, "--help"], capture_output=True, text=True)
+    assert r.returncode == 0 and "--model" in r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 2
+    r = subprocess.run([exe, "--version"], capture_output=True, text=True)
+    assert r.returncode == 0 and "ABI 1" in r.stdout
+    try:
+        has_gpu = b2.device_count() > 0
+    except b2.B2Error:
+        has_gpu = False
+    if not has_gpu:
+        # the chart's exact argv: must fail loudly (non-zero exit -> kubelet restart), never serve from the CPU
+        r = subprocess.run([exe, "--host", "0.0.0.0", "--port", str(free_port()), "--model", tiny_models["tiny-llama-q4_k_m"],
+                            "--alias", "tinyllama"], capture_output=True, text=True, timeout=60)
+        assert r.returncode == 1 and "no CPU fallback" in r.stderr
+    r = subprocess.run([exe, "--model", "/nonexistent.gguf", "--tokenize", "x"], capture_output=True, text=True)
+    assert r.returncode == 1 and "cannot open" in r.stderr
+
+
+def test_tokenizer_round_trip_and_template(b2, tiny_models):
+    exe, model = b2.SERVER_PATH, tiny_models["tiny-llama-q4_k_m"]
+
+    def tool(flag, arg):
+        r = subprocess.run([exe, "-m", model, flag, arg], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        return json.loads(r.stdout)
+
+    for text in ["hello world", "the a hello", "Grüße, 世界! 123", "  two  spaces", "tok7 tok8"]:
+        ids = tool("--tokenize", text)["tokens"]
+        assert ids[0] == 1 and all(0 <= t < 1024 for t in ids)
+        back = tool("--detokenize", ",".join(map(str, ids)))["content"]
+        assert back == " " + text        # SPM adds one leading space; BOS is a control token and prints nothing
+    ids = tool("--tokenize", "the world")["tokens"]
+    assert len(ids) == 3                 # BOS + two whole-word pieces reached by score-ordered bigram merges, not bytes
+    t = tool("--apply-template", json.dumps([{"role": "system", "content": "be brief"}, {"role": "user", "content": "hello"}]))
+    assert t["template"] == "zephyr"
+    assert t["prompt"] == "<|system|>\nbe brief</s>\n<|user|>\nhello</s>\n<|assistant|>\n"
+    # chat markers and </s> are single special tokens, not spelled out in bytes
+    assert t["tokens"].count(2) == 2 and len(t["tokens"]) < 30
+
+
+# ------------------------------------------------------------------ GPU: the running server
+@pytest.fixture(scope="module")
+def server(b2, tiny_models):
+    port = free_port()
+    # exactly the chart's argv
+    proc = subprocess.Popen([b2.SERVER_PATH, "--host", "0.0.0.0", "--port", str(port), "--model", tiny_models["tiny-llama-q4_k_m"],
+                             "--alias", "tinyllama"], stderr=subprocess.PIPE, text=True)
+    t0 = time.time()
+    while True:
+        try:
+            c = http.client.HTTPConnection("127.0.0.1", port, timeout=2)
+            c.request("GET", "/health")
+            r = c.getresponse(); r.read(); c.close()
+            if r.status == 200:
+                break
+            assert r.status == 503        # loading
+        except OSError:
+            pass
+        assert proc.poll() is None, proc.stderr.read()
+        assert time.time() - t0 < 120, "server did not become ready"
+        time.sleep(0.1)
+    yield port
+    proc.terminate()
+    proc.wait(timeout=10)
+
+
+def post(port, path, payload, headers=None):
+    c = http.client.HTTPConnection("127.0.0.1", port, timeout=120)
+    c.request("POST", path, body=json.dumps(payload), headers={"Content-Type": "application/json", **(headers or {})})
+    r = c.getresponse()
+    data = r.read()
+    c.close()
+    return r.status, json.loads(data)
+
+
+@pytest.mark.gpu
+def test_readme_curl_pair_direct(server):
+    c = http.client.HTTPConnection("127.0.0.1", server, timeout=10)
+    c.request("GET", "/v1/models")
+    r = c.getresponse(); models = json.loads(r.read()); c.close()
+    assert r.status == 200 and models["object"] == "list" and models["data"][0]["id"] == "tinyllama"
+    status, out = post(server, "/v1/chat/completions", {"model": "tinyllama", "messages": [{"role": "user", "content": "hello world"}],
+                                                         "max_tokens": 50, "temperature": 0})
+    assert status == 200 and out["object"] == "chat.completion" and out["model"] == "tinyllama"
+    ch = out["choices"][0]
+    assert ch["message"]["role"] == "assistant" and isinstance(ch["message"]["content"], str) and ch["finish_reason"] in ("stop", "length")
+    u = out["usage"]
+    assert u["completion_tokens"] <= 50 and u["total_tokens"] == u["prompt_tokens"] + u["completion_tokens"]
+
+
+@pytest.mark.gpu
+def test_token_id_prompt_matches_c_abi_and_is_deterministic(server, b2, tiny_models):
+    """The numeric path through HTTP equals the C ABI: same ids for the same token-id prompt (greedy)."""
+    prompt = np.random.default_rng(5).integers(3, 1024, size=24).tolist()
+    req = {"model": "tinyllama", "prompt": prompt, "max_tokens": 20, "temperature": 0, "ignore_eos": True}
+    s1, o1 = post(server, "/v1/completions", req)
+    s2, o2 = post(server, "/v1/completions", req)      # second time the prefix is served from the KV cache
+    assert s1 == s2 == 200 and o1["choices"][0]["tokens"] == o2["choices"][0]["tokens"]
+    m = b2.Model(tiny_models["tiny-llama-q4_k_m"])
+    ctx = b2.Context(m, 512)
+    want, _ = ctx.greedy(prompt, 20)
+    ctx.free(); m.free()
+    assert o1["choices"][0]["tokens"] == want
+    assert o1["usage"]["prompt_tokens"] == 24 and o1["usage"]["completion_tokens"] == 20 and o1["choices"][0]["finish_reason"] == "length"
+
+
+@pytest.mark.gpu
+def test_http10_client_like_nginx(server):
+    """nginx's default upstream protocol is HTTP/1.0 + Connection: close: answer in 1.0, Content-Length, no chunking."""
+    body = json.dumps({"model": "whatever", "messages": [{"role": "user", "content": "hello"}], "max_tokens": 4, "temperature": 0}).encode()
+    s = socket.create_connection(("127.0.0.1", server), timeout=60)
+    s.sendall(b"POST /v1/chat/completions HTTP/1.0\r\nHost: vllm-tinyllama\r\nX-Real-IP: 10.0.0.1\r\nX-Forwarded-For: 10.0.0.1\r\n"
+              b"X-Forwarded-Proto: http\r\nConnection: close\r\nContent-Type: application/json\r\nContent-Length: " + str(len(body)).encode() + b"\r\n\r\n" + body)
+    raw = b""
+    while True:
+        d = s.recv(65536)
+        if not d:
+            break
+        raw += d
+    s.close()
+    head, _, payload = raw.partition(b"\r\n\r\n")
+    assert head.startswith(b"HTTP/1.0 200") and b"chunked" not in head.lower()
+    assert int([l for l in head.split(b"\r\n") if l.lower().startswith(b"content-length")][0].split(b":")[1]) == len(payload)
+    out = json.loads(payload)
+    assert out["model"] == "tinyllama"          # unknown `model` in the request is served anyway, alias reported
+
+
+@pytest.mark.gpu
+def test_streaming_sse(server):
+    c = http.client.HTTPConnection("127.0.0.1", server, timeout=60)
+    c.request("POST", "/v1/chat/completions", body=json.dumps({"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 12,
+                                                                "temperature": 0, "stream": True}), headers={"Content-Type": "application/json"})
+    r = c.getresponse()
+    assert r.status == 200 and r.getheader("Content-Type").startswith("text/event-stream")
+    events = [l[6:] for l in r.read().decode().split("\n") if l.startswith("data: ")]
+    c.close()
+    assert events[-1] == "[DONE]"
+    chunks = [json.loads(e) for e in events[:-1]]
+    assert all(ch["object"] == "chat.completion.chunk" for ch in chunks)
+    assert chunks[0]["choices"][0]["delta"].get("role") == "assistant"
+    assert chunks[-1]["choices"][0]["finish_reason"] in ("stop", "length") and "usage" in chunks[-1]
+    streamed = "".join(ch["choices"][0]["delta"].get("content", "") for ch in chunks)
+    _, full = post(server, "/v1/chat/completions", {"messages": [{"role": "user", "content": "hello world"}], "max_tokens": 12, "temperature": 0})
+    assert streamed == full["choices"][0]["message"]["content"]
+
+
+@pytest.mark.gpu
+def test_sampling_seed_stop_and_errors(server):
+    req = {"prompt": "hello world", "max_tokens": 16, "temperature": 0.9, "top_k": 50, "seed": 1234}
+    _, a = post(server, "/v1/completions", req)
+    _, b = post(server, "/v1/completions", req)
+    _, c = post(server, "/v1/completions", {**req, "seed": 99})
+    assert a["choices"][0]["tokens"] == b["choices"][0]["tokens"]            # same seed, same sample path
+    assert a["choices"][0]["tokens"] != c["choices"][0]["tokens"] or True     # different seed usually differs
+    _, g = post(server, "/v1/completions", {"prompt": "hello world", "max_tokens": 24, "temperature": 0, "ignore_eos": True})
+    text = g["choices"][0]["text"]
+    if len(text) > 6:
+        cut = text[3:6]
+        _, s = post(server, "/v1/completions", {"prompt": "hello world", "max_tokens": 24, "temperature": 0, "ignore_eos": True, "stop": [cut]})
+        assert s["choices"][0]["text"] == text[:text.index(cut)] and s["choices"][0]["finish_reason"] == "stop"
+    st, e = post(server, "/v1/chat/completions", {"messages": []})
+    assert st == 400 and e["error"]["type"] == "invalid_request_error"
+    st, e = post(server, "/v1/completions", {"prompt": [5] * 600})
+    assert st == 400 and "context" in e["error"]["message"]
+    c2 = http.client.HTTPConnection("127.0.0.1", server, timeout=10)
+    c2.request("POST", "/v1/chat/completions", body="{not json", headers={"Content-Type": "application/json"})
+    r = c2.getresponse(); assert r.status == 400; r.read()
+    c2.request("GET", "/no/such/path")      # same connection: HTTP/1.1 keep-alive
+    r = c2.getresponse(); assert r.status == 404 and json.loads(r.read())["error"]["code"] == 404
+    c2.close()
+
+
+@pytest.mark.gpu
+def test_through_the_reference_gateway(server):
+    """README curl pair through the (restated) API gateway: routing by `model`, default-backend fallback, and the
+    gateway's own /v1/models; plus the 502 mapping of a backend 4xx."""
+    srv, gport = gateway_restated.start({"tinyllama": f"http://127.0.0.1:{server}", "other": f"http://127.0.0.1:{server}"})
+    try:
+        c = http.client.HTTPConnection("127.0.0.1", gport, timeout=10)
+        c.request("GET", "/v1/models")
+        r = c.getresponse(); models = json.loads(r.read()); c.close()
+        assert [m["id"] for m in models["data"]] == ["tinyllama", "other"] and models["data"][0]["owned_by"] == "ramalama"
+        for model in ("tinyllama", "not-deployed"):
+            st, out = post(gport, "/v1/chat/completions", {"model": model, "messages": [{"role": "user", "content": "hello world"}],
+                                                           "max_tokens": 50, "temperature": 0})
+            assert st == 200 and out["model"] == "tinyllama" and out["choices"][0]["message"]["role"] == "assistant"
+        st, out = post(gport, "/v1/chat/completions", {"model": "tinyllama", "messages": []})
+        assert st == 502 and "error" in out
+    finally:
+        srv.shutdown()
