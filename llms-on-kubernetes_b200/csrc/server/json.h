@@ -72,9 +72,36 @@ struct Value {
     std::string string_or(const std::string& d) const { return kind == String ? str : d; }
 };
 
+// length of the well-formed UTF-8 sequence starting at s[i], or 0 if the bytes there are not valid UTF-8
+inline size_t utf8_valid_len(const std::string& s, size_t i) {
+    const unsigned char c = (unsigned char)s[i];
+    size_t n = c < 0x80 ? 1 : (c >= 0xC2 && c < 0xE0) ? 2 : (c >= 0xE0 && c < 0xF0) ? 3 : (c >= 0xF0 && c < 0xF5) ? 4 : 0;
+    if (n == 0 || i + n > s.size()) return 0;
+    for (size_t k = 1; k < n; k++)
+        if (((unsigned char)s[i + k] & 0xC0) != 0x80) return 0;
+    if (n == 3) {
+        const unsigned char d = (unsigned char)s[i + 1];
+        if ((c == 0xE0 && d < 0xA0) || (c == 0xED && d >= 0xA0)) return 0;   // overlong / surrogate
+    }
+    if (n == 4) {
+        const unsigned char d = (unsigned char)s[i + 1];
+        if ((c == 0xF0 && d < 0x90) || (c == 0xF4 && d >= 0x90)) return 0;
+    }
+    return n;
+}
+
+// A model can emit byte tokens that do not form valid UTF-8; JSON must be valid UTF-8, so such bytes become U+FFFD.
 inline void escape_to(const std::string& s, std::string& out) {
     out.push_back('"');
-    for (unsigned char c : s) {
+    for (size_t i = 0; i < s.size(); i++) {
+        const unsigned char c = (unsigned char)s[i];
+        if (c >= 0x80) {
+            const size_t n = utf8_valid_len(s, i);
+            if (n == 0) { out += "\\ufffd"; continue; }
+            out.append(s, i, n);
+            i += n - 1;
+            continue;
+        }
         switch (c) {
             case '"': out += "\\\""; break;
             case '\\': out += "\\\\"; break;

@@ -146,6 +146,16 @@ struct Engine {
             // do not split a UTF-8 sequence
             size_t emit = pending.size() > hold ? pending.size() - hold : 0;
             while (!final && emit > 0 && emit < pending.size() && ((unsigned char)pending[emit] & 0xC0) == 0x80) emit--;
+            if (!final && emit == pending.size()) {
+                // ... nor emit a lead byte whose continuation bytes have not been generated yet
+                for (size_t back = 1; back <= 3 && back <= emit; back++) {
+                    const unsigned char c = (unsigned char)pending[emit - back];
+                    if ((c & 0xC0) == 0x80) continue;
+                    const size_t need = c >= 0xF0 ? 4 : c >= 0xE0 ? 3 : c >= 0xC0 ? 2 : 1;
+                    if (need > back) emit -= back;
+                    break;
+                }
+            }
             if (!emit) return true;
             const std::string piece = pending.substr(0, emit);
             pending.erase(0, emit);
