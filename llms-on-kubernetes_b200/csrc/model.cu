@@ -19,6 +19,7 @@
 #include <cstring>
 
 #include "gemv.cuh"
+#include "step.cuh"
 #include "ops.h"
 
 using namespace b2;
@@ -298,11 +299,15 @@ void seg_matrix(GemvSeg& s, const b2_model::W& w, int pairing, int epi) {
 }
 
 // enqueue one decode step (token and position are read from device memory)
-int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false) {
+// With `record` set nothing is launched: the stages are appended to *record as the program of the persistent
+// per-token kernel (step.cu), and *record_act receives the activation format they share (-2 if they do not).
+int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false, std::vector<StepOp>* record = nullptr,
+                 int* record_act = nullptr) {
     b2_model* m = c->m;
     const b2_model_info& I = m->info;
     int rc;
     int launches = 0;
+    if (record_act) *record_act = -1;
     const int64_t kv_layer = (int64_t)I.n_kv * c->n_ctx * I.head_dim;
     const int rope_pairing = I.arch == 1 ? PAIR_NEOX : PAIR_ADJ;
     auto common = [&](GemvArgs& a, const float* x, const float* norm_w, int K) {
@@ -318,12 +323,32 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false)
     };
     auto run = [&](GemvArgs& a, int act) -> int {
         if ((rc = gemv_finalize(a, act))) return rc;
+        if (record) {
+            StepOp op{};
+            op.kind = OP_GEMV;
+            op.g = a;
+            record->push_back(op);
+            if (*record_act == -1) *record_act = act;
+            else if (*record_act != act) *record_act = -2;
+            return 0;
+        }
         if ((rc = launch_gemv(a, act, st, pdl))) return rc;
         launches++;
         return 0;
     };
     // the first kernel of a step depends on a memcpy / the previous graph launch: ordinary dependency
-    if (!matvec_only) {
+    if (record) {
+        StepOp op{};
+        op.kind = OP_EMBED;
+        op.e_type = m->tok_embd.type;
+        op.e_table = m->tok_embd.p;
+        op.e_row_bytes = row_bytes(m->tok_embd.type, I.d_model);
+        op.e_d_model = I.d_model;
+        op.e_vocab = I.vocab;
+        op.e_token = c->d_tok;
+        op.e_x = c->x;
+        record->push_back(op);
+    } else if (!matvec_only) {
         if ((rc = launch_embed(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, c->d_tok, c->x,
                                st, false)))
             return rc;
@@ -366,7 +391,23 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false)
                 if ((rc = run(a, acts[i]))) return rc;
             }
         }
-        if (!matvec_only) {
+        if (record) {
+            StepOp op{};
+            op.kind = OP_ATTN;
+            op.a_q = c->q;
+            op.a_k = kc;
+            op.a_v = vc;
+            op.a_out = c->attn_out;
+            op.a_n_head = I.n_head;
+            op.a_n_kv = I.n_kv;
+            op.a_hd = I.head_dim;
+            op.a_n_ctx = c->n_ctx;
+            op.a_max_chunks = step_attn_max_chunks(c->n_ctx);
+            op.a_pos = c->d_pos;
+            op.a_partials = c->step_attn_partials;
+            op.a_counters = c->step_counters + 8;   // [n_kv] after the grid-barrier and argmax counters
+            record->push_back(op);
+        } else if (!matvec_only) {
             if ((rc = launch_attn_decode(c->q, kc, vc, c->attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, c->d_pos, 0, c->max_splits,
                                          c->attn_scratch, st, pdl)))
                 return rc;
@@ -405,6 +446,22 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false)
     a.seg[0].out = c->logits;
     a.n_seg = 1;
     if ((rc = run(a, gemv_act_for_type(m->output.type)))) return rc;
+    if (record) {
+        StepOp op{};
+        op.kind = OP_ARGMAX;
+        op.s_logits = c->logits;
+        op.s_n = I.vocab;
+        op.s_token = c->d_tok;
+        op.s_pos = c->d_pos;
+        op.s_step = c->d_step;
+        op.s_out = c->d_out;
+        op.s_cap = c->out_cap;
+        op.s_val = c->step_argmax_val;
+        op.s_idx = c->step_argmax_idx;
+        op.s_counter = c->step_counters + 1;
+        record->push_back(op);
+        return 0;
+    }
     if (matvec_only) {
         c->matvec_launches = launches;
         return 0;
@@ -412,6 +469,50 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false)
     if ((rc = launch_argmax(c->logits, I.vocab, c->d_tok, c->argmax_scratch, c->d_pos, c->d_step, c->d_out, c->out_cap, st, pdl))) return rc;
     launches++;
     c->launches_per_step = launches;
+    return 0;
+}
+
+// one decode step on the stream: the persistent kernel when a program was built, else one launch per stage
+int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
+    if (c->use_step && c->d_ops) {
+        StepProgram p{};
+        p.ops = (const StepOp*)c->d_ops;
+        p.n_ops = c->n_ops;
+        p.max_k = c->step_max_k;
+        p.sync_counter = c->step_counters;
+        const int rc = launch_step(p, c->step_act, st);
+        if (rc == 0) c->launches_per_step = 1;
+        return rc;
+    }
+    return enqueue_step(c, st, pdl);
+}
+
+// record the stages of a step as the persistent kernel's program and upload it
+int build_step_program(b2_ctx* c) {
+    std::vector<StepOp> ops;
+    int act = -1;
+    int rc = enqueue_step(c, c->stream, false, false, &ops, &act);
+    if (rc) return rc;
+    if (act < 0) {
+        // mat-vecs with different activation formats (K-quants mixed with Q8_0): keep one launch per stage
+        c->use_step = false;
+        return 0;
+    }
+    int max_k = 0;
+    for (auto& op : ops)
+        if (op.kind == OP_GEMV && op.g.K > max_k) max_k = op.g.K;
+    const int grid = step_grid_size(act, max_k);
+    if (grid < 0) return grid;
+    if (grid > 1024) {
+        set_error("step kernel: grid of %d CTAs exceeds the argmax scratch", grid);
+        return B2_ERANGE;
+    }
+    B2_CUDA_CHECK(cudaMalloc(&c->d_ops, ops.size() * sizeof(StepOp)));
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->d_ops, ops.data(), ops.size() * sizeof(StepOp), cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    c->n_ops = (int)ops.size();
+    c->step_act = act;
+    c->step_max_k = max_k;
     return 0;
 }
 
@@ -424,7 +525,7 @@ int build_graph(b2_ctx* c) {
         cudaError_t e = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal);
         int rc = 0;
         if (e == cudaSuccess) {
-            rc = enqueue_step(c, c->stream, pdl);
+            rc = enqueue_decode(c, c->stream, pdl);
             e = cudaStreamEndCapture(c->stream, &graph);
         }
         if (e == cudaSuccess && rc == 0) e = cudaGraphInstantiate(&exec, graph, 0);
@@ -451,7 +552,7 @@ int run_step(b2_ctx* c) {
         B2_CUDA_CHECK(cudaGraphLaunch(c->exec, c->stream));
         return 0;
     }
-    return enqueue_step(c, c->stream, c->use_pdl);
+    return enqueue_decode(c, c->stream, c->use_pdl);
 }
 
 }  // namespace
@@ -525,8 +626,19 @@ extern "C" int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out) {
         B2_CUDA_CHECK(cudaMemcpyAsync(c->rope_tab, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
         B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     }
+    // scratch + program of the persistent per-token kernel (B2_NO_STEP=1 keeps one launch per stage)
+    c->use_step = !env_flag("B2_NO_STEP");
+    if (c->use_step) {
+        const size_t pb = step_attn_partials_bytes(I.n_head, I.head_dim, n_ctx);
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_attn_partials, pb));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_counters, (8 + 2 * I.n_kv) * sizeof(unsigned int)));
+        B2_CUDA_CHECK(cudaMemsetAsync(c->step_counters, 0, (8 + 2 * I.n_kv) * sizeof(unsigned int), c->stream));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_argmax_val, 1024 * sizeof(float)));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_argmax_idx, 1024 * sizeof(int)));
+        if ((rc = build_step_program(c.get()))) return rc;
+    }
     // run one eager step so lazy module loading and attribute setting happen outside capture
-    if ((rc = enqueue_step(c.get(), c->stream, false))) return rc;
+    if ((rc = enqueue_decode(c.get(), c->stream, false))) return rc;
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     B2_CUDA_CHECK(cudaMemsetAsync(c->d_pos, 0, 4, c->stream));
     B2_CUDA_CHECK(cudaMemsetAsync(c->d_step, 0, 4, c->stream));
@@ -545,7 +657,8 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->exec) cudaGraphExecDestroy(c->exec);
     if (c->graph) cudaGraphDestroy(c->graph);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
-                    c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch};
+                    c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch,
+                    c->d_ops, c->step_attn_partials, c->step_counters, c->step_argmax_val, c->step_argmax_idx};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pin) cudaFreeHost(c->h_pin);

@@ -47,5 +47,13 @@ struct b2_ctx {
     cudaGraphExec_t exec = nullptr;
     bool use_graph = true, use_pdl = true;
     int launches_per_step = 0, matvec_launches = 0;
+    // persistent per-token kernel (step.cu): program + scratch; use_step false = one launch per stage
+    bool use_step = true;
+    void* d_ops = nullptr;   // StepOp[n_ops]
+    int n_ops = 0, step_act = -1, step_max_k = 0;
+    float* step_attn_partials = nullptr;
+    unsigned int* step_counters = nullptr;   // [0] grid barrier, [1] argmax arrivals, [8 .. 8 + 2 n_kv) attention arrivals
+    float* step_argmax_val = nullptr;
+    int* step_argmax_idx = nullptr;
     int pos = 0;
 };

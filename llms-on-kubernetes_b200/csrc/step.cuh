@@ -1,0 +1,53 @@
+// step.cuh -- program descriptor of the persistent per-token decode kernel (step.cu)
+#pragma once
+#include "gemv.cuh"
+
+namespace b2 {
+
+enum { OP_EMBED = 0, OP_GEMV = 1, OP_ATTN = 2, OP_ARGMAX = 3 };
+
+// One stage of a decode step.  Stages run in order with a grid-wide barrier between them.
+struct StepOp {
+    int kind;
+    GemvArgs g;   // OP_GEMV
+    // OP_EMBED: x = dequantise(table[*token])
+    int e_type, e_d_model, e_vocab;
+    const uint8_t* e_table;
+    int64_t e_row_bytes;
+    const int32_t* e_token;
+    float* e_x;
+    // OP_ATTN: single-query attention over the fp16 cache at positions [0, *pos]
+    const float* a_q;
+    const __half *a_k, *a_v;
+    float* a_out;
+    int a_n_head, a_n_kv, a_hd, a_n_ctx, a_max_chunks;
+    const int* a_pos;
+    float* a_partials;       // [n_head][max_chunks][hd + 2]
+    unsigned int* a_counters;  // [n_kv], zero between steps
+    // OP_ARGMAX (+ the device-resident loop's bookkeeping)
+    const float* s_logits;
+    int64_t s_n;
+    int32_t *s_token, *s_pos, *s_step, *s_out;
+    int s_cap;
+    float* s_val;            // [grid] partial maxima
+    int* s_idx;              // [grid]
+    unsigned int* s_counter;
+};
+
+struct StepProgram {
+    const StepOp* ops;          // device memory
+    int n_ops;
+    int max_k;                  // largest mat-vec K (sizes the activation buffers)
+    unsigned int* sync_counter;  // grid barrier, zeroed before every launch
+};
+
+constexpr int STEP_ATTN_CHUNK = 256;   // tokens one CTA handles per attention work item
+
+// scratch sizes for a program's attention / argmax stages
+size_t step_attn_partials_bytes(int n_head, int head_dim, int n_ctx);
+int step_attn_max_chunks(int n_ctx);
+// number of CTAs the persistent kernel runs with for this activation format and K (co-resident clusters x 8)
+int step_grid_size(int act, int max_k);
+int launch_step(const StepProgram& p, int act, cudaStream_t st);
+
+}  // namespace b2
