@@ -248,6 +248,15 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int hb, int chunk, 
     named_bar_sync(1, NCT);
 }
 
+// copy a stage's mat-vec descriptor from the program (global memory) into shared memory with one warp
+__device__ __forceinline__ void stage_descriptor(GemvArgs* dst, const GemvArgs* src, int lane) {
+    static_assert(sizeof(GemvArgs) % 4 == 0, "descriptor copy is word-wise");
+    const uint32_t* s = (const uint32_t*)src;
+    uint32_t* d = (uint32_t*)dst;
+    for (int i = lane; i < (int)(sizeof(GemvArgs) / 4); i += 32) d[i] = s[i];
+    __syncwarp();
+}
+
 template <int ACT>
 __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_constant__ StepProgram P) {
     using G = Geo<ACT>;
@@ -264,7 +273,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
     sm.ssbar = sm.xbar + 1;
     sm.ss_span = (double*)(sm.ssbar + 2);
     float* red = (float*)(sm.ss_span + MAX_SPANS);
-    uint8_t* xbase = (uint8_t*)(red + 2 * NCW * TILE_ROWS);   // activation buffers, re-carved per mat-vec; attention aliases them
+    // the current stage's mat-vec descriptor, one private copy per role (the roles are at different stages)
+    GemvArgs* slots = (GemvArgs*)(red + 2 * NCW * TILE_ROWS);
+    uint8_t* xbase = (uint8_t*)(slots + 4);   // activation buffers, re-carved per mat-vec; attention aliases them
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank(), csize = cluster_nctarank();
@@ -292,7 +303,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
         for (int oi = 0; oi < P.n_ops; oi++) {
             const StepOp& op = P.ops[oi];
             if (op.kind != OP_GEMV) continue;
-            const GemvArgs& a = op.g;
+            __syncwarp();
+            stage_descriptor(&slots[0], &op.g, lane);
+            const GemvArgs& a = slots[0];
             const int nblk_row = a.K / (ACT == ACT_Q8K ? 256 : 32);
             const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
             int si = 0;
@@ -332,7 +345,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
         for (int oi = 0; oi < P.n_ops; oi++) {
             const StepOp& op = P.ops[oi];
             if (op.kind != OP_GEMV) continue;
-            const GemvArgs& a = op.g;
+            __syncwarp();
+            stage_descriptor(&slots[1], &op.g, lane);
+            const GemvArgs& a = slots[1];
             const int nblk_row = a.K / (ACT == ACT_Q8K ? 256 : 32);
             const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
             int si = 0;
@@ -365,7 +380,14 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
         for (int oi = 0; oi < P.n_ops; oi++) {
             const StepOp& op = P.ops[oi];
             if (op.kind != OP_GEMV) continue;   // the compute warps signal those stages
-            const GemvArgs& a = op.g;
+            // never arrive for a stage before the previous one is complete everywhere: a CTA without tiles in
+            // this stage would otherwise run ahead and release other CTAs early
+            if (oi > 0) {
+                if (lane == 0) grid_wait(P.sync_counter, (unsigned int)oi * G_CTAS);
+                __syncwarp();
+            }
+            stage_descriptor(&slots[2], &op.g, lane);
+            const GemvArgs& a = slots[2];
             int si = 0;
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
                 while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
@@ -408,7 +430,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             named_bar_sync(1, NCT);
         }
         if (op.kind == OP_GEMV) {
-            const GemvArgs& a = op.g;
+            if (warp == 0) stage_descriptor(&slots[3], &op.g, lane);
+            named_bar_sync(1, NCT);
+            const GemvArgs& a = slots[3];
             const int K = a.K;
             sm.xq = (int8_t*)xbase;
             sm.xd = (float*)(sm.xq + K);
@@ -523,7 +547,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
 }
 
 size_t step_smem_bytes(int act, int max_k) {
-    size_t n = gemv_smem_bytes(act, max_k);
+    size_t n = gemv_smem_bytes(act, max_k) + 4 * sizeof(GemvArgs);
     // attention aliases the activation buffers; make sure they are large enough
     const size_t x_bytes = (size_t)max_k + (act == ACT_Q8K ? max_k / 256 : max_k / 32) * 4 + max_k / 16 * 2 + max_k / 32 * 2;
     if (x_bytes < ATTN_SMEM_BYTES) n += ATTN_SMEM_BYTES - x_bytes;
