@@ -412,8 +412,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                     }
                 }
             }
+            // a fence orders only the calling thread's stores: every lane that wrote results fences, then one arrives
+            __threadfence();
             __syncwarp();
-            if (lane == 0) grid_arrive(P.sync_counter);
+            if (lane == 0) atomicAdd(P.sync_counter, 1u);
         }
         return;
     }
@@ -540,8 +542,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                     }
                 }
             }
+            __threadfence();   // every thread's stores of this stage, before the CTA's single arrival
             named_bar_sync(1, NCT);
-            if (tid == 0) grid_arrive(P.sync_counter);
+            if (tid == 0) atomicAdd(P.sync_counter, 1u);
         }
     }
 }
