@@ -17,6 +17,8 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <string>
 
 #include "gemv.cuh"
 #include "step.cuh"
@@ -480,6 +482,7 @@ int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
         p.n_ops = c->n_ops;
         p.max_k = c->step_max_k;
         p.sync_counter = c->step_counters;
+        p.trace = c->step_trace;
         const int rc = launch_step(p, c->step_act, st);
         if (rc == 0) c->launches_per_step = 1;
         return rc;
@@ -513,7 +516,47 @@ int build_step_program(b2_ctx* c) {
     c->n_ops = (int)ops.size();
     c->step_act = act;
     c->step_max_k = max_k;
+    if (env_flag("B2_STEP_TRACE")) {
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_trace, ops.size() * 4 * sizeof(unsigned long long)));
+        B2_CUDA_CHECK(cudaMemset(c->step_trace, 0, ops.size() * 4 * sizeof(unsigned long long)));
+        for (auto& op : ops) {
+            c->step_desc.push_back(op.kind);
+            c->step_desc.push_back(op.kind == OP_GEMV ? op.g.K : 0);
+            c->step_desc.push_back(op.kind == OP_GEMV ? op.g.n_tiles : 0);
+        }
+    }
     return 0;
+}
+
+// B2_STEP_TRACE=1: print where CTA 0 spent the last step, stage by stage (first two layers) and by stage class
+void dump_step_trace(b2_ctx* c) {
+    if (!c->step_trace) return;
+    std::vector<unsigned long long> t((size_t)c->n_ops * 4);
+    if (cudaMemcpy(t.data(), c->step_trace, t.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return;
+    const char* kinds[] = {"embed", "gemv", "attn", "argmax"};
+    struct Acc { double wait = 0, pro = 0, tiles = 0, epi = 0; int n = 0; };
+    std::map<std::string, Acc> by;
+    unsigned long long prev_arrive = 0;
+    fprintf(stderr, "b2 step trace (CTA 0, ns): stage kind K tiles | barrier-wait  prologue  tiles  epilogue+arrive\n");
+    for (int i = 0; i < c->n_ops; i++) {
+        const int kind = c->step_desc[3 * i], K = c->step_desc[3 * i + 1], tiles = c->step_desc[3 * i + 2];
+        const unsigned long long* s = &t[(size_t)i * 4];
+        const double wait = prev_arrive ? (double)(s[0] - prev_arrive) : 0.0;
+        const double pro = kind == OP_GEMV ? (double)(s[1] - s[0]) : 0.0;
+        const double tl = kind == OP_GEMV ? (double)(s[2] - s[1]) : 0.0;
+        const double epi = (double)(s[3] - (kind == OP_GEMV ? s[2] : s[0]));
+        char key[64];
+        snprintf(key, sizeof key, "%s K=%d tiles=%d", kinds[kind], K, tiles);
+        Acc& a = by[key];
+        a.wait += wait; a.pro += pro; a.tiles += tl; a.epi += epi; a.n++;
+        if (i < 12) fprintf(stderr, "  %3d %-28s | %8.0f %8.0f %8.0f %8.0f\n", i, key, wait, pro, tl, epi);
+        prev_arrive = s[3];
+    }
+    fprintf(stderr, "b2 step trace, mean per stage class:\n");
+    for (auto& kv : by)
+        fprintf(stderr, "  %-28s x%3d | %8.0f %8.0f %8.0f %8.0f\n", kv.first.c_str(), kv.second.n, kv.second.wait / kv.second.n,
+                kv.second.pro / kv.second.n, kv.second.tiles / kv.second.n, kv.second.epi / kv.second.n);
+    fprintf(stderr, "  whole step: %.0f ns\n", (double)(t[(size_t)(c->n_ops - 1) * 4 + 3] - t[0]));
 }
 
 int build_graph(b2_ctx* c) {
@@ -658,7 +701,7 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->graph) cudaGraphDestroy(c->graph);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
                     c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch,
-                    c->d_ops, c->step_attn_partials, c->step_counters, c->step_argmax_val, c->step_argmax_idx};
+                    c->d_ops, c->step_attn_partials, c->step_counters, c->step_argmax_val, c->step_argmax_idx, c->step_trace};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pin) cudaFreeHost(c->h_pin);
@@ -817,6 +860,7 @@ extern "C" int b2_ctx_time_steps(b2_ctx* c, int n_steps, float* ms_out) {
     }
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
+    if (rc == 0) dump_step_trace(c);
     return rc;
 }
 

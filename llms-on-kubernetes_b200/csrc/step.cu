@@ -43,9 +43,14 @@ __device__ __forceinline__ void grid_wait(const unsigned int* ctr, unsigned int 
     }
     asm volatile("trap;");
 }
-__device__ __forceinline__ void grid_arrive(unsigned int* ctr) {
-    __threadfence();
-    atomicAdd(ctr, 1u);
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// profiling stamp of CTA 0 (no-op unless the program carries a trace buffer)
+__device__ __forceinline__ void stamp(const StepProgram& P, int oi, int slot) {
+    if (P.trace && blockIdx.x == 0) P.trace[oi * 4 + slot] = globaltimer_ns();
 }
 
 // ---- attention work item: (kv head, chunk of STEP_ATTN_CHUNK tokens), all query heads of the group ------------
@@ -415,7 +420,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             // a fence orders only the calling thread's stores: every lane that wrote results fences, then one arrives
             __threadfence();
             __syncwarp();
-            if (lane == 0) atomicAdd(P.sync_counter, 1u);
+            if (lane == 0) {
+                atomicAdd(P.sync_counter, 1u);
+                stamp(P, oi, 3);
+            }
         }
         return;
     }
@@ -431,6 +439,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             if (warp == 0 && lane == 0) grid_wait(P.sync_counter, (unsigned int)oi * G_CTAS);
             named_bar_sync(1, NCT);
         }
+        if (tid == 0) stamp(P, oi, 0);
         if (op.kind == OP_GEMV) {
             if (warp == 0) stage_descriptor(&slots[3], &op.g, lane);
             named_bar_sync(1, NCT);
@@ -441,6 +450,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             sm.bs16 = (int16_t*)(sm.xd + (ACT == ACT_Q8K ? K / 256 : K / 32));
             sm.bs32 = sm.bs16 + K / 16;
             build_activation<ACT>(a, sm, smem, tid, rank, csize, xpar, sspar);
+            if (tid == 0) stamp(P, oi, 1);
             xpar ^= 1;
             if (a.prologue == PRO_NORM) sspar ^= 1;
             const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};
@@ -473,6 +483,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&part_full[parity]);
             }
+            if (tid == 0) stamp(P, oi, 2);
             // the epilogue warp arrives on the grid barrier for this stage
         } else {
             if (op.kind == OP_EMBED) {
@@ -544,7 +555,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             }
             __threadfence();   // every thread's stores of this stage, before the CTA's single arrival
             named_bar_sync(1, NCT);
-            if (tid == 0) atomicAdd(P.sync_counter, 1u);
+            if (tid == 0) {
+                atomicAdd(P.sync_counter, 1u);
+                stamp(P, oi, 3);
+            }
         }
     }
 }

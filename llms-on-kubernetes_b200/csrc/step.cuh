@@ -39,6 +39,10 @@ struct StepProgram {
     int n_ops;
     int max_k;                  // largest mat-vec K (sizes the activation buffers)
     unsigned int* sync_counter;  // grid barrier, zeroed before every launch
+    // optional profiling trace (B2_STEP_TRACE=1): [n_ops][4] globaltimer stamps written by CTA 0:
+    // 0 = compute warps passed the grid barrier, 1 = activation vector built, 2 = last tile handed to the
+    // epilogue warp, 3 = this CTA arrived on the stage's grid barrier
+    unsigned long long* trace;
 };
 
 constexpr int STEP_ATTN_CHUNK = 256;   // tokens one CTA handles per attention work item
