@@ -112,6 +112,23 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
 
 // ---- 1-D bulk async copy global -> shared, completion on an mbarrier (SASS: UBLKCP) ---------------
 // dst and src 16-byte aligned, bytes a multiple of 16.
+// L2 policy for data that is read once (the weight stream): evict first, so that activations, KV rows and
+// prefetched operands survive in L2 next to it
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+                 : "memory");
+}
+// pull [src, src + bytes) into L2 ahead of use (16-byte aligned address, size a multiple of 16)
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src_gmem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(dst_smem)),
@@ -129,6 +146,19 @@ __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepc
 // ---- named barrier for a subset of the CTA's warps ----------------------------------------------
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// ---- wall clock (ns) for the optional in-kernel traces ---------------------------------------------
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// same, but not before `dep` has been computed (to time the arrival of loaded data)
+__device__ __forceinline__ unsigned long long globaltimer_after(uint32_t dep) {
+    if (dep == 0x7fc0dead) asm volatile("trap;");   // volatile statements keep their order: the read follows the compare
+    return globaltimer_ns();
 }
 
 // ---- arithmetic ---------------------------------------------------------------------------------

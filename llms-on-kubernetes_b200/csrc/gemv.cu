@@ -54,10 +54,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
     uint64_t* part_full = empty + GEMV_STAGES;                        // [2] partial sums written (compute -> epilogue)
     uint64_t* part_free = part_full + 2;                              // [2] partial sums read    (epilogue -> compute)
     ActSmem sm;
-    sm.xbar = part_free + 2;   // 15 barriers so far; ss_span starts after a pad to keep 16-byte alignment below
-    sm.ssbar = sm.xbar + 1;
-    sm.ss_span = (double*)(sm.ssbar + 2);
-    float* red = (float*)(sm.ss_span + MAX_SPANS);   // [2 parities][NCW warps][TILE_ROWS]
+    sm.xbar = part_free + 2;   // 14 barriers so far; two pad slots keep the 16-byte alignment below
+    sm.ss_warp = (double*)(sm.xbar + 3);
+    float* red = (float*)(sm.ss_warp + NCW);   // [2 parities][NCW warps][TILE_ROWS]
     const int K = a.K;
     sm.xq = (int8_t*)(red + 2 * NCW * TILE_ROWS);
     sm.xd = (float*)(sm.xq + K);
@@ -78,7 +77,6 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
         mbar_init(&part_free[0], 1);
         mbar_init(&part_free[1], 1);
         mbar_init(sm.xbar, csize * NCW);    // one arrival per compute warp of every CTA of the cluster
-        mbar_init(sm.ssbar, csize * NCW);
         mbar_fence_init();
     }
     // peers store into this CTA's shared memory and arrive on its barriers: they must be initialised first
@@ -92,6 +90,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
     if (warp == W_PRODUCER) {
         // ===== producer: weights only, independent of the previous kernel's output =====
         int stage = 0, phase = 0, si = 0;
+        const uint64_t stream_policy = l2_policy_evict_first();
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
             const GemvSeg& s = a.seg[si];
@@ -115,7 +114,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
                     mbar_arrive_expect_tx(&full[stage], total);
                 }
                 __syncwarp();
-                if (sz) bulk_g2s(ring + stage * G::STAGE_BYTES + lane * G::ROW_SLOT, src, sz, &full[stage]);
+                if (sz) bulk_g2s_hint(ring + stage * G::STAGE_BYTES + lane * G::ROW_SLOT, src, sz, &full[stage], stream_policy);
                 if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
             }
         }
@@ -151,29 +150,14 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
     if (warp == W_EPILOGUE) {
         // ===== epilogue: add the compute warps' shares in a fixed order, finish row pairs =====
         pdl_wait();   // the epilogue reads and writes activations of the previous kernel
+        const int pos = a.pos_ptr ? *a.pos_ptr : 0;
         int parity = 0, ph = 0, si = 0;   // ph: bit p = phase of part_full[p]
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
             while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
             const GemvSeg& s = a.seg[si];
-            mbar_wait(&part_full[parity], (ph >> parity) & 1);
-            const float* rp = red + parity * NCW * TILE_ROWS;
-            float v = 0.0f;
-            if (lane < TILE_ROWS) {
-#pragma unroll
-                for (int w = 0; w < NCW; w++) v += rp[w * TILE_ROWS + lane];
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&part_free[parity]);
+            epilogue_tile(a, s, tile - s.tile0, pos, red + parity * NCW * TILE_ROWS, &part_full[parity], &part_free[parity],
+                          (ph >> parity) & 1, lane);
             ph ^= 1 << parity;
-            const float vo = __shfl_xor_sync(0xffffffffu, v, 1);
-            if (lane < TILE_ROWS && (lane & 1) == 0) {
-                const int p = (tile - s.tile0) * GEMV_TILE_PAIRS + (lane >> 1);
-                if (p < s.n_pairs) {
-                    int ra, rb;
-                    pair_rows(s, p, &ra, &rb);
-                    epilogue(a, s, p, ra, rb, v, vo);
-                }
-            }
         }
         return;
     }
@@ -230,7 +214,7 @@ int gemv_act_for_type(int type) {
 size_t gemv_smem_bytes(int act, int K) {
     const size_t stage = act == ACT_Q8K ? Geo<ACT_Q8K>::STAGE_BYTES : Geo<ACT_Q80>::STAGE_BYTES;
     const size_t decb = act == ACT_Q8K ? Geo<ACT_Q8K>::DEC_BYTES : Geo<ACT_Q80>::DEC_BYTES;
-    size_t n = GEMV_STAGES * (stage + decb) + (3 * GEMV_STAGES + 7) * sizeof(uint64_t) + MAX_SPANS * sizeof(double) +
+    size_t n = GEMV_STAGES * (stage + decb) + (3 * GEMV_STAGES + 7) * sizeof(uint64_t) + NCW * sizeof(double) +
                2 * NCW * TILE_ROWS * sizeof(float);
     n += (size_t)K;                                            // int8 activations
     n += (act == ACT_Q8K ? K / 256 : K / 32) * sizeof(float);  // block scales

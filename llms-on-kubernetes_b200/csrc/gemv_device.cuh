@@ -182,7 +182,7 @@ __device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, const u
     float acc = 0.0f;
     if (ACT == ACT_Q8K) {
         const int c = lane & 3;
-        for (int b = warp; b < nb; b += NCW) {
+        for (int b = warp; b < nb; b += NCW) {   // (unrolling by two was measured: no gain)
             const int kb = kb0 + b;
             const float dx = x.d[kb];
             if (type == B2_TYPE_Q6_K) {
@@ -230,9 +230,8 @@ struct ActSmem {
     float* xd;
     int16_t* bs16;
     int16_t* bs32;
-    double* ss_span;   // [MAX_SPANS] per-span sum of squares (PRO_NORM)
+    double* ss_warp;   // [NCW] per-warp sum of squares (PRO_NORM)
     uint64_t* xbar;    // completes when every span has arrived
-    uint64_t* ssbar;
 };
 
 __device__ __forceinline__ void load8(const float* p, int i0, int K, float (&v)[8]) {
@@ -327,10 +326,11 @@ __device__ __forceinline__ void publish_to_cluster(uint64_t* bar, int lane, uint
     if (lane < (int)csize) mbar_arrive_remote(dsmem_addr(bar, (uint32_t)lane));
 }
 
-// parity: phase of xbar / ssbar to wait for (0 for a kernel that builds one activation vector)
+// parity: phase of xbar to wait for (0 for a kernel that builds one activation vector).
+// Called by all NCT compute threads (uses named barrier 1).
 template <int ACT>
 __device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uint8_t* smem_base, int tid, uint32_t rank, uint32_t csize,
-                                 uint32_t parity = 0, uint32_t ss_parity = 0) {
+                                 uint32_t parity = 0, unsigned long long* tr = nullptr) {
     const int K = a.K;
     const int lane = tid & 31, warp = tid >> 5;
     const int nspans = (K + 255) >> 8;
@@ -340,34 +340,32 @@ __device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uin
     // work a warp rarely owns more); further spans are re-read
     float v0[8], v1[8];
     if (a.prologue == PRO_NORM) {
-        // ggml rms_norm: sum of fp32 squares accumulated in double, mean, 1/sqrtf(mean + eps); then (x*scale)*w
-        auto publish_ss = [&](const float (&t)[8], int s) {
-            double ss = 0.0;
-#pragma unroll
-            for (int i = 0; i < 8; i++) ss += (double)(t[i] * t[i]);
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-            const uint32_t off = (uint32_t)((const uint8_t*)(sm.ss_span + s) - smem_base);
-            if (lane < (int)csize) dsmem_st_f64(dsmem_addr(smem_base, (uint32_t)lane) + off, ss);
-        };
+        // ggml rms_norm: sum of fp32 squares accumulated in double, mean, 1/sqrtf(mean + eps); then (x*scale)*w.
+        // Every CTA adds up the whole vector itself (K floats out of L2, in flight together with its own
+        // spans): a round trip through the cluster for the partial sums costs more than the redundant reads.
         if (first < nspans) load8(a.x, (first << 8) + lane * 8, K, v0);
         if (first + stride < nspans) load8(a.x, ((first + stride) << 8) + lane * 8, K, v1);
-        if (first < nspans) publish_ss(v0, first);
-        if (first + stride < nspans) publish_ss(v1, first + stride);
-        for (int s = first + 2 * stride; s < nspans; s += stride) {
+        double ss = 0.0;
+#pragma unroll 2
+        for (int i0 = tid * 8; i0 < K; i0 += NCT * 8) {
             float t[8];
-            load8(a.x, (s << 8) + lane * 8, K, t);
-            publish_ss(t, s);
-        }
-        publish_to_cluster(sm.ssbar, lane, csize);
-        mbar_wait_cluster(sm.ssbar, ss_parity);
-        // every CTA adds the per-span sums in the same order: lane-strided, then a butterfly
-        double tot = 0.0;
-        for (int s = lane; s < nspans; s += 32) tot += sm.ss_span[s];
+            load8(a.x, i0, K, t);
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+            for (int i = 0; i < 8; i++) ss += (double)(t[i] * t[i]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        if (lane == 0) sm.ss_warp[warp] = ss;
+        named_bar_sync(1, NCT);
+        double tot = 0.0;
+#pragma unroll
+        for (int w = 0; w < NCW; w++) tot += sm.ss_warp[w];
         const float mean = (float)(tot / (double)K);
         scale = 1.0f / sqrtf(mean + a.eps);
+        if (tr && tid == 0) {
+            tr[4] = globaltimer_after(__float_as_uint(v0[0]));
+            tr[5] = globaltimer_after(__float_as_uint(scale));
+        }
     }
     if (a.prologue == PRO_NORM) {
         auto norm_quant = [&](float (&t)[8], int s) {
@@ -388,6 +386,7 @@ __device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uin
         // issue the loads of two spans before the first use
         if (first < nspans) load8(a.x, (first << 8) + lane * 8, K, v0);
         if (first + stride < nspans) load8(a.x, ((first + stride) << 8) + lane * 8, K, v1);
+        if (tr && tid == 0) tr[4] = globaltimer_after(__float_as_uint(v0[0]));
         if (first < nspans) quantise_span<ACT>(v0, first << 8, lane, K, sm, smem_base, csize);
         if (first + stride < nspans) quantise_span<ACT>(v1, (first + stride) << 8, lane, K, sm, smem_base, csize);
         for (int s = first + 2 * stride; s < nspans; s += stride) {
@@ -396,17 +395,52 @@ __device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uin
             quantise_span<ACT>(t, s << 8, lane, K, sm, smem_base, csize);
         }
     }
+    if (tr && tid == 0) tr[6] = globaltimer_ns();
     publish_to_cluster(sm.xbar, lane, csize);
+    if (tr && tid == 0) tr[7] = globaltimer_ns();
     mbar_wait_cluster(sm.xbar, parity);
 }
 
 // ------------------------------------------------------------------------------------------------
 // epilogue for one row pair
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void epilogue(const GemvArgs& a, const GemvSeg& s, int p, int ra, int rb, float va, float vb) {
+// The operands that do not depend on the dot products (bias, residual, rotation) are fetched before the
+// epilogue warp waits for the partial sums, so their global-memory latency hides behind the tile's math.
+struct EpiOperands {
+    float bias_a, bias_b;   // 0 without bias
+    float res_a, res_b;     // EPI_RESID: current value of out[ra], out[rb]
+    float2 cs;              // EPI_ROPE_*: (cos, sin) of this pair
+    bool rotate;
+};
+
+__device__ __forceinline__ EpiOperands epilogue_operands(const GemvArgs& a, const GemvSeg& s, int ra, int rb, int pos) {
+    EpiOperands o;
+    o.bias_a = o.bias_b = o.res_a = o.res_b = 0.0f;
+    o.cs = make_float2(1.0f, 0.0f);
+    o.rotate = false;
     if (s.bias) {
-        va += s.bias[ra];
-        if (rb >= 0) vb += (s.pairing == PAIR_SPLIT ? s.bias_b : s.bias)[rb];
+        o.bias_a = s.bias[ra];
+        if (rb >= 0) o.bias_b = (s.pairing == PAIR_SPLIT ? s.bias_b : s.bias)[rb];
+    }
+    if (s.epi == EPI_RESID) {
+        o.res_a = s.out[ra];
+        if (rb >= 0) o.res_b = s.out[rb];
+    } else if (s.epi == EPI_ROPE_Q || s.epi == EPI_ROPE_K) {
+        const int hd = s.head_dim;
+        const int head = ra / hd;
+        const int i = s.pairing == PAIR_NEOX ? ra - head * hd : (ra - head * hd) >> 1;
+        if (i < a.rope_half) {
+            o.rotate = true;
+            o.cs = a.rope_tab[(size_t)pos * a.rope_half + i];
+        }
+    }
+    return o;
+}
+
+__device__ __forceinline__ void epilogue_apply(const GemvSeg& s, int p, int ra, int rb, float va, float vb, const EpiOperands& o, int pos) {
+    if (s.bias) {
+        va += o.bias_a;
+        if (rb >= 0) vb += o.bias_b;
     }
     switch (s.epi) {
         case EPI_STORE:
@@ -414,8 +448,8 @@ __device__ __forceinline__ void epilogue(const GemvArgs& a, const GemvSeg& s, in
             if (rb >= 0) s.out[rb] = vb;
             break;
         case EPI_RESID:
-            s.out[ra] += va;
-            if (rb >= 0) s.out[rb] += vb;
+            s.out[ra] = o.res_a + va;
+            if (rb >= 0) s.out[rb] = o.res_b + vb;
             break;
         case EPI_SWIGLU:
             // ggml silu: x / (1 + expf(-x))
@@ -423,15 +457,12 @@ __device__ __forceinline__ void epilogue(const GemvArgs& a, const GemvSeg& s, in
             break;
         case EPI_ROPE_Q:
         case EPI_ROPE_K: {
-            const int pos = *a.pos_ptr;
             const int hd = s.head_dim;
             const int head = ra / hd;
-            const int i = s.pairing == PAIR_NEOX ? ra - head * hd : (ra - head * hd) >> 1;
             float oa = va, ob = vb;
-            if (i < a.rope_half) {
-                const float2 cs = a.rope_tab[(size_t)pos * a.rope_half + i];
-                oa = va * cs.x - vb * cs.y;
-                ob = va * cs.y + vb * cs.x;
+            if (o.rotate) {
+                oa = va * o.cs.x - vb * o.cs.y;
+                ob = va * o.cs.y + vb * o.cs.x;
             }
             if (s.epi == EPI_ROPE_Q) {
                 s.out[ra] = oa;
@@ -444,7 +475,6 @@ __device__ __forceinline__ void epilogue(const GemvArgs& a, const GemvSeg& s, in
             break;
         }
         case EPI_V: {
-            const int pos = *a.pos_ptr;
             const int hd = s.head_dim;
             const int head = ra / hd;
             __half* dst = s.cache + ((size_t)head * s.n_ctx + pos) * hd;
@@ -453,6 +483,30 @@ __device__ __forceinline__ void epilogue(const GemvArgs& a, const GemvSeg& s, in
             break;
         }
     }
+}
+
+// epilogue warp, one tile: lanes 0, 2, 4, 6 own the tile's row pairs.  Fetch the operands, wait for the eight
+// compute warps' shares, add them in a fixed order, release the buffer, finish the pair.
+__device__ __forceinline__ void epilogue_tile(const GemvArgs& a, const GemvSeg& s, int ptile, int pos, const float* rp,
+                                              uint64_t* part_full, uint64_t* part_free, uint32_t full_phase, int lane) {
+    const int p = ptile * GEMV_TILE_PAIRS + (lane >> 1);
+    const bool owner = lane < TILE_ROWS && (lane & 1) == 0 && p < s.n_pairs;
+    int ra = 0, rb = -1;
+    EpiOperands o{};
+    if (owner) {
+        pair_rows(s, p, &ra, &rb);
+        o = epilogue_operands(a, s, ra, rb, pos);
+    }
+    mbar_wait(part_full, full_phase);
+    float v = 0.0f;
+    if (lane < TILE_ROWS) {
+#pragma unroll
+        for (int w = 0; w < NCW; w++) v += rp[w * TILE_ROWS + lane];
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(part_free);
+    const float vo = __shfl_xor_sync(0xffffffffu, v, 1);
+    if (owner) epilogue_apply(s, p, ra, rb, v, vo, o, pos);
 }
 
 

@@ -404,10 +404,8 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
             op.a_n_kv = I.n_kv;
             op.a_hd = I.head_dim;
             op.a_n_ctx = c->n_ctx;
-            op.a_max_chunks = step_attn_max_chunks(c->n_ctx);
-            op.a_pos = c->d_pos;
-            op.a_partials = c->step_attn_partials;
-            op.a_counters = c->step_counters + 8;   // [n_kv] after the grid-barrier and argmax counters
+            op.a_pos = c->d_pos;   // a_max_chunks / a_partials: build_step_program(), once the grid is known
+            op.a_counters = c->step_counters + 8;   // [<= n_head] after the grid-barrier and argmax counters
             record->push_back(op);
         } else if (!matvec_only) {
             if ((rc = launch_attn_decode(c->q, kc, vc, c->attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, c->d_pos, 0, c->max_splits,
@@ -481,7 +479,7 @@ int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
         p.ops = (const StepOp*)c->d_ops;
         p.n_ops = c->n_ops;
         p.max_k = c->step_max_k;
-        p.sync_counter = c->step_counters;
+        p.sync_counter = c->step_sync;
         p.trace = c->step_trace;
         const int rc = launch_step(p, c->step_act, st);
         if (rc == 0) c->launches_per_step = 1;
@@ -510,6 +508,19 @@ int build_step_program(b2_ctx* c) {
         set_error("step kernel: grid of %d CTAs exceeds the argmax scratch", grid);
         return B2_ERANGE;
     }
+    // attention scratch depends on the grid (the chunk length is chosen so that the items cover it once)
+    const auto& I = c->m->info;
+    B2_CUDA_CHECK(cudaMalloc((void**)&c->step_attn_partials, step_attn_partials_bytes(I.n_head, I.head_dim, c->n_ctx, grid)));
+    for (auto& op : ops)
+        if (op.kind == OP_ATTN) {
+            op.a_max_chunks = step_attn_max_chunks(c->n_ctx, grid);
+            op.a_partials = c->step_attn_partials;
+            op.a_min_chunk = STEP_ATTN_MIN_CHUNK;
+            if (const char* e = getenv("B2_ATTN_MIN_CHUNK")) {   // tuning knob: 32 .. 256 in steps of 32
+                const int v = atoi(e);
+                if (v >= 32 && v <= STEP_ATTN_MAX_CHUNK && v % 32 == 0) op.a_min_chunk = v;
+            }
+        }
     B2_CUDA_CHECK(cudaMalloc(&c->d_ops, ops.size() * sizeof(StepOp)));
     B2_CUDA_CHECK(cudaMemcpyAsync(c->d_ops, ops.data(), ops.size() * sizeof(StepOp), cudaMemcpyHostToDevice, c->stream));
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
@@ -517,8 +528,8 @@ int build_step_program(b2_ctx* c) {
     c->step_act = act;
     c->step_max_k = max_k;
     if (env_flag("B2_STEP_TRACE")) {
-        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_trace, ops.size() * 4 * sizeof(unsigned long long)));
-        B2_CUDA_CHECK(cudaMemset(c->step_trace, 0, ops.size() * 4 * sizeof(unsigned long long)));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_trace, ops.size() * STEP_TRACE_SLOTS * sizeof(unsigned long long)));
+        B2_CUDA_CHECK(cudaMemset(c->step_trace, 0, ops.size() * STEP_TRACE_SLOTS * sizeof(unsigned long long)));
         for (auto& op : ops) {
             c->step_desc.push_back(op.kind);
             c->step_desc.push_back(op.kind == OP_GEMV ? op.g.K : 0);
@@ -531,32 +542,37 @@ int build_step_program(b2_ctx* c) {
 // B2_STEP_TRACE=1: print where CTA 0 spent the last step, stage by stage (first two layers) and by stage class
 void dump_step_trace(b2_ctx* c) {
     if (!c->step_trace) return;
-    std::vector<unsigned long long> t((size_t)c->n_ops * 4);
+    const int S = STEP_TRACE_SLOTS;
+    std::vector<unsigned long long> t((size_t)c->n_ops * S);
     if (cudaMemcpy(t.data(), c->step_trace, t.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return;
     const char* kinds[] = {"embed", "gemv", "attn", "argmax"};
-    struct Acc { double wait = 0, pro = 0, tiles = 0, epi = 0; int n = 0; };
+    struct Acc { double wait = 0, pro = 0, tiles = 0, epi = 0, mark[4] = {0, 0, 0, 0}; int n = 0; };
     std::map<std::string, Acc> by;
     unsigned long long prev_arrive = 0;
-    fprintf(stderr, "b2 step trace (CTA 0, ns): stage kind K tiles | barrier-wait  prologue  tiles  epilogue+arrive\n");
+    fprintf(stderr, "b2 step trace (CTA 0, ns): stage kind K tiles | barrier-wait  prologue  tiles  epilogue+arrive | marks 4..7 after stage start\n");
     for (int i = 0; i < c->n_ops; i++) {
         const int kind = c->step_desc[3 * i], K = c->step_desc[3 * i + 1], tiles = c->step_desc[3 * i + 2];
-        const unsigned long long* s = &t[(size_t)i * 4];
+        const unsigned long long* s = &t[(size_t)i * S];
         const double wait = prev_arrive ? (double)(s[0] - prev_arrive) : 0.0;
-        const double pro = kind == OP_GEMV ? (double)(s[1] - s[0]) : 0.0;
-        const double tl = kind == OP_GEMV ? (double)(s[2] - s[1]) : 0.0;
-        const double epi = (double)(s[3] - (kind == OP_GEMV ? s[2] : s[0]));
+        const bool four = kind == OP_GEMV || kind == OP_ATTN;   // stages that stamp all four slots
+        const double pro = four ? (double)(s[1] - s[0]) : 0.0;
+        const double tl = four ? (double)(s[2] - s[1]) : 0.0;
+        const double epi = (double)(s[3] - (four ? s[2] : s[0]));
         char key[64];
         snprintf(key, sizeof key, "%s K=%d tiles=%d", kinds[kind], K, tiles);
         Acc& a = by[key];
         a.wait += wait; a.pro += pro; a.tiles += tl; a.epi += epi; a.n++;
+        for (int k = 0; k < 4; k++) a.mark[k] += s[4 + k] ? (double)(s[4 + k] - s[0]) : 0.0;
         if (i < 12) fprintf(stderr, "  %3d %-28s | %8.0f %8.0f %8.0f %8.0f\n", i, key, wait, pro, tl, epi);
         prev_arrive = s[3];
     }
     fprintf(stderr, "b2 step trace, mean per stage class:\n");
-    for (auto& kv : by)
-        fprintf(stderr, "  %-28s x%3d | %8.0f %8.0f %8.0f %8.0f\n", kv.first.c_str(), kv.second.n, kv.second.wait / kv.second.n,
-                kv.second.pro / kv.second.n, kv.second.tiles / kv.second.n, kv.second.epi / kv.second.n);
-    fprintf(stderr, "  whole step: %.0f ns\n", (double)(t[(size_t)(c->n_ops - 1) * 4 + 3] - t[0]));
+    for (auto& kv : by) {
+        const Acc& a = kv.second;
+        fprintf(stderr, "  %-28s x%3d | %8.0f %8.0f %8.0f %8.0f | %6.0f %6.0f %6.0f %6.0f\n", kv.first.c_str(), a.n, a.wait / a.n, a.pro / a.n,
+                a.tiles / a.n, a.epi / a.n, a.mark[0] / a.n, a.mark[1] / a.n, a.mark[2] / a.n, a.mark[3] / a.n);
+    }
+    fprintf(stderr, "  whole step: %.0f ns\n", (double)(t[(size_t)(c->n_ops - 1) * S + 3] - t[0]));
 }
 
 int build_graph(b2_ctx* c) {
@@ -672,10 +688,9 @@ extern "C" int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out) {
     // scratch + program of the persistent per-token kernel (B2_NO_STEP=1 keeps one launch per stage)
     c->use_step = !env_flag("B2_NO_STEP");
     if (c->use_step) {
-        const size_t pb = step_attn_partials_bytes(I.n_head, I.head_dim, n_ctx);
-        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_attn_partials, pb));
-        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_counters, (8 + 2 * I.n_kv) * sizeof(unsigned int)));
-        B2_CUDA_CHECK(cudaMemsetAsync(c->step_counters, 0, (8 + 2 * I.n_kv) * sizeof(unsigned int), c->stream));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_counters, (8 + I.n_head) * sizeof(unsigned int)));
+        B2_CUDA_CHECK(cudaMemsetAsync(c->step_counters, 0, (8 + I.n_head) * sizeof(unsigned int), c->stream));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_sync, STEP_SYNC_BYTES));
         B2_CUDA_CHECK(cudaMalloc((void**)&c->step_argmax_val, 1024 * sizeof(float)));
         B2_CUDA_CHECK(cudaMalloc((void**)&c->step_argmax_idx, 1024 * sizeof(int)));
         if ((rc = build_step_program(c.get()))) return rc;
@@ -701,7 +716,7 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->graph) cudaGraphDestroy(c->graph);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
                     c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch,
-                    c->d_ops, c->step_attn_partials, c->step_counters, c->step_argmax_val, c->step_argmax_idx, c->step_trace};
+                    c->d_ops, c->step_attn_partials, c->step_counters, c->step_sync, c->step_argmax_val, c->step_argmax_idx, c->step_trace};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pin) cudaFreeHost(c->h_pin);

@@ -52,7 +52,8 @@ struct b2_ctx {
     void* d_ops = nullptr;   // StepOp[n_ops]
     int n_ops = 0, step_act = -1, step_max_k = 0;
     float* step_attn_partials = nullptr;
-    unsigned int* step_counters = nullptr;   // [0] grid barrier, [1] argmax arrivals, [8 .. 8 + 2 n_kv) attention arrivals
+    unsigned int* step_counters = nullptr;   // [1] argmax arrivals, [8 .. 8 + n_head) attention arrivals
+    unsigned int* step_sync = nullptr;       // grid barrier: arrival counter + flags (STEP_SYNC_BYTES)
     unsigned long long* step_trace = nullptr;   // B2_STEP_TRACE=1: per-stage time stamps of CTA 0
     std::vector<int> step_desc;                 // per stage: kind, K, tiles (for the trace dump)
     float* step_argmax_val = nullptr;

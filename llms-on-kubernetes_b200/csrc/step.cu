@@ -11,7 +11,9 @@
 //     launch;
 //   * a stage ends with one atomic arrival per CTA on a global counter (after the CTA's epilogue
 //     stores, behind a __threadfence); the next stage's consumers poll it with ld.acquire.gpu;
-//   * embedding lookup, attention and greedy sampling run as stages on the compute warps.
+//   * everything a stage needs that does not depend on the previous stage's results -- its descriptor,
+//     the position -- is fetched into shared memory before the wait on the grid barrier;
+//   * embedding lookup, attention (step_attn.cuh) and greedy sampling run as stages on the compute warps.
 // All CTAs must be co-resident (they wait on each other): the grid is sized by
 // cudaOccupancyMaxActiveClusters, and every wait is bounded and traps instead of hanging.
 #include "step.cuh"
@@ -20,10 +22,12 @@
 
 #include "dequant.cuh"
 #include "gemv_device.cuh"
+#include "step_attn.cuh"
 
 namespace b2 {
 
 using namespace gemvdev;
+using namespace stepattn;
 
 namespace {
 
@@ -34,232 +38,195 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-// wait until `target` CTAs have arrived (bounded: a CTA that is not resident must not hang the GPU)
-__device__ __forceinline__ void grid_wait(const unsigned int* ctr, unsigned int target) {
+// ---- grid barrier -------------------------------------------------------------------------------------
+// Arrivals are counted in word 0 of `sync` (stage number s is complete when it reaches s * grid).  One thread
+// per CTA polls it and hands the result to the CTA's other waiting warp through shared memory.  (Tried and
+// measured slower by ~1.2 us per stage: the completing CTA publishing per-group flags on separate L2 lines --
+// the extra hop costs more than the polling traffic on the counter's line.)  All waits are bounded: a CTA
+// that is not resident must not hang the GPU.
+// one thread per CTA, after the CTA's stores of the stage are fenced
+__device__ __forceinline__ void grid_arrive(unsigned int* sync, unsigned int stage_no) {
+    (void)stage_no;
+    atomicAdd(sync, 1u);
+}
+// wait until stage `stage_no` is complete everywhere, then tell the CTA's other waiters
+__device__ __forceinline__ void grid_wait(const unsigned int* sync, unsigned int stage_no, volatile unsigned int* cta_stage) {
+    const unsigned int target = stage_no * gridDim.x;
 #pragma unroll 1
     for (uint32_t i = 0; i < (1u << 24); i++) {
-        if (ld_acquire_gpu(ctr) >= target) return;
-        __nanosleep(32);
+        if (ld_acquire_gpu(sync) >= target) {
+            __threadfence_block();
+            *cta_stage = stage_no;
+            return;
+        }
+        __nanosleep(20);
     }
     asm volatile("trap;");
 }
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
+// the CTA's other waiter (epilogue warp): the polling thread's acquire already refreshed this SM's L1
+__device__ __forceinline__ void grid_wait_local(volatile unsigned int* cta_stage, unsigned int stage_no) {
+#pragma unroll 1
+    for (uint32_t i = 0; i < (1u << 26); i++) {
+        if (*cta_stage >= stage_no) {
+            __threadfence_block();
+            return;
+        }
+        __nanosleep(20);
+    }
+    asm volatile("trap;");
 }
 // profiling stamp of CTA 0 (no-op unless the program carries a trace buffer)
 __device__ __forceinline__ void stamp(const StepProgram& P, int oi, int slot) {
-    if (P.trace && blockIdx.x == 0) P.trace[oi * 4 + slot] = globaltimer_ns();
+    if (P.trace && blockIdx.x == 0) P.trace[oi * STEP_TRACE_SLOTS + slot] = globaltimer_ns();
 }
 
-// ---- attention work item: (kv head, chunk of STEP_ATTN_CHUNK tokens), all query heads of the group ------------
-// Same numerics as attn.cu: q and the probabilities are rounded to fp16, fp32 accumulation; a single
-// chunk normalises before rounding (exactly the oracle's order), several chunks merge by log-sum-exp.
-constexpr int A_MAXG = 4;   // query heads processed together (register budget); larger GQA groups run as two batches
-struct AttnSmem {
-    float* scores;   // [A_MAXG][STEP_ATTN_CHUNK]
-    float* red;      // [A_MAXG][NCW]
-    float* out;      // [A_MAXG][128]
-    float* ml;       // [2][A_MAXG]
-    int* flag;
-};
-constexpr size_t ATTN_SMEM_BYTES = (A_MAXG * STEP_ATTN_CHUNK + A_MAXG * NCW + A_MAXG * 128 + 2 * A_MAXG + 4) * sizeof(float);
-
-// heads [h0, h0 + hb) of the kv head's group (hb <= A_MAXG: the register arrays below are per head)
-template <int HD>
-__device__ void attn_item(const StepOp& op, int kvh, int h0, int hb, int chunk, int n_chunks, int T, const AttnSmem& sm, int tid) {
-    constexpr int LPT = HD / 8, TPW = 32 / LPT;
-    const int gq = op.a_n_head / op.a_n_kv;
-    const int g = hb;
-    const int warp = tid >> 5, lane = tid & 31, sub = lane / LPT, ln = lane % LPT;
-    const int t0 = chunk * STEP_ATTN_CHUNK, n = min(T - t0, STEP_ATTN_CHUNK);
-    const __half* kbase = op.a_k + ((size_t)kvh * op.a_n_ctx + t0) * HD;
-    const __half* vbase = op.a_v + ((size_t)kvh * op.a_n_ctx + t0) * HD;
-    const float scale = 1.0f / sqrtf((float)HD);
-    float qf[A_MAXG][8];
-#pragma unroll
-    for (int h = 0; h < A_MAXG; h++)
-        if (h < g) {
-            const float* qp = op.a_q + ((size_t)(kvh * gq + h0 + h)) * HD + ln * 8;
-#pragma unroll
-            for (int i = 0; i < 8; i++) qf[h][i] = __half2float(__float2half_rn(qp[i]));
-        }
-    for (int tb = warp * TPW; tb < n; tb += NCW * TPW) {
-        const int t = tb + sub;
-        float d[A_MAXG];
-#pragma unroll
-        for (int h = 0; h < A_MAXG; h++) d[h] = 0.0f;
-        if (t < n) {
-            const uint4 kv = *(const uint4*)(kbase + (size_t)t * HD + ln * 8);
-            const __half2* k2 = (const __half2*)&kv;
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const float2 kf = __half22float2(k2[i]);
-#pragma unroll
-                for (int h = 0; h < A_MAXG; h++)
-                    if (h < g) d[h] += kf.x * qf[h][2 * i] + kf.y * qf[h][2 * i + 1];
-            }
-        }
-#pragma unroll
-        for (int h = 0; h < A_MAXG; h++)
-            if (h < g) {
-#pragma unroll
-                for (int o = LPT / 2; o > 0; o >>= 1) d[h] += __shfl_xor_sync(0xffffffffu, d[h], o);
-                if (ln == 0 && t < n) sm.scores[h * STEP_ATTN_CHUNK + t] = d[h] * scale;
-            }
-    }
-    named_bar_sync(1, NCT);
-    float pmax[A_MAXG], psum[A_MAXG];
-#pragma unroll
-    for (int h = 0; h < A_MAXG; h++)
-        if (h < g) {
-            float m = -INFINITY;
-            for (int t = tid; t < n; t += NCT) m = fmaxf(m, sm.scores[h * STEP_ATTN_CHUNK + t]);
-            m = warp_max(m);
-            if (lane == 0) sm.red[h * NCW + warp] = m;
-        }
-    named_bar_sync(1, NCT);
-#pragma unroll
-    for (int h = 0; h < A_MAXG; h++)
-        if (h < g) {
-            float m = sm.red[h * NCW];
-#pragma unroll
-            for (int w = 1; w < NCW; w++) m = fmaxf(m, sm.red[h * NCW + w]);
-            pmax[h] = m;
-        }
-    named_bar_sync(1, NCT);
-#pragma unroll
-    for (int h = 0; h < A_MAXG; h++)
-        if (h < g) {
-            float s = 0.0f;
-            for (int t = tid; t < n; t += NCT) {
-                const float e = expf(sm.scores[h * STEP_ATTN_CHUNK + t] - pmax[h]);
-                sm.scores[h * STEP_ATTN_CHUNK + t] = e;
-                s += e;
-            }
-            s = warp_sum(s);
-            if (lane == 0) sm.red[h * NCW + warp] = s;
-        }
-    named_bar_sync(1, NCT);
-#pragma unroll
-    for (int h = 0; h < A_MAXG; h++)
-        if (h < g) {
-            float s = 0.0f;
-#pragma unroll
-            for (int w = 0; w < NCW; w++) s += sm.red[h * NCW + w];
-            psum[h] = s;
-        }
-    const bool exact = n_chunks == 1;
-    float acc[A_MAXG][8];
-#pragma unroll
-    for (int h = 0; h < A_MAXG; h++)
-#pragma unroll
-        for (int i = 0; i < 8; i++) acc[h][i] = 0.0f;
-    for (int tb = warp * TPW; tb < n; tb += NCW * TPW) {
-        const int t = tb + sub;
-        if (t < n) {
-            const uint4 vv = *(const uint4*)(vbase + (size_t)t * HD + ln * 8);
-            const __half2* v2 = (const __half2*)&vv;
-            float vf[8];
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const float2 f = __half22float2(v2[i]);
-                vf[2 * i] = f.x;
-                vf[2 * i + 1] = f.y;
-            }
-#pragma unroll
-            for (int h = 0; h < A_MAXG; h++)
-                if (h < g) {
-                    const float e = sm.scores[h * STEP_ATTN_CHUNK + t];
-                    const float pr = __half2float(__float2half_rn(exact ? e * (1.0f / psum[h]) : e));
-#pragma unroll
-                    for (int i = 0; i < 8; i++) acc[h][i] += pr * vf[i];
-                }
-        }
-    }
-#pragma unroll
-    for (int h = 0; h < A_MAXG; h++)
-        if (h < g) {
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-                float v = acc[h][i];
-#pragma unroll
-                for (int o = LPT; o < 32; o <<= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                acc[h][i] = v;
-            }
-        }
-    for (int i = tid; i < A_MAXG * 128; i += NCT) sm.out[i] = 0.0f;
-    named_bar_sync(1, NCT);
-    for (int w = 0; w < NCW; w++) {
-        if (warp == w && sub == 0) {
-#pragma unroll
-            for (int h = 0; h < A_MAXG; h++)
-                if (h < g) {
-#pragma unroll
-                    for (int i = 0; i < 8; i++) sm.out[h * 128 + ln * 8 + i] += acc[h][i];
-                }
-        }
-        named_bar_sync(1, NCT);
-    }
-    if (exact) {
-        for (int i = tid; i < g * HD; i += NCT) {
-            const int h = i / HD, dd = i - h * HD;
-            op.a_out[((size_t)(kvh * gq + h0 + h)) * HD + dd] = sm.out[h * 128 + dd];
-        }
-        named_bar_sync(1, NCT);
-        return;
-    }
-    // partial record {max, sum, out[HD]} of this chunk; the last chunk of the head to arrive merges
-    const size_t stride = (size_t)HD + 2;
-    for (int i = tid; i < g * HD; i += NCT) {
-        const int h = i / HD, dd = i - h * HD;
-        op.a_partials[((size_t)(kvh * gq + h0 + h) * op.a_max_chunks + chunk) * stride + 2 + dd] = sm.out[h * 128 + dd];
-    }
-    if (tid == 0) {
-#pragma unroll
-        for (int h = 0; h < A_MAXG; h++)
-            if (h < g) {
-                float* rec = op.a_partials + ((size_t)(kvh * gq + h0 + h) * op.a_max_chunks + chunk) * stride;
-                rec[0] = pmax[h];
-                rec[1] = psum[h];
-            }
-    }
-    __threadfence();
-    named_bar_sync(1, NCT);
-    if (tid == 0) {
-        unsigned int* ctr = &op.a_counters[kvh * 2 + h0 / A_MAXG];   // one arrival counter per (kv head, head batch)
-        const unsigned int arrived = atomicAdd(ctr, 1u) + 1u;
-        *sm.flag = arrived == (unsigned int)n_chunks;
-        if (*sm.flag) *ctr = 0u;
-    }
-    named_bar_sync(1, NCT);
-    if (*sm.flag) {
-        __threadfence();
-        for (int i = tid; i < g * HD; i += NCT) {
-            const int h = i / HD, dd = i - h * HD;
-            const float* base = op.a_partials + ((size_t)(kvh * gq + h0 + h) * op.a_max_chunks) * stride;
-            float m = -INFINITY;
-            for (int s = 0; s < n_chunks; s++) m = fmaxf(m, __ldcg(base + s * stride));
-            float den = 0.0f, num = 0.0f;
-            for (int s = 0; s < n_chunks; s++) {
-                const float w = expf(__ldcg(base + s * stride) - m);
-                den += __ldcg(base + s * stride + 1) * w;
-                num += __ldcg(base + s * stride + 2 + dd) * w;
-            }
-            op.a_out[((size_t)(kvh * gq + h0 + h)) * HD + dd] = num / den;
-        }
-    }
-    named_bar_sync(1, NCT);
-}
-
-// copy a stage's mat-vec descriptor from the program (global memory) into shared memory with one warp
-__device__ __forceinline__ void stage_descriptor(GemvArgs* dst, const GemvArgs* src, int lane) {
-    static_assert(sizeof(GemvArgs) % 4 == 0, "descriptor copy is word-wise");
+// copy `words` 32-bit words of static program data from global into shared memory with one warp
+__device__ __forceinline__ void stage_words(void* dst, const void* src, int words, int lane) {
     const uint32_t* s = (const uint32_t*)src;
     uint32_t* d = (uint32_t*)dst;
-    for (int i = lane; i < (int)(sizeof(GemvArgs) / 4); i += 32) d[i] = s[i];
+    for (int i = lane; i < words; i += 32) d[i] = s[i];
     __syncwarp();
+}
+static_assert(sizeof(GemvArgs) % 4 == 0 && sizeof(StepOp) % 4 == 0, "descriptor copies are word-wise");
+
+// shared-memory carve-up behind the mat-vec kernel's own (ring, decoded headers, barriers, partial sums)
+struct StepSmem {
+    GemvArgs* slots;   // [3] the current mat-vec descriptor of the producer, decoder and epilogue warps
+    StepOp* cslot;     // [2] the compute warps' current / next stage (double-buffered)
+    int* aux;          // [2] per cslot: sequence length of an attention stage
+    uint8_t* xbase;    // activation buffers, re-carved per mat-vec; attention and argmax alias them
+};
+constexpr size_t STEP_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 16 + 16;
+
+// ---- the stages that are not mat-vecs, run by the 256 compute threads (kept out of line: their registers
+// ---- must not weigh on the mat-vec loop) --------------------------------------------------------------------
+__device__ __noinline__ void embed_stage(const StepOp& op, int tid) {
+    int tok = *op.e_token;
+    if (tok < 0 || tok >= op.e_vocab) tok = 0;
+    const uint8_t* row = op.e_table + (size_t)tok * op.e_row_bytes;
+    for (int g4 = blockIdx.x * NCT + tid; g4 < op.e_d_model / 4; g4 += gridDim.x * NCT) ((float4*)op.e_x)[g4] = dq4(op.e_type, row, g4);
+}
+
+// how an attention stage over T tokens is cut into work items (kv head, batch of <= 4 query heads, chunk),
+// dealt round-robin over the grid
+struct AttnSplit {
+    int gq, n_batches, chunk_tokens, n_chunks, n_items;
+    __device__ AttnSplit(int n_head, int n_kv, int min_chunk, int T) {
+        gq = n_head / n_kv;
+        n_batches = (gq + A_MAXG - 1) / A_MAXG;
+        chunk_tokens = attn_chunk_tokens(T, n_kv * n_batches, (int)gridDim.x, min_chunk);
+        n_chunks = (T + chunk_tokens - 1) / chunk_tokens;
+        n_items = n_kv * n_batches * n_chunks;
+    }
+    __device__ void item(int i, int T, int* kvh, int* h0, int* hb, int* chunk, int* t0, int* n) const {
+        *chunk = i % n_chunks;
+        *kvh = i / (n_chunks * n_batches);
+        *h0 = ((i / n_chunks) % n_batches) * A_MAXG;
+        *hb = min(A_MAXG, gq - *h0);
+        *t0 = *chunk * chunk_tokens;
+        *n = min(T - *t0, chunk_tokens);
+    }
+};
+
+__device__ __noinline__ void attn_stage(const StepOp& op, uint8_t* xbase, int T, int tid, unsigned long long* tr) {
+    AttnSmem as;
+    as.scores = (float*)xbase;
+    as.prob = as.scores + A_MAXG * A_TOK;
+    as.part = as.prob + A_MAXG * A_TOK;
+    as.ml = as.part + 3 * A_MAXG * 128;
+    as.flag = (int*)(as.ml + 2 * A_MAXG);
+    const AttnSplit sp(op.a_n_head, op.a_n_kv, op.a_min_chunk, T);
+    if (sp.n_chunks > op.a_max_chunks) asm volatile("trap;");   // scratch is sized for this bound (step_attn_max_chunks)
+    for (int item = blockIdx.x; item < sp.n_items; item += gridDim.x) {
+        int kvh, h0, hb, chunk, t0, n;
+        sp.item(item, T, &kvh, &h0, &hb, &chunk, &t0, &n);
+        if (op.a_hd == 64) attn_item<64>(op, kvh, h0, hb, chunk, sp.n_chunks, t0, n, as, tid, tr);
+        else attn_item<128>(op, kvh, h0, hb, chunk, sp.n_chunks, t0, n, as, tid, tr);
+    }
+}
+
+// Between two tokens 4.6 GB of weights pass through L2, so whatever a stage reads besides the stream -- the KV
+// cache rows of an attention stage, a norm weight vector -- would be a DRAM round trip on the stage's critical
+// path, queued behind the weight prefetch.  One stage ahead (while this CTA still waits for the previous stage)
+// one warp asks L2 to fetch them.  `op` is the NEXT stage's descriptor in global memory (static data).
+__device__ __noinline__ void prefetch_next_stage(const StepOp& op, int lane) {
+    const int kind = op.kind;
+    if (kind == OP_ATTN) {
+        const int T = *op.a_pos + 1;
+        const AttnSplit sp(op.a_n_head, op.a_n_kv, op.a_min_chunk, T);
+        const int hd = op.a_hd;
+        // the K and V rows of this CTA's items; the batches of a kv head share them (first batch fetches)
+        for (int item = blockIdx.x + lane * gridDim.x; item < sp.n_items; item += 32 * gridDim.x) {
+            int kvh, h0, hb, chunk, t0, n;
+            sp.item(item, T, &kvh, &h0, &hb, &chunk, &t0, &n);
+            if (h0 != 0) continue;
+            const size_t off = ((size_t)kvh * op.a_n_ctx + t0) * hd;
+            const uint32_t bytes = (uint32_t)n * hd * sizeof(__half);
+            bulk_prefetch_l2(op.a_k + off, bytes);
+            bulk_prefetch_l2(op.a_v + off, bytes);
+        }
+    } else if (kind == OP_GEMV) {
+        // the norm weights: one CTA per 2 KiB piece
+        if (op.g.prologue == PRO_NORM && lane == 0) {
+            const int piece = 512, n_pieces = (op.g.K + piece - 1) / piece;
+            for (int i = blockIdx.x; i < n_pieces; i += gridDim.x) {
+                const int n = min(piece, op.g.K - i * piece);
+                bulk_prefetch_l2(op.g.norm_w + (size_t)i * piece, (uint32_t)n * sizeof(float));
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void argmax_fold(float& bv, int& bi, float ov, int oi) {
+    if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+}
+
+// greedy sampling (first index of the maximum) + the device-resident loop's bookkeeping in the last CTA to arrive
+__device__ __noinline__ void argmax_stage(const StepOp& op, uint8_t* xbase, int tid) {
+    const int warp = tid >> 5, lane = tid & 31;
+    float bv = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int64_t i = (int64_t)blockIdx.x * NCT + tid; i < op.s_n; i += (int64_t)gridDim.x * NCT) {
+        const float v = op.s_logits[i];
+        if (v > bv) { bv = v; bi = (int)i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) argmax_fold(bv, bi, __shfl_xor_sync(0xffffffffu, bv, o), __shfl_xor_sync(0xffffffffu, bi, o));
+    float* sv = (float*)xbase;
+    int* sidx = (int*)(sv + NCW);
+    if (lane == 0) { sv[warp] = bv; sidx[warp] = bi; }
+    named_bar_sync(1, NCT);
+    if (warp != 0) return;
+    bv = lane < NCW ? sv[lane] : -INFINITY;
+    bi = lane < NCW ? sidx[lane] : 0x7fffffff;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) argmax_fold(bv, bi, __shfl_xor_sync(0xffffffffu, bv, o), __shfl_xor_sync(0xffffffffu, bi, o));
+    unsigned int arrived = 0;
+    if (lane == 0) {
+        op.s_val[blockIdx.x] = bv;
+        op.s_idx[blockIdx.x] = bi;
+        __threadfence();
+        arrived = atomicAdd(op.s_counter, 1u) + 1u;
+    }
+    arrived = __shfl_sync(0xffffffffu, arrived, 0);
+    if (arrived != gridDim.x) return;
+    __threadfence();
+    bv = -INFINITY;
+    bi = 0x7fffffff;
+    for (unsigned int b = lane; b < gridDim.x; b += 32) argmax_fold(bv, bi, __ldcg(op.s_val + b), __ldcg(op.s_idx + b));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) argmax_fold(bv, bi, __shfl_xor_sync(0xffffffffu, bv, o), __shfl_xor_sync(0xffffffffu, bi, o));
+    if (lane == 0) {
+        if (bi == 0x7fffffff) bi = 0;
+        *op.s_token = bi;
+        if (op.s_out) {
+            const int s = *op.s_step;
+            if (s < op.s_cap) op.s_out[s] = bi;
+            *op.s_step = s + 1;
+        }
+        if (op.s_pos) *op.s_pos = *op.s_pos + 1;
+        *op.s_counter = 0u;
+    }
 }
 
 template <int ACT>
@@ -275,12 +242,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
     uint64_t* part_free = part_full + 2;
     ActSmem sm;
     sm.xbar = part_free + 2;
-    sm.ssbar = sm.xbar + 1;
-    sm.ss_span = (double*)(sm.ssbar + 2);
-    float* red = (float*)(sm.ss_span + MAX_SPANS);
-    // the current stage's mat-vec descriptor, one private copy per role (the roles are at different stages)
-    GemvArgs* slots = (GemvArgs*)(red + 2 * NCW * TILE_ROWS);
-    uint8_t* xbase = (uint8_t*)(slots + 4);   // activation buffers, re-carved per mat-vec; attention aliases them
+    sm.ss_warp = (double*)(sm.xbar + 3);
+    float* red = (float*)(sm.ss_warp + NCW);
+    StepSmem ss;
+    ss.slots = (GemvArgs*)(red + 2 * NCW * TILE_ROWS);
+    ss.cslot = (StepOp*)(ss.slots + 3);
+    ss.aux = (int*)(ss.cslot + 2);
+    ss.xbase = (uint8_t*)(((uintptr_t)(ss.aux + 4) + 15) & ~(uintptr_t)15);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank(), csize = cluster_nctarank();
@@ -296,21 +264,22 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
         mbar_init(&part_free[0], 1);
         mbar_init(&part_free[1], 1);
         mbar_init(sm.xbar, csize * NCW);
-        mbar_init(sm.ssbar, csize * NCW);
+        ss.aux[2] = 0;   // cta_stage: the last grid-barrier stage number this CTA has seen complete
         mbar_fence_init();
     }
     cluster_sync_all();
-    const unsigned int G_CTAS = gridDim.x;
+    volatile unsigned int* cta_stage = (volatile unsigned int*)&ss.aux[2];
 
     if (warp == W_PRODUCER) {
         // ===== producer: streams every mat-vec stage's weights in program order, never waits for a stage to start =====
         int stage = 0, phase = 0;
+        const uint64_t stream_policy = l2_policy_evict_first();
         for (int oi = 0; oi < P.n_ops; oi++) {
             const StepOp& op = P.ops[oi];
             if (op.kind != OP_GEMV) continue;
             __syncwarp();
-            stage_descriptor(&slots[0], &op.g, lane);
-            const GemvArgs& a = slots[0];
+            stage_words(&ss.slots[0], &op.g, sizeof(GemvArgs) / 4, lane);
+            const GemvArgs& a = ss.slots[0];
             const int nblk_row = a.K / (ACT == ACT_Q8K ? 256 : 32);
             const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
             int si = 0;
@@ -337,7 +306,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                         mbar_arrive_expect_tx(&full[stage], total);
                     }
                     __syncwarp();
-                    if (sz) bulk_g2s(ring + stage * G::STAGE_BYTES + lane * G::ROW_SLOT, src, sz, &full[stage]);
+                    if (sz) bulk_g2s_hint(ring + stage * G::STAGE_BYTES + lane * G::ROW_SLOT, src, sz, &full[stage], stream_policy);
                     if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -351,8 +320,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             const StepOp& op = P.ops[oi];
             if (op.kind != OP_GEMV) continue;
             __syncwarp();
-            stage_descriptor(&slots[1], &op.g, lane);
-            const GemvArgs& a = slots[1];
+            stage_words(&ss.slots[1], &op.g, sizeof(GemvArgs) / 4, lane);
+            const GemvArgs& a = ss.slots[1];
             const int nblk_row = a.K / (ACT == ACT_Q8K ? 256 : 32);
             const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
             int si = 0;
@@ -382,77 +351,66 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
     if (warp == W_EPILOGUE) {
         // ===== epilogue: finish row pairs; after the CTA's last tile of a stage, arrive on the grid barrier =====
         int parity = 0, ph = 0;
+        int pos = 0;
         for (int oi = 0; oi < P.n_ops; oi++) {
             const StepOp& op = P.ops[oi];
             if (op.kind != OP_GEMV) continue;   // the compute warps signal those stages
-            // never arrive for a stage before the previous one is complete everywhere: a CTA without tiles in
-            // this stage would otherwise run ahead and release other CTAs early
+            // static data first (descriptor; the position only changes in the step's last stage) ...
+            stage_words(&ss.slots[2], &op.g, sizeof(GemvArgs) / 4, lane);
+            const GemvArgs& a = ss.slots[2];
+            if (a.pos_ptr) pos = *a.pos_ptr;
+            // ... then never arrive for a stage before the previous one is complete everywhere: a CTA without
+            // tiles in this stage would otherwise run ahead and release other CTAs early
             if (oi > 0) {
-                if (lane == 0) grid_wait(P.sync_counter, (unsigned int)oi * G_CTAS);
+                if (lane == 0) grid_wait_local(cta_stage, (unsigned int)oi);
                 __syncwarp();
             }
-            stage_descriptor(&slots[2], &op.g, lane);
-            const GemvArgs& a = slots[2];
             int si = 0;
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
                 while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
                 const GemvSeg& s = a.seg[si];
-                mbar_wait(&part_full[parity], (ph >> parity) & 1);
-                const float* rp = red + parity * NCW * TILE_ROWS;
-                float v = 0.0f;
-                if (lane < TILE_ROWS) {
-#pragma unroll
-                    for (int w = 0; w < NCW; w++) v += rp[w * TILE_ROWS + lane];
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&part_free[parity]);
+                epilogue_tile(a, s, tile - s.tile0, pos, red + parity * NCW * TILE_ROWS, &part_full[parity], &part_free[parity],
+                              (ph >> parity) & 1, lane);
                 ph ^= 1 << parity;
-                const float vo = __shfl_xor_sync(0xffffffffu, v, 1);
-                if (lane < TILE_ROWS && (lane & 1) == 0) {
-                    const int p = (tile - s.tile0) * GEMV_TILE_PAIRS + (lane >> 1);
-                    if (p < s.n_pairs) {
-                        int ra, rb;
-                        pair_rows(s, p, &ra, &rb);
-                        epilogue(a, s, p, ra, rb, v, vo);
-                    }
-                }
             }
             // a fence orders only the calling thread's stores: every lane that wrote results fences, then one arrives
             __threadfence();
             __syncwarp();
             if (lane == 0) {
-                atomicAdd(P.sync_counter, 1u);
+                grid_arrive(P.sync_counter, (unsigned int)oi + 1u);
                 stamp(P, oi, 3);
             }
         }
         return;
     }
-
     // ===== compute warps =====
     const int r = lane >> 2;
     int stage = 0, phase = 0, parity = 0, fph = 3;
-    uint32_t xpar = 0, sspar = 0;
+    uint32_t xpar = 0;
     for (int oi = 0; oi < P.n_ops; oi++) {
-        const StepOp& op = P.ops[oi];
-        // every CTA has arrived oi times per completed stage: wait for the previous stage everywhere
-        if (oi > 0) {
-            if (warp == 0 && lane == 0) grid_wait(P.sync_counter, (unsigned int)oi * G_CTAS);
-            named_bar_sync(1, NCT);
+        // warp 0 stages the stage's descriptor (static) while the previous stage is still finishing elsewhere;
+        // the other buffer may still be read by slower warps of this CTA
+        StepOp* cs = &ss.cslot[oi & 1];
+        if (warp == 0) {
+            stage_words(cs, &P.ops[oi], sizeof(StepOp) / 4, lane);
+            if (lane == 0 && cs->kind == OP_ATTN) ss.aux[oi & 1] = *cs->a_pos + 1;
+            if (oi + 1 < P.n_ops) prefetch_next_stage(P.ops[oi + 1], lane);
+            // every CTA has arrived oi times per completed stage: wait for the previous stage everywhere
+            if (oi > 0 && lane == 0) grid_wait(P.sync_counter, (unsigned int)oi, cta_stage);
         }
+        named_bar_sync(1, NCT);
         if (tid == 0) stamp(P, oi, 0);
+        const StepOp& op = *cs;
         if (op.kind == OP_GEMV) {
-            if (warp == 0) stage_descriptor(&slots[3], &op.g, lane);
-            named_bar_sync(1, NCT);
-            const GemvArgs& a = slots[3];
+            const GemvArgs& a = op.g;
             const int K = a.K;
-            sm.xq = (int8_t*)xbase;
+            sm.xq = (int8_t*)ss.xbase;
             sm.xd = (float*)(sm.xq + K);
             sm.bs16 = (int16_t*)(sm.xd + (ACT == ACT_Q8K ? K / 256 : K / 32));
             sm.bs32 = sm.bs16 + K / 16;
-            build_activation<ACT>(a, sm, smem, tid, rank, csize, xpar, sspar);
+            build_activation<ACT>(a, sm, smem, tid, rank, csize, xpar, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
             if (tid == 0) stamp(P, oi, 1);
             xpar ^= 1;
-            if (a.prologue == PRO_NORM) sspar ^= 1;
             const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};
             const int nblk_row = K / (ACT == ACT_Q8K ? 256 : 32);
             const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
@@ -486,77 +444,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             if (tid == 0) stamp(P, oi, 2);
             // the epilogue warp arrives on the grid barrier for this stage
         } else {
-            if (op.kind == OP_EMBED) {
-                int tok = *op.e_token;
-                if (tok < 0 || tok >= op.e_vocab) tok = 0;
-                const uint8_t* row = op.e_table + (size_t)tok * op.e_row_bytes;
-                for (int g4 = blockIdx.x * NCT + tid; g4 < op.e_d_model / 4; g4 += gridDim.x * NCT) ((float4*)op.e_x)[g4] = dq4(op.e_type, row, g4);
-            } else if (op.kind == OP_ATTN) {
-                AttnSmem as;
-                as.scores = (float*)xbase;
-                as.red = as.scores + A_MAXG * STEP_ATTN_CHUNK;
-                as.out = as.red + A_MAXG * NCW;
-                as.ml = as.out + A_MAXG * 128;
-                as.flag = (int*)(as.ml + 2 * A_MAXG);
-                const int T = *op.a_pos + 1;
-                int n_chunks = (T + STEP_ATTN_CHUNK - 1) / STEP_ATTN_CHUNK;
-                if (n_chunks > op.a_max_chunks) n_chunks = op.a_max_chunks;   // cannot happen: T <= n_ctx
-                const int gq = op.a_n_head / op.a_n_kv;
-                const int n_batches = (gq + A_MAXG - 1) / A_MAXG;
-                // work item = (kv head, batch of <= 4 query heads, chunk of 256 tokens), dealt round-robin over the grid
-                for (int item = blockIdx.x; item < op.a_n_kv * n_batches * n_chunks; item += gridDim.x) {
-                    const int chunk = item % n_chunks, hb_i = (item / n_chunks) % n_batches, kvh = item / (n_chunks * n_batches);
-                    const int h0 = hb_i * A_MAXG, hb = min(A_MAXG, gq - h0);
-                    if (op.a_hd == 64) attn_item<64>(op, kvh, h0, hb, chunk, n_chunks, T, as, tid);
-                    else attn_item<128>(op, kvh, h0, hb, chunk, n_chunks, T, as, tid);
-                }
-            } else if (op.kind == OP_ARGMAX) {
-                float bv = -INFINITY;
-                int bi = 0x7fffffff;
-                for (int64_t i = (int64_t)blockIdx.x * NCT + tid; i < op.s_n; i += (int64_t)gridDim.x * NCT) {
-                    const float v = op.s_logits[i];
-                    if (v > bv) { bv = v; bi = (int)i; }
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-                    const int oi2 = __shfl_xor_sync(0xffffffffu, bi, o);
-                    if (ov > bv || (ov == bv && oi2 < bi)) { bv = ov; bi = oi2; }
-                }
-                float* sv = (float*)xbase;
-                int* sidx = (int*)(sv + NCW);
-                if (lane == 0) { sv[warp] = bv; sidx[warp] = bi; }
-                named_bar_sync(1, NCT);
-                if (tid == 0) {
-                    for (int w = 1; w < NCW; w++)
-                        if (sv[w] > bv || (sv[w] == bv && sidx[w] < bi)) { bv = sv[w]; bi = sidx[w]; }
-                    op.s_val[blockIdx.x] = bv;
-                    op.s_idx[blockIdx.x] = bi;
-                    __threadfence();
-                    const unsigned int arrived = atomicAdd(op.s_counter, 1u) + 1u;
-                    if (arrived == gridDim.x) {
-                        __threadfence();
-                        for (unsigned int b = 0; b < gridDim.x; b++) {
-                            const float ov = __ldcg(op.s_val + b);
-                            const int oi2 = __ldcg(op.s_idx + b);
-                            if (ov > bv || (ov == bv && oi2 < bi)) { bv = ov; bi = oi2; }
-                        }
-                        if (bi == 0x7fffffff) bi = 0;
-                        *op.s_token = bi;
-                        if (op.s_out) {
-                            const int s = *op.s_step;
-                            if (s < op.s_cap) op.s_out[s] = bi;
-                            *op.s_step = s + 1;
-                        }
-                        if (op.s_pos) *op.s_pos = *op.s_pos + 1;
-                        *op.s_counter = 0u;
-                    }
-                }
-            }
+            if (op.kind == OP_EMBED) embed_stage(op, tid);
+            else if (op.kind == OP_ATTN) attn_stage(op, ss.xbase, ss.aux[oi & 1], tid, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
+            else if (op.kind == OP_ARGMAX) argmax_stage(op, ss.xbase, tid);
             __threadfence();   // every thread's stores of this stage, before the CTA's single arrival
             named_bar_sync(1, NCT);
             if (tid == 0) {
-                atomicAdd(P.sync_counter, 1u);
+                grid_arrive(P.sync_counter, (unsigned int)oi + 1u);
                 stamp(P, oi, 3);
             }
         }
@@ -564,7 +458,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
 }
 
 size_t step_smem_bytes(int act, int max_k) {
-    size_t n = gemv_smem_bytes(act, max_k) + 4 * sizeof(GemvArgs);
+    size_t n = gemv_smem_bytes(act, max_k) + STEP_EXTRA_SMEM;
     // attention aliases the activation buffers; make sure they are large enough
     const size_t x_bytes = (size_t)max_k + (act == ACT_Q8K ? max_k / 256 : max_k / 32) * 4 + max_k / 16 * 2 + max_k / 32 * 2;
     if (x_bytes < ATTN_SMEM_BYTES) n += ATTN_SMEM_BYTES - x_bytes;
@@ -586,10 +480,16 @@ int step_config(int act, int max_k, size_t* smem_out, int* cluster_out, int* gri
     }
     auto kern = act == ACT_Q8K ? step_kernel<ACT_Q8K> : step_kernel<ACT_Q80>;
     B2_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int ctas_per_sm = (int)((227 * 1024) / (smem + 1024));
+    int ctas_per_sm = (int)((228 * 1024) / (smem + 1024));
     if (ctas_per_sm > 2) ctas_per_sm = 2;
     if (ctas_per_sm < 1) ctas_per_sm = 1;
-    const int cluster = 8;
+    // CTAs that share the work of quantising the activation vector (B2_STEP_CLUSTER: 1, 2, 4 or 8)
+    // measured on Llama-3.1-8B: 4 is best (2.85 ms/token; 8: 2.92, 2: 2.90, 1: 3.09)
+    int cluster = 4;
+    if (const char* e = getenv("B2_STEP_CLUSTER")) {
+        const int v = atoi(e);
+        if (v == 1 || v == 2 || v == 4 || v == 8) cluster = v;
+    }
     cudaLaunchConfig_t q{};
     q.gridDim = dim3(g_step_sms * ctas_per_sm / cluster * cluster);
     q.blockDim = dim3(GEMV_THREADS);
@@ -617,9 +517,15 @@ int step_config(int act, int max_k, size_t* smem_out, int* cluster_out, int* gri
 
 }  // namespace
 
-int step_attn_max_chunks(int n_ctx) { return (n_ctx + STEP_ATTN_CHUNK - 1) / STEP_ATTN_CHUNK; }
-size_t step_attn_partials_bytes(int n_head, int head_dim, int n_ctx) {
-    return (size_t)n_head * step_attn_max_chunks(n_ctx) * ((size_t)head_dim + 2) * sizeof(float);
+int step_attn_max_chunks(int n_ctx, int grid) {
+    // attn_chunk_tokens(): below the cap the items fill the grid once (at most grid + 1 chunks when a kv head is a
+    // single item), at the cap a chunk is STEP_ATTN_MAX_CHUNK tokens
+    const int by_cap = (n_ctx + STEP_ATTN_MAX_CHUNK - 1) / STEP_ATTN_MAX_CHUNK;
+    const int by_grid = grid + 2;
+    return by_cap > by_grid ? by_cap : by_grid;
+}
+size_t step_attn_partials_bytes(int n_head, int head_dim, int n_ctx, int grid) {
+    return (size_t)n_head * step_attn_max_chunks(n_ctx, grid) * ((size_t)head_dim + 2) * sizeof(float);
 }
 
 int step_grid_size(int act, int max_k) {
@@ -634,7 +540,7 @@ int launch_step(const StepProgram& p, int act, cudaStream_t st) {
     int cluster, grid;
     int rc = step_config(act, p.max_k, &smem, &cluster, &grid);
     if (rc) return rc;
-    B2_CUDA_CHECK(cudaMemsetAsync(p.sync_counter, 0, sizeof(unsigned int), st));
+    B2_CUDA_CHECK(cudaMemsetAsync(p.sync_counter, 0, STEP_SYNC_BYTES, st));
     auto kern = act == ACT_Q8K ? step_kernel<ACT_Q8K> : step_kernel<ACT_Q80>;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);

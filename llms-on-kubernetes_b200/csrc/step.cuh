@@ -21,6 +21,7 @@ struct StepOp {
     const __half *a_k, *a_v;
     float* a_out;
     int a_n_head, a_n_kv, a_hd, a_n_ctx, a_max_chunks;
+    int a_min_chunk;         // shortest chunk of tokens per work item (multiple of 32, <= STEP_ATTN_MAX_CHUNK)
     const int* a_pos;
     float* a_partials;       // [n_head][max_chunks][hd + 2]
     unsigned int* a_counters;  // [n_kv], zero between steps
@@ -38,18 +39,24 @@ struct StepProgram {
     const StepOp* ops;          // device memory
     int n_ops;
     int max_k;                  // largest mat-vec K (sizes the activation buffers)
-    unsigned int* sync_counter;  // grid barrier, zeroed before every launch
+    // grid barrier: its own 128-byte line (STEP_SYNC_BYTES), zeroed before every launch; word 0 counts arrivals
+    unsigned int* sync_counter;
     // optional profiling trace (B2_STEP_TRACE=1): [n_ops][4] globaltimer stamps written by CTA 0:
     // 0 = compute warps passed the grid barrier, 1 = activation vector built, 2 = last tile handed to the
     // epilogue warp, 3 = this CTA arrived on the stage's grid barrier
     unsigned long long* trace;
 };
 
-constexpr int STEP_ATTN_CHUNK = 256;   // tokens one CTA handles per attention work item
+// tokens one CTA handles per attention work item: chosen per step from the sequence length so that the
+// items fill the grid once (multiples of 32 between these bounds)
+constexpr int STEP_ATTN_MIN_CHUNK = 32, STEP_ATTN_MAX_CHUNK = 256;
+constexpr int STEP_TRACE_SLOTS = 8;   // time stamps per stage in StepProgram::trace (4 .. 7: finer marks inside a stage)
+constexpr int STEP_MAX_GRID = 1024;   // CTAs (argmax scratch)
+constexpr size_t STEP_SYNC_BYTES = 128;
 
-// scratch sizes for a program's attention / argmax stages
-size_t step_attn_partials_bytes(int n_head, int head_dim, int n_ctx);
-int step_attn_max_chunks(int n_ctx);
+// scratch sizes for a program's attention stages (grid = step_grid_size())
+size_t step_attn_partials_bytes(int n_head, int head_dim, int n_ctx, int grid);
+int step_attn_max_chunks(int n_ctx, int grid);
 // number of CTAs the persistent kernel runs with for this activation format and K (co-resident clusters x 8)
 int step_grid_size(int act, int max_k);
 int launch_step(const StepProgram& p, int act, cudaStream_t st);

@@ -1,0 +1,253 @@
+// step_attn.cuh -- single-query attention as a stage of the persistent decode kernel (step.cu).
+//
+// Work item = (kv head, batch of <= 4 query heads of its group, chunk of n <= 256 tokens); the chunk length is
+// chosen per step so that the items cover the grid once.  The 256 compute threads of a CTA run one item:
+//   scores : a half warp (hd 128) or quarter warp (hd 64) per token, two tokens in flight per lane, the
+//            K rows read with 16-byte loads; each warp keeps its tokens' dot products of all heads in registers
+//   softmax: the two warps that own a head in the PV phase compute its max and sum from shared memory
+//   P.V    : thread = (token quarter, one or two columns) adds its tokens for all heads; its first eight V
+//            values (all of them for a 32-token chunk) were fetched before the score phase, later ones are
+//            double-buffered; the four quarters are added through shared memory
+// Same numerics as attn.cu: q and the probabilities are rounded to fp16, fp32 accumulation; a single chunk
+// normalises before rounding (the oracle's order), several chunks keep exp(s - m_chunk) rounded to fp16 and
+// merge by log-sum-exp in the last CTA of the (kv head, batch) to arrive.
+#pragma once
+#include "gemv_device.cuh"
+#include "step.cuh"
+
+namespace b2 {
+namespace stepattn {
+
+using gemvdev::NCT;
+using gemvdev::NCW;
+
+constexpr int A_MAXG = 4;   // query heads per item; larger GQA groups run as several batches
+constexpr int A_TOK = STEP_ATTN_MAX_CHUNK;
+constexpr int V_PRE = 8;    // V rows fetched ahead of the score phase
+
+struct AttnSmem {
+    float* scores;   // [A_MAXG][A_TOK]
+    float* prob;     // [A_MAXG][A_TOK]
+    float* part;     // [3][A_MAXG][128] P.V partial sums of token quarters 1..3
+    float* ml;       // [2][A_MAXG] max, sum per head
+    int* flag;
+};
+constexpr size_t ATTN_SMEM_BYTES = (2 * A_MAXG * A_TOK + 3 * A_MAXG * 128 + 2 * A_MAXG + 4) * sizeof(float);
+
+// tokens per work item for a sequence of T tokens: one wave of items over the grid
+__host__ __device__ inline int attn_chunk_tokens(int T, int items_per_chunk, int grid, int min_chunk) {
+    int c = (int)(((long long)T * items_per_chunk + grid - 1) / grid);
+    c = (c + 31) & ~31;
+    if (c < min_chunk) c = min_chunk;
+    if (c > STEP_ATTN_MAX_CHUNK) c = STEP_ATTN_MAX_CHUNK;
+    return c;
+}
+
+template <int EPT>
+__device__ __forceinline__ uint32_t ld_v(const __half* p) {
+    if (EPT == 2) return *(const uint32_t*)p;
+    return (uint32_t)*(const uint16_t*)p;
+}
+template <int EPT>
+__device__ __forceinline__ void fma_v(float pr, uint32_t raw, float& a0, float& a1) {
+    if (EPT == 2) {
+        const float2 f = __half22float2(*(const __half2*)&raw);
+        a0 += pr * f.x;
+        a1 += pr * f.y;
+    } else {
+        a0 += pr * h2f_bits(raw & 0xffffu);
+    }
+}
+
+// heads [h0, h0 + g) of kv head kvh, tokens [t0, t0 + n)
+template <int HD>
+__device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, int n_chunks, int t0, int n, const AttnSmem& sm, int tid,
+                          unsigned long long* tr) {
+    constexpr int LPT = HD / 8, TPW = 32 / LPT;   // lanes per token, tokens per warp pass
+    constexpr int CPH = NCT / A_MAXG;             // PV phase: threads per head (two warps)
+    constexpr int EPT = HD / CPH;                 // columns per thread
+    static_assert(EPT == 1 || EPT == 2, "head_dim 64 or 128");
+    const int gq = op.a_n_head / op.a_n_kv;
+    const int warp = tid >> 5, lane = tid & 31, sub = lane / LPT, ln = lane % LPT;
+    const __half* kbase = op.a_k + ((size_t)kvh * op.a_n_ctx + t0) * HD;
+    const __half* vbase = op.a_v + ((size_t)kvh * op.a_n_ctx + t0) * HD;
+    // softmax / merge role: head hh; P.V role: tokens tq, tq + 4, ... and columns c0 (+1) of every head
+    const int hh = tid / CPH, tq = tid / CPH, cp = tid % CPH, c0 = cp * EPT;
+
+    if (tr && tid == 0) tr[4] = globaltimer_ns();
+    // the first V_PRE of this thread's V values are fetched before the score phase (all of them for n <= 32)
+    uint32_t vpre[V_PRE];
+#pragma unroll
+    for (int j = 0; j < V_PRE; j++) vpre[j] = tq + 4 * j < n ? ld_v<EPT>(vbase + (size_t)(tq + 4 * j) * HD + c0) : 0u;
+
+    // ---- scores ----
+    {
+        const float scale = 1.0f / sqrtf((float)HD);
+        float qf[A_MAXG][8];
+#pragma unroll
+        for (int h = 0; h < A_MAXG; h++)
+            if (h < g) {
+                const float* qp = op.a_q + ((size_t)(kvh * gq + h0 + h)) * HD + ln * 8;
+                const float4 q0 = *(const float4*)qp, q1 = *(const float4*)(qp + 4);
+                const float t[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+                for (int i = 0; i < 8; i++) qf[h][i] = __half2float(__float2half_rn(t[i]));
+            }
+        if (tr && tid == 0) tr[5] = globaltimer_after(__float_as_uint(qf[0][0]));   // q arrived
+        for (int tb = warp * TPW; tb < n; tb += NCW * TPW * 2) {
+            const int ta = tb + sub, tc = ta + NCW * TPW;
+            uint4 kq[2];
+            kq[0] = ta < n ? *(const uint4*)(kbase + (size_t)ta * HD + ln * 8) : make_uint4(0, 0, 0, 0);
+            kq[1] = tc < n ? *(const uint4*)(kbase + (size_t)tc * HD + ln * 8) : make_uint4(0, 0, 0, 0);
+            if (tr && tid == 0 && tb == 0) tr[6] = globaltimer_after(kq[0].x ^ kq[1].x);   // first K rows arrived
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                const int t = u ? tc : ta;
+                const __half2* k2 = (const __half2*)&kq[u];
+                float d[A_MAXG];
+#pragma unroll
+                for (int h = 0; h < A_MAXG; h++) d[h] = 0.0f;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const float2 kf = __half22float2(k2[i]);
+#pragma unroll
+                    for (int h = 0; h < A_MAXG; h++)
+                        if (h < g) d[h] += kf.x * qf[h][2 * i] + kf.y * qf[h][2 * i + 1];
+                }
+#pragma unroll
+                for (int h = 0; h < A_MAXG; h++)
+                    if (h < g) {
+#pragma unroll
+                        for (int o = LPT / 2; o > 0; o >>= 1) d[h] += __shfl_xor_sync(0xffffffffu, d[h], o);
+                        if (ln == 0 && t < n) sm.scores[h * A_TOK + t] = d[h] * scale;
+                    }
+            }
+        }
+    }
+    if (tr && tid == 0) tr[7] = globaltimer_ns();   // this warp's scores done
+    named_bar_sync(1, NCT);
+    if (tr && tid == 0) tr[1] = globaltimer_ns();
+
+    // ---- softmax: warps 2h and 2h+1 own head h (both compute the same max and sum) ----
+    const bool exact = n_chunks == 1;
+    if (hh < g) {
+        const float* sc = sm.scores + hh * A_TOK;
+        float pmax = -INFINITY, psum = 0.0f;
+        for (int t = lane; t < n; t += 32) pmax = fmaxf(pmax, sc[t]);
+        pmax = warp_max(pmax);
+        for (int t = lane; t < n; t += 32) psum += expf(sc[t] - pmax);
+        psum = warp_sum(psum);
+        const float inv = 1.0f / psum;
+        for (int t = (warp & 1) * 32 + lane; t < n; t += 64) {
+            const float e = expf(sc[t] - pmax);
+            sm.prob[hh * A_TOK + t] = __half2float(__float2half_rn(exact ? e * inv : e));
+        }
+        if (tid % CPH == 0) {
+            sm.ml[hh] = pmax;
+            sm.ml[A_MAXG + hh] = psum;
+        }
+    }
+    named_bar_sync(1, NCT);
+
+    // ---- P.V: thread (tq, cp) adds tokens tq, tq+4, ... into its columns for all heads ----
+    float acc[A_MAXG][2];
+#pragma unroll
+    for (int h = 0; h < A_MAXG; h++) acc[h][0] = acc[h][1] = 0.0f;
+    {
+        uint32_t cur[V_PRE];
+#pragma unroll
+        for (int j = 0; j < V_PRE; j++) cur[j] = vpre[j];
+        const int nj = (n + 3) >> 2;   // tokens per thread, rounded up
+        for (int jb = 0; jb < nj; jb += V_PRE) {
+            uint32_t nxt[V_PRE];
+#pragma unroll
+            for (int j = 0; j < V_PRE; j++) {
+                const int t = tq + 4 * (jb + V_PRE + j);
+                nxt[j] = t < n ? ld_v<EPT>(vbase + (size_t)t * HD + c0) : 0u;
+            }
+#pragma unroll
+            for (int j = 0; j < V_PRE; j++) {
+                const int t = tq + 4 * (jb + j);
+                if (t < n) {
+#pragma unroll
+                    for (int h = 0; h < A_MAXG; h++)
+                        if (h < g) fma_v<EPT>(sm.prob[h * A_TOK + t], cur[j], acc[h][0], acc[h][1]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < V_PRE; j++) cur[j] = nxt[j];
+        }
+    }
+    if (tq > 0) {
+#pragma unroll
+        for (int h = 0; h < A_MAXG; h++)
+            if (h < g) {
+                float* pp = sm.part + ((tq - 1) * A_MAXG + h) * 128 + c0;
+                pp[0] = acc[h][0];
+                if (EPT == 2) pp[1] = acc[h][1];
+            }
+    }
+    named_bar_sync(1, NCT);
+    const size_t stride = (size_t)HD + 2;
+    if (tq == 0) {
+#pragma unroll
+        for (int h = 0; h < A_MAXG; h++)
+            if (h < g) {
+#pragma unroll
+                for (int q = 0; q < 3; q++) {
+                    const float* pp = sm.part + (q * A_MAXG + h) * 128 + c0;
+                    acc[h][0] += pp[0];
+                    if (EPT == 2) acc[h][1] += pp[1];
+                }
+                const int head = kvh * gq + h0 + h;
+                // one chunk: the result; several: this chunk's record {max, sum, out[HD]}
+                float* o = exact ? op.a_out + (size_t)head * HD + c0
+                                 : op.a_partials + ((size_t)head * op.a_max_chunks + chunk) * stride + 2 + c0;
+                o[0] = acc[h][0];
+                if (EPT == 2) o[1] = acc[h][1];
+                if (!exact && cp == 0) {
+                    o[-2] = sm.ml[h];
+                    o[-1] = sm.ml[A_MAXG + h];
+                }
+            }
+    }
+    if (exact) {
+        named_bar_sync(1, NCT);   // the next item reuses the shared buffers
+        if (tr && tid == 0) tr[2] = globaltimer_ns();
+        return;
+    }
+    // the last chunk of the (kv head, batch) to arrive merges the records by log-sum-exp
+    __threadfence();
+    named_bar_sync(1, NCT);
+    if (tr && tid == 0) tr[2] = globaltimer_ns();
+    if (tid == 0) {
+        // one arrival counter per (kv head, head batch): at most n_head of them
+        unsigned int* ctr = &op.a_counters[kvh * ((gq + A_MAXG - 1) / A_MAXG) + h0 / A_MAXG];
+        const unsigned int arrived = atomicAdd(ctr, 1u) + 1u;
+        const int last = arrived == (unsigned int)n_chunks;
+        *sm.flag = last;
+        if (last) *ctr = 0u;
+    }
+    named_bar_sync(1, NCT);
+    if (*sm.flag && hh < g) {
+        __threadfence();
+        const int head = kvh * gq + h0 + hh;
+        const float* base = op.a_partials + ((size_t)head * op.a_max_chunks) * stride;
+        float m = -INFINITY;
+        for (int s = 0; s < n_chunks; s++) m = fmaxf(m, __ldcg(base + s * stride));
+        float den = 0.0f, n0 = 0.0f, n1 = 0.0f;
+        for (int s = 0; s < n_chunks; s++) {
+            const float w = expf(__ldcg(base + s * stride) - m);
+            den += __ldcg(base + s * stride + 1) * w;
+            n0 += __ldcg(base + s * stride + 2 + c0) * w;
+            if (EPT == 2) n1 += __ldcg(base + s * stride + 2 + c0 + 1) * w;
+        }
+        float* o = op.a_out + (size_t)head * HD + c0;
+        o[0] = n0 / den;
+        if (EPT == 2) o[1] = n1 / den;
+    }
+    named_bar_sync(1, NCT);
+}
+
+}  // namespace stepattn
+}  // namespace b2
