@@ -39,6 +39,14 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(model: str):
+    """DRAM bytes one step_kernel launch moved, from the committed ncu capture (None if there is none for this model)."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "profiles", "step_traffic.json")))[model]["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -214,17 +222,29 @@ def main():
     barrier()
     e2e = world * args.steps / e2e_s
 
-    # ---- roofline of the dominant kernel (gemv_kernel): its launches of one step, back to back, CUDA events
-    reps = max(3, min(20, args.steps // 8))
-    mv_ms, mv_bytes, mv_launches = ctx.time_matvec_only(reps)
+    # ---- roofline of the dominant kernel.  With the persistent per-token kernel (step.cu) one launch IS one decode
+    # step, so the kernel's average duration is the CUDA-event time of the timed region / steps and its algorithmic
+    # bytes are the step's (W_stream + ctx * kv_bytes_per_token).  The mat-vec stages alone, launched one
+    # kernel per stage back to back (gemv_kernel, same device code), are timed beside it as an explanation.
     peak, peak_src = peaks()
-    achieved = mv_bytes * reps / (mv_ms / 1e3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "gemv_kernel (dequant-fused mat-vec, all of a step's launches back to back)",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "peak_source": peak_src, "bytes_per_launch": mv_bytes / mv_launches, "us_per_launch": mv_ms * 1e3 / reps / mv_launches,
-                "launches_per_step": mv_launches,
-                "step": {"achieved": step_bytes * args.steps / (ms / 1e3) / 1e9, "frac": step_bytes * args.steps / (ms / 1e3) / 1e9 / peak,
-                         "bytes_per_step": step_bytes}}
+    launches_per_step = ctx.launches_per_step
+    step_gbs = step_bytes * args.steps / (ms / 1e3) / 1e9
+    roofline = {"bound": "hbm",
+                "kernel": "step_kernel (persistent decode step: all mat-vecs, attention, sampling in one launch)"
+                          if launches_per_step == 1 else "one launch per stage (gemv_kernel dominant)",
+                "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak,
+                "traffic": ncu_traffic(args.model) if launches_per_step == 1 else None,
+                "traffic_source": "profiles/step_traffic.json (ncu --set full: dram__bytes_read.sum + dram__bytes_write.sum of one launch)",
+                "peak_source": peak_src, "bytes_per_launch": step_bytes, "us_per_launch": ms * 1e3 / args.steps,
+                "launches_per_step": launches_per_step}
+    try:
+        reps = max(3, min(20, args.steps // 8))
+        mv_ms, mv_bytes, mv_launches = ctx.time_matvec_only(reps)
+        mv_gbs = mv_bytes * reps / (mv_ms / 1e3) / 1e9
+        roofline["matvec_stages_alone"] = {"achieved": mv_gbs, "frac": mv_gbs / peak, "launches": mv_launches,
+                                           "bytes_per_launch": mv_bytes / mv_launches, "us_per_launch": mv_ms * 1e3 / reps / mv_launches}
+    except Exception as e:
+        roofline["matvec_stages_alone"] = {"error": str(e)}
 
     out = {
         "metric": METRIC, "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
