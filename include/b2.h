@@ -129,6 +129,14 @@ int b2_dequantize_host(int type, const void* src_host, float* dst_host, int64_t 
  * is integer, as on ggml's CPU path.  B > 1 runs B independent columns: x is [B][K], y is [B][N]. */
 int b2_gemv(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int B, void* stream);
 
+/* Y[B][N] = X[B][K] . W[N x K]^T for 1 <= B <= 32 columns in ONE pass over the weights (same row a12 with
+ * n_tokens = B: batched decode and chunked prefill).  Same arithmetic as b2_gemv -- Q8_K activations, integer
+ * sub-block dot products, fp32 scales -- with the dot products on the tensor cores (mma.sync int8).
+ * Q4_K and Q6_K weights; other types return B2_EUNSUP (use b2_gemv).  scratch_dev: b2_gemm_scratch_bytes(K, B)
+ * bytes of device memory, 16-byte aligned, for the quantised activations. */
+size_t b2_gemm_scratch_bytes(int64_t K, int B);
+int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int B, void* scratch_dev, void* stream);
+
 /* y = x * rsqrt(mean(x^2) + eps) * w  over rows of length n   (row a11, ggml rms_norm + mul) */
 int b2_rmsnorm(const float* x_dev, const float* w_dev, float* y_dev, int64_t n, int64_t rows, float eps, void* stream);
 
@@ -193,6 +201,20 @@ int b2_ctx_reset(b2_ctx* c);
  * vocab-sized fp32 logits after the LAST token.  If next_token_out != NULL it receives the greedy
  * continuation.  Host buffers; the H2D / D2H copies are part of the call. */
 int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, float* logits_out_host, int32_t* next_token_out);
+
+/* A context with n_slots independent sequences (KV caches of n_ctx tokens each); b2_ctx_create = 1 slot.
+ * The single-sequence calls above use slot 0. */
+int b2_ctx_create_slots(b2_model* m, int n_ctx, int n_slots, b2_ctx** out);
+int b2_ctx_n_slots(const b2_ctx* c);
+
+/* One pass over the weights for a batch of 1 <= n <= 32 tokens (llama.cpp's llama_batch: row a12 with
+ * n_tokens = n): column j is token tokens[j] at position pos[j] of sequence slot slots[j] (slots == NULL: all
+ * slot 0).  Batched decode = one token of each of n sequences; chunked prefill = n consecutive positions of one
+ * sequence (a column attends to the columns before it).  K/V of every column are written to its slot's cache.
+ * last_only = 0: next_tokens_out[n] / logits_out_host[n][vocab] receive every column's greedy token / logits;
+ * last_only = 1: only the last column's (one entry).  Either output may be NULL.  Q4_K / Q6_K models. */
+int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int32_t* pos, int n, int last_only,
+                        int32_t* next_tokens_out, float* logits_out_host);
 
 /* Greedy generation entirely on the device: starting from the state left by b2_ctx_decode (whose greedy
  * token t0 the caller already has), run n_steps decode steps, each consuming the previous argmax without a

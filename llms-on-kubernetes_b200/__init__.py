@@ -77,6 +77,8 @@ SYMBOLS = {
     "b2_dequantize": (_I, [_I, _P, _P, _I64, _P]),
     "b2_dequantize_host": (_I, [_I, _P, _P, _I64]),
     "b2_gemv": (_I, [_I, _P, _P, _P, _I64, _I64, _I, _P]),
+    "b2_gemm_scratch_bytes": (_SZ, [_I64, _I]),
+    "b2_gemm": (_I, [_I, _P, _P, _P, _I64, _I64, _I, _P, _P]),
     "b2_rmsnorm": (_I, [_P, _P, _P, _I64, _I64, C.c_float, _P]),
     "b2_rope": (_I, [_P, _I, _I, _I, _I, _I, C.c_float, _P, _P]),
     "b2_attn_scratch_bytes": (_SZ, [_I, _I, _I]),
@@ -94,6 +96,9 @@ SYMBOLS = {
     "b2_ctx_n_ctx": (_I, [_P]),
     "b2_ctx_reset": (_I, [_P]),
     "b2_ctx_decode": (_I, [_P, _P, _I, _I, _P, C.POINTER(C.c_int32)]),
+    "b2_ctx_create_slots": (_I, [_P, _I, _I, C.POINTER(_P)]),
+    "b2_ctx_n_slots": (_I, [_P]),
+    "b2_ctx_decode_batch": (_I, [_P, _P, _P, _P, _I, _I, _P, _P]),
     "b2_ctx_generate_greedy": (_I, [_P, _I, _P]),
     "b2_ctx_enqueue_steps": (_I, [_P, _I]),
     "b2_ctx_stream": (_P, [_P]),
@@ -199,6 +204,19 @@ def gemv(qtype: int, W: np.ndarray, x: np.ndarray, N: int, K: int) -> np.ndarray
     check(lib.b2_stream_sync(None))
     y = dy.to_numpy(np.float32)
     return y if x.ndim == 1 else y.reshape(B, N)
+
+
+def gemm(qtype: int, W: np.ndarray, x: np.ndarray, N: int, K: int) -> np.ndarray:
+    """Y[B, N] = X[B, K] . W^T in one pass over the weights (tensor-core kernel, 1 <= B <= 32), host buffers."""
+    x = np.ascontiguousarray(x, np.float32)
+    assert x.ndim == 2
+    B = x.shape[0]
+    dW, dx = DevBuf.from_numpy(np.ascontiguousarray(W, np.uint8)), DevBuf.from_numpy(x)
+    dy = DevBuf(4 * N * B)
+    scratch = DevBuf(max(16, lib.b2_gemm_scratch_bytes(K, B)))
+    check(lib.b2_gemm(qtype, dW.ptr, dx.ptr, dy.ptr, N, K, B, scratch.ptr, None))
+    check(lib.b2_stream_sync(None))
+    return dy.to_numpy(np.float32).reshape(B, N)
 
 
 class Gguf:
@@ -318,11 +336,24 @@ class Model:
 
 
 class Context:
-    def __init__(self, model: Model, n_ctx: int = 0):
+    def __init__(self, model: Model, n_ctx: int = 0, n_slots: int = 1):
         self.model = model
         self.h = _P()
-        check(lib.b2_ctx_create(model.h, n_ctx, C.byref(self.h)))
+        check(lib.b2_ctx_create_slots(model.h, n_ctx, n_slots, C.byref(self.h)))
         self.n_ctx = lib.b2_ctx_n_ctx(self.h)
+        self.n_slots = lib.b2_ctx_n_slots(self.h)
+
+    def decode_batch(self, tokens, pos, slots=None, last_only: bool = False, want_logits: bool = True):
+        """One pass over the weights for up to 32 (token, slot, position) columns -> (greedy ids, logits [n, vocab])."""
+        toks = np.ascontiguousarray(tokens, np.int32)
+        p = np.ascontiguousarray(pos, np.int32)
+        s = None if slots is None else np.ascontiguousarray(slots, np.int32)
+        n_out = 1 if last_only else toks.size
+        nxt = np.empty(n_out, np.int32)
+        logits = np.empty((n_out, self.model.info.vocab), np.float32) if want_logits else None
+        check(lib.b2_ctx_decode_batch(self.h, toks.ctypes.data, None if s is None else s.ctypes.data, p.ctypes.data, toks.size,
+                                      1 if last_only else 0, nxt.ctypes.data, logits.ctypes.data if want_logits else None))
+        return nxt.tolist(), logits
 
     def decode(self, tokens, pos0: int, want_logits: bool = True):
         toks = np.ascontiguousarray(tokens, np.int32)

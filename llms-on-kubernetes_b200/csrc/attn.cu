@@ -42,14 +42,25 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
                                                                    const __half* __restrict__ vc, float* __restrict__ out,
                                                                    int n_head, int n_kv, int n_ctx, const int* __restrict__ n_tokens_ptr,
                                                                    int n_tokens_imm, int max_splits, float* __restrict__ partials,
-                                                                   unsigned int* __restrict__ counters) {
+                                                                   unsigned int* __restrict__ counters, const int* __restrict__ col_slot,
+                                                                   long long slot_stride) {
     pdl_launch_dependents();
     pdl_wait();
     constexpr int LPT = HD / 8;              // lanes per token row (8 halves = 16 bytes per lane)
     constexpr int TPW = 32 / LPT;            // tokens per warp load
     const int kvh = blockIdx.x, split = blockIdx.y;
     const int g = n_head / n_kv;
-    const int T = n_tokens_ptr ? *n_tokens_ptr + 1 : n_tokens_imm;   // device position + the token just written
+    // blockIdx.z = column of a batch: its own query / output row, position, sequence slot and scratch
+    const int col = blockIdx.z;
+    q += (size_t)col * n_head * HD;
+    out += (size_t)col * n_head * HD;
+    if (col_slot) {
+        kc += (size_t)col_slot[col] * slot_stride;
+        vc += (size_t)col_slot[col] * slot_stride;
+    }
+    partials += (size_t)col * n_head * max_splits * part_stride(HD);
+    counters += (size_t)col * n_kv;
+    const int T = n_tokens_ptr ? n_tokens_ptr[col] + 1 : n_tokens_imm;   // device position + the token just written
     const int n_splits = min(max_splits, (T + ATTN_SPLIT_TOKENS - 1) / ATTN_SPLIT_TOKENS);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
@@ -294,8 +305,19 @@ size_t attn_scratch_bytes(int n_head, int head_dim, int max_splits) {
     return part + (((size_t)n_head * sizeof(unsigned int) + 255) & ~(size_t)255);
 }
 
+size_t attn_scratch_bytes_batch(int n_head, int head_dim, int max_splits, int n_cols) {
+    size_t part = (size_t)n_cols * n_head * max_splits * ((size_t)head_dim + 2) * sizeof(float);
+    part = (part + 255) & ~(size_t)255;
+    return part + (((size_t)n_cols * n_head * sizeof(unsigned int) + 255) & ~(size_t)255);
+}
+
 int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim,
-                       int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl) {
+                       int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl,
+                       int n_cols, const int* col_slot, int64_t slot_stride) {
+    if (n_cols < 1 || (n_cols > 1 && !pos_ptr)) {
+        set_error("attn_decode: a batch of %d columns needs per-column positions", n_cols);
+        return B2_EINVAL;
+    }
     if (n_head <= 0 || n_kv <= 0 || n_head % n_kv || n_head / n_kv > MAX_GROUP) {
         set_error("attn_decode: n_head=%d n_kv=%d unsupported (group size must divide and be <= %d)", n_head, n_kv, MAX_GROUP);
         return B2_EUNSUP;
@@ -312,7 +334,7 @@ int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float
         set_error("attn_decode: max_splits=%d out of range", max_splits);
         return B2_EINVAL;
     }
-    size_t part = (size_t)n_head * max_splits * ((size_t)head_dim + 2) * sizeof(float);
+    size_t part = (size_t)n_cols * n_head * max_splits * ((size_t)head_dim + 2) * sizeof(float);
     part = (part + 255) & ~(size_t)255;
     float* partials = (float*)scratch;
     unsigned int* counters = (unsigned int*)((uint8_t*)scratch + part);
@@ -323,7 +345,7 @@ int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float
         if (gy > max_splits) gy = max_splits;
     }
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(n_kv, gy);
+    cfg.gridDim = dim3(n_kv, gy, n_cols);
     cfg.blockDim = dim3(ATTN_THREADS);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -333,10 +355,10 @@ int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float
     cfg.numAttrs = pdl ? 1 : 0;
     if (head_dim == 64)
         B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, attn_decode_kernel<64>, q, kc, vc, out, n_head, n_kv, n_ctx, pos_ptr, n_tokens_imm,
-                                         gy, partials, counters));
+                                         gy, partials, counters, col_slot, (long long)slot_stride));
     else
         B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, attn_decode_kernel<128>, q, kc, vc, out, n_head, n_kv, n_ctx, pos_ptr, n_tokens_imm,
-                                         gy, partials, counters));
+                                         gy, partials, counters, col_slot, (long long)slot_stride));
     return 0;
 }
 

@@ -4,6 +4,7 @@
 
 #include <cstring>
 
+#include "gemm.cuh"
 #include "gemv.cuh"
 #include "gguf.h"
 #include "ops.h"
@@ -188,6 +189,36 @@ int b2_gemv(int type, const void* W_dev, const float* x_dev, float* y_dev, int64
         if ((rc = launch_gemv(a, act, (cudaStream_t)stream, false))) return rc;
     }
     return 0;
+}
+
+size_t b2_gemm_scratch_bytes(int64_t K, int B) {
+    if (K <= 0 || B < 1 || B > GEMM_MAX_COLS) return 0;
+    return gemm_act_bytes((int)K, B);
+}
+
+int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int B, void* scratch_dev, void* stream) {
+    if (!W_dev || !x_dev || !y_dev || !scratch_dev || N <= 0 || K <= 0 || B < 1 || B > GEMM_MAX_COLS || N > 0x3fffffff || K > 0x3fffffff) {
+        set_error("b2_gemm: bad arguments (N=%lld K=%lld B=%d)", (long long)N, (long long)K, B);
+        return B2_EINVAL;
+    }
+    int rc = launch_act_quant(x_dev, K, nullptr, 0.0f, (int)K, B, (uint8_t*)scratch_dev, (cudaStream_t)stream);
+    if (rc) return rc;
+    GemmArgs a{};
+    a.K = (int)K;
+    a.act = (const uint8_t*)scratch_dev;
+    a.cols.n = B;
+    a.out_stride = N;
+    GemvSeg& s = a.seg[0];
+    s.wa = (const uint8_t*)W_dev;
+    s.type = type;
+    s.pairing = PAIR_ADJ;
+    s.epi = EPI_STORE;
+    s.n_rows = (int)N;
+    s.n_pairs = (int)((N + 1) / 2);
+    s.out = y_dev;
+    a.n_seg = 1;
+    if ((rc = gemm_finalize(a))) return rc;
+    return launch_gemm(a, (cudaStream_t)stream);
 }
 
 int b2_rmsnorm(const float* x_dev, const float* w_dev, float* y_dev, int64_t n, int64_t rows, float eps, void* stream) {

@@ -20,6 +20,9 @@
 #include <map>
 #include <string>
 
+#include <algorithm>
+
+#include "gemm.cuh"
 #include "gemv.cuh"
 #include "step.cuh"
 #include "ops.h"
@@ -616,12 +619,208 @@ int run_step(b2_ctx* c) {
 
 }  // namespace
 
-extern "C" int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out) {
+// ---- batched path: up to GEMM_MAX_COLS tokens per pass over the weights (batched decode, chunked prefill) ----
+
+// every matrix in a type the tensor-core kernel computes?
+bool batch_supported(const b2_model* m) {
+    if (env_flag("B2_NO_BATCH")) return false;
+    auto ok = [](const b2_model::W& w) { return gemm_supports_type(w.type); };
+    if (!ok(m->output)) return false;
+    for (const auto& L : m->layers)
+        if (!ok(L.wq) || !ok(L.wk) || !ok(L.wv) || !ok(L.wo) || !ok(L.gate) || !ok(L.up) || !ok(L.down)) return false;
+    return true;
+}
+
+int ensure_batch(b2_ctx* c) {
+    if (c->bt.cap) return 0;
+    const b2_model_info& I = c->m->info;
+    const int cap = GEMM_MAX_COLS;
+    int rc;
+    auto& b = c->bt;
+    if ((rc = dmalloc(&b.x, (size_t)cap * I.d_model))) return rc;
+    if ((rc = dmalloc(&b.q, (size_t)cap * I.n_head * I.head_dim))) return rc;
+    if ((rc = dmalloc(&b.attn_out, (size_t)cap * I.n_head * I.head_dim))) return rc;
+    if ((rc = dmalloc(&b.h, (size_t)cap * I.d_ff))) return rc;
+    if ((rc = dmalloc(&b.logits, (size_t)cap * I.vocab))) return rc;
+    const int max_k = std::max(std::max(I.d_model, I.d_ff), I.n_head * I.head_dim);
+    if ((rc = dmalloc(&b.act, gemm_act_bytes(max_k, cap)))) return rc;
+    if ((rc = dmalloc(&b.tok, cap))) return rc;
+    if ((rc = dmalloc(&b.pos, cap))) return rc;
+    if ((rc = dmalloc(&b.slot, cap))) return rc;
+    if ((rc = dmalloc(&b.out, cap))) return rc;
+    const size_t asz = attn_scratch_bytes_batch(I.n_head, I.head_dim, c->max_splits, cap);
+    B2_CUDA_CHECK(cudaMalloc(&b.attn_scratch, asz));
+    B2_CUDA_CHECK(cudaMemsetAsync(b.attn_scratch, 0, asz, c->stream));
+    B2_CUDA_CHECK(cudaMalloc(&b.argmax_scratch, argmax_scratch_bytes() * cap));
+    B2_CUDA_CHECK(cudaMemsetAsync(b.argmax_scratch, 0, argmax_scratch_bytes() * cap, c->stream));
+    b.cap = cap;
+    return 0;
+}
+
+// one pass over the weights for n columns whose (token, slot, position) are in c->bt.tok/slot/pos.
+// logits (and the greedy token per column in c->bt.out) are computed for the last n_logits columns.
+int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
+    b2_model* m = c->m;
+    const b2_model_info& I = m->info;
+    auto& b = c->bt;
+    int rc;
+    const int64_t kv_layer = (int64_t)I.n_kv * c->n_ctx * I.head_dim;
+    const int rope_pairing = I.arch == 1 ? PAIR_NEOX : PAIR_ADJ;
+    const int qdim = I.n_head * I.head_dim;
+    for (int j = 0; j < n; j++)
+        if ((rc = launch_embed(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, b.tok + j,
+                               b.x + (size_t)j * I.d_model, st, false)))
+            return rc;
+    auto common = [&](GemmArgs& a, int K, int cols, int64_t out_stride) {
+        a = GemmArgs{};
+        a.K = K;
+        a.act = b.act;
+        a.cols.n = cols;
+        a.cols.pos = b.pos;
+        a.cols.slot = b.slot;
+        a.out_stride = out_stride;
+        a.slot_stride = c->slot_stride;
+        a.rope_tab = c->rope_tab;
+        a.rope_half = I.rope_dim / 2;
+    };
+    auto run = [&](GemmArgs& a) -> int {
+        if ((rc = gemm_finalize(a))) return rc;
+        return launch_gemm(a, st);
+    };
+    GemmArgs a;
+    for (int il = 0; il < I.n_layer; il++) {
+        const auto& L = m->layers[il];
+        __half* kc = c->k_cache + il * kv_layer;
+        __half* vc = c->v_cache + il * kv_layer;
+        // RMSNorm -> Q, K, V (+bias) -> RoPE -> cache
+        if ((rc = launch_act_quant(b.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, n, b.act, st))) return rc;
+        common(a, I.d_model, n, qdim);
+        seg_matrix(a.seg[0], L.wq, rope_pairing, EPI_ROPE_Q);
+        a.seg[0].out = b.q;
+        a.seg[0].bias = L.bq;
+        a.seg[0].head_dim = I.head_dim;
+        seg_matrix(a.seg[1], L.wk, rope_pairing, EPI_ROPE_K);
+        a.seg[1].cache = kc;
+        a.seg[1].bias = L.bk;
+        a.seg[1].head_dim = I.head_dim;
+        a.seg[1].n_ctx = c->n_ctx;
+        seg_matrix(a.seg[2], L.wv, PAIR_ADJ, EPI_V);
+        a.seg[2].cache = vc;
+        a.seg[2].bias = L.bv;
+        a.seg[2].head_dim = I.head_dim;
+        a.seg[2].n_ctx = c->n_ctx;
+        a.n_seg = 3;
+        if ((rc = run(a))) return rc;
+        // attention of every column over its own sequence
+        if ((rc = launch_attn_decode(b.q, kc, vc, b.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, b.pos, 0, c->max_splits,
+                                     b.attn_scratch, st, false, n, b.slot, c->slot_stride)))
+            return rc;
+        // output projection + residual
+        if ((rc = launch_act_quant(b.attn_out, qdim, nullptr, 0.0f, qdim, n, b.act, st))) return rc;
+        common(a, qdim, n, I.d_model);
+        seg_matrix(a.seg[0], L.wo, PAIR_ADJ, EPI_RESID);
+        a.seg[0].out = b.x;
+        a.n_seg = 1;
+        if ((rc = run(a))) return rc;
+        // RMSNorm -> gate, up -> SwiGLU
+        if ((rc = launch_act_quant(b.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, n, b.act, st))) return rc;
+        if (L.gate.type != L.up.type) {
+            set_error("model: ffn_gate and ffn_up of layer %d have different types: unsupported", il);
+            return B2_EUNSUP;
+        }
+        common(a, I.d_model, n, I.d_ff);
+        seg_matrix(a.seg[0], L.gate, PAIR_SPLIT, EPI_SWIGLU);
+        a.seg[0].wb = L.up.p;
+        a.seg[0].out = b.h;
+        a.n_seg = 1;
+        if ((rc = run(a))) return rc;
+        // down projection + residual
+        if ((rc = launch_act_quant(b.h, I.d_ff, nullptr, 0.0f, I.d_ff, n, b.act, st))) return rc;
+        common(a, I.d_ff, n, I.d_model);
+        seg_matrix(a.seg[0], L.down, PAIR_ADJ, EPI_RESID);
+        a.seg[0].out = b.x;
+        a.n_seg = 1;
+        if ((rc = run(a))) return rc;
+    }
+    // final norm + lm_head + greedy token for the last n_logits columns (none for the inner chunks of a prompt)
+    if (n_logits <= 0) return 0;
+    const int first = n - n_logits;
+    if ((rc = launch_act_quant(b.x + (size_t)first * I.d_model, I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits, b.act, st)))
+        return rc;
+    common(a, I.d_model, n_logits, I.vocab);
+    a.cols.pos = nullptr;
+    a.cols.slot = nullptr;
+    seg_matrix(a.seg[0], m->output, PAIR_ADJ, EPI_STORE);
+    a.seg[0].out = b.logits;
+    a.n_seg = 1;
+    if ((rc = run(a))) return rc;
+    for (int j = 0; j < n_logits; j++)
+        if ((rc = launch_argmax(b.logits + (size_t)j * I.vocab, I.vocab, b.out + j, (uint8_t*)b.argmax_scratch + (size_t)j * argmax_scratch_bytes(),
+                                nullptr, nullptr, nullptr, 0, st, false)))
+            return rc;
+    return 0;
+}
+
+// host arrays -> device columns (through the pinned staging buffer), then enqueue_batch
+int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int32_t* pos, int n, int n_logits) {
+    int rc;
+    if ((rc = ensure_batch(c))) return rc;
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // staging buffer reuse
+    for (int j = 0; j < n; j++) {
+        c->h_pin[j] = tokens[j];
+        c->h_pin[GEMM_MAX_COLS + j] = pos[j];
+        c->h_pin[2 * GEMM_MAX_COLS + j] = slots ? slots[j] : 0;
+    }
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.tok, c->h_pin, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.pos, c->h_pin + GEMM_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.slot, c->h_pin + 2 * GEMM_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    return enqueue_batch(c, n, n_logits, c->stream);
+}
+
+extern "C" int b2_ctx_n_slots(const b2_ctx* c) { return c ? c->n_slots : B2_EINVAL; }
+
+extern "C" int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int32_t* pos, int n, int last_only,
+                                   int32_t* next_tokens_out, float* logits_out_host) {
+    if (!c || !tokens || !pos || n < 1 || n > GEMM_MAX_COLS) {
+        set_error("b2_ctx_decode_batch: bad arguments (n=%d, at most %d columns per call)", n, GEMM_MAX_COLS);
+        return B2_EINVAL;
+    }
+    const b2_model_info& I = c->m->info;
+    if (!batch_supported(c->m)) {
+        set_error("b2_ctx_decode_batch: this model has matrices outside Q4_K / Q6_K; the batched kernel does not compute them yet");
+        return B2_EUNSUP;
+    }
+    for (int j = 0; j < n; j++) {
+        const int s = slots ? slots[j] : 0;
+        if (tokens[j] < 0 || tokens[j] >= I.vocab || pos[j] < 0 || pos[j] >= c->n_ctx || s < 0 || s >= c->n_slots) {
+            set_error("b2_ctx_decode_batch: column %d (token %d, slot %d, position %d) out of range", j, tokens[j], s, pos[j]);
+            return B2_ERANGE;
+        }
+    }
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    const int n_logits = last_only ? 1 : n;
+    int rc;
+    if ((rc = run_batch(c, tokens, slots, pos, n, n_logits))) return rc;
+    if (logits_out_host)
+        B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->bt.logits, (size_t)n_logits * I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (next_tokens_out) B2_CUDA_CHECK(cudaMemcpyAsync(c->h_pin, c->bt.out, (size_t)n_logits * 4, cudaMemcpyDeviceToHost, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    if (next_tokens_out) memcpy(next_tokens_out, c->h_pin, (size_t)n_logits * 4);
+    return 0;
+}
+
+extern "C" int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out) { return b2_ctx_create_slots(m, n_ctx, 1, out); }
+
+extern "C" int b2_ctx_create_slots(b2_model* m, int n_ctx, int n_slots, b2_ctx** out) {
     if (!m || !out) {
         set_error("b2_ctx_create: NULL argument");
         return B2_EINVAL;
     }
     *out = nullptr;
+    if (n_slots < 1 || n_slots > 256) {
+        set_error("b2_ctx_create_slots: n_slots=%d outside [1, 256]", n_slots);
+        return B2_EINVAL;
+    }
     const b2_model_info& I = m->info;
     if (n_ctx <= 0) {
         const char* e = getenv("B2_CTX_SIZE");
@@ -637,7 +836,10 @@ extern "C" int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out) {
     c->use_pdl = !env_flag("B2_NO_PDL");
     B2_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     int rc;
-    const size_t kv_elems = (size_t)I.n_layer * I.n_kv * n_ctx * I.head_dim;
+    // [slot][layer][kv head][position][head_dim]: slot 0 is the single-sequence paths' cache
+    c->n_slots = n_slots;
+    c->slot_stride = (int64_t)I.n_layer * I.n_kv * n_ctx * I.head_dim;
+    const size_t kv_elems = (size_t)c->slot_stride * n_slots;
     if ((rc = dmalloc(&c->k_cache, kv_elems))) return rc;
     if ((rc = dmalloc(&c->v_cache, kv_elems))) return rc;
     B2_CUDA_CHECK(cudaMemsetAsync(c->k_cache, 0, kv_elems * sizeof(__half), c->stream));
@@ -719,6 +921,10 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
                     c->d_ops, c->step_attn_partials, c->step_counters, c->step_sync, c->step_argmax_val, c->step_argmax_idx, c->step_trace};
     for (void* p : ptrs)
         if (p) cudaFree(p);
+    void* bptrs[] = {c->bt.x, c->bt.q, c->bt.attn_out, c->bt.h, c->bt.logits, c->bt.act, c->bt.tok, c->bt.pos, c->bt.slot, c->bt.out,
+                     c->bt.attn_scratch, c->bt.argmax_scratch};
+    for (void* p : bptrs)
+        if (p) cudaFree(p);
     if (c->h_pin) cudaFreeHost(c->h_pin);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -759,6 +965,34 @@ extern "C" int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, 
         }
     B2_CUDA_CHECK(cudaSetDevice(c->m->device));
     int rc;
+    // prompts: chunks of up to 32 tokens per pass over the weights on the tensor-core path (sequence slot 0), the
+    // last chunk producing the logits / greedy token of the final position; then the device-resident state
+    // (token, position, logits) is left exactly as the per-token path leaves it
+    const int n_in = n;
+    if (n >= 4 && batch_supported(c->m)) {
+        int32_t pos[GEMM_MAX_COLS];
+        for (int done = 0; done < n;) {
+            const int chunk = std::min(n - done, GEMM_MAX_COLS);
+            for (int j = 0; j < chunk; j++) pos[j] = pos0 + done + j;
+            const bool last = done + chunk == n;
+            if ((rc = run_batch(c, tokens + done, nullptr, pos, chunk, last ? 1 : 0))) return rc;
+            if (last) {
+                const size_t j = (size_t)chunk - 1, qdim = (size_t)I.n_head * I.head_dim;
+                B2_CUDA_CHECK(cudaMemcpyAsync(c->logits, c->bt.logits, (size_t)I.vocab * 4, cudaMemcpyDeviceToDevice, c->stream));
+                B2_CUDA_CHECK(cudaMemcpyAsync(c->d_tok, c->bt.out, 4, cudaMemcpyDeviceToDevice, c->stream));
+                // the last position's activations, where the per-token path keeps them (b2_ctx_get_activation)
+                B2_CUDA_CHECK(cudaMemcpyAsync(c->x, c->bt.x + j * I.d_model, (size_t)I.d_model * 4, cudaMemcpyDeviceToDevice, c->stream));
+                B2_CUDA_CHECK(cudaMemcpyAsync(c->q, c->bt.q + j * qdim, qdim * 4, cudaMemcpyDeviceToDevice, c->stream));
+                B2_CUDA_CHECK(cudaMemcpyAsync(c->attn_out, c->bt.attn_out + j * qdim, qdim * 4, cudaMemcpyDeviceToDevice, c->stream));
+                B2_CUDA_CHECK(cudaMemcpyAsync(c->h, c->bt.h + j * I.d_ff, (size_t)I.d_ff * 4, cudaMemcpyDeviceToDevice, c->stream));
+            }
+            done += chunk;
+        }
+        B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // staging buffer reuse
+        c->h_pin[0] = pos0 + n;
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->d_pos, c->h_pin, 4, cudaMemcpyHostToDevice, c->stream));
+        n = 0;   // nothing left for the per-token loop
+    }
     for (int done = 0; done < n;) {
         const int chunk = std::min(n - done, std::min(c->prompt_cap, c->h_pin_cap - 2));
         // pinned staging: [0] = position, [1..] = token ids
@@ -773,7 +1007,7 @@ extern "C" int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, 
         }
         done += chunk;
     }
-    c->pos = pos0 + n;
+    c->pos = pos0 + n_in;
     if (logits_out_host)
         B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->logits, (size_t)I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
     if (next_token_out) {

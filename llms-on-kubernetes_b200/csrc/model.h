@@ -59,4 +59,15 @@ struct b2_ctx {
     float* step_argmax_val = nullptr;
     int* step_argmax_idx = nullptr;
     int pos = 0;
+    // batched path (gemm.cu): up to GEMM_MAX_COLS tokens per pass over the weights, each with its own
+    // (sequence slot, position).  KV caches of slot s start s * slot_stride halfs after slot 0's.
+    int n_slots = 1;
+    int64_t slot_stride = 0;
+    struct Batch {
+        float *x = nullptr, *q = nullptr, *attn_out = nullptr, *h = nullptr, *logits = nullptr;
+        uint8_t* act = nullptr;                                   // quantised activations of the current mat-mul input
+        int32_t *tok = nullptr, *pos = nullptr, *slot = nullptr, *out = nullptr;   // [cap] device
+        void *attn_scratch = nullptr, *argmax_scratch = nullptr;
+        int cap = 0;
+    } bt;
 };

@@ -18,7 +18,11 @@ size_t attn_scratch_bytes(int n_head, int head_dim, int max_splits);
 // pos_ptr != NULL: attend positions [0, *pos_ptr] (device-resident position, graph-replayable);
 // otherwise attend [0, n_tokens_imm).
 int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim,
-                       int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl);
+                       int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl,
+                       int n_cols = 1, const int* col_slot = nullptr, int64_t slot_stride = 0);
+// n_cols > 1: a batch of queries q[n_cols][n_head][hd] -> out, column j at position pos_ptr[j] of sequence slot
+// col_slot[j] (caches slot_stride halfs apart); scratch of attn_scratch_bytes_batch()
+size_t attn_scratch_bytes_batch(int n_head, int head_dim, int max_splits, int n_cols);
 
 // misc.cu
 // x[d] = dequantised row *token_ptr of the embedding table (row a10)

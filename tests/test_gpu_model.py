@@ -118,10 +118,17 @@ def test_hidden_state_and_position_restart(b2, tiny_models, name):
     n1, l1 = ctx.decode(toks, 0)
     n2, l2 = ctx.decode(toks, 0)
     assert n1 == n2 and np.array_equal(l1, l2)
-    # token-by-token == all at once
+    # token-by-token (the per-token kernel) against all at once (prompts of >= 4 tokens take the batched tensor-core
+    # kernel when the model's types allow it): same integer arithmetic, fp32 summation order differs
     for p, t in enumerate(toks):
         n3, l3 = ctx.decode([t], p)
-    assert n3 == n1 and np.array_equal(l3, l1)
+    assert np.abs(l3 - l1).max() <= LOGIT_TOL * np.abs(l1).max() and kl(l1, l3) < KL_TOL
+    top2 = np.partition(l1, -2)[-2:]
+    assert n3 == n1 or float(top2.max() - top2.min()) <= 2 * LOGIT_TOL * np.abs(l1).max()
+    # ... and the per-token path is itself idempotent
+    for p, t in enumerate(toks):
+        n4, l4 = ctx.decode([t], p)
+    assert n4 == n3 and np.array_equal(l4, l3)
     ctx.free(); m.free(); ref.close()
 
 
