@@ -115,6 +115,80 @@ def cpu_decode_sample(path: str, n_tokens: int, warm: int):
     return n_tokens / dt, dt, rm.lib().ref_num_threads()
 
 
+def bench_batched(b2, synth, spec, model, args, world, barrier, max_over_ranks, gpu_index):
+    """The other decode / prefill configurations of SURVEY 8d (not the headline): `--batch B` = one token of each of B
+    sequences per step through b2_ctx_decode_batch, `--prefill T` = a T-token prompt through b2_ctx_decode.  Both go
+    through the C ABI with host buffers (token ids in, sampled ids out, every step), so value == e2e."""
+    info = model.info
+    rng = np.random.default_rng(args.seed)
+    peak, peak_src = peaks()
+    if args.prefill > 0:
+        T = args.prefill
+        ctx = b2.Context(model, T + 8)
+        prompt = rng.integers(3, info.vocab, size=T).tolist()
+        for _ in range(max(1, min(args.warmup, 3))):
+            ctx.decode(prompt, 0, want_logits=False)
+        reps = max(1, min(args.steps, 8))
+        barrier(); ctx.sync()
+        sampler = ClockSampler(gpu_index); sampler.start()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            ctx.decode(prompt, 0, want_logits=False)
+        ctx.sync()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        clocks = sampler.stop()
+        ctx.free()
+        value = world * reps * T / dt
+        flops = 2.0 * synth.matmul_params(spec) * T if hasattr(synth, "matmul_params") else None
+        return {"metric": "prefill tok/s", "value": value, "unit": "tok/s", "n_gpus": world, "steps": reps, "warmup": min(args.warmup, 3),
+                "ms_per_step": dt / reps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "int8 x int4..6 mma.sync (u8.s8 -> s32), fp32 scales", "data": "synthetic",
+                "config": {"workload": f"{spec.name} {spec.ftype} synthetic GGUF, prefill of {T} tokens in 32-token chunks",
+                           "parallelism": f"replicas x{world}" if world > 1 else "single GPU"},
+                "e2e": {"value": value, "unit": "tok/s", "h2d_bytes_per_step": 4 * T, "d2h_bytes_per_step": 4},
+                "gpu_launches": None, "clocks": clocks,
+                "roofline": {"bound": "hbm", "note": "32-token chunks re-stream the weights: T/32 passes",
+                             "achieved": info.stream_bytes * ((T + 31) // 32) * reps / dt / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": info.stream_bytes * ((T + 31) // 32) * reps / dt / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                             "matmul_flops_per_prompt": flops}}
+    B = args.batch
+    n_ctx = args.prompt + args.steps + args.warmup + 8
+    ctx = b2.Context(model, n_ctx, n_slots=B)
+    toks = []
+    for s in range(B):
+        prompt = rng.integers(3, info.vocab, size=args.prompt).tolist()
+        for p0 in range(0, args.prompt, 32):
+            chunk = prompt[p0:p0 + 32]
+            ids, _ = ctx.decode_batch(chunk, list(range(p0, p0 + len(chunk))), slots=[s] * len(chunk), last_only=True, want_logits=False)
+        toks.append(ids[0])
+    pos = args.prompt
+    slots = list(range(B))
+    for _ in range(args.warmup):
+        toks, _ = ctx.decode_batch(toks, [pos] * B, slots=slots, want_logits=False); pos += 1
+    barrier(); ctx.sync()
+    sampler = ClockSampler(gpu_index); sampler.start()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        toks, _ = ctx.decode_batch(toks, [pos] * B, slots=slots, want_logits=False); pos += 1
+    ctx.sync()
+    dt = max_over_ranks(time.perf_counter() - t0)
+    clocks = sampler.stop()
+    ctx.free()
+    value = world * B * args.steps / dt
+    step_bytes = info.stream_bytes + B * (args.prompt + args.warmup + args.steps // 2) * synth.kv_bytes_per_token(spec)
+    gbs = step_bytes * args.steps / dt / 1e9
+    return {"metric": f"decode tok/s at batch {B}", "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int8 x int4..6 mma.sync (u8.s8 -> s32), fp32 scales", "data": "synthetic",
+            "config": {"workload": f"{spec.name} {spec.ftype} synthetic GGUF, batch-{B} greedy decode at ctx {args.prompt}",
+                       "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
+                       "l2": "inputs exceed L2 (4.6 GB of weights streamed per step vs 126 MB)"},
+            "e2e": {"value": value, "unit": "tok/s", "h2d_bytes_per_step": 12 * B, "d2h_bytes_per_step": 4 * B},
+            "gpu_launches": None, "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+                         "peak_source": peak_src, "bytes_per_step": step_bytes}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -125,6 +199,8 @@ def main():
     ap.add_argument("--prompt", type=int, default=128, help="tokens in the KV cache when the timed decode starts")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--batch", type=int, default=1, help="> 1: batched decode of this many sequences (SURVEY 8d config 3: 8, 32)")
+    ap.add_argument("--prefill", type=int, default=0, help="> 0: time the prefill of a prompt of this many tokens instead")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -189,6 +265,14 @@ def main():
     b2 = importlib.import_module(PKG)  # raises if libb2.so is missing: no fallback
     path = ensure_model(synth, args.model, args.seed, rank, barrier)
     model = b2.Model(path, device=local_rank)
+    if args.batch > 1 or args.prefill > 0:
+        out = bench_batched(b2, synth, spec, model, args, world, barrier, max_over_ranks, local_rank)
+        model.free()
+        if rank == 0:
+            print(json.dumps(out))
+        if dist is not None:
+            dist.destroy_process_group()
+        return
     n_ctx = max(512, args.prompt + 2 * (args.steps + args.warmup) + 64)
     ctx = b2.Context(model, n_ctx)
     info = model.info

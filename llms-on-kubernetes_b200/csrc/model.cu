@@ -774,7 +774,32 @@ int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int3
     B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.tok, c->h_pin, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
     B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.pos, c->h_pin + GEMM_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
     B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.slot, c->h_pin + 2 * GEMM_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
-    return enqueue_batch(c, n, n_logits, c->stream);
+    if (!c->use_graph) return enqueue_batch(c, n, n_logits, c->stream);
+    auto& graphs = c->bt.graphs;
+    if (graphs.empty()) graphs.resize((size_t)(GEMM_MAX_COLS + 1) * (GEMM_MAX_COLS + 1));
+    auto& g = graphs[(size_t)n * (GEMM_MAX_COLS + 1) + n_logits];
+    if (g.exec) {
+        B2_CUDA_CHECK(cudaGraphLaunch(g.exec, c->stream));
+        return 0;
+    }
+    if (!g.seen) {   // first use of this shape: eager (lazy module loading, function attributes)
+        g.seen = true;
+        return enqueue_batch(c, n, n_logits, c->stream);
+    }
+    cudaGraph_t graph = nullptr;
+    B2_CUDA_CHECK(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    rc = enqueue_batch(c, n, n_logits, c->stream);
+    const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+    if (rc) {
+        if (graph) cudaGraphDestroy(graph);
+        return rc;
+    }
+    B2_CUDA_CHECK(e);
+    const cudaError_t ei = cudaGraphInstantiate(&g.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    B2_CUDA_CHECK(ei);
+    B2_CUDA_CHECK(cudaGraphLaunch(g.exec, c->stream));
+    return 0;
 }
 
 extern "C" int b2_ctx_n_slots(const b2_ctx* c) { return c ? c->n_slots : B2_EINVAL; }
@@ -921,6 +946,8 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
                     c->d_ops, c->step_attn_partials, c->step_counters, c->step_sync, c->step_argmax_val, c->step_argmax_idx, c->step_trace};
     for (void* p : ptrs)
         if (p) cudaFree(p);
+    for (auto& g : c->bt.graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
     void* bptrs[] = {c->bt.x, c->bt.q, c->bt.attn_out, c->bt.h, c->bt.logits, c->bt.act, c->bt.tok, c->bt.pos, c->bt.slot, c->bt.out,
                      c->bt.attn_scratch, c->bt.argmax_scratch};
     for (void* p : bptrs)

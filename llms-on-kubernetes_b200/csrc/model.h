@@ -69,5 +69,9 @@ struct b2_ctx {
         int32_t *tok = nullptr, *pos = nullptr, *slot = nullptr, *out = nullptr;   // [cap] device
         void *attn_scratch = nullptr, *argmax_scratch = nullptr;
         int cap = 0;
+        // one CUDA graph per (columns, logit columns): ~310 launches per pass replayed as one; an entry is
+        // captured the second time its shape is used (the first use runs eagerly)
+        struct G { cudaGraphExec_t exec = nullptr; bool seen = false; };
+        std::vector<G> graphs;   // index = n * (cap + 1) + n_logits
     } bt;
 };
