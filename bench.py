@@ -199,6 +199,7 @@ def main():
     ap.add_argument("--prompt", type=int, default=128, help="tokens in the KV cache when the timed decode starts")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dist-selftest", action="store_true", help="CPU-only check of the multi-rank aggregation (gloo)")
     ap.add_argument("--batch", type=int, default=1, help="> 1: batched decode of this many sequences (SURVEY 8d config 3: 8, 32)")
     ap.add_argument("--prefill", type=int, default=0, help="> 0: time the prefill of a prompt of this many tokens instead")
     args = ap.parse_args()
@@ -235,12 +236,19 @@ def main():
         return
 
     # ------------------------------------------------------------------ B200 arm
+    # Replicas only: the path shards by request, every rank serves its own copy of the model on its own GPU and no
+    # collective touches the data path.  torch.distributed carries the barrier and the max-over-ranks of the timings.
     dist = None
+    red_device = "cuda"
     if world > 1:
         import torch
         import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        if args.dist_selftest:
+            red_device = "cpu"
+            dist.init_process_group("gloo")
+        else:
+            torch.cuda.set_device(local_rank)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
         if dist is not None:
@@ -250,17 +258,20 @@ def main():
         if dist is None:
             return v
         import torch
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        t = torch.tensor([v], dtype=torch.float64, device=red_device)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    def sum_over_ranks(v: float) -> float:
-        if dist is None:
-            return v
-        import torch
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    if args.dist_selftest:
+        # CPU check of the multi-rank plumbing (tests/test_multi_rank.py, gloo): every rank "measures" a different time;
+        # the job's throughput is all ranks' steps over the slowest rank's time
+        barrier()
+        ms = max_over_ranks(10.0 * (rank + 1))
+        if rank == 0:
+            print(json.dumps({"selftest": True, "n_gpus": world, "ms": ms, "value": world * args.steps / (ms / 1e3), "scaling": "weak"}))
+        if dist is not None:
+            dist.destroy_process_group()
+        return
 
     b2 = importlib.import_module(PKG)  # raises if libb2.so is missing: no fallback
     path = ensure_model(synth, args.model, args.seed, rank, barrier)
