@@ -247,6 +247,7 @@ def main():
             red_device = "cpu"
             dist.init_process_group("gloo")
         else:
+            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL's version banner goes to stdout; rank 0 prints exactly one line
             torch.cuda.set_device(local_rank)
             dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
