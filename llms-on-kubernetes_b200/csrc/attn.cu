@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
                                                                    int n_head, int n_kv, int n_ctx, const int* __restrict__ n_tokens_ptr,
                                                                    int n_tokens_imm, int max_splits, float* __restrict__ partials,
                                                                    unsigned int* __restrict__ counters, const int* __restrict__ col_slot,
-                                                                   long long slot_stride) {
+                                                                   long long slot_stride, int split_tokens) {
     pdl_launch_dependents();
     pdl_wait();
     constexpr int LPT = HD / 8;              // lanes per token row (8 halves = 16 bytes per lane)
@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
     partials += (size_t)col * n_head * max_splits * part_stride(HD);
     counters += (size_t)col * n_kv;
     const int T = n_tokens_ptr ? n_tokens_ptr[col] + 1 : n_tokens_imm;   // device position + the token just written
-    const int n_splits = min(max_splits, (T + ATTN_SPLIT_TOKENS - 1) / ATTN_SPLIT_TOKENS);
+    const int n_splits = min(max_splits, (T + split_tokens - 1) / split_tokens);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     __shared__ float s_scores[MAX_GROUP][ATTN_SPLIT_TOKENS];
@@ -71,8 +71,8 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
     __shared__ int s_last;
 
     if (split < n_splits) {
-        const int t0 = split * ATTN_SPLIT_TOKENS;
-        const int t1 = min(T, (split == n_splits - 1) ? T : t0 + ATTN_SPLIT_TOKENS);
+        const int t0 = split * split_tokens;
+        const int t1 = min(T, (split == n_splits - 1) ? T : t0 + split_tokens);
         // tokens beyond max_splits*ATTN_SPLIT_TOKENS fall into the last split: cover them in passes
         const __half* kbase = kc + (size_t)kvh * n_ctx * HD;
         const __half* vbase = vc + (size_t)kvh * n_ctx * HD;
@@ -98,8 +98,8 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
             for (int i = 0; i < 8; i++) acc[h][i] = 0.0f;
         }
 
-        for (int p0 = t0; p0 < t1; p0 += ATTN_SPLIT_TOKENS) {
-            const int p1 = min(t1, p0 + ATTN_SPLIT_TOKENS);
+        for (int p0 = t0; p0 < t1; p0 += split_tokens) {
+            const int p1 = min(t1, p0 + split_tokens);
             const int n = p1 - p0;
             // ---- scores s[h][t] = scale * <k_t, q_h> ----
             for (int tb = warp * TPW; tb < n; tb += ATTN_WARPS * TPW) {
@@ -313,7 +313,11 @@ size_t attn_scratch_bytes_batch(int n_head, int head_dim, int max_splits, int n_
 
 int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim,
                        int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl,
-                       int n_cols, const int* col_slot, int64_t slot_stride) {
+                       int n_cols, const int* col_slot, int64_t slot_stride, int split_tokens) {
+    if (split_tokens < 16 || split_tokens > ATTN_SPLIT_TOKENS) {
+        set_error("attn_decode: split_tokens=%d outside [16, %d]", split_tokens, ATTN_SPLIT_TOKENS);
+        return B2_EINVAL;
+    }
     if (n_cols < 1 || (n_cols > 1 && !pos_ptr)) {
         set_error("attn_decode: a batch of %d columns needs per-column positions", n_cols);
         return B2_EINVAL;
@@ -341,7 +345,7 @@ int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float
     // with an immediate length the grid can be sized to the splits actually needed
     int gy = max_splits;
     if (!pos_ptr) {
-        gy = (n_tokens_imm + ATTN_SPLIT_TOKENS - 1) / ATTN_SPLIT_TOKENS;
+        gy = (n_tokens_imm + split_tokens - 1) / split_tokens;
         if (gy > max_splits) gy = max_splits;
     }
     cudaLaunchConfig_t cfg{};
@@ -355,10 +359,10 @@ int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float
     cfg.numAttrs = pdl ? 1 : 0;
     if (head_dim == 64)
         B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, attn_decode_kernel<64>, q, kc, vc, out, n_head, n_kv, n_ctx, pos_ptr, n_tokens_imm,
-                                         gy, partials, counters, col_slot, (long long)slot_stride));
+                                         gy, partials, counters, col_slot, (long long)slot_stride, split_tokens));
     else
         B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, attn_decode_kernel<128>, q, kc, vc, out, n_head, n_kv, n_ctx, pos_ptr, n_tokens_imm,
-                                         gy, partials, counters, col_slot, (long long)slot_stride));
+                                         gy, partials, counters, col_slot, (long long)slot_stride, split_tokens));
     return 0;
 }
 

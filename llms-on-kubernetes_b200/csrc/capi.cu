@@ -193,7 +193,8 @@ int b2_gemv(int type, const void* W_dev, const float* x_dev, float* y_dev, int64
 
 size_t b2_gemm_scratch_bytes(int64_t K, int B) {
     if (K <= 0 || B < 1 || B > GEMM_MAX_COLS) return 0;
-    return gemm_act_bytes((int)K, B);
+    const size_t a = gemm_act_bytes((int)K, B, ACT_Q8K), b = gemm_act_bytes((int)K, B, ACT_Q80);
+    return a > b ? a : b;
 }
 
 int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int B, void* scratch_dev, void* stream) {
@@ -201,7 +202,12 @@ int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64
         set_error("b2_gemm: bad arguments (N=%lld K=%lld B=%d)", (long long)N, (long long)K, B);
         return B2_EINVAL;
     }
-    int rc = launch_act_quant(x_dev, K, nullptr, 0.0f, (int)K, B, (uint8_t*)scratch_dev, (cudaStream_t)stream);
+    const int fmt = gemm_act_for_type(type);
+    if (fmt < 0) {
+        set_error("b2_gemm: ggml type %d is not computed by the batched kernel (Q4_K, Q6_K, Q8_0); use b2_gemv", type);
+        return B2_EUNSUP;
+    }
+    int rc = launch_act_quant(x_dev, K, nullptr, 0.0f, (int)K, B, (uint8_t*)scratch_dev, (cudaStream_t)stream, fmt);
     if (rc) return rc;
     GemmArgs a{};
     a.K = (int)K;

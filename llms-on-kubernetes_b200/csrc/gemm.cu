@@ -36,10 +36,14 @@ constexpr int W_STAGE = GEMM_TILE_ROWS * ROW_SLOT;           // 27136
 constexpr int DEC_ROW = GEMM_CHUNK_BLOCKS * 32 + 16;         // decoded Q4_K headers of one row (padded against bank conflicts)
 constexpr int DEC_BYTES = GEMM_TILE_ROWS * DEC_ROW;
 
-template <int NG>
+// FMT = activation format: ACT_Q8K (K-quant weights: chunks of 8 super-blocks) or ACT_Q80 (Q8_0 weights: 32 blocks of 32)
+template <int NG, int FMT>
 struct Geo {
     static constexpr int NB = 8 * NG;
-    static constexpr int ACT_BYTES = (int)((size_t)NB * GEMM_Q_PITCH + (size_t)GEMM_CHUNK_BLOCKS * NB * 20);
+    static constexpr int CB = FMT == ACT_Q8K ? GEMM_CHUNK_BLOCKS : GEMM80_CHUNK_BLOCKS;   // weight blocks per chunk and row
+    static constexpr int BLK = FMT == ACT_Q8K ? 256 : 32;                                   // elements per weight block
+    static constexpr int ACT_BYTES = FMT == ACT_Q8K ? (int)((size_t)NB * GEMM_Q_PITCH + (size_t)GEMM_CHUNK_BLOCKS * NB * 20)
+                                                    : (int)((size_t)NB * GEMM80_Q_PITCH + (size_t)GEMM80_CHUNK_BLOCKS * NB * 4);
     static constexpr int STAGE_BYTES = (W_STAGE + ACT_BYTES + 127) & ~127;
     static constexpr int STAGES = NG == 2 ? 3 : 2;   // NG 1: two CTAs per SM; NG 2, 4: one CTA per SM
     static constexpr int RED_FLOATS = NCW * GEMM_TILE_ROWS * NB;   // one buffer of partial sums
@@ -135,6 +139,72 @@ __global__ void __launch_bounds__(256) act_quant_kernel(const float* __restrict_
             const int sub = lane >> 2;
             bl[(kb * nb_cols + col) * 8 + sub] = (uint8_t)(s32 & 127);
             bh[(kb * nb_cols + col) * 8 + sub] = (uint8_t)(int8_t)(s32 >> 7);
+        }
+    }
+}
+
+// Q8_0 activations (quantize_row_q8_0: d = amax / 127 per 32 elements, q = roundf(x / d), d kept fp16-rounded)
+__global__ void __launch_bounds__(256) act_quant80_kernel(const float* __restrict__ x, int64_t x_stride, const float* __restrict__ norm_w,
+                                                          float eps, int K, int cols, int nb_cols, uint8_t* __restrict__ act) {
+    __shared__ double ss_warp[8];
+    const int col = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const size_t chunk_bytes = gemm80_act_chunk_bytes(nb_cols);
+    const bool live = col < cols;
+    const float* xc = x + (size_t)col * x_stride;
+    float scale = 1.0f;
+    if (live && norm_w) {
+        double ss = 0.0;
+        for (int i0 = tid * 8; i0 < K; i0 += 256 * 8) {
+            const float4 p0 = *(const float4*)(xc + i0), p1 = *(const float4*)(xc + i0 + 4);
+            const float t[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+            for (int i = 0; i < 8; i++) ss += (double)(t[i] * t[i]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        if (lane == 0) ss_warp[warp] = ss;
+        __syncthreads();
+        double tot = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; w++) tot += ss_warp[w];
+        scale = 1.0f / sqrtf((float)(tot / (double)K) + eps);
+    }
+    // 8 consecutive elements per lane, 4 lanes per 32-element block (K is a multiple of 32)
+    for (int w0 = warp * 256; w0 < K; w0 += 256 * 8) {   // warp-uniform bound: the shuffles below need the whole warp
+        const int i0 = w0 + lane * 8;
+        const bool in_range = i0 < K;
+        float v[8];
+        if (live && in_range) {
+            const float4 p0 = *(const float4*)(xc + i0), p1 = *(const float4*)(xc + i0 + 4);
+            v[0] = p0.x; v[1] = p0.y; v[2] = p0.z; v[3] = p0.w; v[4] = p1.x; v[5] = p1.y; v[6] = p1.z; v[7] = p1.w;
+            if (norm_w) {
+                const float4 w0 = *(const float4*)(norm_w + i0), w1 = *(const float4*)(norm_w + i0 + 4);
+                const float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[i] = (v[i] * scale) * w[i];
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = 0.0f;
+        }
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+        float d = amax / 127.0f;
+        const float id = d != 0.0f ? 1.0f / d : 0.0f;
+        int q[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) q[i] = (int)roundf(v[i] * id);
+        d = __half2float(__float2half_rn(d));
+        const uint32_t pk0 = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
+        const uint32_t pk1 = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
+        if (in_range) {
+            const int chunk = i0 / GEMM80_CHUNK_K, kin = i0 % GEMM80_CHUNK_K;
+            uint8_t* base = act + (size_t)chunk * chunk_bytes;
+            *(uint2*)(base + (size_t)col * GEMM80_Q_PITCH + kin) = make_uint2(pk0, pk1);
+            if ((lane & 3) == 0) ((float*)(base + (size_t)nb_cols * GEMM80_Q_PITCH))[(kin >> 5) * nb_cols + col] = d;
         }
     }
 }
@@ -293,6 +363,44 @@ __device__ __forceinline__ void q6k_block_mma(const uint8_t* blk0, const uint8_t
     }
 }
 
+// Q8_0: one 34-byte block (fp16 d, 32 int8) per row and MMA; blk0 / blk1 = rows g and g+8 (2-byte aligned)
+template <int NB>
+struct ActChunk80 {
+    const int8_t* q;   // [NB][GEMM80_Q_PITCH]
+    const float* d;    // [32][NB]
+    __device__ explicit ActChunk80(const uint8_t* base) {
+        q = (const int8_t*)base;
+        d = (const float*)(base + (size_t)NB * GEMM80_Q_PITCH);
+    }
+};
+// D = A(16x32 s8) . B(32x8 s8)
+__device__ __forceinline__ void mma_s8s8_k32(int (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+                 : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
+}
+template <int NG>
+__device__ __forceinline__ void q80_block_mma(const uint8_t* blk0, const uint8_t* blk1, int kb, const ActChunk80<8 * NG>& x, int g, int c,
+                                              float (&acc)[NG][4]) {
+    constexpr int NB = 8 * NG;
+    // bytes 8c .. 8c+7 of the block's 32 values (k permuted as in the K-quant path)
+    const uint32_t a0 = lds32_a2(blk0 + 2 + 8 * c), a2 = lds32_a2(blk0 + 6 + 8 * c);
+    const uint32_t a1 = lds32_a2(blk1 + 2 + 8 * c), a3 = lds32_a2(blk1 + 6 + 8 * c);
+    const float d0 = h2f_bits(*(const uint16_t*)blk0), d1 = h2f_bits(*(const uint16_t*)blk1);
+#pragma unroll
+    for (int n = 0; n < NG; n++) {
+        const uint2 xb = *(const uint2*)(x.q + (size_t)(n * 8 + g) * GEMM80_Q_PITCH + kb * 32 + 8 * c);
+        int d4[4];
+        mma_s8s8_k32(d4, a0, a1, a2, a3, xb.x, xb.y);
+        const float2 dx = *(const float2*)(x.d + kb * NB + n * 8 + 2 * c);
+        // ggml: sumi * (d_w * d_x)
+        acc[n][0] += (float)d4[0] * (d0 * dx.x);
+        acc[n][1] += (float)d4[1] * (d0 * dx.y);
+        acc[n][2] += (float)d4[2] * (d1 * dx.x);
+        acc[n][3] += (float)d4[3] * (d1 * dx.y);
+    }
+}
+
 // fused epilogue of one (row pair, column): the mat-vec's, with per-column position, slot and output row
 __device__ __forceinline__ void epilogue_col(const GemmArgs& a, const GemvSeg& s, int p, int ra, int rb, float va, float vb, int j, int pos,
                                              int slot) {
@@ -345,9 +453,9 @@ __device__ __forceinline__ void epilogue_col(const GemmArgs& a, const GemvSeg& s
     }
 }
 
-template <int NG>
+template <int NG, int FMT>
 __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(const __grid_constant__ GemmArgs a) {
-    using G = Geo<NG>;
+    using G = Geo<NG, FMT>;
     constexpr int NB = G::NB;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* ring = smem;                                      // STAGES x { 16 row slots | activation chunk }
@@ -376,8 +484,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
     __syncthreads();
 
     const int K = a.K;
-    const int nblk_row = K / 256;
-    const int n_chunks = (nblk_row + GEMM_CHUNK_BLOCKS - 1) / GEMM_CHUNK_BLOCKS;
+    const int nblk_row = K / G::BLK;
+    const int n_chunks = (nblk_row + G::CB - 1) / G::CB;
 
     if (warp == W_PRODUCER) {
         int stage = 0, phase = 0, si = 0;
@@ -388,11 +496,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
             const int bb = block_bytes_of(s.type);
             const uint8_t* rowp = lane < GEMM_TILE_ROWS ? slot_row_ptr16(s, tile - s.tile0, lane, nblk_row * bb) : nullptr;
             for (int c = 0; c < n_chunks; c++) {
-                const int nb = min(GEMM_CHUNK_BLOCKS, nblk_row - c * GEMM_CHUNK_BLOCKS);
+                const int nb = min(G::CB, nblk_row - c * G::CB);
                 const uint8_t* src = nullptr;
                 uint32_t sz = 0;
                 if (rowp) {
-                    const uintptr_t lo = (uintptr_t)(rowp + (size_t)c * GEMM_CHUNK_BLOCKS * bb);
+                    const uintptr_t lo = (uintptr_t)(rowp + (size_t)c * G::CB * bb);
                     const uintptr_t hi = lo + (size_t)nb * bb;
                     src = (const uint8_t*)(lo & ~(uintptr_t)15);
                     sz = (uint32_t)(((hi + 15) & ~(uintptr_t)15) - (uintptr_t)src);
@@ -426,7 +534,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
             while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
             const int type = a.seg[si].type;
             for (int c = 0; c < n_chunks; c++) {
-                const int nb = min(GEMM_CHUNK_BLOCKS, nblk_row - c * GEMM_CHUNK_BLOCKS);
+                const int nb = min(G::CB, nblk_row - c * G::CB);
                 mbar_wait(&full[stage], phase);
                 if (type == B2_TYPE_Q4_K) {
                     for (int i = lane; i < GEMM_TILE_ROWS * nb; i += 32) {
@@ -502,7 +610,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
         const int bb = block_bytes_of(type);
         // row segment offset inside its slot (source address mod 16; chunks are multiples of 16 bytes for both types)
         uint32_t off0 = 0, off1 = 0;
-        if (type == B2_TYPE_Q6_K) {
+        if (type != B2_TYPE_Q4_K) {
             off0 = (uint32_t)((uintptr_t)slot_row_ptr16(s, tile - s.tile0, g, nblk_row * bb) & 15);
             off1 = (uint32_t)((uintptr_t)slot_row_ptr16(s, tile - s.tile0, g + 8, nblk_row * bb) & 15);
         }
@@ -512,18 +620,24 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
 #pragma unroll
             for (int j = 0; j < 4; j++) acc[n][j] = 0.0f;
         for (int ch = 0; ch < n_chunks; ch++) {
-            const int nb = min(GEMM_CHUNK_BLOCKS, nblk_row - ch * GEMM_CHUNK_BLOCKS);
+            const int nb = min(G::CB, nblk_row - ch * G::CB);
             mbar_wait(&ready[stage], phase);
             if (warp < nb) {
                 const uint8_t* st = ring + stage * G::STAGE_BYTES;
-                const ActChunk<NB> x(st + W_STAGE);
                 const uint8_t* row0 = st + g * ROW_SLOT + off0 + warp * bb;
                 const uint8_t* row1 = st + (g + 8) * ROW_SLOT + off1 + warp * bb;
-                if (type == B2_TYPE_Q4_K) {
-                    const uint8_t* dr = dec + stage * DEC_BYTES;
-                    q4k_block_mma<NG>(row0, row1, dr + g * DEC_ROW + warp * 32, dr + (g + 8) * DEC_ROW + warp * 32, warp, x, g, c, acc);
+                if (FMT == ACT_Q8K) {
+                    const ActChunk<NB> x(st + W_STAGE);
+                    if (type == B2_TYPE_Q4_K) {
+                        const uint8_t* dr = dec + stage * DEC_BYTES;
+                        q4k_block_mma<NG>(row0, row1, dr + g * DEC_ROW + warp * 32, dr + (g + 8) * DEC_ROW + warp * 32, warp, x, g, c, acc);
+                    } else {
+                        q6k_block_mma<NG>(row0, row1, warp, x, g, c, acc);
+                    }
                 } else {
-                    q6k_block_mma<NG>(row0, row1, warp, x, g, c, acc);
+                    // 32 blocks of 32 per chunk: warp w takes blocks w, w + 8, w + 16, w + 24
+                    const ActChunk80<NB> x(st + W_STAGE);
+                    for (int kb = warp; kb < nb; kb += NCW) q80_block_mma<NG>(row0 + (kb - warp) * 34, row1 + (kb - warp) * 34, kb, x, g, c, acc);
                 }
             }
             __syncwarp();
@@ -545,26 +659,26 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
     }
 }
 
-template <int NG>
+template <int NG, int FMT>
 size_t gemm_smem_bytes() {
-    using G = Geo<NG>;
+    using G = Geo<NG, FMT>;
     return (size_t)G::STAGES * (G::STAGE_BYTES + DEC_BYTES) + (size_t)G::RED_BUFS * G::RED_FLOATS * sizeof(float) +
            (3 * G::STAGES + 4) * sizeof(uint64_t);
 }
 
 int g_gemm_sms = 0;
 
-template <int NG>
+template <int NG, int FMT>
 int launch_gemm_ng(const GemmArgs& a, cudaStream_t st) {
     static bool configured = false;
-    const size_t smem = gemm_smem_bytes<NG>();
+    const size_t smem = gemm_smem_bytes<NG, FMT>();
     if (!configured) {
-        B2_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B2_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<NG, FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
     const int ctas = g_gemm_sms * (NG == 1 ? 2 : 1);
     const int grid = a.n_tiles < ctas ? a.n_tiles : ctas;
-    gemm_kernel<NG><<<grid, GEMM_THREADS, smem, st>>>(a);
+    gemm_kernel<NG, FMT><<<grid, GEMM_THREADS, smem, st>>>(a);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
@@ -576,8 +690,14 @@ int gemm_finalize(GemmArgs& a) {
         set_error("gemm: n_seg=%d out of range", a.n_seg);
         return B2_EINVAL;
     }
-    if (a.K <= 0 || a.K % 256) {
-        set_error("gemm: K=%d must be a positive multiple of 256", a.K);
+    a.act_fmt = gemm_act_for_type(a.seg[0].type);
+    if (a.act_fmt < 0) {
+        set_error("gemm: ggml type %d is not computed by the batched kernel (Q4_K, Q6_K, Q8_0)", a.seg[0].type);
+        return B2_EUNSUP;
+    }
+    const int kmult = a.act_fmt == ACT_Q8K ? 256 : 32;
+    if (a.K <= 0 || a.K % kmult) {
+        set_error("gemm: K=%d must be a positive multiple of %d", a.K, kmult);
         return B2_EINVAL;
     }
     if (a.cols.n < 1 || a.cols.n > GEMM_MAX_COLS) {
@@ -591,8 +711,8 @@ int gemm_finalize(GemmArgs& a) {
     int tiles = 0;
     for (int i = 0; i < a.n_seg; i++) {
         GemvSeg& s = a.seg[i];
-        if (s.type != B2_TYPE_Q4_K && s.type != B2_TYPE_Q6_K) {
-            set_error("gemm: segment %d is ggml type %d; the batched kernel computes Q4_K and Q6_K", i, s.type);
+        if (gemm_act_for_type(s.type) != a.act_fmt) {
+            set_error("gemm: segment %d is ggml type %d; the batched kernel computes Q4_K / Q6_K (together) and Q8_0", i, s.type);
             return B2_EUNSUP;
         }
         const uintptr_t need = s.type == B2_TYPE_Q4_K ? 15 : 1;
@@ -611,10 +731,16 @@ int gemm_finalize(GemmArgs& a) {
     return 0;
 }
 
-bool gemm_supports_type(int type) { return type == B2_TYPE_Q4_K || type == B2_TYPE_Q6_K; }
+int gemm_act_for_type(int type) {
+    if (type == B2_TYPE_Q4_K || type == B2_TYPE_Q6_K) return ACT_Q8K;
+    if (type == B2_TYPE_Q8_0) return ACT_Q80;
+    return -1;
+}
+bool gemm_supports_type(int type) { return gemm_act_for_type(type) >= 0; }
 
-int launch_act_quant(const float* x, int64_t x_stride, const float* norm_w, float eps, int K, int cols, uint8_t* act, cudaStream_t st) {
-    if (K <= 0 || K % 256 || cols < 1 || cols > GEMM_MAX_COLS) {
+int launch_act_quant(const float* x, int64_t x_stride, const float* norm_w, float eps, int K, int cols, uint8_t* act, cudaStream_t st,
+                     int act_fmt) {
+    if (K <= 0 || K % (act_fmt == ACT_Q80 ? 32 : 256) || cols < 1 || cols > GEMM_MAX_COLS) {
         set_error("act_quant: K=%d cols=%d", K, cols);
         return B2_EINVAL;
     }
@@ -623,7 +749,8 @@ int launch_act_quant(const float* x, int64_t x_stride, const float* norm_w, floa
         return B2_EINVAL;
     }
     const int nb = gemm_nb(cols);
-    act_quant_kernel<<<nb, 256, 0, st>>>(x, x_stride, norm_w, eps, K, cols, nb, act);
+    if (act_fmt == ACT_Q80) act_quant80_kernel<<<nb, 256, 0, st>>>(x, x_stride, norm_w, eps, K, cols, nb, act);
+    else act_quant_kernel<<<nb, 256, 0, st>>>(x, x_stride, norm_w, eps, K, cols, nb, act);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
@@ -635,9 +762,14 @@ int launch_gemm(const GemmArgs& a, cudaStream_t st) {
         B2_CUDA_CHECK(cudaDeviceGetAttribute(&g_gemm_sms, cudaDevAttrMultiProcessorCount, dev));
     }
     const int nb = gemm_nb(a.cols.n);
-    if (nb == 8) return launch_gemm_ng<1>(a, st);
-    if (nb == 16) return launch_gemm_ng<2>(a, st);
-    return launch_gemm_ng<4>(a, st);
+    if (a.act_fmt == ACT_Q80) {
+        if (nb == 8) return launch_gemm_ng<1, ACT_Q80>(a, st);
+        if (nb == 16) return launch_gemm_ng<2, ACT_Q80>(a, st);
+        return launch_gemm_ng<4, ACT_Q80>(a, st);
+    }
+    if (nb == 8) return launch_gemm_ng<1, ACT_Q8K>(a, st);
+    if (nb == 16) return launch_gemm_ng<2, ACT_Q8K>(a, st);
+    return launch_gemm_ng<4, ACT_Q8K>(a, st);
 }
 
 }  // namespace b2

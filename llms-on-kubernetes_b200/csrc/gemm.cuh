@@ -28,7 +28,15 @@ __host__ __device__ inline int gemm_nb(int cols) { return cols <= 8 ? 8 : (cols 
 __host__ __device__ inline size_t gemm_act_chunk_bytes(int nb) {
     return (size_t)nb * GEMM_Q_PITCH + (size_t)GEMM_CHUNK_BLOCKS * nb * (4 + 8 + 8);
 }
-inline size_t gemm_act_bytes(int K, int cols) {
+// Q8_0 weights take Q8_0 activations (32-element blocks, fp16-rounded scale each) in K-chunks of 32 blocks:
+// chunk c = { int8 q[NB][GEMM80_Q_PITCH]; float d[32][NB] }
+constexpr int GEMM80_CHUNK_BLOCKS = 32;
+constexpr int GEMM80_CHUNK_K = GEMM80_CHUNK_BLOCKS * 32;      // = 1024 elements
+constexpr int GEMM80_Q_PITCH = GEMM80_CHUNK_K + 32;
+__host__ __device__ inline size_t gemm80_act_chunk_bytes(int nb) { return (size_t)nb * GEMM80_Q_PITCH + (size_t)GEMM80_CHUNK_BLOCKS * nb * 4; }
+// act_fmt: ACT_Q8K (K-quant weights) or ACT_Q80 (Q8_0 weights)
+inline size_t gemm_act_bytes(int K, int cols, int act_fmt = ACT_Q8K) {
+    if (act_fmt == ACT_Q80) return (size_t)((K + GEMM80_CHUNK_K - 1) / GEMM80_CHUNK_K) * gemm80_act_chunk_bytes(gemm_nb(cols));
     return (size_t)((K + GEMM_CHUNK_K - 1) / GEMM_CHUNK_K) * gemm_act_chunk_bytes(gemm_nb(cols));
 }
 
@@ -45,6 +53,7 @@ struct GemmArgs {
     GemvSeg seg[3];
     int n_seg, n_tiles;          // tiles of GEMM_TILE_ROWS rows
     int K;
+    int act_fmt;                 // ACT_Q8K / ACT_Q80, set by gemm_finalize from the segment types (all segments agree)
     const uint8_t* act;          // quantised activations (gemm_act_bytes)
     GemmCols cols;
     int64_t out_stride;          // floats between columns of seg[].out (and of the residual input for EPI_RESID)
@@ -54,9 +63,11 @@ struct GemmArgs {
 };
 
 // X[cols][K] fp32 (column stride x_stride) -> quantised chunks; optional RMS norm (norm_w != NULL)
-int launch_act_quant(const float* x, int64_t x_stride, const float* norm_w, float eps, int K, int cols, uint8_t* act, cudaStream_t st);
+int launch_act_quant(const float* x, int64_t x_stride, const float* norm_w, float eps, int K, int cols, uint8_t* act, cudaStream_t st,
+                     int act_fmt = ACT_Q8K);
 int gemm_finalize(GemmArgs& a);
-bool gemm_supports_type(int type);   // Q4_K, Q6_K
+bool gemm_supports_type(int type);   // Q4_K, Q6_K, Q8_0
+int gemm_act_for_type(int type);     // ACT_Q8K / ACT_Q80 / -1
 int launch_gemm(const GemmArgs& a, cudaStream_t st);
 
 }  // namespace b2

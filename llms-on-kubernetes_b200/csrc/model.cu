@@ -626,9 +626,18 @@ bool batch_supported(const b2_model* m) {
     if (env_flag("B2_NO_BATCH")) return false;
     auto ok = [](const b2_model::W& w) { return gemm_supports_type(w.type); };
     if (!ok(m->output)) return false;
-    for (const auto& L : m->layers)
+    for (const auto& L : m->layers) {
         if (!ok(L.wq) || !ok(L.wk) || !ok(L.wv) || !ok(L.wo) || !ok(L.gate) || !ok(L.up) || !ok(L.down)) return false;
+        // Q, K, V share one launch and one quantised input: same activation format
+        if (gemm_act_for_type(L.wq.type) != gemm_act_for_type(L.wk.type) || gemm_act_for_type(L.wq.type) != gemm_act_for_type(L.wv.type)) return false;
+    }
     return true;
+}
+
+// the batched attention cuts a column's sequence into shorter pieces than the single-sequence launch: more CTAs per column
+int batch_attn_splits(int n_ctx) {
+    const int s = (n_ctx + ATTN_BATCH_SPLIT_TOKENS - 1) / ATTN_BATCH_SPLIT_TOKENS;
+    return s < 1 ? 1 : (s > ATTN_MAX_SPLITS ? ATTN_MAX_SPLITS : s);
 }
 
 int ensure_batch(b2_ctx* c) {
@@ -643,12 +652,12 @@ int ensure_batch(b2_ctx* c) {
     if ((rc = dmalloc(&b.h, (size_t)cap * I.d_ff))) return rc;
     if ((rc = dmalloc(&b.logits, (size_t)cap * I.vocab))) return rc;
     const int max_k = std::max(std::max(I.d_model, I.d_ff), I.n_head * I.head_dim);
-    if ((rc = dmalloc(&b.act, gemm_act_bytes(max_k, cap)))) return rc;
+    if ((rc = dmalloc(&b.act, std::max(gemm_act_bytes(max_k, cap, ACT_Q8K), gemm_act_bytes(max_k, cap, ACT_Q80))))) return rc;
     if ((rc = dmalloc(&b.tok, cap))) return rc;
     if ((rc = dmalloc(&b.pos, cap))) return rc;
     if ((rc = dmalloc(&b.slot, cap))) return rc;
     if ((rc = dmalloc(&b.out, cap))) return rc;
-    const size_t asz = attn_scratch_bytes_batch(I.n_head, I.head_dim, c->max_splits, cap);
+    const size_t asz = attn_scratch_bytes_batch(I.n_head, I.head_dim, batch_attn_splits(c->n_ctx), cap);
     B2_CUDA_CHECK(cudaMalloc(&b.attn_scratch, asz));
     B2_CUDA_CHECK(cudaMemsetAsync(b.attn_scratch, 0, asz, c->stream));
     B2_CUDA_CHECK(cudaMalloc(&b.argmax_scratch, argmax_scratch_bytes() * cap));
@@ -693,7 +702,7 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         __half* kc = c->k_cache + il * kv_layer;
         __half* vc = c->v_cache + il * kv_layer;
         // RMSNorm -> Q, K, V (+bias) -> RoPE -> cache
-        if ((rc = launch_act_quant(b.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, n, b.act, st))) return rc;
+        if ((rc = launch_act_quant(b.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, n, b.act, st, gemm_act_for_type(L.wq.type)))) return rc;
         common(a, I.d_model, n, qdim);
         seg_matrix(a.seg[0], L.wq, rope_pairing, EPI_ROPE_Q);
         a.seg[0].out = b.q;
@@ -712,18 +721,18 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         a.n_seg = 3;
         if ((rc = run(a))) return rc;
         // attention of every column over its own sequence
-        if ((rc = launch_attn_decode(b.q, kc, vc, b.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, b.pos, 0, c->max_splits,
-                                     b.attn_scratch, st, false, n, b.slot, c->slot_stride)))
+        if ((rc = launch_attn_decode(b.q, kc, vc, b.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, b.pos, 0, batch_attn_splits(c->n_ctx),
+                                     b.attn_scratch, st, false, n, b.slot, c->slot_stride, ATTN_BATCH_SPLIT_TOKENS)))
             return rc;
         // output projection + residual
-        if ((rc = launch_act_quant(b.attn_out, qdim, nullptr, 0.0f, qdim, n, b.act, st))) return rc;
+        if ((rc = launch_act_quant(b.attn_out, qdim, nullptr, 0.0f, qdim, n, b.act, st, gemm_act_for_type(L.wo.type)))) return rc;
         common(a, qdim, n, I.d_model);
         seg_matrix(a.seg[0], L.wo, PAIR_ADJ, EPI_RESID);
         a.seg[0].out = b.x;
         a.n_seg = 1;
         if ((rc = run(a))) return rc;
         // RMSNorm -> gate, up -> SwiGLU
-        if ((rc = launch_act_quant(b.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, n, b.act, st))) return rc;
+        if ((rc = launch_act_quant(b.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, n, b.act, st, gemm_act_for_type(L.gate.type)))) return rc;
         if (L.gate.type != L.up.type) {
             set_error("model: ffn_gate and ffn_up of layer %d have different types: unsupported", il);
             return B2_EUNSUP;
@@ -735,7 +744,7 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         a.n_seg = 1;
         if ((rc = run(a))) return rc;
         // down projection + residual
-        if ((rc = launch_act_quant(b.h, I.d_ff, nullptr, 0.0f, I.d_ff, n, b.act, st))) return rc;
+        if ((rc = launch_act_quant(b.h, I.d_ff, nullptr, 0.0f, I.d_ff, n, b.act, st, gemm_act_for_type(L.down.type)))) return rc;
         common(a, I.d_ff, n, I.d_model);
         seg_matrix(a.seg[0], L.down, PAIR_ADJ, EPI_RESID);
         a.seg[0].out = b.x;
@@ -745,7 +754,8 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
     // final norm + lm_head + greedy token for the last n_logits columns (none for the inner chunks of a prompt)
     if (n_logits <= 0) return 0;
     const int first = n - n_logits;
-    if ((rc = launch_act_quant(b.x + (size_t)first * I.d_model, I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits, b.act, st)))
+    if ((rc = launch_act_quant(b.x + (size_t)first * I.d_model, I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits, b.act, st,
+                               gemm_act_for_type(m->output.type))))
         return rc;
     common(a, I.d_model, n_logits, I.vocab);
     a.cols.pos = nullptr;
@@ -812,7 +822,7 @@ extern "C" int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32
     }
     const b2_model_info& I = c->m->info;
     if (!batch_supported(c->m)) {
-        set_error("b2_ctx_decode_batch: this model has matrices outside Q4_K / Q6_K; the batched kernel does not compute them yet");
+        set_error("b2_ctx_decode_batch: this model has matrices outside Q4_K / Q6_K / Q8_0; the batched kernel does not compute them yet");
         return B2_EUNSUP;
     }
     for (int j = 0; j < n; j++) {

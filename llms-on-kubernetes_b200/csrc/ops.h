@@ -12,14 +12,16 @@ int launch_dequantize(int type, const void* src, float* dst, int64_t n, cudaStre
 
 // attn.cu
 constexpr int ATTN_SPLIT_TOKENS = 1024;  // tokens one CTA handles per pass (shared-memory score buffer)
-constexpr int ATTN_MAX_SPLITS = 16;
+constexpr int ATTN_MAX_SPLITS = 64;
 int attn_max_splits(int n_ctx);
 size_t attn_scratch_bytes(int n_head, int head_dim, int max_splits);
 // pos_ptr != NULL: attend positions [0, *pos_ptr] (device-resident position, graph-replayable);
 // otherwise attend [0, n_tokens_imm).
 int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim,
                        int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl,
-                       int n_cols = 1, const int* col_slot = nullptr, int64_t slot_stride = 0);
+                       int n_cols = 1, const int* col_slot = nullptr, int64_t slot_stride = 0, int split_tokens = ATTN_SPLIT_TOKENS);
+// split_tokens: tokens per CTA (<= ATTN_SPLIT_TOKENS); the batched path uses shorter splits for more CTAs per column
+constexpr int ATTN_BATCH_SPLIT_TOKENS = 256;
 // n_cols > 1: a batch of queries q[n_cols][n_head][hd] -> out, column j at position pos_ptr[j] of sequence slot
 // col_slot[j] (caches slot_stride halfs apart); scratch of attn_scratch_bytes_batch()
 size_t attn_scratch_bytes_batch(int n_head, int head_dim, int max_splits, int n_cols);

@@ -415,6 +415,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             const int nblk_row = K / (ACT == ACT_Q8K ? 256 : 32);
             const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
             int si = 0;
+            // B2_STEP_TRACE: cycles warp 0 of CTA 0 spends waiting for data / in the dot products / waiting for the
+            // epilogue warp, summed over the stage's tiles (marks 4..6 of the trace)
+            const bool tracing = P.trace && blockIdx.x == 0 && tid == 0;
+            long long cyc_ready = 0, cyc_dot = 0, cyc_free = 0;
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
                 while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
                 const GemvSeg& s = a.seg[si];
@@ -426,20 +430,35 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                 float acc = 0.0f;
                 for (int c = 0; c < n_chunks; c++) {
                     const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
+                    const long long c0 = tracing ? clock64() : 0;
                     mbar_wait(&ready[stage], phase);
+                    const long long c1 = tracing ? clock64() : 0;
                     const uint8_t* row = ring + stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
                     acc += dot_chunk<ACT>(type, row, dec + stage * G::DEC_BYTES + r * G::DEC_ROW, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&empty[stage]);
+                    if (tracing) {
+                        const long long c2 = clock64();
+                        cyc_ready += c1 - c0;
+                        cyc_dot += c2 - c1 + (__float_as_uint(acc) == 0x7fc0dead ? 1 : 0);
+                    }
                     if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
                 }
                 acc += __shfl_xor_sync(0xffffffffu, acc, 1);
                 acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                const long long c3 = tracing ? clock64() : 0;
                 mbar_wait(&part_free[parity], (fph >> parity) & 1);
+                if (tracing) cyc_free += clock64() - c3;
                 fph ^= 1 << parity;
                 if ((lane & 3) == 0) red[(parity * NCW + warp) * TILE_ROWS + r] = acc;
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&part_full[parity]);
+            }
+            if (tracing) {
+                unsigned long long* tr = P.trace + oi * STEP_TRACE_SLOTS;
+                tr[4] = tr[0] + (unsigned long long)(cyc_ready * 1000 / 1965);
+                tr[5] = tr[0] + (unsigned long long)(cyc_dot * 1000 / 1965);
+                tr[6] = tr[0] + (unsigned long long)(cyc_free * 1000 / 1965);
             }
             if (tid == 0) stamp(P, oi, 2);
             // the epilogue warp arrives on the grid barrier for this stage

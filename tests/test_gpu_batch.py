@@ -7,7 +7,7 @@ import pytest
 from oracle import ref_model as rm
 
 pytestmark = pytest.mark.gpu
-MODELS = ["tiny-llama-q4_k_m", "tiny-llama3-q4_k_m"]   # Q4_K / Q6_K mixes: what the tensor-core kernel computes
+MODELS = ["tiny-llama-q4_k_m", "tiny-llama3-q4_k_m", "tiny-qwen2-q8_0"]   # Q4_K / Q6_K mixes and Q8_0: what the tensor-core kernel computes
 LOGIT_TOL = 0.03   # of the logit range, see tests/test_gpu_model.py
 KL_TOL = 1e-3
 
@@ -121,10 +121,10 @@ def test_decode_batch_argument_checks(b2, tiny_models):
     with pytest.raises(b2.B2Error):
         ctx.decode_batch([m.info.vocab], [0])                 # token outside the vocabulary
     ctx.free(); m.free()
-    q8 = b2.Model(tiny_models["tiny-qwen2-q8_0"])
+    q8 = b2.Model(tiny_models["tiny-llama-q5_k_m"])
     c8 = b2.Context(q8, 64)
     with pytest.raises(b2.B2Error):
-        c8.decode_batch([1, 2], [0, 1])                       # Q8_0 matrices: not on the batched path (yet)
+        c8.decode_batch([1, 2], [0, 1])                       # Q5_K matrices: not on the batched path (yet)
     # ... and its prompts take the per-token path
     tok, lg = c8.decode([1, 2, 3, 4, 5], 0)
     assert np.isfinite(lg).all()

@@ -8,12 +8,12 @@ from oracle import quants_np as qn
 from oracle import ref_model as rm
 
 pytestmark = pytest.mark.gpu
-TYPES = [qn.Q4_K, qn.Q6_K]
+TYPES = [qn.Q4_K, qn.Q6_K, qn.Q8_0]
 
 
 def _case(b2, synth, qt, N, K, B, seed, scale=1.0):
     rng = np.random.default_rng(seed)
-    W = synth.random_blocks(qt, N * (K // 256), rng).reshape(N, -1)
+    W = synth.random_blocks(qt, N * (K // qn.BLOCK[qt][0]), rng).reshape(N, -1)
     X = (rng.standard_normal((B, K)) * scale).astype(np.float32)
     got = b2.gemm(qt, W, X, N, K)
     assert got.shape == (B, N)
@@ -43,12 +43,18 @@ def test_gemm_agrees_with_gemv_kernel(b2, synth, qt):
     """Same integer arithmetic as the single-column kernel: results agree to fp32 summation order."""
     rng = np.random.default_rng(11 + qt)
     N, K, B = 256, 4096, 8
-    W = synth.random_blocks(qt, N * (K // 256), rng).reshape(N, -1)
+    W = synth.random_blocks(qt, N * (K // qn.BLOCK[qt][0]), rng).reshape(N, -1)
     X = rng.standard_normal((B, K)).astype(np.float32)
     Y = b2.gemm(qt, W, X, N, K)
     for b in range(B):
         y = b2.gemv(qt, W, X[b], N, K)
         assert np.allclose(Y[b], y, rtol=0, atol=4e-6 * np.abs(y).max() + 1e-6)
+
+
+@pytest.mark.parametrize("N,K,B", [(24, 1536, 8), (16, 8960, 20), (10, 96, 3)])
+def test_gemm_q8_0_ragged_k(b2, synth, N, K, B):
+    """Q8_0 rows need K to be a multiple of 32 only (Qwen2.5: 1536, 8960): partial last chunk, partial warp."""
+    _case(b2, synth, qn.Q8_0, N, K, B, seed=N + K + B)
 
 
 def test_gemm_zero_columns_and_tiny_values(b2, synth):
@@ -64,7 +70,7 @@ def test_gemm_zero_columns_and_tiny_values(b2, synth):
 
 def test_gemm_rejects_unsupported(b2):
     d = b2.DevBuf(1 << 16)
-    assert b2.lib.b2_gemm(b2.Q8_0, d.ptr, d.ptr, d.ptr, 16, 256, 8, d.ptr, None) == b2.lib.b2_gemm(b2.Q5_K, d.ptr, d.ptr, d.ptr, 16, 256, 8, d.ptr, None) < 0
+    assert b2.lib.b2_gemm(b2.Q5_K, d.ptr, d.ptr, d.ptr, 16, 256, 8, d.ptr, None) < 0 and b2.lib.b2_gemm(b2.F16, d.ptr, d.ptr, d.ptr, 16, 256, 8, d.ptr, None) < 0
     assert b2.lib.b2_gemm(b2.Q4_K, d.ptr, d.ptr, d.ptr, 16, 256, 33, d.ptr, None) < 0
     assert b2.lib.b2_gemm(b2.Q4_K, d.ptr, d.ptr, d.ptr, 16, 100, 8, d.ptr, None) < 0
-    assert b2.lib.b2_gemm_scratch_bytes(4096, 8) == 2 * (8 * 2080 + 8 * 8 * 20)
+    assert b2.lib.b2_gemm_scratch_bytes(4096, 8) == max(2 * (8 * 2080 + 8 * 8 * 20), 4 * (8 * 1056 + 32 * 8 * 4))
