@@ -37,8 +37,9 @@ constexpr int MAX_HD = 256;
 // partial record: [0] = max, [1] = sum, [2..2+hd) = unnormalised output
 __device__ __forceinline__ size_t part_stride(int hd) { return (size_t)hd + 2; }
 
-template <int HD>
-__global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* __restrict__ q, const __half* __restrict__ kc,
+// MG = query heads per kv head the registers are sized for (4 keeps two CTAs per SM; 8 for wider GQA groups)
+template <int HD, int MG>
+__global__ void __launch_bounds__(ATTN_THREADS, MG <= 4 ? 2 : 1) attn_decode_kernel(const float* __restrict__ q, const __half* __restrict__ kc,
                                                                    const __half* __restrict__ vc, float* __restrict__ out,
                                                                    int n_head, int n_kv, int n_ctx, const int* __restrict__ n_tokens_ptr,
                                                                    int n_tokens_imm, int max_splits, float* __restrict__ partials,
@@ -64,10 +65,10 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
     const int n_splits = min(max_splits, (T + split_tokens - 1) / split_tokens);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-    __shared__ float s_scores[MAX_GROUP][ATTN_SPLIT_TOKENS];
-    __shared__ float s_red[MAX_GROUP][ATTN_WARPS];
-    __shared__ float s_out[MAX_GROUP][HD];
-    __shared__ float s_m[MAX_GROUP], s_l[MAX_GROUP];
+    __shared__ float s_scores[MG][ATTN_SPLIT_TOKENS];
+    __shared__ float s_red[MG][ATTN_WARPS];
+    __shared__ float s_out[MG][HD];
+    __shared__ float s_m[MG], s_l[MG];
     __shared__ int s_last;
 
     if (split < n_splits) {
@@ -80,18 +81,18 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
         const float scale = 1.0f / sqrtf((float)HD);
 
         // query slice for this lane, rounded to fp16 like ggml's F16 vec_dot operand
-        float qf[MAX_GROUP][8];
+        float qf[MG][8];
 #pragma unroll
-        for (int h = 0; h < MAX_GROUP; h++)
+        for (int h = 0; h < MG; h++)
             if (h < g) {
                 const float* qp = q + ((size_t)(kvh * g + h)) * HD + ln * 8;
 #pragma unroll
                 for (int i = 0; i < 8; i++) qf[h][i] = __half2float(__float2half_rn(qp[i]));
             }
 
-        float run_max[MAX_GROUP], run_sum[MAX_GROUP], acc[MAX_GROUP][8];
+        float run_max[MG], run_sum[MG], acc[MG][8];
 #pragma unroll
-        for (int h = 0; h < MAX_GROUP; h++) {
+        for (int h = 0; h < MG; h++) {
             run_max[h] = -INFINITY;
             run_sum[h] = 0.0f;
 #pragma unroll
@@ -104,9 +105,9 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
             // ---- scores s[h][t] = scale * <k_t, q_h> ----
             for (int tb = warp * TPW; tb < n; tb += ATTN_WARPS * TPW) {
                 const int t = tb + sub;
-                float d[MAX_GROUP];
+                float d[MG];
 #pragma unroll
-                for (int h = 0; h < MAX_GROUP; h++) d[h] = 0.0f;
+                for (int h = 0; h < MG; h++) d[h] = 0.0f;
                 if (t < n) {
                     const uint4 kv = *(const uint4*)(kbase + (size_t)(p0 + t) * HD + ln * 8);
                     const __half2* k2 = (const __half2*)&kv;
@@ -114,12 +115,12 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
                     for (int i = 0; i < 4; i++) {
                         const float2 kf = __half22float2(k2[i]);
 #pragma unroll
-                        for (int h = 0; h < MAX_GROUP; h++)
+                        for (int h = 0; h < MG; h++)
                             if (h < g) d[h] += kf.x * qf[h][2 * i] + kf.y * qf[h][2 * i + 1];
                     }
                 }
 #pragma unroll
-                for (int h = 0; h < MAX_GROUP; h++)
+                for (int h = 0; h < MG; h++)
                     if (h < g) {
 #pragma unroll
                         for (int o = LPT / 2; o > 0; o >>= 1) d[h] += __shfl_xor_sync(0xffffffffu, d[h], o);
@@ -128,9 +129,9 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
             }
             __syncthreads();
             // ---- pass maximum, probabilities (fp32 exp, fp16-rounded for the V product), sum ----
-            float pmax[MAX_GROUP], psum[MAX_GROUP];
+            float pmax[MG], psum[MG];
 #pragma unroll
-            for (int h = 0; h < MAX_GROUP; h++)
+            for (int h = 0; h < MG; h++)
                 if (h < g) {
                     float m = -INFINITY;
                     for (int t = tid; t < n; t += ATTN_THREADS) m = fmaxf(m, s_scores[h][t]);
@@ -139,7 +140,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
                 }
             __syncthreads();
 #pragma unroll
-            for (int h = 0; h < MAX_GROUP; h++)
+            for (int h = 0; h < MG; h++)
                 if (h < g) {
                     float m = s_red[h][0];
 #pragma unroll
@@ -148,7 +149,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
                 }
             __syncthreads();
 #pragma unroll
-            for (int h = 0; h < MAX_GROUP; h++)
+            for (int h = 0; h < MG; h++)
                 if (h < g) {
                     float s = 0.0f;
                     for (int t = tid; t < n; t += ATTN_THREADS) {
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
                 }
             __syncthreads();
 #pragma unroll
-            for (int h = 0; h < MAX_GROUP; h++)
+            for (int h = 0; h < MG; h++)
                 if (h < g) {
                     float s = 0.0f;
 #pragma unroll
@@ -171,9 +172,9 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
             // single pass over the whole sequence: normalise before rounding, exactly like the oracle
             const bool exact = (n_splits == 1 && p0 == t0 && p1 == t1);
             // ---- o[h][d] += p[h][t] * v[t][d] ----
-            float corr[MAX_GROUP], pn[MAX_GROUP];
+            float corr[MG], pn[MG];
 #pragma unroll
-            for (int h = 0; h < MAX_GROUP; h++)
+            for (int h = 0; h < MG; h++)
                 if (h < g) {
                     const float nm = fmaxf(run_max[h], pmax[h]);
                     corr[h] = run_max[h] == -INFINITY ? 0.0f : expf(run_max[h] - nm);
@@ -196,7 +197,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
                         vf[2 * i + 1] = f.y;
                     }
 #pragma unroll
-                    for (int h = 0; h < MAX_GROUP; h++)
+                    for (int h = 0; h < MG; h++)
                         if (h < g) {
                             const float e = s_scores[h][t];
                             const float pr = exact ? __half2float(__float2half_rn(e * pn[h]))
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
         }
         // ---- reduce acc over the token sub-lanes of a warp, then over warps ----
 #pragma unroll
-        for (int h = 0; h < MAX_GROUP; h++)
+        for (int h = 0; h < MG; h++)
             if (h < g) {
 #pragma unroll
                 for (int i = 0; i < 8; i++) {
@@ -220,12 +221,12 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
                     acc[h][i] = v;
                 }
             }
-        for (int i = tid; i < MAX_GROUP * HD; i += ATTN_THREADS) (&s_out[0][0])[i] = 0.0f;
+        for (int i = tid; i < MG * HD; i += ATTN_THREADS) (&s_out[0][0])[i] = 0.0f;
         __syncthreads();
         for (int w = 0; w < ATTN_WARPS; w++) {
             if (warp == w && sub == 0) {
 #pragma unroll
-                for (int h = 0; h < MAX_GROUP; h++)
+                for (int h = 0; h < MG; h++)
                     if (h < g) {
 #pragma unroll
                         for (int i = 0; i < 8; i++) s_out[h][ln * 8 + i] += acc[h][i];
@@ -235,7 +236,7 @@ __global__ void __launch_bounds__(ATTN_THREADS) attn_decode_kernel(const float* 
         }
         if (tid == 0) {
 #pragma unroll
-            for (int h = 0; h < MAX_GROUP; h++)
+            for (int h = 0; h < MG; h++)
                 if (h < g) {
                     s_m[h] = run_max[h];
                     s_l[h] = run_sum[h];
@@ -357,12 +358,11 @@ int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    if (head_dim == 64)
-        B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, attn_decode_kernel<64>, q, kc, vc, out, n_head, n_kv, n_ctx, pos_ptr, n_tokens_imm,
-                                         gy, partials, counters, col_slot, (long long)slot_stride, split_tokens));
-    else
-        B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, attn_decode_kernel<128>, q, kc, vc, out, n_head, n_kv, n_ctx, pos_ptr, n_tokens_imm,
-                                         gy, partials, counters, col_slot, (long long)slot_stride, split_tokens));
+    const bool narrow = n_head / n_kv <= 4;
+    auto kern = head_dim == 64 ? (narrow ? attn_decode_kernel<64, 4> : attn_decode_kernel<64, MAX_GROUP>)
+                               : (narrow ? attn_decode_kernel<128, 4> : attn_decode_kernel<128, MAX_GROUP>);
+    B2_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, q, kc, vc, out, n_head, n_kv, n_ctx, pos_ptr, n_tokens_imm, gy, partials, counters,
+                                     col_slot, (long long)slot_stride, split_tokens));
     return 0;
 }
 
