@@ -215,6 +215,9 @@ int b2_ctx_n_slots(const b2_ctx* c);
  * last_only = 1: only the last column's (one entry).  Either output may be NULL.  Q4_K / Q6_K models. */
 int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int32_t* pos, int n, int last_only,
                         int32_t* next_tokens_out, float* logits_out_host);
+/* fp32 logits [vocab] of output column col of the last b2_ctx_decode_batch (for callers that sample only some
+ * columns on the host instead of copying all of them) */
+int b2_ctx_batch_logits(b2_ctx* c, int col, float* logits_out_host);
 
 /* Greedy generation entirely on the device: starting from the state left by b2_ctx_decode (whose greedy
  * token t0 the caller already has), run n_steps decode steps, each consuming the previous argmax without a

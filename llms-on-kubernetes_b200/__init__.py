@@ -99,6 +99,7 @@ SYMBOLS = {
     "b2_ctx_create_slots": (_I, [_P, _I, _I, C.POINTER(_P)]),
     "b2_ctx_n_slots": (_I, [_P]),
     "b2_ctx_decode_batch": (_I, [_P, _P, _P, _P, _I, _I, _P, _P]),
+    "b2_ctx_batch_logits": (_I, [_P, _I, _P]),
     "b2_ctx_generate_greedy": (_I, [_P, _I, _P]),
     "b2_ctx_enqueue_steps": (_I, [_P, _I]),
     "b2_ctx_stream": (_P, [_P]),

@@ -844,6 +844,17 @@ extern "C" int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32
     return 0;
 }
 
+extern "C" int b2_ctx_batch_logits(b2_ctx* c, int col, float* logits_out_host) {
+    if (!c || !logits_out_host || !c->bt.cap || col < 0 || col >= c->bt.cap) {
+        set_error("b2_ctx_batch_logits: bad arguments (column %d)", col);
+        return B2_EINVAL;
+    }
+    const b2_model_info& I = c->m->info;
+    B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->bt.logits + (size_t)col * I.vocab, (size_t)I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
 extern "C" int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out) { return b2_ctx_create_slots(m, n_ctx, 1, out); }
 
 extern "C" int b2_ctx_create_slots(b2_model* m, int n_ctx, int n_slots, b2_ctx** out) {

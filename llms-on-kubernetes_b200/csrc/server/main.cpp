@@ -25,204 +25,16 @@
 #include <sstream>
 #include <thread>
 
+#include "engine.h"
 #include "json.h"
 #include "tokenizer.h"
 
 using b2json::Value;
+using b2srv::Engine;
+using b2srv::GenParams;
+using b2srv::GenResult;
 
 namespace {
-
-// ------------------------------------------------------------------------------------------------
-// engine: one model, one decode context, requests serialised (continuous batching is SURVEY 8f "next")
-// ------------------------------------------------------------------------------------------------
-struct GenParams {
-    int max_tokens = 256;
-    float temperature = 0.8f, top_p = 0.95f, min_p = 0.05f;   // llama-server's defaults when the request omits them
-    int top_k = 40;
-    uint64_t seed = 0xFFFFFFFFull;
-    std::vector<std::string> stop;
-    bool ignore_eos = false;
-};
-struct GenResult {
-    std::vector<int32_t> tokens;
-    std::string text, finish = "length";
-    int prompt_tokens = 0;
-    std::string error;
-    int error_status = 0;
-};
-
-struct Engine {
-    b2_model* model = nullptr;
-    b2_ctx* ctx = nullptr;
-    b2_model_info info{};
-    b2srv::Tokenizer tok;
-    std::string alias, model_path;
-    std::atomic<bool> ready{false};
-    std::string load_error;
-    std::mutex mu;
-    std::vector<int32_t> cached;   // tokens whose K/V rows are in the cache at positions [0, size)
-    std::vector<float> logits;
-
-    int n_ctx() const { return b2_ctx_n_ctx(ctx); }
-
-    bool load(const std::string& path, int n_ctx_req) {
-        int rc = b2_model_load(path.c_str(), 0, 0, 1, &model);
-        if (rc) { load_error = b2_last_error(); return false; }
-        b2_model_get_info(model, &info);
-        std::string err;
-        if (!tok.load(b2_model_gguf(model), &err)) { load_error = err; return false; }
-        rc = b2_ctx_create(model, n_ctx_req, &ctx);
-        if (rc) { load_error = b2_last_error(); return false; }
-        logits.resize(info.vocab);
-        ready = true;
-        return true;
-    }
-
-    int32_t sample(const GenParams& p, std::mt19937_64& rng) {
-        const int V = info.vocab;
-        std::vector<std::pair<float, int32_t>> c(V);
-        for (int i = 0; i < V; i++) c[i] = {logits[i], i};
-        int k = p.top_k > 0 && p.top_k < V ? p.top_k : V;
-        std::partial_sort(c.begin(), c.begin() + k, c.end(), [](auto& a, auto& b) { return a.first > b.first || (a.first == b.first && a.second < b.second); });
-        c.resize(k);
-        const float mx = c[0].first;
-        double sum = 0;
-        std::vector<double> pr(k);
-        for (int i = 0; i < k; i++) { pr[i] = std::exp((double)(c[i].first - mx) / p.temperature); sum += pr[i]; }
-        for (auto& x : pr) x /= sum;
-        int keep = k;
-        if (p.min_p > 0) {
-            keep = 0;
-            while (keep < k && pr[keep] >= p.min_p * pr[0]) keep++;
-            keep = std::max(keep, 1);
-        }
-        if (p.top_p < 1.0f) {
-            double acc = 0;
-            int n = 0;
-            while (n < keep) { acc += pr[n++]; if (acc >= p.top_p) break; }
-            keep = std::max(n, 1);
-        }
-        double tot = 0;
-        for (int i = 0; i < keep; i++) tot += pr[i];
-        double r = std::uniform_real_distribution<double>(0.0, tot)(rng);
-        for (int i = 0; i < keep; i++) { r -= pr[i]; if (r <= 0) return c[i].second; }
-        return c[keep - 1].second;
-    }
-
-    // on_text(piece) is called as text becomes final; returning false aborts (client gone)
-    GenResult generate(const std::vector<int32_t>& prompt, const GenParams& p, const std::function<bool(const std::string&)>& on_text) {
-        std::lock_guard<std::mutex> lk(mu);
-        GenResult res;
-        res.prompt_tokens = (int)prompt.size();
-        const int nctx = n_ctx();
-        if (prompt.empty()) { res.error = "the prompt is empty"; res.error_status = 400; return res; }
-        if ((int)prompt.size() >= nctx) {
-            res.error = "the prompt (" + std::to_string(prompt.size()) + " tokens) does not fit the context size " + std::to_string(nctx);
-            res.error_status = 400;
-            return res;
-        }
-        for (int32_t t : prompt)
-            if (t < 0 || t >= info.vocab) { res.error = "token id out of range in prompt"; res.error_status = 400; return res; }
-        int max_new = std::min(p.max_tokens < 0 ? nctx : p.max_tokens, nctx - (int)prompt.size());
-        const bool greedy = p.temperature <= 0.0f || p.top_k == 1;
-        std::mt19937_64 rng(p.seed == 0xFFFFFFFFull ? std::random_device{}() : p.seed);
-
-        // reuse the longest common prefix already in the KV cache, but always re-evaluate the last prompt token
-        size_t cp = 0;
-        while (cp < cached.size() && cp < prompt.size() && cached[cp] == prompt[cp]) cp++;
-        if (cp >= prompt.size()) cp = prompt.size() - 1;
-        int32_t next = 0;
-        int rc = b2_ctx_decode(ctx, prompt.data() + cp, (int)(prompt.size() - cp), (int)cp, greedy ? nullptr : logits.data(), &next);
-        if (rc) { res.error = b2_last_error(); res.error_status = 500; cached.clear(); return res; }
-        cached = prompt;
-        if (!greedy) next = sample(p, rng);
-
-        std::string pending;   // text held back because it may be the start of a stop string
-        size_t max_stop = 0;
-        for (auto& s : p.stop) max_stop = std::max(max_stop, s.size());
-        auto flush = [&](bool final) -> bool {
-            // emit everything except a tail that could still grow into a stop string
-            const size_t hold = final ? 0 : (max_stop ? max_stop - 1 : 0);
-            // do not split a UTF-8 sequence
-            size_t emit = pending.size() > hold ? pending.size() - hold : 0;
-            while (!final && emit > 0 && emit < pending.size() && ((unsigned char)pending[emit] & 0xC0) == 0x80) emit--;
-            if (!final && emit == pending.size()) {
-                // ... nor emit a lead byte whose continuation bytes have not been generated yet
-                for (size_t back = 1; back <= 3 && back <= emit; back++) {
-                    const unsigned char c = (unsigned char)pending[emit - back];
-                    if ((c & 0xC0) == 0x80) continue;
-                    const size_t need = c >= 0xF0 ? 4 : c >= 0xE0 ? 3 : c >= 0xC0 ? 2 : 1;
-                    if (need > back) emit -= back;
-                    break;
-                }
-            }
-            if (!emit) return true;
-            const std::string piece = pending.substr(0, emit);
-            pending.erase(0, emit);
-            res.text += piece;
-            return on_text ? on_text(piece) : true;
-        };
-        bool done = max_new <= 0;
-        std::vector<int32_t> chunk;
-        while (!done) {
-            // `next` has been sampled but not yet fed to the model
-            if (!p.ignore_eos && tok.is_eog(next)) { res.finish = "stop"; break; }
-            res.tokens.push_back(next);
-            tok.decode_append(next, pending);
-            bool stopped = false;
-            for (auto& s : p.stop) {
-                const size_t at = s.empty() ? std::string::npos : pending.find(s);
-                if (at != std::string::npos) { pending.erase(at); stopped = true; break; }
-            }
-            if (stopped) { res.finish = "stop"; break; }
-            if (!flush(false)) { res.finish = "abort"; break; }
-            if ((int)res.tokens.size() >= max_new) break;
-            if (greedy) {
-                // feed it and take the argmax on the device; a few steps at a time without a host round trip
-                const int room = std::min({8, max_new - (int)res.tokens.size(), nctx - (int)cached.size()});
-                if (room <= 0) break;
-                chunk.resize(room);
-                rc = b2_ctx_generate_greedy(ctx, room, chunk.data());
-                if (rc) { res.error = b2_last_error(); res.error_status = 500; cached.clear(); return res; }
-                // tokens consumed by those steps: next, chunk[0..room-2]; chunk[room-1] is sampled, not yet fed
-                cached.push_back(next);
-                int used = 0;
-                for (; used < room - 1; used++) {
-                    const int32_t t = chunk[used];
-                    if ((!p.ignore_eos && tok.is_eog(t))) break;
-                    res.tokens.push_back(t);
-                    tok.decode_append(t, pending);
-                    bool st = false;
-                    for (auto& s : p.stop) {
-                        const size_t at = s.empty() ? std::string::npos : pending.find(s);
-                        if (at != std::string::npos) { pending.erase(at); st = true; break; }
-                    }
-                    if (st) { stopped = true; break; }
-                    if (!flush(false)) { res.finish = "abort"; stopped = true; break; }
-                    cached.push_back(t);
-                    if ((int)res.tokens.size() >= max_new) { done = true; break; }
-                }
-                if (stopped) { if (res.finish != "abort") res.finish = "stop"; break; }
-                if (used < room - 1 && !done) {
-                    // an end-of-generation token inside the chunk: the cache holds rows past it, forget them
-                    res.finish = "stop";
-                    break;
-                }
-                if (done) break;
-                next = chunk[room - 1];
-            } else {
-                if ((int)cached.size() >= nctx) break;
-                int32_t dummy;
-                rc = b2_ctx_decode(ctx, &next, 1, (int)cached.size(), logits.data(), &dummy);
-                if (rc) { res.error = b2_last_error(); res.error_status = 500; cached.clear(); return res; }
-                cached.push_back(next);
-                next = sample(p, rng);
-            }
-        }
-        flush(true);
-        return res;
-    }
-};
 
 Engine g_engine;
 
@@ -578,6 +390,8 @@ int main(int argc, char** argv) {
     signal(SIGPIPE, SIG_IGN);
     std::string host = "127.0.0.1", model, alias, tool_mode, tool_arg;
     int port = 8080, n_ctx = 0;
+    // sequences decoded together (llama-server's --parallel); the chart cannot pass it, so the default serves concurrency
+    int n_parallel = getenv("B2_N_SLOTS") ? atoi(getenv("B2_N_SLOTS")) : 16;
     // flags of upstream llama-server that take a value: accepted and ignored so existing launch lines keep working
     const char* valued[] = {"-t", "--threads", "-tb", "--threads-batch", "-ngl", "--n-gpu-layers", "--gpu-layers", "-b", "--batch-size", "-ub", "--ubatch-size",
                             "-np", "--parallel", "--temp", "--top-k", "--top-p", "--min-p", "-n", "--n-predict", "--chat-template", "-fa", "--flash-attn",
@@ -595,6 +409,7 @@ int main(int argc, char** argv) {
         else if (a == "--model" || a == "-m") model = need("--model");
         else if (a == "--alias" || a == "-a") alias = need("--alias");
         else if (a == "--ctx-size" || a == "-c") n_ctx = atoi(need("--ctx-size"));
+        else if (a == "--parallel" || a == "-np") n_parallel = atoi(need("--parallel"));
         else if (a == "--tokenize") { tool_mode = "tokenize"; tool_arg = need("--tokenize"); }
         else if (a == "--detokenize") { tool_mode = "detokenize"; tool_arg = need("--detokenize"); }
         else if (a == "--apply-template") { tool_mode = "template"; tool_arg = need("--apply-template"); }
@@ -665,7 +480,7 @@ int main(int argc, char** argv) {
     // serve /health (503) while the model loads, like upstream
     std::thread loader([&] {
         const auto t0 = std::chrono::steady_clock::now();
-        if (!g_engine.load(model, n_ctx)) {
+        if (!g_engine.load(model, n_ctx, n_parallel)) {
             fprintf(stderr, "llama-server: failed to load model: %s\n", g_engine.load_error.c_str());
             _exit(1);
         }

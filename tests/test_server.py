@@ -214,3 +214,43 @@ def test_through_the_reference_gateway(server):
         assert st == 502 and "error" in out
     finally:
         srv.shutdown()
+
+
+@pytest.mark.gpu
+def test_concurrent_requests_are_batched_and_deterministic(server):
+    """Continuous batching: 12 requests in flight at once (the chart's Services and gateways deliver them concurrently).
+    Each column of a batch is computed independently of its neighbours, so the same request gives the same tokens
+    whatever else is running; against the same request served alone (single-sequence kernel) only near-ties may differ."""
+    import threading
+    rng = np.random.default_rng(21)
+    reqs = [{"model": "tinyllama", "prompt": rng.integers(3, 1024, size=int(rng.integers(2, 60))).tolist(), "max_tokens": 24,
+             "temperature": 0, "ignore_eos": True} for _ in range(12)]
+
+    def run_all():
+        out = [None] * len(reqs)
+
+        def one(i):
+            out[i] = post(server, "/v1/completions", reqs[i])
+
+        ts = [threading.Thread(target=one, args=(i,)) for i in range(len(reqs))]
+        for t in ts: t.start()
+        for t in ts: t.join()
+        return out
+
+    a, b = run_all(), run_all()
+    for (sa, oa), (sb, ob), rq in zip(a, b, reqs):
+        assert sa == sb == 200
+        assert oa["usage"]["prompt_tokens"] == len(rq["prompt"]) and oa["usage"]["completion_tokens"] == 24
+        assert len(oa["choices"][0]["tokens"]) == 24
+    same_runs = sum(oa["choices"][0]["tokens"] == ob["choices"][0]["tokens"] for (_, oa), (_, ob) in zip(a, b))
+    assert same_runs >= 10, same_runs      # (a sequence may meet the single-sequence kernel when it is the last one running)
+    alone = [post(server, "/v1/completions", rq) for rq in reqs]
+    same_alone = sum(oa["choices"][0]["tokens"][:8] == o1["choices"][0]["tokens"][:8] for (_, oa), (_, o1) in zip(a, alone))
+    assert same_alone >= 8, same_alone
+    # a sampled (non-greedy) request among greedy ones: per-column logits reach the host sampler
+    mixed = [dict(reqs[0]), dict(reqs[1], temperature=0.9, seed=7, top_k=20)]
+    res = [None, None]
+    ts = [threading.Thread(target=lambda i=i: res.__setitem__(i, post(server, "/v1/completions", mixed[i]))) for i in range(2)]
+    for t in ts: t.start()
+    for t in ts: t.join()
+    assert res[0][0] == res[1][0] == 200 and len(res[1][1]["choices"][0]["tokens"]) == 24
