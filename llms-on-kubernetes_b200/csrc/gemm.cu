@@ -29,8 +29,6 @@ using gemvdev::pair_rows;
 namespace {
 
 constexpr int NCW = 8, NCT = NCW * 32;
-constexpr int W_PRODUCER = NCW, W_DECODER = NCW + 1, W_EPILOGUE = NCW + 2;
-constexpr int GEMM_THREADS = (NCW + 3) * 32;
 constexpr int ROW_SLOT = GEMM_CHUNK_BLOCKS * 210 + 16;      // largest row segment of a chunk + alignment slack
 constexpr int W_STAGE = GEMM_TILE_ROWS * ROW_SLOT;           // 27136
 constexpr int DEC_ROW = GEMM_CHUNK_BLOCKS * 32 + 16;         // decoded Q4_K headers of one row (padded against bank conflicts)
@@ -40,6 +38,11 @@ constexpr int DEC_BYTES = GEMM_TILE_ROWS * DEC_ROW;
 template <int NG, int FMT>
 struct Geo {
     static constexpr int NB = 8 * NG;
+    // 16 / 32 columns (one CTA per SM): two groups of 8 compute warps, each group takes half of the columns
+    static constexpr int WG = NG >= 2 ? 2 : 1;
+    static constexpr int NGL = NG / WG;            // column groups per compute warp
+    static constexpr int NCWT = NCW * WG;          // compute warps
+    static constexpr int THREADS = (NCWT + 3) * 32;   // + producer, header decoder, epilogue warps
     static constexpr int CB = FMT == ACT_Q8K ? GEMM_CHUNK_BLOCKS : GEMM80_CHUNK_BLOCKS;   // weight blocks per chunk and row
     static constexpr int BLK = FMT == ACT_Q8K ? 256 : 32;                                   // elements per weight block
     static constexpr int ACT_BYTES = FMT == ACT_Q8K ? (int)((size_t)NB * GEMM_Q_PITCH + (size_t)GEMM_CHUNK_BLOCKS * NB * 20)
@@ -260,10 +263,11 @@ struct ActChunk {
 };
 
 // Q4_K super-block kb of rows g and g+8 of the stage against NG groups of 8 columns
-template <int NG>
+// NGL column groups starting at group ng0 of the NB columns
+template <int NGL, int NB>
 __device__ __forceinline__ void q4k_block_mma(const uint8_t* blk0, const uint8_t* blk1, const uint8_t* rec0, const uint8_t* rec1, int kb,
-                                              const ActChunk<8 * NG>& x, int g, int c, float (&acc)[NG][4]) {
-    constexpr int NB = 8 * NG;
+                                              const ActChunk<NB>& x, int ng0, int g, int c, float (&acc)[NGL][4]) {
+    constexpr int NG = NGL;
     const uint4 w0 = *(const uint4*)(rec0 + 16), w1 = *(const uint4*)(rec1 + 16);   // (sc[2p], sc[2p+1], m[2p], m[2p+1]) per word
     const uint32_t ws0[4] = {w0.x, w0.y, w0.z, w0.w}, ws1[4] = {w1.x, w1.y, w1.z, w1.w};
     int ilo[NG][4], ihi[NG][4];
@@ -278,7 +282,7 @@ __device__ __forceinline__ void q4k_block_mma(const uint8_t* blk0, const uint8_t
         const int s0l = ws0[p] & 0xff, s0h = (ws0[p] >> 8) & 0xff, s1l = ws1[p] & 0xff, s1h = (ws1[p] >> 8) & 0xff;
 #pragma unroll
         for (int n = 0; n < NG; n++) {
-            const int8_t* xq = x.q + (size_t)(n * 8 + g) * GEMM_Q_PITCH + kb * 256 + 64 * p + 8 * c;
+            const int8_t* xq = x.q + (size_t)((ng0 + n) * 8 + g) * GEMM_Q_PITCH + kb * 256 + 64 * p + 8 * c;
             const uint2 xl = *(const uint2*)xq, xh = *(const uint2*)(xq + 32);
             int dl[4], dh[4];
             mma_u8s8_k32(dl, qa.x & 0x0F0F0F0Fu, qb.x & 0x0F0F0F0Fu, qa.y & 0x0F0F0F0Fu, qb.y & 0x0F0F0F0Fu, xl.x, xl.y);
@@ -293,13 +297,13 @@ __device__ __forceinline__ void q4k_block_mma(const uint8_t* blk0, const uint8_t
     const float2 dd0 = *(const float2*)rec0, dd1 = *(const float2*)rec1;   // (d, dmin) of rows g, g+8
 #pragma unroll
     for (int n = 0; n < NG; n++) {
-        const int col = n * 8 + g;
+        const int col = (ng0 + n) * 8 + g;
         const uint32_t bl = c < 2 ? *(const uint32_t*)(x.bl + (kb * NB + col) * 8 + 4 * c) : 0u;
         const uint32_t bh = c < 2 ? *(const uint32_t*)(x.bh + (kb * NB + col) * 8 + 4 * c) : 0u;
         int cl[4], ch[4];
         mma_u8s8_k32(cl, m0, m1, 0u, 0u, bl, 0u);
         mma_u8s8_k32(ch, m0, m1, 0u, 0u, bh, 0u);
-        const float2 dx = *(const float2*)(x.d + kb * NB + n * 8 + 2 * c);   // columns 2c, 2c+1
+        const float2 dx = *(const float2*)(x.d + kb * NB + (ng0 + n) * 8 + 2 * c);   // columns 2c, 2c+1
         // the high-nibble dots are exact multiples of 16
         acc[n][0] += dx.x * (dd0.x * (float)(ilo[n][0] + (ihi[n][0] >> 4)) - dd0.y * (float)(cl[0] + 128 * ch[0]));
         acc[n][1] += dx.y * (dd0.x * (float)(ilo[n][1] + (ihi[n][1] >> 4)) - dd0.y * (float)(cl[1] + 128 * ch[1]));
@@ -309,10 +313,10 @@ __device__ __forceinline__ void q4k_block_mma(const uint8_t* blk0, const uint8_t
 }
 
 // Q6_K super-block: 16 scale groups of 16 elements, one m16n8k16 MMA each; weights as signed q - 32
-template <int NG>
-__device__ __forceinline__ void q6k_block_mma(const uint8_t* blk0, const uint8_t* blk1, int kb, const ActChunk<8 * NG>& x, int g, int c,
-                                              float (&acc)[NG][4]) {
-    constexpr int NB = 8 * NG;
+template <int NGL, int NB>
+__device__ __forceinline__ void q6k_block_mma(const uint8_t* blk0, const uint8_t* blk1, int kb, const ActChunk<NB>& x, int ng0, int g, int c,
+                                              float (&acc)[NGL][4]) {
+    constexpr int NG = NGL;
     uint32_t sw0[4], sw1[4];   // the 16 int8 scales of each row
 #pragma unroll
     for (int i = 0; i < 4; i++) {
@@ -345,7 +349,7 @@ __device__ __forceinline__ void q6k_block_mma(const uint8_t* blk0, const uint8_t
                 const int kofs = 128 * h + 32 * j + 16 * is + 4 * c;
 #pragma unroll
                 for (int n = 0; n < NG; n++) {
-                    const uint32_t xw = *(const uint32_t*)(x.q + (size_t)(n * 8 + g) * GEMM_Q_PITCH + kb * 256 + kofs);
+                    const uint32_t xw = *(const uint32_t*)(x.q + (size_t)((ng0 + n) * 8 + g) * GEMM_Q_PITCH + kb * 256 + kofs);
                     int d4[4];
                     mma_s8s8_k16(d4, a0, a1, xw);
                     isum[n][0] += sc0 * d4[0]; isum[n][1] += sc0 * d4[1]; isum[n][2] += sc1 * d4[2]; isum[n][3] += sc1 * d4[3];
@@ -355,7 +359,7 @@ __device__ __forceinline__ void q6k_block_mma(const uint8_t* blk0, const uint8_t
     const float d0 = h2f_bits(*(const uint16_t*)(blk0 + 208)), d1 = h2f_bits(*(const uint16_t*)(blk1 + 208));
 #pragma unroll
     for (int n = 0; n < NG; n++) {
-        const float2 dx = *(const float2*)(x.d + kb * NB + n * 8 + 2 * c);
+        const float2 dx = *(const float2*)(x.d + kb * NB + (ng0 + n) * 8 + 2 * c);
         acc[n][0] += dx.x * (d0 * (float)isum[n][0]);
         acc[n][1] += dx.y * (d0 * (float)isum[n][1]);
         acc[n][2] += dx.x * (d1 * (float)isum[n][2]);
@@ -379,20 +383,20 @@ __device__ __forceinline__ void mma_s8s8_k32(int (&d)[4], uint32_t a0, uint32_t 
                  : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
 }
-template <int NG>
-__device__ __forceinline__ void q80_block_mma(const uint8_t* blk0, const uint8_t* blk1, int kb, const ActChunk80<8 * NG>& x, int g, int c,
-                                              float (&acc)[NG][4]) {
-    constexpr int NB = 8 * NG;
+template <int NGL, int NB>
+__device__ __forceinline__ void q80_block_mma(const uint8_t* blk0, const uint8_t* blk1, int kb, const ActChunk80<NB>& x, int ng0, int g, int c,
+                                              float (&acc)[NGL][4]) {
+    constexpr int NG = NGL;
     // bytes 8c .. 8c+7 of the block's 32 values (k permuted as in the K-quant path)
     const uint32_t a0 = lds32_a2(blk0 + 2 + 8 * c), a2 = lds32_a2(blk0 + 6 + 8 * c);
     const uint32_t a1 = lds32_a2(blk1 + 2 + 8 * c), a3 = lds32_a2(blk1 + 6 + 8 * c);
     const float d0 = h2f_bits(*(const uint16_t*)blk0), d1 = h2f_bits(*(const uint16_t*)blk1);
 #pragma unroll
     for (int n = 0; n < NG; n++) {
-        const uint2 xb = *(const uint2*)(x.q + (size_t)(n * 8 + g) * GEMM80_Q_PITCH + kb * 32 + 8 * c);
+        const uint2 xb = *(const uint2*)(x.q + (size_t)((ng0 + n) * 8 + g) * GEMM80_Q_PITCH + kb * 32 + 8 * c);
         int d4[4];
         mma_s8s8_k32(d4, a0, a1, a2, a3, xb.x, xb.y);
-        const float2 dx = *(const float2*)(x.d + kb * NB + n * 8 + 2 * c);
+        const float2 dx = *(const float2*)(x.d + kb * NB + (ng0 + n) * 8 + 2 * c);
         // ggml: sumi * (d_w * d_x)
         acc[n][0] += (float)d4[0] * (d0 * dx.x);
         acc[n][1] += (float)d4[1] * (d0 * dx.y);
@@ -454,7 +458,7 @@ __device__ __forceinline__ void epilogue_col(const GemmArgs& a, const GemvSeg& s
 }
 
 template <int NG, int FMT>
-__global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(const __grid_constant__ GemmArgs a) {
+__global__ void __launch_bounds__((Geo<NG, FMT>::THREADS), NG == 1 ? 2 : 1) gemm_kernel(const __grid_constant__ GemmArgs a) {
     using G = Geo<NG, FMT>;
     constexpr int NB = G::NB;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -473,10 +477,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
         for (int s = 0; s < G::STAGES; s++) {
             mbar_init(&full[s], 1);
             mbar_init(&ready[s], 1);
-            mbar_init(&empty[s], NCW);
+            mbar_init(&empty[s], G::NCWT);
         }
         for (int i = 0; i < 2; i++) {
-            mbar_init(&part_full[i], NCW);
+            mbar_init(&part_full[i], G::NCWT);
             mbar_init(&part_free[i], 1);
         }
         mbar_fence_init();
@@ -487,7 +491,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
     const int nblk_row = K / G::BLK;
     const int n_chunks = (nblk_row + G::CB - 1) / G::CB;
 
-    if (warp == W_PRODUCER) {
+    if (warp == G::NCWT) {   // producer
         int stage = 0, phase = 0, si = 0;
         const uint64_t stream_policy = l2_policy_evict_first();
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
@@ -528,7 +532,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
         return;
     }
 
-    if (warp == W_DECODER) {
+    if (warp == G::NCWT + 1) {   // header decoder
         int stage = 0, phase = 0, si = 0;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
             while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
@@ -550,7 +554,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
         return;
     }
 
-    if (warp == W_EPILOGUE) {
+    if (warp == G::NCWT + 2) {   // epilogue
         // lane (p = lane / 4, cq = lane % 4) finishes row pair p of the tile for columns n * 8 + 2 cq, + 1
         const int p_in = lane >> 2, cq = lane & 3;
         int pos[NG][2], slot[NG][2];
@@ -600,58 +604,60 @@ __global__ void __launch_bounds__(GEMM_THREADS, NG == 1 ? 2 : 1) gemm_kernel(con
         return;
     }
 
-    // ===== compute warps: warp w owns super-block w of every chunk =====
+    // ===== compute warps: warp wb of a group owns super-block wb of every chunk; group grp its share of the columns =====
+    constexpr int NGL = G::NGL;
     const int g = lane >> 2, c = lane & 3;
+    const int grp = warp / NCW, wb = warp % NCW, ng0 = grp * NGL;
     int stage = 0, phase = 0, parity = 0, fph = 3, si = 0;
     for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
         while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
         const GemvSeg& s = a.seg[si];
         const int type = s.type;
         const int bb = block_bytes_of(type);
-        // row segment offset inside its slot (source address mod 16; chunks are multiples of 16 bytes for both types)
+        // row segment offset inside its slot (source address mod 16; chunks are multiples of 16 bytes for all types)
         uint32_t off0 = 0, off1 = 0;
         if (type != B2_TYPE_Q4_K) {
             off0 = (uint32_t)((uintptr_t)slot_row_ptr16(s, tile - s.tile0, g, nblk_row * bb) & 15);
             off1 = (uint32_t)((uintptr_t)slot_row_ptr16(s, tile - s.tile0, g + 8, nblk_row * bb) & 15);
         }
-        float acc[NG][4];
+        float acc[NGL][4];
 #pragma unroll
-        for (int n = 0; n < NG; n++)
+        for (int n = 0; n < NGL; n++)
 #pragma unroll
             for (int j = 0; j < 4; j++) acc[n][j] = 0.0f;
         for (int ch = 0; ch < n_chunks; ch++) {
             const int nb = min(G::CB, nblk_row - ch * G::CB);
             mbar_wait(&ready[stage], phase);
-            if (warp < nb) {
+            if (wb < nb) {
                 const uint8_t* st = ring + stage * G::STAGE_BYTES;
-                const uint8_t* row0 = st + g * ROW_SLOT + off0 + warp * bb;
-                const uint8_t* row1 = st + (g + 8) * ROW_SLOT + off1 + warp * bb;
+                const uint8_t* row0 = st + g * ROW_SLOT + off0 + wb * bb;
+                const uint8_t* row1 = st + (g + 8) * ROW_SLOT + off1 + wb * bb;
                 if (FMT == ACT_Q8K) {
                     const ActChunk<NB> x(st + W_STAGE);
                     if (type == B2_TYPE_Q4_K) {
                         const uint8_t* dr = dec + stage * DEC_BYTES;
-                        q4k_block_mma<NG>(row0, row1, dr + g * DEC_ROW + warp * 32, dr + (g + 8) * DEC_ROW + warp * 32, warp, x, g, c, acc);
+                        q4k_block_mma<NGL, NB>(row0, row1, dr + g * DEC_ROW + wb * 32, dr + (g + 8) * DEC_ROW + wb * 32, wb, x, ng0, g, c, acc);
                     } else {
-                        q6k_block_mma<NG>(row0, row1, warp, x, g, c, acc);
+                        q6k_block_mma<NGL, NB>(row0, row1, wb, x, ng0, g, c, acc);
                     }
                 } else {
-                    // 32 blocks of 32 per chunk: warp w takes blocks w, w + 8, w + 16, w + 24
+                    // 32 blocks of 32 per chunk: warp wb takes blocks wb, wb + 8, wb + 16, wb + 24
                     const ActChunk80<NB> x(st + W_STAGE);
-                    for (int kb = warp; kb < nb; kb += NCW) q80_block_mma<NG>(row0 + (kb - warp) * 34, row1 + (kb - warp) * 34, kb, x, g, c, acc);
+                    for (int kb = wb; kb < nb; kb += NCW) q80_block_mma<NGL, NB>(row0 + (kb - wb) * 34, row1 + (kb - wb) * 34, kb, x, ng0, g, c, acc);
                 }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (++stage == G::STAGES) { stage = 0; phase ^= 1; }
         }
-        // hand this warp's share of the tile (16 rows x NB columns) to the epilogue warp
+        // hand this warp's share of the tile (16 rows x its columns) to the epilogue warp
         mbar_wait(&part_free[parity], (fph >> parity) & 1);
         fph ^= 1 << parity;
-        float* rp = red + (G::RED_BUFS == 2 ? parity : 0) * G::RED_FLOATS + warp * GEMM_TILE_ROWS * NB;
+        float* rp = red + (G::RED_BUFS == 2 ? parity : 0) * G::RED_FLOATS + wb * GEMM_TILE_ROWS * NB;
 #pragma unroll
-        for (int n = 0; n < NG; n++) {
-            *(float2*)(rp + g * NB + n * 8 + 2 * c) = make_float2(acc[n][0], acc[n][1]);
-            *(float2*)(rp + (g + 8) * NB + n * 8 + 2 * c) = make_float2(acc[n][2], acc[n][3]);
+        for (int n = 0; n < NGL; n++) {
+            *(float2*)(rp + g * NB + (ng0 + n) * 8 + 2 * c) = make_float2(acc[n][0], acc[n][1]);
+            *(float2*)(rp + (g + 8) * NB + (ng0 + n) * 8 + 2 * c) = make_float2(acc[n][2], acc[n][3]);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&part_full[parity]);
@@ -678,7 +684,7 @@ int launch_gemm_ng(const GemmArgs& a, cudaStream_t st) {
     }
     const int ctas = g_gemm_sms * (NG == 1 ? 2 : 1);
     const int grid = a.n_tiles < ctas ? a.n_tiles : ctas;
-    gemm_kernel<NG, FMT><<<grid, GEMM_THREADS, smem, st>>>(a);
+    gemm_kernel<NG, FMT><<<grid, Geo<NG, FMT>::THREADS, smem, st>>>(a);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
