@@ -76,6 +76,16 @@ __device__ __forceinline__ void dsmem_st_v2(uint32_t addr, uint32_t a, uint32_t 
 __device__ __forceinline__ void dsmem_st_f64(uint32_t addr, double v) {
     asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
 }
+// Asynchronous store into a peer CTA's shared memory that reports its bytes to an mbarrier there
+// (complete_tx), like a bulk copy: the receiver's wait on the barrier makes the data visible, so the
+// sender needs neither a cluster fence nor a separate arrival.
+__device__ __forceinline__ void dsmem_st_async_b32(uint32_t addr, uint32_t v, uint32_t mbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(addr), "r"(v), "r"(mbar) : "memory");
+}
+__device__ __forceinline__ void dsmem_st_async_v2(uint32_t addr, uint32_t a, uint32_t b, uint32_t mbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(addr), "r"(a), "r"(b), "r"(mbar)
+                 : "memory");
+}
 __device__ __forceinline__ void fence_cluster() { asm volatile("fence.acq_rel.cluster;" ::: "memory"); }
 // arrive on an mbarrier that lives in another CTA of the cluster, releasing this thread's prior writes
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {

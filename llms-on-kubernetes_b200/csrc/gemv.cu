@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
         mbar_init(&part_full[1], NCW);
         mbar_init(&part_free[0], 1);
         mbar_init(&part_free[1], 1);
-        mbar_init(sm.xbar, csize * NCW);    // one arrival per compute warp of every CTA of the cluster
+        mbar_init(sm.xbar, 1);    // one local arrival announcing the bytes the cluster will store (build_activation)
         mbar_fence_init();
     }
     // peers store into this CTA's shared memory and arrive on its barriers: they must be initialised first
@@ -304,13 +304,13 @@ int launch_gemv(const GemvArgs& a, int act, cudaStream_t st, bool pdl) {
     cfg.stream = st;
     cudaLaunchAttribute attr[2];
     int na = 0;
-    if (cluster > 1) {
-        attr[na].id = cudaLaunchAttributeClusterDimension;
-        attr[na].val.clusterDim.x = cluster;
-        attr[na].val.clusterDim.y = 1;
-        attr[na].val.clusterDim.z = 1;
-        na++;
-    }
+    // always a cluster launch, even of one CTA: the activation exchange uses st.async, which is a cluster instruction
+    // (measured: cudaErrorIllegalInstruction in a launch without the attribute)
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cluster;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    na++;
     int max_clusters = want / cluster;
     if (cluster > 1) {
         // cached per (activation format, cluster size, shared-memory size)

@@ -298,32 +298,36 @@ __device__ __forceinline__ void quantise_span(const float (&v)[8], int base, int
     }
     const uint32_t pk0 = (uint32_t)(q[0] & 0xff) | ((uint32_t)(q[1] & 0xff) << 8) | ((uint32_t)(q[2] & 0xff) << 16) | ((uint32_t)(q[3] & 0xff) << 24);
     const uint32_t pk1 = (uint32_t)(q[4] & 0xff) | ((uint32_t)(q[5] & 0xff) << 8) | ((uint32_t)(q[6] & 0xff) << 16) | ((uint32_t)(q[7] & 0xff) << 24);
+    // the 16-bit sums travel in pairs (asynchronous stores are 4 bytes at least): sums of 16 of lanes l, l+2; sums of 32 of lanes l, l+4
+    const uint32_t p16 = ((uint32_t)s16 & 0xffffu) | ((uint32_t)__shfl_down_sync(0xffffffffu, s16, 2) << 16);
+    const uint32_t p32 = ((uint32_t)s32 & 0xffffu) | ((uint32_t)__shfl_down_sync(0xffffffffu, s32, 4) << 16);
     if (i0 < K) {
         const int qpos = ACT == ACT_Q8K ? base + 16 * xswz(lane >> 1) + 8 * (lane & 1) : i0;
         const uint32_t o_q = (uint32_t)((const uint8_t*)(sm.xq + qpos) - smem_base);
         const uint32_t o_d = (uint32_t)((const uint8_t*)(sm.xd + (ACT == ACT_Q8K ? (base >> 8) : (i0 >> 5))) - smem_base);
         const uint32_t o_16 = (uint32_t)((const uint8_t*)(sm.bs16 + (i0 >> 4)) - smem_base);
         const uint32_t o_32 = (uint32_t)((const uint8_t*)(sm.bs32 + (i0 >> 5)) - smem_base);
+        const uint32_t o_bar = (uint32_t)((const uint8_t*)sm.xbar - smem_base);
+        // every byte is reported to the receiving CTA's barrier (activation_bytes() of them complete its phase)
         for (uint32_t r = 0; r < csize; r++) {
             const uint32_t pb = dsmem_addr(smem_base, r);
-            dsmem_st_v2(pb + o_q, pk0, pk1);
+            const uint32_t bar = pb + o_bar;
+            dsmem_st_async_v2(pb + o_q, pk0, pk1, bar);
             if (ACT == ACT_Q8K) {
-                if ((lane & 1) == 0) dsmem_st_u16(pb + o_16, (uint16_t)(int16_t)s16);
-                if ((lane & 3) == 0) dsmem_st_u16(pb + o_32, (uint16_t)(int16_t)s32);
-                if (lane == 0) dsmem_st_u32(pb + o_d, __float_as_uint(d));
+                if ((lane & 3) == 0) dsmem_st_async_b32(pb + o_16, p16, bar);
+                if ((lane & 7) == 0) dsmem_st_async_b32(pb + o_32, p32, bar);
+                if (lane == 0) dsmem_st_async_b32(pb + o_d, __float_as_uint(d), bar);
             } else {
-                if ((lane & 3) == 0) dsmem_st_u32(pb + o_d, __float_as_uint(d));
+                if ((lane & 3) == 0) dsmem_st_async_b32(pb + o_d, __float_as_uint(d), bar);
             }
         }
     }
 }
 
-// every warp of every CTA arrives exactly once per phase on each peer's barrier (so the expected count,
-// csize * NCW, does not depend on K and the barrier can be reused by the next mat-vec of a persistent kernel)
-__device__ __forceinline__ void publish_to_cluster(uint64_t* bar, int lane, uint32_t csize) {
-    fence_cluster();   // every lane's DSMEM stores ...
-    __syncwarp();      // ... are ordered before the arrivals below
-    if (lane < (int)csize) mbar_arrive_remote(dsmem_addr(bar, (uint32_t)lane));
+// bytes one activation vector occupies in a CTA's shared memory = what its barrier waits for per phase
+template <int ACT>
+__device__ __forceinline__ uint32_t activation_bytes(int K) {
+    return ACT == ACT_Q8K ? (uint32_t)(K + (K >> 8) * 4 + (K >> 4) * 2 + (K >> 5) * 2) : (uint32_t)(K + (K >> 5) * 4);
 }
 
 // parity: phase of xbar to wait for (0 for a kernel that builds one activation vector).
@@ -396,9 +400,11 @@ __device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uin
         }
     }
     if (tr && tid == 0) tr[6] = globaltimer_ns();
-    publish_to_cluster(sm.xbar, lane, csize);
+    // the barrier's phase completes when this CTA's copy is whole: one local arrival that announces the byte count
+    // (stores of faster peers may already have been counted: the transaction count is signed)
+    if (tid == 0) mbar_arrive_expect_tx(sm.xbar, activation_bytes<ACT>(K));
     if (tr && tid == 0) tr[7] = globaltimer_ns();
-    mbar_wait_cluster(sm.xbar, parity);
+    mbar_wait(sm.xbar, parity);
 }
 
 // ------------------------------------------------------------------------------------------------

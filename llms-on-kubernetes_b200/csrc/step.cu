@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
         mbar_init(&part_full[1], NCW);
         mbar_init(&part_free[0], 1);
         mbar_init(&part_free[1], 1);
-        mbar_init(sm.xbar, csize * NCW);
+        mbar_init(sm.xbar, 1);
         ss.aux[2] = 0;   // cta_stage: the last grid-barrier stage number this CTA has seen complete
         mbar_fence_init();
     }
