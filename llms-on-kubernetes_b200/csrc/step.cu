@@ -229,6 +229,59 @@ __device__ __noinline__ void argmax_stage(const StepOp& op, uint8_t* xbase, int 
     }
 }
 
+// a compute warp's position in the weight ring and the partial-sum hand-off, carried from tile to tile and stage to stage
+struct TileWalk {
+    uint8_t *ring, *dec;
+    float* red;
+    uint64_t *ready, *empty, *part_full, *part_free;
+    int stage, phase, parity, fph;
+    long long cyc_ready, cyc_dot, cyc_free;   // B2_STEP_TRACE
+};
+
+// The tiles of one segment that belong to this CTA (tile, tile + grid, ... < tile_end), for a weight type known at
+// compile time: nothing in the loop depends on the segment but the row-alignment offsets of the 2-byte-aligned types.
+template <int ACT, int TYPE>
+__device__ __forceinline__ void segment_tiles(const GemvSeg& s, int& tile, int tile_end, int nblk_row, int n_chunks, const ActView& xv,
+                                              int warp, int lane, TileWalk& w, bool tracing) {
+    using G = Geo<ACT>;
+    constexpr int bb = TYPE == B2_TYPE_Q4_K ? 144 : TYPE == B2_TYPE_Q5_K ? 176 : TYPE == B2_TYPE_Q6_K ? 210 : 34;
+    constexpr bool unaligned = TYPE == B2_TYPE_Q6_K || TYPE == B2_TYPE_Q8_0;
+    constexpr uint32_t chunk_step = (uint32_t)(G::CHUNK_BLOCKS * bb) & 15;
+    const int r = lane >> 2;
+    const int step = (int)gridDim.x;
+    for (; tile < tile_end; tile += step) {
+        uint32_t off0 = 0;
+        if (unaligned) off0 = (uint32_t)((uintptr_t)slot_row_ptr(s, tile - s.tile0, r, nblk_row * bb) & 15);
+        float acc = 0.0f;
+        for (int c = 0; c < n_chunks; c++) {
+            const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
+            const long long c0 = tracing ? clock64() : 0;
+            mbar_wait(&w.ready[w.stage], w.phase);
+            const long long c1 = tracing ? clock64() : 0;
+            const uint8_t* row = w.ring + w.stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
+            acc += dot_chunk<ACT>(TYPE, row, w.dec + w.stage * G::DEC_BYTES + r * G::DEC_ROW, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&w.empty[w.stage]);
+            if (tracing) {
+                const long long c2 = clock64();
+                w.cyc_ready += c1 - c0;
+                w.cyc_dot += c2 - c1 + (__float_as_uint(acc) == 0x7fc0dead ? 1 : 0);
+            }
+            if (++w.stage == GEMV_STAGES) { w.stage = 0; w.phase ^= 1; }
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        const long long c3 = tracing ? clock64() : 0;
+        mbar_wait(&w.part_free[w.parity], (w.fph >> w.parity) & 1);
+        if (tracing) w.cyc_free += clock64() - c3;
+        w.fph ^= 1 << w.parity;
+        if ((lane & 3) == 0) w.red[(w.parity * NCW + warp) * TILE_ROWS + r] = acc;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&w.part_full[w.parity]);
+        w.parity ^= 1;
+    }
+}
+
 template <int ACT>
 __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_constant__ StepProgram P) {
     using G = Geo<ACT>;
@@ -414,51 +467,29 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};
             const int nblk_row = K / (ACT == ACT_Q8K ? 256 : 32);
             const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
-            int si = 0;
-            // B2_STEP_TRACE: cycles warp 0 of CTA 0 spends waiting for data / in the dot products / waiting for the
-            // epilogue warp, summed over the stage's tiles (marks 4..6 of the trace)
+            // this CTA's tiles, segment by segment (a segment has one weight type: the tile loop is specialised for it)
+            TileWalk tw{ring, dec, red, ready, empty, part_full, part_free, stage, phase, parity, fph, 0, 0, 0};
             const bool tracing = P.trace && blockIdx.x == 0 && tid == 0;
-            long long cyc_ready = 0, cyc_dot = 0, cyc_free = 0;
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
-                while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
+            int tile = blockIdx.x;
+            for (int si = 0; si < a.n_seg; si++) {
                 const GemvSeg& s = a.seg[si];
-                const int type = s.type;
-                const int bb = block_bytes_of(type);
-                uint32_t off0 = 0;
-                if (ACT != ACT_Q8K || type == B2_TYPE_Q6_K) off0 = (uint32_t)((uintptr_t)slot_row_ptr(s, tile - s.tile0, r, nblk_row * bb) & 15);
-                const uint32_t chunk_step = (uint32_t)(G::CHUNK_BLOCKS * bb) & 15;
-                float acc = 0.0f;
-                for (int c = 0; c < n_chunks; c++) {
-                    const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
-                    const long long c0 = tracing ? clock64() : 0;
-                    mbar_wait(&ready[stage], phase);
-                    const long long c1 = tracing ? clock64() : 0;
-                    const uint8_t* row = ring + stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
-                    acc += dot_chunk<ACT>(type, row, dec + stage * G::DEC_BYTES + r * G::DEC_ROW, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&empty[stage]);
-                    if (tracing) {
-                        const long long c2 = clock64();
-                        cyc_ready += c1 - c0;
-                        cyc_dot += c2 - c1 + (__float_as_uint(acc) == 0x7fc0dead ? 1 : 0);
-                    }
-                    if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
+                const int tile_end = si + 1 < a.n_seg ? a.seg[si + 1].tile0 : a.n_tiles;
+                if (tile >= tile_end) continue;
+                if constexpr (ACT == ACT_Q8K) {
+                    if (s.type == B2_TYPE_Q4_K) segment_tiles<ACT, B2_TYPE_Q4_K>(s, tile, tile_end, nblk_row, n_chunks, xv, warp, lane, tw, tracing);
+                    else if (s.type == B2_TYPE_Q6_K) segment_tiles<ACT, B2_TYPE_Q6_K>(s, tile, tile_end, nblk_row, n_chunks, xv, warp, lane, tw, tracing);
+                    else segment_tiles<ACT, B2_TYPE_Q5_K>(s, tile, tile_end, nblk_row, n_chunks, xv, warp, lane, tw, tracing);
+                } else {
+                    segment_tiles<ACT, B2_TYPE_Q8_0>(s, tile, tile_end, nblk_row, n_chunks, xv, warp, lane, tw, tracing);
                 }
-                acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-                acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-                const long long c3 = tracing ? clock64() : 0;
-                mbar_wait(&part_free[parity], (fph >> parity) & 1);
-                if (tracing) cyc_free += clock64() - c3;
-                fph ^= 1 << parity;
-                if ((lane & 3) == 0) red[(parity * NCW + warp) * TILE_ROWS + r] = acc;
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&part_full[parity]);
             }
+            stage = tw.stage; phase = tw.phase; parity = tw.parity; fph = tw.fph;
             if (tracing) {
+                // cycles warp 0 of CTA 0 spent waiting for data / in the dot products / waiting for the epilogue warp (marks 4..6)
                 unsigned long long* tr = P.trace + oi * STEP_TRACE_SLOTS;
-                tr[4] = tr[0] + (unsigned long long)(cyc_ready * 1000 / 1965);
-                tr[5] = tr[0] + (unsigned long long)(cyc_dot * 1000 / 1965);
-                tr[6] = tr[0] + (unsigned long long)(cyc_free * 1000 / 1965);
+                tr[4] = tr[0] + (unsigned long long)(tw.cyc_ready * 1000 / 1965);
+                tr[5] = tr[0] + (unsigned long long)(tw.cyc_dot * 1000 / 1965);
+                tr[6] = tr[0] + (unsigned long long)(tw.cyc_free * 1000 / 1965);
             }
             if (tid == 0) stamp(P, oi, 2);
             // the epilogue warp arrives on the grid barrier for this stage
