@@ -543,7 +543,8 @@ __global__ void __launch_bounds__((Geo<NG, FMT>::THREADS), NG == 1 ? 2 : 1) gemm
                 if (type == B2_TYPE_Q4_K) {
                     for (int i = lane; i < GEMM_TILE_ROWS * nb; i += 32) {
                         const int rr = i / nb, b = i - rr * nb;
-                        decode_k4_header(ring + stage * G::STAGE_BYTES + rr * ROW_SLOT + b * 144, dec + stage * DEC_BYTES + rr * DEC_ROW + b * 32);
+                        uint8_t* rec = dec + stage * DEC_BYTES + rr * DEC_ROW + b * 32;
+                        decode_k4_header(ring + stage * G::STAGE_BYTES + rr * ROW_SLOT + b * 144, rec, rec + 16);
                     }
                 }
                 __syncwarp();

@@ -135,8 +135,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
                     // Q4_K / Q5_K rows are 16-byte aligned in their slots
                     for (int i = lane; i < TILE_ROWS * nb; i += 32) {
                         const int rr = i / nb, b = i - rr * nb;
-                        decode_k4_header(ring + stage * G::STAGE_BYTES + rr * G::ROW_SLOT + b * bb,
-                                         dec + stage * G::DEC_BYTES + rr * G::DEC_ROW + b * 32);
+                        uint8_t* rec = dec + stage * G::DEC_BYTES + rr * G::DEC_ROW + b * 32;   // {d, dmin, pad, scale words}
+                        decode_k4_header(ring + stage * G::STAGE_BYTES + rr * G::ROW_SLOT + b * bb, rec, rec + 16);
                     }
                 }
                 __syncwarp();
@@ -185,7 +185,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const __grid_cons
             const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
             mbar_wait(&ready[stage], phase);
             const uint8_t* row = ring + stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
-            acc += dot_chunk<ACT>(type, row, dec + stage * G::DEC_BYTES + r * G::DEC_ROW, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
+            const uint8_t* drow = dec + stage * G::DEC_BYTES + r * G::DEC_ROW;
+            acc += dot_chunk<ACT>(type, row, DecPtr{drow, drow + 16}, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);
             if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }

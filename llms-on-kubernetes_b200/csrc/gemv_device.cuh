@@ -33,7 +33,12 @@ struct Geo {
 __device__ __forceinline__ int xswz(int g) { return g ^ ((g & 8) >> 2); }
 
 // decoded header record: {float d, float dmin, pad, pad, w[4]} with w[c] = bytes (sc[2c], sc[2c+1], m[2c], m[2c+1])
-__device__ __forceinline__ void decode_k4_header(const uint8_t* blk, uint8_t* rec) {
+// the decoded header of one (row, block): (d, dmin) as a float2 and the four scale words; kernels choose where they live
+struct DecPtr {
+    const uint8_t* dd;
+    const uint8_t* w;
+};
+__device__ __forceinline__ void decode_k4_header(const uint8_t* blk, uint8_t* dd_out, uint8_t* w_out) {
     const uint4 hdr = *(const uint4*)blk;
     const uint32_t sc_lo = hdr.y & 0x3f3f3f3fu, m_lo = hdr.z & 0x3f3f3f3fu;
     const uint32_t sc_hi = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
@@ -43,8 +48,8 @@ __device__ __forceinline__ void decode_k4_header(const uint8_t* blk, uint8_t* re
     w.y = __byte_perm(sc_lo, m_lo, 0x7632);
     w.z = __byte_perm(sc_hi, m_hi, 0x5410);
     w.w = __byte_perm(sc_hi, m_hi, 0x7632);
-    *(float2*)rec = make_float2(h2f_bits(hdr.x & 0xffffu), h2f_bits(hdr.x >> 16));
-    *(uint4*)(rec + 16) = w;
+    *(float2*)dd_out = make_float2(h2f_bits(hdr.x & 0xffffu), h2f_bits(hdr.x >> 16));
+    *(uint4*)w_out = w;
 }
 
 __host__ __device__ inline int block_bytes_of(int type) {
@@ -98,15 +103,15 @@ struct ActView {
 // ------------------------------------------------------------------------------------------------
 // Q4_K quarter c: qs[32c .. 32c+31]; low nibbles are sub-block 2c, high nibbles sub-block 2c+1.
 // rec = the decoded header record of this (row, block).
-__device__ __forceinline__ float k4_finish(const uint8_t* rec, int c, int dlo, int dhi, uint32_t bs2, float dx) {
-    const float2 dd = *(const float2*)rec;
-    const uint32_t w = *(const uint32_t*)(rec + 16 + 4 * c);
+__device__ __forceinline__ float k4_finish(const DecPtr rec, int c, int dlo, int dhi, uint32_t bs2, float dx) {
+    const float2 dd = *(const float2*)rec.dd;
+    const uint32_t w = *(const uint32_t*)(rec.w + 4 * c);
     const int isum = (int)(w & 0xffu) * dlo + (int)((w >> 8) & 0xffu) * dhi;
     const int msum = (int)((w >> 16) & 0xffu) * (int)(int16_t)(bs2 & 0xffffu) + (int)(w >> 24) * ((int)bs2 >> 16);
     return dx * (dd.x * (float)isum - dd.y * (float)msum);
 }
 
-__device__ __forceinline__ float q4k_quarter(const uint8_t* blk, const uint8_t* rec, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
+__device__ __forceinline__ float q4k_quarter(const uint8_t* blk, const DecPtr rec, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
     const uint4 q0 = *(const uint4*)(blk + 16 + 32 * c), q1 = *(const uint4*)(blk + 32 + 32 * c);
     // four independent accumulation chains
     int l0 = dp4a_ss(q0.x & 0x0F0F0F0Fu, xv[0].x, 0), h0 = dp4a_us(q0.x & 0xF0F0F0F0u, xv[2].x, 0);
@@ -122,7 +127,7 @@ __device__ __forceinline__ float q4k_quarter(const uint8_t* blk, const uint8_t* 
 }
 
 // Q5_K quarter c: as Q4_K plus bit 2c / 2c+1 of qh[0..31] as the fifth bit.
-__device__ __forceinline__ float q5k_quarter(const uint8_t* blk, const uint8_t* rec, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
+__device__ __forceinline__ float q5k_quarter(const uint8_t* blk, const DecPtr rec, int c, const uint4 (&xv)[4], uint32_t bs2, float dx) {
     const uint4 h0 = *(const uint4*)(blk + 16), h1 = *(const uint4*)(blk + 32);
     const uint4 q0 = *(const uint4*)(blk + 48 + 32 * c), q1 = *(const uint4*)(blk + 64 + 32 * c);
     const int s0 = 2 * c, s1 = 2 * c + 1;
@@ -176,8 +181,9 @@ __device__ __forceinline__ float q80_block(const uint8_t* blk, const uint4& x0, 
 }
 
 // one warp's share of a K-chunk for the tile's 8 rows; `row` = this lane's row segment in the ring
-template <int ACT>
-__device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, const uint8_t* dec_row, int nb, int kb0, const ActView& x,
+// DDS / WS: bytes between consecutive blocks' (d, dmin) pairs / scale words in the row's decoded-header storage
+template <int ACT, int DDS = 32, int WS = 32>
+__device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, const DecPtr dec_row, int nb, int kb0, const ActView& x,
                                            int warp, int lane) {
     float acc = 0.0f;
     if (ACT == ACT_Q8K) {
@@ -204,8 +210,9 @@ __device__ __forceinline__ float dot_chunk(int type, const uint8_t* row, const u
                 xv[2] = *(const uint4*)(xb + 16 * xswz(4 * c + 2));   // sub-block 2c+1
                 xv[3] = *(const uint4*)(xb + 16 * xswz(4 * c + 3));
                 const uint32_t bs2 = *(const uint32_t*)(x.bs32 + kb * 8 + 2 * c);
-                if (type == B2_TYPE_Q4_K) acc += q4k_quarter(row + b * 144, dec_row + b * 32, c, xv, bs2, dx);
-                else acc += q5k_quarter(row + b * 176, dec_row + b * 32, c, xv, bs2, dx);
+                const DecPtr rec{dec_row.dd + b * DDS, dec_row.w + b * WS};
+                if (type == B2_TYPE_Q4_K) acc += q4k_quarter(row + b * 144, rec, c, xv, bs2, dx);
+                else acc += q5k_quarter(row + b * 176, rec, c, xv, bs2, dx);
             }
         }
     } else {

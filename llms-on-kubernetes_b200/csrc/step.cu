@@ -229,12 +229,47 @@ __device__ __noinline__ void argmax_stage(const StepOp& op, uint8_t* xbase, int 
     }
 }
 
+// ---- the weight ring of the persistent kernel ------------------------------------------------------------------
+// One allocation per (tile, K-chunk): 8 row slots whose pitch depends on the weight type, placed back to back in a
+// circular buffer (an allocation that would straddle the end starts at 0 again).  Up to NSLOT allocations are in
+// flight -- four Q4_K tiles (18.6 KB each) or three Q6_K tiles (27 KB): with the tile loop at ~1 us per tile, three
+// Q4_K tiles in flight left the compute warps waiting for data a third of the time.  Producer, decoder and compute
+// warps walk the same sequence of sizes, so their offsets agree without communication; the producer also waits for
+// the release of any older allocation its new one overlaps.
+constexpr int NSLOT = 4;
+template <int ACT>
+struct Ring {
+    static constexpr int CHUNK_BLOCKS = Geo<ACT>::CHUNK_BLOCKS;
+    static constexpr uint32_t BYTES = ACT == ACT_Q8K ? 3 * TILE_ROWS * (16 * 210 + 16) : 4 * TILE_ROWS * (64 * 34 + 16);
+    // decoded Q4_K / Q5_K headers of one slot: (d, dmin) pairs and scale words in separate, bank-padded rows
+    static constexpr int DD_ROW = CHUNK_BLOCKS * 8 + 8, W_ROW = CHUNK_BLOCKS * 16 + 16;
+    static constexpr int DEC_SLOT = ACT == ACT_Q8K ? TILE_ROWS * (DD_ROW + W_ROW) : 0;
+    __host__ __device__ static constexpr uint32_t pitch(int bb) { return (uint32_t)(CHUNK_BLOCKS * bb + 16); }
+};
+struct RingPos {
+    uint32_t off = 0, par = 0;   // par bit s: parity of the next use of slot s
+    int slot = 0;
+    template <int ACT>
+    __device__ __forceinline__ uint32_t place(uint32_t sz) {
+        if (off + sz > Ring<ACT>::BYTES) off = 0;
+        const uint32_t o = off;
+        off += sz;
+        return o;
+    }
+    __device__ __forceinline__ uint32_t parity() const { return (par >> slot) & 1u; }
+    __device__ __forceinline__ void next() {
+        par ^= 1u << slot;
+        slot = (slot + 1) & (NSLOT - 1);
+    }
+};
+
 // a compute warp's position in the weight ring and the partial-sum hand-off, carried from tile to tile and stage to stage
 struct TileWalk {
     uint8_t *ring, *dec;
     float* red;
     uint64_t *ready, *empty, *part_full, *part_free;
-    int stage, phase, parity, fph;
+    RingPos rp;
+    int parity, fph;
     long long cyc_ready, cyc_dot, cyc_free;   // B2_STEP_TRACE
 };
 
@@ -244,9 +279,11 @@ template <int ACT, int TYPE>
 __device__ __forceinline__ void segment_tiles(const GemvSeg& s, int& tile, int tile_end, int nblk_row, int n_chunks, const ActView& xv,
                                               int warp, int lane, TileWalk& w, bool tracing) {
     using G = Geo<ACT>;
+    using R = Ring<ACT>;
     constexpr int bb = TYPE == B2_TYPE_Q4_K ? 144 : TYPE == B2_TYPE_Q5_K ? 176 : TYPE == B2_TYPE_Q6_K ? 210 : 34;
     constexpr bool unaligned = TYPE == B2_TYPE_Q6_K || TYPE == B2_TYPE_Q8_0;
     constexpr uint32_t chunk_step = (uint32_t)(G::CHUNK_BLOCKS * bb) & 15;
+    constexpr uint32_t pitch = R::pitch(bb), tile_bytes = TILE_ROWS * pitch;
     const int r = lane >> 2;
     const int step = (int)gridDim.x;
     for (; tile < tile_end; tile += step) {
@@ -255,19 +292,23 @@ __device__ __forceinline__ void segment_tiles(const GemvSeg& s, int& tile, int t
         float acc = 0.0f;
         for (int c = 0; c < n_chunks; c++) {
             const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
+            const uint32_t o = w.rp.place<ACT>(tile_bytes);
+            const int sl = w.rp.slot;
             const long long c0 = tracing ? clock64() : 0;
-            mbar_wait(&w.ready[w.stage], w.phase);
+            mbar_wait(&w.ready[sl], w.rp.parity());
             const long long c1 = tracing ? clock64() : 0;
-            const uint8_t* row = w.ring + w.stage * G::STAGE_BYTES + r * G::ROW_SLOT + ((off0 + c * chunk_step) & 15);
-            acc += dot_chunk<ACT>(TYPE, row, w.dec + w.stage * G::DEC_BYTES + r * G::DEC_ROW, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
+            const uint8_t* row = w.ring + o + r * pitch + ((off0 + c * chunk_step) & 15);
+            const uint8_t* ds = w.dec + sl * R::DEC_SLOT;
+            const DecPtr drow{ds + r * R::DD_ROW, ds + TILE_ROWS * R::DD_ROW + r * R::W_ROW};
+            acc += dot_chunk<ACT, 8, 16>(TYPE, row, drow, nb, c * G::CHUNK_BLOCKS, xv, warp, lane);
             __syncwarp();
-            if (lane == 0) mbar_arrive(&w.empty[w.stage]);
+            if (lane == 0) mbar_arrive(&w.empty[sl]);
             if (tracing) {
                 const long long c2 = clock64();
                 w.cyc_ready += c1 - c0;
                 w.cyc_dot += c2 - c1 + (__float_as_uint(acc) == 0x7fc0dead ? 1 : 0);
             }
-            if (++w.stage == GEMV_STAGES) { w.stage = 0; w.phase ^= 1; }
+            w.rp.next();
         }
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
@@ -285,17 +326,18 @@ __device__ __forceinline__ void segment_tiles(const GemvSeg& s, int& tile, int t
 template <int ACT>
 __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_constant__ StepProgram P) {
     using G = Geo<ACT>;
+    using R = Ring<ACT>;
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* ring = smem;
-    uint8_t* dec = smem + GEMV_STAGES * G::STAGE_BYTES;
-    uint64_t* full = (uint64_t*)(dec + GEMV_STAGES * G::DEC_BYTES);
-    uint64_t* ready = full + GEMV_STAGES;
-    uint64_t* empty = ready + GEMV_STAGES;
-    uint64_t* part_full = empty + GEMV_STAGES;
+    uint8_t* dec = smem + R::BYTES;
+    uint64_t* full = (uint64_t*)(dec + NSLOT * R::DEC_SLOT);
+    uint64_t* ready = full + NSLOT;
+    uint64_t* empty = ready + NSLOT;
+    uint64_t* part_full = empty + NSLOT;
     uint64_t* part_free = part_full + 2;
     ActSmem sm;
-    sm.xbar = part_free + 2;
-    sm.ss_warp = (double*)(sm.xbar + 3);
+    sm.xbar = part_free + 2;   // 17 barriers; one pad slot keeps the 16-byte alignment below
+    sm.ss_warp = (double*)(sm.xbar + 2);
     float* red = (float*)(sm.ss_warp + NCW);
     StepSmem ss;
     ss.slots = (GemvArgs*)(red + 2 * NCW * TILE_ROWS);
@@ -307,7 +349,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
     const uint32_t rank = cluster_ctarank(), csize = cluster_nctarank();
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < GEMV_STAGES; s++) {
+        for (int s = 0; s < NSLOT; s++) {
             mbar_init(&full[s], 1);
             mbar_init(&ready[s], 1);
             mbar_init(&empty[s], NCW);
@@ -325,7 +367,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
 
     if (warp == W_PRODUCER) {
         // ===== producer: streams every mat-vec stage's weights in program order, never waits for a stage to start =====
-        int stage = 0, phase = 0;
+        RingPos rp;
+        // the last three allocations (they may still be in use): range, slot and the parity of that use of the slot
+        uint32_t h_off[3] = {0, 0, 0}, h_end[3] = {0, 0, 0}, h_par[3] = {0, 0, 0};
+        int h_slot[3] = {0, 0, 0};
         const uint64_t stream_policy = l2_policy_evict_first();
         for (int oi = 0; oi < P.n_ops; oi++) {
             const StepOp& op = P.ops[oi];
@@ -340,6 +385,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                 while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
                 const GemvSeg& s = a.seg[si];
                 const int bb = block_bytes_of(s.type);
+                const uint32_t pitch = R::pitch(bb), tile_bytes = TILE_ROWS * pitch;
                 const uint8_t* rowp = lane < TILE_ROWS ? slot_row_ptr(s, tile - s.tile0, lane, nblk_row * bb) : nullptr;
                 for (int c = 0; c < n_chunks; c++) {
                     const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
@@ -354,13 +400,22 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                     uint32_t total = sz;
 #pragma unroll
                     for (int o = 4; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+                    const uint32_t o = rp.place<ACT>(tile_bytes);
+                    const int sl = rp.slot;
+                    const uint32_t par = rp.parity();
                     if (lane == 0) {
-                        mbar_wait(&empty[stage], phase ^ 1);
-                        mbar_arrive_expect_tx(&full[stage], total);
+                        mbar_wait(&empty[sl], par ^ 1);   // the slot's previous use (four allocations ago) is released
+#pragma unroll
+                        for (int j = 0; j < 3; j++)       // ... and so is any younger allocation these bytes overlap
+                            if (h_end[j] > h_off[j] && o < h_end[j] && h_off[j] < o + tile_bytes) mbar_wait(&empty[h_slot[j]], h_par[j]);
+                        mbar_arrive_expect_tx(&full[sl], total);
                     }
                     __syncwarp();
-                    if (sz) bulk_g2s_hint(ring + stage * G::STAGE_BYTES + lane * G::ROW_SLOT, src, sz, &full[stage], stream_policy);
-                    if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
+                    if (sz) bulk_g2s_hint(ring + o + lane * pitch, src, sz, &full[sl], stream_policy);
+                    h_off[2] = h_off[1]; h_end[2] = h_end[1]; h_slot[2] = h_slot[1]; h_par[2] = h_par[1];
+                    h_off[1] = h_off[0]; h_end[1] = h_end[0]; h_slot[1] = h_slot[0]; h_par[1] = h_par[0];
+                    h_off[0] = o; h_end[0] = o + tile_bytes; h_slot[0] = sl; h_par[0] = par;
+                    rp.next();
                 }
             }
         }
@@ -368,7 +423,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
     }
 
     if (warp == W_DECODER) {
-        int stage = 0, phase = 0;
+        RingPos rp;
         for (int oi = 0; oi < P.n_ops; oi++) {
             const StepOp& op = P.ops[oi];
             if (op.kind != OP_GEMV) continue;
@@ -382,19 +437,23 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                 while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
                 const int type = a.seg[si].type;
                 const int bb = block_bytes_of(type);
+                const uint32_t pitch = R::pitch(bb), tile_bytes = TILE_ROWS * pitch;
                 for (int c = 0; c < n_chunks; c++) {
                     const int nb = min(G::CHUNK_BLOCKS, nblk_row - c * G::CHUNK_BLOCKS);
-                    mbar_wait(&full[stage], phase);
+                    const uint32_t o = rp.place<ACT>(tile_bytes);
+                    const int sl = rp.slot;
+                    mbar_wait(&full[sl], rp.parity());
                     if (ACT == ACT_Q8K && (type == B2_TYPE_Q4_K || type == B2_TYPE_Q5_K)) {
+                        uint8_t* ds = dec + sl * R::DEC_SLOT;
                         for (int i = lane; i < TILE_ROWS * nb; i += 32) {
                             const int rr = i / nb, b = i - rr * nb;
-                            decode_k4_header(ring + stage * G::STAGE_BYTES + rr * G::ROW_SLOT + b * bb,
-                                             dec + stage * G::DEC_BYTES + rr * G::DEC_ROW + b * 32);
+                            decode_k4_header(ring + o + rr * pitch + b * bb, ds + rr * R::DD_ROW + b * 8,
+                                             ds + TILE_ROWS * R::DD_ROW + rr * R::W_ROW + b * 16);
                         }
                     }
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&ready[stage]);
-                    if (++stage == GEMV_STAGES) { stage = 0; phase ^= 1; }
+                    if (lane == 0) mbar_arrive(&ready[sl]);
+                    rp.next();
                 }
             }
         }
@@ -438,7 +497,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
     }
     // ===== compute warps =====
     const int r = lane >> 2;
-    int stage = 0, phase = 0, parity = 0, fph = 3;
+    RingPos rpos;
+    int parity = 0, fph = 3;
     uint32_t xpar = 0;
     for (int oi = 0; oi < P.n_ops; oi++) {
         // warp 0 stages the stage's descriptor (static) while the previous stage is still finishing elsewhere;
@@ -468,7 +528,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             const int nblk_row = K / (ACT == ACT_Q8K ? 256 : 32);
             const int n_chunks = (nblk_row + G::CHUNK_BLOCKS - 1) / G::CHUNK_BLOCKS;
             // this CTA's tiles, segment by segment (a segment has one weight type: the tile loop is specialised for it)
-            TileWalk tw{ring, dec, red, ready, empty, part_full, part_free, stage, phase, parity, fph, 0, 0, 0};
+            TileWalk tw{ring, dec, red, ready, empty, part_full, part_free, rpos, parity, fph, 0, 0, 0};
             const bool tracing = P.trace && blockIdx.x == 0 && tid == 0;
             int tile = blockIdx.x;
             for (int si = 0; si < a.n_seg; si++) {
@@ -483,7 +543,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                     segment_tiles<ACT, B2_TYPE_Q8_0>(s, tile, tile_end, nblk_row, n_chunks, xv, warp, lane, tw, tracing);
                 }
             }
-            stage = tw.stage; phase = tw.phase; parity = tw.parity; fph = tw.fph;
+            rpos = tw.rp; parity = tw.parity; fph = tw.fph;
             if (tracing) {
                 // cycles warp 0 of CTA 0 spent waiting for data / in the dot products / waiting for the epilogue warp (marks 4..6)
                 unsigned long long* tr = P.trace + oi * STEP_TRACE_SLOTS;
@@ -508,7 +568,11 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
 }
 
 size_t step_smem_bytes(int act, int max_k) {
-    size_t n = gemv_smem_bytes(act, max_k) + STEP_EXTRA_SMEM;
+    // ring + decoded headers + 18 barrier slots + RMS partial sums + the tile's partial dot products + the descriptors ...
+    size_t n = (act == ACT_Q8K ? Ring<ACT_Q8K>::BYTES + NSLOT * Ring<ACT_Q8K>::DEC_SLOT : Ring<ACT_Q80>::BYTES) + 18 * sizeof(uint64_t) +
+               NCW * sizeof(double) + 2 * NCW * TILE_ROWS * sizeof(float) + STEP_EXTRA_SMEM;
+    // ... + the quantised activation vector
+    n += (size_t)max_k + (act == ACT_Q8K ? max_k / 256 : max_k / 32) * 4 + max_k / 16 * 2 + max_k / 32 * 2;
     // attention aliases the activation buffers; make sure they are large enough
     const size_t x_bytes = (size_t)max_k + (act == ACT_Q8K ? max_k / 256 : max_k / 32) * 4 + max_k / 16 * 2 + max_k / 32 * 2;
     if (x_bytes < ATTN_SMEM_BYTES) n += ATTN_SMEM_BYTES - x_bytes;
