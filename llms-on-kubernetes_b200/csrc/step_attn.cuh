@@ -75,10 +75,7 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
     const int hh = tid / CPH, tq = tid / CPH, cp = tid % CPH, c0 = cp * EPT;
 
     if (tr && tid == 0) tr[4] = globaltimer_ns();
-    // the first V_PRE of this thread's V values are fetched before the score phase (all of them for n <= 32)
     uint32_t vpre[V_PRE];
-#pragma unroll
-    for (int j = 0; j < V_PRE; j++) vpre[j] = tq + 4 * j < n ? ld_v<EPT>(vbase + (size_t)(tq + 4 * j) * HD + c0) : 0u;
 
     // ---- scores ----
     {
@@ -94,6 +91,10 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
                 for (int i = 0; i < 8; i++) qf[h][i] = __half2float(__float2half_rn(t[i]));
             }
         if (tr && tid == 0) tr[5] = globaltimer_after(__float_as_uint(qf[0][0]));   // q arrived
+        // the first V_PRE of this thread's V values (all of them for n <= 32) are requested once q is here, so that they
+        // travel while the scores are computed without standing between the score phase and its own operands
+#pragma unroll
+        for (int j = 0; j < V_PRE; j++) vpre[j] = tq + 4 * j < n ? ld_v<EPT>(vbase + (size_t)(tq + 4 * j) * HD + c0) : 0u;
         for (int tb = warp * TPW; tb < n; tb += NCW * TPW * 2) {
             const int ta = tb + sub, tc = ta + NCW * TPW;
             uint4 kq[2];
