@@ -93,10 +93,10 @@ static_assert(sizeof(GemvArgs) % 4 == 0 && sizeof(StepOp) % 4 == 0, "descriptor 
 struct StepSmem {
     GemvArgs* slots;   // [3] the current mat-vec descriptor of the producer, decoder and epilogue warps
     StepOp* cslot;     // [2] the compute warps' current / next stage (double-buffered)
-    int* aux;          // [2] per cslot: sequence length of an attention stage
+    int* aux;          // [0..1] per cslot: sequence length of an attention stage; [2] cta_stage; [4 + 8 cslot ..]: its AttnSplit
     uint8_t* xbase;    // activation buffers, re-carved per mat-vec; attention and argmax alias them
 };
-constexpr size_t STEP_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 16 + 16;
+constexpr size_t STEP_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 20 * sizeof(int) + 16;
 
 // ---- the stages that are not mat-vecs, run by the 256 compute threads (kept out of line: their registers
 // ---- must not weigh on the mat-vec loop) --------------------------------------------------------------------
@@ -118,6 +118,10 @@ struct AttnSplit {
         n_chunks = (T + chunk_tokens - 1) / chunk_tokens;
         n_items = n_kv * n_batches * n_chunks;
     }
+    // the integer divisions above cost ~1 us of dependent instructions: one thread does them while the CTA still waits
+    // for the previous stage and leaves the result in shared memory
+    __device__ void store(int* p) const { p[0] = gq; p[1] = n_batches; p[2] = chunk_tokens; p[3] = n_chunks; p[4] = n_items; }
+    __device__ explicit AttnSplit(const int* p) : gq(p[0]), n_batches(p[1]), chunk_tokens(p[2]), n_chunks(p[3]), n_items(p[4]) {}
     __device__ void item(int i, int T, int* kvh, int* h0, int* hb, int* chunk, int* t0, int* n) const {
         *chunk = i % n_chunks;
         *kvh = i / (n_chunks * n_batches);
@@ -128,14 +132,14 @@ struct AttnSplit {
     }
 };
 
-__device__ __noinline__ void attn_stage(const StepOp& op, uint8_t* xbase, int T, int tid, unsigned long long* tr) {
+__device__ __noinline__ void attn_stage(const StepOp& op, uint8_t* xbase, int T, const int* split, int tid, unsigned long long* tr) {
     AttnSmem as;
     as.scores = (float*)xbase;
     as.prob = as.scores + A_MAXG * A_TOK;
     as.part = as.prob + A_MAXG * A_TOK;
     as.ml = as.part + 3 * A_MAXG * 128;
     as.flag = (int*)(as.ml + 2 * A_MAXG);
-    const AttnSplit sp(op.a_n_head, op.a_n_kv, op.a_min_chunk, T);
+    const AttnSplit sp(split);
     if (sp.n_chunks > op.a_max_chunks) asm volatile("trap;");   // scratch is sized for this bound (step_attn_max_chunks)
     for (int item = blockIdx.x; item < sp.n_items; item += gridDim.x) {
         int kvh, h0, hb, chunk, t0, n;
@@ -343,7 +347,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
     ss.slots = (GemvArgs*)(red + 2 * NCW * TILE_ROWS);
     ss.cslot = (StepOp*)(ss.slots + 3);
     ss.aux = (int*)(ss.cslot + 2);
-    ss.xbase = (uint8_t*)(((uintptr_t)(ss.aux + 4) + 15) & ~(uintptr_t)15);
+    ss.xbase = (uint8_t*)(((uintptr_t)(ss.aux + 20) + 15) & ~(uintptr_t)15);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank(), csize = cluster_nctarank();
@@ -506,7 +510,11 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
         StepOp* cs = &ss.cslot[oi & 1];
         if (warp == 0) {
             stage_words(cs, &P.ops[oi], sizeof(StepOp) / 4, lane);
-            if (lane == 0 && cs->kind == OP_ATTN) ss.aux[oi & 1] = *cs->a_pos + 1;
+            if (lane == 0 && cs->kind == OP_ATTN) {
+                const int T = *cs->a_pos + 1;
+                ss.aux[oi & 1] = T;
+                AttnSplit(cs->a_n_head, cs->a_n_kv, cs->a_min_chunk, T).store(ss.aux + 4 + 8 * (oi & 1));
+            }
             if (oi + 1 < P.n_ops) prefetch_next_stage(P.ops[oi + 1], lane);
             // every CTA has arrived oi times per completed stage: wait for the previous stage everywhere
             if (oi > 0 && lane == 0) grid_wait(P.sync_counter, (unsigned int)oi, cta_stage);
@@ -555,7 +563,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             // the epilogue warp arrives on the grid barrier for this stage
         } else {
             if (op.kind == OP_EMBED) embed_stage(op, tid);
-            else if (op.kind == OP_ATTN) attn_stage(op, ss.xbase, ss.aux[oi & 1], tid, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
+            else if (op.kind == OP_ATTN) attn_stage(op, ss.xbase, ss.aux[oi & 1], ss.aux + 4 + 8 * (oi & 1), tid, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
             else if (op.kind == OP_ARGMAX) argmax_stage(op, ss.xbase, tid);
             __threadfence();   // every thread's stores of this stage, before the CTA's single arrival
             named_bar_sync(1, NCT);

@@ -2,8 +2,8 @@
 //
 // Work item = (kv head, batch of <= 4 query heads of its group, chunk of n <= 256 tokens); the chunk length is
 // chosen per step so that the items cover the grid once.  The 256 compute threads of a CTA run one item:
-//   scores : a half warp (hd 128) or quarter warp (hd 64) per token, two tokens in flight per lane, the
-//            K rows read with 16-byte loads; each warp keeps its tokens' dot products of all heads in registers
+//   scores : tensor cores (mma.sync m16n8k16, fp16 x fp16 -> fp32): rows = the query heads, columns = 8 tokens per
+//            warp and step; a lane reads one quarter of its token's K row with 16-byte loads
 //   softmax: the two warps that own a head in the PV phase compute its max and sum from shared memory
 //   P.V    : thread = (token quarter, one or two columns) adds its tokens for all heads; its first eight V
 //            values (all of them for a 32-token chunk) were fetched before the score phase, later ones are
@@ -63,12 +63,11 @@ __device__ __forceinline__ void fma_v(float pr, uint32_t raw, float& a0, float& 
 template <int HD>
 __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, int n_chunks, int t0, int n, const AttnSmem& sm, int tid,
                           unsigned long long* tr) {
-    constexpr int LPT = HD / 8, TPW = 32 / LPT;   // lanes per token, tokens per warp pass
     constexpr int CPH = NCT / A_MAXG;             // PV phase: threads per head (two warps)
     constexpr int EPT = HD / CPH;                 // columns per thread
     static_assert(EPT == 1 || EPT == 2, "head_dim 64 or 128");
     const int gq = op.a_n_head / op.a_n_kv;
-    const int warp = tid >> 5, lane = tid & 31, sub = lane / LPT, ln = lane % LPT;
+    const int warp = tid >> 5, lane = tid & 31;
     const __half* kbase = op.a_k + ((size_t)kvh * op.a_n_ctx + t0) * HD;
     const __half* vbase = op.a_v + ((size_t)kvh * op.a_n_ctx + t0) * HD;
     // softmax / merge role: head hh; P.V role: tokens tq, tq + 4, ... and columns c0 (+1) of every head
@@ -77,51 +76,55 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
     if (tr && tid == 0) tr[4] = globaltimer_ns();
     uint32_t vpre[V_PRE];
 
-    // ---- scores ----
+    // ---- scores on the tensor cores: S[head][token] = q[head] . k[token] ----
+    // mma.sync m16n8k16 (fp16 operands, fp32 accumulate): rows = the item's query heads (rows >= g are zero),
+    // columns = 8 tokens, k = 16 dims per step.  ggml rounds q to fp16 for this product and K is stored fp16, so the
+    // operands are exactly the oracle's.  The dims are permuted so that lane (tk = lane / 4, c = lane % 4) feeds all
+    // HD / 16 steps from one contiguous quarter of its token's row: dims [DPT c, DPT c + DPT).
     {
+        constexpr int NMMA = HD / 16, DPT = HD / 4;
         const float scale = 1.0f / sqrtf((float)HD);
-        float qf[A_MAXG][8];
+        const int tk = lane >> 2, c = lane & 3;
+        uint32_t qa[NMMA][2];   // a0, a2 of every step: head tk's dims DPT c + 4 j + {0,1}, {2,3} as half2
+        if (tk < g) {
+            const float* qp = op.a_q + ((size_t)(kvh * gq + h0 + tk)) * HD + DPT * c;
 #pragma unroll
-        for (int h = 0; h < A_MAXG; h++)
-            if (h < g) {
-                const float* qp = op.a_q + ((size_t)(kvh * gq + h0 + h)) * HD + ln * 8;
-                const float4 q0 = *(const float4*)qp, q1 = *(const float4*)(qp + 4);
-                const float t[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
-#pragma unroll
-                for (int i = 0; i < 8; i++) qf[h][i] = __half2float(__float2half_rn(t[i]));
+            for (int j = 0; j < NMMA; j++) {
+                const float4 q4 = *(const float4*)(qp + 4 * j);
+                const __half2 lo = __floats2half2_rn(q4.x, q4.y), hi = __floats2half2_rn(q4.z, q4.w);
+                qa[j][0] = *(const uint32_t*)&lo;
+                qa[j][1] = *(const uint32_t*)&hi;
             }
-        if (tr && tid == 0) tr[5] = globaltimer_after(__float_as_uint(qf[0][0]));   // q arrived
+        } else {
+#pragma unroll
+            for (int j = 0; j < NMMA; j++) qa[j][0] = qa[j][1] = 0u;
+        }
+        if (tr && tid == 0) tr[5] = globaltimer_after(qa[0][0]);   // q arrived
         // the first V_PRE of this thread's V values (all of them for n <= 32) are requested once q is here, so that they
         // travel while the scores are computed without standing between the score phase and its own operands
 #pragma unroll
         for (int j = 0; j < V_PRE; j++) vpre[j] = tq + 4 * j < n ? ld_v<EPT>(vbase + (size_t)(tq + 4 * j) * HD + c0) : 0u;
-        for (int tb = warp * TPW; tb < n; tb += NCW * TPW * 2) {
-            const int ta = tb + sub, tc = ta + NCW * TPW;
-            uint4 kq[2];
-            kq[0] = ta < n ? *(const uint4*)(kbase + (size_t)ta * HD + ln * 8) : make_uint4(0, 0, 0, 0);
-            kq[1] = tc < n ? *(const uint4*)(kbase + (size_t)tc * HD + ln * 8) : make_uint4(0, 0, 0, 0);
-            if (tr && tid == 0 && tb == 0) tr[6] = globaltimer_after(kq[0].x ^ kq[1].x);   // first K rows arrived
+        // token groups of 8, dealt over the warps
+        for (int tg = warp; tg * 8 < n; tg += NCW) {
+            const int t = tg * 8 + tk;
+            uint32_t kw[DPT / 2];   // this lane's quarter of the token's K row
 #pragma unroll
-            for (int u = 0; u < 2; u++) {
-                const int t = u ? tc : ta;
-                const __half2* k2 = (const __half2*)&kq[u];
-                float d[A_MAXG];
+            for (int i = 0; i < DPT / 8; i++) {
+                const uint4 v = t < n ? *(const uint4*)(kbase + (size_t)t * HD + DPT * c + 8 * i) : make_uint4(0, 0, 0, 0);
+                kw[4 * i] = v.x; kw[4 * i + 1] = v.y; kw[4 * i + 2] = v.z; kw[4 * i + 3] = v.w;
+            }
+            if (tr && tid == 0 && tg == 0) tr[6] = globaltimer_after(kw[0]);   // first K rows arrived
+            float s4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
-                for (int h = 0; h < A_MAXG; h++) d[h] = 0.0f;
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const float2 kf = __half22float2(k2[i]);
-#pragma unroll
-                    for (int h = 0; h < A_MAXG; h++)
-                        if (h < g) d[h] += kf.x * qf[h][2 * i] + kf.y * qf[h][2 * i + 1];
-                }
-#pragma unroll
-                for (int h = 0; h < A_MAXG; h++)
-                    if (h < g) {
-#pragma unroll
-                        for (int o = LPT / 2; o > 0; o >>= 1) d[h] += __shfl_xor_sync(0xffffffffu, d[h], o);
-                        if (ln == 0 && t < n) sm.scores[h * A_TOK + t] = d[h] * scale;
-                    }
+            for (int j = 0; j < NMMA; j++)
+                asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%5}, {%7,%8}, {%0,%1,%2,%3};"
+                             : "+f"(s4[0]), "+f"(s4[1]), "+f"(s4[2]), "+f"(s4[3])
+                             : "r"(qa[j][0]), "r"(0u), "r"(qa[j][1]), "r"(kw[2 * j]), "r"(kw[2 * j + 1]));
+            // lane (tk, c) holds head tk's scores of tokens 8 tg + 2c, + 1
+            if (tk < g) {
+                const int ts = tg * 8 + 2 * c;
+                if (ts < n) sm.scores[tk * A_TOK + ts] = s4[0] * scale;
+                if (ts + 1 < n) sm.scores[tk * A_TOK + ts + 1] = s4[1] * scale;
             }
         }
     }
