@@ -93,10 +93,10 @@ static_assert(sizeof(GemvArgs) % 4 == 0 && sizeof(StepOp) % 4 == 0, "descriptor 
 struct StepSmem {
     GemvArgs* slots;   // [3] the current mat-vec descriptor of the producer, decoder and epilogue warps
     StepOp* cslot;     // [2] the compute warps' current / next stage (double-buffered)
-    int* aux;          // [0..1] per cslot: sequence length of an attention stage; [2] cta_stage; [4 + 8 cslot ..]: its AttnSplit
+    int* aux;          // [0..1] per cslot: sequence length of an attention stage; [2] cta_stage; [4 + 12 cslot ..]: its AttnSplit and this CTA's first item
     uint8_t* xbase;    // activation buffers, re-carved per mat-vec; attention and argmax alias them
 };
-constexpr size_t STEP_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 20 * sizeof(int) + 16;
+constexpr size_t STEP_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 28 * sizeof(int) + 16;
 
 // ---- the stages that are not mat-vecs, run by the 256 compute threads (kept out of line: their registers
 // ---- must not weigh on the mat-vec loop) --------------------------------------------------------------------
@@ -143,7 +143,11 @@ __device__ __noinline__ void attn_stage(const StepOp& op, uint8_t* xbase, int T,
     if (sp.n_chunks > op.a_max_chunks) asm volatile("trap;");   // scratch is sized for this bound (step_attn_max_chunks)
     for (int item = blockIdx.x; item < sp.n_items; item += gridDim.x) {
         int kvh, h0, hb, chunk, t0, n;
-        sp.item(item, T, &kvh, &h0, &hb, &chunk, &t0, &n);
+        if (item == (int)blockIdx.x) {   // decomposed ahead of the barrier
+            kvh = split[5]; h0 = split[6]; hb = split[7]; chunk = split[8]; t0 = split[9]; n = split[10];
+        } else {
+            sp.item(item, T, &kvh, &h0, &hb, &chunk, &t0, &n);
+        }
         if (op.a_hd == 64) attn_item<64>(op, kvh, h0, hb, chunk, sp.n_chunks, t0, n, as, tid, tr);
         else attn_item<128>(op, kvh, h0, hb, chunk, sp.n_chunks, t0, n, as, tid, tr);
     }
@@ -347,7 +351,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
     ss.slots = (GemvArgs*)(red + 2 * NCW * TILE_ROWS);
     ss.cslot = (StepOp*)(ss.slots + 3);
     ss.aux = (int*)(ss.cslot + 2);
-    ss.xbase = (uint8_t*)(((uintptr_t)(ss.aux + 20) + 15) & ~(uintptr_t)15);
+    ss.xbase = (uint8_t*)(((uintptr_t)(ss.aux + 28) + 15) & ~(uintptr_t)15);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank(), csize = cluster_nctarank();
@@ -513,7 +517,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             if (lane == 0 && cs->kind == OP_ATTN) {
                 const int T = *cs->a_pos + 1;
                 ss.aux[oi & 1] = T;
-                AttnSplit(cs->a_n_head, cs->a_n_kv, cs->a_min_chunk, T).store(ss.aux + 4 + 8 * (oi & 1));
+                int* pre = ss.aux + 4 + 12 * (oi & 1);
+                const AttnSplit sp(cs->a_n_head, cs->a_n_kv, cs->a_min_chunk, T);
+                sp.store(pre);
+                if ((int)blockIdx.x < sp.n_items) sp.item((int)blockIdx.x, T, pre + 5, pre + 6, pre + 7, pre + 8, pre + 9, pre + 10);
             }
             if (oi + 1 < P.n_ops) prefetch_next_stage(P.ops[oi + 1], lane);
             // every CTA has arrived oi times per completed stage: wait for the previous stage everywhere
@@ -563,7 +570,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             // the epilogue warp arrives on the grid barrier for this stage
         } else {
             if (op.kind == OP_EMBED) embed_stage(op, tid);
-            else if (op.kind == OP_ATTN) attn_stage(op, ss.xbase, ss.aux[oi & 1], ss.aux + 4 + 8 * (oi & 1), tid, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
+            else if (op.kind == OP_ATTN) attn_stage(op, ss.xbase, ss.aux[oi & 1], ss.aux + 4 + 12 * (oi & 1), tid, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
             else if (op.kind == OP_ARGMAX) argmax_stage(op, ss.xbase, tid);
             __threadfence();   // every thread's stores of this stage, before the CTA's single arrival
             named_bar_sync(1, NCT);
