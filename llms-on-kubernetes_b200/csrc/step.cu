@@ -136,8 +136,7 @@ __device__ __noinline__ void attn_stage(const StepOp& op, uint8_t* xbase, int T,
     AttnSmem as;
     as.scores = (float*)xbase;
     as.prob = as.scores + A_MAXG * A_TOK;
-    as.part = as.prob + A_MAXG * A_TOK;
-    as.ml = as.part + 3 * A_MAXG * 128;
+    as.ml = as.prob + A_MAXG * A_TOK;
     as.flag = (int*)(as.ml + 2 * A_MAXG);
     const AttnSplit sp(split);
     if (sp.n_chunks > op.a_max_chunks) asm volatile("trap;");   // scratch is sized for this bound (step_attn_max_chunks)

@@ -5,9 +5,8 @@
 //   scores : tensor cores (mma.sync m16n8k16, fp16 x fp16 -> fp32): rows = the query heads, columns = 8 tokens per
 //            warp and step; a lane reads one quarter of its token's K row with 16-byte loads
 //   softmax: the two warps that own a head in the PV phase compute its max and sum from shared memory
-//   P.V    : thread = (token quarter, one or two columns) adds its tokens for all heads; its first eight V
-//            values (all of them for a 32-token chunk) were fetched before the score phase, later ones are
-//            double-buffered; the four quarters are added through shared memory
+//   P.V    : tensor cores again: rows = heads, k = 16 tokens, columns = 8 dims; a warp owns 8 or 16 dims and walks all
+//            tokens, V rows reach the B fragments through movmatrix.trans (no shared-memory staging, no reduction)
 // Same numerics as attn.cu: q and the probabilities are rounded to fp16, fp32 accumulation; a single chunk
 // normalises before rounding (the oracle's order), several chunks keep exp(s - m_chunk) rounded to fp16 and
 // merge by log-sum-exp in the last CTA of the (kv head, batch) to arrive.
@@ -23,16 +22,14 @@ using gemvdev::NCW;
 
 constexpr int A_MAXG = 4;   // query heads per item; larger GQA groups run as several batches
 constexpr int A_TOK = STEP_ATTN_MAX_CHUNK;
-constexpr int V_PRE = 8;    // V rows fetched ahead of the score phase
 
 struct AttnSmem {
     float* scores;   // [A_MAXG][A_TOK]
     float* prob;     // [A_MAXG][A_TOK]
-    float* part;     // [3][A_MAXG][128] P.V partial sums of token quarters 1..3
     float* ml;       // [2][A_MAXG] max, sum per head
     int* flag;
 };
-constexpr size_t ATTN_SMEM_BYTES = (2 * A_MAXG * A_TOK + 3 * A_MAXG * 128 + 2 * A_MAXG + 4) * sizeof(float);
+constexpr size_t ATTN_SMEM_BYTES = (2 * A_MAXG * A_TOK + 2 * A_MAXG + 4) * sizeof(float);
 
 // tokens per work item for a sequence of T tokens: one wave of items over the grid
 __host__ __device__ inline int attn_chunk_tokens(int T, int items_per_chunk, int grid, int min_chunk) {
@@ -43,19 +40,15 @@ __host__ __device__ inline int attn_chunk_tokens(int T, int items_per_chunk, int
     return c;
 }
 
-template <int EPT>
-__device__ __forceinline__ uint32_t ld_v(const __half* p) {
-    if (EPT == 2) return *(const uint32_t*)p;
-    return (uint32_t)*(const uint16_t*)p;
-}
-template <int EPT>
-__device__ __forceinline__ void fma_v(float pr, uint32_t raw, float& a0, float& a1) {
-    if (EPT == 2) {
-        const float2 f = __half22float2(*(const __half2*)&raw);
-        a0 += pr * f.x;
-        a1 += pr * f.y;
+// the words of V row t (zero beyond the chunk) this lane feeds to its warp's TPWV output tiles: dims vcol .. vcol + 2 TPWV
+template <int HD, int TPWV>
+__device__ __forceinline__ void load_v_words(const __half* vbase, int t, int n, int vcol, uint32_t (&w)[TPWV]) {
+    if (TPWV == 2) {
+        const uint2 v = t < n ? *(const uint2*)(vbase + (size_t)t * HD + vcol) : make_uint2(0u, 0u);
+        w[0] = v.x;
+        w[TPWV - 1] = v.y;
     } else {
-        a0 += pr * h2f_bits(raw & 0xffffu);
+        w[0] = t < n ? *(const uint32_t*)(vbase + (size_t)t * HD + vcol) : 0u;
     }
 }
 
@@ -70,11 +63,16 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
     const int warp = tid >> 5, lane = tid & 31;
     const __half* kbase = op.a_k + ((size_t)kvh * op.a_n_ctx + t0) * HD;
     const __half* vbase = op.a_v + ((size_t)kvh * op.a_n_ctx + t0) * HD;
-    // softmax / merge role: head hh; P.V role: tokens tq, tq + 4, ... and columns c0 (+1) of every head
-    const int hh = tid / CPH, tq = tid / CPH, cp = tid % CPH, c0 = cp * EPT;
+    // softmax / merge role: head hh and columns c0 (+1)
+    const int hh = tid / CPH, cp = tid % CPH, c0 = cp * EPT;
+
+    constexpr int TPWV = HD / 8 / NCW;   // P.V output tiles (8 dims) per warp
+    constexpr int V_PRE_KS = 2;          // 16-token steps of V fetched ahead of the score phase (a 32-token chunk whole)
+    const int tk = lane >> 2, c = lane & 3;
+    const int vcol = (HD / 4) * c + 2 * TPWV * warp;   // first dim of this lane's V words / outputs
 
     if (tr && tid == 0) tr[4] = globaltimer_ns();
-    uint32_t vpre[V_PRE];
+    uint32_t vpre[V_PRE_KS][2][TPWV];
 
     // ---- scores on the tensor cores: S[head][token] = q[head] . k[token] ----
     // mma.sync m16n8k16 (fp16 operands, fp32 accumulate): rows = the item's query heads (rows >= g are zero),
@@ -84,7 +82,6 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
     {
         constexpr int NMMA = HD / 16, DPT = HD / 4;
         const float scale = 1.0f / sqrtf((float)HD);
-        const int tk = lane >> 2, c = lane & 3;
         uint32_t qa[NMMA][2];   // a0, a2 of every step: head tk's dims DPT c + 4 j + {0,1}, {2,3} as half2
         if (tk < g) {
             const float* qp = op.a_q + ((size_t)(kvh * gq + h0 + tk)) * HD + DPT * c;
@@ -100,10 +97,13 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
             for (int j = 0; j < NMMA; j++) qa[j][0] = qa[j][1] = 0u;
         }
         if (tr && tid == 0) tr[5] = globaltimer_after(qa[0][0]);   // q arrived
-        // the first V_PRE of this thread's V values (all of them for n <= 32) are requested once q is here, so that they
-        // travel while the scores are computed without standing between the score phase and its own operands
+        // the V words of the first 32 tokens are requested once q is here, so that they travel while the scores are
+        // computed without standing between the score phase and its own operands
 #pragma unroll
-        for (int j = 0; j < V_PRE; j++) vpre[j] = tq + 4 * j < n ? ld_v<EPT>(vbase + (size_t)(tq + 4 * j) * HD + c0) : 0u;
+        for (int ks = 0; ks < V_PRE_KS; ks++) {
+            load_v_words<HD, TPWV>(vbase, 16 * ks + tk, n, vcol, vpre[ks][0]);
+            load_v_words<HD, TPWV>(vbase, 16 * ks + 8 + tk, n, vcol, vpre[ks][1]);
+        }
         // token groups of 8, dealt over the warps
         for (int tg = warp; tg * 8 < n; tg += NCW) {
             const int t = tg * 8 + tk;
@@ -153,67 +153,62 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
     }
     named_bar_sync(1, NCT);
 
-    // ---- P.V: thread (tq, cp) adds tokens tq, tq+4, ... into its columns for all heads ----
-    float acc[A_MAXG][2];
+    // ---- P.V on the tensor cores: out[head][dim] = sum_t p[head][t] v[t][dim] ----
+    // mma.sync m16n8k16: rows = heads, k = 16 tokens per step, columns = 8 dims.  Warp w owns TPWV output tiles; the dims
+    // are permuted so that tile j's column 2c' + e is dim DPT c' + 2 j + e: lane (tk, c) then reads its tiles' values of
+    // token row tk as one contiguous word (pair) at dim DPT c + 2 j, in the natural layout of an 8 x 8 b16 matrix, and
+    // movmatrix.trans turns that into the B fragment (tokens 2c, 2c+1 of column tk).  No cross-warp reduction: every warp
+    // walks all tokens for its own dims, and lane (tk, c) ends up with out[head tk][DPT c + 2 j + {0, 1}].
+    float o4[TPWV][4];
 #pragma unroll
-    for (int h = 0; h < A_MAXG; h++) acc[h][0] = acc[h][1] = 0.0f;
+    for (int i = 0; i < TPWV; i++) o4[i][0] = o4[i][1] = o4[i][2] = o4[i][3] = 0.0f;
     {
-        uint32_t cur[V_PRE];
+        const int n_ks = (n + 15) >> 4;
+        for (int ks = 0; ks < n_ks; ks++) {
+            uint32_t w0[TPWV], w1[TPWV];
+            static_assert(V_PRE_KS == 2, "the two prefetched steps are selected with constant indices (registers)");
+            if (ks == 0) {
 #pragma unroll
-        for (int j = 0; j < V_PRE; j++) cur[j] = vpre[j];
-        const int nj = (n + 3) >> 2;   // tokens per thread, rounded up
-        for (int jb = 0; jb < nj; jb += V_PRE) {
-            uint32_t nxt[V_PRE];
+                for (int i = 0; i < TPWV; i++) { w0[i] = vpre[0][0][i]; w1[i] = vpre[0][1][i]; }
+            } else if (ks == 1) {
 #pragma unroll
-            for (int j = 0; j < V_PRE; j++) {
-                const int t = tq + 4 * (jb + V_PRE + j);
-                nxt[j] = t < n ? ld_v<EPT>(vbase + (size_t)t * HD + c0) : 0u;
+                for (int i = 0; i < TPWV; i++) { w0[i] = vpre[1][0][i]; w1[i] = vpre[1][1][i]; }
+            } else {
+                load_v_words<HD, TPWV>(vbase, 16 * ks + tk, n, vcol, w0);
+                load_v_words<HD, TPWV>(vbase, 16 * ks + 8 + tk, n, vcol, w1);
+            }
+            // A: head tk's probabilities of tokens 16 ks + 2c, + 1 (a0) and + 8, + 9 (a2); fp16 values already
+            uint32_t a0 = 0u, a2 = 0u;
+            if (tk < g) {
+                const int ta = 16 * ks + 2 * c;
+                const float2 pa = *(const float2*)(sm.prob + tk * A_TOK + ta), pb = *(const float2*)(sm.prob + tk * A_TOK + ta + 8);
+                const __half2 ha = __floats2half2_rn(ta < n ? pa.x : 0.0f, ta + 1 < n ? pa.y : 0.0f);
+                const __half2 hb = __floats2half2_rn(ta + 8 < n ? pb.x : 0.0f, ta + 9 < n ? pb.y : 0.0f);
+                a0 = *(const uint32_t*)&ha;
+                a2 = *(const uint32_t*)&hb;
             }
 #pragma unroll
-            for (int j = 0; j < V_PRE; j++) {
-                const int t = tq + 4 * (jb + j);
-                if (t < n) {
-#pragma unroll
-                    for (int h = 0; h < A_MAXG; h++)
-                        if (h < g) fma_v<EPT>(sm.prob[h * A_TOK + t], cur[j], acc[h][0], acc[h][1]);
-                }
+            for (int i = 0; i < TPWV; i++) {
+                uint32_t b0, b1;
+                asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(b0) : "r"(w0[i]));
+                asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(b1) : "r"(w1[i]));
+                asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%5}, {%7,%8}, {%0,%1,%2,%3};"
+                             : "+f"(o4[i][0]), "+f"(o4[i][1]), "+f"(o4[i][2]), "+f"(o4[i][3])
+                             : "r"(a0), "r"(0u), "r"(a2), "r"(b0), "r"(b1));
             }
-#pragma unroll
-            for (int j = 0; j < V_PRE; j++) cur[j] = nxt[j];
         }
     }
-    if (tq > 0) {
-#pragma unroll
-        for (int h = 0; h < A_MAXG; h++)
-            if (h < g) {
-                float* pp = sm.part + ((tq - 1) * A_MAXG + h) * 128 + c0;
-                pp[0] = acc[h][0];
-                if (EPT == 2) pp[1] = acc[h][1];
-            }
-    }
-    named_bar_sync(1, NCT);
     const size_t stride = (size_t)HD + 2;
-    if (tq == 0) {
+    if (tk < g) {
+        const int head = kvh * gq + h0 + tk;
+        // one chunk: the result; several: this chunk's record {max, sum, out[HD]}
+        float* o = exact ? op.a_out + (size_t)head * HD : op.a_partials + ((size_t)head * op.a_max_chunks + chunk) * stride + 2;
 #pragma unroll
-        for (int h = 0; h < A_MAXG; h++)
-            if (h < g) {
-#pragma unroll
-                for (int q = 0; q < 3; q++) {
-                    const float* pp = sm.part + (q * A_MAXG + h) * 128 + c0;
-                    acc[h][0] += pp[0];
-                    if (EPT == 2) acc[h][1] += pp[1];
-                }
-                const int head = kvh * gq + h0 + h;
-                // one chunk: the result; several: this chunk's record {max, sum, out[HD]}
-                float* o = exact ? op.a_out + (size_t)head * HD + c0
-                                 : op.a_partials + ((size_t)head * op.a_max_chunks + chunk) * stride + 2 + c0;
-                o[0] = acc[h][0];
-                if (EPT == 2) o[1] = acc[h][1];
-                if (!exact && cp == 0) {
-                    o[-2] = sm.ml[h];
-                    o[-1] = sm.ml[A_MAXG + h];
-                }
-            }
+        for (int i = 0; i < TPWV; i++) *(float2*)(o + vcol + 2 * i) = make_float2(o4[i][0], o4[i][1]);
+        if (!exact && warp == 0 && c == 0) {
+            o[-2] = sm.ml[tk];
+            o[-1] = sm.ml[A_MAXG + tk];
+        }
     }
     if (exact) {
         named_bar_sync(1, NCT);   // the next item reuses the shared buffers
