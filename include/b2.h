@@ -132,7 +132,7 @@ int b2_gemv(int type, const void* W_dev, const float* x_dev, float* y_dev, int64
 /* Y[B][N] = X[B][K] . W[N x K]^T for 1 <= B <= 32 columns in ONE pass over the weights (same row a12 with
  * n_tokens = B: batched decode and chunked prefill).  Same arithmetic as b2_gemv -- Q8_K activations, integer
  * sub-block dot products, fp32 scales -- with the dot products on the tensor cores (mma.sync int8).
- * Q4_K and Q6_K weights; other types return B2_EUNSUP (use b2_gemv).  scratch_dev: b2_gemm_scratch_bytes(K, B)
+ * Q4_K, Q5_K, Q6_K and Q8_0 weights (Q8_0 with Q8_0 activations, as b2_gemv).  scratch_dev: b2_gemm_scratch_bytes(K, B)
  * bytes of device memory, 16-byte aligned, for the quantised activations. */
 size_t b2_gemm_scratch_bytes(int64_t K, int B);
 int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int B, void* scratch_dev, void* stream);
@@ -212,7 +212,7 @@ int b2_ctx_n_slots(const b2_ctx* c);
  * slot 0).  Batched decode = one token of each of n sequences; chunked prefill = n consecutive positions of one
  * sequence (a column attends to the columns before it).  K/V of every column are written to its slot's cache.
  * last_only = 0: next_tokens_out[n] / logits_out_host[n][vocab] receive every column's greedy token / logits;
- * last_only = 1: only the last column's (one entry).  Either output may be NULL.  Q4_K / Q6_K models. */
+ * last_only = 1: only the last column's (one entry).  Either output may be NULL. */
 int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int32_t* pos, int n, int last_only,
                         int32_t* next_tokens_out, float* logits_out_host);
 /* fp32 logits [vocab] of output column col of the last b2_ctx_decode_batch (for callers that sample only some

@@ -204,7 +204,7 @@ int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64
     }
     const int fmt = gemm_act_for_type(type);
     if (fmt < 0) {
-        set_error("b2_gemm: ggml type %d is not computed by the batched kernel (Q4_K, Q6_K, Q8_0); use b2_gemv", type);
+        set_error("b2_gemm: ggml type %d is not computed by the batched kernel (Q4_K, Q5_K, Q6_K, Q8_0); use b2_gemv", type);
         return B2_EUNSUP;
     }
     int rc = launch_act_quant(x_dev, K, nullptr, 0.0f, (int)K, B, (uint8_t*)scratch_dev, (cudaStream_t)stream, fmt);

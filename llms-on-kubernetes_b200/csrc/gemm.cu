@@ -312,6 +312,59 @@ __device__ __forceinline__ void q4k_block_mma(const uint8_t* blk0, const uint8_t
     }
 }
 
+// Q5_K super-block: as Q4_K with the fifth bit of element j of sub-blocks 2p / 2p+1 in bits 2p / 2p+1 of qh[j]
+// (block = d, dmin, 12 scale bytes, qh[32], qs[128]).  The values reach 31, so the high nibbles are shifted down
+// instead of being multiplied in place.
+template <int NGL, int NB>
+__device__ __forceinline__ void q5k_block_mma(const uint8_t* blk0, const uint8_t* blk1, const uint8_t* rec0, const uint8_t* rec1, int kb,
+                                              const ActChunk<NB>& x, int ng0, int g, int c, float (&acc)[NGL][4]) {
+    const uint4 w0 = *(const uint4*)(rec0 + 16), w1 = *(const uint4*)(rec1 + 16);
+    const uint32_t ws0[4] = {w0.x, w0.y, w0.z, w0.w}, ws1[4] = {w1.x, w1.y, w1.z, w1.w};
+    const uint2 ha = *(const uint2*)(blk0 + 16 + 8 * c), hb = *(const uint2*)(blk1 + 16 + 8 * c);   // qh[8c .. 8c+7] of rows g, g+8
+    int ilo[NGL][4], ihi[NGL][4];
+#pragma unroll
+    for (int n = 0; n < NGL; n++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) ilo[n][j] = ihi[n][j] = 0;
+#pragma unroll
+    for (int p = 0; p < 4; p++) {
+        const uint2 qa = *(const uint2*)(blk0 + 48 + 32 * p + 8 * c), qb = *(const uint2*)(blk1 + 48 + 32 * p + 8 * c);
+        // fifth bits moved to bit 4 of every byte: bit 2p for the low sub-block, bit 2p+1 for the high one
+        auto lo5 = [p](uint32_t q, uint32_t h) { return (q & 0x0F0F0F0Fu) | ((p < 2 ? h << (4 - 2 * p) : h >> (2 * p - 4)) & 0x10101010u); };
+        auto hi5 = [p](uint32_t q, uint32_t h) { return ((q >> 4) & 0x0F0F0F0Fu) | ((p < 2 ? h << (3 - 2 * p) : h >> (2 * p - 3)) & 0x10101010u); };
+        const uint32_t al0 = lo5(qa.x, ha.x), al1 = lo5(qb.x, hb.x), al2 = lo5(qa.y, ha.y), al3 = lo5(qb.y, hb.y);
+        const uint32_t ah0 = hi5(qa.x, ha.x), ah1 = hi5(qb.x, hb.x), ah2 = hi5(qa.y, ha.y), ah3 = hi5(qb.y, hb.y);
+        const int s0l = ws0[p] & 0xff, s0h = (ws0[p] >> 8) & 0xff, s1l = ws1[p] & 0xff, s1h = (ws1[p] >> 8) & 0xff;
+#pragma unroll
+        for (int n = 0; n < NGL; n++) {
+            const int8_t* xq = x.q + (size_t)((ng0 + n) * 8 + g) * GEMM_Q_PITCH + kb * 256 + 64 * p + 8 * c;
+            const uint2 xl = *(const uint2*)xq, xh = *(const uint2*)(xq + 32);
+            int dl[4], dh[4];
+            mma_u8s8_k32(dl, al0, al1, al2, al3, xl.x, xl.y);
+            mma_u8s8_k32(dh, ah0, ah1, ah2, ah3, xh.x, xh.y);
+            ilo[n][0] += s0l * dl[0]; ilo[n][1] += s0l * dl[1]; ilo[n][2] += s1l * dl[2]; ilo[n][3] += s1l * dl[3];
+            ihi[n][0] += s0h * dh[0]; ihi[n][1] += s0h * dh[1]; ihi[n][2] += s1h * dh[2]; ihi[n][3] += s1h * dh[3];
+        }
+    }
+    const uint32_t m0 = c == 0 ? __byte_perm(ws0[0], ws0[1], 0x7632) : (c == 1 ? __byte_perm(ws0[2], ws0[3], 0x7632) : 0u);
+    const uint32_t m1 = c == 0 ? __byte_perm(ws1[0], ws1[1], 0x7632) : (c == 1 ? __byte_perm(ws1[2], ws1[3], 0x7632) : 0u);
+    const float2 dd0 = *(const float2*)rec0, dd1 = *(const float2*)rec1;
+#pragma unroll
+    for (int n = 0; n < NGL; n++) {
+        const int col = (ng0 + n) * 8 + g;
+        const uint32_t bl = c < 2 ? *(const uint32_t*)(x.bl + (kb * NB + col) * 8 + 4 * c) : 0u;
+        const uint32_t bh = c < 2 ? *(const uint32_t*)(x.bh + (kb * NB + col) * 8 + 4 * c) : 0u;
+        int cl[4], ch[4];
+        mma_u8s8_k32(cl, m0, m1, 0u, 0u, bl, 0u);
+        mma_u8s8_k32(ch, m0, m1, 0u, 0u, bh, 0u);
+        const float2 dx = *(const float2*)(x.d + kb * NB + (ng0 + n) * 8 + 2 * c);
+        acc[n][0] += dx.x * (dd0.x * (float)(ilo[n][0] + ihi[n][0]) - dd0.y * (float)(cl[0] + 128 * ch[0]));
+        acc[n][1] += dx.y * (dd0.x * (float)(ilo[n][1] + ihi[n][1]) - dd0.y * (float)(cl[1] + 128 * ch[1]));
+        acc[n][2] += dx.x * (dd1.x * (float)(ilo[n][2] + ihi[n][2]) - dd1.y * (float)(cl[2] + 128 * ch[2]));
+        acc[n][3] += dx.y * (dd1.x * (float)(ilo[n][3] + ihi[n][3]) - dd1.y * (float)(cl[3] + 128 * ch[3]));
+    }
+}
+
 // Q6_K super-block: 16 scale groups of 16 elements, one m16n8k16 MMA each; weights as signed q - 32
 template <int NGL, int NB>
 __device__ __forceinline__ void q6k_block_mma(const uint8_t* blk0, const uint8_t* blk1, int kb, const ActChunk<NB>& x, int ng0, int g, int c,
@@ -540,11 +593,12 @@ __global__ void __launch_bounds__((Geo<NG, FMT>::THREADS), NG == 1 ? 2 : 1) gemm
             for (int c = 0; c < n_chunks; c++) {
                 const int nb = min(G::CB, nblk_row - c * G::CB);
                 mbar_wait(&full[stage], phase);
-                if (type == B2_TYPE_Q4_K) {
+                if (type == B2_TYPE_Q4_K || type == B2_TYPE_Q5_K) {
+                    const int bb = block_bytes_of(type);
                     for (int i = lane; i < GEMM_TILE_ROWS * nb; i += 32) {
                         const int rr = i / nb, b = i - rr * nb;
                         uint8_t* rec = dec + stage * DEC_BYTES + rr * DEC_ROW + b * 32;
-                        decode_k4_header(ring + stage * G::STAGE_BYTES + rr * ROW_SLOT + b * 144, rec, rec + 16);
+                        decode_k4_header(ring + stage * G::STAGE_BYTES + rr * ROW_SLOT + b * bb, rec, rec + 16);
                     }
                 }
                 __syncwarp();
@@ -617,7 +671,7 @@ __global__ void __launch_bounds__((Geo<NG, FMT>::THREADS), NG == 1 ? 2 : 1) gemm
         const int bb = block_bytes_of(type);
         // row segment offset inside its slot (source address mod 16; chunks are multiples of 16 bytes for all types)
         uint32_t off0 = 0, off1 = 0;
-        if (type != B2_TYPE_Q4_K) {
+        if (type != B2_TYPE_Q4_K && type != B2_TYPE_Q5_K) {
             off0 = (uint32_t)((uintptr_t)slot_row_ptr16(s, tile - s.tile0, g, nblk_row * bb) & 15);
             off1 = (uint32_t)((uintptr_t)slot_row_ptr16(s, tile - s.tile0, g + 8, nblk_row * bb) & 15);
         }
@@ -638,6 +692,9 @@ __global__ void __launch_bounds__((Geo<NG, FMT>::THREADS), NG == 1 ? 2 : 1) gemm
                     if (type == B2_TYPE_Q4_K) {
                         const uint8_t* dr = dec + stage * DEC_BYTES;
                         q4k_block_mma<NGL, NB>(row0, row1, dr + g * DEC_ROW + wb * 32, dr + (g + 8) * DEC_ROW + wb * 32, wb, x, ng0, g, c, acc);
+                    } else if (type == B2_TYPE_Q5_K) {
+                        const uint8_t* dr = dec + stage * DEC_BYTES;
+                        q5k_block_mma<NGL, NB>(row0, row1, dr + g * DEC_ROW + wb * 32, dr + (g + 8) * DEC_ROW + wb * 32, wb, x, ng0, g, c, acc);
                     } else {
                         q6k_block_mma<NGL, NB>(row0, row1, wb, x, ng0, g, c, acc);
                     }
@@ -699,7 +756,7 @@ int gemm_finalize(GemmArgs& a) {
     }
     a.act_fmt = gemm_act_for_type(a.seg[0].type);
     if (a.act_fmt < 0) {
-        set_error("gemm: ggml type %d is not computed by the batched kernel (Q4_K, Q6_K, Q8_0)", a.seg[0].type);
+        set_error("gemm: ggml type %d is not computed by the batched kernel (Q4_K, Q5_K, Q6_K, Q8_0)", a.seg[0].type);
         return B2_EUNSUP;
     }
     const int kmult = a.act_fmt == ACT_Q8K ? 256 : 32;
@@ -719,10 +776,10 @@ int gemm_finalize(GemmArgs& a) {
     for (int i = 0; i < a.n_seg; i++) {
         GemvSeg& s = a.seg[i];
         if (gemm_act_for_type(s.type) != a.act_fmt) {
-            set_error("gemm: segment %d is ggml type %d; the batched kernel computes Q4_K / Q6_K (together) and Q8_0", i, s.type);
+            set_error("gemm: segment %d is ggml type %d; the batched kernel computes Q4_K / Q5_K / Q6_K (together) and Q8_0", i, s.type);
             return B2_EUNSUP;
         }
-        const uintptr_t need = s.type == B2_TYPE_Q4_K ? 15 : 1;
+        const uintptr_t need = (s.type == B2_TYPE_Q4_K || s.type == B2_TYPE_Q5_K) ? 15 : 1;
         if (((uintptr_t)s.wa & need) || (s.pairing == PAIR_SPLIT && ((uintptr_t)s.wb & need))) {
             set_error("gemm: weight pointer of segment %d is misaligned for type %d", i, s.type);
             return B2_EINVAL;
@@ -739,7 +796,7 @@ int gemm_finalize(GemmArgs& a) {
 }
 
 int gemm_act_for_type(int type) {
-    if (type == B2_TYPE_Q4_K || type == B2_TYPE_Q6_K) return ACT_Q8K;
+    if (type == B2_TYPE_Q4_K || type == B2_TYPE_Q5_K || type == B2_TYPE_Q6_K) return ACT_Q8K;
     if (type == B2_TYPE_Q8_0) return ACT_Q80;
     return -1;
 }

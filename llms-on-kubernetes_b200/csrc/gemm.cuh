@@ -66,7 +66,7 @@ struct GemmArgs {
 int launch_act_quant(const float* x, int64_t x_stride, const float* norm_w, float eps, int K, int cols, uint8_t* act, cudaStream_t st,
                      int act_fmt = ACT_Q8K);
 int gemm_finalize(GemmArgs& a);
-bool gemm_supports_type(int type);   // Q4_K, Q6_K, Q8_0
+bool gemm_supports_type(int type);   // Q4_K, Q5_K, Q6_K, Q8_0
 int gemm_act_for_type(int type);     // ACT_Q8K / ACT_Q80 / -1
 int launch_gemm(const GemmArgs& a, cudaStream_t st);
 

@@ -822,7 +822,7 @@ extern "C" int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32
     }
     const b2_model_info& I = c->m->info;
     if (!batch_supported(c->m)) {
-        set_error("b2_ctx_decode_batch: this model has matrices outside Q4_K / Q6_K / Q8_0; the batched kernel does not compute them yet");
+        set_error("b2_ctx_decode_batch: this model has matrices outside Q4_K / Q5_K / Q6_K / Q8_0; the batched kernel does not compute them yet");
         return B2_EUNSUP;
     }
     for (int j = 0; j < n; j++) {

@@ -8,7 +8,7 @@ from oracle import quants_np as qn
 from oracle import ref_model as rm
 
 pytestmark = pytest.mark.gpu
-TYPES = [qn.Q4_K, qn.Q6_K, qn.Q8_0]
+TYPES = [qn.Q4_K, qn.Q5_K, qn.Q6_K, qn.Q8_0]
 
 
 def _case(b2, synth, qt, N, K, B, seed, scale=1.0):
@@ -70,7 +70,7 @@ def test_gemm_zero_columns_and_tiny_values(b2, synth):
 
 def test_gemm_rejects_unsupported(b2):
     d = b2.DevBuf(1 << 16)
-    assert b2.lib.b2_gemm(b2.Q5_K, d.ptr, d.ptr, d.ptr, 16, 256, 8, d.ptr, None) < 0 and b2.lib.b2_gemm(b2.F16, d.ptr, d.ptr, d.ptr, 16, 256, 8, d.ptr, None) < 0
+    assert b2.lib.b2_gemm(b2.F16, d.ptr, d.ptr, d.ptr, 16, 256, 8, d.ptr, None) < 0 and b2.lib.b2_gemm(99, d.ptr, d.ptr, d.ptr, 16, 256, 8, d.ptr, None) < 0
     assert b2.lib.b2_gemm(b2.Q4_K, d.ptr, d.ptr, d.ptr, 16, 256, 33, d.ptr, None) < 0
     assert b2.lib.b2_gemm(b2.Q4_K, d.ptr, d.ptr, d.ptr, 16, 100, 8, d.ptr, None) < 0
     assert b2.lib.b2_gemm_scratch_bytes(4096, 8) == max(2 * (8 * 2080 + 8 * 8 * 20), 4 * (8 * 1056 + 32 * 8 * 4))
