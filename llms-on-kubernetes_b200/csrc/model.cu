@@ -519,6 +519,7 @@ int build_step_program(b2_ctx* c) {
             op.a_max_chunks = step_attn_max_chunks(c->n_ctx, grid);
             op.a_partials = c->step_attn_partials;
             op.a_min_chunk = STEP_ATTN_MIN_CHUNK;
+            op.a_cluster_merge = env_flag("B2_ATTN_NO_CLUSTER") ? 0 : 1;
             if (const char* e = getenv("B2_ATTN_MIN_CHUNK")) {   // tuning knob: 32 .. 256 in steps of 32
                 const int v = atoi(e);
                 if (v >= 32 && v <= STEP_ATTN_MAX_CHUNK && v % 32 == 0) op.a_min_chunk = v;

@@ -111,10 +111,15 @@ __device__ __noinline__ void embed_stage(const StepOp& op, int tid) {
 // dealt round-robin over the grid
 struct AttnSplit {
     int gq, n_batches, chunk_tokens, n_chunks, n_items;
-    __device__ AttnSplit(int n_head, int n_kv, int min_chunk, int T) {
+    // cluster > 1: prefer chunks long enough that a (kv head, batch) fits the ranks of one cluster (in-cluster merge)
+    __device__ AttnSplit(int n_head, int n_kv, int min_chunk, int T, int cluster = 0) {
         gq = n_head / n_kv;
         n_batches = (gq + A_MAXG - 1) / A_MAXG;
         chunk_tokens = attn_chunk_tokens(T, n_kv * n_batches, (int)gridDim.x, min_chunk);
+        if (cluster > 1 && n_kv * n_batches <= (int)gridDim.x / cluster) {
+            const int c = ((T + cluster - 1) / cluster + 31) & ~31;
+            if (c <= STEP_ATTN_MAX_CHUNK && c > chunk_tokens) chunk_tokens = c;
+        }
         n_chunks = (T + chunk_tokens - 1) / chunk_tokens;
         n_items = n_kv * n_batches * n_chunks;
     }
@@ -132,14 +137,26 @@ struct AttnSplit {
     }
 };
 
-__device__ __noinline__ void attn_stage(const StepOp& op, uint8_t* xbase, int T, const int* split, int tid, unsigned long long* tr) {
+__device__ __noinline__ void attn_stage(const StepOp& op, uint8_t* xbase, int T, const int* split, uint64_t* abar, int* apar, int tid,
+                                        unsigned long long* tr) {
     AttnSmem as;
     as.scores = (float*)xbase;
     as.prob = as.scores + A_MAXG * A_TOK;
     as.ml = as.prob + A_MAXG * A_TOK;
     as.flag = (int*)(as.ml + 2 * A_MAXG);
+    as.inbox = (float*)(as.flag + 4);
+    as.abar = abar;
+    as.apar = apar;
     const AttnSplit sp(split);
     if (sp.n_chunks > op.a_max_chunks) asm volatile("trap;");   // scratch is sized for this bound (step_attn_max_chunks)
+    if (split[11]) {
+        // short sequences: cluster k holds (kv head, batch) k, its rank r chunk r; rank 0 merges (attn_item)
+        if (split[5] >= 0) {
+            if (op.a_hd == 64) attn_item<64>(op, split[5], split[6], split[7], split[8], sp.n_chunks, split[9], split[10], as, tid, true, tr);
+            else attn_item<128>(op, split[5], split[6], split[7], split[8], sp.n_chunks, split[9], split[10], as, tid, true, tr);
+        }
+        return;
+    }
     for (int item = blockIdx.x; item < sp.n_items; item += gridDim.x) {
         int kvh, h0, hb, chunk, t0, n;
         if (item == (int)blockIdx.x) {   // decomposed ahead of the barrier
@@ -147,8 +164,8 @@ __device__ __noinline__ void attn_stage(const StepOp& op, uint8_t* xbase, int T,
         } else {
             sp.item(item, T, &kvh, &h0, &hb, &chunk, &t0, &n);
         }
-        if (op.a_hd == 64) attn_item<64>(op, kvh, h0, hb, chunk, sp.n_chunks, t0, n, as, tid, tr);
-        else attn_item<128>(op, kvh, h0, hb, chunk, sp.n_chunks, t0, n, as, tid, tr);
+        if (op.a_hd == 64) attn_item<64>(op, kvh, h0, hb, chunk, sp.n_chunks, t0, n, as, tid, false, tr);
+        else attn_item<128>(op, kvh, h0, hb, chunk, sp.n_chunks, t0, n, as, tid, false, tr);
     }
 }
 
@@ -367,6 +384,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
         mbar_init(&part_free[1], 1);
         mbar_init(sm.xbar, 1);
         ss.aux[2] = 0;   // cta_stage: the last grid-barrier stage number this CTA has seen complete
+        mbar_init(sm.xbar + 1, 1);   // attention records arriving from the cluster (step_attn.cuh); aux[3] = its next phase
+        ss.aux[3] = 0;
         mbar_fence_init();
     }
     cluster_sync_all();
@@ -517,9 +536,21 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
                 const int T = *cs->a_pos + 1;
                 ss.aux[oi & 1] = T;
                 int* pre = ss.aux + 4 + 12 * (oi & 1);
-                const AttnSplit sp(cs->a_n_head, cs->a_n_kv, cs->a_min_chunk, T);
+                const AttnSplit sp(cs->a_n_head, cs->a_n_kv, cs->a_min_chunk, T, (cs->a_cluster_merge && (int)csize <= A_MAXCL) ? (int)csize : 0);
                 sp.store(pre);
-                if ((int)blockIdx.x < sp.n_items) sp.item((int)blockIdx.x, T, pre + 5, pre + 6, pre + 7, pre + 8, pre + 9, pre + 10);
+                // a few chunks per (kv head, batch) and enough clusters: one cluster per (kv head, batch), merged through
+                // distributed shared memory; otherwise items round-robin over the grid, merged through global memory
+                const int groups = cs->a_n_kv * sp.n_batches;
+                const bool in_cluster = cs->a_cluster_merge && sp.n_chunks > 1 && sp.n_chunks <= (int)csize && (int)csize <= A_MAXCL &&
+                                        groups <= (int)(gridDim.x / csize);
+                pre[11] = in_cluster;
+                if (in_cluster) {
+                    const int cl = (int)(blockIdx.x / csize);
+                    pre[5] = -1;
+                    if (cl < groups && (int)rank < sp.n_chunks) sp.item(cl * sp.n_chunks + (int)rank, T, pre + 5, pre + 6, pre + 7, pre + 8, pre + 9, pre + 10);
+                } else if ((int)blockIdx.x < sp.n_items) {
+                    sp.item((int)blockIdx.x, T, pre + 5, pre + 6, pre + 7, pre + 8, pre + 9, pre + 10);
+                }
             }
             if (oi + 1 < P.n_ops) prefetch_next_stage(P.ops[oi + 1], lane);
             // every CTA has arrived oi times per completed stage: wait for the previous stage everywhere
@@ -569,7 +600,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             // the epilogue warp arrives on the grid barrier for this stage
         } else {
             if (op.kind == OP_EMBED) embed_stage(op, tid);
-            else if (op.kind == OP_ATTN) attn_stage(op, ss.xbase, ss.aux[oi & 1], ss.aux + 4 + 12 * (oi & 1), tid, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
+            else if (op.kind == OP_ATTN)
+                attn_stage(op, ss.xbase, ss.aux[oi & 1], ss.aux + 4 + 12 * (oi & 1), sm.xbar + 1, ss.aux + 3, tid,
+                           (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
             else if (op.kind == OP_ARGMAX) argmax_stage(op, ss.xbase, tid);
             __threadfence();   // every thread's stores of this stage, before the CTA's single arrival
             named_bar_sync(1, NCT);

@@ -22,6 +22,7 @@ struct StepOp {
     float* a_out;
     int a_n_head, a_n_kv, a_hd, a_n_ctx, a_max_chunks;
     int a_min_chunk;         // shortest chunk of tokens per work item (multiple of 32, <= STEP_ATTN_MAX_CHUNK)
+    int a_cluster_merge;     // 1: merge the chunks of a kv head inside a cluster when they fit (B2_ATTN_NO_CLUSTER=1 clears it)
     const int* a_pos;
     float* a_partials;       // [n_head][max_chunks][hd + 2]
     unsigned int* a_counters;  // [n_kv], zero between steps

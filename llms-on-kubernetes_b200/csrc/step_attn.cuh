@@ -28,8 +28,14 @@ struct AttnSmem {
     float* prob;     // [A_MAXG][A_TOK]
     float* ml;       // [2][A_MAXG] max, sum per head
     int* flag;
+    // merge inside a cluster (rank 0 receives): records {max, sum, out[HD]} of ranks 1.., the barrier their bytes complete
+    // and the parity of its next phase
+    float* inbox;    // [A_MAXCL - 1][A_MAXG][128 + 2]
+    uint64_t* abar;
+    int* apar;
 };
-constexpr size_t ATTN_SMEM_BYTES = (2 * A_MAXG * A_TOK + 2 * A_MAXG + 4) * sizeof(float);
+constexpr int A_MAXCL = 4;   // largest cluster the in-cluster merge is laid out for
+constexpr size_t ATTN_SMEM_BYTES = (2 * A_MAXG * A_TOK + 2 * A_MAXG + 4 + (A_MAXCL - 1) * A_MAXG * (128 + 2)) * sizeof(float);
 
 // tokens per work item for a sequence of T tokens: one wave of items over the grid
 __host__ __device__ inline int attn_chunk_tokens(int T, int items_per_chunk, int grid, int min_chunk) {
@@ -55,7 +61,7 @@ __device__ __forceinline__ void load_v_words(const __half* vbase, int t, int n, 
 // heads [h0, h0 + g) of kv head kvh, tokens [t0, t0 + n)
 template <int HD>
 __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, int n_chunks, int t0, int n, const AttnSmem& sm, int tid,
-                          unsigned long long* tr) {
+                          bool merge_in_cluster, unsigned long long* tr) {
     constexpr int CPH = NCT / A_MAXG;             // PV phase: threads per head (two warps)
     constexpr int EPT = HD / CPH;                 // columns per thread
     static_assert(EPT == 1 || EPT == 2, "head_dim 64 or 128");
@@ -199,6 +205,53 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
         }
     }
     const size_t stride = (size_t)HD + 2;
+    if (!exact && merge_in_cluster) {
+        // ---- the chunks of this (kv head, batch) sit in the CTAs of one cluster: rank `chunk` sends its record to rank 0
+        // through distributed shared memory (st.async: the bytes complete rank 0's barrier), rank 0 merges by
+        // log-sum-exp.  No global-memory round trip (record stores, fence, arrival atomic, record loads). ----
+        constexpr uint32_t REC = (uint32_t)(HD + 2) * 4;          // bytes of one head's record
+        if (chunk != 0) {
+            if (tk < g) {
+                float* rec = sm.inbox + ((size_t)(chunk - 1) * A_MAXG + tk) * (HD + 2);   // same offset in rank 0's shared memory
+                const uint32_t bar = dsmem_addr(sm.abar, 0u);
+#pragma unroll
+                for (int i = 0; i < TPWV; i++)
+                    dsmem_st_async_v2(dsmem_addr(rec + 2 + vcol + 2 * i, 0u), __float_as_uint(o4[i][0]), __float_as_uint(o4[i][1]), bar);
+                if (warp == 0 && c == 0) dsmem_st_async_v2(dsmem_addr(rec, 0u), __float_as_uint(sm.ml[tk]), __float_as_uint(sm.ml[A_MAXG + tk]), bar);
+            }
+        } else {
+            const uint32_t parity = (uint32_t)*sm.apar & 1u;
+            if (tid == 0) mbar_arrive_expect_tx(sm.abar, (uint32_t)(n_chunks - 1) * (uint32_t)g * REC);
+            mbar_wait(sm.abar, parity);
+            if (tk < g) {
+                float m = sm.ml[tk];
+                for (int s = 0; s + 1 < n_chunks; s++) m = fmaxf(m, sm.inbox[((size_t)s * A_MAXG + tk) * (HD + 2)]);
+                const float w0 = expf(sm.ml[tk] - m);
+                float den = sm.ml[A_MAXG + tk] * w0;
+                float num[TPWV][2];
+#pragma unroll
+                for (int i = 0; i < TPWV; i++) { num[i][0] = o4[i][0] * w0; num[i][1] = o4[i][1] * w0; }
+                for (int s = 0; s + 1 < n_chunks; s++) {
+                    const float* rec = sm.inbox + ((size_t)s * A_MAXG + tk) * (HD + 2);
+                    const float ws = expf(rec[0] - m);
+                    den += rec[1] * ws;
+#pragma unroll
+                    for (int i = 0; i < TPWV; i++) {
+                        const float2 v = *(const float2*)(rec + 2 + vcol + 2 * i);
+                        num[i][0] += v.x * ws;
+                        num[i][1] += v.y * ws;
+                    }
+                }
+                float* o = op.a_out + (size_t)(kvh * gq + h0 + tk) * HD;
+#pragma unroll
+                for (int i = 0; i < TPWV; i++) *(float2*)(o + vcol + 2 * i) = make_float2(num[i][0] / den, num[i][1] / den);
+            }
+        }
+        named_bar_sync(1, NCT);
+        if (chunk == 0 && tid == 0) *sm.apar ^= 1;   // the barrier's next phase
+        if (tr && tid == 0) tr[2] = globaltimer_ns();
+        return;
+    }
     if (tk < g) {
         const int head = kvh * gq + h0 + tk;
         // one chunk: the result; several: this chunk's record {max, sum, out[HD]}
