@@ -52,14 +52,17 @@ __device__ __forceinline__ void grid_arrive(unsigned int* sync, unsigned int sta
 // wait until stage `stage_no` is complete everywhere, then tell the CTA's other waiters
 __device__ __forceinline__ void grid_wait(const unsigned int* sync, unsigned int stage_no, volatile unsigned int* cta_stage) {
     const unsigned int target = stage_no * gridDim.x;
+    // relaxed probes (no L1 invalidation each time), one acquire once the count is there
 #pragma unroll 1
     for (uint32_t i = 0; i < (1u << 24); i++) {
-        if (ld_acquire_gpu(sync) >= target) {
+        unsigned int v;
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(sync) : "memory");
+        if (v >= target) {
+            (void)ld_acquire_gpu(sync);
             __threadfence_block();
             *cta_stage = stage_no;
             return;
         }
-        __nanosleep(20);
     }
     asm volatile("trap;");
 }
