@@ -137,6 +137,16 @@ int b2_gemv(int type, const void* W_dev, const float* x_dev, float* y_dev, int64
 size_t b2_gemm_scratch_bytes(int64_t K, int B);
 int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int B, void* scratch_dev, void* stream);
 
+/* Y[T][N] (+)= X[T][K] . W[N x K]^T for a whole prompt chunk of T tokens on the 5th-generation tensor cores (row a12
+ * with n_tokens = T, ggml_compute_forward_mul_mat's prompt path; BASELINE north_star "dequant-to-bf16 tile staging
+ * through TMA/shared memory into tcgen05").  The blocks are dequantised exactly as ggml does and rounded once to
+ * bf16, the activations are rounded to bf16, products accumulate in fp32 in tensor memory.  accumulate != 0 adds
+ * into y (the residual form).  K a multiple of 64; scratch_dev: b2_tc_gemm_scratch_bytes(N, K, T) bytes, 256-byte
+ * aligned (the bf16 copies of W and X). */
+size_t b2_tc_gemm_scratch_bytes(int64_t N, int64_t K, int T);
+int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int T, int accumulate, void* scratch_dev,
+               void* stream);
+
 /* y = x * rsqrt(mean(x^2) + eps) * w  over rows of length n   (row a11, ggml rms_norm + mul) */
 int b2_rmsnorm(const float* x_dev, const float* w_dev, float* y_dev, int64_t n, int64_t rows, float eps, void* stream);
 

@@ -8,6 +8,7 @@
 #include "gemv.cuh"
 #include "gguf.h"
 #include "ops.h"
+#include "tc_gemm.cuh"
 
 using namespace b2;
 
@@ -225,6 +226,36 @@ int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64
     a.n_seg = 1;
     if ((rc = gemm_finalize(a))) return rc;
     return launch_gemm(a, (cudaStream_t)stream);
+}
+
+size_t b2_tc_gemm_scratch_bytes(int64_t N, int64_t K, int T) {
+    if (N <= 0 || K <= 0 || T <= 0) return 0;
+    return ((size_t)N * K * 2 + 255) / 256 * 256 + (size_t)T * K * 2;
+}
+
+int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int T, int accumulate, void* scratch_dev,
+               void* stream) {
+    if (!W_dev || !x_dev || !y_dev || !scratch_dev || N <= 0 || K <= 0 || T <= 0 || N > 0x3fffffff || K > 0x3fffffff || K % TC_BK ||
+        ((uintptr_t)scratch_dev & 255)) {
+        set_error("b2_tc_gemm: bad arguments (N=%lld K=%lld T=%d; K must be a multiple of %d, scratch 256-byte aligned)", (long long)N, (long long)K, T,
+                  TC_BK);
+        return B2_EINVAL;
+    }
+    __nv_bfloat16* wb = (__nv_bfloat16*)scratch_dev;
+    __nv_bfloat16* xb = (__nv_bfloat16*)((uint8_t*)scratch_dev + ((size_t)N * K * 2 + 255) / 256 * 256);
+    int rc;
+    if ((rc = launch_dequant_bf16(type, W_dev, wb, N * K, (cudaStream_t)stream))) return rc;
+    if ((rc = launch_rows_to_bf16(x_dev, K, nullptr, 0.0f, (int)K, T, xb, (cudaStream_t)stream))) return rc;
+    TcGemmArgs a{};
+    a.w = wb;
+    a.x = xb;
+    a.out = y_dev;
+    a.N = (int)N;
+    a.K = (int)K;
+    a.T = T;
+    a.ldo = N;
+    a.epi = accumulate ? TC_EPI_ADD : TC_EPI_STORE;
+    return launch_tc_gemm(a, (cudaStream_t)stream);
 }
 
 int b2_rmsnorm(const float* x_dev, const float* w_dev, float* y_dev, int64_t n, int64_t rows, float eps, void* stream) {

@@ -1,0 +1,410 @@
+// tc_gemm.cu -- prompt-phase mat-mul: TMA -> shared memory -> tcgen05.mma -> tensor memory -> epilogue.
+//
+// Replaces ggml_compute_forward_mul_mat for n_tokens >> 1 (the chart's llama-server prompt
+// path).  One persistent CTA per SM, six warps with fixed roles:
+//   warp 0      TMA producer: per K step one 128 x 64 tile of the dequantised weights and one BN x 64 tile of
+//               the activations, both bf16, 128-byte swizzle, into a ring of STAGES shared-memory slots
+//   warp 1      allocates tensor memory; one lane issues tcgen05.mma (M = 128 weight rows, N = BN tokens, K = 16)
+//               four times per slot and commits the slot back to the producer; two accumulators of BN columns
+//               alternate between tiles so the epilogue of tile i overlaps the MMAs of tile i + 1
+//   warps 2..5  epilogue: tcgen05.ld 32 lanes x 32 columns, (+ bias, + residual), coalesced fp32 stores --
+//               lanes are weight rows, so for one token the 32 lanes of a warp write 128 contiguous bytes
+// Tiles are handed out m-major (all token tiles of one 128-row weight tile run at the same time on neighbouring
+// CTAs), so a weight tile comes out of HBM once and the activations stay in L2.
+//
+// Arithmetic: bf16 x bf16 products (exact in fp32) accumulated in fp32; the quantised block values are dequantised
+// exactly as ggml does and rounded once to bf16, the activations once to bf16 -- against the reference's Q8_K
+// activation quantisation (int8 per 256-block) this is the smaller of the two perturbations (tests/test_gpu_tc_gemm.py
+// states the tolerance).
+#include "tc_gemm.cuh"
+
+#include <cuda.h>
+
+#include "common.h"
+#include "dequant.cuh"
+#include "device_utils.cuh"
+
+namespace b2 {
+namespace {
+
+template <int BN>
+struct TcGeo {
+    static constexpr int STAGES = BN == 256 ? 4 : 6;
+    static constexpr int A_BYTES = TC_BM * TC_BK * 2;
+    static constexpr int B_BYTES = BN * TC_BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int N_BARS = 2 * STAGES + 4;
+    static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /* 1024-byte alignment of the swizzled tiles */ + 8 * N_BARS + 16;
+    static constexpr int TMEM_COLS = 2 * BN;   // two accumulators; a power of two >= 32
+    static constexpr int THREADS = 192;
+    // instruction descriptor (kind::f16): fp32 accumulator, bf16 A and B, both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+    static constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+};
+
+// shared-memory matrix descriptor of a K-major tile in the 128-byte-swizzle canonical layout: rows of 128 bytes,
+// groups of 8 rows 1024 bytes apart (stride byte offset), descriptor version 1 (sm_100), layout type 2 = SWIZZLE_128B
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    uint64_t d = (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= 1ull << 46;
+    d |= 2ull << 61;
+    return d;
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 :: "r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+
+__device__ __forceinline__ void bar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}\n"
+            : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}\n"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// arrives on the mbarrier once every tcgen05.mma issued so far by this thread has finished (implies fence::before_thread_sync)
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+
+// 32 lanes x 32 consecutive fp32 columns of tensor memory: thread l of the warp gets lane (base lane + l)
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+          "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+template <int BN>
+__global__ void __launch_bounds__(TcGeo<BN>::THREADS, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, const TcGemmArgs a) {
+    using G = TcGeo<BN>;
+    extern __shared__ uint8_t tc_smem[];
+    const uint32_t tiles0 = (smem_u32(tc_smem) + 1023u) & ~1023u;
+    const uint32_t bars = tiles0 + G::STAGES * G::STAGE_BYTES;
+    auto full = [&](int s) { return bars + 8u * s; };
+    auto empty = [&](int s) { return bars + 8u * (G::STAGES + s); };
+    auto acc_full = [&](int i) { return bars + 8u * (2 * G::STAGES + i); };
+    auto acc_empty = [&](int i) { return bars + 8u * (2 * G::STAGES + 2 + i); };
+    const uint32_t tmem_slot = bars + 8u * G::N_BARS;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < G::STAGES; s++) {
+            bar_init(full(s), 1);
+            bar_init(empty(s), 1);
+        }
+        for (int i = 0; i < 2; i++) {
+            bar_init(acc_full(i), 1);
+            bar_init(acc_empty(i), 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" :: "l"(&map_w) : "memory");
+        asm volatile("prefetch.tensormap [%0];" :: "l"(&map_x) : "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "n"(G::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+    const int tiles_m = (a.N + TC_BM - 1) / TC_BM;
+    const int tiles_t = (a.T + BN - 1) / BN;
+    const int n_tiles = tiles_m * tiles_t;
+    const int n_kb = a.K / TC_BK;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int m0 = (tile / tiles_t) * TC_BM, t0 = (tile % tiles_t) * BN;
+                for (int kb = 0; kb < n_kb; kb++) {
+                    bar_wait(empty(s), ph ^ 1);
+                    bar_expect_tx(full(s), G::STAGE_BYTES);
+                    const uint32_t sa = tiles0 + s * G::STAGE_BYTES;
+                    tma_load_2d(sa, &map_w, full(s), kb * TC_BK, m0);
+                    tma_load_2d(sa + G::A_BYTES, &map_x, full(s), kb * TC_BK, t0);
+                    if (++s == G::STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            int j = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, j++) {
+                const int as = j & 1;
+                const uint32_t aph = (j >> 1) & 1;
+                bar_wait(acc_empty(as), aph ^ 1);   // the epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
+                for (int kb = 0; kb < n_kb; kb++) {
+                    bar_wait(full(s), ph);
+                    tc_fence_after();
+                    const uint32_t sa = tiles0 + s * G::STAGE_BYTES;
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + G::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < TC_BK / 16; k++)   // 16 bf16 = 32 bytes further along the swizzled row
+                        umma_bf16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), G::IDESC, (kb | k) != 0);
+                    umma_commit(empty(s));
+                    if (++s == G::STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+                umma_commit(acc_full(as));
+            }
+        }
+        __syncwarp();
+    } else {
+        const int q = warp & 3;   // the quarter of the 128 tensor-memory lanes this warp may read
+        int j = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, j++) {
+            const int m0 = (tile / tiles_t) * TC_BM, t0 = (tile % tiles_t) * BN;
+            const int as = j & 1;
+            const uint32_t aph = (j >> 1) & 1;
+            bar_wait(acc_full(as), aph);
+            tc_fence_after();
+            const int n = m0 + q * 32 + lane;
+            const bool row_ok = n < a.N;
+            const float bias = (a.bias && row_ok) ? a.bias[n] : 0.0f;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; c++) {
+                const int tc0 = t0 + c * 32;
+                if (tc0 >= a.T) break;
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
+                if (row_ok) {
+                    float* p = a.out + (int64_t)tc0 * a.ldo + n;
+                    const int nt = min(32, a.T - tc0);
+                    if (a.epi == TC_EPI_ADD) {
+#pragma unroll
+                        for (int i = 0; i < 32; i++)
+                            if (i < nt) p[(int64_t)i * a.ldo] += __uint_as_float(v[i]) + bias;
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 32; i++)
+                            if (i < nt) p[(int64_t)i * a.ldo] = __uint_as_float(v[i]) + bias;
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) bar_arrive(acc_empty(as));
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(G::TMEM_COLS) : "memory");
+    }
+}
+
+// ---- elementwise producers of the bf16 operands ----
+
+template <int TYPE>
+__global__ void dequant_bf16_kernel(const uint8_t* __restrict__ src, uint4* __restrict__ dst, int64_t n8) {
+    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < n8; g += (int64_t)gridDim.x * blockDim.x) {
+        const float4 lo = dq4(TYPE, src, 2 * g), hi = dq4(TYPE, src, 2 * g + 1);
+        const __nv_bfloat162 p0 = __floats2bfloat162_rn(lo.x, lo.y), p1 = __floats2bfloat162_rn(lo.z, lo.w);
+        const __nv_bfloat162 p2 = __floats2bfloat162_rn(hi.x, hi.y), p3 = __floats2bfloat162_rn(hi.z, hi.w);
+        dst[g] = make_uint4(*(const uint32_t*)&p0, *(const uint32_t*)&p1, *(const uint32_t*)&p2, *(const uint32_t*)&p3);
+    }
+}
+
+// one CTA per row: optional RMS norm (same association as the per-token path: (x * scale) * w), then bf16
+__global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, float eps, int n,
+                                                           __nv_bfloat16* __restrict__ y) {
+    const float* xr = x + (int64_t)blockIdx.x * ldx;
+    __nv_bfloat16* yr = y + (int64_t)blockIdx.x * n;
+    float scale = 1.0f;
+    if (w) {
+        float ss = 0.0f;
+        for (int i = threadIdx.x * 4; i < n; i += blockDim.x * 4) {
+            const float4 v = *(const float4*)(xr + i);
+            ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+        }
+        __shared__ float red[8];
+        ss = warp_sum(ss);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+        __syncthreads();
+        float tot = 0.0f;
+        for (int i = 0; i < (int)(blockDim.x >> 5); i++) tot += red[i];
+        scale = 1.0f / sqrtf(tot / (float)n + eps);
+    }
+    for (int i = threadIdx.x * 4; i < n; i += blockDim.x * 4) {
+        float4 v = *(const float4*)(xr + i);
+        if (w) {
+            const float4 g = *(const float4*)(w + i);
+            v.x = v.x * scale * g.x;
+            v.y = v.y * scale * g.y;
+            v.z = v.z * scale * g.z;
+            v.w = v.w * scale * g.w;
+        }
+        const __nv_bfloat162 p0 = __floats2bfloat162_rn(v.x, v.y), p1 = __floats2bfloat162_rn(v.z, v.w);
+        *(uint2*)(yr + i) = make_uint2(*(const uint32_t*)&p0, *(const uint32_t*)&p1);
+    }
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (libb2.so does not link libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int encode_fn(EncodeTiledFn* out) {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        B2_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (q != cudaDriverEntryPointSuccess || !p) {
+            set_error("tc_gemm: the driver does not export cuTensorMapEncodeTiled");
+            return B2_ECUDA;
+        }
+        fn = (EncodeTiledFn)p;
+    }
+    *out = fn;
+    return 0;
+}
+
+// [rows][K] bf16 row-major, boxes of box_rows x 64 elements, 128-byte swizzle, zero fill past the last row
+int encode_bf16_rows(CUtensorMap* map, const void* base, int64_t rows, int64_t K, int box_rows) {
+    EncodeTiledFn fn;
+    int rc;
+    if ((rc = encode_fn(&fn))) return rc;
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("tc_gemm: cuTensorMapEncodeTiled failed (%d) for a [%lld][%lld] bf16 matrix", (int)r, (long long)rows, (long long)K);
+        return B2_ECUDA;
+    }
+    return 0;
+}
+
+int sm_count() {
+    static int n = 0;
+    if (!n) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    }
+    return n;
+}
+
+template <int BN>
+int launch_tc(const TcGemmArgs& a, cudaStream_t st) {
+    using G = TcGeo<BN>;
+    CUtensorMap mw, mx;
+    int rc;
+    if ((rc = encode_bf16_rows(&mw, a.w, a.N, a.K, TC_BM))) return rc;
+    if ((rc = encode_bf16_rows(&mx, a.x, a.T, a.K, BN))) return rc;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B2_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
+        attr_set = true;
+    }
+    const int tiles = ((a.N + TC_BM - 1) / TC_BM) * ((a.T + BN - 1) / BN);
+    const int grid = tiles < sm_count() ? tiles : sm_count();
+    tc_gemm_kernel<BN><<<grid, G::THREADS, G::SMEM, st>>>(mw, mx, a);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+int launch_tc_gemm(const TcGemmArgs& a, cudaStream_t st) {
+    if (!a.w || !a.x || !a.out || a.N <= 0 || a.K <= 0 || a.T <= 0 || a.K % TC_BK || ((uintptr_t)a.w & 15) || ((uintptr_t)a.x & 15)) {
+        set_error("tc_gemm: bad arguments (N=%d K=%d T=%d; K must be a multiple of %d, operands 16-byte aligned)", a.N, a.K, a.T, TC_BK);
+        return B2_EINVAL;
+    }
+    // 256-token tiles halve the shared-memory traffic per flop; 128-token tiles when that would leave SMs without a tile
+    const int tiles256 = ((a.N + TC_BM - 1) / TC_BM) * ((a.T + 255) / 256);
+    if (a.T > 128 && tiles256 >= sm_count()) return launch_tc<256>(a, st);
+    return launch_tc<128>(a, st);
+}
+
+int launch_dequant_bf16(int type, const void* src, __nv_bfloat16* dst, int64_t n, cudaStream_t st) {
+    const TypeTraits* t = type_traits(type);
+    if (!t || !src || !dst || n <= 0 || n % t->block_elems || n % 8 || ((uintptr_t)dst & 15)) {
+        set_error("dequant_bf16: bad arguments (type %d, n=%lld)", type, (long long)n);
+        return t ? B2_EINVAL : B2_EUNSUP;
+    }
+    const int threads = 256;
+    const int64_t n8 = n / 8;
+    int64_t blocks = (n8 + threads - 1) / threads;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    const uint8_t* s = (const uint8_t*)src;
+    uint4* d = (uint4*)dst;
+    switch (type) {
+        case B2_TYPE_F32: dequant_bf16_kernel<B2_TYPE_F32><<<(int)blocks, threads, 0, st>>>(s, d, n8); break;
+        case B2_TYPE_F16: dequant_bf16_kernel<B2_TYPE_F16><<<(int)blocks, threads, 0, st>>>(s, d, n8); break;
+        case B2_TYPE_BF16: dequant_bf16_kernel<B2_TYPE_BF16><<<(int)blocks, threads, 0, st>>>(s, d, n8); break;
+        case B2_TYPE_Q8_0: dequant_bf16_kernel<B2_TYPE_Q8_0><<<(int)blocks, threads, 0, st>>>(s, d, n8); break;
+        case B2_TYPE_Q4_K: dequant_bf16_kernel<B2_TYPE_Q4_K><<<(int)blocks, threads, 0, st>>>(s, d, n8); break;
+        case B2_TYPE_Q5_K: dequant_bf16_kernel<B2_TYPE_Q5_K><<<(int)blocks, threads, 0, st>>>(s, d, n8); break;
+        case B2_TYPE_Q6_K: dequant_bf16_kernel<B2_TYPE_Q6_K><<<(int)blocks, threads, 0, st>>>(s, d, n8); break;
+        default: set_error("dequant_bf16: unsupported ggml type %d", type); return B2_EUNSUP;
+    }
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int launch_rows_to_bf16(const float* x, int64_t ldx, const float* norm_w, float eps, int n, int rows, __nv_bfloat16* y, cudaStream_t st) {
+    if (!x || !y || n <= 0 || rows <= 0 || n % 4 || ldx % 4 || ((uintptr_t)x & 15) || ((uintptr_t)y & 7)) {
+        set_error("rows_to_bf16: bad arguments (n=%d rows=%d)", n, rows);
+        return B2_EINVAL;
+    }
+    rows_to_bf16_kernel<<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace b2

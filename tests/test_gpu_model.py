@@ -164,3 +164,34 @@ def test_graph_and_eager_paths_agree(b2, tiny_models, monkeypatch):
     ids_e, lg_e = ctx.greedy(prompt, 16)
     ctx.free(); m.free()
     assert ids_g == ids_e and np.array_equal(lg_g, lg_e)
+
+
+@pytest.mark.parametrize("env", [{}, {"B2_ATTN_NO_CLUSTER": "1"}, {"B2_ATTN_MIN_CHUNK": "64"}],
+                         ids=["default", "global-merge", "min-chunk-64"])
+@pytest.mark.parametrize("name", ["tiny-llama-q4_k_m", "tiny-llama3-q4_k_m"])
+def test_every_sequence_length_through_the_step_kernel(b2, synth, gguf_dir, monkeypatch, name, env):
+    """Token by token through the persistent kernel up to 1300 positions: every way the attention stage splits a
+    kv head (one chunk, 2-4 chunks merged inside a cluster, more chunks than a cluster holds merged through global
+    partials) and every chunk-size boundary, checked against the oracle at positions around the boundaries."""
+    import dataclasses
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    spec = dataclasses.replace(synth.SPECS[name], ctx=2048)
+    path = str(gguf_dir / (name + "-ctx2048.gguf"))
+    synth.write_model(path, spec, seed=9)
+    n = 1300
+    ref = rm.RefGGUFModel(path, n_ctx=n)
+    m = b2.Model(path)
+    ctx = b2.Context(m, n)
+    toks = np.random.default_rng(21).integers(3, m.info.vocab, size=n).tolist()
+    check = {p + d for p in (32, 64, 96, 128, 256, 384, 512, 768, 1024, 1152, 1280) for d in (-1, 0, 1)} | {0, 1, n - 1}
+    worst = 0.0
+    for p, t in enumerate(toks):
+        want = p in check
+        _, lr = ref.decode(t, p, want_logits=want)
+        _, lg = ctx.decode([t], p, want_logits=want)
+        if want:
+            err = float(np.abs(lg - lr).max() / np.abs(lr).max())
+            worst = max(worst, err)
+            assert err <= LOGIT_TOL and kl(lr, lg) < KL_TOL, (p, err)
+    ctx.free(); m.free(); ref.close()
