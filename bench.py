@@ -39,6 +39,18 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def tensor_peak():
+    """Dense bf16 TFLOP/s: the sustained figure (the prompt pass is one long back-to-back run of mat-muls)."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            j = json.load(open(p))
+            return float(j.get("bf16_tflops_sustained") or j["bf16_tflops"]), "measured, sustained (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 2250.0, "fallback (nominal dense bf16, B200_PROFILING.md)"
+
+
 def ncu_traffic(model: str):
     """DRAM bytes one step_kernel launch moved, from the committed ncu capture (None if there is none for this model)."""
     try:
@@ -139,18 +151,23 @@ def bench_batched(b2, synth, spec, model, args, world, barrier, max_over_ranks, 
         clocks = sampler.stop()
         ctx.free()
         value = world * reps * T / dt
-        flops = 2.0 * synth.matmul_params(spec) * T if hasattr(synth, "matmul_params") else None
+        # mat-mul flops of the prompt (2 x parameters in the layer matrices x T) + attention (4 x head_dim x n_head x T^2 / 2)
+        flops = 2.0 * synth.matmul_params(spec) * T + 2.0 * spec.n_layer * spec.n_head * spec.head_dim * float(T) * T
+        tf_peak, tf_src = tensor_peak()
+        tc = T >= 48
         return {"metric": "prefill tok/s", "value": value, "unit": "tok/s", "n_gpus": world, "steps": reps, "warmup": min(args.warmup, 3),
                 "ms_per_step": dt / reps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-                "dtype": "int8 x int4..6 mma.sync (u8.s8 -> s32), fp32 scales", "data": "synthetic",
-                "config": {"workload": f"{spec.name} {spec.ftype} synthetic GGUF, prefill of {T} tokens in 32-token chunks",
+                "dtype": "bf16 x bf16 tcgen05.mma, fp32 accumulate (weights dequantised to bf16 tiles)" if tc else
+                         "int8 x int4..6 mma.sync (u8.s8 -> s32), fp32 scales", "data": "synthetic",
+                "config": {"workload": f"{spec.name} {spec.ftype} synthetic GGUF, prefill of {T} tokens" +
+                                       (" in chunks of up to 2048 tokens on the tcgen05 path" if tc else " in 32-token chunks"),
                            "parallelism": f"replicas x{world}" if world > 1 else "single GPU"},
                 "e2e": {"value": value, "unit": "tok/s", "h2d_bytes_per_step": 4 * T, "d2h_bytes_per_step": 4},
                 "gpu_launches": None, "clocks": clocks,
-                "roofline": {"bound": "hbm", "note": "32-token chunks re-stream the weights: T/32 passes",
-                             "achieved": info.stream_bytes * ((T + 31) // 32) * reps / dt / 1e9, "peak": peak, "unit": "GB/s",
-                             "frac": info.stream_bytes * ((T + 31) // 32) * reps / dt / 1e9 / peak, "traffic": None, "peak_source": peak_src,
-                             "matmul_flops_per_prompt": flops}}
+                "roofline": {"bound": "tensor", "achieved": flops * reps / dt / 1e12, "peak": tf_peak, "unit": "TFLOP/s",
+                             "frac": flops * reps / dt / 1e12 / tf_peak, "traffic": None, "peak_source": tf_src,
+                             "flops_per_prompt": flops,
+                             "note": "whole prompt pass: dequantisation to bf16, mat-muls, attention, elementwise kernels and the last position's lm_head"}}
     B = args.batch
     n_ctx = args.prompt + args.steps + args.warmup + 8
     ctx = b2.Context(model, n_ctx, n_slots=B)

@@ -138,11 +138,12 @@ size_t b2_gemm_scratch_bytes(int64_t K, int B);
 int b2_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int B, void* scratch_dev, void* stream);
 
 /* Y[T][N] (+)= X[T][K] . W[N x K]^T for a whole prompt chunk of T tokens on the 5th-generation tensor cores (row a12
- * with n_tokens = T, ggml_compute_forward_mul_mat's prompt path; BASELINE north_star "dequant-to-bf16 tile staging
- * through TMA/shared memory into tcgen05").  The blocks are dequantised exactly as ggml does and rounded once to
- * bf16, the activations are rounded to bf16, products accumulate in fp32 in tensor memory.  accumulate != 0 adds
- * into y (the residual form).  K a multiple of 64; scratch_dev: b2_tc_gemm_scratch_bytes(N, K, T) bytes, 256-byte
- * aligned (the bf16 copies of W and X). */
+ * with n_tokens = T, ggml_compute_forward_mul_mat's prompt path; BASELINE north_star "dequant tile staging through
+ * TMA/shared memory into tcgen05").  The blocks are dequantised exactly as ggml does and rounded once to fp16; the
+ * activations are quantised as the reference quantises them for this weight type (Q8_K / Q8_0 blocks) and d * q is
+ * rounded to fp16; products accumulate in fp32 in tensor memory.  accumulate != 0 adds into y (the residual form).
+ * K a multiple of 64; scratch_dev: b2_tc_gemm_scratch_bytes(N, K, T) bytes, 256-byte aligned (the fp16 copies of W
+ * and X). */
 size_t b2_tc_gemm_scratch_bytes(int64_t N, int64_t K, int T);
 int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int T, int accumulate, void* scratch_dev,
                void* stream);
@@ -228,6 +229,13 @@ int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, 
 /* fp32 logits [vocab] of output column col of the last b2_ctx_decode_batch (for callers that sample only some
  * columns on the host instead of copying all of them) */
 int b2_ctx_batch_logits(b2_ctx* c, int col, float* logits_out_host);
+
+/* A prompt (or the rest of one after a reused prefix) of ONE sequence: n tokens at positions pos0 .. pos0 + n - 1 of
+ * sequence slot `slot`, processed in whole chunks on the tensor-core prompt path (b2_tc_gemm's kernel per matrix,
+ * causal attention over the chunk; llama_decode with a single-sequence batch of n tokens).  Fills the slot's KV
+ * cache; next_token_out / logits_out_host (either may be NULL) receive the greedy token and the logits of the LAST
+ * position.  B2_EUNSUP when the model's shapes or types are outside the path (use b2_ctx_decode_batch). */
+int b2_ctx_prefill(b2_ctx* ctx, int slot, const int32_t* tokens, int n, int pos0, int32_t* next_token_out, float* logits_out_host);
 
 /* Greedy generation entirely on the device: starting from the state left by b2_ctx_decode (whose greedy
  * token t0 the caller already has), run n_steps decode steps, each consuming the previous argmax without a

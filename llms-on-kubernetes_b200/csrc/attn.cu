@@ -314,7 +314,8 @@ size_t attn_scratch_bytes_batch(int n_head, int head_dim, int max_splits, int n_
 
 int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim,
                        int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl,
-                       int n_cols, const int* col_slot, int64_t slot_stride, int split_tokens) {
+                       int n_cols, const int* col_slot, int64_t slot_stride, int split_tokens, int cols_cap) {
+    if (cols_cap < n_cols) cols_cap = n_cols;
     if (split_tokens < 16 || split_tokens > ATTN_SPLIT_TOKENS) {
         set_error("attn_decode: split_tokens=%d outside [16, %d]", split_tokens, ATTN_SPLIT_TOKENS);
         return B2_EINVAL;
@@ -339,7 +340,10 @@ int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float
         set_error("attn_decode: max_splits=%d out of range", max_splits);
         return B2_EINVAL;
     }
-    size_t part = (size_t)n_cols * n_head * max_splits * ((size_t)head_dim + 2) * sizeof(float);
+    // the arrival counters follow the partial records of cols_cap columns -- the capacity the scratch was sized and
+    // zeroed for (attn_scratch_bytes_batch), NOT this launch's column count: a smaller batch must find its counters
+    // where every other batch size leaves them at zero, not inside a region earlier launches wrote records to
+    size_t part = (size_t)cols_cap * n_head * max_splits * ((size_t)head_dim + 2) * sizeof(float);
     part = (part + 255) & ~(size_t)255;
     float* partials = (float*)scratch;
     unsigned int* counters = (unsigned int*)((uint8_t*)scratch + part);

@@ -241,11 +241,14 @@ int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, in
                   TC_BK);
         return B2_EINVAL;
     }
-    __nv_bfloat16* wb = (__nv_bfloat16*)scratch_dev;
-    __nv_bfloat16* xb = (__nv_bfloat16*)((uint8_t*)scratch_dev + ((size_t)N * K * 2 + 255) / 256 * 256);
+    __half* wb = (__half*)scratch_dev;
+    __half* xb = (__half*)((uint8_t*)scratch_dev + ((size_t)N * K * 2 + 255) / 256 * 256);
     int rc;
-    if ((rc = launch_dequant_bf16(type, W_dev, wb, N * K, (cudaStream_t)stream))) return rc;
-    if ((rc = launch_rows_to_bf16(x_dev, K, nullptr, 0.0f, (int)K, T, xb, (cudaStream_t)stream))) return rc;
+    if ((rc = launch_dequant_f16(type, W_dev, wb, N * K, (cudaStream_t)stream))) return rc;
+    // activations quantised as the reference's mat-mul with this weight type quantises them (Q8_K / Q8_0), then fp16
+    int fmt = gemm_act_for_type(type);
+    if ((fmt == ACT_Q8K && K % 256) || (fmt == ACT_Q80 && K % 32)) fmt = -1;
+    if ((rc = launch_rows_to_f16(x_dev, K, nullptr, 0.0f, (int)K, T, fmt, xb, (cudaStream_t)stream))) return rc;
     TcGemmArgs a{};
     a.w = wb;
     a.x = xb;

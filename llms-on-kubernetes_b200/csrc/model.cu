@@ -26,6 +26,7 @@
 #include "gemv.cuh"
 #include "step.cuh"
 #include "ops.h"
+#include "tc_gemm.cuh"
 
 using namespace b2;
 
@@ -667,6 +668,35 @@ int ensure_batch(b2_ctx* c) {
     return 0;
 }
 
+// final norm + lm_head + greedy token of n_logits rows of the residual stream -> c->bt.logits / c->bt.out
+int enqueue_logits(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t st) {
+    b2_model* m = c->m;
+    const b2_model_info& I = m->info;
+    auto& b = c->bt;
+    int rc;
+    if ((rc = launch_act_quant(x_rows, I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits, b.act, st,
+                               gemm_act_for_type(m->output.type))))
+        return rc;
+    GemmArgs a{};
+    a.K = I.d_model;
+    a.act = b.act;
+    a.cols.n = n_logits;
+    a.out_stride = I.vocab;
+    a.slot_stride = c->slot_stride;
+    a.rope_tab = c->rope_tab;
+    a.rope_half = I.rope_dim / 2;
+    seg_matrix(a.seg[0], m->output, PAIR_ADJ, EPI_STORE);
+    a.seg[0].out = b.logits;
+    a.n_seg = 1;
+    if ((rc = gemm_finalize(a))) return rc;
+    if ((rc = launch_gemm(a, st))) return rc;
+    for (int j = 0; j < n_logits; j++)
+        if ((rc = launch_argmax(b.logits + (size_t)j * I.vocab, I.vocab, b.out + j, (uint8_t*)b.argmax_scratch + (size_t)j * argmax_scratch_bytes(),
+                                nullptr, nullptr, nullptr, 0, st, false)))
+            return rc;
+    return 0;
+}
+
 // one pass over the weights for n columns whose (token, slot, position) are in c->bt.tok/slot/pos.
 // logits (and the greedy token per column in c->bt.out) are computed for the last n_logits columns.
 int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
@@ -723,7 +753,7 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         if ((rc = run(a))) return rc;
         // attention of every column over its own sequence
         if ((rc = launch_attn_decode(b.q, kc, vc, b.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, b.pos, 0, batch_attn_splits(c->n_ctx),
-                                     b.attn_scratch, st, false, n, b.slot, c->slot_stride, ATTN_BATCH_SPLIT_TOKENS)))
+                                     b.attn_scratch, st, false, n, b.slot, c->slot_stride, ATTN_BATCH_SPLIT_TOKENS, b.cap)))
             return rc;
         // output projection + residual
         if ((rc = launch_act_quant(b.attn_out, qdim, nullptr, 0.0f, qdim, n, b.act, st, gemm_act_for_type(L.wo.type)))) return rc;
@@ -754,22 +784,7 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
     }
     // final norm + lm_head + greedy token for the last n_logits columns (none for the inner chunks of a prompt)
     if (n_logits <= 0) return 0;
-    const int first = n - n_logits;
-    if ((rc = launch_act_quant(b.x + (size_t)first * I.d_model, I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits, b.act, st,
-                               gemm_act_for_type(m->output.type))))
-        return rc;
-    common(a, I.d_model, n_logits, I.vocab);
-    a.cols.pos = nullptr;
-    a.cols.slot = nullptr;
-    seg_matrix(a.seg[0], m->output, PAIR_ADJ, EPI_STORE);
-    a.seg[0].out = b.logits;
-    a.n_seg = 1;
-    if ((rc = run(a))) return rc;
-    for (int j = 0; j < n_logits; j++)
-        if ((rc = launch_argmax(b.logits + (size_t)j * I.vocab, I.vocab, b.out + j, (uint8_t*)b.argmax_scratch + (size_t)j * argmax_scratch_bytes(),
-                                nullptr, nullptr, nullptr, 0, st, false)))
-            return rc;
-    return 0;
+    return enqueue_logits(c, b.x + (size_t)(n - n_logits) * I.d_model, n_logits, st);
 }
 
 // host arrays -> device columns (through the pinned staging buffer), then enqueue_batch
@@ -810,6 +825,185 @@ int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int3
     cudaGraphDestroy(graph);
     B2_CUDA_CHECK(ei);
     B2_CUDA_CHECK(cudaGraphLaunch(g.exec, c->stream));
+    return 0;
+}
+
+// ---- prompt phase on the tcgen05 path: whole chunks of one sequence's prompt per pass over the weights ----
+
+// prompts at least this long take the tensor-core path (below it the 32-column int8 kernel is faster: one pass
+// of the tensor-core path dequantises every matrix to fp16 first)
+int prefill_tc_min_tokens() {
+    static const int v = [] {
+        const char* e = getenv("B2_TC_PREFILL_MIN");
+        const int x = e ? atoi(e) : 0;
+        return x > 0 ? x : 48;
+    }();
+    return v;
+}
+
+int prefill_tc_chunk(const b2_ctx* c) {
+    const char* e = getenv("B2_PREFILL_CHUNK");
+    int x = e ? atoi(e) : 0;
+    if (x <= 0) x = 2048;
+    return std::min(x, c->n_ctx);
+}
+
+bool prefill_tc_supported(const b2_model* m) {
+    if (env_flag("B2_NO_TC_PREFILL") || !batch_supported(m)) return false;
+    const b2_model_info& I = m->info;
+    if (I.head_dim != 64 && I.head_dim != 128) return false;
+    if (I.d_model % TC_BK || I.d_ff % TC_BK || (I.n_head * I.head_dim) % TC_BK) return false;
+    for (const auto& L : m->layers) {
+        const b2_model::W* ws[] = {&L.wq, &L.wk, &L.wv, &L.wo, &L.gate, &L.up, &L.down};
+        for (const b2_model::W* w : ws)
+            if (!type_traits(w->type)) return false;
+    }
+    return true;
+}
+
+int ensure_prefill(b2_ctx* c) {
+    auto& p = c->pf;
+    if (p.cap) return 0;
+    const b2_model_info& I = c->m->info;
+    const size_t cap = (size_t)prefill_tc_chunk(c);
+    const size_t qdim = (size_t)I.n_head * I.head_dim, kvdim = (size_t)I.n_kv * I.head_dim;
+    const size_t max_k = std::max(std::max((size_t)I.d_model, (size_t)I.d_ff), qdim);
+    const size_t max_w = std::max(std::max((qdim + 2 * kvdim) * I.d_model, (size_t)I.d_model * qdim), 2 * (size_t)I.d_ff * I.d_model);
+    int rc;
+    if ((rc = dmalloc(&p.x, cap * I.d_model))) return rc;
+    if ((rc = dmalloc(&p.qkv, cap * (qdim + 2 * kvdim)))) return rc;
+    if ((rc = dmalloc(&p.q, cap * qdim))) return rc;
+    if ((rc = dmalloc(&p.attn_out, cap * qdim))) return rc;
+    if ((rc = dmalloc(&p.gu, cap * 2 * I.d_ff))) return rc;
+    B2_CUDA_CHECK(cudaMalloc(&p.xb, cap * max_k * 2));
+    B2_CUDA_CHECK(cudaMalloc(&p.wb, max_w * 2));
+    if ((rc = dmalloc(&p.tok, cap))) return rc;
+    p.cap = (int)cap;
+    return 0;
+}
+
+// T consecutive positions [pos0, pos0 + T) of sequence slot `slot`, token ids in c->pf.tok: fills the slot's KV
+// cache and leaves the residual stream of every position in c->pf.x
+int enqueue_prefill_tc(b2_ctx* c, int slot, int T, int pos0, cudaStream_t st) {
+    b2_model* m = c->m;
+    const b2_model_info& I = m->info;
+    auto& p = c->pf;
+    int rc;
+    const int qdim = I.n_head * I.head_dim, kvdim = I.n_kv * I.head_dim;
+    const int64_t kv_layer = (int64_t)I.n_kv * c->n_ctx * I.head_dim;
+    __half* xb = (__half*)p.xb;
+    __half* wb = (__half*)p.wb;
+    auto dq = [&](const b2_model::W& w, __half* dst) { return launch_dequant_f16(w.type, w.p, dst, (int64_t)w.rows * w.cols, st); };
+    auto mm = [&](int N, int K, float* out, int64_t ldo, int epi) {
+        TcGemmArgs a{};
+        a.w = wb;
+        a.x = xb;
+        a.out = out;
+        a.N = N;
+        a.K = K;
+        a.T = T;
+        a.ldo = ldo;
+        a.epi = epi;
+        return launch_tc_gemm(a, st);
+    };
+    if ((rc = launch_embed_rows(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, p.tok, T, p.x, st))) return rc;
+    for (int il = 0; il < I.n_layer; il++) {
+        const auto& L = m->layers[il];
+        __half* kc = c->k_cache + (size_t)slot * c->slot_stride + il * kv_layer;
+        __half* vc = c->v_cache + (size_t)slot * c->slot_stride + il * kv_layer;
+        // RMSNorm -> one mat-mul over the stacked Q | K | V matrices -> bias, RoPE, KV cache
+        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.wq.type), xb, st))) return rc;
+        if ((rc = dq(L.wq, wb))) return rc;
+        if ((rc = dq(L.wk, wb + (size_t)qdim * I.d_model))) return rc;
+        if ((rc = dq(L.wv, wb + (size_t)(qdim + kvdim) * I.d_model))) return rc;
+        if ((rc = mm(qdim + 2 * kvdim, I.d_model, p.qkv, qdim + 2 * kvdim, TC_EPI_STORE))) return rc;
+        PrefillQkvArgs qa{};
+        qa.qkv = p.qkv;
+        qa.bq = L.bq;
+        qa.bk = L.bk;
+        qa.bv = L.bv;
+        qa.q = p.q;
+        qa.k_cache = kc;
+        qa.v_cache = vc;
+        qa.rope_tab = c->rope_tab;
+        qa.nq = qdim;
+        qa.nk = kvdim;
+        qa.head_dim = I.head_dim;
+        qa.n_ctx = c->n_ctx;
+        qa.pos0 = pos0;
+        qa.rope_half = I.rope_dim / 2;
+        qa.neox = I.arch == 1;
+        if ((rc = launch_prefill_qkv_post(qa, T, st))) return rc;
+        if ((rc = launch_prefill_attn(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, T, pos0, st))) return rc;
+        // output projection + residual
+        if ((rc = launch_rows_to_f16(p.attn_out, qdim, nullptr, 0.0f, qdim, T, gemm_act_for_type(L.wo.type), xb, st))) return rc;
+        if ((rc = dq(L.wo, wb))) return rc;
+        if ((rc = mm(I.d_model, qdim, p.x, I.d_model, TC_EPI_ADD))) return rc;
+        // RMSNorm -> stacked gate | up -> SwiGLU -> down + residual
+        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.gate.type), xb, st))) return rc;
+        if ((rc = dq(L.gate, wb))) return rc;
+        if ((rc = dq(L.up, wb + (size_t)I.d_ff * I.d_model))) return rc;
+        if ((rc = mm(2 * I.d_ff, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE))) return rc;
+        if ((rc = launch_swiglu_rows(p.gu, I.d_ff, T, il == I.n_layer - 1 ? c->h : nullptr, st))) return rc;
+        if ((rc = launch_rows_to_f16(p.gu, 2 * (int64_t)I.d_ff, nullptr, 0.0f, I.d_ff, T, gemm_act_for_type(L.down.type), xb, st))) return rc;
+        if ((rc = dq(L.down, wb))) return rc;
+        if ((rc = mm(I.d_model, I.d_ff, p.x, I.d_model, TC_EPI_ADD))) return rc;
+    }
+    return 0;
+}
+
+// a prompt (or a prompt's tail after a reused prefix) of one sequence: chunks of up to prefill_tc_chunk() tokens;
+// the last position's logits and greedy token end up in c->bt.logits / c->bt.out[0] when want_logits
+int prefill_tc(b2_ctx* c, int slot, const int32_t* tokens, int n, int pos0, bool want_logits) {
+    int rc;
+    if ((rc = ensure_batch(c))) return rc;
+    if ((rc = ensure_prefill(c))) return rc;
+    const b2_model_info& I = c->m->info;
+    for (int done = 0; done < n;) {
+        const int T = std::min(n - done, c->pf.cap);
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->pf.tok, tokens + done, (size_t)T * 4, cudaMemcpyHostToDevice, c->stream));
+        if ((rc = enqueue_prefill_tc(c, slot, T, pos0 + done, c->stream))) return rc;
+        done += T;
+        if (done == n) {
+            const size_t j = (size_t)T - 1, qdim = (size_t)I.n_head * I.head_dim;
+            if (want_logits && (rc = enqueue_logits(c, c->pf.x + j * I.d_model, 1, c->stream))) return rc;
+            // the last position's activations where the per-token path keeps them (b2_ctx_get_activation)
+            B2_CUDA_CHECK(cudaMemcpyAsync(c->x, c->pf.x + j * I.d_model, (size_t)I.d_model * 4, cudaMemcpyDeviceToDevice, c->stream));
+            B2_CUDA_CHECK(cudaMemcpyAsync(c->q, c->pf.q + j * qdim, qdim * 4, cudaMemcpyDeviceToDevice, c->stream));
+            B2_CUDA_CHECK(cudaMemcpyAsync(c->attn_out, c->pf.attn_out + j * qdim, qdim * 4, cudaMemcpyDeviceToDevice, c->stream));
+        }
+        // the token ids are pageable host memory: the copy above has completed when cudaMemcpyAsync returns
+    }
+    return 0;
+}
+
+extern "C" int b2_ctx_prefill(b2_ctx* c, int slot, const int32_t* tokens, int n, int pos0, int32_t* next_token_out, float* logits_out_host) {
+    if (!c || !tokens || n < 1) {
+        set_error("b2_ctx_prefill: bad arguments");
+        return B2_EINVAL;
+    }
+    const b2_model_info& I = c->m->info;
+    if (slot < 0 || slot >= c->n_slots || pos0 < 0 || (int64_t)pos0 + n > c->n_ctx) {
+        set_error("b2_ctx_prefill: slot %d / positions %d..%d out of range (%d slots, context %d)", slot, pos0, pos0 + n - 1, c->n_slots, c->n_ctx);
+        return B2_ERANGE;
+    }
+    for (int i = 0; i < n; i++)
+        if (tokens[i] < 0 || tokens[i] >= I.vocab) {
+            set_error("b2_ctx_prefill: token %d at index %d is outside the vocabulary (%d)", tokens[i], i, I.vocab);
+            return B2_ERANGE;
+        }
+    if (!prefill_tc_supported(c->m)) {
+        set_error("b2_ctx_prefill: this model's shapes or types are outside the tensor-core prompt path; use b2_ctx_decode_batch");
+        return B2_EUNSUP;
+    }
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    int rc;
+    const bool want = next_token_out || logits_out_host;
+    if ((rc = prefill_tc(c, slot, tokens, n, pos0, want))) return rc;
+    if (logits_out_host) B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->bt.logits, (size_t)I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (next_token_out) B2_CUDA_CHECK(cudaMemcpyAsync(c->h_pin, c->bt.out, 4, cudaMemcpyDeviceToHost, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    if (next_token_out) *next_token_out = c->h_pin[0];
     return 0;
 }
 
@@ -974,6 +1168,9 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
                      c->bt.attn_scratch, c->bt.argmax_scratch};
     for (void* p : bptrs)
         if (p) cudaFree(p);
+    void* pptrs[] = {c->pf.x, c->pf.qkv, c->pf.q, c->pf.attn_out, c->pf.gu, c->pf.xb, c->pf.wb, c->pf.tok};
+    for (void* p : pptrs)
+        if (p) cudaFree(p);
     if (c->h_pin) cudaFreeHost(c->h_pin);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -1018,7 +1215,16 @@ extern "C" int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, 
     // last chunk producing the logits / greedy token of the final position; then the device-resident state
     // (token, position, logits) is left exactly as the per-token path leaves it
     const int n_in = n;
-    if (n >= 4 && batch_supported(c->m)) {
+    if (n >= prefill_tc_min_tokens() && prefill_tc_supported(c->m)) {
+        // long prompts: whole chunks on the tcgen05 path (fp16 tiles of the dequantised matrices)
+        if ((rc = prefill_tc(c, 0, tokens, n, pos0, true))) return rc;
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->logits, c->bt.logits, (size_t)I.vocab * 4, cudaMemcpyDeviceToDevice, c->stream));
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->d_tok, c->bt.out, 4, cudaMemcpyDeviceToDevice, c->stream));
+        B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // staging buffer reuse
+        c->h_pin[0] = pos0 + n;
+        B2_CUDA_CHECK(cudaMemcpyAsync(c->d_pos, c->h_pin, 4, cudaMemcpyHostToDevice, c->stream));
+        n = 0;
+    } else if (n >= 4 && batch_supported(c->m)) {
         int32_t pos[GEMM_MAX_COLS];
         for (int done = 0; done < n;) {
             const int chunk = std::min(n - done, GEMM_MAX_COLS);

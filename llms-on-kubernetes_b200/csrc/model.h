@@ -74,4 +74,12 @@ struct b2_ctx {
         struct G { cudaGraphExec_t exec = nullptr; bool seen = false; };
         std::vector<G> graphs;   // index = n * (cap + 1) + n_logits
     } bt;
+    // prompt-phase path (tc_gemm.cu, prefill_attn.cu): whole chunks of a prompt per pass over fp16 copies of the
+    // weights, allocated on the first long prompt
+    struct Prefill {
+        int cap = 0;                       // rows (prompt tokens per chunk)
+        float *x = nullptr, *qkv = nullptr, *q = nullptr, *attn_out = nullptr, *gu = nullptr;
+        void *xb = nullptr, *wb = nullptr; // fp16: activations [cap][max K], one dequantised matrix
+        int32_t* tok = nullptr;            // [cap] device
+    } pf;
 };

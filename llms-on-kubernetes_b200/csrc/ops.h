@@ -19,7 +19,8 @@ size_t attn_scratch_bytes(int n_head, int head_dim, int max_splits);
 // otherwise attend [0, n_tokens_imm).
 int launch_attn_decode(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim,
                        int n_ctx, const int* pos_ptr, int n_tokens_imm, int max_splits, void* scratch, cudaStream_t st, bool pdl,
-                       int n_cols = 1, const int* col_slot = nullptr, int64_t slot_stride = 0, int split_tokens = ATTN_SPLIT_TOKENS);
+                       int n_cols = 1, const int* col_slot = nullptr, int64_t slot_stride = 0, int split_tokens = ATTN_SPLIT_TOKENS,
+                       int cols_cap = 0 /* columns the scratch was sized for (>= n_cols; 0 = n_cols) */);
 // split_tokens: tokens per CTA (<= ATTN_SPLIT_TOKENS); the batched path uses shorter splits for more CTAs per column
 constexpr int ATTN_BATCH_SPLIT_TOKENS = 256;
 // n_cols > 1: a batch of queries q[n_cols][n_head][hd] -> out, column j at position pos_ptr[j] of sequence slot
@@ -39,5 +40,23 @@ int launch_argmax(const float* logits, int64_t n, int32_t* token_out, void* scra
 int launch_rmsnorm(const float* x, const float* w, float* y, int64_t n, int64_t rows, float eps, cudaStream_t st);
 int launch_rope(float* x, int n_heads, int head_dim, int n_dims, int mode, int pos, float freq_base, const float* freq_factors,
                 cudaStream_t st);
+
+// prefill_attn.cu: causal attention of T consecutive prompt positions [pos0, pos0 + T) of one sequence over its fp16
+// cache (kc, vc: the slot's and layer's [n_kv][n_ctx][head_dim]); q, out: [T][n_head * head_dim] fp32
+int launch_prefill_attn(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim, int n_ctx, int T, int pos0,
+                        cudaStream_t st);
+
+// prefill_ops.cu: the elementwise kernels of the prompt-phase (tensor-core) path, over all T rows at once
+struct PrefillQkvArgs {
+    const float* qkv;            // [T][nq + 2 nk]: Q | K | V mat-mul outputs
+    const float *bq, *bk, *bv;   // optional biases (qwen2)
+    float* q;                    // [T][nq] rotated queries
+    __half *k_cache, *v_cache;   // the slot's and layer's cache [n_kv][n_ctx][head_dim]
+    const float2* rope_tab;      // [n_ctx][rope_half] (cos, sin)
+    int nq, nk, head_dim, n_ctx, pos0, rope_half, neox;
+};
+int launch_embed_rows(int type, const void* table, int64_t row_bytes, int d_model, int vocab, const int32_t* tokens, int T, float* x, cudaStream_t st);
+int launch_prefill_qkv_post(const PrefillQkvArgs& a, int T, cudaStream_t st);
+int launch_swiglu_rows(float* gu, int d_ff, int T, float* h_last, cudaStream_t st);
 
 }  // namespace b2

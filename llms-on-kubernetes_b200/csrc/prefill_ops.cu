@@ -1,0 +1,126 @@
+// prefill_ops.cu -- the elementwise kernels between the prompt-phase mat-muls (tc_gemm.cu) and attention
+// (prefill_attn.cu), each over all T prompt rows at once: embedding rows (row a10), bias + RoPE + KV-cache store
+// (rows a13, a15), SwiGLU (row a11's activation).  Same formulas as the fused epilogues of the decode kernels
+// (gemv_device.cuh / gemm.cu), so a prompt and a token-by-token replay agree to rounding.
+#include <cuda_fp16.h>
+
+#include "common.h"
+#include "dequant.cuh"
+#include "gemv.cuh"
+#include "ops.h"
+
+namespace b2 {
+namespace {
+
+__global__ void embed_rows_kernel(int type, const uint8_t* __restrict__ table, int64_t row_bytes, int d_model, int vocab,
+                                  const int32_t* __restrict__ tokens, float* __restrict__ x) {
+    int tok = tokens[blockIdx.y];
+    if (tok < 0 || tok >= vocab) tok = 0;   // validated on the host
+    const uint8_t* row = table + (size_t)tok * row_bytes;
+    float4* dst = (float4*)(x + (size_t)blockIdx.y * d_model);
+    for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < d_model / 4; g += gridDim.x * blockDim.x) dst[g] = dq4(type, row, g);
+}
+
+// qkv: [T][nq + 2 nk] mat-mul output.  One thread per element pair: Q pairs are rotated into q, K pairs rotated into
+// the fp16 cache, V pairs stored to the fp16 cache.
+__global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
+    const int t = blockIdx.y;
+    const int pi = blockIdx.x * blockDim.x + threadIdx.x;
+    const int nq2 = a.nq / 2, nk2 = a.nk / 2;
+    if (pi >= nq2 + 2 * nk2) return;
+    const float* row = a.qkv + (size_t)t * (a.nq + 2 * a.nk);
+    const int pos = a.pos0 + t;
+    const int hd = a.head_dim, hp = hd / 2;
+    if (pi < nq2 + nk2) {
+        const bool is_q = pi < nq2;
+        const int lp = is_q ? pi : pi - nq2;             // pair index inside Q or K
+        const int head = lp / hp, i = lp - head * hp;    // pair i of the head
+        const int ea = a.neox ? head * hd + i : head * hd + 2 * i;
+        const int eb = a.neox ? ea + hp : ea + 1;
+        const float* src = row + (is_q ? 0 : a.nq);
+        const float* bias = is_q ? a.bq : a.bk;
+        float va = src[ea], vb = src[eb];
+        if (bias) {
+            va += bias[ea];
+            vb += bias[eb];
+        }
+        float oa = va, ob = vb;
+        if (i < a.rope_half) {
+            const float2 cs = a.rope_tab[(size_t)pos * a.rope_half + i];
+            oa = va * cs.x - vb * cs.y;
+            ob = va * cs.y + vb * cs.x;
+        }
+        if (is_q) {
+            float* dst = a.q + (size_t)t * a.nq;
+            dst[ea] = oa;
+            dst[eb] = ob;
+        } else {
+            __half* dst = a.k_cache + ((size_t)head * a.n_ctx + pos) * hd;
+            dst[ea - head * hd] = __float2half_rn(oa);
+            dst[eb - head * hd] = __float2half_rn(ob);
+        }
+    } else {
+        const int lp = pi - nq2 - nk2;
+        const int ea = 2 * lp, head = ea / hd;
+        float va = row[a.nq + a.nk + ea], vb = row[a.nq + a.nk + ea + 1];
+        if (a.bv) {
+            va += a.bv[ea];
+            vb += a.bv[ea + 1];
+        }
+        __half* dst = a.v_cache + ((size_t)head * a.n_ctx + pos) * hd + (ea - head * hd);
+        *(__half2*)dst = __floats2half2_rn(va, vb);
+    }
+}
+
+// gu: [T][2 d_ff] = gate | up  ->  the gate half becomes h = silu(gate) * up in place (fp32; the down projection's
+// activation quantiser reads it with row stride 2 d_ff); the last row also goes to h_last
+__global__ void __launch_bounds__(256) swiglu_rows_kernel(float* __restrict__ gu, int d_ff, int T, float* __restrict__ h_last) {
+    const int t = blockIdx.y;
+    float* g = gu + (size_t)t * 2 * d_ff;
+    const float* u = g + d_ff;
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4; i < d_ff; i += gridDim.x * blockDim.x * 4) {
+        const float4 a = *(const float4*)(g + i), b = *(const float4*)(u + i);
+        float4 h;
+        h.x = (a.x / (1.0f + expf(-a.x))) * b.x;
+        h.y = (a.y / (1.0f + expf(-a.y))) * b.y;
+        h.z = (a.z / (1.0f + expf(-a.z))) * b.z;
+        h.w = (a.w / (1.0f + expf(-a.w))) * b.w;
+        *(float4*)(g + i) = h;
+        if (h_last && t == T - 1) *(float4*)(h_last + i) = h;
+    }
+}
+
+}  // namespace
+
+int launch_embed_rows(int type, const void* table, int64_t row_bytes, int d_model, int vocab, const int32_t* tokens, int T, float* x, cudaStream_t st) {
+    const int threads = 128;
+    const dim3 grid((d_model / 4 + threads - 1) / threads, T);
+    embed_rows_kernel<<<grid, threads, 0, st>>>(type, (const uint8_t*)table, row_bytes, d_model, vocab, tokens, x);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int launch_prefill_qkv_post(const PrefillQkvArgs& a, int T, cudaStream_t st) {
+    if (a.nq % 2 || a.nk % 2 || a.head_dim % 2 || T <= 0) {
+        set_error("prefill_qkv_post: bad shape");
+        return B2_EINVAL;
+    }
+    const int pairs = a.nq / 2 + a.nk;
+    const dim3 grid((pairs + 255) / 256, T);
+    qkv_post_kernel<<<grid, 256, 0, st>>>(a);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int launch_swiglu_rows(float* gu, int d_ff, int T, float* h_last, cudaStream_t st) {
+    if (d_ff % 4 || T <= 0) {
+        set_error("swiglu_rows: bad shape");
+        return B2_EINVAL;
+    }
+    const dim3 grid(std::min((d_ff / 4 + 255) / 256, 16), T);
+    swiglu_rows_kernel<<<grid, 256, 0, st>>>(gu, d_ff, T, h_last);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace b2

@@ -332,6 +332,12 @@ def kv_bytes_per_token(spec: ModelSpec) -> int:
     return 2 * spec.n_layer * spec.n_kv * spec.head_dim * 2  # K and V, fp16
 
 
+def matmul_params(spec: ModelSpec) -> int:
+    """Weights in the layer matrices every prompt token multiplies (Q, K, V, O, gate, up, down; not the lm_head)."""
+    qdim, kvdim = spec.n_head * spec.head_dim, spec.n_kv * spec.head_dim
+    return spec.n_layer * (spec.d_model * (qdim + 2 * kvdim) + qdim * spec.d_model + 3 * spec.d_model * spec.d_ff)
+
+
 def write_model(path: str, spec: ModelSpec | str, seed: int = 0, vocab_strings: bool = True,
                 norm_jitter: float = 0.0) -> ModelSpec:
     if isinstance(spec, str):

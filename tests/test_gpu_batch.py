@@ -127,3 +127,34 @@ def test_decode_batch_argument_checks(b2, tiny_models):
     with pytest.raises(b2.B2Error):
         ctx.decode_batch([m.info.vocab], [0])                 # token outside the vocabulary
     ctx.free(); m.free()
+
+
+def test_batch_sizes_change_past_the_first_attention_split(b2, tiny_models, monkeypatch):
+    """Regression: beyond 256 positions the batched attention merges several splits per column through scratch
+    records and arrival counters.  The counters must sit at the same place for every batch size -- a 1-column
+    batch after a 32-column batch used to find its counters inside the region the wider batch wrote records to."""
+    monkeypatch.setenv("B2_NO_TC_PREFILL", "1")      # the 32-column chunked prompt path
+    path = tiny_models["tiny-llama-q4_k_m"]
+    m = b2.Model(path)
+    ref = rm.RefGGUFModel(path, n_ctx=512)
+    toks = np.random.default_rng(1).integers(3, m.info.vocab, size=400).tolist()
+    want = {}
+    for p, t in enumerate(toks):
+        _, lr = ref.decode(t, p, want_logits=(p + 1) in (289, 333, 400))
+        want[p + 1] = lr
+    for n in (289, 333, 400):                         # 9+ full chunks, then a narrower last chunk
+        ctx = b2.Context(m, 512)
+        _, lg = ctx.decode(toks[:n], 0)
+        assert np.abs(lg - want[n]).max() <= 0.03 * np.abs(want[n]).max(), n
+        ctx.free()
+    # the same through b2_ctx_decode_batch with a different column count on every call
+    ctx = b2.Context(m, 512, n_slots=2)
+    pos = 0
+    for width in (32, 32, 32, 32, 32, 32, 32, 32, 32, 1, 7, 32, 3, 2):
+        chunk = toks[pos:pos + width]
+        ids, lg = ctx.decode_batch(chunk, list(range(pos, pos + width)), last_only=True)
+        pos += width
+        if pos in want and want[pos] is not None:
+            assert np.abs(lg[0] - want[pos]).max() <= 0.03 * np.abs(want[pos]).max(), pos
+    assert pos == 333
+    ctx.free(); m.free(); ref.close()
