@@ -218,6 +218,12 @@ int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, float* logi
 int b2_ctx_create_slots(b2_model* m, int n_ctx, int n_slots, b2_ctx** out);
 int b2_ctx_n_slots(const b2_ctx* c);
 
+/* Widest batch b2_ctx_decode_batch accepts for this context: 32 columns on the int8 tensor-core kernel; 256 when the
+ * model's fp16 copy is resident (built on the first call that needs it, budget B2_F16_CACHE_GB, default 64 GB and at
+ * most half of the free HBM), where batches of 16 and more columns run one HBM sweep of fp16 tiles through
+ * tcgen05.mma.  0 when the model has matrices the batched kernels do not compute. */
+int b2_ctx_max_batch(b2_ctx* ctx);
+
 /* One pass over the weights for a batch of 1 <= n <= 32 tokens (llama.cpp's llama_batch: row a12 with
  * n_tokens = n): column j is token tokens[j] at position pos[j] of sequence slot slots[j] (slots == NULL: all
  * slot 0).  Batched decode = one token of each of n sequences; chunked prefill = n consecutive positions of one

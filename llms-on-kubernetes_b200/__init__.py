@@ -103,6 +103,7 @@ SYMBOLS = {
     "b2_ctx_decode_batch": (_I, [_P, _P, _P, _P, _I, _I, _P, _P]),
     "b2_ctx_batch_logits": (_I, [_P, _I, _P]),
     "b2_ctx_prefill": (_I, [_P, _I, _P, _I, _I, _P, _P]),
+    "b2_ctx_max_batch": (_I, [_P]),
     "b2_ctx_generate_greedy": (_I, [_P, _I, _P]),
     "b2_ctx_enqueue_steps": (_I, [_P, _I]),
     "b2_ctx_stream": (_P, [_P]),
@@ -371,6 +372,9 @@ class Context:
         check(lib.b2_ctx_decode_batch(self.h, toks.ctypes.data, None if s is None else s.ctypes.data, p.ctypes.data, toks.size,
                                       1 if last_only else 0, nxt.ctypes.data, logits.ctypes.data if want_logits else None))
         return nxt.tolist(), logits
+
+    def max_batch(self) -> int:
+        return check(lib.b2_ctx_max_batch(self.h))
 
     def prefill(self, tokens, pos0: int = 0, slot: int = 0, want_logits: bool = True):
         """A whole prompt of one sequence slot on the tensor-core prompt path -> (greedy id, logits of the last position)."""

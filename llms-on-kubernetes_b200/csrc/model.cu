@@ -253,6 +253,7 @@ extern "C" int b2_model_load(const char* path, int device, int tp_rank, int tp_s
 extern "C" void b2_model_free(b2_model* m) {
     if (!m) return;
     if (m->d_alloc) cudaFree(m->d_alloc);
+    if (m->f16_cache) cudaFree(m->f16_cache);
     delete m;
 }
 
@@ -645,7 +646,7 @@ int batch_attn_splits(int n_ctx) {
 int ensure_batch(b2_ctx* c) {
     if (c->bt.cap) return 0;
     const b2_model_info& I = c->m->info;
-    const int cap = GEMM_MAX_COLS;
+    const int cap = BATCH_MAX_COLS;
     int rc;
     auto& b = c->bt;
     if ((rc = dmalloc(&b.x, (size_t)cap * I.d_model))) return rc;
@@ -654,7 +655,7 @@ int ensure_batch(b2_ctx* c) {
     if ((rc = dmalloc(&b.h, (size_t)cap * I.d_ff))) return rc;
     if ((rc = dmalloc(&b.logits, (size_t)cap * I.vocab))) return rc;
     const int max_k = std::max(std::max(I.d_model, I.d_ff), I.n_head * I.head_dim);
-    if ((rc = dmalloc(&b.act, std::max(gemm_act_bytes(max_k, cap, ACT_Q8K), gemm_act_bytes(max_k, cap, ACT_Q80))))) return rc;
+    if ((rc = dmalloc(&b.act, std::max(gemm_act_bytes(max_k, GEMM_MAX_COLS, ACT_Q8K), gemm_act_bytes(max_k, GEMM_MAX_COLS, ACT_Q80))))) return rc;
     if ((rc = dmalloc(&b.tok, cap))) return rc;
     if ((rc = dmalloc(&b.pos, cap))) return rc;
     if ((rc = dmalloc(&b.slot, cap))) return rc;
@@ -697,6 +698,21 @@ int enqueue_logits(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t st
     return 0;
 }
 
+// the tensor-core pass (defined with the prompt path below)
+bool prefill_tc_supported(const b2_model* m);
+int ensure_prefill(b2_ctx* c);
+int tc_min_rows(const b2_model* m);
+int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0, const int32_t* col_pos, const int32_t* col_slot,
+                    cudaStream_t st);
+int enqueue_logits_tc(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t st);
+
+// does a decode batch of n columns take the tensor-core pass?  Wider than the int8 kernel's 32 columns: always (the
+// caller has checked that the pass exists); otherwise from tc_min_rows() columns when the fp16 copy is resident.
+bool batch_uses_tc(const b2_ctx* c, int n) {
+    if (n > GEMM_MAX_COLS) return true;
+    return c->pf.cap && c->m->f16_cache && n >= tc_min_rows(c->m);
+}
+
 // one pass over the weights for n columns whose (token, slot, position) are in c->bt.tok/slot/pos.
 // logits (and the greedy token per column in c->bt.out) are computed for the last n_logits columns.
 int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
@@ -704,6 +720,12 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
     const b2_model_info& I = m->info;
     auto& b = c->bt;
     int rc;
+    if (batch_uses_tc(c, n)) {
+        if ((rc = enqueue_tc_pass(c, b.tok, n, 0, 0, b.pos, b.slot, st))) return rc;
+        if (n_logits <= 0) return 0;
+        const float* rows = c->pf.x + (size_t)(n - n_logits) * I.d_model;
+        return n_logits >= tc_min_rows(m) ? enqueue_logits_tc(c, rows, n_logits, st) : enqueue_logits(c, rows, n_logits, st);
+    }
     const int64_t kv_layer = (int64_t)I.n_kv * c->n_ctx * I.head_dim;
     const int rope_pairing = I.arch == 1 ? PAIR_NEOX : PAIR_ADJ;
     const int qdim = I.n_head * I.head_dim;
@@ -791,19 +813,24 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
 int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int32_t* pos, int n, int n_logits) {
     int rc;
     if ((rc = ensure_batch(c))) return rc;
+    if (n >= 16 && !c->pf.cap && prefill_tc_supported(c->m) && (rc = ensure_prefill(c))) return rc;
+    if (n > GEMM_MAX_COLS && !(c->pf.cap && c->m->f16_cache)) {
+        set_error("b2_ctx_decode_batch: %d columns need the tensor-core pass with a resident fp16 copy of the model (b2_ctx_max_batch)", n);
+        return B2_EUNSUP;
+    }
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // staging buffer reuse
     for (int j = 0; j < n; j++) {
         c->h_pin[j] = tokens[j];
-        c->h_pin[GEMM_MAX_COLS + j] = pos[j];
-        c->h_pin[2 * GEMM_MAX_COLS + j] = slots ? slots[j] : 0;
+        c->h_pin[BATCH_MAX_COLS + j] = pos[j];
+        c->h_pin[2 * BATCH_MAX_COLS + j] = slots ? slots[j] : 0;
     }
     B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.tok, c->h_pin, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
-    B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.pos, c->h_pin + GEMM_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
-    B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.slot, c->h_pin + 2 * GEMM_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.pos, c->h_pin + BATCH_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.slot, c->h_pin + 2 * BATCH_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
     if (!c->use_graph) return enqueue_batch(c, n, n_logits, c->stream);
     auto& graphs = c->bt.graphs;
-    if (graphs.empty()) graphs.resize((size_t)(GEMM_MAX_COLS + 1) * (GEMM_MAX_COLS + 1));
-    auto& g = graphs[(size_t)n * (GEMM_MAX_COLS + 1) + n_logits];
+    if (graphs.empty()) graphs.resize((size_t)(BATCH_MAX_COLS + 1) * (BATCH_MAX_COLS + 1));
+    auto& g = graphs[(size_t)n * (BATCH_MAX_COLS + 1) + n_logits];
     if (g.exec) {
         B2_CUDA_CHECK(cudaGraphLaunch(g.exec, c->stream));
         return 0;
@@ -832,13 +859,13 @@ int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int3
 
 // prompts at least this long take the tensor-core path (below it the 32-column int8 kernel is faster: one pass
 // of the tensor-core path dequantises every matrix to fp16 first)
-int prefill_tc_min_tokens() {
+int tc_min_rows(const b2_model* m) {
     static const int v = [] {
-        const char* e = getenv("B2_TC_PREFILL_MIN");
-        const int x = e ? atoi(e) : 0;
-        return x > 0 ? x : 48;
+        const char* e = getenv("B2_TC_MIN_ROWS");
+        return e ? atoi(e) : 0;
     }();
-    return v;
+    if (v > 0) return v;
+    return m->f16_cache ? 24 : 48;   // with the fp16 copy resident a pass is one HBM sweep: measured faster than the int8 kernel beyond ~20 rows
 }
 
 int prefill_tc_chunk(const b2_ctx* c) {
@@ -861,30 +888,96 @@ bool prefill_tc_supported(const b2_model* m) {
     return true;
 }
 
+// fp16 copies of every layer matrix, built once per model when the budget allows (see model.h)
+int ensure_f16_cache(b2_model* m, cudaStream_t st) {
+    std::lock_guard<std::mutex> lk(m->f16_mu);
+    if (m->f16_tried) return 0;
+    m->f16_tried = true;
+    if (env_flag("B2_NO_F16_CACHE")) return 0;
+    const b2_model_info& I = m->info;
+    const size_t qdim = (size_t)I.n_head * I.head_dim, kvdim = (size_t)I.n_kv * I.head_dim, d = (size_t)I.d_model, ff = (size_t)I.d_ff;
+    const size_t per_layer = (qdim + 2 * kvdim) * d + d * qdim + 2 * ff * d + d * ff;
+    const size_t out_elems = (size_t)I.vocab * d;   // lm_head: the logits of wide decode batches
+    const size_t bytes = (per_layer * I.n_layer + out_elems) * 2;
+    const char* e = getenv("B2_F16_CACHE_GB");
+    const double cap_gb = e ? atof(e) : 64.0;
+    size_t free_b = 0, total_b = 0;
+    B2_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+    if ((double)bytes > cap_gb * 1e9 || bytes > free_b / 2) return 0;
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    __half* base = (__half*)p;
+    std::vector<b2_model::F16Layer> off(I.n_layer);
+    size_t o = 0;
+    int rc = 0;
+    auto dq = [&](const b2_model::W& w, size_t at) { return launch_dequant_f16(w.type, w.p, base + at, (int64_t)w.rows * w.cols, st); };
+    for (int il = 0; il < I.n_layer && !rc; il++) {
+        const auto& L = m->layers[il];
+        off[il].qkv = o;
+        if (!rc) rc = dq(L.wq, o);
+        if (!rc) rc = dq(L.wk, o + qdim * d);
+        if (!rc) rc = dq(L.wv, o + (qdim + kvdim) * d);
+        o += (qdim + 2 * kvdim) * d;
+        off[il].o = o;
+        if (!rc) rc = dq(L.wo, o);
+        o += d * qdim;
+        off[il].gate_up = o;
+        if (!rc) rc = dq(L.gate, o);
+        if (!rc) rc = dq(L.up, o + ff * d);
+        o += 2 * ff * d;
+        off[il].down = o;
+        if (!rc) rc = dq(L.down, o);
+        o += d * ff;
+    }
+    m->f16_output = o;
+    if (!rc) rc = dq(m->output, o);
+    if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = B2_ECUDA;
+    if (rc) {
+        cudaFree(p);
+        return rc;
+    }
+    m->f16_off = std::move(off);
+    m->f16_cache = p;
+    return 0;
+}
+
 int ensure_prefill(b2_ctx* c) {
     auto& p = c->pf;
     if (p.cap) return 0;
     const b2_model_info& I = c->m->info;
-    const size_t cap = (size_t)prefill_tc_chunk(c);
+    // rows: a prompt chunk, and never fewer than the widest decode batch (the batch form of the pass uses the same buffers)
+    const size_t cap = (size_t)std::max(prefill_tc_chunk(c), BATCH_MAX_COLS);
     const size_t qdim = (size_t)I.n_head * I.head_dim, kvdim = (size_t)I.n_kv * I.head_dim;
     const size_t max_k = std::max(std::max((size_t)I.d_model, (size_t)I.d_ff), qdim);
     const size_t max_w = std::max(std::max((qdim + 2 * kvdim) * I.d_model, (size_t)I.d_model * qdim), 2 * (size_t)I.d_ff * I.d_model);
     int rc;
+    if ((rc = ensure_f16_cache(c->m, c->stream))) return rc;
     if ((rc = dmalloc(&p.x, cap * I.d_model))) return rc;
     if ((rc = dmalloc(&p.qkv, cap * (qdim + 2 * kvdim)))) return rc;
     if ((rc = dmalloc(&p.q, cap * qdim))) return rc;
     if ((rc = dmalloc(&p.attn_out, cap * qdim))) return rc;
     if ((rc = dmalloc(&p.gu, cap * 2 * I.d_ff))) return rc;
     B2_CUDA_CHECK(cudaMalloc(&p.xb, cap * max_k * 2));
-    B2_CUDA_CHECK(cudaMalloc(&p.wb, max_w * 2));
+    if (!c->m->f16_cache) B2_CUDA_CHECK(cudaMalloc(&p.wb, max_w * 2));   // one matrix at a time, dequantised per pass
     if ((rc = dmalloc(&p.tok, cap))) return rc;
+    // split-K workspace for passes of up to 128 rows (short prompts, decode batches)
+    const int shapes[5][2] = {{(int)(qdim + 2 * kvdim), I.d_model}, {I.d_model, (int)qdim}, {2 * I.d_ff, I.d_model}, {I.d_model, I.d_ff}, {I.vocab, I.d_model}};
+    for (const auto& s : shapes) p.ws_bytes = std::max(p.ws_bytes, tc_gemm_ws_bytes(s[0], s[1], 128));
+    if (p.ws_bytes) B2_CUDA_CHECK(cudaMalloc(&p.ws, p.ws_bytes));
     p.cap = (int)cap;
     return 0;
 }
 
-// T consecutive positions [pos0, pos0 + T) of sequence slot `slot`, token ids in c->pf.tok: fills the slot's KV
-// cache and leaves the residual stream of every position in c->pf.x
-int enqueue_prefill_tc(b2_ctx* c, int slot, int T, int pos0, cudaStream_t st) {
+// One pass of T rows over the layers on the tensor-core path; the residual stream of every row ends up in c->pf.x.
+//   prompt form (col_pos == nullptr): the rows are consecutive positions [pos0, pos0 + T) of sequence slot `slot`,
+//     causal attention over the chunk (prefill_attn.cu)
+//   batch form: row j is column j of a decode batch with its own position col_pos[j] and slot col_slot[j] (device
+//     arrays), attention per column over its own sequence (attn.cu)
+int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0, const int32_t* col_pos, const int32_t* col_slot,
+                    cudaStream_t st) {
     b2_model* m = c->m;
     const b2_model_info& I = m->info;
     auto& p = c->pf;
@@ -894,9 +987,10 @@ int enqueue_prefill_tc(b2_ctx* c, int slot, int T, int pos0, cudaStream_t st) {
     __half* xb = (__half*)p.xb;
     __half* wb = (__half*)p.wb;
     auto dq = [&](const b2_model::W& w, __half* dst) { return launch_dequant_f16(w.type, w.p, dst, (int64_t)w.rows * w.cols, st); };
-    auto mm = [&](int N, int K, float* out, int64_t ldo, int epi) {
+    const __half* cache = (const __half*)m->f16_cache;
+    auto mm = [&](const __half* w, int N, int K, float* out, int64_t ldo, int epi) {
         TcGemmArgs a{};
-        a.w = wb;
+        a.w = w;
         a.x = xb;
         a.out = out;
         a.N = N;
@@ -904,19 +998,24 @@ int enqueue_prefill_tc(b2_ctx* c, int slot, int T, int pos0, cudaStream_t st) {
         a.T = T;
         a.ldo = ldo;
         a.epi = epi;
+        a.ws = p.ws;
+        a.ws_bytes = p.ws_bytes;
         return launch_tc_gemm(a, st);
     };
-    if ((rc = launch_embed_rows(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, p.tok, T, p.x, st))) return rc;
+    if ((rc = launch_embed_rows(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, tok_dev, T, p.x, st))) return rc;
     for (int il = 0; il < I.n_layer; il++) {
         const auto& L = m->layers[il];
-        __half* kc = c->k_cache + (size_t)slot * c->slot_stride + il * kv_layer;
-        __half* vc = c->v_cache + (size_t)slot * c->slot_stride + il * kv_layer;
+        // slot 0's cache in the batch form (the kernels add col_slot[j] * slot_stride per column)
+        __half* kc = c->k_cache + (size_t)(col_pos ? 0 : slot) * c->slot_stride + il * kv_layer;
+        __half* vc = c->v_cache + (size_t)(col_pos ? 0 : slot) * c->slot_stride + il * kv_layer;
         // RMSNorm -> one mat-mul over the stacked Q | K | V matrices -> bias, RoPE, KV cache
         if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.wq.type), xb, st))) return rc;
-        if ((rc = dq(L.wq, wb))) return rc;
-        if ((rc = dq(L.wk, wb + (size_t)qdim * I.d_model))) return rc;
-        if ((rc = dq(L.wv, wb + (size_t)(qdim + kvdim) * I.d_model))) return rc;
-        if ((rc = mm(qdim + 2 * kvdim, I.d_model, p.qkv, qdim + 2 * kvdim, TC_EPI_STORE))) return rc;
+        if (!cache) {
+            if ((rc = dq(L.wq, wb))) return rc;
+            if ((rc = dq(L.wk, wb + (size_t)qdim * I.d_model))) return rc;
+            if ((rc = dq(L.wv, wb + (size_t)(qdim + kvdim) * I.d_model))) return rc;
+        }
+        if ((rc = mm(cache ? cache + m->f16_off[il].qkv : wb, qdim + 2 * kvdim, I.d_model, p.qkv, qdim + 2 * kvdim, TC_EPI_STORE))) return rc;
         PrefillQkvArgs qa{};
         qa.qkv = p.qkv;
         qa.bq = L.bq;
@@ -933,21 +1032,32 @@ int enqueue_prefill_tc(b2_ctx* c, int slot, int T, int pos0, cudaStream_t st) {
         qa.pos0 = pos0;
         qa.rope_half = I.rope_dim / 2;
         qa.neox = I.arch == 1;
+        qa.col_pos = col_pos;
+        qa.col_slot = col_slot;
+        qa.slot_stride = c->slot_stride;
         if ((rc = launch_prefill_qkv_post(qa, T, st))) return rc;
-        if ((rc = launch_prefill_attn(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, T, pos0, st))) return rc;
+        if (col_pos) {
+            if ((rc = launch_attn_decode(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, col_pos, 0, batch_attn_splits(c->n_ctx),
+                                         c->bt.attn_scratch, st, false, T, col_slot, c->slot_stride, ATTN_BATCH_SPLIT_TOKENS, c->bt.cap)))
+                return rc;
+        } else if ((rc = launch_prefill_attn(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, T, pos0, st))) {
+            return rc;
+        }
         // output projection + residual
         if ((rc = launch_rows_to_f16(p.attn_out, qdim, nullptr, 0.0f, qdim, T, gemm_act_for_type(L.wo.type), xb, st))) return rc;
-        if ((rc = dq(L.wo, wb))) return rc;
-        if ((rc = mm(I.d_model, qdim, p.x, I.d_model, TC_EPI_ADD))) return rc;
+        if (!cache && (rc = dq(L.wo, wb))) return rc;
+        if ((rc = mm(cache ? cache + m->f16_off[il].o : wb, I.d_model, qdim, p.x, I.d_model, TC_EPI_ADD))) return rc;
         // RMSNorm -> stacked gate | up -> SwiGLU -> down + residual
         if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.gate.type), xb, st))) return rc;
-        if ((rc = dq(L.gate, wb))) return rc;
-        if ((rc = dq(L.up, wb + (size_t)I.d_ff * I.d_model))) return rc;
-        if ((rc = mm(2 * I.d_ff, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE))) return rc;
+        if (!cache) {
+            if ((rc = dq(L.gate, wb))) return rc;
+            if ((rc = dq(L.up, wb + (size_t)I.d_ff * I.d_model))) return rc;
+        }
+        if ((rc = mm(cache ? cache + m->f16_off[il].gate_up : wb, 2 * I.d_ff, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE))) return rc;
         if ((rc = launch_swiglu_rows(p.gu, I.d_ff, T, il == I.n_layer - 1 ? c->h : nullptr, st))) return rc;
         if ((rc = launch_rows_to_f16(p.gu, 2 * (int64_t)I.d_ff, nullptr, 0.0f, I.d_ff, T, gemm_act_for_type(L.down.type), xb, st))) return rc;
-        if ((rc = dq(L.down, wb))) return rc;
-        if ((rc = mm(I.d_model, I.d_ff, p.x, I.d_model, TC_EPI_ADD))) return rc;
+        if (!cache && (rc = dq(L.down, wb))) return rc;
+        if ((rc = mm(cache ? cache + m->f16_off[il].down : wb, I.d_model, I.d_ff, p.x, I.d_model, TC_EPI_ADD))) return rc;
     }
     return 0;
 }
@@ -960,9 +1070,9 @@ int prefill_tc(b2_ctx* c, int slot, const int32_t* tokens, int n, int pos0, bool
     if ((rc = ensure_prefill(c))) return rc;
     const b2_model_info& I = c->m->info;
     for (int done = 0; done < n;) {
-        const int T = std::min(n - done, c->pf.cap);
+        const int T = std::min(n - done, std::min(prefill_tc_chunk(c), c->pf.cap));
         B2_CUDA_CHECK(cudaMemcpyAsync(c->pf.tok, tokens + done, (size_t)T * 4, cudaMemcpyHostToDevice, c->stream));
-        if ((rc = enqueue_prefill_tc(c, slot, T, pos0 + done, c->stream))) return rc;
+        if ((rc = enqueue_tc_pass(c, c->pf.tok, T, slot, pos0 + done, nullptr, nullptr, c->stream))) return rc;
         done += T;
         if (done == n) {
             const size_t j = (size_t)T - 1, qdim = (size_t)I.n_head * I.head_dim;
@@ -975,6 +1085,35 @@ int prefill_tc(b2_ctx* c, int slot, const int32_t* tokens, int n, int pos0, bool
         // the token ids are pageable host memory: the copy above has completed when cudaMemcpyAsync returns
     }
     return 0;
+}
+
+// final norm + lm_head (fp16 copy) + greedy token of n_logits rows -> c->bt.logits / c->bt.out
+int enqueue_logits_tc(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t st) {
+    b2_model* m = c->m;
+    const b2_model_info& I = m->info;
+    int rc;
+    __half* xb = (__half*)c->pf.xb;
+    if ((rc = launch_rows_to_f16(x_rows, I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits, gemm_act_for_type(m->output.type), xb, st)))
+        return rc;
+    TcGemmArgs a{};
+    a.w = (const __half*)m->f16_cache + m->f16_output;
+    a.x = xb;
+    a.out = c->bt.logits;
+    a.N = I.vocab;
+    a.K = I.d_model;
+    a.T = n_logits;
+    a.ldo = I.vocab;
+    a.epi = TC_EPI_STORE;
+    if ((rc = launch_tc_gemm(a, st))) return rc;
+    return launch_argmax_rows(c->bt.logits, I.vocab, n_logits, c->bt.out, st);
+}
+
+extern "C" int b2_ctx_max_batch(b2_ctx* c) {
+    if (!c) return B2_EINVAL;
+    if (!batch_supported(c->m)) return 0;
+    if (cudaSetDevice(c->m->device) != cudaSuccess) return GEMM_MAX_COLS;
+    if (prefill_tc_supported(c->m) && !ensure_batch(c) && !ensure_prefill(c) && c->m->f16_cache) return BATCH_MAX_COLS;
+    return GEMM_MAX_COLS;
 }
 
 extern "C" int b2_ctx_prefill(b2_ctx* c, int slot, const int32_t* tokens, int n, int pos0, int32_t* next_token_out, float* logits_out_host) {
@@ -1011,8 +1150,8 @@ extern "C" int b2_ctx_n_slots(const b2_ctx* c) { return c ? c->n_slots : B2_EINV
 
 extern "C" int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int32_t* pos, int n, int last_only,
                                    int32_t* next_tokens_out, float* logits_out_host) {
-    if (!c || !tokens || !pos || n < 1 || n > GEMM_MAX_COLS) {
-        set_error("b2_ctx_decode_batch: bad arguments (n=%d, at most %d columns per call)", n, GEMM_MAX_COLS);
+    if (!c || !tokens || !pos || n < 1 || n > BATCH_MAX_COLS) {
+        set_error("b2_ctx_decode_batch: bad arguments (n=%d, at most %d columns per call)", n, BATCH_MAX_COLS);
         return B2_EINVAL;
     }
     const b2_model_info& I = c->m->info;
@@ -1168,7 +1307,7 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
                      c->bt.attn_scratch, c->bt.argmax_scratch};
     for (void* p : bptrs)
         if (p) cudaFree(p);
-    void* pptrs[] = {c->pf.x, c->pf.qkv, c->pf.q, c->pf.attn_out, c->pf.gu, c->pf.xb, c->pf.wb, c->pf.tok};
+    void* pptrs[] = {c->pf.x, c->pf.qkv, c->pf.q, c->pf.attn_out, c->pf.gu, c->pf.xb, c->pf.wb, c->pf.tok, c->pf.ws};
     for (void* p : pptrs)
         if (p) cudaFree(p);
     if (c->h_pin) cudaFreeHost(c->h_pin);
@@ -1215,7 +1354,9 @@ extern "C" int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, 
     // last chunk producing the logits / greedy token of the final position; then the device-resident state
     // (token, position, logits) is left exactly as the per-token path leaves it
     const int n_in = n;
-    if (n >= prefill_tc_min_tokens() && prefill_tc_supported(c->m)) {
+    const bool tc = n >= 16 && prefill_tc_supported(c->m);
+    if (tc && (rc = ensure_prefill(c))) return rc;   // builds the fp16 copy when it fits: decides the threshold below
+    if (tc && n >= tc_min_rows(c->m)) {
         // long prompts: whole chunks on the tcgen05 path (fp16 tiles of the dequantised matrices)
         if ((rc = prefill_tc(c, 0, tokens, n, pos0, true))) return rc;
         B2_CUDA_CHECK(cudaMemcpyAsync(c->logits, c->bt.logits, (size_t)I.vocab * 4, cudaMemcpyDeviceToDevice, c->stream));

@@ -6,6 +6,8 @@
 #include <memory>
 #include <vector>
 
+#include <mutex>
+
 #include "gguf.h"
 
 struct b2_model {
@@ -28,7 +30,18 @@ struct b2_model {
     const float* rope_freqs = nullptr;
     std::vector<float> rope_freqs_host;
     std::vector<Layer> layers;
+    // fp16 copies of the layer matrices for the tensor-core prompt / wide-batch path (tc_gemm.cu), built on first
+    // use when they fit the budget (B2_F16_CACHE_GB, default 64 GB and at most half of the free HBM): per layer the
+    // stacked Q | K | V, O, stacked gate | up, down.  Without it the path dequantises each matrix per pass.
+    void* f16_cache = nullptr;
+    bool f16_tried = false;
+    struct F16Layer { size_t qkv, o, gate_up, down; };   // element offsets into f16_cache
+    size_t f16_output = 0;                                // the lm_head matrix
+    std::vector<F16Layer> f16_off;
+    std::mutex f16_mu;
 };
+
+constexpr int BATCH_MAX_COLS = 256;
 
 struct b2_ctx {
     b2_model* m = nullptr;
@@ -59,8 +72,10 @@ struct b2_ctx {
     float* step_argmax_val = nullptr;
     int* step_argmax_idx = nullptr;
     int pos = 0;
-    // batched path (gemm.cu): up to GEMM_MAX_COLS tokens per pass over the weights, each with its own
-    // (sequence slot, position).  KV caches of slot s start s * slot_stride halfs after slot 0's.
+    // batched path: up to BATCH_MAX_COLS tokens per pass over the weights, each with its own (sequence slot,
+    // position) -- up to GEMM_MAX_COLS columns on the int8 kernel (gemm.cu), wider batches (and any batch of at least
+    // tc_batch_min() columns when the model's fp16 copy is resident) on the tensor-core pass (tc_gemm.cu).  KV caches
+    // of slot s start s * slot_stride halfs after slot 0's.
     int n_slots = 1;
     int64_t slot_stride = 0;
     struct Batch {
@@ -81,5 +96,7 @@ struct b2_ctx {
         float *x = nullptr, *qkv = nullptr, *q = nullptr, *attn_out = nullptr, *gu = nullptr;
         void *xb = nullptr, *wb = nullptr; // fp16: activations [cap][max K], one dequantised matrix
         int32_t* tok = nullptr;            // [cap] device
+        float* ws = nullptr;               // split-K workspace of the mat-muls (passes of <= 128 rows)
+        size_t ws_bytes = 0;
     } pf;
 };

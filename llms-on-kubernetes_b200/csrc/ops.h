@@ -54,9 +54,14 @@ struct PrefillQkvArgs {
     __half *k_cache, *v_cache;   // the slot's and layer's cache [n_kv][n_ctx][head_dim]
     const float2* rope_tab;      // [n_ctx][rope_half] (cos, sin)
     int nq, nk, head_dim, n_ctx, pos0, rope_half, neox;
+    // batch form: row t is its own sequence -- position col_pos[t], cache of slot col_slot[t] (k_cache / v_cache then
+    // point at slot 0); nullptr: row t is position pos0 + t of the one sequence k_cache / v_cache belong to
+    const int32_t *col_pos, *col_slot;
+    int64_t slot_stride;
 };
 int launch_embed_rows(int type, const void* table, int64_t row_bytes, int d_model, int vocab, const int32_t* tokens, int T, float* x, cudaStream_t st);
 int launch_prefill_qkv_post(const PrefillQkvArgs& a, int T, cudaStream_t st);
 int launch_swiglu_rows(float* gu, int d_ff, int T, float* h_last, cudaStream_t st);
+int launch_argmax_rows(const float* logits, int64_t n, int rows, int32_t* out, cudaStream_t st);
 
 }  // namespace b2

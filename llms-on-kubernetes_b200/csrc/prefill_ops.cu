@@ -29,7 +29,8 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
     const int nq2 = a.nq / 2, nk2 = a.nk / 2;
     if (pi >= nq2 + 2 * nk2) return;
     const float* row = a.qkv + (size_t)t * (a.nq + 2 * a.nk);
-    const int pos = a.pos0 + t;
+    const int pos = a.col_pos ? a.col_pos[t] : a.pos0 + t;
+    const size_t slot_off = a.col_slot ? (size_t)a.col_slot[t] * a.slot_stride : 0;
     const int hd = a.head_dim, hp = hd / 2;
     if (pi < nq2 + nk2) {
         const bool is_q = pi < nq2;
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
             dst[ea] = oa;
             dst[eb] = ob;
         } else {
-            __half* dst = a.k_cache + ((size_t)head * a.n_ctx + pos) * hd;
+            __half* dst = a.k_cache + slot_off + ((size_t)head * a.n_ctx + pos) * hd;
             dst[ea - head * hd] = __float2half_rn(oa);
             dst[eb - head * hd] = __float2half_rn(ob);
         }
@@ -67,7 +68,7 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
             va += a.bv[ea];
             vb += a.bv[ea + 1];
         }
-        __half* dst = a.v_cache + ((size_t)head * a.n_ctx + pos) * hd + (ea - head * hd);
+        __half* dst = a.v_cache + slot_off + ((size_t)head * a.n_ctx + pos) * hd + (ea - head * hd);
         *(__half2*)dst = __floats2half2_rn(va, vb);
     }
 }
@@ -90,7 +91,60 @@ __global__ void __launch_bounds__(256) swiglu_rows_kernel(float* __restrict__ gu
     }
 }
 
+// greedy token of every row of logits[rows][n]: one CTA per row; the largest value wins, equal values keep the lower
+// index (the oracle scans upwards with '>')
+__global__ void __launch_bounds__(1024) argmax_rows_kernel(const float* __restrict__ logits, int64_t n, int32_t* __restrict__ out) {
+    const float* row = logits + (size_t)blockIdx.x * n;
+    float bv = -INFINITY;
+    int bi = 0x7fffffff;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const float v = row[i];
+        if (v > bv) {   // ascending i per thread: strict '>' keeps the first maximum
+            bv = v;
+            bi = (int)i;
+        }
+    }
+    auto better = [](float v, int i, float ov, int oi) { return ov > v || (ov == v && oi < i); };
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (better(bv, bi, ov, oi)) {
+            bv = ov;
+            bi = oi;
+        }
+    }
+    __shared__ float sv[32];
+    __shared__ int si[32];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) {
+        sv[warp] = bv;
+        si[warp] = bi;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        bv = lane < (int)(blockDim.x >> 5) ? sv[lane] : -INFINITY;
+        bi = lane < (int)(blockDim.x >> 5) ? si[lane] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (better(bv, bi, ov, oi)) {
+                bv = ov;
+                bi = oi;
+            }
+        }
+        if (lane == 0) out[blockIdx.x] = bi == 0x7fffffff ? 0 : bi;
+    }
+}
+
 }  // namespace
+
+int launch_argmax_rows(const float* logits, int64_t n, int rows, int32_t* out, cudaStream_t st) {
+    argmax_rows_kernel<<<rows, 1024, 0, st>>>(logits, n, out);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
 
 int launch_embed_rows(int type, const void* table, int64_t row_bytes, int d_model, int vocab, const int32_t* tokens, int T, float* x, cudaStream_t st) {
     const int threads = 128;

@@ -3,7 +3,8 @@
 // gateways deliver requests concurrently, ramalama-models/helm-chart/templates/model-services.yaml:16-17).
 //
 // Connection threads call generate(): it queues a job and relays the text pieces the scheduler produces.
-// The scheduler thread owns the GPU context.  Every iteration it builds one batch of up to 32 columns for
+// The scheduler thread owns the GPU context.  Every iteration it builds one batch of up to max_cols columns (32, or
+// 256 with the model's fp16 copy resident) for
 // b2_ctx_decode_batch: one column per sequence that is generating, the rest filled with prompt tokens of
 // the sequences that are still being prefilled.  A lone greedy request in slot 0 takes the device-resident
 // single-sequence loop instead (a few tokens per iteration, so a newcomer waits a few milliseconds at most).
@@ -82,6 +83,8 @@ struct Engine {
     std::thread sched;
     std::vector<float> logits;
     bool batch_ok = true;   // false: the model's types are not on the batched path -> one request at a time
+    int max_cols = 32;      // widest batch per pass (b2_ctx_max_batch: 32 on the int8 kernel, 256 on the tcgen05 pass)
+    bool tc_prefill = false;   // long prompts go through b2_ctx_prefill (whole chunks on the tensor-core prompt path)
 
     int n_ctx() const { return b2_ctx_n_ctx(ctx); }
 
@@ -91,7 +94,7 @@ struct Engine {
         b2_model_get_info(model, &info);
         std::string err;
         if (!tok.load(b2_model_gguf(model), &err)) { load_error = err; return false; }
-        n_slots = std::max(1, std::min(slots_req, 64));
+        n_slots = std::max(1, std::min(slots_req, 256));
         rc = b2_ctx_create_slots(model, n_ctx_req, n_slots, &ctx);
         if (rc) { load_error = b2_last_error(); return false; }
         // probe the batched path once: models with other matrix types keep the single-sequence path
@@ -100,6 +103,13 @@ struct Engine {
             if (b2_ctx_decode_batch(ctx, &t, nullptr, &p0, 1, 1, &out, nullptr) != 0) {
                 batch_ok = false;
                 n_slots = 1;
+            }
+        }
+        if (batch_ok) {
+            const int mb = b2_ctx_max_batch(ctx);   // builds the resident fp16 copy when it fits
+            if (mb > max_cols) {
+                max_cols = mb;
+                tc_prefill = !getenv("B2_NO_TC_PREFILL");
             }
         }
         slot_cached.assign(n_slots, {});
@@ -365,9 +375,25 @@ struct Engine {
                 retire_finished();
                 continue;
             }
+            // ---- long prompts: the whole remainder in one call on the tensor-core prompt path ----
+            if (tc_prefill) {
+                for (Job* j : slot_job) {
+                    if (!j || j->finished || j->have_next || j->prompt->size() - j->fed < 64) continue;
+                    int32_t t = 0;
+                    const int rc = b2_ctx_prefill(ctx, j->slot, j->prompt->data() + j->fed, (int)(j->prompt->size() - j->fed), (int)j->fed,
+                                                  &t, j->greedy ? nullptr : logits.data());
+                    if (rc) { fail(*j, b2_last_error()); continue; }
+                    auto& cached = slot_cached[j->slot];
+                    cached.insert(cached.end(), j->prompt->begin() + j->fed, j->prompt->end());
+                    j->fed = j->prompt->size();
+                    j->next = j->greedy ? t : sample(j->p, j->rng);
+                    j->have_next = false;
+                    accept_next(*j);
+                }
+            }
             // ---- one batch: a column per generating sequence, the rest prompt tokens ----
             b_tok.clear(); b_slot.clear(); b_pos.clear(); b_job.clear(); b_last.clear();
-            const int cap = 32;
+            const int cap = max_cols;
             for (Job* j : slot_job)
                 if (j && !j->finished && j->have_next && (int)b_tok.size() < cap) {
                     b_tok.push_back(j->next);

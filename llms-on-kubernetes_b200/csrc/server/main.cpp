@@ -391,7 +391,7 @@ int main(int argc, char** argv) {
     std::string host = "127.0.0.1", model, alias, tool_mode, tool_arg;
     int port = 8080, n_ctx = 0;
     // sequences decoded together (llama-server's --parallel); the chart cannot pass it, so the default serves concurrency
-    int n_parallel = getenv("B2_N_SLOTS") ? atoi(getenv("B2_N_SLOTS")) : 16;
+    int n_parallel = getenv("B2_N_SLOTS") ? atoi(getenv("B2_N_SLOTS")) : 32;
     // flags of upstream llama-server that take a value: accepted and ignored so existing launch lines keep working
     const char* valued[] = {"-t", "--threads", "-tb", "--threads-batch", "-ngl", "--n-gpu-layers", "--gpu-layers", "-b", "--batch-size", "-ub", "--ubatch-size",
                             "-np", "--parallel", "--temp", "--top-k", "--top-p", "--min-p", "-n", "--n-predict", "--chat-template", "-fa", "--flash-attn",

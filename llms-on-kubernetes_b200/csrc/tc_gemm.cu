@@ -22,6 +22,8 @@
 
 #include <cuda.h>
 
+#include <algorithm>
+
 #include "common.h"
 #include "dequant.cuh"
 #include "device_utils.cuh"
@@ -153,16 +155,19 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
 
     const int tiles_m = (a.N + TC_BM - 1) / TC_BM;
     const int tiles_t = (a.T + BN - 1) / BN;
-    const int n_tiles = tiles_m * tiles_t;
-    const int n_kb = a.K / TC_BK;
+    // split-K: `splits` CTAs share an output tile, each over n_kb consecutive K steps, partial sums to a.ws
+    const int splits = a.splits > 1 ? a.splits : 1;
+    const int n_tiles = tiles_m * tiles_t * splits;
+    const int n_kb = a.K / TC_BK / splits;
 
     if (warp == 0) {
         if (lane == 0) {
             int s = 0;
             uint32_t ph = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                const int m0 = (tile / tiles_t) * TC_BM, t0 = (tile % tiles_t) * BN;
-                for (int kb = 0; kb < n_kb; kb++) {
+                const int ot = tile / splits, k0 = (tile % splits) * n_kb;
+                const int m0 = (ot / tiles_t) * TC_BM, t0 = (ot % tiles_t) * BN;
+                for (int kb = k0; kb < k0 + n_kb; kb++) {
                     bar_wait(empty(s), ph ^ 1);
                     bar_expect_tx(full(s), G::STAGE_BYTES);
                     const uint32_t sa = tiles0 + s * G::STAGE_BYTES;
@@ -209,14 +214,19 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
         const int q = warp & 3;   // the quarter of the 128 tensor-memory lanes this warp may read
         int j = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, j++) {
-            const int m0 = (tile / tiles_t) * TC_BM, t0 = (tile % tiles_t) * BN;
+            const int ot = tile / splits, ks = tile % splits;
+            const int m0 = (ot / tiles_t) * TC_BM, t0 = (ot % tiles_t) * BN;
             const int as = j & 1;
             const uint32_t aph = (j >> 1) & 1;
             bar_wait(acc_full(as), aph);
             tc_fence_after();
             const int n = m0 + q * 32 + lane;
             const bool row_ok = n < a.N;
-            const float bias = (a.bias && row_ok) ? a.bias[n] : 0.0f;
+            const float bias = (a.bias && row_ok && splits == 1) ? a.bias[n] : 0.0f;
+            // split-K partial sums go to slice ks of the workspace ([splits][T][N]); splitk_reduce_kernel applies the epilogue
+            float* const obase = splits > 1 ? a.ws + (size_t)ks * a.T * a.N : a.out;
+            const int64_t ldo = splits > 1 ? (int64_t)a.N : a.ldo;
+            const bool add = splits == 1 && a.epi == TC_EPI_ADD;
 #pragma unroll 1
             for (int c = 0; c < BN / 32; c++) {
                 const int tc0 = t0 + c * 32;
@@ -224,16 +234,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
                 uint32_t v[32];
                 tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 32), v);
                 if (row_ok) {
-                    float* p = a.out + (int64_t)tc0 * a.ldo + n;
+                    float* p = obase + (int64_t)tc0 * ldo + n;
                     const int nt = min(32, a.T - tc0);
-                    if (a.epi == TC_EPI_ADD) {
+                    if (add) {
 #pragma unroll
                         for (int i = 0; i < 32; i++)
-                            if (i < nt) p[(int64_t)i * a.ldo] += __uint_as_float(v[i]) + bias;
+                            if (i < nt) p[(int64_t)i * ldo] += __uint_as_float(v[i]) + bias;
                     } else {
 #pragma unroll
                         for (int i = 0; i < 32; i++)
-                            if (i < nt) p[(int64_t)i * a.ldo] = __uint_as_float(v[i]) + bias;
+                            if (i < nt) p[(int64_t)i * ldo] = __uint_as_float(v[i]) + bias;
                     }
                 }
             }
@@ -247,6 +257,40 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant_
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(G::TMEM_COLS) : "memory");
+    }
+}
+
+// out[t][n] (+)= sum over the split-K slices of ws[s][t][n] (+ bias[n]), in slice order (deterministic)
+__global__ void __launch_bounds__(256) splitk_reduce_kernel(const float* __restrict__ ws, int splits, int T, int N, float* __restrict__ out,
+                                                            int64_t ldo, const float* __restrict__ bias, int epi) {
+    const int64_t n4 = (int64_t)T * N / 4;
+    for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < n4; g += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t e = g * 4;
+        const int t = (int)(e / N), n = (int)(e - (int64_t)t * N);
+        float4 acc = *(const float4*)(ws + e);
+        for (int s = 1; s < splits; s++) {
+            const float4 v = *(const float4*)(ws + (size_t)s * T * N + e);
+            acc.x += v.x;
+            acc.y += v.y;
+            acc.z += v.z;
+            acc.w += v.w;
+        }
+        if (bias) {
+            const float4 b = *(const float4*)(bias + n);
+            acc.x += b.x;
+            acc.y += b.y;
+            acc.z += b.z;
+            acc.w += b.w;
+        }
+        float4* o = (float4*)(out + (int64_t)t * ldo + n);
+        if (epi == TC_EPI_ADD) {
+            const float4 r = *o;
+            acc.x += r.x;
+            acc.y += r.y;
+            acc.z += r.z;
+            acc.w += r.w;
+        }
+        *o = acc;
     }
 }
 
@@ -412,16 +456,42 @@ int launch_tc(const TcGemmArgs& a, cudaStream_t st) {
         B2_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
         attr_set = true;
     }
-    const int tiles = ((a.N + TC_BM - 1) / TC_BM) * ((a.T + BN - 1) / BN);
+    const int tiles = ((a.N + TC_BM - 1) / TC_BM) * ((a.T + BN - 1) / BN) * (a.splits > 1 ? a.splits : 1);
     const int grid = tiles < sm_count() ? tiles : sm_count();
     tc_gemm_kernel<BN><<<grid, G::THREADS, G::SMEM, st>>>(mw, mx, a);
     B2_CUDA_CHECK(cudaGetLastError());
+    if (a.splits > 1) {
+        const int64_t n4 = (int64_t)a.T * a.N / 4;
+        const int blocks = (int)std::min<int64_t>((n4 + 255) / 256, 148 * 8);
+        splitk_reduce_kernel<<<blocks, 256, 0, st>>>(a.ws, a.splits, a.T, a.N, a.out, a.ldo, a.bias, a.epi);
+        B2_CUDA_CHECK(cudaGetLastError());
+    }
     return 0;
 }
 
 }  // namespace
 
-int launch_tc_gemm(const TcGemmArgs& a, cudaStream_t st) {
+int tc_gemm_splits(int N, int K, int T) {
+    // few output tiles (short prompts, decode batches): cut K so that about two waves of CTAs stream the matrix;
+    // each split keeps at least 8 K steps
+    const int tiles = ((N + TC_BM - 1) / TC_BM) * ((T + 127) / 128);
+    int s = 1;
+    while (s < 8 && tiles * s < 2 * sm_count() && (K / TC_BK) % (2 * s) == 0 && K / TC_BK / (2 * s) >= 8) s *= 2;
+    return s;
+}
+
+size_t tc_gemm_ws_bytes(int N, int K, int T) {
+    const int s = tc_gemm_splits(N, K, T);
+    return s > 1 ? (size_t)s * T * N * sizeof(float) : 0;
+}
+
+int launch_tc_gemm(const TcGemmArgs& a_in, cudaStream_t st) {
+    TcGemmArgs a = a_in;
+    a.splits = 1;
+    if (a.ws && a.T <= 128 && a.N % 4 == 0 && a.ldo % 4 == 0) {
+        const int s = tc_gemm_splits(a.N, a.K, a.T);
+        if (s > 1 && (size_t)s * a.T * a.N * sizeof(float) <= a.ws_bytes) a.splits = s;
+    }
     if (!a.w || !a.x || !a.out || a.N <= 0 || a.K <= 0 || a.T <= 0 || a.K % TC_BK || ((uintptr_t)a.w & 15) || ((uintptr_t)a.x & 15)) {
         set_error("tc_gemm: bad arguments (N=%d K=%d T=%d; K must be a multiple of %d, operands 16-byte aligned)", a.N, a.K, a.T, TC_BK);
         return B2_EINVAL;

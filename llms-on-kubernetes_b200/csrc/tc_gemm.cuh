@@ -26,7 +26,13 @@ struct TcGemmArgs {
     int N, K, T;
     int64_t ldo;
     int epi;                  // TC_EPI_STORE: out = acc (+ bias); TC_EPI_ADD: out += acc (+ bias)
+    // split-K workspace (optional): with T <= 128 and few output tiles the launcher cuts K across `splits` CTAs per
+    // tile, partial sums go to ws[splits][T][N] and a second kernel reduces them in a fixed order
+    float* ws;
+    size_t ws_bytes;
+    int splits;               // set by launch_tc_gemm
 };
+size_t tc_gemm_ws_bytes(int N, int K, int T);   // workspace that lets launch_tc_gemm split K for this shape (0: no split)
 
 // K must be a multiple of TC_BK; w and x 16-byte aligned
 int launch_tc_gemm(const TcGemmArgs& a, cudaStream_t st);

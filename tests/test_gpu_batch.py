@@ -119,7 +119,7 @@ def test_decode_batch_argument_checks(b2, tiny_models):
     m = b2.Model(tiny_models["tiny-llama-q4_k_m"])
     ctx = b2.Context(m, 64, n_slots=2)
     with pytest.raises(b2.B2Error):
-        ctx.decode_batch([1] * 33, list(range(33)))          # more than 32 columns
+        ctx.decode_batch([1] * 257, [0] * 257)               # more than 256 columns
     with pytest.raises(b2.B2Error):
         ctx.decode_batch([1], [64])                           # position outside the context
     with pytest.raises(b2.B2Error):
@@ -157,4 +157,44 @@ def test_batch_sizes_change_past_the_first_attention_split(b2, tiny_models, monk
         if pos in want and want[pos] is not None:
             assert np.abs(lg[0] - want[pos]).max() <= 0.03 * np.abs(want[pos]).max(), pos
     assert pos == 333
+    ctx.free(); m.free(); ref.close()
+
+
+@pytest.mark.parametrize("name", ["tiny-llama-q4_k_m", "tiny-qwen2-q8_0"])
+def test_wide_batch_on_the_tensor_core_pass(b2, tiny_models, name):
+    """Batches of 16 and more columns (up to b2_ctx_max_batch = 256 with the fp16 copy resident) run the tcgen05 pass
+    with per-column positions and slots: 70 sequences of different lengths decoded together, every column against the
+    oracle's own decode of that sequence."""
+    path = tiny_models[name]
+    m = b2.Model(path)
+    B, steps = 70, 3
+    ctx = b2.Context(m, 96, n_slots=B)
+    assert ctx.max_batch() == 256
+    ref = rm.RefGGUFModel(path, n_ctx=96)
+    rng = np.random.default_rng(3)
+    lens = [int(rng.integers(1, 40)) for _ in range(B)]
+    prompts = [rng.integers(3, m.info.vocab, size=n).tolist() for n in lens]
+    follow = [rng.integers(3, m.info.vocab, size=steps).tolist() for _ in range(B)]
+    # oracle: each sequence on its own, logits after the prompt's last token and after every forced follow-up token
+    want = []
+    for s in range(B):
+        seq = prompts[s] + follow[s]
+        rows = []
+        for p, t in enumerate(seq):
+            _, lr = ref.decode(t, p, want_logits=p >= lens[s] - 1)
+            if p >= lens[s] - 1:
+                rows.append(lr)
+        want.append(rows)
+    # prompts: all sequences advance together, one column each (ragged: finished prompts drop out)
+    for p in range(max(lens)):
+        cols = [s for s in range(B) if p < lens[s]]
+        ids, lg = ctx.decode_batch([prompts[s][p] for s in cols], [p] * len(cols), slots=cols)
+        for j, s in enumerate(cols):
+            if p == lens[s] - 1:
+                assert np.abs(lg[j] - want[s][0]).max() <= 0.03 * np.abs(want[s][0]).max(), (s, p)
+    for i in range(steps):
+        ids, lg = ctx.decode_batch([follow[s][i] for s in range(B)], [lens[s] + i for s in range(B)], slots=list(range(B)))
+        for s in range(B):
+            assert np.abs(lg[s] - want[s][1 + i]).max() <= 0.03 * np.abs(want[s][1 + i]).max(), (s, i)
+            assert ids[s] == int(np.argmax(lg[s]))
     ctx.free(); m.free(); ref.close()
