@@ -963,9 +963,10 @@ int ensure_prefill(b2_ctx* c) {
     B2_CUDA_CHECK(cudaMalloc(&p.xb, cap * max_k * 2));
     if (!c->m->f16_cache) B2_CUDA_CHECK(cudaMalloc(&p.wb, max_w * 2));   // one matrix at a time, dequantised per pass
     if ((rc = dmalloc(&p.tok, cap))) return rc;
-    // split-K workspace for passes of up to 128 rows (short prompts, decode batches)
+    // split-K workspace: the largest any mat-mul of a pass of up to `cap` rows asks for
     const int shapes[5][2] = {{(int)(qdim + 2 * kvdim), I.d_model}, {I.d_model, (int)qdim}, {2 * I.d_ff, I.d_model}, {I.d_model, I.d_ff}, {I.vocab, I.d_model}};
-    for (const auto& s : shapes) p.ws_bytes = std::max(p.ws_bytes, tc_gemm_ws_bytes(s[0], s[1], 128));
+    for (const auto& s : shapes)
+        for (size_t T = 128; T < 2 * cap; T *= 2) p.ws_bytes = std::max(p.ws_bytes, tc_gemm_ws_bytes(s[0], s[1], (int)std::min(T, cap)));
     if (p.ws_bytes) B2_CUDA_CHECK(cudaMalloc(&p.ws, p.ws_bytes));
     p.cap = (int)cap;
     return 0;
@@ -988,6 +989,19 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
     __half* wb = (__half*)p.wb;
     auto dq = [&](const b2_model::W& w, __half* dst) { return launch_dequant_f16(w.type, w.p, dst, (int64_t)w.rows * w.cols, st); };
     const __half* cache = (const __half*)m->f16_cache;
+    // B2_TC_TRACE=1 (with B2_NO_GRAPH=1): device time per kernel family of this pass, printed to stderr
+    static const bool trace = env_flag("B2_TC_TRACE");
+    std::vector<cudaEvent_t> ev;
+    std::vector<int> ev_cat;
+    auto mark = [&](int cat) {   // the work enqueued since the previous mark belongs to family `cat`
+        if (!trace) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, st);
+        ev.push_back(e);
+        ev_cat.push_back(cat);
+    };
+    mark(-1);
     auto mm = [&](const __half* w, int N, int K, float* out, int64_t ldo, int epi) {
         TcGemmArgs a{};
         a.w = w;
@@ -1000,7 +1014,10 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         a.epi = epi;
         a.ws = p.ws;
         a.ws_bytes = p.ws_bytes;
-        return launch_tc_gemm(a, st);
+        mark(1);
+        const int r = launch_tc_gemm(a, st);
+        mark(0);
+        return r;
     };
     if ((rc = launch_embed_rows(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, tok_dev, T, p.x, st))) return rc;
     for (int il = 0; il < I.n_layer; il++) {
@@ -1035,7 +1052,9 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         qa.col_pos = col_pos;
         qa.col_slot = col_slot;
         qa.slot_stride = c->slot_stride;
+        mark(0);
         if ((rc = launch_prefill_qkv_post(qa, T, st))) return rc;
+        mark(1);
         if (col_pos) {
             if ((rc = launch_attn_decode(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, col_pos, 0, batch_attn_splits(c->n_ctx),
                                          c->bt.attn_scratch, st, false, T, col_slot, c->slot_stride, ATTN_BATCH_SPLIT_TOKENS, c->bt.cap)))
@@ -1043,6 +1062,7 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         } else if ((rc = launch_prefill_attn(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, T, pos0, st))) {
             return rc;
         }
+        mark(2);
         // output projection + residual
         if ((rc = launch_rows_to_f16(p.attn_out, qdim, nullptr, 0.0f, qdim, T, gemm_act_for_type(L.wo.type), xb, st))) return rc;
         if (!cache && (rc = dq(L.wo, wb))) return rc;
@@ -1058,6 +1078,18 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         if ((rc = launch_rows_to_f16(p.gu, 2 * (int64_t)I.d_ff, nullptr, 0.0f, I.d_ff, T, gemm_act_for_type(L.down.type), xb, st))) return rc;
         if (!cache && (rc = dq(L.down, wb))) return rc;
         if ((rc = mm(cache ? cache + m->f16_off[il].down : wb, I.d_model, I.d_ff, p.x, I.d_model, TC_EPI_ADD))) return rc;
+    }
+    if (trace && ev.size() > 1) {
+        cudaStreamSynchronize(st);
+        float tot[3] = {0, 0, 0};
+        for (size_t i = 1; i < ev.size(); i++) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, ev[i - 1], ev[i]);
+            if (ev_cat[i] >= 0) tot[ev_cat[i]] += ms;
+        }
+        for (cudaEvent_t e : ev) cudaEventDestroy(e);
+        fprintf(stderr, "[b2 tc pass] rows=%d %s: mat-mul (+split-K reduce) %.3f ms, elementwise %.3f ms, attention %.3f ms\n", T,
+                col_pos ? "batch" : "prompt", tot[0], tot[1], tot[2]);
     }
     return 0;
 }

@@ -471,12 +471,16 @@ int launch_tc(const TcGemmArgs& a, cudaStream_t st) {
 
 }  // namespace
 
+// token tile: 256 columns per tile halve the shared-memory traffic per flop; up to 128 rows fit the 128-column tile
+static int tc_tile_cols(int T) { return T > 128 ? 256 : 128; }
+
 int tc_gemm_splits(int N, int K, int T) {
-    // few output tiles (short prompts, decode batches): cut K so that about two waves of CTAs stream the matrix;
-    // each split keeps at least 8 K steps
-    const int tiles = ((N + TC_BM - 1) / TC_BM) * ((T + 127) / 128);
+    // fewer output tiles than SMs (short prompts, decode batches, narrow matrices): cut K until every SM streams a
+    // share of the matrix; each split keeps at least 8 K steps
+    const int bn = tc_tile_cols(T);
+    const int tiles = ((N + TC_BM - 1) / TC_BM) * ((T + bn - 1) / bn);
     int s = 1;
-    while (s < 8 && tiles * s < 2 * sm_count() && (K / TC_BK) % (2 * s) == 0 && K / TC_BK / (2 * s) >= 8) s *= 2;
+    while (s < 8 && tiles * s < sm_count() && (K / TC_BK) % (2 * s) == 0 && K / TC_BK / (2 * s) >= 8) s *= 2;
     return s;
 }
 
@@ -488,7 +492,7 @@ size_t tc_gemm_ws_bytes(int N, int K, int T) {
 int launch_tc_gemm(const TcGemmArgs& a_in, cudaStream_t st) {
     TcGemmArgs a = a_in;
     a.splits = 1;
-    if (a.ws && a.T <= 128 && a.N % 4 == 0 && a.ldo % 4 == 0) {
+    if (a.ws && a.N % 4 == 0 && a.ldo % 4 == 0) {
         const int s = tc_gemm_splits(a.N, a.K, a.T);
         if (s > 1 && (size_t)s * a.T * a.N * sizeof(float) <= a.ws_bytes) a.splits = s;
     }
@@ -496,10 +500,7 @@ int launch_tc_gemm(const TcGemmArgs& a_in, cudaStream_t st) {
         set_error("tc_gemm: bad arguments (N=%d K=%d T=%d; K must be a multiple of %d, operands 16-byte aligned)", a.N, a.K, a.T, TC_BK);
         return B2_EINVAL;
     }
-    // 256-token tiles halve the shared-memory traffic per flop; 128-token tiles when that would leave SMs without a tile
-    const int tiles256 = ((a.N + TC_BM - 1) / TC_BM) * ((a.T + 255) / 256);
-    if (a.T > 128 && tiles256 >= sm_count()) return launch_tc<256>(a, st);
-    return launch_tc<128>(a, st);
+    return tc_tile_cols(a.T) == 256 ? launch_tc<256>(a, st) : launch_tc<128>(a, st);
 }
 
 int launch_dequant_f16(int type, const void* src, __half* dst, int64_t n, cudaStream_t st) {

@@ -26,8 +26,9 @@ struct TcGemmArgs {
     int N, K, T;
     int64_t ldo;
     int epi;                  // TC_EPI_STORE: out = acc (+ bias); TC_EPI_ADD: out += acc (+ bias)
-    // split-K workspace (optional): with T <= 128 and few output tiles the launcher cuts K across `splits` CTAs per
-    // tile, partial sums go to ws[splits][T][N] and a second kernel reduces them in a fixed order
+    // split-K workspace (optional): with few output tiles (short prompts, decode batches, narrow matrices) the launcher
+    // cuts K across `splits` CTAs per tile, partial sums go to ws[splits][T][N] and a second kernel reduces them in a
+    // fixed order
     float* ws;
     size_t ws_bytes;
     int splits;               // set by launch_tc_gemm
