@@ -248,7 +248,7 @@ int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, in
     // activations quantised as the reference's mat-mul with this weight type quantises them (Q8_K / Q8_0), then fp16
     int fmt = gemm_act_for_type(type);
     if ((fmt == ACT_Q8K && K % 256) || (fmt == ACT_Q80 && K % 32)) fmt = -1;
-    if ((rc = launch_rows_to_f16(x_dev, K, nullptr, 0.0f, (int)K, T, fmt, xb, (cudaStream_t)stream))) return rc;
+    if ((rc = launch_rows_to_f16(const_cast<float*>(x_dev), K, nullptr, 0.0f, (int)K, T, fmt, xb, (cudaStream_t)stream))) return rc;
     TcGemmArgs a{};
     a.w = wb;
     a.x = xb;

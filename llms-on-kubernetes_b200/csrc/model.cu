@@ -1002,7 +1002,8 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         ev_cat.push_back(cat);
     };
     mark(-1);
-    auto mm = [&](const __half* w, int N, int K, float* out, int64_t ldo, int epi) {
+    // defer != nullptr: a split-K reduction (and the epilogue) is left to the kernel that consumes the output
+    auto mm = [&](const __half* w, int N, int K, float* out, int64_t ldo, int epi, TcParts* defer) {
         TcGemmArgs a{};
         a.w = w;
         a.x = xb;
@@ -1015,10 +1016,11 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         a.ws = p.ws;
         a.ws_bytes = p.ws_bytes;
         mark(1);
-        const int r = launch_tc_gemm(a, st);
+        const int r = launch_tc_gemm(a, st, defer);
         mark(0);
         return r;
     };
+    TcParts pend{nullptr, 1, 0};   // residual mat-mul (O, down) whose slices the next norm kernel adds into x
     if ((rc = launch_embed_rows(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, tok_dev, T, p.x, st))) return rc;
     for (int il = 0; il < I.n_layer; il++) {
         const auto& L = m->layers[il];
@@ -1026,15 +1028,20 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         __half* kc = c->k_cache + (size_t)(col_pos ? 0 : slot) * c->slot_stride + il * kv_layer;
         __half* vc = c->v_cache + (size_t)(col_pos ? 0 : slot) * c->slot_stride + il * kv_layer;
         // RMSNorm -> one mat-mul over the stacked Q | K | V matrices -> bias, RoPE, KV cache
-        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.wq.type), xb, st))) return rc;
+        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.wq.type), xb, st, pend)))
+            return rc;
         if (!cache) {
             if ((rc = dq(L.wq, wb))) return rc;
             if ((rc = dq(L.wk, wb + (size_t)qdim * I.d_model))) return rc;
             if ((rc = dq(L.wv, wb + (size_t)(qdim + kvdim) * I.d_model))) return rc;
         }
-        if ((rc = mm(cache ? cache + m->f16_off[il].qkv : wb, qdim + 2 * kvdim, I.d_model, p.qkv, qdim + 2 * kvdim, TC_EPI_STORE))) return rc;
+        TcParts parts;
+        if ((rc = mm(cache ? cache + m->f16_off[il].qkv : wb, qdim + 2 * kvdim, I.d_model, p.qkv, qdim + 2 * kvdim, TC_EPI_STORE, &parts))) return rc;
         PrefillQkvArgs qa{};
         qa.qkv = p.qkv;
+        qa.parts_ws = parts.ws;
+        qa.parts_splits = parts.splits;
+        qa.parts_slice = parts.slice;
         qa.bq = L.bq;
         qa.bk = L.bk;
         qa.bv = L.bv;
@@ -1066,18 +1073,20 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         // output projection + residual
         if ((rc = launch_rows_to_f16(p.attn_out, qdim, nullptr, 0.0f, qdim, T, gemm_act_for_type(L.wo.type), xb, st))) return rc;
         if (!cache && (rc = dq(L.wo, wb))) return rc;
-        if ((rc = mm(cache ? cache + m->f16_off[il].o : wb, I.d_model, qdim, p.x, I.d_model, TC_EPI_ADD))) return rc;
-        // RMSNorm -> stacked gate | up -> SwiGLU -> down + residual
-        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.gate.type), xb, st))) return rc;
+        if ((rc = mm(cache ? cache + m->f16_off[il].o : wb, I.d_model, qdim, p.x, I.d_model, TC_EPI_ADD, &pend))) return rc;
+        // (+ the O slices) RMSNorm -> stacked gate | up -> SwiGLU -> down + residual
+        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.gate.type), xb, st, pend)))
+            return rc;
         if (!cache) {
             if ((rc = dq(L.gate, wb))) return rc;
             if ((rc = dq(L.up, wb + (size_t)I.d_ff * I.d_model))) return rc;
         }
-        if ((rc = mm(cache ? cache + m->f16_off[il].gate_up : wb, 2 * I.d_ff, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE))) return rc;
-        if ((rc = launch_swiglu_rows(p.gu, I.d_ff, T, il == I.n_layer - 1 ? c->h : nullptr, st))) return rc;
-        if ((rc = launch_rows_to_f16(p.gu, 2 * (int64_t)I.d_ff, nullptr, 0.0f, I.d_ff, T, gemm_act_for_type(L.down.type), xb, st))) return rc;
+        if ((rc = mm(cache ? cache + m->f16_off[il].gate_up : wb, 2 * I.d_ff, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE, &parts))) return rc;
+        if ((rc = launch_swiglu_to_f16(p.gu, parts, I.d_ff, T, gemm_act_for_type(L.down.type), xb, il == I.n_layer - 1 ? c->h : nullptr, st))) return rc;
         if (!cache && (rc = dq(L.down, wb))) return rc;
-        if ((rc = mm(cache ? cache + m->f16_off[il].down : wb, I.d_model, I.d_ff, p.x, I.d_model, TC_EPI_ADD))) return rc;
+        // the last layer's down projection reduces its own slices: nothing after it in this pass reads x through a norm kernel
+        const bool last = il == I.n_layer - 1;
+        if ((rc = mm(cache ? cache + m->f16_off[il].down : wb, I.d_model, I.d_ff, p.x, I.d_model, TC_EPI_ADD, last ? nullptr : &pend))) return rc;
     }
     if (trace && ev.size() > 1) {
         cudaStreamSynchronize(st);
@@ -1125,7 +1134,8 @@ int enqueue_logits_tc(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t
     const b2_model_info& I = m->info;
     int rc;
     __half* xb = (__half*)c->pf.xb;
-    if ((rc = launch_rows_to_f16(x_rows, I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits, gemm_act_for_type(m->output.type), xb, st)))
+    if ((rc = launch_rows_to_f16(const_cast<float*>(x_rows), I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits,
+                                 gemm_act_for_type(m->output.type), xb, st)))
         return rc;
     TcGemmArgs a{};
     a.w = (const __half*)m->f16_cache + m->f16_output;

@@ -58,10 +58,14 @@ struct PrefillQkvArgs {
     // point at slot 0); nullptr: row t is position pos0 + t of the one sequence k_cache / v_cache belong to
     const int32_t *col_pos, *col_slot;
     int64_t slot_stride;
+    // the mat-mul's split-K reduction deferred to this kernel (tc_gemm.cuh TcParts): splits > 1 -> element (t, col) is
+    // the sum over s of parts_ws[s * parts_slice + t * (nq + 2 nk) + col] and qkv is not read
+    const float* parts_ws;
+    int parts_splits;
+    size_t parts_slice;
 };
 int launch_embed_rows(int type, const void* table, int64_t row_bytes, int d_model, int vocab, const int32_t* tokens, int T, float* x, cudaStream_t st);
 int launch_prefill_qkv_post(const PrefillQkvArgs& a, int T, cudaStream_t st);
-int launch_swiglu_rows(float* gu, int d_ff, int T, float* h_last, cudaStream_t st);
 int launch_argmax_rows(const float* logits, int64_t n, int rows, int32_t* out, cudaStream_t st);
 
 }  // namespace b2

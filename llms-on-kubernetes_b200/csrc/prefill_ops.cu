@@ -1,6 +1,6 @@
 // prefill_ops.cu -- the elementwise kernels between the prompt-phase mat-muls (tc_gemm.cu) and attention
 // (prefill_attn.cu), each over all T prompt rows at once: embedding rows (row a10), bias + RoPE + KV-cache store
-// (rows a13, a15), SwiGLU (row a11's activation).  Same formulas as the fused epilogues of the decode kernels
+// (rows a13, a15), greedy sampling over rows of logits (row a16).  Same formulas as the fused epilogues of the decode kernels
 // (gemv_device.cuh / gemm.cu), so a prompt and a token-by-token replay agree to rounding.
 #include <cuda_fp16.h>
 
@@ -28,7 +28,14 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
     const int pi = blockIdx.x * blockDim.x + threadIdx.x;
     const int nq2 = a.nq / 2, nk2 = a.nk / 2;
     if (pi >= nq2 + 2 * nk2) return;
-    const float* row = a.qkv + (size_t)t * (a.nq + 2 * a.nk);
+    const size_t row_off = (size_t)t * (a.nq + 2 * a.nk);
+    // element `col` of this row of the mat-mul output: the buffer, or the sum of its deferred split-K slices
+    auto val = [&](int col) {
+        if (a.parts_splits <= 1) return a.qkv[row_off + col];
+        float v = 0.0f;
+        for (int s = 0; s < a.parts_splits; s++) v += a.parts_ws[s * a.parts_slice + row_off + col];
+        return v;
+    };
     const int pos = a.col_pos ? a.col_pos[t] : a.pos0 + t;
     const size_t slot_off = a.col_slot ? (size_t)a.col_slot[t] * a.slot_stride : 0;
     const int hd = a.head_dim, hp = hd / 2;
@@ -38,9 +45,9 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
         const int head = lp / hp, i = lp - head * hp;    // pair i of the head
         const int ea = a.neox ? head * hd + i : head * hd + 2 * i;
         const int eb = a.neox ? ea + hp : ea + 1;
-        const float* src = row + (is_q ? 0 : a.nq);
+        const int src = is_q ? 0 : a.nq;
         const float* bias = is_q ? a.bq : a.bk;
-        float va = src[ea], vb = src[eb];
+        float va = val(src + ea), vb = val(src + eb);
         if (bias) {
             va += bias[ea];
             vb += bias[eb];
@@ -63,31 +70,13 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
     } else {
         const int lp = pi - nq2 - nk2;
         const int ea = 2 * lp, head = ea / hd;
-        float va = row[a.nq + a.nk + ea], vb = row[a.nq + a.nk + ea + 1];
+        float va = val(a.nq + a.nk + ea), vb = val(a.nq + a.nk + ea + 1);
         if (a.bv) {
             va += a.bv[ea];
             vb += a.bv[ea + 1];
         }
         __half* dst = a.v_cache + slot_off + ((size_t)head * a.n_ctx + pos) * hd + (ea - head * hd);
         *(__half2*)dst = __floats2half2_rn(va, vb);
-    }
-}
-
-// gu: [T][2 d_ff] = gate | up  ->  the gate half becomes h = silu(gate) * up in place (fp32; the down projection's
-// activation quantiser reads it with row stride 2 d_ff); the last row also goes to h_last
-__global__ void __launch_bounds__(256) swiglu_rows_kernel(float* __restrict__ gu, int d_ff, int T, float* __restrict__ h_last) {
-    const int t = blockIdx.y;
-    float* g = gu + (size_t)t * 2 * d_ff;
-    const float* u = g + d_ff;
-    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) * 4; i < d_ff; i += gridDim.x * blockDim.x * 4) {
-        const float4 a = *(const float4*)(g + i), b = *(const float4*)(u + i);
-        float4 h;
-        h.x = (a.x / (1.0f + expf(-a.x))) * b.x;
-        h.y = (a.y / (1.0f + expf(-a.y))) * b.y;
-        h.z = (a.z / (1.0f + expf(-a.z))) * b.z;
-        h.w = (a.w / (1.0f + expf(-a.w))) * b.w;
-        *(float4*)(g + i) = h;
-        if (h_last && t == T - 1) *(float4*)(h_last + i) = h;
     }
 }
 
@@ -162,17 +151,6 @@ int launch_prefill_qkv_post(const PrefillQkvArgs& a, int T, cudaStream_t st) {
     const int pairs = a.nq / 2 + a.nk;
     const dim3 grid((pairs + 255) / 256, T);
     qkv_post_kernel<<<grid, 256, 0, st>>>(a);
-    B2_CUDA_CHECK(cudaGetLastError());
-    return 0;
-}
-
-int launch_swiglu_rows(float* gu, int d_ff, int T, float* h_last, cudaStream_t st) {
-    if (d_ff % 4 || T <= 0) {
-        set_error("swiglu_rows: bad shape");
-        return B2_EINVAL;
-    }
-    const dim3 grid(std::min((d_ff / 4 + 255) / 256, 16), T);
-    swiglu_rows_kernel<<<grid, 256, 0, st>>>(gu, d_ff, T, h_last);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

@@ -310,19 +310,87 @@ __global__ void dequant_f16_kernel(const uint8_t* __restrict__ src, uint4* __res
     }
 }
 
-// One CTA per row: optional RMS norm (ggml's: fp32 squares summed in double, (x * scale) * w), then the reference's
-// activation quantisation REPRODUCED and folded back: the row is quantised exactly as ggml's quantize_row_q8_K
-// (FMT = ACT_Q8K: 256-element blocks, iscale = -127 / signed max, nearest-int) or quantize_row_q8_0 (ACT_Q80:
-// 32-element blocks, d = amax / 127 stored as fp16, roundf) would, and y = fp16(d * q).  d * q has at most 8 + 11
-// significant bits, so the only new rounding is the final one to fp16 (2^-11 relative) -- the mat-mul then sees the
-// same quantised activations as the reference's integer dot products.  FMT < 0: plain rounding to fp16.
+// The reference's activation quantisation REPRODUCED and folded back, 8 consecutive elements per lane of a warp that
+// covers a 256-element span: the values are quantised exactly as ggml's quantize_row_q8_K (FMT = ACT_Q8K: one
+// 256-element block per warp, iscale = -127 / signed max, nearest-int) or quantize_row_q8_0 (ACT_Q80: 32-element
+// blocks = 4 lanes, d = amax / 127 stored as fp16, roundf) would, and replaced by d * q.  d * q has at most 8 + 11
+// significant bits, so the only new rounding is the caller's final one to fp16 (2^-11 relative): the mat-mul then
+// sees the same quantised activations as the reference's integer dot products.  FMT < 0: values unchanged.
+// Warp-collective: every lane calls it (lanes past the row end with zeros).
 template <int FMT>
-__global__ void __launch_bounds__(256) rows_to_f16_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, float eps, int n,
-                                                          __half* __restrict__ y) {
+__device__ __forceinline__ void act_requantise8(float (&v)[8]) {
+    if (FMT == ACT_Q8K) {
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+        const float wmax = warp_max(amax);
+        // the FIRST element of the block attaining the maximum magnitude gives the sign of the scale
+        int first = 8;
+#pragma unroll
+        for (int i = 7; i >= 0; i--)
+            if (fabsf(v[i]) == wmax) first = i;
+        const uint32_t owners = __ballot_sync(0xffffffffu, first < 8);
+        float mval = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            if (i == first) mval = v[i];
+        mval = __shfl_sync(0xffffffffu, mval, owners ? __ffs(owners) - 1 : 0);
+        if (wmax != 0.0f) {
+            const float iscale = -127.0f / mval;
+            const float d = 1.0f / iscale;
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = d * (float)min(127, __float2int_rn(iscale * v[i]));
+        }
+    } else if (FMT == ACT_Q80) {
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+        const float d = amax / 127.0f;
+        const float id = d != 0.0f ? 1.0f / d : 0.0f;
+        const float d16 = __half2float(__float2half_rn(d));
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = d16 * (float)(int)roundf(v[i] * id);
+    }
+}
+
+// 8 consecutive floats of a mat-mul output: from the output buffer, or summed over the split-K slices in slice order
+__device__ __forceinline__ void load8_parts(const float* __restrict__ direct, const TcParts& pp, size_t off, float (&v)[8]) {
+    if (pp.splits > 1) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = 0.0f;
+        for (int s = 0; s < pp.splits; s++) {
+            const float4 p0 = *(const float4*)(pp.ws + s * pp.slice + off), p1 = *(const float4*)(pp.ws + s * pp.slice + off + 4);
+            v[0] += p0.x; v[1] += p0.y; v[2] += p0.z; v[3] += p0.w; v[4] += p1.x; v[5] += p1.y; v[6] += p1.z; v[7] += p1.w;
+        }
+    } else {
+        const float4 p0 = *(const float4*)(direct + off), p1 = *(const float4*)(direct + off + 4);
+        v[0] = p0.x; v[1] = p0.y; v[2] = p0.z; v[3] = p0.w; v[4] = p1.x; v[5] = p1.y; v[6] = p1.z; v[7] = p1.w;
+    }
+}
+
+// One CTA per row.  (0) a pending split-K residual: x[row] += sum of the slices of the previous mat-mul (its deferred
+// epilogue; row stride n in the slices); (1) optional RMS norm (ggml's: fp32 squares summed in double, (x * scale) * w);
+// (2) the activation quantisation of the mat-mul that follows (act_requantise8) and the rounding to fp16.
+template <int FMT>
+__global__ void __launch_bounds__(256) rows_to_f16_kernel(float* __restrict__ x, int64_t ldx, const float* __restrict__ w, float eps, int n,
+                                                          __half* __restrict__ y, const TcParts pend) {
     __shared__ double ss_warp[8];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const float* xr = x + (int64_t)blockIdx.x * ldx;
+    float* xr = x + (int64_t)blockIdx.x * ldx;
     __half* yr = y + (int64_t)blockIdx.x * n;
+    if (pend.splits > 1) {
+        for (int i0 = tid * 8; i0 < n; i0 += 256 * 8) {
+            float v[8];
+            load8_parts(nullptr, pend, (size_t)blockIdx.x * n + i0, v);
+            float4 p0 = *(const float4*)(xr + i0), p1 = *(const float4*)(xr + i0 + 4);
+            p0.x += v[0]; p0.y += v[1]; p0.z += v[2]; p0.w += v[3]; p1.x += v[4]; p1.y += v[5]; p1.z += v[6]; p1.w += v[7];
+            *(float4*)(xr + i0) = p0;
+            *(float4*)(xr + i0 + 4) = p1;
+        }
+        __syncthreads();   // the row is re-read below by other threads of this CTA
+    }
     float scale = 1.0f;
     if (w) {
         double ss = 0.0;
@@ -359,41 +427,39 @@ __global__ void __launch_bounds__(256) rows_to_f16_kernel(const float* __restric
 #pragma unroll
             for (int i = 0; i < 8; i++) v[i] = 0.0f;
         }
-        if (FMT == ACT_Q8K) {
-            float amax = 0.0f;
-#pragma unroll
-            for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
-            const float wmax = warp_max(amax);
-            // the FIRST element of the block attaining the maximum magnitude gives the sign of the scale
-            int first = 8;
-#pragma unroll
-            for (int i = 7; i >= 0; i--)
-                if (fabsf(v[i]) == wmax) first = i;
-            const uint32_t owners = __ballot_sync(0xffffffffu, first < 8);
-            float mval = 0.0f;
-#pragma unroll
-            for (int i = 0; i < 8; i++)
-                if (i == first) mval = v[i];
-            mval = __shfl_sync(0xffffffffu, mval, owners ? __ffs(owners) - 1 : 0);
-            if (wmax != 0.0f) {
-                const float iscale = -127.0f / mval;
-                const float d = 1.0f / iscale;
-#pragma unroll
-                for (int i = 0; i < 8; i++) v[i] = d * (float)min(127, __float2int_rn(iscale * v[i]));
-            }
-        } else if (FMT == ACT_Q80) {
-            float amax = 0.0f;
-#pragma unroll
-            for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(v[i]));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-            const float d = amax / 127.0f;
-            const float id = d != 0.0f ? 1.0f / d : 0.0f;
-            const float d16 = __half2float(__float2half_rn(d));
-#pragma unroll
-            for (int i = 0; i < 8; i++) v[i] = d16 * (float)(int)roundf(v[i] * id);
-        }
+        act_requantise8<FMT>(v);
         if (in) *(uint4*)(yr + i0) = make_uint4(pack_h2s(v[0], v[1]), pack_h2s(v[2], v[3]), pack_h2s(v[4], v[5]), pack_h2s(v[6], v[7]));
+    }
+}
+
+// One CTA per row of the stacked gate | up mat-mul output (gu[T][2 d_ff], or its split-K slices): h = silu(gate) * up
+// (the formula of the decode kernels' fused epilogue), quantised for the down projection and rounded to fp16; the
+// last row's h also in fp32 (h_last, b2_ctx_get_activation)
+template <int FMT>
+__global__ void __launch_bounds__(256) swiglu_to_f16_kernel(const float* __restrict__ gu, const TcParts parts, int d_ff, int T,
+                                                            __half* __restrict__ y, float* __restrict__ h_last) {
+    const int t = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t row = (size_t)t * 2 * d_ff;
+    for (int s = warp; s < (d_ff + 255) / 256; s += 8) {
+        const int i0 = (s << 8) + lane * 8;
+        const bool in = i0 < d_ff;
+        float v[8];
+        if (in) {
+            float g[8], u[8];
+            load8_parts(gu, parts, row + i0, g);
+            load8_parts(gu, parts, row + d_ff + i0, u);
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = (g[i] / (1.0f + expf(-g[i]))) * u[i];
+            if (h_last && t == T - 1) {
+                *(float4*)(h_last + i0) = make_float4(v[0], v[1], v[2], v[3]);
+                *(float4*)(h_last + i0 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = 0.0f;
+        }
+        act_requantise8<FMT>(v);
+        if (in) *(uint4*)(y + (size_t)t * d_ff + i0) = make_uint4(pack_h2s(v[0], v[1]), pack_h2s(v[2], v[3]), pack_h2s(v[4], v[5]), pack_h2s(v[6], v[7]));
     }
 }
 
@@ -460,7 +526,7 @@ int launch_tc(const TcGemmArgs& a, cudaStream_t st) {
     const int grid = tiles < sm_count() ? tiles : sm_count();
     tc_gemm_kernel<BN><<<grid, G::THREADS, G::SMEM, st>>>(mw, mx, a);
     B2_CUDA_CHECK(cudaGetLastError());
-    if (a.splits > 1) {
+    if (a.splits > 1 && !a.defer_reduce) {
         const int64_t n4 = (int64_t)a.T * a.N / 4;
         const int blocks = (int)std::min<int64_t>((n4 + 255) / 256, 148 * 8);
         splitk_reduce_kernel<<<blocks, 256, 0, st>>>(a.ws, a.splits, a.T, a.N, a.out, a.ldo, a.bias, a.epi);
@@ -489,9 +555,11 @@ size_t tc_gemm_ws_bytes(int N, int K, int T) {
     return s > 1 ? (size_t)s * T * N * sizeof(float) : 0;
 }
 
-int launch_tc_gemm(const TcGemmArgs& a_in, cudaStream_t st) {
+int launch_tc_gemm(const TcGemmArgs& a_in, cudaStream_t st, TcParts* deferred) {
     TcGemmArgs a = a_in;
     a.splits = 1;
+    a.defer_reduce = deferred != nullptr;
+    if (deferred) *deferred = TcParts{nullptr, 1, 0};
     if (a.ws && a.N % 4 == 0 && a.ldo % 4 == 0) {
         const int s = tc_gemm_splits(a.N, a.K, a.T);
         if (s > 1 && (size_t)s * a.T * a.N * sizeof(float) <= a.ws_bytes) a.splits = s;
@@ -500,6 +568,7 @@ int launch_tc_gemm(const TcGemmArgs& a_in, cudaStream_t st) {
         set_error("tc_gemm: bad arguments (N=%d K=%d T=%d; K must be a multiple of %d, operands 16-byte aligned)", a.N, a.K, a.T, TC_BK);
         return B2_EINVAL;
     }
+    if (deferred && a.splits > 1) *deferred = TcParts{a.ws, a.splits, (size_t)a.T * a.N};
     return tc_tile_cols(a.T) == 256 ? launch_tc<256>(a, st) : launch_tc<128>(a, st);
 }
 
@@ -529,7 +598,7 @@ int launch_dequant_f16(int type, const void* src, __half* dst, int64_t n, cudaSt
     return 0;
 }
 
-int launch_rows_to_f16(const float* x, int64_t ldx, const float* norm_w, float eps, int n, int rows, int act_fmt, __half* y, cudaStream_t st) {
+int launch_rows_to_f16(float* x, int64_t ldx, const float* norm_w, float eps, int n, int rows, int act_fmt, __half* y, cudaStream_t st, TcParts pend) {
     if (!x || !y || n <= 0 || rows <= 0 || n % 8 || ldx % 4 || ((uintptr_t)x & 15) || ((uintptr_t)y & 15) || (norm_w && ((uintptr_t)norm_w & 15))) {
         set_error("rows_to_f16: bad arguments (n=%d rows=%d)", n, rows);
         return B2_EINVAL;
@@ -538,9 +607,21 @@ int launch_rows_to_f16(const float* x, int64_t ldx, const float* norm_w, float e
         set_error("rows_to_f16: row length %d is not a whole number of activation blocks", n);
         return B2_EINVAL;
     }
-    if (act_fmt == ACT_Q8K) rows_to_f16_kernel<ACT_Q8K><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y);
-    else if (act_fmt == ACT_Q80) rows_to_f16_kernel<ACT_Q80><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y);
-    else rows_to_f16_kernel<-1><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y);
+    if (act_fmt == ACT_Q8K) rows_to_f16_kernel<ACT_Q8K><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend);
+    else if (act_fmt == ACT_Q80) rows_to_f16_kernel<ACT_Q80><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend);
+    else rows_to_f16_kernel<-1><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int launch_swiglu_to_f16(const float* gu, TcParts parts, int d_ff, int T, int act_fmt, __half* y, float* h_last, cudaStream_t st) {
+    if (!gu || !y || d_ff <= 0 || T <= 0 || d_ff % 8 || (act_fmt == ACT_Q8K && d_ff % 256) || (act_fmt == ACT_Q80 && d_ff % 32)) {
+        set_error("swiglu_to_f16: bad arguments (d_ff=%d T=%d)", d_ff, T);
+        return B2_EINVAL;
+    }
+    if (act_fmt == ACT_Q8K) swiglu_to_f16_kernel<ACT_Q8K><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last);
+    else if (act_fmt == ACT_Q80) swiglu_to_f16_kernel<ACT_Q80><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last);
+    else swiglu_to_f16_kernel<-1><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
