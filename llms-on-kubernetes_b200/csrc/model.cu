@@ -643,6 +643,20 @@ int batch_attn_splits(int n_ctx) {
     return s < 1 ? 1 : (s > ATTN_MAX_SPLITS ? ATTN_MAX_SPLITS : s);
 }
 
+// attention of n batch columns (positions / slots in device arrays) over their own sequences: the tensor-core kernel
+// (attn_batch.cu) when the context fits its chunking, attn.cu's otherwise (B2_ATTN_BATCH_OLD=1 forces the latter)
+int enqueue_batch_attention(b2_ctx* c, const float* q, const __half* kc, const __half* vc, float* out, const int32_t* col_pos,
+                            const int32_t* col_slot, int n, cudaStream_t st) {
+    const b2_model_info& I = c->m->info;
+    const int splits = batch_attn_splits(c->n_ctx);
+    static const bool old_kernel = env_flag("B2_ATTN_BATCH_OLD");
+    if (!old_kernel && attn_batch_supported(I.head_dim, c->n_ctx, splits))
+        return launch_attn_batch(q, kc, vc, out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, col_pos, col_slot, c->slot_stride, n, splits,
+                                 c->bt.attn_scratch, c->bt.cap, st);
+    return launch_attn_decode(q, kc, vc, out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, col_pos, 0, splits, c->bt.attn_scratch, st, false, n, col_slot,
+                              c->slot_stride, ATTN_BATCH_SPLIT_TOKENS, c->bt.cap);
+}
+
 int ensure_batch(b2_ctx* c) {
     if (c->bt.cap) return 0;
     const b2_model_info& I = c->m->info;
@@ -774,9 +788,7 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         a.n_seg = 3;
         if ((rc = run(a))) return rc;
         // attention of every column over its own sequence
-        if ((rc = launch_attn_decode(b.q, kc, vc, b.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, b.pos, 0, batch_attn_splits(c->n_ctx),
-                                     b.attn_scratch, st, false, n, b.slot, c->slot_stride, ATTN_BATCH_SPLIT_TOKENS, b.cap)))
-            return rc;
+        if ((rc = enqueue_batch_attention(c, b.q, kc, vc, b.attn_out, b.pos, b.slot, n, st))) return rc;
         // output projection + residual
         if ((rc = launch_act_quant(b.attn_out, qdim, nullptr, 0.0f, qdim, n, b.act, st, gemm_act_for_type(L.wo.type)))) return rc;
         common(a, qdim, n, I.d_model);
@@ -1063,9 +1075,7 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         if ((rc = launch_prefill_qkv_post(qa, T, st))) return rc;
         mark(1);
         if (col_pos) {
-            if ((rc = launch_attn_decode(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, col_pos, 0, batch_attn_splits(c->n_ctx),
-                                         c->bt.attn_scratch, st, false, T, col_slot, c->slot_stride, ATTN_BATCH_SPLIT_TOKENS, c->bt.cap)))
-                return rc;
+            if ((rc = enqueue_batch_attention(c, p.q, kc, vc, p.attn_out, col_pos, col_slot, T, st))) return rc;
         } else if ((rc = launch_prefill_attn(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, T, pos0, st))) {
             return rc;
         }

@@ -27,6 +27,13 @@ constexpr int ATTN_BATCH_SPLIT_TOKENS = 256;
 // col_slot[j] (caches slot_stride halfs apart); scratch of attn_scratch_bytes_batch()
 size_t attn_scratch_bytes_batch(int n_head, int head_dim, int max_splits, int n_cols);
 
+// attn_batch.cu: the same batched decode attention on the tensor cores (the step kernel's work item per (column, kv
+// head, 256-token chunk)); scratch and cols_cap as for launch_attn_decode's batched form, max_chunks * 256 >= n_ctx
+bool attn_batch_supported(int head_dim, int n_ctx, int max_chunks);
+int launch_attn_batch(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim, int n_ctx,
+                      const int* col_pos, const int* col_slot, int64_t slot_stride, int n_cols, int max_chunks, void* scratch, int cols_cap,
+                      cudaStream_t st);
+
 // misc.cu
 // x[d] = dequantised row *token_ptr of the embedding table (row a10)
 int launch_embed(int type, const void* table, int64_t row_bytes, int d_model, int vocab, const int32_t* token_ptr, float* x,
