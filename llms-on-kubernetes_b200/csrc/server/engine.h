@@ -83,6 +83,9 @@ struct Engine {
     std::thread sched;
     std::vector<float> logits;
     bool batch_ok = true;   // false: the model's types are not on the batched path -> one request at a time
+    // counters behind GET /metrics (Prometheus text; llama.cpp's metric names where it has one)
+    std::atomic<uint64_t> m_requests{0}, m_prompt_tokens{0}, m_prompt_reused{0}, m_predicted{0}, m_passes{0}, m_pass_cols{0};
+    std::atomic<int> m_processing{0}, m_deferred{0};
     int max_cols = 32;      // widest batch per pass (b2_ctx_max_batch: 32 on the int8 kernel, 256 on the tcgen05 pass)
     bool tc_prefill = false;   // long prompts go through b2_ctx_prefill (whole chunks on the tensor-core prompt path)
 
@@ -171,6 +174,8 @@ struct Engine {
         job.greedy = p.temperature <= 0.0f || p.top_k == 1;
         job.rng.seed(p.seed == 0xFFFFFFFFull ? std::random_device{}() : p.seed);
         for (auto& s : p.stop) job.max_stop = std::max(job.max_stop, s.size());
+        m_requests++;
+        m_deferred++;
         {
             std::lock_guard<std::mutex> lk(qmu);
             waiting.push_back(&job);
@@ -235,6 +240,7 @@ struct Engine {
         if (!j.p.ignore_eos && tok.is_eog(j.next)) { finish(j, "stop"); return false; }
         if ((int)j.res.tokens.size() >= j.max_new) { finish(j, nullptr); return false; }
         j.res.tokens.push_back(j.next);
+        m_predicted++;
         tok.decode_append(j.next, j.pending);
         for (auto& s : j.p.stop) {
             const size_t at = s.empty() ? std::string::npos : j.pending.find(s);
@@ -261,6 +267,7 @@ struct Engine {
             Job* j = slot_job[s];
             if (!j || !j->finished) continue;
             slot_job[s] = nullptr;   // the slot keeps its tokens: the next request may share the prefix
+            m_processing--;
             // notify under the lock: the waiter cannot return (and destroy the job) before we are done with it
             std::lock_guard<std::mutex> lk(j->m);
             j->done = true;
@@ -288,6 +295,10 @@ struct Engine {
             j->fed = best_cp;
             slot_cached[best].resize(best_cp);
             slot_job[best] = j;
+            m_deferred--;
+            m_processing++;
+            m_prompt_reused += best_cp;
+            m_prompt_tokens += j->prompt->size() - best_cp;
         }
     }
 
@@ -418,6 +429,8 @@ struct Engine {
             const int n = (int)b_tok.size();
             if (n == 0) { retire_finished(); continue; }
             b_out.resize(n);
+            m_passes++;
+            m_pass_cols += (uint64_t)n;
             const int rc = b2_ctx_decode_batch(ctx, b_tok.data(), b_slot.data(), b_pos.data(), n, 0, b_out.data(), nullptr);
             if (rc) {
                 const std::string msg = b2_last_error();

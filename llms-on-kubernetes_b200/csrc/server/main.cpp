@@ -327,6 +327,31 @@ bool handle(int fd, const Request& rq, bool keep_alive) {
         list.set("data", data);
         return respond(fd, rq, 200, "application/json", b2json::dump(list), keep_alive);
     }
+    if (path == "/metrics") {
+        // Prometheus text format; llama.cpp's server exports the same names behind --metrics
+        if (rq.method != "GET") return respond(fd, rq, 405, "application/json", error_json(405, "use GET", "invalid_request_error"), keep_alive);
+        char buf[2048];
+        const unsigned long long passes = E.m_passes.load(), cols = E.m_pass_cols.load();
+        snprintf(buf, sizeof buf,
+                 "# HELP llamacpp:prompt_tokens_total Number of prompt tokens processed.\n# TYPE llamacpp:prompt_tokens_total counter\n"
+                 "llamacpp:prompt_tokens_total %llu\n"
+                 "# HELP llamacpp:tokens_predicted_total Number of generation tokens processed.\n# TYPE llamacpp:tokens_predicted_total counter\n"
+                 "llamacpp:tokens_predicted_total %llu\n"
+                 "# HELP llamacpp:requests_processing Number of requests processing.\n# TYPE llamacpp:requests_processing gauge\n"
+                 "llamacpp:requests_processing %d\n"
+                 "# HELP llamacpp:requests_deferred Number of requests deferred.\n# TYPE llamacpp:requests_deferred gauge\n"
+                 "llamacpp:requests_deferred %d\n"
+                 "# HELP b2:requests_total Completion requests accepted.\n# TYPE b2:requests_total counter\nb2:requests_total %llu\n"
+                 "# HELP b2:prompt_tokens_reused_total Prompt tokens served from a slot's cached prefix.\n# TYPE b2:prompt_tokens_reused_total counter\n"
+                 "b2:prompt_tokens_reused_total %llu\n"
+                 "# HELP b2:batch_passes_total Batched passes over the weights.\n# TYPE b2:batch_passes_total counter\nb2:batch_passes_total %llu\n"
+                 "# HELP b2:batch_columns_total Columns (tokens) in those passes.\n# TYPE b2:batch_columns_total counter\nb2:batch_columns_total %llu\n"
+                 "# HELP b2:slots Sequence slots of the context.\n# TYPE b2:slots gauge\nb2:slots %d\n"
+                 "# HELP b2:max_batch_columns Widest batch per pass.\n# TYPE b2:max_batch_columns gauge\nb2:max_batch_columns %d\n",
+                 (unsigned long long)E.m_prompt_tokens.load(), (unsigned long long)E.m_predicted.load(), E.m_processing.load(), E.m_deferred.load(),
+                 (unsigned long long)E.m_requests.load(), (unsigned long long)E.m_prompt_reused.load(), passes, cols, E.n_slots, E.max_cols);
+        return respond(fd, rq, 200, "text/plain; version=0.0.4", buf, keep_alive);
+    }
     const bool chat = path == "/v1/chat/completions" || path == "/chat/completions";
     const bool text = path == "/v1/completions" || path == "/completions";
     if (chat || text) {

@@ -295,3 +295,35 @@ def test_many_concurrent_requests_on_the_wide_batch_path(server):
     alone = [post(server, "/v1/completions", rq) for rq in reqs[-8:]]
     same_first = sum(o["choices"][0]["tokens"][0] == a["choices"][0]["tokens"][0] for (_, o), (_, a) in zip(out[-8:], alone))
     assert same_first >= 6, same_first
+
+
+@pytest.mark.gpu
+def test_metrics_endpoint_counts_the_work(server):
+    """GET /metrics (Prometheus text, llama.cpp's metric names): what a ServiceMonitor on the ramalama Deployment scrapes."""
+    def scrape():
+        c = http.client.HTTPConnection("127.0.0.1", server, timeout=10)
+        c.request("GET", "/metrics")
+        r = c.getresponse(); text = r.read().decode(); c.close()
+        assert r.status == 200 and r.getheader("Content-Type").startswith("text/plain")
+        vals = {}
+        for line in text.splitlines():
+            if line and not line.startswith("#"):
+                k, v = line.rsplit(" ", 1)
+                vals[k] = float(v)
+        return vals
+    before = scrape()
+    prompt = np.random.default_rng(77).integers(3, 1024, size=17).tolist()
+    st, o = post(server, "/v1/completions", {"model": "tinyllama", "prompt": prompt, "max_tokens": 9, "temperature": 0, "ignore_eos": True})
+    assert st == 200
+    for _ in range(50):          # the scheduler retires the slot right after the response is handed over
+        after = scrape()
+        if after["llamacpp:requests_processing"] == 0:
+            break
+        time.sleep(0.02)
+    assert after["llamacpp:tokens_predicted_total"] - before["llamacpp:tokens_predicted_total"] == 9
+    fed = after["llamacpp:prompt_tokens_total"] - before["llamacpp:prompt_tokens_total"]
+    reused = after["b2:prompt_tokens_reused_total"] - before["b2:prompt_tokens_reused_total"]
+    assert fed + reused == 17 and fed >= 1
+    assert after["b2:requests_total"] - before["b2:requests_total"] == 1
+    assert after["llamacpp:requests_processing"] == 0 and after["llamacpp:requests_deferred"] == 0
+    assert after["b2:slots"] >= 1 and after["b2:max_batch_columns"] in (32, 256)
