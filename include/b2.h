@@ -193,8 +193,17 @@ typedef struct {
     uint64_t stream_bytes;  /* bytes one decode step reads (SURVEY 8d W_stream) */
 } b2_model_info;
 
-/* Upload the GGUF's tensor data to `device` unmodified.  tp_rank/tp_size: 0/1 for a full replica. */
+/* Upload the GGUF's tensor data to `device` unmodified.  tp_rank/tp_size: 0/1 for a full replica.
+ * tp_size > 1 (the 70B configuration: one process per GPU): this process keeps shard tp_rank -- attn_q/k/v
+ * by heads and ffn_gate/up by ff rows (row ranges), attn_output and ffn_down along K on super-block boundaries; norms,
+ * embeddings and the lm_head stay whole.  b2_model_get_info then reports the shard's n_head / n_kv / d_ff and
+ * stream_bytes.  A context of a sharded model decodes one sequence, one kernel per stage with an NCCL all-reduce after
+ * each row-split mat-vec, and must be given the communicator before the first decode: rank 0 calls
+ * b2_allreduce_unique_id (128 bytes), the launcher hands the same bytes to every rank, every rank calls
+ * b2_allreduce_init(ctx, id, 128) (collective).  libnccl.so.2 is loaded at that point, not linked. */
 int b2_model_load(const char* path, int device, int tp_rank, int tp_size, b2_model** out);
+int b2_allreduce_unique_id(void* id_out, size_t cap);   /* -> bytes written (128), or a negative status */
+int b2_allreduce_init(b2_ctx* ctx, const void* id, size_t id_bytes);
 void b2_model_free(b2_model* m);
 int b2_model_get_info(const b2_model* m, b2_model_info* out);
 const b2_gguf* b2_model_gguf(const b2_model* m);

@@ -89,6 +89,8 @@ SYMBOLS = {
     "b2_argmax_scratch_bytes": (_SZ, [_I64]),
     "b2_sample_greedy": (_I, [_P, _I64, _P, _P, _P]),
     "b2_model_load": (_I, [C.c_char_p, _I, _I, _I, C.POINTER(_P)]),
+    "b2_allreduce_unique_id": (_I, [_P, _SZ]),
+    "b2_allreduce_init": (_I, [_P, _P, _SZ]),
     "b2_model_free": (None, [_P]),
     "b2_model_get_info": (_I, [_P, C.POINTER(ModelInfo)]),
     "b2_model_gguf": (_P, [_P]),
@@ -323,10 +325,17 @@ class Gguf:
         return C.string_at(lib.b2_gguf_tensor_data(self.h, i), info["n_bytes"])
 
 
+def allreduce_unique_id() -> bytes:
+    """NCCL id for a tensor-parallel group: create on rank 0, hand the same bytes to every rank's Context.allreduce_init."""
+    buf = C.create_string_buffer(128)
+    n = check(lib.b2_allreduce_unique_id(buf, 128))
+    return buf.raw[:n]
+
+
 class Model:
-    def __init__(self, path: str, device: int = 0):
+    def __init__(self, path: str, device: int = 0, tp_rank: int = 0, tp_size: int = 1):
         self.h = _P()
-        check(lib.b2_model_load(os.fsencode(path), device, 0, 1, C.byref(self.h)))
+        check(lib.b2_model_load(os.fsencode(path), device, tp_rank, tp_size, C.byref(self.h)))
         self.info = ModelInfo()
         check(lib.b2_model_get_info(self.h, C.byref(self.info)))
 
@@ -372,6 +381,10 @@ class Context:
         check(lib.b2_ctx_decode_batch(self.h, toks.ctypes.data, None if s is None else s.ctypes.data, p.ctypes.data, toks.size,
                                       1 if last_only else 0, nxt.ctypes.data, logits.ctypes.data if want_logits else None))
         return nxt.tolist(), logits
+
+    def allreduce_init(self, unique_id: bytes):
+        """Collective over the tensor-parallel ranks: joins the NCCL communicator and finishes the context's set-up."""
+        check(lib.b2_allreduce_init(self.h, unique_id, len(unique_id)))
 
     def max_batch(self) -> int:
         return check(lib.b2_ctx_max_batch(self.h))

@@ -75,6 +75,66 @@ int check_vec(const b2_model::W& w, const char* what, int64_t n) {
     return 0;
 }
 
+// Tensor-parallel shard `rank` of `size`: attn_q/k/v by heads and ffn_gate/up by ff rows are row ranges of
+// the matrices already in HBM (pointer + row count); attn_output and ffn_down are split along K on block boundaries --
+// every row keeps blocks [rank * K/size, (rank + 1) * K/size), copied into a compact matrix.  The blocks themselves are
+// untouched.  Norms, the embedding table and the lm_head stay whole on every rank; info.n_head / n_kv / d_ff become the
+// shard's.  (The whole file image stays resident: 42 GB of the 180 on the 70B model; trimming it is bookkeeping.)
+int shard_model(b2_model* m, int rank, int size) {
+    b2_model_info& I = m->info;
+    const int hd = I.head_dim;
+    if (I.n_head % size || I.n_kv % size || I.d_ff % size) {
+        set_error("model: %d heads / %d kv heads / d_ff %d do not divide over %d tensor-parallel ranks", I.n_head, I.n_kv, I.d_ff, size);
+        return B2_EUNSUP;
+    }
+    const int64_t h_l = I.n_head / size, kv_l = I.n_kv / size, ff_l = I.d_ff / size;
+    auto rows_of = [&](b2_model::W& w, int64_t first, int64_t n) {
+        w.p += first * row_bytes(w.type, w.cols);
+        w.rows = n;
+    };
+    auto k_slice = [&](b2_model::W& w, int64_t first, int64_t n, const char* what) -> int {
+        const TypeTraits* t = type_traits(w.type);
+        if (first % t->block_elems || n % t->block_elems || (gemv_act_for_type(w.type) == ACT_Q8K && n % 256)) {
+            set_error("model: the K slice [%lld, +%lld) of %s does not fall on block boundaries", (long long)first, (long long)n, what);
+            return B2_EUNSUP;
+        }
+        const size_t full = (size_t)row_bytes(w.type, w.cols), part = (size_t)row_bytes(w.type, n);
+        const size_t off = (size_t)(first / t->block_elems) * t->block_bytes;
+        uint8_t* dst = nullptr;
+        B2_CUDA_CHECK(cudaMalloc((void**)&dst, part * w.rows + 256));
+        m->tp_allocs.push_back(dst);
+        B2_CUDA_CHECK(cudaMemcpy2D(dst, part, w.p + off, full, part, (size_t)w.rows, cudaMemcpyDeviceToDevice));
+        B2_CUDA_CHECK(cudaMemset(dst + part * w.rows, 0, 256));
+        w.p = dst;
+        w.cols = n;
+        return 0;
+    };
+    uint64_t stream = m->output.rows * (uint64_t)row_bytes(m->output.type, m->output.cols) + (uint64_t)I.d_model * 4;
+    int rc;
+    for (auto& L : m->layers) {
+        rows_of(L.wq, rank * h_l * hd, h_l * hd);
+        rows_of(L.wk, rank * kv_l * hd, kv_l * hd);
+        rows_of(L.wv, rank * kv_l * hd, kv_l * hd);
+        if (L.bq) L.bq += rank * h_l * hd;
+        if (L.bk) L.bk += rank * kv_l * hd;
+        if (L.bv) L.bv += rank * kv_l * hd;
+        rows_of(L.gate, rank * ff_l, ff_l);
+        rows_of(L.up, rank * ff_l, ff_l);
+        if ((rc = k_slice(L.wo, rank * h_l * hd, h_l * hd, "attn_output.weight"))) return rc;
+        if ((rc = k_slice(L.down, rank * ff_l, ff_l, "ffn_down.weight"))) return rc;
+        const b2_model::W* ws[] = {&L.wq, &L.wk, &L.wv, &L.wo, &L.gate, &L.up, &L.down};
+        for (const b2_model::W* w : ws) stream += (uint64_t)w->rows * row_bytes(w->type, w->cols);
+        stream += 2ull * I.d_model * 4;
+    }
+    I.n_head = (int32_t)h_l;
+    I.n_kv = (int32_t)kv_l;
+    I.d_ff = (int32_t)ff_l;
+    I.stream_bytes = stream;
+    m->tp_rank = rank;
+    m->tp_size = size;
+    return 0;
+}
+
 }  // namespace
 
 extern "C" int b2_model_load(const char* path, int device, int tp_rank, int tp_size, b2_model** out) {
@@ -83,9 +143,9 @@ extern "C" int b2_model_load(const char* path, int device, int tp_rank, int tp_s
         return B2_EINVAL;
     }
     *out = nullptr;
-    if (tp_size != 1 || tp_rank != 0) {
-        set_error("b2_model_load: tensor parallelism (tp_size=%d) is not built yet; load a full replica (tp 0/1)", tp_size);
-        return B2_EUNSUP;
+    if (tp_size < 1 || tp_size > 64 || tp_rank < 0 || tp_rank >= tp_size) {
+        set_error("b2_model_load: tensor-parallel rank %d of %d is not valid", tp_rank, tp_size);
+        return B2_EINVAL;
     }
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) {
@@ -246,6 +306,7 @@ extern "C" int b2_model_load(const char* path, int device, int tp_rank, int tp_s
         }
     }
     I.stream_bytes = stream;
+    if (tp_size > 1 && (rc = shard_model(m.get(), tp_rank, tp_size))) return rc;
     *out = m.release();
     return 0;
 }
@@ -254,6 +315,7 @@ extern "C" void b2_model_free(b2_model* m) {
     if (!m) return;
     if (m->d_alloc) cudaFree(m->d_alloc);
     if (m->f16_cache) cudaFree(m->f16_cache);
+    for (void* p : m->tp_allocs) cudaFree(p);
     delete m;
 }
 
@@ -419,11 +481,17 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
             launches++;
         }
         // --- attention output projection + residual ---
+        // (tensor parallel: this rank's K slice gives a partial vector -> summed over the ranks, then added to x)
+        const bool tp = m->tp_size > 1;
         common(a, c->attn_out, nullptr, I.n_head * I.head_dim);
-        seg_matrix(a.seg[0], L.wo, PAIR_ADJ, EPI_RESID);
-        a.seg[0].out = c->x;
+        seg_matrix(a.seg[0], L.wo, PAIR_ADJ, tp ? EPI_STORE : EPI_RESID);
+        a.seg[0].out = tp ? c->tp_part : c->x;
         a.n_seg = 1;
         if ((rc = run(a, gemv_act_for_type(L.wo.type)))) return rc;
+        if (tp && !matvec_only) {
+            if ((rc = tp_allreduce_add(c->tp_comm, c->tp_part, c->x, I.d_model, st))) return rc;
+            launches += 2;
+        }
         // --- FFN: RMSNorm -> gate, up -> SwiGLU ---
         const int ag = gemv_act_for_type(L.gate.type), au = gemv_act_for_type(L.up.type);
         if (ag == au && L.gate.type == L.up.type) {
@@ -439,10 +507,14 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
         }
         // --- FFN down projection + residual ---
         common(a, c->h, nullptr, I.d_ff);
-        seg_matrix(a.seg[0], L.down, PAIR_ADJ, EPI_RESID);
-        a.seg[0].out = c->x;
+        seg_matrix(a.seg[0], L.down, PAIR_ADJ, tp ? EPI_STORE : EPI_RESID);
+        a.seg[0].out = tp ? c->tp_part : c->x;
         a.n_seg = 1;
         if ((rc = run(a, gemv_act_for_type(L.down.type)))) return rc;
+        if (tp && !matvec_only) {
+            if ((rc = tp_allreduce_add(c->tp_comm, c->tp_part, c->x, I.d_model, st))) return rc;
+            launches += 2;
+        }
     }
     // --- final norm + lm_head ---
     GemvArgs a;
@@ -626,7 +698,7 @@ int run_step(b2_ctx* c) {
 
 // every matrix in a type the tensor-core kernel computes?
 bool batch_supported(const b2_model* m) {
-    if (env_flag("B2_NO_BATCH")) return false;
+    if (env_flag("B2_NO_BATCH") || m->tp_size > 1) return false;   // shards decode one sequence, one launch per stage
     auto ok = [](const b2_model::W& w) { return gemm_supports_type(w.type); };
     if (!ok(m->output)) return false;
     for (const auto& L : m->layers) {
@@ -1320,7 +1392,15 @@ extern "C" int b2_ctx_create_slots(b2_model* m, int n_ctx, int n_slots, b2_ctx**
         B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     }
     // scratch + program of the persistent per-token kernel (B2_NO_STEP=1 keeps one launch per stage)
-    c->use_step = !env_flag("B2_NO_STEP");
+    c->use_step = !env_flag("B2_NO_STEP") && m->tp_size == 1;   // a shard exchanges partial sums between stages
+    if (m->tp_size > 1) {
+        // the first step (and the CUDA graph of a step) need the communicator: b2_allreduce_init finishes the set-up
+        if ((rc = dmalloc(&c->tp_part, (size_t)I.d_model))) return rc;
+        B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+        c->pos = 0;
+        *out = c.release();
+        return 0;
+    }
     if (c->use_step) {
         B2_CUDA_CHECK(cudaMalloc((void**)&c->step_counters, (8 + I.n_head) * sizeof(unsigned int)));
         B2_CUDA_CHECK(cudaMemsetAsync(c->step_counters, 0, (8 + I.n_head) * sizeof(unsigned int), c->stream));
@@ -1348,6 +1428,8 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->exec) cudaGraphExecDestroy(c->exec);
     if (c->graph) cudaGraphDestroy(c->graph);
+    if (c->tp_comm) tp_comm_free(c->tp_comm);
+    if (c->tp_part) cudaFree(c->tp_part);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
                     c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch,
                     c->d_ops, c->step_attn_partials, c->step_counters, c->step_sync, c->step_argmax_val, c->step_argmax_idx, c->step_trace};
@@ -1365,6 +1447,31 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->h_pin) cudaFreeHost(c->h_pin);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
+}
+
+extern "C" int b2_allreduce_unique_id(void* id_out, size_t cap) { return tp_unique_id(id_out, cap); }
+
+extern "C" int b2_allreduce_init(b2_ctx* c, const void* id, size_t id_bytes) {
+    if (!c) return B2_EINVAL;
+    if (c->m->tp_size < 2) {
+        set_error("b2_allreduce_init: the model was loaded as a full replica (tp_size 1)");
+        return B2_EINVAL;
+    }
+    if (c->tp_comm) return 0;
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    int rc;
+    if ((rc = tp_comm_init(id, id_bytes, c->m->tp_rank, c->m->tp_size, &c->tp_comm))) return rc;
+    // what b2_ctx_create does for a replica: one eager step (lazy module loading outside capture), then the graph.
+    // Every rank runs the same steps, so the collectives inside match up.
+    if ((rc = enqueue_decode(c, c->stream, false))) return rc;
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_pos, 0, 4, c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_step, 0, 4, c->stream));
+    B2_CUDA_CHECK(cudaMemsetAsync(c->d_tok, 0, 4, c->stream));
+    if (!env_flag("B2_TP_NO_GRAPH") && (rc = build_graph(c))) return rc;   // the all-reduces are captured with the step
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    c->pos = 0;
+    return 0;
 }
 
 extern "C" int b2_ctx_n_ctx(const b2_ctx* c) { return c ? c->n_ctx : B2_EINVAL; }

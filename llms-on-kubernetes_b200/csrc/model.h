@@ -30,6 +30,11 @@ struct b2_model {
     const float* rope_freqs = nullptr;
     std::vector<float> rope_freqs_host;
     std::vector<Layer> layers;
+    // tensor parallelism: this process holds shard tp_rank of tp_size.  info.n_head / n_kv / d_ff are then
+    // the shard's; attn_output and ffn_down point at compact copies of their K slices (tp_allocs), the row-split
+    // matrices at their row range inside the uploaded file image
+    int tp_rank = 0, tp_size = 1;
+    std::vector<void*> tp_allocs;
     // fp16 copies of the layer matrices for the tensor-core prompt / wide-batch path (tc_gemm.cu), built on first
     // use when they fit the budget (B2_F16_CACHE_GB, default 64 GB and at most half of the free HBM): per layer the
     // stacked Q | K | V, O, stacked gate | up, down.  Without it the path dequantises each matrix per pass.
@@ -72,6 +77,9 @@ struct b2_ctx {
     float* step_argmax_val = nullptr;
     int* step_argmax_idx = nullptr;
     int pos = 0;
+    // tensor parallelism: NCCL communicator (b2_allreduce_init) and the partial d_model vector of a row-split mat-vec
+    void* tp_comm = nullptr;
+    float* tp_part = nullptr;
     // batched path: up to BATCH_MAX_COLS tokens per pass over the weights, each with its own (sequence slot,
     // position) -- up to GEMM_MAX_COLS columns on the int8 kernel (gemm.cu), wider batches (and any batch of at least
     // tc_batch_min() columns when the model's fp16 copy is resident) on the tensor-core pass (tc_gemm.cu).  KV caches

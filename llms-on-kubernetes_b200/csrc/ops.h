@@ -75,4 +75,10 @@ int launch_embed_rows(int type, const void* table, int64_t row_bytes, int d_mode
 int launch_prefill_qkv_post(const PrefillQkvArgs& a, int T, cudaStream_t st);
 int launch_argmax_rows(const float* logits, int64_t n, int rows, int32_t* out, cudaStream_t st);
 
+// tp.cu: the tensor-parallel exchange (NCCL through dlopen)
+int tp_unique_id(void* out, size_t cap);                                   // -> bytes written (128) or an error
+int tp_comm_init(const void* id_bytes, size_t len, int rank, int size, void** comm_out);
+void tp_comm_free(void* comm);
+int tp_allreduce_add(void* comm, float* part, float* x, int n, cudaStream_t st);   // x += allreduce_sum(part)
+
 }  // namespace b2

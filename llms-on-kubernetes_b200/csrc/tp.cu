@@ -1,0 +1,133 @@
+// tp.cu -- the exchange step of tensor parallelism (the 70B model over 2/4/8 GPUs of one box).
+//
+// Row/column split as the scope table prescribes: attn_q/k/v by heads and ffn_gate/up by ff rows (contiguous row
+// ranges of the GGUF matrices), attn_output and ffn_down along K on super-block boundaries (model.cu uploads each
+// rank's slice).  Every rank therefore ends a half-layer with a partial d_model vector; this file sums them:
+// ncclAllReduce(sum, fp32) over NVLink, then x += sum.  One process per GPU; the host application hands every rank the
+// same 128-byte NCCL id (b2_allreduce_unique_id on rank 0, broadcast by whatever launched the ranks).
+//
+// libnccl is loaded with dlopen on first use: a single-GPU deployment of libb2.so neither links nor needs it.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cstring>
+#include <mutex>
+
+#include "common.h"
+#include "ops.h"
+
+namespace b2 {
+namespace {
+
+struct Nccl {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+int nccl(Nccl** out) {
+    static Nccl n;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lk(mu);
+    if (!n.lib) {
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names)
+            if ((n.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL))) break;
+        if (!n.lib) {
+            set_error("tensor parallelism needs libnccl.so.2 on the library path: %s", dlerror());
+            return B2_EUNSUP;
+        }
+        n.GetUniqueId = (decltype(n.GetUniqueId))dlsym(n.lib, "ncclGetUniqueId");
+        n.CommInitRank = (decltype(n.CommInitRank))dlsym(n.lib, "ncclCommInitRank");
+        n.CommDestroy = (decltype(n.CommDestroy))dlsym(n.lib, "ncclCommDestroy");
+        n.AllReduce = (decltype(n.AllReduce))dlsym(n.lib, "ncclAllReduce");
+        n.GetErrorString = (decltype(n.GetErrorString))dlsym(n.lib, "ncclGetErrorString");
+        if (!n.GetUniqueId || !n.CommInitRank || !n.CommDestroy || !n.AllReduce || !n.GetErrorString) {
+            set_error("libnccl does not export the expected symbols");
+            dlclose(n.lib);
+            n.lib = nullptr;
+            return B2_EUNSUP;
+        }
+    }
+    *out = &n;
+    return 0;
+}
+
+#define B2_NCCL_CHECK(N, expr)                                                                 \
+    do {                                                                                       \
+        ncclResult_t _r = (expr);                                                              \
+        if (_r != ncclSuccess) {                                                               \
+            set_error("NCCL error at %s:%d: %s", __FILE__, __LINE__, (N)->GetErrorString(_r)); \
+            return B2_ECUDA;                                                                   \
+        }                                                                                      \
+    } while (0)
+
+__global__ void residual_add_kernel(float4* __restrict__ x, const float4* __restrict__ part, int n4) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n4) {
+        float4 a = x[i];
+        const float4 b = part[i];
+        a.x += b.x;
+        a.y += b.y;
+        a.z += b.z;
+        a.w += b.w;
+        x[i] = a;
+    }
+}
+
+}  // namespace
+
+int tp_unique_id(void* out, size_t cap) {
+    if (!out || cap < sizeof(ncclUniqueId)) {
+        set_error("b2_allreduce_unique_id: the buffer must hold %zu bytes", sizeof(ncclUniqueId));
+        return B2_EINVAL;
+    }
+    Nccl* n;
+    int rc;
+    if ((rc = nccl(&n))) return rc;
+    ncclUniqueId id;
+    B2_NCCL_CHECK(n, n->GetUniqueId(&id));
+    memcpy(out, &id, sizeof id);
+    return (int)sizeof id;
+}
+
+int tp_comm_init(const void* id_bytes, size_t len, int rank, int size, void** comm_out) {
+    if (!id_bytes || len < sizeof(ncclUniqueId) || !comm_out || size < 2 || rank < 0 || rank >= size) {
+        set_error("b2_allreduce_init: bad arguments (rank %d of %d, id of %zu bytes)", rank, size, len);
+        return B2_EINVAL;
+    }
+    Nccl* n;
+    int rc;
+    if ((rc = nccl(&n))) return rc;
+    ncclUniqueId id;
+    memcpy(&id, id_bytes, sizeof id);
+    ncclComm_t comm = nullptr;
+    B2_NCCL_CHECK(n, n->CommInitRank(&comm, size, id, rank));
+    *comm_out = comm;
+    return 0;
+}
+
+void tp_comm_free(void* comm) {
+    Nccl* n;
+    if (comm && nccl(&n) == 0) n->CommDestroy((ncclComm_t)comm);
+}
+
+// x[0..n) += sum over the ranks of part[0..n)   (part is overwritten with the sum)
+int tp_allreduce_add(void* comm, float* part, float* x, int n, cudaStream_t st) {
+    Nccl* nc;
+    int rc;
+    if ((rc = nccl(&nc))) return rc;
+    if (!comm) {
+        set_error("tensor-parallel context used before b2_allreduce_init");
+        return B2_EINVAL;
+    }
+    B2_NCCL_CHECK(nc, nc->AllReduce(part, part, (size_t)n, ncclFloat, ncclSum, (ncclComm_t)comm, st));
+    residual_add_kernel<<<(n / 4 + 255) / 256, 256, 0, st>>>((float4*)x, (const float4*)part, n / 4);
+    B2_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace b2
