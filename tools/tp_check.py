@@ -67,6 +67,8 @@ def main():
         ctx.free(); m.free()
         dist.barrier()
 
+    if os.environ.get("B2_TP_PARITY_ONLY"):
+        return ok
     # throughput: the Llama-3.1-8B shape at this TP degree (the 70B file is 42 GB of synthetic blocks: not generated here)
     name = os.environ.get("B2_TP_MODEL", "llama-3.1-8b-q4_k_m")
     path = os.path.join(tmp, f"b2_synth_{name}_s0.gguf")
@@ -85,7 +87,7 @@ def main():
     dt = time.perf_counter() - t0
     if rank == 0:
         print(json.dumps({"model": name, "tp": world, "decode_tok_per_s": steps / dt, "ms_per_token": dt / steps * 1e3,
-                          "shard_stream_bytes": int(m.info.stream_bytes), "launches_per_step": ctx.launches_per_step(),
+                          "shard_stream_bytes": int(m.info.stream_bytes), "launches_per_step": ctx.launches_per_step,
                           "graph": not os.environ.get("B2_TP_NO_GRAPH"), "parity_ok": ok}), flush=True)
     ctx.free(); m.free()
     dist.barrier()
