@@ -34,6 +34,8 @@ def main():
     tmp = os.environ.get("B2_BENCH_DIR", "/tmp")
     ok = True
     for name in ("tiny-llama-q4_k_m", "tiny-llama3-q4_k_m", "tiny-qwen2-q8_0"):
+        if os.environ.get("B2_TP_BENCH_ONLY"):
+            break
         spec = sg.SPECS[name]
         if spec.n_kv % world or spec.n_head % world:
             continue
@@ -81,7 +83,7 @@ def main():
     ctx.generate_greedy(16)
     ctx.sync(); dist.barrier()
     t0 = time.perf_counter()
-    steps = 128
+    steps = int(os.environ.get("B2_TP_STEPS", "128"))
     ctx.generate_greedy(steps)
     ctx.sync()
     dt = time.perf_counter() - t0
