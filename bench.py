@@ -219,6 +219,8 @@ def main():
     ap.add_argument("--dist-selftest", action="store_true", help="CPU-only check of the multi-rank aggregation (gloo)")
     ap.add_argument("--batch", type=int, default=1, help="> 1: batched decode of this many sequences (SURVEY 8d config 3: 8, 32)")
     ap.add_argument("--prefill", type=int, default=0, help="> 0: time the prefill of a prompt of this many tokens instead")
+    ap.add_argument("--tp", action="store_true", help="under torchrun: ONE model sharded over all ranks (tensor parallel, SURVEY 8e "
+                                                      "config 5, e.g. --model llama-3.1-70b-q4_k_m) instead of one replica per rank")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -293,7 +295,11 @@ def main():
 
     b2 = importlib.import_module(PKG)  # raises if libb2.so is missing: no fallback
     path = ensure_model(synth, args.model, args.seed, rank, barrier)
-    model = b2.Model(path, device=local_rank)
+    tp = args.tp and world > 1
+    model = b2.Model(path, device=local_rank, tp_rank=rank if tp else 0, tp_size=world if tp else 1)
+    jobs = 1 if tp else world          # sequences decoded at once over the whole job
+    if tp and (args.batch > 1 or args.prefill > 0):
+        raise SystemExit("--tp measures batch-1 decode (a sharded context decodes one sequence)")
     if args.batch > 1 or args.prefill > 0:
         out = bench_batched(b2, synth, spec, model, args, world, barrier, max_over_ranks, local_rank)
         model.free()
@@ -304,6 +310,10 @@ def main():
         return
     n_ctx = max(512, args.prompt + 2 * (args.steps + args.warmup) + 64)
     ctx = b2.Context(model, n_ctx)
+    if tp:
+        box = [b2.allreduce_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        ctx.allreduce_init(box[0])       # collective: NCCL communicator + the step's CUDA graph
     info = model.info
     rng = np.random.default_rng(args.seed)
     prompt = rng.integers(3, info.vocab, size=args.prompt).tolist()
@@ -318,7 +328,7 @@ def main():
     ctx.sync(); barrier()
     clocks = sampler.stop()
     ms = max_over_ranks(ms)
-    value = world * args.steps / (ms / 1e3)
+    value = jobs * args.steps / (ms / 1e3)
     ctx_mid = args.prompt + args.warmup + args.steps // 2
     step_bytes = info.stream_bytes + ctx_mid * synth.kv_bytes_per_token(spec)
 
@@ -333,7 +343,7 @@ def main():
     ctx.sync()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
-    e2e = world * args.steps / e2e_s
+    e2e = jobs * args.steps / e2e_s
 
     # ---- roofline of the dominant kernel.  With the persistent per-token kernel (step.cu) one launch IS one decode
     # step, so the kernel's average duration is the CUDA-event time of the timed region / steps and its algorithmic
@@ -360,10 +370,14 @@ def main():
         roofline["matvec_stages_alone"] = {"error": str(e)}
 
     out = {
-        "metric": METRIC, "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": METRIC if not tp else f"decode tok/s, {spec.name} {spec.ftype} tensor-parallel", "value": value, "unit": "tok/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if tp else "weak", "vs_baseline": None,
         "dtype": "int8 x int4..8 dot (dp4a), fp32 accumulate", "data": "synthetic",
-        "config": {"workload": workload, "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
+        "config": {"workload": workload,
+                   "parallelism": (f"tensor parallel x{world}: Q/K/V by heads, gate/up by rows, O/down along K, NCCL all-reduce per half-layer; "
+                                   "roofline.achieved is ONE rank's weight stream") if tp
+                   else f"replicas x{world}" if world > 1 else "single GPU",
                    "l2": "inputs exceed L2 (4.6 GB of weights streamed per step vs 126 MB)", "graph": True},
         "e2e": {"value": e2e, "unit": "tok/s", "h2d_bytes_per_step": 8, "d2h_bytes_per_step": 4},
         "gpu_launches": ctx.launches_per_step * args.steps,
