@@ -38,7 +38,8 @@ enum {
     B2_EUNSUP = -4,   /* valid GGUF, but arch / tensor type unsupported */
     B2_ECUDA = -5,    /* CUDA runtime error (no device, OOM, launch) */
     B2_ERANGE = -6,   /* position / token / size outside limits      */
-    B2_ENOTFOUND = -7
+    B2_ENOTFOUND = -7,
+    B2_ENOMEM = -8    /* the KV pool has no free page (b2_ctx_slot_truncate)  */
 };
 
 /* ggml tensor type ids as stored in GGUF (gguf-py constants.py:4059-4093) */
@@ -232,6 +233,16 @@ int b2_ctx_n_slots(const b2_ctx* c);
  * most half of the free HBM), where batches of 16 and more columns run one HBM sweep of fp16 tiles through
  * tcgen05.mma.  0 when the model has matrices the batched kernels do not compute. */
 int b2_ctx_max_batch(b2_ctx* ctx);
+
+/* The KV cache of a context with several slots is one pool of pages of 256 positions (paged KV).
+ * When the pool holds every slot at full length -- the default while n_slots x n_ctx fits 60 % of the free HBM -- all
+ * pages are mapped up front and these calls are no-ops.  A smaller pool (that cap, or B2_KV_POOL_TOKENS) maps a page
+ * when a batch or prompt first touches it (B2_ENOMEM when none is free) and
+ * b2_ctx_slot_truncate(ctx, slot, n_keep) gives back the pages of `slot` beyond its first n_keep positions (0: all) --
+ * call it when a sequence ends or is cut back to a shared prefix.  Slot 0 (the single-sequence calls' cache) is never
+ * paged out.  b2_ctx_kv_pages reports the pool (returns 1 when pages are mapped on demand, 0 when statically). */
+int b2_ctx_slot_truncate(b2_ctx* ctx, int slot, int n_keep);
+int b2_ctx_kv_pages(const b2_ctx* ctx, int* total_out, int* free_out, int* page_tokens_out);
 
 /* One pass over the weights for a batch of 1 <= n <= 32 tokens (llama.cpp's llama_batch: row a12 with
  * n_tokens = n): column j is token tokens[j] at position pos[j] of sequence slot slots[j] (slots == NULL: all

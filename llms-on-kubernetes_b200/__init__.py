@@ -106,6 +106,8 @@ SYMBOLS = {
     "b2_ctx_batch_logits": (_I, [_P, _I, _P]),
     "b2_ctx_prefill": (_I, [_P, _I, _P, _I, _I, _P, _P]),
     "b2_ctx_max_batch": (_I, [_P]),
+    "b2_ctx_slot_truncate": (_I, [_P, _I, _I]),
+    "b2_ctx_kv_pages": (_I, [_P, C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)]),
     "b2_ctx_generate_greedy": (_I, [_P, _I, _P]),
     "b2_ctx_enqueue_steps": (_I, [_P, _I]),
     "b2_ctx_stream": (_P, [_P]),
@@ -385,6 +387,15 @@ class Context:
     def allreduce_init(self, unique_id: bytes):
         """Collective over the tensor-parallel ranks: joins the NCCL communicator and finishes the context's set-up."""
         check(lib.b2_allreduce_init(self.h, unique_id, len(unique_id)))
+
+    def slot_truncate(self, slot: int, n_keep: int = 0):
+        check(lib.b2_ctx_slot_truncate(self.h, slot, n_keep))
+
+    def kv_pages(self):
+        """(total pages, free pages, positions per page, mapped on demand?)"""
+        t, f, p = _I(), _I(), _I()
+        dyn = check(lib.b2_ctx_kv_pages(self.h, C.byref(t), C.byref(f), C.byref(p)))
+        return t.value, f.value, p.value, bool(dyn)
 
     def max_batch(self) -> int:
         return check(lib.b2_ctx_max_batch(self.h))

@@ -22,7 +22,8 @@ template <int HD>
 __global__ void __launch_bounds__(NCT) attn_batch_kernel(const float* __restrict__ q, const __half* __restrict__ kc, const __half* __restrict__ vc,
                                                          float* __restrict__ out, int n_head, int n_kv, int n_ctx, const int* __restrict__ col_pos,
                                                          const int* __restrict__ col_slot, long long slot_stride, int max_chunks,
-                                                         float* __restrict__ partials, unsigned int* __restrict__ counters) {
+                                                         float* __restrict__ partials, unsigned int* __restrict__ counters,
+                                                         const int* __restrict__ kv_table, int kv_pps) {
     __shared__ float s_scores[A_MAXG * A_TOK], s_prob[A_MAXG * A_TOK], s_ml[2 * A_MAXG];
     __shared__ int s_flag;
     __shared__ StepOp s_op;   // only the attention fields are filled
@@ -36,7 +37,13 @@ __global__ void __launch_bounds__(NCT) attn_batch_kernel(const float* __restrict
     const int t0 = chunk * AB_CHUNK, n = min(AB_CHUNK, T - t0);
     if (threadIdx.x == 0) {
         const size_t qdim = (size_t)n_head * HD;
-        const size_t slot_off = col_slot ? (size_t)col_slot[col] * (size_t)slot_stride : 0;
+        // the work item addresses rows as base + (kvh * n_ctx + t0 + i) * HD.  Paged cache: the chunk [t0, t0 + 256) is one
+        // page; shift the base so that t0 lands on the page's first token (n_ctx = tokens in the whole pool)
+        long long slot_off = col_slot ? (long long)col_slot[col] * slot_stride : 0;
+        if (kv_table) {
+            const int slot = col_slot ? col_slot[col] : 0;
+            slot_off = ((long long)kv_table[slot * kv_pps + chunk] * AB_CHUNK - t0) * HD;
+        }
         s_op.a_q = q + (size_t)col * qdim;
         s_op.a_k = kc + slot_off;
         s_op.a_v = vc + slot_off;
@@ -62,9 +69,9 @@ bool attn_batch_supported(int head_dim, int n_ctx, int max_chunks) {
 
 int launch_attn_batch(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim, int n_ctx,
                       const int* col_pos, const int* col_slot, int64_t slot_stride, int n_cols, int max_chunks, void* scratch, int cols_cap,
-                      cudaStream_t st) {
+                      cudaStream_t st, const int* kv_table, int kv_pps) {
     if (!q || !kc || !vc || !out || !col_pos || !scratch || n_cols < 1 || cols_cap < n_cols || n_kv <= 0 || n_head % n_kv ||
-        !attn_batch_supported(head_dim, n_ctx, max_chunks)) {
+        (head_dim != 64 && head_dim != 128)) {
         set_error("attn_batch: bad arguments (heads %d/%d, head_dim %d, n_ctx %d, %d chunks, %d columns)", n_head, n_kv, head_dim, n_ctx, max_chunks,
                   n_cols);
         return B2_EINVAL;
@@ -78,10 +85,10 @@ int launch_attn_batch(const float* q, const __half* kc, const __half* vc, float*
     const dim3 grid(n_kv * nb, max_chunks, n_cols);
     if (head_dim == 128)
         attn_batch_kernel<128><<<grid, NCT, 0, st>>>(q, kc, vc, out, n_head, n_kv, n_ctx, col_pos, col_slot, (long long)slot_stride, max_chunks, partials,
-                                                     counters);
+                                                     counters, kv_table, kv_pps);
     else
         attn_batch_kernel<64><<<grid, NCT, 0, st>>>(q, kc, vc, out, n_head, n_kv, n_ctx, col_pos, col_slot, (long long)slot_stride, max_chunks, partials,
-                                                    counters);
+                                                    counters, kv_table, kv_pps);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

@@ -458,6 +458,15 @@ __device__ __forceinline__ void q80_block_mma(const uint8_t* blk0, const uint8_t
     }
 }
 
+// cache row of (slot, kv head, position): through the page table when there is one
+__device__ __forceinline__ __half* kv_row(const GemmArgs& a, const GemvSeg& s, int slot, int head, int pos) {
+    if (a.kv_table) {
+        const size_t tok = (size_t)a.kv_table[slot * a.kv_pps + (pos >> 8)] * 256 + (pos & 255);
+        return s.cache + ((size_t)head * s.n_ctx + tok) * s.head_dim;
+    }
+    return s.cache + (size_t)slot * a.slot_stride + ((size_t)head * s.n_ctx + pos) * s.head_dim;
+}
+
 // fused epilogue of one (row pair, column): the mat-vec's, with per-column position, slot and output row
 __device__ __forceinline__ void epilogue_col(const GemmArgs& a, const GemvSeg& s, int p, int ra, int rb, float va, float vb, int j, int pos,
                                              int slot) {
@@ -493,7 +502,7 @@ __device__ __forceinline__ void epilogue_col(const GemmArgs& a, const GemvSeg& s
                 out[ra] = oa;
                 out[rb] = ob;
             } else {
-                __half* dst = s.cache + (size_t)slot * a.slot_stride + ((size_t)head * s.n_ctx + pos) * hd;
+                __half* dst = kv_row(a, s, slot, head, pos);
                 dst[ra - head * hd] = __float2half_rn(oa);
                 dst[rb - head * hd] = __float2half_rn(ob);
             }
@@ -502,7 +511,7 @@ __device__ __forceinline__ void epilogue_col(const GemmArgs& a, const GemvSeg& s
         case EPI_V: {
             const int hd = s.head_dim;
             const int head = ra / hd;
-            __half* dst = s.cache + (size_t)slot * a.slot_stride + ((size_t)head * s.n_ctx + pos) * hd;
+            __half* dst = kv_row(a, s, slot, head, pos);
             dst[ra - head * hd] = __float2half_rn(va);
             if (rb >= 0) dst[rb - head * hd] = __float2half_rn(vb);
             break;

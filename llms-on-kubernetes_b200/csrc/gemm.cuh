@@ -57,7 +57,11 @@ struct GemmArgs {
     const uint8_t* act;          // quantised activations (gemm_act_bytes)
     GemmCols cols;
     int64_t out_stride;          // floats between columns of seg[].out (and of the residual input for EPI_RESID)
-    int64_t slot_stride;         // halfs between sequence slots in seg[].cache
+    int64_t slot_stride;         // halfs between sequence slots in seg[].cache (kv_table == nullptr)
+    // paged KV: row `pos` of sequence slot s lives at token kv_table[s * kv_pps + pos / 256] * 256 + pos % 256 of the
+    // cache (seg[].n_ctx = tokens in the whole pool); nullptr: slot s is the contiguous window at s * slot_stride
+    const int32_t* kv_table;
+    int kv_pps;
     const float2* rope_tab;
     int rope_half;
 };

@@ -377,7 +377,7 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
     int rc;
     int launches = 0;
     if (record_act) *record_act = -1;
-    const int64_t kv_layer = (int64_t)I.n_kv * c->n_ctx * I.head_dim;
+    const int64_t kv_layer = (int64_t)I.n_kv * c->kv_tokens * I.head_dim;   // slot 0 = rows [0, n_ctx) of every kv head
     const int rope_pairing = I.arch == 1 ? PAIR_NEOX : PAIR_ADJ;
     auto common = [&](GemvArgs& a, const float* x, const float* norm_w, int K) {
         a = GemvArgs{};
@@ -437,12 +437,12 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
         sk.cache = kc;
         sk.bias = L.bk;
         sk.head_dim = I.head_dim;
-        sk.n_ctx = c->n_ctx;
+        sk.n_ctx = c->kv_tokens;
         seg_matrix(sv, L.wv, PAIR_ADJ, EPI_V);
         sv.cache = vc;
         sv.bias = L.bv;
         sv.head_dim = I.head_dim;
-        sv.n_ctx = c->n_ctx;
+        sv.n_ctx = c->kv_tokens;
         const int aq = gemv_act_for_type(L.wq.type), ak = gemv_act_for_type(L.wk.type), av = gemv_act_for_type(L.wv.type);
         GemvArgs a;
         if (aq == ak && ak == av) {
@@ -470,12 +470,12 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
             op.a_n_head = I.n_head;
             op.a_n_kv = I.n_kv;
             op.a_hd = I.head_dim;
-            op.a_n_ctx = c->n_ctx;
+            op.a_n_ctx = c->kv_tokens;   // row stride of a kv head
             op.a_pos = c->d_pos;   // a_max_chunks / a_partials: build_step_program(), once the grid is known
             op.a_counters = c->step_counters + 8;   // [<= n_head] after the grid-barrier and argmax counters
             record->push_back(op);
         } else if (!matvec_only) {
-            if ((rc = launch_attn_decode(c->q, kc, vc, c->attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, c->d_pos, 0, c->max_splits,
+            if ((rc = launch_attn_decode(c->q, kc, vc, c->attn_out, I.n_head, I.n_kv, I.head_dim, c->kv_tokens, c->d_pos, 0, c->max_splits,
                                          c->attn_scratch, st, pdl)))
                 return rc;
             launches++;
@@ -723,10 +723,39 @@ int enqueue_batch_attention(b2_ctx* c, const float* q, const __half* kc, const _
     const int splits = batch_attn_splits(c->n_ctx);
     static const bool old_kernel = env_flag("B2_ATTN_BATCH_OLD");
     if (!old_kernel && attn_batch_supported(I.head_dim, c->n_ctx, splits))
-        return launch_attn_batch(q, kc, vc, out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, col_pos, col_slot, c->slot_stride, n, splits,
-                                 c->bt.attn_scratch, c->bt.cap, st);
-    return launch_attn_decode(q, kc, vc, out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, col_pos, 0, splits, c->bt.attn_scratch, st, false, n, col_slot,
+        return launch_attn_batch(q, kc, vc, out, I.n_head, I.n_kv, I.head_dim, c->kv_tokens, col_pos, col_slot, c->slot_stride, n, splits,
+                                 c->bt.attn_scratch, c->bt.cap, st, c->d_kv_table, c->pages_per_seq);
+    // (only with the static mapping: slot s is the contiguous window at s * slot_stride)
+    return launch_attn_decode(q, kc, vc, out, I.n_head, I.n_kv, I.head_dim, c->kv_tokens, col_pos, 0, splits, c->bt.attn_scratch, st, false, n, col_slot,
                               c->slot_stride, ATTN_BATCH_SPLIT_TOKENS, c->bt.cap);
+}
+
+// ---- KV pages (model.h) ----
+// make positions [p0, p1] of `slot` addressable; with the static mapping everything already is
+int kv_map(b2_ctx* c, int slot, int p0, int p1) {
+    if (!c->kv_dynamic || slot == 0) return 0;
+    int32_t* row = c->kv_table.data() + (size_t)slot * c->pages_per_seq;
+    for (int i = p0 / KV_PAGE; i <= p1 / KV_PAGE; i++) {
+        if (row[i] >= 0) continue;
+        if (c->kv_free.empty()) {
+            set_error("KV pool exhausted: %d pages of %d positions, all mapped (b2_ctx_slot_truncate releases a sequence's pages; "
+                      "B2_KV_POOL_TOKENS sizes the pool)", c->n_pages, KV_PAGE);
+            return B2_ENOMEM;
+        }
+        row[i] = c->kv_free.back();
+        c->kv_free.pop_back();
+        c->kv_table_dirty = true;
+    }
+    return 0;
+}
+
+// the device copy of the table follows the host's before the next pass is enqueued (stream order)
+int kv_sync_table(b2_ctx* c) {
+    if (!c->kv_table_dirty) return 0;
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->d_kv_table, c->kv_table.data(), c->kv_table.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // pageable source: keep the host vector free to change
+    c->kv_table_dirty = false;
+    return 0;
 }
 
 int ensure_batch(b2_ctx* c) {
@@ -812,7 +841,7 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         const float* rows = c->pf.x + (size_t)(n - n_logits) * I.d_model;
         return n_logits >= tc_min_rows(m) ? enqueue_logits_tc(c, rows, n_logits, st) : enqueue_logits(c, rows, n_logits, st);
     }
-    const int64_t kv_layer = (int64_t)I.n_kv * c->n_ctx * I.head_dim;
+    const int64_t kv_layer = (int64_t)I.n_kv * c->kv_tokens * I.head_dim;
     const int rope_pairing = I.arch == 1 ? PAIR_NEOX : PAIR_ADJ;
     const int qdim = I.n_head * I.head_dim;
     for (int j = 0; j < n; j++)
@@ -828,6 +857,8 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         a.cols.slot = b.slot;
         a.out_stride = out_stride;
         a.slot_stride = c->slot_stride;
+        a.kv_table = c->d_kv_table;
+        a.kv_pps = c->pages_per_seq;
         a.rope_tab = c->rope_tab;
         a.rope_half = I.rope_dim / 2;
     };
@@ -851,12 +882,12 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         a.seg[1].cache = kc;
         a.seg[1].bias = L.bk;
         a.seg[1].head_dim = I.head_dim;
-        a.seg[1].n_ctx = c->n_ctx;
+        a.seg[1].n_ctx = c->kv_tokens;
         seg_matrix(a.seg[2], L.wv, PAIR_ADJ, EPI_V);
         a.seg[2].cache = vc;
         a.seg[2].bias = L.bv;
         a.seg[2].head_dim = I.head_dim;
-        a.seg[2].n_ctx = c->n_ctx;
+        a.seg[2].n_ctx = c->kv_tokens;
         a.n_seg = 3;
         if ((rc = run(a))) return rc;
         // attention of every column over its own sequence
@@ -902,6 +933,9 @@ int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int3
         set_error("b2_ctx_decode_batch: %d columns need the tensor-core pass with a resident fp16 copy of the model (b2_ctx_max_batch)", n);
         return B2_EUNSUP;
     }
+    for (int j = 0; j < n; j++)
+        if ((rc = kv_map(c, slots ? slots[j] : 0, pos[j], pos[j]))) return rc;
+    if ((rc = kv_sync_table(c))) return rc;
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // staging buffer reuse
     for (int j = 0; j < n; j++) {
         c->h_pin[j] = tokens[j];
@@ -1068,7 +1102,7 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
     auto& p = c->pf;
     int rc;
     const int qdim = I.n_head * I.head_dim, kvdim = I.n_kv * I.head_dim;
-    const int64_t kv_layer = (int64_t)I.n_kv * c->n_ctx * I.head_dim;
+    const int64_t kv_layer = (int64_t)I.n_kv * c->kv_tokens * I.head_dim;
     __half* xb = (__half*)p.xb;
     __half* wb = (__half*)p.wb;
     auto dq = [&](const b2_model::W& w, __half* dst) { return launch_dequant_f16(w.type, w.p, dst, (int64_t)w.rows * w.cols, st); };
@@ -1108,9 +1142,9 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
     if ((rc = launch_embed_rows(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, tok_dev, T, p.x, st))) return rc;
     for (int il = 0; il < I.n_layer; il++) {
         const auto& L = m->layers[il];
-        // slot 0's cache in the batch form (the kernels add col_slot[j] * slot_stride per column)
-        __half* kc = c->k_cache + (size_t)(col_pos ? 0 : slot) * c->slot_stride + il * kv_layer;
-        __half* vc = c->v_cache + (size_t)(col_pos ? 0 : slot) * c->slot_stride + il * kv_layer;
+        // the layer's part of the pool; rows are found through the page table (slot = the column's, or `slot`)
+        __half* kc = c->k_cache + il * kv_layer;
+        __half* vc = c->v_cache + il * kv_layer;
         // RMSNorm -> one mat-mul over the stacked Q | K | V matrices -> bias, RoPE, KV cache
         if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.wq.type), xb, st, pend)))
             return rc;
@@ -1136,7 +1170,10 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         qa.nq = qdim;
         qa.nk = kvdim;
         qa.head_dim = I.head_dim;
-        qa.n_ctx = c->n_ctx;
+        qa.n_ctx = c->kv_tokens;
+        qa.kv_table = c->d_kv_table;
+        qa.kv_pps = c->pages_per_seq;
+        qa.slot = slot;
         qa.pos0 = pos0;
         qa.rope_half = I.rope_dim / 2;
         qa.neox = I.arch == 1;
@@ -1148,7 +1185,8 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         mark(1);
         if (col_pos) {
             if ((rc = enqueue_batch_attention(c, p.q, kc, vc, p.attn_out, col_pos, col_slot, T, st))) return rc;
-        } else if ((rc = launch_prefill_attn(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->n_ctx, T, pos0, st))) {
+        } else if ((rc = launch_prefill_attn(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->kv_tokens, T, pos0, st,
+                                             c->d_kv_table + (size_t)slot * c->pages_per_seq))) {
             return rc;
         }
         mark(2);
@@ -1192,6 +1230,8 @@ int prefill_tc(b2_ctx* c, int slot, const int32_t* tokens, int n, int pos0, bool
     if ((rc = ensure_batch(c))) return rc;
     if ((rc = ensure_prefill(c))) return rc;
     const b2_model_info& I = c->m->info;
+    if ((rc = kv_map(c, slot, pos0, pos0 + n - 1))) return rc;
+    if ((rc = kv_sync_table(c))) return rc;
     for (int done = 0; done < n;) {
         const int T = std::min(n - done, std::min(prefill_tc_chunk(c), c->pf.cap));
         B2_CUDA_CHECK(cudaMemcpyAsync(c->pf.tok, tokens + done, (size_t)T * 4, cudaMemcpyHostToDevice, c->stream));
@@ -1238,6 +1278,32 @@ extern "C" int b2_ctx_max_batch(b2_ctx* c) {
     if (cudaSetDevice(c->m->device) != cudaSuccess) return GEMM_MAX_COLS;
     if (prefill_tc_supported(c->m) && !ensure_batch(c) && !ensure_prefill(c) && c->m->f16_cache) return BATCH_MAX_COLS;
     return GEMM_MAX_COLS;
+}
+
+extern "C" int b2_ctx_slot_truncate(b2_ctx* c, int slot, int n_keep) {
+    if (!c || slot < 0 || slot >= c->n_slots || n_keep < 0) {
+        set_error("b2_ctx_slot_truncate: bad arguments (slot %d, keep %d)", slot, n_keep);
+        return B2_EINVAL;
+    }
+    if (!c->kv_dynamic || slot == 0) return 0;   // statically mapped: nothing to give back
+    // the pages may still be read by work in flight
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    int32_t* row = c->kv_table.data() + (size_t)slot * c->pages_per_seq;
+    for (int i = (n_keep + KV_PAGE - 1) / KV_PAGE; i < c->pages_per_seq; i++)
+        if (row[i] >= 0) {
+            c->kv_free.push_back(row[i]);
+            row[i] = -1;
+            c->kv_table_dirty = true;
+        }
+    return 0;
+}
+
+extern "C" int b2_ctx_kv_pages(const b2_ctx* c, int* total_out, int* free_out, int* page_tokens_out) {
+    if (!c) return B2_EINVAL;
+    if (total_out) *total_out = c->n_pages;
+    if (free_out) *free_out = c->kv_dynamic ? (int)c->kv_free.size() : 0;
+    if (page_tokens_out) *page_tokens_out = KV_PAGE;
+    return c->kv_dynamic ? 1 : 0;
 }
 
 extern "C" int b2_ctx_prefill(b2_ctx* c, int slot, const int32_t* tokens, int n, int pos0, int32_t* next_token_out, float* logits_out_host) {
@@ -1340,10 +1406,43 @@ extern "C" int b2_ctx_create_slots(b2_model* m, int n_ctx, int n_slots, b2_ctx**
     c->use_pdl = !env_flag("B2_NO_PDL");
     B2_CUDA_CHECK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     int rc;
-    // [slot][layer][kv head][position][head_dim]: slot 0 is the single-sequence paths' cache
+    // the KV pool (model.h): [layer][kv head][kv_tokens][head_dim], pages of KV_PAGE positions, slot 0 = pages 0..
     c->n_slots = n_slots;
-    c->slot_stride = (int64_t)I.n_layer * I.n_kv * n_ctx * I.head_dim;
-    const size_t kv_elems = (size_t)c->slot_stride * n_slots;
+    c->pages_per_seq = (n_ctx + KV_PAGE - 1) / KV_PAGE;
+    {
+        const size_t full_pages = (size_t)c->pages_per_seq * n_slots;
+        const size_t page_bytes = 2ull * I.n_layer * I.n_kv * KV_PAGE * I.head_dim * sizeof(__half);   // K and V
+        size_t pages = full_pages;
+        if (const char* e = getenv("B2_KV_POOL_TOKENS")) {
+            const long long t = atoll(e);
+            if (t > 0) pages = (size_t)((t + KV_PAGE - 1) / KV_PAGE);
+        }
+        size_t free_b = 0, total_b = 0;
+        B2_CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+        const size_t cap_pages = (size_t)((double)free_b * 0.6 / (double)page_bytes);   // leave room for the fp16 copy and scratch
+        if (n_slots > 1 && pages > cap_pages) pages = cap_pages;
+        // at least slot 0 whole and one page for every other slot
+        pages = std::max(pages, (size_t)c->pages_per_seq + (size_t)(n_slots - 1));
+        pages = std::min(pages, full_pages);
+        c->n_pages = (int)pages;
+        c->kv_dynamic = pages < full_pages;
+    }
+    if (c->kv_dynamic && !attn_batch_supported(I.head_dim, n_ctx, batch_attn_splits(n_ctx))) {
+        set_error("ctx: a KV pool smaller than n_slots x n_ctx needs head_dim 64/128 and n_ctx <= %d", KV_PAGE * ATTN_MAX_SPLITS);
+        return B2_EUNSUP;
+    }
+    c->kv_tokens = c->n_pages * KV_PAGE;
+    c->slot_stride = (int64_t)c->pages_per_seq * KV_PAGE * I.head_dim;   // static mapping: slot s = rows [s * pps * KV_PAGE, ..)
+    c->kv_table.assign((size_t)n_slots * c->pages_per_seq, -1);
+    for (int s = 0; s < n_slots; s++)
+        for (int i = 0; i < c->pages_per_seq; i++)
+            if (s == 0 || !c->kv_dynamic) c->kv_table[(size_t)s * c->pages_per_seq + i] = s * c->pages_per_seq + i;
+    if (c->kv_dynamic)
+        for (int pg = c->n_pages - 1; pg >= c->pages_per_seq; pg--) c->kv_free.push_back(pg);
+    if ((rc = dmalloc(&c->d_kv_table, c->kv_table.size()))) return rc;
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->d_kv_table, c->kv_table.data(), c->kv_table.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    const size_t kv_elems = (size_t)I.n_layer * I.n_kv * c->kv_tokens * I.head_dim;
     if ((rc = dmalloc(&c->k_cache, kv_elems))) return rc;
     if ((rc = dmalloc(&c->v_cache, kv_elems))) return rc;
     B2_CUDA_CHECK(cudaMemsetAsync(c->k_cache, 0, kv_elems * sizeof(__half), c->stream));
@@ -1428,6 +1527,7 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->exec) cudaGraphExecDestroy(c->exec);
     if (c->graph) cudaGraphDestroy(c->graph);
+    if (c->d_kv_table) cudaFree(c->d_kv_table);
     if (c->tp_comm) tp_comm_free(c->tp_comm);
     if (c->tp_part) cudaFree(c->tp_part);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
@@ -1633,9 +1733,9 @@ extern "C" int b2_ctx_get_kv(b2_ctx* c, int layer, int pos, uint16_t* k_out_host
         set_error("b2_ctx_get_kv: layer %d / position %d out of range", layer, pos);
         return B2_ERANGE;
     }
-    const size_t kv_layer = (size_t)I.n_kv * c->n_ctx * I.head_dim;
+    const size_t kv_layer = (size_t)I.n_kv * c->kv_tokens * I.head_dim;
     for (int h = 0; h < I.n_kv; h++) {
-        const size_t off = layer * kv_layer + ((size_t)h * c->n_ctx + pos) * I.head_dim;
+        const size_t off = layer * kv_layer + ((size_t)h * c->kv_tokens + pos) * I.head_dim;   // slot 0: identity pages
         B2_CUDA_CHECK(cudaMemcpyAsync(k_out_host + (size_t)h * I.head_dim, c->k_cache + off, I.head_dim * 2, cudaMemcpyDeviceToHost, c->stream));
         B2_CUDA_CHECK(cudaMemcpyAsync(v_out_host + (size_t)h * I.head_dim, c->v_cache + off, I.head_dim * 2, cudaMemcpyDeviceToHost, c->stream));
     }

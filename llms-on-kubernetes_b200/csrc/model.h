@@ -47,6 +47,7 @@ struct b2_model {
 };
 
 constexpr int BATCH_MAX_COLS = 256;
+constexpr int KV_PAGE = 256;   // positions per page of the KV pool = the attention kernels' chunk
 
 struct b2_ctx {
     b2_model* m = nullptr;
@@ -86,6 +87,19 @@ struct b2_ctx {
     // of slot s start s * slot_stride halfs after slot 0's.
     int n_slots = 1;
     int64_t slot_stride = 0;
+    // Paged KV: the cache is one pool of kv_tokens rows per (layer, kv head), [layer][kv head][kv_tokens][head_dim], cut
+    // into pages of KV_PAGE positions.  kv_table[slot][i] (host mirror + device copy) is the page holding positions
+    // [i * KV_PAGE, (i + 1) * KV_PAGE) of the slot, or -1.  Slot 0 owns pages 0 .. pages_per_seq - 1 for good (identity),
+    // so the single-sequence kernels address it as a contiguous cache with row stride kv_tokens.  With a pool large
+    // enough for every slot at full length (the default when it fits) every slot is mapped like that up front
+    // (kv_dynamic = false, slot_stride = pages_per_seq * KV_PAGE rows); a smaller pool (B2_KV_POOL_TOKENS, or the
+    // HBM cap) maps pages on demand and releases them with b2_ctx_slot_truncate.
+    int kv_tokens = 0, pages_per_seq = 0, n_pages = 0;
+    bool kv_dynamic = false;
+    std::vector<int32_t> kv_table;     // [n_slots][pages_per_seq]
+    std::vector<int32_t> kv_free;      // unmapped pages (stack)
+    int32_t* d_kv_table = nullptr;
+    bool kv_table_dirty = false;
     struct Batch {
         float *x = nullptr, *q = nullptr, *attn_out = nullptr, *h = nullptr, *logits = nullptr;
         uint8_t* act = nullptr;                                   // quantised activations of the current mat-mul input

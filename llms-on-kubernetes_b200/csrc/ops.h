@@ -30,9 +30,11 @@ size_t attn_scratch_bytes_batch(int n_head, int head_dim, int max_splits, int n_
 // attn_batch.cu: the same batched decode attention on the tensor cores (the step kernel's work item per (column, kv
 // head, 256-token chunk)); scratch and cols_cap as for launch_attn_decode's batched form, max_chunks * 256 >= n_ctx
 bool attn_batch_supported(int head_dim, int n_ctx, int max_chunks);
+// n_ctx: rows per kv head in kc / vc (the stride).  kv_table != nullptr (paged cache): position p of slot s is row
+// kv_table[s * kv_pps + p / 256] * 256 + p % 256; col_slot / slot_stride then only name the slot
 int launch_attn_batch(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim, int n_ctx,
                       const int* col_pos, const int* col_slot, int64_t slot_stride, int n_cols, int max_chunks, void* scratch, int cols_cap,
-                      cudaStream_t st);
+                      cudaStream_t st, const int* kv_table = nullptr, int kv_pps = 0);
 
 // misc.cu
 // x[d] = dequantised row *token_ptr of the embedding table (row a10)
@@ -50,8 +52,10 @@ int launch_rope(float* x, int n_heads, int head_dim, int n_dims, int mode, int p
 
 // prefill_attn.cu: causal attention of T consecutive prompt positions [pos0, pos0 + T) of one sequence over its fp16
 // cache (kc, vc: the slot's and layer's [n_kv][n_ctx][head_dim]); q, out: [T][n_head * head_dim] fp32
+// pages != nullptr (paged cache): the sequence's page list -- position p is row pages[p / 256] * 256 + p % 256 of the
+// n_ctx rows per kv head
 int launch_prefill_attn(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim, int n_ctx, int T, int pos0,
-                        cudaStream_t st);
+                        cudaStream_t st, const int* pages = nullptr);
 
 // prefill_ops.cu: the elementwise kernels of the prompt-phase (tensor-core) path, over all T rows at once
 struct PrefillQkvArgs {
@@ -65,6 +69,10 @@ struct PrefillQkvArgs {
     // point at slot 0); nullptr: row t is position pos0 + t of the one sequence k_cache / v_cache belong to
     const int32_t *col_pos, *col_slot;
     int64_t slot_stride;
+    // paged cache: position p of slot s (the column's, or `slot` in the prompt form) is row
+    // kv_table[s * kv_pps + p / 256] * 256 + p % 256 of the n_ctx rows per kv head; nullptr: contiguous slots
+    const int32_t* kv_table;
+    int kv_pps, slot;
     // the mat-mul's split-K reduction deferred to this kernel (tc_gemm.cuh TcParts): splits > 1 -> element (t, col) is
     // the sum over s of parts_ws[s * parts_slice + t * (nq + 2 nk) + col] and qkv is not read
     const float* parts_ws;

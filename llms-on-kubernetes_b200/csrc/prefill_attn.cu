@@ -48,7 +48,7 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
 template <int HD>
 __global__ void __launch_bounds__(PA_THREADS, HD == 128 ? 3 : 4)
 prefill_attn_kernel(const float* __restrict__ q, const __half* __restrict__ kc, const __half* __restrict__ vc, float* __restrict__ out, int n_head,
-                    int n_kv, int n_ctx, int T, int pos0, float scale) {
+                    int n_kv, int n_ctx, int T, int pos0, float scale, const int* __restrict__ pages) {
     constexpr int CH = HD / 8;                    // 16-byte chunks per row
     constexpr int TILE = PA_BK * HD * 2;          // bytes of one K or V block
     extern __shared__ __align__(128) uint8_t pa_smem[];
@@ -71,7 +71,9 @@ prefill_attn_kernel(const float* __restrict__ q, const __half* __restrict__ kc, 
             const int key = idx / CH, ch = idx % CH;
             const int kabs = kb * PA_BK + key;
             const bool ok = kabs < kv_end;
-            const size_t src = (size_t)(ok ? kabs : 0) * HD + ch * 8;
+            // paged cache: position kabs is row pages[kabs / 256] * 256 + kabs % 256 (a 64-key block never straddles a page)
+            const int krow = !ok ? 0 : pages ? pages[kabs >> 8] * 256 + (kabs & 255) : kabs;
+            const size_t src = (size_t)krow * HD + ch * 8;
             const uint32_t off = (uint32_t)(key * HD * 2 + ((ch ^ (key & 7)) << 4));
             cp_async16(kdst + off, kh + src, ok);
             cp_async16(vdst + off, vh + src, ok);
@@ -201,8 +203,8 @@ prefill_attn_kernel(const float* __restrict__ q, const __half* __restrict__ kc, 
 }  // namespace
 
 int launch_prefill_attn(const float* q, const __half* kc, const __half* vc, float* out, int n_head, int n_kv, int head_dim, int n_ctx, int T, int pos0,
-                        cudaStream_t st) {
-    if (!q || !kc || !vc || !out || T <= 0 || pos0 < 0 || pos0 + T > n_ctx || n_kv <= 0 || n_head % n_kv) {
+                        cudaStream_t st, const int* pages) {
+    if (!q || !kc || !vc || !out || T <= 0 || pos0 < 0 || (!pages && pos0 + T > n_ctx) || n_kv <= 0 || n_head % n_kv) {
         set_error("prefill_attn: bad arguments (T=%d pos0=%d n_ctx=%d heads %d/%d)", T, pos0, n_ctx, n_head, n_kv);
         return B2_EINVAL;
     }
@@ -211,10 +213,10 @@ int launch_prefill_attn(const float* q, const __half* kc, const __half* vc, floa
     if (head_dim == 128) {
         constexpr int smem = 4 * PA_BK * 128 * 2;
         B2_CUDA_CHECK(cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        prefill_attn_kernel<128><<<grid, PA_THREADS, smem, st>>>(q, kc, vc, out, n_head, n_kv, n_ctx, T, pos0, scale);
+        prefill_attn_kernel<128><<<grid, PA_THREADS, smem, st>>>(q, kc, vc, out, n_head, n_kv, n_ctx, T, pos0, scale, pages);
     } else if (head_dim == 64) {
         constexpr int smem = 4 * PA_BK * 64 * 2;
-        prefill_attn_kernel<64><<<grid, PA_THREADS, smem, st>>>(q, kc, vc, out, n_head, n_kv, n_ctx, T, pos0, scale);
+        prefill_attn_kernel<64><<<grid, PA_THREADS, smem, st>>>(q, kc, vc, out, n_head, n_kv, n_ctx, T, pos0, scale, pages);
     } else {
         set_error("prefill_attn: head_dim %d is not built (64, 128)", head_dim);
         return B2_EUNSUP;

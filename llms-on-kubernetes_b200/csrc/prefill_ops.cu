@@ -37,7 +37,15 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
         return v;
     };
     const int pos = a.col_pos ? a.col_pos[t] : a.pos0 + t;
-    const size_t slot_off = a.col_slot ? (size_t)a.col_slot[t] * a.slot_stride : 0;
+    // cache row of this position: through the page table (slot = the column's, or the prompt's one sequence), else the
+    // contiguous window of the slot
+    size_t slot_off = a.col_slot ? (size_t)a.col_slot[t] * a.slot_stride : 0;
+    int row = pos;
+    if (a.kv_table) {
+        const int slot = a.col_slot ? a.col_slot[t] : a.slot;
+        row = a.kv_table[slot * a.kv_pps + (pos >> 8)] * 256 + (pos & 255);
+        slot_off = 0;
+    }
     const int hd = a.head_dim, hp = hd / 2;
     if (pi < nq2 + nk2) {
         const bool is_q = pi < nq2;
@@ -63,7 +71,7 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
             dst[ea] = oa;
             dst[eb] = ob;
         } else {
-            __half* dst = a.k_cache + slot_off + ((size_t)head * a.n_ctx + pos) * hd;
+            __half* dst = a.k_cache + slot_off + ((size_t)head * a.n_ctx + row) * hd;
             dst[ea - head * hd] = __float2half_rn(oa);
             dst[eb - head * hd] = __float2half_rn(ob);
         }
@@ -75,7 +83,7 @@ __global__ void __launch_bounds__(256) qkv_post_kernel(PrefillQkvArgs a) {
             va += a.bv[ea];
             vb += a.bv[ea + 1];
         }
-        __half* dst = a.v_cache + slot_off + ((size_t)head * a.n_ctx + pos) * hd + (ea - head * hd);
+        __half* dst = a.v_cache + slot_off + ((size_t)head * a.n_ctx + row) * hd + (ea - head * hd);
         *(__half2*)dst = __floats2half2_rn(va, vb);
     }
 }

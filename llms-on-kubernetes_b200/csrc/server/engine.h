@@ -294,6 +294,7 @@ struct Engine {
             j->slot = best;
             j->fed = best_cp;
             slot_cached[best].resize(best_cp);
+            b2_ctx_slot_truncate(ctx, best, (int)best_cp);   // paged KV: the pages past the shared prefix go back to the pool
             slot_job[best] = j;
             m_deferred--;
             m_processing++;
@@ -324,6 +325,18 @@ struct Engine {
             if (!accept_next(j)) return;   // rows past this token in the cache are simply not recorded
             if (i < k - 1) cached.push_back(chunk[i]);
         }
+    }
+
+    // the KV pool is out of pages: idle slots give up the prefixes they were keeping for reuse
+    bool reclaim_idle_slots() {
+        bool any = false;
+        for (int s = 1; s < n_slots; s++)
+            if (!slot_job[s] && !slot_cached[s].empty()) {
+                slot_cached[s].clear();
+                b2_ctx_slot_truncate(ctx, s, 0);
+                any = true;
+            }
+        return any;
     }
 
     void run_scheduler() {
@@ -391,8 +404,11 @@ struct Engine {
                 for (Job* j : slot_job) {
                     if (!j || j->finished || j->have_next || j->prompt->size() - j->fed < 64) continue;
                     int32_t t = 0;
-                    const int rc = b2_ctx_prefill(ctx, j->slot, j->prompt->data() + j->fed, (int)(j->prompt->size() - j->fed), (int)j->fed,
-                                                  &t, j->greedy ? nullptr : logits.data());
+                    int rc = b2_ctx_prefill(ctx, j->slot, j->prompt->data() + j->fed, (int)(j->prompt->size() - j->fed), (int)j->fed, &t,
+                                            j->greedy ? nullptr : logits.data());
+                    if (rc == B2_ENOMEM && reclaim_idle_slots())
+                        rc = b2_ctx_prefill(ctx, j->slot, j->prompt->data() + j->fed, (int)(j->prompt->size() - j->fed), (int)j->fed, &t,
+                                            j->greedy ? nullptr : logits.data());
                     if (rc) { fail(*j, b2_last_error()); continue; }
                     auto& cached = slot_cached[j->slot];
                     cached.insert(cached.end(), j->prompt->begin() + j->fed, j->prompt->end());
@@ -431,7 +447,9 @@ struct Engine {
             b_out.resize(n);
             m_passes++;
             m_pass_cols += (uint64_t)n;
-            const int rc = b2_ctx_decode_batch(ctx, b_tok.data(), b_slot.data(), b_pos.data(), n, 0, b_out.data(), nullptr);
+            int rc = b2_ctx_decode_batch(ctx, b_tok.data(), b_slot.data(), b_pos.data(), n, 0, b_out.data(), nullptr);
+            if (rc == B2_ENOMEM && reclaim_idle_slots())
+                rc = b2_ctx_decode_batch(ctx, b_tok.data(), b_slot.data(), b_pos.data(), n, 0, b_out.data(), nullptr);
             if (rc) {
                 const std::string msg = b2_last_error();
                 for (Job* j : b_job)
