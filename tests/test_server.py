@@ -327,3 +327,26 @@ def test_metrics_endpoint_counts_the_work(server):
     assert after["b2:requests_total"] - before["b2:requests_total"] == 1
     assert after["llamacpp:requests_processing"] == 0 and after["llamacpp:requests_deferred"] == 0
     assert after["b2:slots"] >= 1 and after["b2:max_batch_columns"] in (32, 256)
+
+
+@pytest.mark.gpu
+def test_oversubscribed_kv_pool_recycles_pages(b2, tiny_models):
+    """Eight slots over a pool of six pages (two of them slot 0's): idle slots keep their prefixes only until somebody
+    needs the pages.  Five rounds of three concurrent requests with fresh prompts all complete."""
+    import threading
+    port, proc = run_server(b2, tiny_models["tiny-llama-q4_k_m"], {"B2_N_SLOTS": "8", "B2_KV_POOL_TOKENS": str(6 * 256)})
+    try:
+        rng = np.random.default_rng(31)
+        for rnd in range(5):
+            reqs = [{"model": "tinyllama", "prompt": rng.integers(3, 1024, size=int(rng.integers(20, 90))).tolist(), "max_tokens": 10,
+                     "temperature": 0, "ignore_eos": True} for _ in range(3)]
+            out = [None] * 3
+            ts = [threading.Thread(target=lambda i=i: out.__setitem__(i, post(port, "/v1/completions", reqs[i]))) for i in range(3)]
+            for t in ts: t.start()
+            for t in ts: t.join()
+            for (st, o), rq in zip(out, reqs):
+                assert st == 200, o
+                assert o["usage"]["completion_tokens"] == 10 and o["usage"]["prompt_tokens"] == len(rq["prompt"])
+    finally:
+        proc.terminate()
+        proc.wait(timeout=10)
