@@ -263,6 +263,14 @@ int b2_ctx_batch_logits(b2_ctx* c, int col, float* logits_out_host);
  * position.  B2_EUNSUP when the model's shapes or types are outside the path (use b2_ctx_decode_batch). */
 int b2_ctx_prefill(b2_ctx* ctx, int slot, const int32_t* tokens, int n, int pos0, int32_t* next_token_out, float* logits_out_host);
 
+/* The prompts (or prompt tails) of several sequences in ONE pass over the weights (llama_decode with a batch holding
+ * several sequences' prompt tokens): segment i is lens[i] tokens at positions pos0[i] .. of slot slots[i] (distinct
+ * slots), the token ids of all segments concatenated in `tokens`; at most 2048 rows (B2_PREFILL_CHUNK) and 256
+ * segments per call.  next_tokens_out[n_seq] / logits_out_host[n_seq][vocab] (either may be NULL): greedy token and
+ * logits of every segment's LAST position.  Same kernels as b2_ctx_prefill, causal attention per segment. */
+int b2_ctx_prefill_multi(b2_ctx* ctx, int n_seq, const int32_t* slots, const int32_t* pos0, const int32_t* lens, const int32_t* tokens,
+                         int32_t* next_tokens_out, float* logits_out_host);
+
 /* Greedy generation entirely on the device: starting from the state left by b2_ctx_decode (whose greedy
  * token t0 the caller already has), run n_steps decode steps, each consuming the previous argmax without a
  * host round trip, then copy the n_steps newly produced token ids t1..tn to tokens_out_host. */

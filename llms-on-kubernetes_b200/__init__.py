@@ -106,6 +106,7 @@ SYMBOLS = {
     "b2_ctx_batch_logits": (_I, [_P, _I, _P]),
     "b2_ctx_prefill": (_I, [_P, _I, _P, _I, _I, _P, _P]),
     "b2_ctx_max_batch": (_I, [_P]),
+    "b2_ctx_prefill_multi": (_I, [_P, _I, _P, _P, _P, _P, _P, _P]),
     "b2_ctx_slot_truncate": (_I, [_P, _I, _I]),
     "b2_ctx_kv_pages": (_I, [_P, C.POINTER(_I), C.POINTER(_I), C.POINTER(_I)]),
     "b2_ctx_generate_greedy": (_I, [_P, _I, _P]),
@@ -387,6 +388,19 @@ class Context:
     def allreduce_init(self, unique_id: bytes):
         """Collective over the tensor-parallel ranks: joins the NCCL communicator and finishes the context's set-up."""
         check(lib.b2_allreduce_init(self.h, unique_id, len(unique_id)))
+
+    def prefill_multi(self, prompts, slots, pos0=None, want_logits: bool = True):
+        """Several sequences' prompts in one pass -> (greedy ids [n_seq], logits [n_seq, vocab] of each last position)."""
+        n = len(prompts)
+        sl = np.ascontiguousarray(slots, np.int32)
+        p0 = np.zeros(n, np.int32) if pos0 is None else np.ascontiguousarray(pos0, np.int32)
+        ln = np.ascontiguousarray([len(p) for p in prompts], np.int32)
+        toks = np.ascontiguousarray(np.concatenate([np.asarray(p, np.int32) for p in prompts]), np.int32)
+        nxt = np.empty(n, np.int32)
+        logits = np.empty((n, self.model.info.vocab), np.float32) if want_logits else None
+        check(lib.b2_ctx_prefill_multi(self.h, n, sl.ctypes.data, p0.ctypes.data, ln.ctypes.data, toks.ctypes.data, nxt.ctypes.data,
+                                       logits.ctypes.data if want_logits else None))
+        return nxt.tolist(), logits
 
     def slot_truncate(self, slot: int, n_keep: int = 0):
         check(lib.b2_ctx_slot_truncate(self.h, slot, n_keep))

@@ -817,8 +817,9 @@ int enqueue_logits(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t st
 bool prefill_tc_supported(const b2_model* m);
 int ensure_prefill(b2_ctx* c);
 int tc_min_rows(const b2_model* m);
+struct PromptSeg { int row0, T, pos0, slot; };   // rows [row0, row0 + T) of a pass = positions [pos0, pos0 + T) of `slot`
 int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0, const int32_t* col_pos, const int32_t* col_slot,
-                    cudaStream_t st);
+                    cudaStream_t st, const std::vector<PromptSeg>* segs = nullptr);
 int enqueue_logits_tc(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t st);
 
 // does a decode batch of n columns take the tensor-core pass?  Wider than the int8 kernel's 32 columns: always (the
@@ -1081,6 +1082,8 @@ int ensure_prefill(b2_ctx* c) {
     B2_CUDA_CHECK(cudaMalloc(&p.xb, cap * max_k * 2));
     if (!c->m->f16_cache) B2_CUDA_CHECK(cudaMalloc(&p.wb, max_w * 2));   // one matrix at a time, dequantised per pass
     if ((rc = dmalloc(&p.tok, cap))) return rc;
+    if ((rc = dmalloc(&p.col_pos, cap))) return rc;
+    if ((rc = dmalloc(&p.col_slot, cap))) return rc;
     // split-K workspace: the largest any mat-mul of a pass of up to `cap` rows asks for
     const int shapes[5][2] = {{(int)(qdim + 2 * kvdim), I.d_model}, {I.d_model, (int)qdim}, {2 * I.d_ff, I.d_model}, {I.d_model, I.d_ff}, {I.vocab, I.d_model}};
     for (const auto& s : shapes)
@@ -1094,9 +1097,10 @@ int ensure_prefill(b2_ctx* c) {
 //   prompt form (col_pos == nullptr): the rows are consecutive positions [pos0, pos0 + T) of sequence slot `slot`,
 //     causal attention over the chunk (prefill_attn.cu)
 //   batch form: row j is column j of a decode batch with its own position col_pos[j] and slot col_slot[j] (device
-//     arrays), attention per column over its own sequence (attn.cu)
+//     arrays), attention per column over its own sequence (attn_batch.cu)
+//   several prompts (segs != nullptr): the batch form's per-row positions and slots, with causal attention per segment
 int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0, const int32_t* col_pos, const int32_t* col_slot,
-                    cudaStream_t st) {
+                    cudaStream_t st, const std::vector<PromptSeg>* segs) {
     b2_model* m = c->m;
     const b2_model_info& I = m->info;
     auto& p = c->pf;
@@ -1183,7 +1187,12 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         mark(0);
         if ((rc = launch_prefill_qkv_post(qa, T, st))) return rc;
         mark(1);
-        if (col_pos) {
+        if (segs) {
+            for (const PromptSeg& sg : *segs)
+                if ((rc = launch_prefill_attn(p.q + (size_t)sg.row0 * qdim, kc, vc, p.attn_out + (size_t)sg.row0 * qdim, I.n_head, I.n_kv, I.head_dim,
+                                              c->kv_tokens, sg.T, sg.pos0, st, c->d_kv_table + (size_t)sg.slot * c->pages_per_seq)))
+                    return rc;
+        } else if (col_pos) {
             if ((rc = enqueue_batch_attention(c, p.q, kc, vc, p.attn_out, col_pos, col_slot, T, st))) return rc;
         } else if ((rc = launch_prefill_attn(p.q, kc, vc, p.attn_out, I.n_head, I.n_kv, I.head_dim, c->kv_tokens, T, pos0, st,
                                              c->d_kv_table + (size_t)slot * c->pages_per_seq))) {
@@ -1278,6 +1287,83 @@ extern "C" int b2_ctx_max_batch(b2_ctx* c) {
     if (cudaSetDevice(c->m->device) != cudaSuccess) return GEMM_MAX_COLS;
     if (prefill_tc_supported(c->m) && !ensure_batch(c) && !ensure_prefill(c) && c->m->f16_cache) return BATCH_MAX_COLS;
     return GEMM_MAX_COLS;
+}
+
+// The prompts (or prompt tails) of several sequences in ONE pass over the weights: n_seq segments, segment i = lens[i]
+// tokens at positions pos0[i].. of slot slots[i], their token ids concatenated in `tokens`.
+extern "C" int b2_ctx_prefill_multi(b2_ctx* c, int n_seq, const int32_t* slots, const int32_t* pos0, const int32_t* lens, const int32_t* tokens,
+                                    int32_t* next_tokens_out, float* logits_out_host) {
+    if (!c || n_seq < 1 || n_seq > BATCH_MAX_COLS || !slots || !pos0 || !lens || !tokens) {
+        set_error("b2_ctx_prefill_multi: bad arguments (%d sequences, at most %d)", n_seq, BATCH_MAX_COLS);
+        return B2_EINVAL;
+    }
+    if (!prefill_tc_supported(c->m)) {
+        set_error("b2_ctx_prefill_multi: this model's shapes or types are outside the tensor-core prompt path");
+        return B2_EUNSUP;
+    }
+    const b2_model_info& I = c->m->info;
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    int rc;
+    if ((rc = ensure_batch(c))) return rc;
+    if ((rc = ensure_prefill(c))) return rc;
+    std::vector<PromptSeg> segs(n_seq);
+    int rows = 0;
+    for (int i = 0; i < n_seq; i++) {
+        if (slots[i] < 0 || slots[i] >= c->n_slots || lens[i] < 1 || pos0[i] < 0 || (int64_t)pos0[i] + lens[i] > c->n_ctx) {
+            set_error("b2_ctx_prefill_multi: segment %d (slot %d, positions %d..+%d) out of range", i, slots[i], pos0[i], lens[i]);
+            return B2_ERANGE;
+        }
+        for (int k = 0; k < i; k++)
+            if (slots[k] == slots[i]) {
+                set_error("b2_ctx_prefill_multi: slot %d appears twice", slots[i]);
+                return B2_EINVAL;
+            }
+        segs[i] = PromptSeg{rows, lens[i], pos0[i], slots[i]};
+        rows += lens[i];
+    }
+    if (rows > c->pf.cap) {
+        set_error("b2_ctx_prefill_multi: %d rows in one pass, at most %d", rows, c->pf.cap);
+        return B2_ERANGE;
+    }
+    for (int r = 0; r < rows; r++)
+        if (tokens[r] < 0 || tokens[r] >= I.vocab) {
+            set_error("b2_ctx_prefill_multi: token %d at row %d is outside the vocabulary (%d)", tokens[r], r, I.vocab);
+            return B2_ERANGE;
+        }
+    for (const PromptSeg& sg : segs)
+        if ((rc = kv_map(c, sg.slot, sg.pos0, sg.pos0 + sg.T - 1))) return rc;
+    if ((rc = kv_sync_table(c))) return rc;
+    std::vector<int32_t> rpos(rows), rslot(rows);
+    for (const PromptSeg& sg : segs)
+        for (int t = 0; t < sg.T; t++) {
+            rpos[sg.row0 + t] = sg.pos0 + t;
+            rslot[sg.row0 + t] = sg.slot;
+        }
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->pf.tok, tokens, (size_t)rows * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->pf.col_pos, rpos.data(), (size_t)rows * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->pf.col_slot, rslot.data(), (size_t)rows * 4, cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // pageable sources
+    if ((rc = enqueue_tc_pass(c, c->pf.tok, rows, 0, 0, c->pf.col_pos, c->pf.col_slot, c->stream, &segs))) return rc;
+    if (next_tokens_out || logits_out_host) {
+        // the last row of every segment, gathered (the Q|K|V buffer is free by now), through the lm_head
+        float* gathered = c->pf.qkv;
+        for (int i = 0; i < n_seq; i++)
+            B2_CUDA_CHECK(cudaMemcpyAsync(gathered + (size_t)i * I.d_model, c->pf.x + (size_t)(segs[i].row0 + segs[i].T - 1) * I.d_model,
+                                          (size_t)I.d_model * 4, cudaMemcpyDeviceToDevice, c->stream));
+        if (n_seq >= tc_min_rows(c->m) && c->m->f16_cache) rc = enqueue_logits_tc(c, gathered, n_seq, c->stream);
+        else if (n_seq <= GEMM_MAX_COLS) rc = enqueue_logits(c, gathered, n_seq, c->stream);
+        else {
+            set_error("b2_ctx_prefill_multi: %d sequences need the resident fp16 copy for their logits", n_seq);
+            rc = B2_EUNSUP;
+        }
+        if (rc) return rc;
+        if (logits_out_host)
+            B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->bt.logits, (size_t)n_seq * I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (next_tokens_out) B2_CUDA_CHECK(cudaMemcpyAsync(c->h_pin, c->bt.out, (size_t)n_seq * 4, cudaMemcpyDeviceToHost, c->stream));
+    }
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    if (next_tokens_out) memcpy(next_tokens_out, c->h_pin, (size_t)n_seq * 4);
+    return 0;
 }
 
 extern "C" int b2_ctx_slot_truncate(b2_ctx* c, int slot, int n_keep) {
@@ -1541,7 +1627,7 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
                      c->bt.attn_scratch, c->bt.argmax_scratch};
     for (void* p : bptrs)
         if (p) cudaFree(p);
-    void* pptrs[] = {c->pf.x, c->pf.qkv, c->pf.q, c->pf.attn_out, c->pf.gu, c->pf.xb, c->pf.wb, c->pf.tok, c->pf.ws};
+    void* pptrs[] = {c->pf.x, c->pf.qkv, c->pf.q, c->pf.attn_out, c->pf.gu, c->pf.xb, c->pf.wb, c->pf.tok, c->pf.ws, c->pf.col_pos, c->pf.col_slot};
     for (void* p : pptrs)
         if (p) cudaFree(p);
     if (c->h_pin) cudaFreeHost(c->h_pin);

@@ -118,6 +118,7 @@ struct b2_ctx {
         float *x = nullptr, *qkv = nullptr, *q = nullptr, *attn_out = nullptr, *gu = nullptr;
         void *xb = nullptr, *wb = nullptr; // fp16: activations [cap][max K], one dequantised matrix
         int32_t* tok = nullptr;            // [cap] device
+        int32_t *col_pos = nullptr, *col_slot = nullptr;   // [cap] device: per-row position / slot of a several-prompt pass
         float* ws = nullptr;               // split-K workspace of the mat-muls (passes of <= 128 rows)
         size_t ws_bytes = 0;
     } pf;

@@ -399,23 +399,65 @@ struct Engine {
                 retire_finished();
                 continue;
             }
-            // ---- long prompts: the whole remainder in one call on the tensor-core prompt path ----
+            // ---- long prompts: the remainders of as many waiting prompts as fit one pass of the tensor-core prompt path
+            // (b2_ctx_prefill_multi: up to 2048 rows); a prompt longer than that goes alone, in chunks (b2_ctx_prefill) ----
             if (tc_prefill) {
-                for (Job* j : slot_job) {
-                    if (!j || j->finished || j->have_next || j->prompt->size() - j->fed < 64) continue;
-                    int32_t t = 0;
-                    int rc = b2_ctx_prefill(ctx, j->slot, j->prompt->data() + j->fed, (int)(j->prompt->size() - j->fed), (int)j->fed, &t,
-                                            j->greedy ? nullptr : logits.data());
-                    if (rc == B2_ENOMEM && reclaim_idle_slots())
-                        rc = b2_ctx_prefill(ctx, j->slot, j->prompt->data() + j->fed, (int)(j->prompt->size() - j->fed), (int)j->fed, &t,
-                                            j->greedy ? nullptr : logits.data());
-                    if (rc) { fail(*j, b2_last_error()); continue; }
-                    auto& cached = slot_cached[j->slot];
-                    cached.insert(cached.end(), j->prompt->begin() + j->fed, j->prompt->end());
-                    j->fed = j->prompt->size();
-                    j->next = j->greedy ? t : sample(j->p, j->rng);
-                    j->have_next = false;
-                    accept_next(*j);
+                std::vector<Job*> todo;
+                for (Job* j : slot_job)
+                    if (j && !j->finished && !j->have_next && j->prompt->size() - j->fed >= 64) todo.push_back(j);
+                const size_t max_rows = (size_t)std::min(2048, n_ctx());
+                size_t at = 0;
+                while (at < todo.size()) {
+                    std::vector<Job*> grp;
+                    std::vector<int32_t> g_slot, g_pos0, g_len, g_tok, g_out;
+                    size_t rows = 0;
+                    while (at < todo.size() && grp.size() < 64) {
+                        Job* j = todo[at];
+                        const size_t rem = j->prompt->size() - j->fed;
+                        if (!grp.empty() && rows + rem > max_rows) break;
+                        grp.push_back(j);
+                        at++;
+                        rows += rem;
+                        if (rem > max_rows) break;   // alone: chunked inside b2_ctx_prefill
+                        g_slot.push_back(j->slot);
+                        g_pos0.push_back((int32_t)j->fed);
+                        g_len.push_back((int32_t)rem);
+                        g_tok.insert(g_tok.end(), j->prompt->begin() + j->fed, j->prompt->end());
+                    }
+                    const bool single = grp.size() == 1;   // (also every sampled request: its logits come back alone)
+                    g_out.assign(grp.size(), 0);
+                    auto call = [&]() -> int {
+                        if (single) {
+                            Job* j = grp[0];
+                            return b2_ctx_prefill(ctx, j->slot, j->prompt->data() + j->fed, (int)(j->prompt->size() - j->fed), (int)j->fed, &g_out[0],
+                                                  j->greedy ? nullptr : logits.data());
+                        }
+                        return b2_ctx_prefill_multi(ctx, (int)grp.size(), g_slot.data(), g_pos0.data(), g_len.data(), g_tok.data(), g_out.data(), nullptr);
+                    };
+                    int rc = call();
+                    if (rc == B2_ENOMEM && reclaim_idle_slots()) rc = call();
+                    if (rc) {
+                        const std::string msg = b2_last_error();
+                        for (Job* j : grp) fail(*j, msg);
+                        continue;
+                    }
+                    for (size_t i = 0; i < grp.size(); i++) {
+                        Job* j = grp[i];
+                        auto& cached = slot_cached[j->slot];
+                        cached.insert(cached.end(), j->prompt->begin() + j->fed, j->prompt->end());
+                        j->fed = j->prompt->size();
+                        if (j->greedy) j->next = g_out[i];
+                        else if (single) j->next = sample(j->p, j->rng);
+                        else {
+                            // a sampled request inside a group: its last prompt token is fed again through the batch below, whose
+                            // per-column logits reach the host sampler
+                            cached.pop_back();
+                            j->fed--;
+                            continue;
+                        }
+                        j->have_next = false;
+                        accept_next(*j);
+                    }
                 }
             }
             // ---- one batch: a column per generating sequence, the rest prompt tokens ----

@@ -118,3 +118,41 @@ def test_prefill_rejects_out_of_range(b2, tiny_models):
     with pytest.raises(b2.B2Error):
         ctx.prefill([1, 2], slot=1)
     ctx.free(); m.free()
+
+
+@pytest.mark.parametrize("name", MODELS[:2] + MODELS[3:])
+def test_several_prompts_in_one_pass(b2, tiny_models, name):
+    """b2_ctx_prefill_multi: prompts of different lengths (one of them a tail after a reused prefix) share one pass over
+    the weights; every sequence's last-position logits match the oracle's own decode of that sequence, and the caches
+    serve the decode steps that follow."""
+    path = tiny_models[name]
+    m = b2.Model(path)
+    ctx = b2.Context(m, 512, n_slots=8)
+    ref = rm.RefGGUFModel(path, n_ctx=512)
+    rng = np.random.default_rng(17)
+    lens = [70, 33, 300, 5, 129, 64]
+    seqs = [rng.integers(3, m.info.vocab, size=n).tolist() for n in lens]
+    slots = [3, 1, 7, 2, 5, 6]
+    ctx.prefill(seqs[2][:100], slot=7, want_logits=False)            # sequence 2 already has a 100-token prefix cached
+    prompts = [s if i != 2 else s[100:] for i, s in enumerate(seqs)]
+    pos0 = [0 if i != 2 else 100 for i in range(len(seqs))]
+    ids, lg = ctx.prefill_multi(prompts, slots, pos0)
+    want = []
+    for i, s in enumerate(seqs):
+        for p, t in enumerate(s):
+            tok, lr = ref.decode(t, p, want_logits=p == len(s) - 1)
+        want.append((tok, lr))
+        assert close(lg[i], lr), (i, float(np.abs(lg[i] - lr).max() / np.abs(lr).max()))
+        assert ids[i] == int(np.argmax(lg[i]))
+    # one decode step of all six together on the caches the pass wrote
+    nxt = [w[0] for w in want]
+    ids2, lg2 = ctx.decode_batch(nxt, lens, slots=slots)
+    for i, s in enumerate(seqs):
+        for p, t in enumerate(s + [nxt[i]]):
+            tok, lr = ref.decode(t, p, want_logits=p == len(s))
+        assert close(lg2[i], lr), i
+    with pytest.raises(b2.B2Error):
+        ctx.prefill_multi([[1, 2], [3]], [1, 1])                     # the same slot twice
+    with pytest.raises(b2.B2Error):
+        ctx.prefill_multi([[1] * 300, [2] * 300], [1, 2])            # more rows than one pass takes (n_ctx = 512)
+    ctx.free(); m.free(); ref.close()
