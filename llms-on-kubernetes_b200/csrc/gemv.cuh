@@ -16,7 +16,9 @@ enum { EPI_STORE = 0,   // out[row] = v (+bias)
        EPI_SWIGLU = 2,  // out[p] = silu(v_a) * v_b
        EPI_ROPE_Q = 3,  // rotate the pair, store fp32 q
        EPI_ROPE_K = 4,  // rotate the pair, store fp16 into the K cache at the current position
-       EPI_V = 5 };     // store fp16 into the V cache at the current position
+       EPI_V = 5,       // store fp16 into the V cache at the current position
+       EPI_RESID_TP = 6 };  // out[row] = out[row] * res_scale + v: a tensor-parallel shard's partial sum plus its 1/tp share
+                            // of the residual, so that the all-reduce over the ranks yields residual + sum in place
 
 enum { PRO_PLAIN = 0,   // activation = x
        PRO_NORM = 1 };  // activation = rmsnorm(x) * norm_w
@@ -33,6 +35,7 @@ struct GemvSeg {
     int type, pairing, epi;
     int n_pairs, n_rows, tile0;
     int head_dim, n_ctx;
+    float res_scale;     // EPI_RESID_TP
 };
 
 struct GemvArgs {

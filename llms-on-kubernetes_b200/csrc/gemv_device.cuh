@@ -435,7 +435,7 @@ __device__ __forceinline__ EpiOperands epilogue_operands(const GemvArgs& a, cons
         o.bias_a = s.bias[ra];
         if (rb >= 0) o.bias_b = (s.pairing == PAIR_SPLIT ? s.bias_b : s.bias)[rb];
     }
-    if (s.epi == EPI_RESID) {
+    if (s.epi == EPI_RESID || s.epi == EPI_RESID_TP) {
         o.res_a = s.out[ra];
         if (rb >= 0) o.res_b = s.out[rb];
     } else if (s.epi == EPI_ROPE_Q || s.epi == EPI_ROPE_K) {
@@ -463,6 +463,10 @@ __device__ __forceinline__ void epilogue_apply(const GemvSeg& s, int p, int ra, 
         case EPI_RESID:
             s.out[ra] = o.res_a + va;
             if (rb >= 0) s.out[rb] = o.res_b + vb;
+            break;
+        case EPI_RESID_TP:
+            s.out[ra] = o.res_a * s.res_scale + va;
+            if (rb >= 0) s.out[rb] = o.res_b * s.res_scale + vb;
             break;
         case EPI_SWIGLU:
             // ggml silu: x / (1 + expf(-x))

@@ -484,13 +484,14 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
         // (tensor parallel: this rank's K slice gives a partial vector -> summed over the ranks, then added to x)
         const bool tp = m->tp_size > 1;
         common(a, c->attn_out, nullptr, I.n_head * I.head_dim);
-        seg_matrix(a.seg[0], L.wo, PAIR_ADJ, tp ? EPI_STORE : EPI_RESID);
-        a.seg[0].out = tp ? c->tp_part : c->x;
+        seg_matrix(a.seg[0], L.wo, PAIR_ADJ, tp ? EPI_RESID_TP : EPI_RESID);
+        a.seg[0].out = c->x;
+        a.seg[0].res_scale = 1.0f / (float)m->tp_size;   // exact for 2 / 4 / 8 ranks
         a.n_seg = 1;
         if ((rc = run(a, gemv_act_for_type(L.wo.type)))) return rc;
         if (tp && !matvec_only) {
-            if ((rc = tp_allreduce_add(c->tp_comm, c->tp_part, c->x, I.d_model, st))) return rc;
-            launches += 2;
+            if ((rc = tp_allreduce_inplace(c->tp_comm, c->x, I.d_model, st))) return rc;
+            launches += 1;
         }
         // --- FFN: RMSNorm -> gate, up -> SwiGLU ---
         const int ag = gemv_act_for_type(L.gate.type), au = gemv_act_for_type(L.up.type);
@@ -507,13 +508,14 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
         }
         // --- FFN down projection + residual ---
         common(a, c->h, nullptr, I.d_ff);
-        seg_matrix(a.seg[0], L.down, PAIR_ADJ, tp ? EPI_STORE : EPI_RESID);
-        a.seg[0].out = tp ? c->tp_part : c->x;
+        seg_matrix(a.seg[0], L.down, PAIR_ADJ, tp ? EPI_RESID_TP : EPI_RESID);
+        a.seg[0].out = c->x;
+        a.seg[0].res_scale = 1.0f / (float)m->tp_size;
         a.n_seg = 1;
         if ((rc = run(a, gemv_act_for_type(L.down.type)))) return rc;
         if (tp && !matvec_only) {
-            if ((rc = tp_allreduce_add(c->tp_comm, c->tp_part, c->x, I.d_model, st))) return rc;
-            launches += 2;
+            if ((rc = tp_allreduce_inplace(c->tp_comm, c->x, I.d_model, st))) return rc;
+            launches += 1;
         }
     }
     // --- final norm + lm_head ---

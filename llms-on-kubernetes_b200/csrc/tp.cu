@@ -115,6 +115,20 @@ void tp_comm_free(void* comm) {
     if (comm && nccl(&n) == 0) n->CommDestroy((ncclComm_t)comm);
 }
 
+// x[0..n) = sum over the ranks of x[0..n), in place.  The row-split mat-vecs leave x = x / tp + partial on every rank
+// (EPI_RESID_TP), so the sum is residual + the whole product without a separate add kernel.
+int tp_allreduce_inplace(void* comm, float* x, int n, cudaStream_t st) {
+    Nccl* nc;
+    int rc;
+    if ((rc = nccl(&nc))) return rc;
+    if (!comm) {
+        set_error("tensor-parallel context used before b2_allreduce_init");
+        return B2_EINVAL;
+    }
+    B2_NCCL_CHECK(nc, nc->AllReduce(x, x, (size_t)n, ncclFloat, ncclSum, (ncclComm_t)comm, st));
+    return 0;
+}
+
 // x[0..n) += sum over the ranks of part[0..n)   (part is overwritten with the sum)
 int tp_allreduce_add(void* comm, float* part, float* x, int n, cudaStream_t st) {
     Nccl* nc;
