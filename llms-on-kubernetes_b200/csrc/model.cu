@@ -490,7 +490,7 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
         a.n_seg = 1;
         if ((rc = run(a, gemv_act_for_type(L.wo.type)))) return rc;
         if (tp && !matvec_only) {
-            if ((rc = c->tp_oneshot ? tp_oneshot_allreduce(c->tp_oneshot, c->x, st) : tp_allreduce_inplace(c->tp_comm, c->x, I.d_model, st))) return rc;
+            if ((rc = tp_allreduce_inplace(c->tp_comm, c->x, I.d_model, st))) return rc;
             launches += 1;
         }
         // --- FFN: RMSNorm -> gate, up -> SwiGLU ---
@@ -514,7 +514,7 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
         a.n_seg = 1;
         if ((rc = run(a, gemv_act_for_type(L.down.type)))) return rc;
         if (tp && !matvec_only) {
-            if ((rc = c->tp_oneshot ? tp_oneshot_allreduce(c->tp_oneshot, c->x, st) : tp_allreduce_inplace(c->tp_comm, c->x, I.d_model, st))) return rc;
+            if ((rc = tp_allreduce_inplace(c->tp_comm, c->x, I.d_model, st))) return rc;
             launches += 1;
         }
     }
@@ -1616,7 +1616,6 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->exec) cudaGraphExecDestroy(c->exec);
     if (c->graph) cudaGraphDestroy(c->graph);
     if (c->d_kv_table) cudaFree(c->d_kv_table);
-    if (c->tp_oneshot) tp_oneshot_free(c->tp_oneshot);
     if (c->tp_comm) tp_comm_free(c->tp_comm);
     if (c->tp_part) cudaFree(c->tp_part);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
@@ -1650,9 +1649,6 @@ extern "C" int b2_allreduce_init(b2_ctx* c, const void* id, size_t id_bytes) {
     B2_CUDA_CHECK(cudaSetDevice(c->m->device));
     int rc;
     if ((rc = tp_comm_init(id, id_bytes, c->m->tp_rank, c->m->tp_size, &c->tp_comm))) return rc;
-    // the per-half-layer exchange: one-shot over peer memory when the ranks can map each other (B2_TP_NCCL=1 keeps NCCL)
-    if (!env_flag("B2_TP_NCCL") && tp_oneshot_init(c->tp_comm, c->m->tp_rank, c->m->tp_size, c->m->info.d_model, c->stream, &c->tp_oneshot))
-        fprintf(stderr, "b2: one-shot all-reduce unavailable (%s); using NCCL\n", get_error());
     // what b2_ctx_create does for a replica: one eager step (lazy module loading outside capture), then the graph.
     // Every rank runs the same steps, so the collectives inside match up.
     if ((rc = enqueue_decode(c, c->stream, false))) return rc;

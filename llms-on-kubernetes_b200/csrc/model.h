@@ -80,7 +80,6 @@ struct b2_ctx {
     int pos = 0;
     // tensor parallelism: NCCL communicator (b2_allreduce_init) and the partial d_model vector of a row-split mat-vec
     void* tp_comm = nullptr;
-    void* tp_oneshot = nullptr;   // tp.cu: exchange areas of the one-shot all-reduce (nullptr: NCCL)
     float* tp_part = nullptr;
     // batched path: up to BATCH_MAX_COLS tokens per pass over the weights, each with its own (sequence slot,
     // position) -- up to GEMM_MAX_COLS columns on the int8 kernel (gemm.cu), wider batches (and any batch of at least

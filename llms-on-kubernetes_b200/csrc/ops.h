@@ -89,9 +89,5 @@ int tp_comm_init(const void* id_bytes, size_t len, int rank, int size, void** co
 void tp_comm_free(void* comm);
 int tp_allreduce_add(void* comm, float* part, float* x, int n, cudaStream_t st);   // x += allreduce_sum(part)
 int tp_allreduce_inplace(void* comm, float* x, int n, cudaStream_t st);            // x = allreduce_sum(x)
-// the same sum as one kernel over peer memory (CUDA IPC); init is collective over the communicator's ranks
-int tp_oneshot_init(void* comm, int rank, int size, int n, cudaStream_t st, void** state_out);
-int tp_oneshot_allreduce(void* state, float* x, cudaStream_t st);
-void tp_oneshot_free(void* state);
 
 }  // namespace b2
