@@ -1582,7 +1582,6 @@ extern "C" int b2_ctx_create_slots(b2_model* m, int n_ctx, int n_slots, b2_ctx**
     c->use_step = !env_flag("B2_NO_STEP") && m->tp_size == 1;   // a shard exchanges partial sums between stages
     if (m->tp_size > 1) {
         // the first step (and the CUDA graph of a step) need the communicator: b2_allreduce_init finishes the set-up
-        if ((rc = dmalloc(&c->tp_part, (size_t)I.d_model))) return rc;
         B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
         c->pos = 0;
         *out = c.release();
@@ -1617,7 +1616,6 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->graph) cudaGraphDestroy(c->graph);
     if (c->d_kv_table) cudaFree(c->d_kv_table);
     if (c->tp_comm) tp_comm_free(c->tp_comm);
-    if (c->tp_part) cudaFree(c->tp_part);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
                     c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch,
                     c->d_ops, c->step_attn_partials, c->step_counters, c->step_sync, c->step_argmax_val, c->step_argmax_idx, c->step_trace};

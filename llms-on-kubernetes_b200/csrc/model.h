@@ -78,9 +78,8 @@ struct b2_ctx {
     float* step_argmax_val = nullptr;
     int* step_argmax_idx = nullptr;
     int pos = 0;
-    // tensor parallelism: NCCL communicator (b2_allreduce_init) and the partial d_model vector of a row-split mat-vec
+    // tensor parallelism: NCCL communicator (b2_allreduce_init)
     void* tp_comm = nullptr;
-    float* tp_part = nullptr;
     // batched path: up to BATCH_MAX_COLS tokens per pass over the weights, each with its own (sequence slot,
     // position) -- up to GEMM_MAX_COLS columns on the int8 kernel (gemm.cu), wider batches (and any batch of at least
     // tc_batch_min() columns when the model's fp16 copy is resident) on the tensor-core pass (tc_gemm.cu).  KV caches

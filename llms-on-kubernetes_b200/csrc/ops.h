@@ -87,7 +87,6 @@ int launch_argmax_rows(const float* logits, int64_t n, int rows, int32_t* out, c
 int tp_unique_id(void* out, size_t cap);                                   // -> bytes written (128) or an error
 int tp_comm_init(const void* id_bytes, size_t len, int rank, int size, void** comm_out);
 void tp_comm_free(void* comm);
-int tp_allreduce_add(void* comm, float* part, float* x, int n, cudaStream_t st);   // x += allreduce_sum(part)
 int tp_allreduce_inplace(void* comm, float* x, int n, cudaStream_t st);            // x = allreduce_sum(x)
 
 }  // namespace b2

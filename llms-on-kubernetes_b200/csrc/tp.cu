@@ -3,7 +3,8 @@
 // Row/column split as the scope table prescribes: attn_q/k/v by heads and ffn_gate/up by ff rows (contiguous row
 // ranges of the GGUF matrices), attn_output and ffn_down along K on super-block boundaries (model.cu uploads each
 // rank's slice).  Every rank therefore ends a half-layer with a partial d_model vector; this file sums them:
-// ncclAllReduce(sum, fp32) over NVLink, then x += sum.  One process per GPU; the host application hands every rank the
+// the row-split mat-vecs leave x / tp + partial in place of x, ncclAllReduce(sum, fp32) over NVLink makes that the new
+// residual stream on every rank.  One process per GPU; the host application hands every rank the
 // same 128-byte NCCL id (b2_allreduce_unique_id on rank 0, broadcast by whatever launched the ranks).
 //
 // libnccl is loaded with dlopen on first use: a single-GPU deployment of libb2.so neither links nor needs it.
@@ -65,19 +66,6 @@ int nccl(Nccl** out) {
         }                                                                                      \
     } while (0)
 
-__global__ void residual_add_kernel(float4* __restrict__ x, const float4* __restrict__ part, int n4) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n4) {
-        float4 a = x[i];
-        const float4 b = part[i];
-        a.x += b.x;
-        a.y += b.y;
-        a.z += b.z;
-        a.w += b.w;
-        x[i] = a;
-    }
-}
-
 }  // namespace
 
 int tp_unique_id(void* out, size_t cap) {
@@ -126,21 +114,6 @@ int tp_allreduce_inplace(void* comm, float* x, int n, cudaStream_t st) {
         return B2_EINVAL;
     }
     B2_NCCL_CHECK(nc, nc->AllReduce(x, x, (size_t)n, ncclFloat, ncclSum, (ncclComm_t)comm, st));
-    return 0;
-}
-
-// x[0..n) += sum over the ranks of part[0..n)   (part is overwritten with the sum)
-int tp_allreduce_add(void* comm, float* part, float* x, int n, cudaStream_t st) {
-    Nccl* nc;
-    int rc;
-    if ((rc = nccl(&nc))) return rc;
-    if (!comm) {
-        set_error("tensor-parallel context used before b2_allreduce_init");
-        return B2_EINVAL;
-    }
-    B2_NCCL_CHECK(nc, nc->AllReduce(part, part, (size_t)n, ncclFloat, ncclSum, (ncclComm_t)comm, st));
-    residual_add_kernel<<<(n / 4 + 255) / 256, 256, 0, st>>>((float4*)x, (const float4*)part, n / 4);
-    B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
 
