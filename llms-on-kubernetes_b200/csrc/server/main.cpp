@@ -22,6 +22,7 @@
 #include <functional>
 #include <mutex>
 #include <random>
+#include <fstream>
 #include <sstream>
 #include <thread>
 
@@ -438,6 +439,30 @@ int main(int argc, char** argv) {
         else if (a == "--tokenize") { tool_mode = "tokenize"; tool_arg = need("--tokenize"); }
         else if (a == "--detokenize") { tool_mode = "detokenize"; tool_arg = need("--detokenize"); }
         else if (a == "--apply-template") { tool_mode = "template"; tool_arg = need("--apply-template"); }
+        else if (a == "--pre-split") {
+            // offline check of the BPE pre-tokeniser: --pre-split <llama3|qwen2|gpt2> <text> prints the pieces (no model)
+            const std::string kind = need("--pre-split");
+            const std::string text = need("--pre-split");
+            Value out = Value::object(), pieces = Value::array();
+            if (!text.empty() && text[0] == '@') {
+                // @file: a JSON array of strings -> an array of piece lists
+                std::ifstream f(text.substr(1));
+                std::stringstream buf;
+                buf << f.rdbuf();
+                Value arr;
+                if (!f || !b2json::parse(buf.str(), arr) || !arr.is_array()) { fprintf(stderr, "llama-server: --pre-split @file needs a JSON array of strings\n"); return 2; }
+                for (size_t k = 0; k < arr.size(); k++) {
+                    Value one = Value::array();
+                    for (const std::string& p : b2srv::bpe_pre_split(kind, arr.at(k).string_or(""))) one.push(Value(p));
+                    pieces.push(one);
+                }
+            } else {
+                for (const std::string& p : b2srv::bpe_pre_split(kind, text)) pieces.push(Value(p));
+            }
+            out.set("pieces", pieces);
+            printf("%s\n", b2json::dump(out).c_str());
+            return 0;
+        }
         else if (a == "--help" || a == "-h") { usage(); return 0; }
         else if (a == "--version") { printf("b2 llama-server (ABI %d)\n", b2_abi_version()); return 0; }
         else {

@@ -4,14 +4,18 @@
 // of the llama-server the chart launches.
 //
 // Fidelity: the SPM path follows llama.cpp's algorithm (UTF-8 symbols, highest-score bigram merged first,
-// <0xXX> byte fallback).  The BPE path applies the GGUF's merge ranks over a GPT-2-style pre-split that is an
-// approximation of the per-model regexes (exact pre-tokenisers are "next").  Templates are
-// recognised by their markers, not interpreted as Jinja.
+// <0xXX> byte fallback).  The BPE path applies the GGUF's merge ranks over the pre-split the model's
+// tokenizer.ggml.pre names: the llama-3, qwen2 and gpt-2 regexes are matched by hand over Unicode code points
+// (bpe_pre_split; letters and numbers from unicode_tables.h), checked piece for piece against the `tokenizers`
+// library running the same regexes (tests/test_tokenizer_presplit.py).  Templates are recognised by their markers,
+// not interpreted as Jinja.
 #include "tokenizer.h"
 
 #include <algorithm>
 #include <cstring>
 #include <queue>
+
+#include "unicode_tables.h"
 
 namespace b2srv {
 
@@ -30,6 +34,14 @@ static bool kv_int(const b2_gguf* g, const char* key, int64_t* out) {
 
 bool Tokenizer::load(const b2_gguf* g, std::string* err) {
     if (!kv_string(g, "tokenizer.ggml.model", &model)) model = "llama";
+    {
+        // llama.cpp's names for the pre-tokeniser regex families (tokenizer.ggml.pre)
+        std::string pre;
+        kv_string(g, "tokenizer.ggml.pre", &pre);
+        if (pre == "llama-bpe" || pre == "llama3" || pre == "llama-v3") pre_kind = "llama3";
+        else if (pre == "qwen2" || pre == "deepseek-r1-qwen") pre_kind = "qwen2";
+        else pre_kind = "gpt2";
+    }
     const int64_t ti = b2_gguf_find_kv(g, "tokenizer.ggml.tokens");
     if (ti < 0 || b2_gguf_kv_type(g, ti) != B2_KV_ARRAY) {
         if (err) *err = "GGUF has no tokenizer.ggml.tokens";
@@ -204,9 +216,26 @@ const std::unordered_map<std::string, unsigned char>& unicode_to_byte() {
     }();
     return m;
 }
-bool is_letter(unsigned char c) { return (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z') || c >= 0x80; }
-bool is_digit(unsigned char c) { return c >= '0' && c <= '9'; }
-bool is_space(unsigned char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r'; }
+template <size_t NR>
+bool in_ranges(const uint32_t (&r)[NR][2], uint32_t cp) {
+    size_t lo = 0, hi = NR;
+    while (lo < hi) {
+        const size_t mid = (lo + hi) / 2;
+        if (cp < r[mid][0]) hi = mid;
+        else if (cp > r[mid][1]) lo = mid + 1;
+        else return true;
+    }
+    return false;
+}
+bool cp_letter(uint32_t c) { return c < 0x80 ? ((c | 0x20) >= 'a' && (c | 0x20) <= 'z') : in_ranges(UNICODE_LETTER_RANGES, c); }
+bool cp_number(uint32_t c) { return c < 0x80 ? (c >= '0' && c <= '9') : in_ranges(UNICODE_NUMBER_RANGES, c); }
+// \s of the regex engines: Unicode White_Space
+bool cp_space(uint32_t c) {
+    return (c >= 9 && c <= 13) || c == 0x20 || c == 0x85 || c == 0xA0 || c == 0x1680 || (c >= 0x2000 && c <= 0x200A) || c == 0x2028 || c == 0x2029 ||
+           c == 0x202F || c == 0x205F || c == 0x3000;
+}
+bool cp_newline(uint32_t c) { return c == '\r' || c == '\n'; }
+bool cp_symbol(uint32_t c) { return !cp_space(c) && !cp_letter(c) && !cp_number(c); }   // [^\s\p{L}\p{N}]
 }  // namespace
 
 void Tokenizer::bpe_word(const std::string& word, std::vector<int32_t>& out) const {
@@ -237,33 +266,87 @@ void Tokenizer::bpe_word(const std::string& word, std::vector<int32_t>& out) con
     }
 }
 
-void Tokenizer::encode_bpe(const std::string& text, std::vector<int32_t>& out) const {
-    // GPT-2 style pre-split: optional leading space + letters | digits (up to 3) | other symbols; runs of whitespace
+// The pre-tokeniser regexes, matched by hand (first alternative that matches wins, as in the regex engines):
+//   llama3: (?i:'s|'t|'re|'ve|'m|'ll|'d) | [^\r\n\p{L}\p{N}]?\p{L}+ | \p{N}{1,3} | ?[^\s\p{L}\p{N}]+[\r\n]* | \s*[\r\n]+ | \s+(?!\S) | \s+
+//   qwen2 : the same with \p{N} one digit at a time
+//   gpt2  : 's|'t|'re|'ve|'m|'ll|'d | ?\p{L}+ | ?\p{N}+ | ?[^\s\p{L}\p{N}]+ | \s+(?!\S) | \s+
+std::vector<std::string> bpe_pre_split(const std::string& kind, const std::string& text) {
+    const bool gpt2 = kind != "llama3" && kind != "qwen2";
+    const int max_digits = kind == "llama3" ? 3 : kind == "qwen2" ? 1 : 1 << 30;
+    // code points with their byte offsets (invalid bytes pass through as themselves)
+    std::vector<uint32_t> cp;
+    std::vector<size_t> off;
+    for (size_t i = 0; i < text.size();) {
+        const unsigned char c = text[i];
+        size_t len = utf8_len(c);
+        if (len > text.size() - i) len = 1;
+        uint32_t v = c;
+        if (len == 2) v = ((c & 0x1F) << 6) | (text[i + 1] & 0x3F);
+        else if (len == 3) v = ((c & 0x0F) << 12) | ((text[i + 1] & 0x3F) << 6) | (text[i + 2] & 0x3F);
+        else if (len == 4) v = ((c & 0x07) << 18) | ((text[i + 1] & 0x3F) << 12) | ((text[i + 2] & 0x3F) << 6) | (text[i + 3] & 0x3F);
+        cp.push_back(v);
+        off.push_back(i);
+        i += len;
+    }
+    const size_t n = cp.size();
+    off.push_back(text.size());
+    auto at = [&](size_t i) -> uint32_t { return i < n ? cp[i] : 0xFFFFFFFFu; };
+    auto lower = [](uint32_t c) { return c < 0x80 ? (uint32_t)(c | 0x20) : c; };
+    std::vector<std::string> out;
     size_t i = 0;
-    const size_t n = text.size();
     while (i < n) {
         size_t j = i;
-        const unsigned char c = text[i];
-        if (c == '\'' && i + 1 < n && strchr("sStTmMdD", text[i + 1])) j = i + 2;
-        else if (c == '\'' && i + 2 < n && (!strncasecmp(&text[i + 1], "re", 2) || !strncasecmp(&text[i + 1], "ve", 2) || !strncasecmp(&text[i + 1], "ll", 2))) j = i + 3;
-        else {
-            size_t k = i;
-            if (c == ' ' && k + 1 < n && !is_space(text[k + 1])) k++;
-            const unsigned char d = text[k];
-            if (is_letter(d)) { j = k; while (j < n && is_letter(text[j])) j++; }
-            else if (is_digit(d)) { j = k; int cnt = 0; while (j < n && is_digit(text[j]) && cnt < 3) { j++; cnt++; } }
-            else if (!is_space(d)) { j = k; while (j < n && !is_space(text[j]) && !is_letter(text[j]) && !is_digit(text[j])) j++; }
-            else {
-                j = i;
-                while (j < n && is_space(text[j])) j++;
-                // leave the last space for the following word
-                if (j < n && j - i > 1 && text[j - 1] == ' ') j--;
+        const uint32_t c = cp[i];
+        // 1. contractions
+        if (c == '\'' && i + 1 < n) {
+            const uint32_t a = gpt2 ? cp[i + 1] : lower(cp[i + 1]), b = i + 2 < n ? (gpt2 ? cp[i + 2] : lower(cp[i + 2])) : 0;
+            if (a == 's' || a == 't' || a == 'm' || a == 'd') j = i + 2;
+            else if ((a == 'r' && b == 'e') || (a == 'v' && b == 'e') || (a == 'l' && b == 'l')) j = i + 3;
+        }
+        if (j == i) {
+            if (gpt2) {
+                const size_t k = (c == ' ' && i + 1 < n) ? i + 1 : i;   // optional leading space
+                if (cp_letter(at(k))) { j = k; while (j < n && cp_letter(cp[j])) j++; }
+                else if (cp_number(at(k))) { j = k; while (j < n && cp_number(cp[j])) j++; }
+                else if (k < n && cp_symbol(cp[k])) { j = k; while (j < n && cp_symbol(cp[j])) j++; }
+            } else {
+                // 2. [^\r\n\p{L}\p{N}]?\p{L}+
+                if (cp_letter(c)) { j = i; while (j < n && cp_letter(cp[j])) j++; }
+                else if (!cp_newline(c) && !cp_number(c) && cp_letter(at(i + 1))) { j = i + 1; while (j < n && cp_letter(cp[j])) j++; }
+                // 3. \p{N}{1,3} (qwen2: one)
+                else if (cp_number(c)) { int cnt = 0; while (j < n && cp_number(cp[j]) && cnt < max_digits) { j++; cnt++; } }
+                else {
+                    // 4.  ?[^\s\p{L}\p{N}]+[\r\n]*
+                    const size_t k = (c == ' ' && i + 1 < n && cp_symbol(cp[i + 1])) ? i + 1 : i;
+                    if (cp_symbol(at(k))) {
+                        j = k;
+                        while (j < n && cp_symbol(cp[j])) j++;
+                        while (j < n && cp_newline(cp[j])) j++;
+                    }
+                }
             }
         }
-        if (j <= i) j = i + 1;
-        bpe_word(text.substr(i, j - i), out);
+        if (j == i) {
+            // whitespace run [i, e)
+            size_t e = i;
+            while (e < n && cp_space(cp[e])) e++;
+            if (e == i) e = i + 1;   // (cannot happen: every code point is letter, number, symbol or space)
+            j = e;
+            size_t last_nl = n;
+            if (!gpt2)
+                for (size_t k = i; k < e; k++)
+                    if (cp_newline(cp[k])) last_nl = k;
+            if (last_nl != n) j = last_nl + 1;            // 5. \s*[\r\n]+
+            else if (e < n && e - i > 1) j = e - 1;       // 6. \s+(?!\S): leave the last space to the next piece
+        }
+        out.push_back(text.substr(off[i], off[j] - off[i]));
         i = j;
     }
+    return out;
+}
+
+void Tokenizer::encode_bpe(const std::string& text, std::vector<int32_t>& out) const {
+    for (const std::string& piece : bpe_pre_split(pre_kind, text)) bpe_word(piece, out);
 }
 
 std::vector<int32_t> Tokenizer::encode(const std::string& text, bool with_bos, bool parse_special) const {

@@ -15,6 +15,9 @@ struct ChatMessage {
     std::string role, content;
 };
 
+// the pieces a byte-level BPE model's pre-tokeniser cuts `text` into; kind: "llama3", "qwen2", anything else = gpt-2
+std::vector<std::string> bpe_pre_split(const std::string& kind, const std::string& text);
+
 class Tokenizer {
    public:
     // reads tokenizer.ggml.* from the parsed GGUF; returns false (with err) if the vocabulary is missing
@@ -43,6 +46,7 @@ class Tokenizer {
     void bpe_word(const std::string& word, std::vector<int32_t>& out) const;
 
     std::string model;       // "llama" (SPM) or "gpt2" (byte-level BPE)
+    std::string pre_kind;    // BPE pre-tokeniser family from tokenizer.ggml.pre: "llama3", "qwen2" or "gpt2"
     std::string tmpl, tmpl_kind;
     std::vector<std::string> tokens;
     std::vector<float> scores;
