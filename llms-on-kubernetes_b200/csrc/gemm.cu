@@ -4,14 +4,17 @@
 //   producer warp : per (tile of 16 rows, K-chunk of 2048): 16 bulk copies of row segments + one bulk copy
 //                   of the chunk's quantised activations into the stage
 //   decoder warp  : unpacks the 6-bit Q4_K scale headers of the stage once
-//   8 compute warps: warp w owns super-block w of the chunk: nibbles -> u8 A fragments (16 rows x 32 k,
-//                   k permuted so that one 8-byte load feeds both halves of the fragment), activations ->
-//                   s8 B fragments (32 k x 8 columns), one MMA per sub-block and column group, the s32
-//                   results scaled per sub-block with the 6-bit scales; the "mins" term is two more MMAs
-//                   against the 32-element sums of the activations (split into 7 low bits and the rest
-//                   so that they fit int8)
-//   epilogue warp : adds the eight warps' shares and runs the fused epilogue per (row pair, column)
-// Q6_K segments use m16n8k16 s8 x s8 with one MMA per 16-element scale group.
+//   compute warps : 8 (8 columns) or 16 in two groups that split the columns (16 / 32 columns); warp w of a group
+//                   owns super-block w of the chunk: nibbles -> u8 A fragments (16 rows x 32 k, k permuted so that
+//                   one 8-byte load feeds both halves of the fragment), activations -> s8 B fragments (32 k x 8
+//                   columns), one MMA per sub-block and column group, the s32 results scaled per sub-block with
+//                   the 6-bit scales; the "mins" term is two more MMAs against the 32-element sums of the
+//                   activations (split into 7 low bits and the rest so that they fit int8)
+//   epilogue warp : adds the warps' shares and runs the fused epilogue per (row pair, column); K / V rows go to the
+//                   paged cache through the page table
+// Q5_K adds the fifth bit to the A fragments, Q6_K uses m16n8k16 s8 x s8 with one MMA per 16-element scale group,
+// Q8_0 (Q8_0 activations, K-chunks of 1024) one MMA per 32-element block.  Serves decode batches below 24 columns
+// (and every batch <= 32 when the model's fp16 copy is not resident); wider batches and prompts: tc_gemm.cu.
 #include "gemm.cuh"
 
 #include <cstdlib>

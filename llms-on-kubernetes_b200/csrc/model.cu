@@ -7,11 +7,16 @@
 //
 // HBM layout: the GGUF data section is uploaded as ONE allocation, byte for byte, at the same
 // relative offsets (so every tensor keeps its 32-byte file alignment and nothing is repacked); the
-// KV cache is fp16 [layer][kv head][position][head_dim]; activations are a handful of fp32 vectors.
-// A decode step is 5 kernels per layer + 3, captured once into a CUDA graph with programmatic
-// dependent launch edges so each mat-vec prefetches its weights under the previous kernel's tail.
-// Token id, position and step counter live on the device: greedy generation replays the graph with
-// no host round trip.
+// KV cache is one paged fp16 pool [layer][kv head][pool row][head_dim] (model.h); activations are a
+// handful of fp32 vectors.  Paths through this file:
+//   one sequence, one token : the persistent step kernel (step.cu; one launch per token, replayed as a CUDA graph with
+//                             token id, position and step counter on the device), or one launch per stage (B2_NO_STEP,
+//                             mixed activation formats, tensor-parallel shards with an NCCL all-reduce per half-layer)
+//   batches of columns      : b2_ctx_decode_batch -- int8 mma.sync kernel (gemm.cu) below 24 columns, the tensor-core
+//                             pass (tc_gemm.cu) above, per-column positions / sequence slots, attn_batch.cu
+//   prompts                 : b2_ctx_prefill(_multi) -- the tensor-core pass over whole chunks with causal attention
+//                             (prefill_attn.cu); b2_ctx_decode takes it for prompts of 24+ tokens
+// plus the resident fp16 copy of the model the tensor-core pass reads, the KV page table, and tensor-parallel shards.
 #include "model.h"
 
 #include <cmath>
