@@ -133,9 +133,13 @@ def make_handler(backends):
     return Handler
 
 
+class GatewayServer(http.server.ThreadingHTTPServer):
+    daemon_threads = True
+    request_queue_size = 1024   # hundreds of clients connect at once; the default backlog of 5 refuses most of them
+
+
 def make_gateway(backends, port=0, host="0.0.0.0"):
-    srv = http.server.ThreadingHTTPServer((host, port), make_handler(backends))
-    srv.daemon_threads = True
+    srv = GatewayServer((host, port), make_handler(backends))
     return srv, srv.server_address[1]
 
 
