@@ -565,7 +565,8 @@ int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
         p.max_k = c->step_max_k;
         p.sync_counter = c->step_sync;
         p.trace = c->step_trace;
-        const int rc = launch_step(p, c->step_act, st);
+        p.l2_ahead = c->step_l2_ahead;
+        const int rc = c->step_version == 2 ? launch_step2(p, c->step_act, st) : launch_step(p, c->step_act, st);
         if (rc == 0) c->launches_per_step = 1;
         return rc;
     }
@@ -586,7 +587,13 @@ int build_step_program(b2_ctx* c) {
     int max_k = 0;
     for (auto& op : ops)
         if (op.kind == OP_GEMV && op.g.K > max_k) max_k = op.g.K;
-    const int grid = step_grid_size(act, max_k);
+    c->step_version = 2;
+    if (const char* e = getenv("B2_STEP_V")) c->step_version = atoi(e) == 1 ? 1 : 2;
+    for (auto& op : ops)
+        if (op.kind == OP_GEMV && !step2_supports(act, op.g.K)) c->step_version = 1;
+    c->step_l2_ahead = 8;
+    if (const char* e = getenv("B2_STEP_L2_AHEAD")) c->step_l2_ahead = atoi(e) < 0 ? 0 : atoi(e);
+    const int grid = c->step_version == 2 ? step2_grid_size(act, max_k) : step_grid_size(act, max_k);
     if (grid < 0) return grid;
     if (grid > 1024) {
         set_error("step kernel: grid of %d CTAs exceeds the argmax scratch", grid);

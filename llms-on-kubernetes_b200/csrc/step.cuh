@@ -46,6 +46,8 @@ struct StepProgram {
     // 0 = compute warps passed the grid barrier, 1 = activation vector built, 2 = last tile handed to the
     // epilogue warp, 3 = this CTA arrived on the stage's grid barrier
     unsigned long long* trace;
+    // step2.cu: ring steps the L2 look-ahead warp runs in front of the producer (0 = no look-ahead; B2_STEP_L2_AHEAD)
+    int l2_ahead;
 };
 
 // tokens one CTA handles per attention work item: chosen per step from the sequence length so that the
@@ -61,5 +63,9 @@ int step_attn_max_chunks(int n_ctx, int grid);
 // number of CTAs the persistent kernel runs with for this activation format and K (co-resident clusters x 8)
 int step_grid_size(int act, int max_k);
 int launch_step(const StepProgram& p, int act, cudaStream_t st);
+// second design (step2.cu, the default; B2_STEP_V=1 keeps the first): needs every mat-vec K to be a multiple of 256
+bool step2_supports(int act, int K);
+int step2_grid_size(int act, int max_k);
+int launch_step2(const StepProgram& p, int act, cudaStream_t st);
 
 }  // namespace b2
