@@ -169,7 +169,9 @@ int b2_attn_decode(const float* q_dev, const void* k_cache_dev, const void* v_ca
  * budget, hosts whose own allocator owns all of HBM).  No counterpart in the reference: its scratch is a
  * fixed array inside libb2.so (about 133 KiB on every GPU that loads the library), so there is no
  * scratch argument.  Limits: n_head <= 64, head_dim <= 128, n_tokens <= 4096 -- larger requests fail with
- * B2_ERANGE; use b2_attn_decode for those.  The first call on each device looks up the array's device
+ * B2_ERANGE; use b2_attn_decode for those (n_ctx, the row stride of the caches, has no limit of its own beyond
+ * n_tokens <= n_ctx; sizes that are zero, negative or otherwise invalid fail with B2_EINVAL before the array is
+ * touched).  The first call on each device looks up the array's device
  * address; make that first call outside any stream capture.  All calls on a device share the array: calls
  * whose kernels overlap on the GPU race.  Calls no cudaMalloc / cudaFree. */
 int b2_attn_decode_static(const float* q_dev, const void* k_cache_dev, const void* v_cache_dev, float* out_dev,

@@ -419,6 +419,14 @@ extern "C" int b2_attn_decode_static(const float* q_dev, const void* k_cache_dev
                   n_head, head_dim, n_tokens, STATIC_MAX_HEADS, STATIC_MAX_HD, STATIC_MAX_TOKENS);
         return B2_ERANGE;
     }
+    // every precondition of the launch is checked here, BEFORE the array is touched: a negative or zero size would
+    // otherwise wrap the counter offset below and the memset would clear device globals in front of the array
+    if (n_head < 1 || n_kv < 1 || n_head % n_kv || (head_dim != 64 && head_dim != 128) || n_tokens < 1 || n_ctx < 1 || n_tokens > n_ctx) {
+        set_error("b2_attn_decode_static: n_head=%d n_kv=%d head_dim=%d n_ctx=%d n_tokens=%d: need n_head >= 1, n_kv >= 1 dividing n_head, "
+                  "head_dim 64 or 128, 1 <= n_tokens <= n_ctx",
+                  n_head, n_kv, head_dim, n_ctx, n_tokens);
+        return B2_EINVAL;
+    }
     int dev = 0;
     B2_CUDA_CHECK(cudaGetDevice(&dev));
     if (dev < 0 || dev >= MAX_DEVICES) {
@@ -440,6 +448,10 @@ extern "C" int b2_attn_decode_static(const float* q_dev, const void* k_cache_dev
     // same layout launch_attn_decode derives from (n_head, head_dim, max_splits): partial records, then counters
     size_t part = (size_t)n_head * max_splits * ((size_t)head_dim + 2) * sizeof(float);
     part = (part + 255) & ~(size_t)255;
+    if (max_splits < 1 || max_splits > STATIC_MAX_SPLITS || part + 256 > STATIC_SCRATCH_BYTES) {
+        set_error("b2_attn_decode_static: internal layout (%zu + 256 bytes, %d splits) does not fit the built-in scratch", part, max_splits);
+        return B2_ERANGE;
+    }
     // the counters must start at zero even if an earlier call on this array was interrupted
     B2_CUDA_CHECK(cudaMemsetAsync((unsigned char*)scratch + part, 0, 256, (cudaStream_t)stream));
     return launch_attn_decode(q_dev, (const __half*)k_cache_dev, (const __half*)v_cache_dev, out_dev, n_head, n_kv, head_dim, n_ctx,

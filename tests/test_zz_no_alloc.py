@@ -50,3 +50,18 @@ def test_static_scratch_refuses_oversize_requests(b2):
         rc = b2.lib.b2_attn_decode_static(d.ptr, d.ptr, d.ptr, d.ptr, n_head, n_kv, hd, n_ctx, T, None)
         assert rc == -6, (n_head, hd, T, rc)
         assert b"built-in scratch" in b2.lib.b2_last_error()
+
+
+def test_static_scratch_refuses_zero_and_negative_sizes(b2):
+    """Sizes below the valid range must be turned away before the built-in array is addressed at all: with a negative
+    head count the offset of the arrival counters would wrap around and the clearing memset would land in front of
+    the array, in some other device global of the library."""
+    d = b2.DevBuf(1 << 16)
+    for n_head, n_kv, hd, n_ctx, T in [(-1, 1, 128, 1024, 16), (0, 1, 128, 1024, 16), (32, 0, 128, 1024, 16), (32, -8, 128, 1024, 16),
+                                        (32, 5, 128, 1024, 16), (32, 8, -128, 1024, 16), (32, 8, 0, 1024, 16), (32, 8, 96, 1024, 16),
+                                        (32, 8, 128, 1024, 0), (32, 8, 128, 1024, -3), (32, 8, 128, 0, 16), (32, 8, 128, 64, 65)]:
+        rc = b2.lib.b2_attn_decode_static(d.ptr, d.ptr, d.ptr, d.ptr, n_head, n_kv, hd, n_ctx, T, None)
+        assert rc == -1, (n_head, n_kv, hd, n_ctx, T, rc)
+        assert b"b2_attn_decode_static" in b2.lib.b2_last_error()
+    b2.check(b2.lib.b2_stream_sync(None))
+
