@@ -1,21 +1,24 @@
 // matvec_team.cuh -- the mat-vec inner loop of the persistent decode kernel, second design (step2.cu).
 //
-// What the first design (gemv_device.cuh: dot_chunk) paid for: every lane re-read its 64 int8 activations from shared
-// memory for every 64 weights (64 B of x per 32 B of Q4_K), and a decoder warp rewrote the 6-bit scale headers into a
-// second shared-memory table that the compute lanes read back.  ncu showed the shared-memory pipe, not HBM, saturated
-// inside the tile phases (L1/TEX 38 % over a step whose tile phases are half of it, 20 % of the wavefronts bank
-// conflicts).  Here the activations live in REGISTERS for a whole stage:
-//   * a compute warp owns one K-slice of 8 super-blocks (2048 weights per row) for the whole stage: lane (b, c) =
-//     (block b of the slice, quarter c of the block) holds its 64 int8 activations, their scale and partial sums in
-//     22 registers, loaded once after the activation vector has been built;
-//   * the warps of a CTA form T teams of WPT slices (K = 4096: 4 teams of 2 warps; K = 14336: one team of 7); a team
-//     walks whole weight rows, so a row's 144-byte blocks are read once, by 16-byte loads that are conflict-free by
-//     construction (consecutive blocks sit 36 words apart), and nothing else is read from shared memory;
-//   * the 6-bit scales and mins of a lane's two sub-blocks are unpacked by the lane itself from the block header it
-//     loads with the quants (13 integer instructions) -- no decoder warp, no second barrier per ring slot;
-//   * the per-row sums are reduced over the 32 lanes two rows at a time (5 shuffles per pair).
-// The arithmetic per (row, block quarter) is the first design's, instruction for instruction (k4_finish etc.), so the
-// partial products are bit-identical; only the order in which quarters are added differs.
+// Measured on the B200 (tools/ubench.cu): dp4a, lop3 and imad each issue at 2 warp-instructions per clock and SM, a
+// 16-byte shared-memory load at one per 8 clocks, and the first design's tile loop (gemv_device.cuh: dot_chunk) spends
+// ~0.14 warp-instructions per weight byte -- at ~2 issued instructions per clock and SM that is 4 TB/s, which is what
+// its tile phases reach.  The limit is instruction issue, so this design cuts instructions per byte by ~3.5:
+//   * work item = 8 weight rows x two 256-element blocks, done by one warp.  For Q4_K the quants go through
+//     mma.sync.m16n8k32 (u8 x s8 -> s32) as the A operand -- loaded with ldmatrix, raw bytes, no nibble unpack for the
+//     low halves -- against a B operand whose eight columns are 32-element sub-blocks of the int8 activation vector.
+//     One MMA of the raw bytes and one of the bytes masked to their high nibbles per 32-byte chunk give every
+//     sub-block's integer dot product in the lane that finishes it (layout: q4k_rows8_blocks2_mma).  The MMA unit
+//     delivers for one useful column what dp4a delivers per lane, but in 1/16 of the issue slots, and the fma / alu
+//     pipes are left to the scale arithmetic;
+//   * the 6-bit scales and mins of a lane's two sub-blocks are unpacked by the lane itself from the block header
+//     (13 integer instructions) -- no decoder warp, no second barrier per ring slot;
+//   * every lane keeps one fp32 row sum over the whole K loop; the four lanes of a row meet once per tile (two
+//     shuffles), not once per block.
+// The other weight types run the dp4a quarter products of the first design on the same work item (lane (g, t) =
+// quarter t of row g, one block after the other).
+// The arithmetic per (row, sub-block pair) is the first design's (k4_finish), so the partial products are
+// bit-identical; only the order in which they are added differs.
 #pragma once
 #include "gemv_device.cuh"
 
@@ -25,40 +28,15 @@ namespace teamdev {
 using namespace gemvdev;
 
 constexpr int TS_NSLOT = 8;                                            // ring allocations in flight (barrier pairs)
-constexpr uint32_t TS_RING_BYTES = 3 * TILE_ROWS * (16 * 210 + 16);   // 81 024 B: three 8-row Q6_K steps at K = 4096
-constexpr uint32_t TS_STEP_CAP = TS_RING_BYTES / 3;                    // largest allocation (one step)
+constexpr uint32_t TS_RING_BYTES = 3 * TILE_ROWS * (16 * 210 + 16);   // 81 024 B: three Q6_K steps
+constexpr int MT_CHUNK = 16;      // 256-element blocks of K per ring step: two per compute warp
 
-// how the 8 compute warps split a row of K elements
-struct TeamGeo {
-    int nblk;   // 256-element blocks per row
-    int S;      // 8-block slices per row
-    int WPT;    // warps per team (slices worked on at the same time)
-    int T;      // teams = rows in flight per step
-    int nsl;    // slices per warp (1 unless a row has more than 8 slices)
-};
-__host__ __device__ inline TeamGeo team_geo(int K) {
-    TeamGeo g;
-    g.nblk = K >> 8;
-    g.S = (g.nblk + 7) >> 3;
-    if (g.S <= NCW) {
-        g.WPT = g.S;
-        g.T = NCW / g.S;          // 8, 4, 2, 2, 1, 1, 1, 1
-        g.nsl = 1;
-    } else {
-        g.WPT = NCW;
-        g.T = 1;
-        g.nsl = (g.S + NCW - 1) / NCW;
-    }
-    return g;
-}
-// bytes between consecutive rows of a step in the ring (row + 16 bytes of alignment slack, 16-byte multiple)
-__host__ __device__ inline uint32_t ts_pitch(int row_bytes) { return (((uint32_t)row_bytes + 15u) & ~15u) + 16u; }
-// rows of a tile that share one ring allocation: 8, or fewer when 8 rows do not fit TS_STEP_CAP
-__host__ __device__ inline int ts_rows_per_step(uint32_t pitch) {
-    int R = TILE_ROWS;
-    while (R > 1 && (uint32_t)R * pitch > TS_STEP_CAP) R >>= 1;
-    return R;
-}
+// bytes of one 256-element block / of one row's share of a ring step (16 blocks + 16 bytes of alignment slack).
+// Q4_K: 2320 = 18 x 128 + 16, so the eight rows of an ldmatrix 8x8 start in distinct 16-byte bank groups.
+// (Copies of half this size -- 8 blocks per step -- were measured: the SM's copy engine takes ~46 cycles per bulk
+// copy whatever its size, so 1152-byte copies cap the stream near 7 TB/s before any arithmetic.)
+__host__ __device__ inline int ts_block_bytes(int type) { return type == B2_TYPE_Q8_0 ? 8 * 34 : block_bytes_of(type); }
+__host__ __device__ inline uint32_t ts_pitch(int type) { return (uint32_t)(MT_CHUNK * ts_block_bytes(type) + 16); }
 
 // activation layout classes: which 64 elements of a block a lane (b, c) owns
 enum { XC_CONTIG = 0,   // Q4_K / Q5_K: elements 64c .. 64c+63 (sub-blocks 2c, 2c+1)
@@ -160,6 +138,107 @@ __device__ __forceinline__ float row_quarter(const uint8_t* row, int kb, int c, 
         const uint8_t* blk = row + (kb * 8 + 2 * c) * 34;
         return q80_block(blk, x.xv[0], x.xv[1], x.d0) + q80_block(blk + 34, x.xv[2], x.xv[3], x.d1);
     }
+}
+
+// ---- Q4_K: 8 rows x two blocks on the tensor cores ---------------------------------------------------------------
+// A (16 x 32 bytes per MMA) = the 32-byte chunk j of block kb0 for the tile's 8 rows (A rows 0-7) and of block
+// kb0 + 1 for the same 8 rows (A rows 8-15).  B's eight columns carry, for two chunks at a time (accumulator set A:
+// chunks 0 and 1, set B: chunks 2 and 3), the activations that belong to them:
+//     column c: chunk parity c >> 2, block (c >> 1) & 1, low / high nibbles c & 1
+// and for the MMA of chunk j the columns of the other chunk parity are zero, so the two chunks of a set accumulate
+// into the same registers without mixing.  Lane (g, t) provides column g and receives columns 2t, 2t+1: of weight row
+// g, block kb0 + (t & 1), chunk (t >> 1) [+ 2] -- in c0, c1 when t is even (A row g), in c2, c3 when odd (A row g + 8).
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t (&r)[4]) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_u8s8(int (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+// lane-constant byte offsets into a block's 256 int8 activations (swizzled granules) and sums
+struct MmaLane {
+    uint32_t xo[4];   // B fragments: set A b0, b1, set B b0, b1
+    uint32_t so;      // byte offset of this lane's first int16 sum pair inside the block's 8 sums of 32
+    bool even_chunk;  // this lane's column belongs to the even chunk of a set (g < 4)
+    bool odd_t;       // results in c2, c3
+};
+__device__ __forceinline__ MmaLane mma_lane(int lane) {
+    const int g = lane >> 2, t = lane & 3;
+    const int cp = g >> 2, bsel = (g >> 1) & 1, nh = g & 1;
+    MmaLane m;
+    const int sub_a = 2 * cp + nh, sub_b = 4 + 2 * cp + nh;
+    m.xo[0] = (uint32_t)(bsel * 256 + 16 * xswz(2 * sub_a) + 4 * t);
+    m.xo[1] = (uint32_t)(bsel * 256 + 16 * xswz(2 * sub_a + 1) + 4 * t);
+    m.xo[2] = (uint32_t)(bsel * 256 + 16 * xswz(2 * sub_b) + 4 * t);
+    m.xo[3] = (uint32_t)(bsel * 256 + 16 * xswz(2 * sub_b + 1) + 4 * t);
+    m.so = (uint32_t)((t & 1) * 16 + 4 * (t >> 1));
+    m.even_chunk = cp == 0;
+    m.odd_t = (t & 1) != 0;
+    return m;
+}
+// xq_s / bs32_s / xd_s: shared-memory addresses of the activation vector's parts; kb0: first of the warp's two blocks
+// (block kb0 + 1 may lie beyond the row: n_valid = 1); lm: this lane's ldmatrix address for chunk 0; hdr: first byte of
+// block kb0 + (t & 1) in weight row g.  Returns this lane's share of row g's dot product.
+__device__ __forceinline__ float q4k_rows8_blocks2_mma(uint32_t lm, const uint8_t* hdr, const MmaLane& ml, uint32_t xq_s, uint32_t bs32_s, uint32_t xd_s,
+                                                       int kb0, int n_valid) {
+    const uint32_t xb = xq_s + (uint32_t)kb0 * 256u;
+    // a lane whose column belongs to the second block contributes zeros when that block does not exist
+    const bool col_ok = n_valid > 1 || ml.xo[0] < 256u;
+    uint32_t xa0 = 0, xa1 = 0, xb0 = 0, xb1 = 0;
+    if (col_ok) {
+        xa0 = lds32(xb + ml.xo[0]); xa1 = lds32(xb + ml.xo[1]);
+        xb0 = lds32(xb + ml.xo[2]); xb1 = lds32(xb + ml.xo[3]);
+    }
+    const uint32_t ea0 = ml.even_chunk ? xa0 : 0u, ea1 = ml.even_chunk ? xa1 : 0u, oa0 = ml.even_chunk ? 0u : xa0, oa1 = ml.even_chunk ? 0u : xa1;
+    const uint32_t eb0 = ml.even_chunk ? xb0 : 0u, eb1 = ml.even_chunk ? xb1 : 0u, ob0 = ml.even_chunk ? 0u : xb0, ob1 = ml.even_chunk ? 0u : xb1;
+    int ra[4] = {0, 0, 0, 0}, ha[4] = {0, 0, 0, 0}, rb[4] = {0, 0, 0, 0}, hb[4] = {0, 0, 0, 0};
+    uint32_t a[4], h[4];
+    ldmatrix_x4(lm, a);
+#pragma unroll
+    for (int i = 0; i < 4; i++) h[i] = a[i] & 0xF0F0F0F0u;
+    mma_u8s8(ra, a, ea0, ea1);
+    mma_u8s8(ha, h, ea0, ea1);
+    ldmatrix_x4(lm + 64, a);
+#pragma unroll
+    for (int i = 0; i < 4; i++) h[i] = a[i] & 0xF0F0F0F0u;
+    mma_u8s8(rb, a, eb0, eb1);
+    mma_u8s8(hb, h, eb0, eb1);
+    ldmatrix_x4(lm + 32, a);
+#pragma unroll
+    for (int i = 0; i < 4; i++) h[i] = a[i] & 0xF0F0F0F0u;
+    mma_u8s8(ra, a, oa0, oa1);
+    mma_u8s8(ha, h, oa0, oa1);
+    ldmatrix_x4(lm + 96, a);
+#pragma unroll
+    for (int i = 0; i < 4; i++) h[i] = a[i] & 0xF0F0F0F0u;
+    mma_u8s8(rb, a, ob0, ob1);
+    mma_u8s8(hb, h, ob0, ob1);
+    // raw = lo + 16 hi against the low-nibble sub-block (first column), 16 hi against the high-nibble sub-block (second)
+    const int lo_a = ml.odd_t ? ra[2] - ha[2] : ra[0] - ha[0], hi_a = (ml.odd_t ? ha[3] : ha[1]) >> 4;
+    const int lo_b = ml.odd_t ? rb[2] - hb[2] : rb[0] - hb[0], hi_b = (ml.odd_t ? hb[3] : hb[1]) >> 4;
+    // scales and mins of sub-blocks 2c, 2c+1 (set A: c = t >> 1 < 2) and 2c+4, 2c+5 (set B) of this lane's block
+    const uint4 hd = *(const uint4*)hdr;
+    const uint32_t sh = (ml.so & 4u) << 2;   // 16 for the odd chunk of a set
+    const uint32_t y = hd.y >> sh, z = hd.z >> sh, w = hd.w >> sh;
+    const uint32_t sc_a = y & 0x3f3fu, mn_a = z & 0x3f3fu;
+    const uint32_t sc_b = (w & 0x0f0fu) | ((y >> 2) & 0x3030u), mn_b = ((w >> 4) & 0x0f0fu) | ((z >> 2) & 0x3030u);
+    const uint32_t blk = (uint32_t)kb0 + (ml.odd_t ? 1u : 0u);
+    const uint32_t sa = bs32_s + (uint32_t)kb0 * 16u + ml.so;
+    const int bs_a = (int)lds32(sa), bs_b = (int)lds32(sa + 8);
+    const float dx = __uint_as_float(lds32(xd_s + blk * 4u));
+    // the integer part of ggml's block sum restricted to this lane's four sub-blocks
+    const int isum = (int)(sc_a & 0xffu) * lo_a + (int)(sc_a >> 8) * hi_a + (int)(sc_b & 0xffu) * lo_b + (int)(sc_b >> 8) * hi_b;
+    const int msum = (int)(mn_a & 0xffu) * (int)(int16_t)((uint32_t)bs_a & 0xffffu) + (int)(mn_a >> 8) * (bs_a >> 16) +
+                     (int)(mn_b & 0xffu) * (int)(int16_t)((uint32_t)bs_b & 0xffffu) + (int)(mn_b >> 8) * (bs_b >> 16);
+    const float d = h2f_bits(hd.x & 0xffffu), dmin = h2f_bits(hd.x >> 16);
+    const float v = dx * (d * (float)isum - dmin * (float)msum);
+    return (n_valid > 1 || !ml.odd_t) ? v : 0.0f;
 }
 
 // sums over the warp of two values at once: lane 0 returns the total of a, lane 16 the total of b

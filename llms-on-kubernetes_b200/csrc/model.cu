@@ -566,6 +566,8 @@ int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
         p.sync_counter = c->step_sync;
         p.trace = c->step_trace;
         p.l2_ahead = c->step_l2_ahead;
+        p.fine_op = c->step_fine_op;
+        p.n_prod = c->step_n_prod;
         const int rc = c->step_version == 2 ? launch_step2(p, c->step_act, st) : launch_step(p, c->step_act, st);
         if (rc == 0) c->launches_per_step = 1;
         return rc;
@@ -591,7 +593,8 @@ int build_step_program(b2_ctx* c) {
     if (const char* e = getenv("B2_STEP_V")) c->step_version = atoi(e) == 1 ? 1 : 2;
     for (auto& op : ops)
         if (op.kind == OP_GEMV && !step2_supports(act, op.g.K)) c->step_version = 1;
-    c->step_l2_ahead = 8;
+    c->step_l2_ahead = 0;
+    if (const char* e = getenv("B2_STEP_PRODUCERS")) c->step_n_prod = atoi(e) == 2 ? 2 : 1;
     if (const char* e = getenv("B2_STEP_L2_AHEAD")) c->step_l2_ahead = atoi(e) < 0 ? 0 : atoi(e);
     const int grid = c->step_version == 2 ? step2_grid_size(act, max_k) : step_grid_size(act, max_k);
     if (grid < 0) return grid;
@@ -620,8 +623,10 @@ int build_step_program(b2_ctx* c) {
     c->step_act = act;
     c->step_max_k = max_k;
     if (env_flag("B2_STEP_TRACE")) {
-        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_trace, ops.size() * STEP_TRACE_SLOTS * sizeof(unsigned long long)));
-        B2_CUDA_CHECK(cudaMemset(c->step_trace, 0, ops.size() * STEP_TRACE_SLOTS * sizeof(unsigned long long)));
+        const size_t words = ops.size() * STEP_TRACE_SLOTS + 8 * STEP_FINE_STEPS;
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_trace, words * sizeof(unsigned long long)));
+        B2_CUDA_CHECK(cudaMemset(c->step_trace, 0, words * sizeof(unsigned long long)));
+        if (const char* e = getenv("B2_STEP_FINE")) c->step_fine_op = atoi(e);
         for (auto& op : ops) {
             c->step_desc.push_back(op.kind);
             c->step_desc.push_back(op.kind == OP_GEMV ? op.g.K : 0);
@@ -638,7 +643,7 @@ void dump_step_trace(b2_ctx* c) {
     std::vector<unsigned long long> t((size_t)c->n_ops * S);
     if (cudaMemcpy(t.data(), c->step_trace, t.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return;
     const char* kinds[] = {"embed", "gemv", "attn", "argmax"};
-    struct Acc { double wait = 0, pro = 0, tiles = 0, epi = 0, mark[4] = {0, 0, 0, 0}; int n = 0; };
+    struct Acc { double wait = 0, pro = 0, tiles = 0, epi = 0, mark[7] = {0, 0, 0, 0, 0, 0, 0}; int n = 0; };
     std::map<std::string, Acc> by;
     unsigned long long prev_arrive = 0;
     fprintf(stderr, "b2 step trace (CTA 0, ns): stage kind K tiles | barrier-wait  prologue  tiles  epilogue+arrive | marks 4..7 after stage start\n");
@@ -649,22 +654,32 @@ void dump_step_trace(b2_ctx* c) {
         const bool four = kind == OP_GEMV || kind == OP_ATTN;   // stages that stamp all four slots
         const double pro = four ? (double)(s[1] - s[0]) : 0.0;
         const double tl = four ? (double)(s[2] - s[1]) : 0.0;
-        const double epi = (double)(s[3] - (four ? s[2] : s[0]));
+        const double epi = (double)((long long)s[3] - (long long)(four ? s[2] : s[0]));
         char key[64];
         snprintf(key, sizeof key, "%s K=%d tiles=%d", kinds[kind], K, tiles);
         Acc& a = by[key];
         a.wait += wait; a.pro += pro; a.tiles += tl; a.epi += epi; a.n++;
-        for (int k = 0; k < 4; k++) a.mark[k] += s[4 + k] ? (double)(s[4 + k] - s[0]) : 0.0;
+        for (int k = 0; k < 7; k++) a.mark[k] += s[4 + k] ? (double)(s[4 + k] - s[0]) : 0.0;
         if (i < 12) fprintf(stderr, "  %3d %-28s | %8.0f %8.0f %8.0f %8.0f\n", i, key, wait, pro, tl, epi);
         prev_arrive = s[3];
     }
     fprintf(stderr, "b2 step trace, mean per stage class:\n");
     for (auto& kv : by) {
         const Acc& a = kv.second;
-        fprintf(stderr, "  %-28s x%3d | %8.0f %8.0f %8.0f %8.0f | %6.0f %6.0f %6.0f %6.0f\n", kv.first.c_str(), a.n, a.wait / a.n, a.pro / a.n,
-                a.tiles / a.n, a.epi / a.n, a.mark[0] / a.n, a.mark[1] / a.n, a.mark[2] / a.n, a.mark[3] / a.n);
+        fprintf(stderr, "  %-28s x%3d | %8.0f %8.0f %8.0f %8.0f | %6.0f %6.0f %6.0f %6.0f | ready %6.0f dot %6.0f free %6.0f\n", kv.first.c_str(), a.n, a.wait / a.n,
+                a.pro / a.n, a.tiles / a.n, a.epi / a.n, a.mark[0] / a.n, a.mark[1] / a.n, a.mark[2] / a.n, a.mark[3] / a.n, a.mark[4] / a.n, a.mark[5] / a.n,
+                a.mark[6] / a.n);
     }
     fprintf(stderr, "  whole step: %.0f ns\n", (double)(t[(size_t)(c->n_ops - 1) * S + 3] - t[0]));
+    if (c->step_fine_op >= 0 && c->step_fine_op < c->n_ops) {
+        std::vector<unsigned long long> f(8 * STEP_FINE_STEPS);
+        if (cudaMemcpy(f.data(), c->step_trace + (size_t)c->n_ops * S, f.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return;
+        const long long t0 = (long long)f[6];   // SM clock when CTA 0's compute warps passed the stage's barrier
+        fprintf(stderr, "b2 step trace, stage %d, ring steps of CTA 0 (SM cycles after the stage began): producer at step, slot free, copies issued | wait begin  data there  step done\n", c->step_fine_op);
+        for (int k = 0; k < STEP_FINE_STEPS && f[8 * k + 2]; k++)
+            fprintf(stderr, "  step %3d | %8lld %8lld %8lld | %8lld %8lld %8lld\n", k, (long long)f[8 * k + 3] - t0, (long long)f[8 * k + 4] - t0,
+                    (long long)f[8 * k + 5] - t0, (long long)f[8 * k] - t0, (long long)f[8 * k + 1] - t0, (long long)f[8 * k + 2] - t0);
+    }
 }
 
 int build_graph(b2_ctx* c) {

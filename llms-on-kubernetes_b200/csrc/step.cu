@@ -367,11 +367,11 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step_kernel(const __grid_cons
             }
             rpos = tw.rp; parity = tw.parity; fph = tw.fph;
             if (tracing) {
-                // cycles warp 0 of CTA 0 spent waiting for data / in the dot products / waiting for the epilogue warp (marks 4..6)
+                // cycles warp 0 of CTA 0 spent waiting for data / in the dot products / waiting for the epilogue warp (marks 8..10)
                 unsigned long long* tr = P.trace + oi * STEP_TRACE_SLOTS;
-                tr[4] = tr[0] + (unsigned long long)(tw.cyc_ready * 1000 / 1965);
-                tr[5] = tr[0] + (unsigned long long)(tw.cyc_dot * 1000 / 1965);
-                tr[6] = tr[0] + (unsigned long long)(tw.cyc_free * 1000 / 1965);
+                tr[8] = tr[0] + (unsigned long long)(tw.cyc_ready * 1000 / 1965);
+                tr[9] = tr[0] + (unsigned long long)(tw.cyc_dot * 1000 / 1965);
+                tr[10] = tr[0] + (unsigned long long)(tw.cyc_free * 1000 / 1965);
             }
             if (tid == 0) stamp(P, oi, 2);
             // the epilogue warp arrives on the grid barrier for this stage

@@ -48,12 +48,17 @@ struct StepProgram {
     unsigned long long* trace;
     // step2.cu: ring steps the L2 look-ahead warp runs in front of the producer (0 = no look-ahead; B2_STEP_L2_AHEAD)
     int l2_ahead;
+    // B2_STEP_FINE=<stage index>: per ring step of that stage, CTA 0 stamps {wait begin, data there, step done, copy issued}
+    // into trace[n_ops * STEP_TRACE_SLOTS + 4 k ..] (STEP_FINE_STEPS steps at most); -1 = off
+    int fine_op;
+    int n_prod;   // step2.cu: producer warps (1 or 2; B2_STEP_PRODUCERS)
 };
 
 // tokens one CTA handles per attention work item: chosen per step from the sequence length so that the
 // items fill the grid once (multiples of 32 between these bounds)
 constexpr int STEP_ATTN_MIN_CHUNK = 32, STEP_ATTN_MAX_CHUNK = 256;
-constexpr int STEP_TRACE_SLOTS = 8;   // time stamps per stage in StepProgram::trace (4 .. 7: finer marks inside a stage)
+constexpr int STEP_TRACE_SLOTS = 12;  // time stamps per stage in StepProgram::trace (4 .. 7: finer marks inside a stage, 8 .. 10: tile-loop cycles)
+constexpr int STEP_FINE_STEPS = 512;
 constexpr int STEP_MAX_GRID = 1024;   // CTAs (argmax scratch)
 constexpr size_t STEP_SYNC_BYTES = 128;
 

@@ -1,14 +1,16 @@
 // step2.cu -- the persistent per-token decode kernel, second design (SURVEY 8a rows a10-a16 in one launch).
 //
 // Same program of stages, grid barrier, attention / embedding / sampling stages and epilogues as step.cu; what changed
-// is how the weight stream reaches the arithmetic (matvec_team.cuh) and that the stream no longer stops at a hand-off:
-//   * ring allocation = one STEP: R whole weight rows of a tile (8 rows, or fewer when rows are long), copied by the
+// is how the weight stream reaches the arithmetic (matvec_team.cuh: the first design was bound by instruction issue):
+//   * tile = 8 weight rows (4 row pairs); ring allocation = one STEP = the tile's rows x 16 blocks of K, copied by the
 //     producer warp with one bulk copy per row; up to 8 steps in flight in an 81 KB byte ring;
-//   * the 8 compute warps are T teams of WPT K-slices (matvec_team.cuh); the lane's activations sit in registers for
-//     the whole stage, the 6-bit scales are unpacked in the lane: no decoder warp, one barrier per step;
-//   * the warp that used to decode headers now runs AHEAD of the producer through the same sequence of rows and asks
-//     L2 to fetch them (cp.async.bulk.prefetch.L2), a fixed number of steps ahead: while the compute warps sit in a
-//     grid barrier and the ring is full, HBM keeps streaming into L2, and the tile phase that follows is fed from L2.
+//   * compute warp w owns blocks 2w, 2w + 1 of the step for all 8 rows: Q4_K through ldmatrix + mma.sync (u8 x s8), the
+//     other types through dp4a quarters; a lane keeps one fp32 row sum over the tile's whole K loop; the 6-bit scales
+//     are unpacked in the lane: no decoder warp, one barrier per step;
+//   * the warp that used to decode headers is a second producer (measured: a look-ahead warp that asked L2 to fetch the
+//     rows some steps ahead, cp.async.bulk.prefetch.L2, bought nothing: the stream is limited by how fast copies are
+//     issued and slots released, not by DRAM latency -- tools/ubench_stream.cu reaches 7.2 TB/s with 108 KB in flight
+//     per SM, and prefetching on top of a ring that deep lowers it).
 // B2_STEP_V=1 selects the first design (step.cu) for comparison.
 #include <cstdlib>
 
@@ -24,7 +26,7 @@ using namespace teamdev;
 
 namespace {
 
-constexpr int W_PREFETCH = W_DECODER;   // the 10th warp: L2 look-ahead
+constexpr int W_PRODUCER2 = W_DECODER;   // the 10th warp: second producer
 
 struct RingPos2 {
     uint32_t off = 0, par = 0;   // par bit s: parity of the next use of slot s
@@ -42,25 +44,6 @@ struct RingPos2 {
     }
 };
 
-// per-segment geometry every role derives the same way
-struct SegGeo {
-    int bb, row_bytes, R, steps, Te, RW;
-    uint32_t pitch, step_bytes;
-};
-template <int ACT>
-__device__ __forceinline__ SegGeo seg_geo(int type, int K, const TeamGeo& g) {
-    SegGeo s;
-    s.bb = block_bytes_of(type);
-    s.row_bytes = (ACT == ACT_Q8K ? (K >> 8) : (K >> 5)) * s.bb;
-    s.pitch = ts_pitch(s.row_bytes);
-    s.R = ts_rows_per_step(s.pitch);
-    s.steps = TILE_ROWS / s.R;
-    s.Te = g.T < s.R ? g.T : s.R;
-    s.RW = s.R / s.Te;
-    s.step_bytes = (uint32_t)s.R * s.pitch;
-    return s;
-}
-
 struct TileWalk2 {
     uint8_t* ring;
     float* red;
@@ -68,63 +51,55 @@ struct TileWalk2 {
     RingPos2 rp;
     int parity, fph;
     long long cyc_ready, cyc_dot, cyc_free;   // B2_STEP_TRACE
-};
-
-// the lane's activation registers and the layout class they were loaded for (-1: stale, a new stage began)
-struct XState {
-    XR x;
-    int cls;
+    unsigned long long* fine;                 // B2_STEP_FINE: this stage's per-step stamps, or nullptr
+    int fine_k;
 };
 
 // The tiles of one segment that belong to this CTA, for a weight type known at compile time.
 template <int ACT, int TYPE>
-__device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int tile_end, int K, const TeamGeo& g, const ActView& xa, int warp,
-                                               int lane, TileWalk2& w, XState& xs, bool tracing) {
+__device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int tile_end, int nblk, const ActView& xa, int warp, int lane,
+                                               TileWalk2& w, bool tracing) {
     constexpr int CLS = XClass<TYPE>::value;
     constexpr bool unaligned = TYPE == B2_TYPE_Q6_K || TYPE == B2_TYPE_Q8_0;
-    const SegGeo sg = seg_geo<ACT>(TYPE, K, g);
-    const int team = warp / g.WPT, sl0 = warp - team * g.WPT;
-    const bool active = team < sg.Te;
-    const int b = lane >> 2, c = lane & 3;
-    const int kb0 = sl0 * 8 + b;
-    if (g.nsl == 1 && xs.cls != CLS) {
-        if (active && kb0 < g.nblk) load_x<CLS>(xs.x, xa, kb0, c);
-        xs.cls = CLS;
-    }
+    constexpr int bb = TYPE == B2_TYPE_Q4_K ? 144 : TYPE == B2_TYPE_Q5_K ? 176 : TYPE == B2_TYPE_Q6_K ? 210 : 8 * 34;
+    constexpr uint32_t pitch = MT_CHUNK * bb + 16, step_bytes = TILE_ROWS * pitch;
+    constexpr uint32_t chunk_drift = (uint32_t)(MT_CHUNK * bb) & 15;   // alignment drift of a row's data per K chunk
+    const int row_bytes = nblk * bb;
+    const int n_chunks = (nblk + MT_CHUNK - 1) / MT_CHUNK;
+    const int g = lane >> 2, t = lane & 3;
     const int step = (int)gridDim.x;
+    const MmaLane ml = mma_lane(lane);
+    const uint32_t xq_s = smem_u32(xa.q), bs32_s = smem_u32(xa.bs32), xd_s = smem_u32(xa.d);
+    // ldmatrix row address of this lane inside a step: row lane & 7, block 2 warp + ((lane >> 3) & 1), qs bytes 16 (lane >> 4) ..
+    const uint32_t lm_off = (uint32_t)((lane & 7) * pitch + (2 * warp + ((lane >> 3) & 1)) * bb + 16 + 16 * (lane >> 4));
+    const uint32_t hdr_off = (uint32_t)(g * pitch + (2 * warp + (t & 1)) * bb);
     for (; tile < tile_end; tile += step) {
-        const int ptile = tile - s.tile0;
-        // the partial-sum buffer of this parity must have been read by the epilogue warp (two tiles ago)
-        const long long c3 = tracing ? clock64() : 0;
-        mbar_wait(&w.part_free[w.parity], (w.fph >> w.parity) & 1);
-        if (tracing) w.cyc_free += clock64() - c3;
-        w.fph ^= 1 << w.parity;
-        float* red = w.red + (w.parity * NCW + warp) * TILE_ROWS;
-        for (int st = 0; st < sg.steps; st++) {
-            const uint32_t o = w.rp.place(sg.step_bytes);
+        // where the row's first byte sits inside its 16-byte-aligned ring slot (2-byte-aligned types only)
+        uint32_t off_g = 0;
+        if (unaligned) off_g = (uint32_t)((uintptr_t)slot_row_ptr(s, tile - s.tile0, g, row_bytes) & 15);
+        float acc = 0.0f;
+        for (int c = 0; c < n_chunks; c++) {
+            const uint32_t o = w.rp.place(step_bytes);
             const int sl = w.rp.slot;
             const long long c0 = tracing ? clock64() : 0;
+            const bool fine = tracing && w.fine && w.fine_k < STEP_FINE_STEPS;
+            if (fine) w.fine[8 * w.fine_k] = (unsigned long long)clock64();
             mbar_wait(&w.full[sl], w.rp.parity());
+            if (fine) w.fine[8 * w.fine_k + 1] = (unsigned long long)clock64();
             const long long c1 = tracing ? clock64() : 0;
-            float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-            if (active) {
+            const int kb0 = c * MT_CHUNK + 2 * warp;
+            if (kb0 < nblk) {
+                const uint8_t* base = w.ring + o;
+                if (TYPE == B2_TYPE_Q4_K) {
+                    acc += q4k_rows8_blocks2_mma(smem_u32(base) + lm_off, base + hdr_off, ml, xq_s, bs32_s, xd_s, kb0, min(2, nblk - kb0));
+                } else {
+                    const uint8_t* row = base + g * pitch + ((off_g + c * chunk_drift) & 15);
 #pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    if (i < sg.RW) {
-                        const int ris = team + sg.Te * i;     // row inside the step
-                        uint32_t off = 0;
-                        if (unaligned) off = (uint32_t)((uintptr_t)slot_row_ptr(s, ptile, st * sg.R + ris, sg.row_bytes) & 15);
-                        const uint8_t* row = w.ring + o + ris * sg.pitch + off;
-                        if (g.nsl == 1) {
-                            if (kb0 < g.nblk) acc[i] += row_quarter<TYPE>(row, kb0, c, xs.x);
-                        } else {
-                            for (int q = 0; q < g.nsl; q++) {
-                                const int kb = kb0 + q * NCW * 8;
-                                if (kb < g.nblk) {
-                                    load_x<CLS>(xs.x, xa, kb, c);
-                                    acc[i] += row_quarter<TYPE>(row, kb, c, xs.x);
-                                }
-                            }
+                    for (int b = 0; b < 2; b++) {
+                        if (kb0 + b < nblk) {
+                            XR x;
+                            load_x<CLS>(x, xa, kb0 + b, t);
+                            acc += row_quarter<TYPE>(row, 2 * warp + b, t, x);
                         }
                     }
                 }
@@ -132,53 +107,25 @@ __device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int 
             __syncwarp();
             if (lane == 0) mbar_arrive(&w.empty[sl]);
             w.rp.next();
-            if (active) {
-                // row sums of this warp's slice: two rows per reduction
-                if (sg.RW == 1) {
-                    const float v = warp_sum(acc[0]);
-                    if (lane == 0) red[st * sg.R + team] = v;
-                } else {
-                    const float v = warp_sum_pair(acc[0], acc[1], lane);
-                    if ((lane & 15) == 0) red[st * sg.R + team + sg.Te * (lane >> 4)] = v;
-                    if (sg.RW == 4) {
-                        const float u = warp_sum_pair(acc[2], acc[3], lane);
-                        if ((lane & 15) == 0) red[st * sg.R + team + sg.Te * (2 + (lane >> 4))] = u;
-                    }
-                }
-            }
             if (tracing) {
                 const long long c2 = clock64();
                 w.cyc_ready += c1 - c0;
-                w.cyc_dot += c2 - c1 + (__float_as_uint(acc[0]) == 0x7fc0dead ? 1 : 0);
+                w.cyc_dot += c2 - c1 + (__float_as_uint(acc) == 0x7fc0dead ? 1 : 0);
+                if (fine) w.fine[8 * w.fine_k++ + 2] = (unsigned long long)clock64();
             }
         }
+        // the four lanes of a row add up; the warp's 8 row sums go to the epilogue warp
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        const long long c3 = tracing ? clock64() : 0;
+        mbar_wait(&w.part_free[w.parity], (w.fph >> w.parity) & 1);
+        if (tracing) w.cyc_free += clock64() - c3;
+        w.fph ^= 1 << w.parity;
+        if (t == 0) w.red[(w.parity * NCW + warp) * TILE_ROWS + g] = acc;
         __syncwarp();
         if (lane == 0) mbar_arrive(&w.part_full[w.parity]);
         w.parity ^= 1;
     }
-}
-
-// epilogue warp, one tile: as gemvdev::epilogue_tile, but row r's shares come from the WPT warps of its team only
-__device__ __forceinline__ void epilogue_tile2(const GemvArgs& a, const GemvSeg& s, int ptile, int pos, const float* rp, uint64_t* part_full,
-                                               uint64_t* part_free, uint32_t full_phase, int lane, int R, int Te, int WPT) {
-    const int p = ptile * GEMV_TILE_PAIRS + (lane >> 1);
-    const bool owner = lane < TILE_ROWS && (lane & 1) == 0 && p < s.n_pairs;
-    int ra = 0, rb = -1;
-    EpiOperands o{};
-    if (owner) {
-        pair_rows(s, p, &ra, &rb);
-        o = epilogue_operands(a, s, ra, rb, pos);
-    }
-    mbar_wait(part_full, full_phase);
-    float v = 0.0f;
-    if (lane < TILE_ROWS) {
-        const int w0 = ((lane & (R - 1)) % Te) * WPT;
-        for (int w = 0; w < WPT; w++) v += rp[(w0 + w) * TILE_ROWS + lane];
-    }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(part_free);
-    const float vo = __shfl_xor_sync(0xffffffffu, v, 1);
-    if (owner) epilogue_apply(s, p, ra, rb, v, vo, o, pos);
 }
 
 constexpr size_t STEP2_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 32 * sizeof(int) + 16;
@@ -200,15 +147,13 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
     ss.cslot = (StepOp*)(ss.slots + 3);
     ss.aux = (int*)(ss.cslot + 2);
     ss.xbase = (uint8_t*)(((uintptr_t)(ss.aux + 32) + 15) & ~(uintptr_t)15);
-    // aux[28]: steps the producer has issued (read by the look-ahead warp)
-    volatile int* prod_steps = (volatile int*)&ss.aux[28];
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank(), csize = cluster_nctarank();
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < TS_NSLOT; s++) {
-            mbar_init(&full[s], 1);
+            mbar_init(&full[s], P.n_prod == 2 ? 2 : 1);   // one arrival per producer warp
             mbar_init(&empty[s], NCW);
         }
         mbar_init(&part_full[0], NCW);
@@ -219,83 +164,82 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
         ss.aux[2] = 0;   // cta_stage: the last grid-barrier stage number this CTA has seen complete
         mbar_init(sm.xbar + 1, 1);   // attention records arriving from the cluster (step_attn.cuh); aux[3] = its next phase
         ss.aux[3] = 0;
-        ss.aux[28] = 0;
         mbar_fence_init();
     }
     cluster_sync_all();
     volatile unsigned int* cta_stage = (volatile unsigned int*)&ss.aux[2];
 
-    if (warp == W_PRODUCER || warp == W_PREFETCH) {
-        // ===== producer: streams every mat-vec stage's weights in program order, never waits for a stage to start.
-        // ===== look-ahead: the same walk, P.l2_ahead steps ahead of the producer, fetching into L2 only.
-        const bool is_prod = warp == W_PRODUCER;
-        if (!is_prod && P.l2_ahead <= 0) return;
+    if (warp == W_PRODUCER || warp == W_PRODUCER2) {
+        // ===== producers: stream every mat-vec stage's weights in program order, never wait for a stage to start.
+        // Two warps, four rows of every step each: the SM's copy engine takes ~46 cycles per bulk copy, and a warp's
+        // copies are issued lane after lane.  The slot of a step is not waited for by itself: eight barrier slots
+        // cover more bytes than the ring holds, so its previous use was released before some younger allocation
+        // overwrote it (static_assert below); only the allocations the new bytes overlap are waited for.
+        static_assert(TS_NSLOT * TILE_ROWS * (MT_CHUNK * 144 + 16) > TS_RING_BYTES, "a slot's previous use must be out of the ring");
+        const int half = warp - W_PRODUCER;
+        const int rows_mine = P.n_prod == 2 ? 4 : TILE_ROWS;
+        if (half >= (P.n_prod == 2 ? 2 : 1)) return;
         RingPos2 rp;
         uint32_t my_off = 0, my_end = 0;   // lane j < TS_NSLOT: the latest allocation placed in slot j
-        int n_issued = 0;
         const uint64_t stream_policy = l2_policy_evict_first();
-        GemvArgs* slot = &ss.slots[is_prod ? 0 : 1];
+        GemvArgs* slot = &ss.slots[half];
+        const int rslot = rows_mine * half + (lane & (rows_mine - 1));   // the row slot of the tile this lane copies
         for (int oi = 0; oi < P.n_ops; oi++) {
             const StepOp& op = P.ops[oi];
             if (op.kind != OP_GEMV) continue;
             __syncwarp();
             stage_words(slot, &op.g, sizeof(GemvArgs) / 4, lane);
             const GemvArgs& a = *slot;
-            const TeamGeo g = team_geo(a.K);
-            int si = 0;
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
-                while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
-                const GemvSeg& s = a.seg[si];
-                const SegGeo sg = seg_geo<ACT>(s.type, a.K, g);
-                for (int st = 0; st < sg.steps; st++) {
-                    const uint8_t* src = nullptr;
-                    uint32_t sz = 0;
-                    if (lane < sg.R) {
-                        const uint8_t* rowp = slot_row_ptr(s, tile - s.tile0, st * sg.R + lane, sg.row_bytes);
+            const int nblk = a.K >> 8, n_seg = a.n_seg, n_tiles = a.n_tiles;
+            const int n_chunks = (nblk + MT_CHUNK - 1) / MT_CHUNK;
+            unsigned long long* fine = (half == 0 && P.trace && P.fine_op == oi && blockIdx.x == 0 && lane == 0) ? P.trace + (size_t)P.n_ops * STEP_TRACE_SLOTS : nullptr;
+            int fine_k = 0;
+            int tile = blockIdx.x;
+            for (int si = 0; si < n_seg; si++) {
+                const int tile_end = si + 1 < n_seg ? a.seg[si + 1].tile0 : n_tiles;
+                if (tile >= tile_end) continue;
+                // the segment's descriptor in registers (the barrier operations below are memory clobbers)
+                const GemvSeg s = a.seg[si];
+                const int bb = ts_block_bytes(s.type);
+                const uint32_t pitch = ts_pitch(s.type), step_bytes = TILE_ROWS * pitch;
+                const int row_bytes = nblk * bb;
+                for (; tile < tile_end; tile += gridDim.x) {
+                    const uint8_t* rowp = lane < rows_mine ? slot_row_ptr(s, tile - s.tile0, rslot, row_bytes) : nullptr;
+                    for (int c = 0; c < n_chunks; c++) {
+                        const int nb = min(MT_CHUNK, nblk - c * MT_CHUNK);
+                        const uint8_t* src = nullptr;
+                        uint32_t sz = 0;
                         if (rowp) {
-                            const uintptr_t lo = (uintptr_t)rowp, hi = lo + (size_t)sg.row_bytes;
+                            const uintptr_t lo = (uintptr_t)(rowp + (size_t)c * MT_CHUNK * bb), hi = lo + (size_t)nb * bb;
                             src = (const uint8_t*)(lo & ~(uintptr_t)15);
                             sz = (uint32_t)(((hi + 15) & ~(uintptr_t)15) - (uintptr_t)src);
                         }
-                    }
-                    if (!is_prod) {
-                        // stay at most l2_ahead steps in front of the producer
-                        if (lane == 0) {
-#pragma unroll 1
-                            for (uint32_t spin = 0; n_issued >= *prod_steps + P.l2_ahead; spin++) {
-                                __nanosleep(64);
-                                if (spin > (1u << 26)) asm volatile("trap;");
+                        if (fine && fine_k < STEP_FINE_STEPS) fine[8 * fine_k + 3] = (unsigned long long)clock64();
+                        const uint32_t o = rp.place(step_bytes);
+                        const int sl = rp.slot;
+                        if (lane < TS_NSLOT) {
+                            if (lane != sl && my_end > my_off && o < my_end && my_off < o + step_bytes) {
+                                // a younger allocation these bytes overlap: its latest use (the parity before the next) must be released
+                                mbar_wait(&empty[lane], ((rp.par >> lane) & 1u) ^ 1u);
+                                my_end = my_off;
+                            }
+                            if (lane == sl) {
+                                my_off = o;
+                                my_end = o + step_bytes;
                             }
                         }
                         __syncwarp();
-                        if (sz) bulk_prefetch_l2(src, sz);
-                        n_issued++;
-                        continue;
-                    }
-                    uint32_t total = sz;
-#pragma unroll
-                    for (int o = 4; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
-                    const uint32_t o = rp.place(sg.step_bytes);
-                    const int sl = rp.slot;
-                    const uint32_t par = rp.parity();
-                    if (lane < TS_NSLOT) {
-                        if (lane == sl) {
-                            mbar_wait(&empty[sl], par ^ 1);   // the slot's previous use is released ...
-                            my_off = o;
-                            my_end = o + sg.step_bytes;
-                        } else if (my_end > my_off && o < my_end && my_off < o + sg.step_bytes) {
-                            // ... and so is every younger allocation these bytes overlap (its latest use: the parity before the next)
-                            mbar_wait(&empty[lane], ((rp.par >> lane) & 1u) ^ 1u);
-                            my_end = my_off;
+                        if (fine && fine_k < STEP_FINE_STEPS) fine[8 * fine_k + 4] = (unsigned long long)clock64();
+                        // every copying lane announces its own bytes; the phase cannot complete before the two producers' arrivals
+                        if (sz) {
+                            mbar_expect_tx(&full[sl], sz);
+                            bulk_g2s_hint(ring + o + rslot * pitch, src, sz, &full[sl], stream_policy);
                         }
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&full[sl]);
+                        if (fine && fine_k < STEP_FINE_STEPS) fine[8 * fine_k++ + 5] = (unsigned long long)clock64();
+                        rp.next();
                     }
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive_expect_tx(&full[sl], total);
-                    __syncwarp();
-                    if (sz) bulk_g2s_hint(ring + o + lane * sg.pitch, src, sz, &full[sl], stream_policy);
-                    rp.next();
-                    n_issued++;
-                    if (lane == 0) *prod_steps = n_issued;
                 }
             }
         }
@@ -313,7 +257,6 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
             stage_words(&ss.slots[2], &op.g, sizeof(GemvArgs) / 4, lane);
             const GemvArgs& a = ss.slots[2];
             if (a.pos_ptr) pos = *a.pos_ptr;
-            const TeamGeo g = team_geo(a.K);
             // ... then never arrive for a stage before the previous one is complete everywhere: a CTA without
             // tiles in this stage would otherwise run ahead and release other CTAs early
             if (oi > 0) {
@@ -324,9 +267,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
                 while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
                 const GemvSeg& s = a.seg[si];
-                const SegGeo sg = seg_geo<ACT>(s.type, a.K, g);
-                epilogue_tile2(a, s, tile - s.tile0, pos, red + parity * NCW * TILE_ROWS, &part_full[parity], &part_free[parity],
-                               (ph >> parity) & 1, lane, sg.R, sg.Te, g.WPT);
+                epilogue_tile(a, s, tile - s.tile0, pos, red + parity * NCW * TILE_ROWS, &part_full[parity], &part_free[parity],
+                              (ph >> parity) & 1, lane);
                 ph ^= 1 << parity;
             }
             // a fence orders only the calling thread's stores: every lane that wrote results fences, then one arrives
@@ -343,8 +285,6 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
     RingPos2 rpos;
     int parity = 0, fph = 3;
     uint32_t xpar = 0;
-    XState xs;
-    xs.cls = -1;
     for (int oi = 0; oi < P.n_ops; oi++) {
         // warp 0 stages the stage's descriptor (static) while the previous stage is still finishing elsewhere;
         // the other buffer may still be read by slower warps of this CTA
@@ -375,6 +315,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
         }
         named_bar_sync(1, NCT);
         if (tid == 0) stamp(P, oi, 0);
+        if (tid == 0 && blockIdx.x == 0 && P.trace && P.fine_op == oi) P.trace[(size_t)P.n_ops * STEP_TRACE_SLOTS + 6] = (unsigned long long)clock64();
         const StepOp& op = *cs;
         if (op.kind == OP_GEMV) {
             const GemvArgs& a = op.g;
@@ -387,10 +328,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
             if (tid == 0) stamp(P, oi, 1);
             xpar ^= 1;
             const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};
-            const TeamGeo g = team_geo(K);
-            xs.cls = -1;   // new activations: the registers are stale
+            const int nblk = K >> 8;
             // this CTA's tiles, segment by segment (a segment has one weight type: the tile loop is specialised for it)
-            TileWalk2 tw{ring, red, full, empty, part_full, part_free, rpos, parity, fph, 0, 0, 0};
+            TileWalk2 tw{ring, red, full, empty, part_full, part_free, rpos, parity, fph, 0, 0, 0,
+                         (P.trace && P.fine_op == oi) ? P.trace + (size_t)P.n_ops * STEP_TRACE_SLOTS : nullptr, 0};
             const bool tracing = P.trace && blockIdx.x == 0 && tid == 0;
             int tile = blockIdx.x;
             for (int si = 0; si < a.n_seg; si++) {
@@ -398,20 +339,20 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
                 const int tile_end = si + 1 < a.n_seg ? a.seg[si + 1].tile0 : a.n_tiles;
                 if (tile >= tile_end) continue;
                 if constexpr (ACT == ACT_Q8K) {
-                    if (s.type == B2_TYPE_Q4_K) segment_tiles2<ACT, B2_TYPE_Q4_K>(s, tile, tile_end, K, g, xv, warp, lane, tw, xs, tracing);
-                    else if (s.type == B2_TYPE_Q6_K) segment_tiles2<ACT, B2_TYPE_Q6_K>(s, tile, tile_end, K, g, xv, warp, lane, tw, xs, tracing);
-                    else segment_tiles2<ACT, B2_TYPE_Q5_K>(s, tile, tile_end, K, g, xv, warp, lane, tw, xs, tracing);
+                    if (s.type == B2_TYPE_Q4_K) segment_tiles2<ACT, B2_TYPE_Q4_K>(s, tile, tile_end, nblk, xv, warp, lane, tw, tracing);
+                    else if (s.type == B2_TYPE_Q6_K) segment_tiles2<ACT, B2_TYPE_Q6_K>(s, tile, tile_end, nblk, xv, warp, lane, tw, tracing);
+                    else segment_tiles2<ACT, B2_TYPE_Q5_K>(s, tile, tile_end, nblk, xv, warp, lane, tw, tracing);
                 } else {
-                    segment_tiles2<ACT, B2_TYPE_Q8_0>(s, tile, tile_end, K, g, xv, warp, lane, tw, xs, tracing);
+                    segment_tiles2<ACT, B2_TYPE_Q8_0>(s, tile, tile_end, nblk, xv, warp, lane, tw, tracing);
                 }
             }
             rpos = tw.rp; parity = tw.parity; fph = tw.fph;
             if (tracing) {
-                // cycles warp 0 of CTA 0 spent waiting for data / in the dot products / waiting for the epilogue warp (marks 4..6)
+                // cycles warp 0 of CTA 0 spent waiting for data / in the dot products / waiting for the epilogue warp (marks 8..10)
                 unsigned long long* tr = P.trace + oi * STEP_TRACE_SLOTS;
-                tr[4] = tr[0] + (unsigned long long)(tw.cyc_ready * 1000 / 1965);
-                tr[5] = tr[0] + (unsigned long long)(tw.cyc_dot * 1000 / 1965);
-                tr[6] = tr[0] + (unsigned long long)(tw.cyc_free * 1000 / 1965);
+                tr[8] = tr[0] + (unsigned long long)(tw.cyc_ready * 1000 / 1965);
+                tr[9] = tr[0] + (unsigned long long)(tw.cyc_dot * 1000 / 1965);
+                tr[10] = tr[0] + (unsigned long long)(tw.cyc_free * 1000 / 1965);
             }
             if (tid == 0) stamp(P, oi, 2);
             // the epilogue warp arrives on the grid barrier for this stage
@@ -487,11 +428,10 @@ int step2_config(int act, int max_k, size_t* smem_out, int* cluster_out, int* gr
 
 }  // namespace
 
-// every mat-vec K of a program must be a whole number of 256-element blocks whose longest row fits one ring step
+// every mat-vec K of a program must be a whole number of 256-element blocks
 bool step2_supports(int act, int K) {
-    if (K <= 0 || (K & 255)) return false;
-    const int row_bytes = act == ACT_Q8K ? (K >> 8) * 210 : (K >> 5) * 34;   // the widest type of the format
-    return ts_pitch(row_bytes) <= TS_STEP_CAP;
+    (void)act;
+    return K > 0 && (K & 255) == 0;
 }
 
 int step2_grid_size(int act, int max_k) {
