@@ -182,11 +182,18 @@ __device__ __forceinline__ MmaLane mma_lane(int lane) {
     m.odd_t = (t & 1) != 0;
     return m;
 }
+// a lane's share of the activations of blocks kb0, kb0 + 1, ready for the eight MMAs and the finish: the B fragments
+// of accumulator sets A and B, split into "column of an even chunk" / "column of an odd chunk" (one of each pair is 0),
+// the sums of the lane's sub-blocks and the block scale.  Constant over a stage when a row has one K chunk.
+struct XMma {
+    uint32_t ea0, ea1, oa0, oa1, eb0, eb1, ob0, ob1;
+    int bs_a, bs_b;
+    float dx;
+    bool live;   // false: this lane finishes a block beyond the end of the row (its result is dropped, whatever the stale bytes give)
+};
 // xq_s / bs32_s / xd_s: shared-memory addresses of the activation vector's parts; kb0: first of the warp's two blocks
-// (block kb0 + 1 may lie beyond the row: n_valid = 1); lm: this lane's ldmatrix address for chunk 0; hdr: first byte of
-// block kb0 + (t & 1) in weight row g.  Returns this lane's share of row g's dot product.
-__device__ __forceinline__ float q4k_rows8_blocks2_mma(uint32_t lm, const uint8_t* hdr, const MmaLane& ml, uint32_t xq_s, uint32_t bs32_s, uint32_t xd_s,
-                                                       int kb0, int n_valid) {
+// (block kb0 + 1 may lie beyond the row: n_valid = 1)
+__device__ __forceinline__ void load_x_mma(XMma& x, const MmaLane& ml, uint32_t xq_s, uint32_t bs32_s, uint32_t xd_s, int kb0, int n_valid) {
     const uint32_t xb = xq_s + (uint32_t)kb0 * 256u;
     // a lane whose column belongs to the second block contributes zeros when that block does not exist
     const bool col_ok = n_valid > 1 || ml.xo[0] < 256u;
@@ -195,30 +202,40 @@ __device__ __forceinline__ float q4k_rows8_blocks2_mma(uint32_t lm, const uint8_
         xa0 = lds32(xb + ml.xo[0]); xa1 = lds32(xb + ml.xo[1]);
         xb0 = lds32(xb + ml.xo[2]); xb1 = lds32(xb + ml.xo[3]);
     }
-    const uint32_t ea0 = ml.even_chunk ? xa0 : 0u, ea1 = ml.even_chunk ? xa1 : 0u, oa0 = ml.even_chunk ? 0u : xa0, oa1 = ml.even_chunk ? 0u : xa1;
-    const uint32_t eb0 = ml.even_chunk ? xb0 : 0u, eb1 = ml.even_chunk ? xb1 : 0u, ob0 = ml.even_chunk ? 0u : xb0, ob1 = ml.even_chunk ? 0u : xb1;
+    x.ea0 = ml.even_chunk ? xa0 : 0u; x.ea1 = ml.even_chunk ? xa1 : 0u; x.oa0 = ml.even_chunk ? 0u : xa0; x.oa1 = ml.even_chunk ? 0u : xa1;
+    x.eb0 = ml.even_chunk ? xb0 : 0u; x.eb1 = ml.even_chunk ? xb1 : 0u; x.ob0 = ml.even_chunk ? 0u : xb0; x.ob1 = ml.even_chunk ? 0u : xb1;
+    const uint32_t blk = (uint32_t)kb0 + (ml.odd_t ? 1u : 0u);
+    const uint32_t sa = bs32_s + (uint32_t)kb0 * 16u + ml.so;
+    x.bs_a = (int)lds32(sa);
+    x.bs_b = (int)lds32(sa + 8);
+    x.live = n_valid > 1 || !ml.odd_t;
+    x.dx = x.live ? __uint_as_float(lds32(xd_s + blk * 4u)) : 0.0f;
+}
+// lm: this lane's ldmatrix address for chunk 0; hdr: first byte of block kb0 + (t & 1) in weight row g.
+// Returns this lane's share of row g's dot product.
+__device__ __forceinline__ float q4k_rows8_blocks2_mma(uint32_t lm, const uint8_t* hdr, const MmaLane& ml, const XMma& x) {
     int ra[4] = {0, 0, 0, 0}, ha[4] = {0, 0, 0, 0}, rb[4] = {0, 0, 0, 0}, hb[4] = {0, 0, 0, 0};
     uint32_t a[4], h[4];
     ldmatrix_x4(lm, a);
 #pragma unroll
     for (int i = 0; i < 4; i++) h[i] = a[i] & 0xF0F0F0F0u;
-    mma_u8s8(ra, a, ea0, ea1);
-    mma_u8s8(ha, h, ea0, ea1);
+    mma_u8s8(ra, a, x.ea0, x.ea1);
+    mma_u8s8(ha, h, x.ea0, x.ea1);
     ldmatrix_x4(lm + 64, a);
 #pragma unroll
     for (int i = 0; i < 4; i++) h[i] = a[i] & 0xF0F0F0F0u;
-    mma_u8s8(rb, a, eb0, eb1);
-    mma_u8s8(hb, h, eb0, eb1);
+    mma_u8s8(rb, a, x.eb0, x.eb1);
+    mma_u8s8(hb, h, x.eb0, x.eb1);
     ldmatrix_x4(lm + 32, a);
 #pragma unroll
     for (int i = 0; i < 4; i++) h[i] = a[i] & 0xF0F0F0F0u;
-    mma_u8s8(ra, a, oa0, oa1);
-    mma_u8s8(ha, h, oa0, oa1);
+    mma_u8s8(ra, a, x.oa0, x.oa1);
+    mma_u8s8(ha, h, x.oa0, x.oa1);
     ldmatrix_x4(lm + 96, a);
 #pragma unroll
     for (int i = 0; i < 4; i++) h[i] = a[i] & 0xF0F0F0F0u;
-    mma_u8s8(rb, a, ob0, ob1);
-    mma_u8s8(hb, h, ob0, ob1);
+    mma_u8s8(rb, a, x.ob0, x.ob1);
+    mma_u8s8(hb, h, x.ob0, x.ob1);
     // raw = lo + 16 hi against the low-nibble sub-block (first column), 16 hi against the high-nibble sub-block (second)
     const int lo_a = ml.odd_t ? ra[2] - ha[2] : ra[0] - ha[0], hi_a = (ml.odd_t ? ha[3] : ha[1]) >> 4;
     const int lo_b = ml.odd_t ? rb[2] - hb[2] : rb[0] - hb[0], hi_b = (ml.odd_t ? hb[3] : hb[1]) >> 4;
@@ -228,17 +245,13 @@ __device__ __forceinline__ float q4k_rows8_blocks2_mma(uint32_t lm, const uint8_
     const uint32_t y = hd.y >> sh, z = hd.z >> sh, w = hd.w >> sh;
     const uint32_t sc_a = y & 0x3f3fu, mn_a = z & 0x3f3fu;
     const uint32_t sc_b = (w & 0x0f0fu) | ((y >> 2) & 0x3030u), mn_b = ((w >> 4) & 0x0f0fu) | ((z >> 2) & 0x3030u);
-    const uint32_t blk = (uint32_t)kb0 + (ml.odd_t ? 1u : 0u);
-    const uint32_t sa = bs32_s + (uint32_t)kb0 * 16u + ml.so;
-    const int bs_a = (int)lds32(sa), bs_b = (int)lds32(sa + 8);
-    const float dx = __uint_as_float(lds32(xd_s + blk * 4u));
     // the integer part of ggml's block sum restricted to this lane's four sub-blocks
     const int isum = (int)(sc_a & 0xffu) * lo_a + (int)(sc_a >> 8) * hi_a + (int)(sc_b & 0xffu) * lo_b + (int)(sc_b >> 8) * hi_b;
-    const int msum = (int)(mn_a & 0xffu) * (int)(int16_t)((uint32_t)bs_a & 0xffffu) + (int)(mn_a >> 8) * (bs_a >> 16) +
-                     (int)(mn_b & 0xffu) * (int)(int16_t)((uint32_t)bs_b & 0xffffu) + (int)(mn_b >> 8) * (bs_b >> 16);
+    const int msum = (int)(mn_a & 0xffu) * (int)(int16_t)((uint32_t)x.bs_a & 0xffffu) + (int)(mn_a >> 8) * (x.bs_a >> 16) +
+                     (int)(mn_b & 0xffu) * (int)(int16_t)((uint32_t)x.bs_b & 0xffffu) + (int)(mn_b >> 8) * (x.bs_b >> 16);
     const float d = h2f_bits(hd.x & 0xffffu), dmin = h2f_bits(hd.x >> 16);
-    const float v = dx * (d * (float)isum - dmin * (float)msum);
-    return (n_valid > 1 || !ml.odd_t) ? v : 0.0f;
+    const float v = x.dx * (d * (float)isum - dmin * (float)msum);
+    return x.live ? v : 0.0f;
 }
 
 // sums over the warp of two values at once: lane 0 returns the total of a, lane 16 the total of b

@@ -567,7 +567,6 @@ int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
         p.trace = c->step_trace;
         p.l2_ahead = c->step_l2_ahead;
         p.fine_op = c->step_fine_op;
-        p.n_prod = c->step_n_prod;
         const int rc = c->step_version == 2 ? launch_step2(p, c->step_act, st) : launch_step(p, c->step_act, st);
         if (rc == 0) c->launches_per_step = 1;
         return rc;
@@ -594,7 +593,6 @@ int build_step_program(b2_ctx* c) {
     for (auto& op : ops)
         if (op.kind == OP_GEMV && !step2_supports(act, op.g.K)) c->step_version = 1;
     c->step_l2_ahead = 0;
-    if (const char* e = getenv("B2_STEP_PRODUCERS")) c->step_n_prod = atoi(e) == 2 ? 2 : 1;
     if (const char* e = getenv("B2_STEP_L2_AHEAD")) c->step_l2_ahead = atoi(e) < 0 ? 0 : atoi(e);
     const int grid = c->step_version == 2 ? step2_grid_size(act, max_k) : step_grid_size(act, max_k);
     if (grid < 0) return grid;

@@ -70,7 +70,7 @@ struct b2_ctx {
     bool use_step = true;
     void* d_ops = nullptr;   // StepOp[n_ops]
     int n_ops = 0, step_act = -1, step_max_k = 0;
-    int step_version = 2, step_l2_ahead = 0, step_fine_op = -1, step_n_prod = 1;   // step2.cu unless B2_STEP_V=1 or a K it does not take
+    int step_version = 2, step_l2_ahead = 0, step_fine_op = -1;   // step2.cu unless B2_STEP_V=1 or a K it does not take
     float* step_attn_partials = nullptr;
     unsigned int* step_counters = nullptr;   // [1] argmax arrivals, [8 .. 8 + n_head) attention arrivals
     unsigned int* step_sync = nullptr;       // grid barrier: arrival counter + flags (STEP_SYNC_BYTES)

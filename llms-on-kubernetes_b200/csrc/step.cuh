@@ -51,7 +51,6 @@ struct StepProgram {
     // B2_STEP_FINE=<stage index>: per ring step of that stage, CTA 0 stamps {wait begin, data there, step done, copy issued}
     // into trace[n_ops * STEP_TRACE_SLOTS + 4 k ..] (STEP_FINE_STEPS steps at most); -1 = off
     int fine_op;
-    int n_prod;   // step2.cu: producer warps (1 or 2; B2_STEP_PRODUCERS)
 };
 
 // tokens one CTA handles per attention work item: chosen per step from the sequence length so that the

@@ -26,7 +26,9 @@ using namespace teamdev;
 
 namespace {
 
-constexpr int W_PRODUCER2 = W_DECODER;   // the 10th warp: second producer
+// ten warps: 8 compute, producer, epilogue (320 threads x 2 CTAs per SM leave 96 registers per thread)
+constexpr int W_PROD = NCW, W_EPI = NCW + 1;
+constexpr int STEP2_THREADS = (NCW + 2) * 32;
 
 struct RingPos2 {
     uint32_t off = 0, par = 0;   // par bit s: parity of the next use of slot s
@@ -73,6 +75,9 @@ __device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int 
     // ldmatrix row address of this lane inside a step: row lane & 7, block 2 warp + ((lane >> 3) & 1), qs bytes 16 (lane >> 4) ..
     const uint32_t lm_off = (uint32_t)((lane & 7) * pitch + (2 * warp + ((lane >> 3) & 1)) * bb + 16 + 16 * (lane >> 4));
     const uint32_t hdr_off = (uint32_t)(g * pitch + (2 * warp + (t & 1)) * bb);
+    // a row of one K chunk: the warp's two blocks, hence its activations, are the same for every tile of the stage
+    XMma xm;
+    if (TYPE == B2_TYPE_Q4_K && n_chunks == 1 && 2 * warp < nblk) load_x_mma(xm, ml, xq_s, bs32_s, xd_s, 2 * warp, min(2, nblk - 2 * warp));
     for (; tile < tile_end; tile += step) {
         // where the row's first byte sits inside its 16-byte-aligned ring slot (2-byte-aligned types only)
         uint32_t off_g = 0;
@@ -91,7 +96,8 @@ __device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int 
             if (kb0 < nblk) {
                 const uint8_t* base = w.ring + o;
                 if (TYPE == B2_TYPE_Q4_K) {
-                    acc += q4k_rows8_blocks2_mma(smem_u32(base) + lm_off, base + hdr_off, ml, xq_s, bs32_s, xd_s, kb0, min(2, nblk - kb0));
+                    if (n_chunks > 1) load_x_mma(xm, ml, xq_s, bs32_s, xd_s, kb0, min(2, nblk - kb0));
+                    acc += q4k_rows8_blocks2_mma(smem_u32(base) + lm_off, base + hdr_off, ml, xm);
                 } else {
                     const uint8_t* row = base + g * pitch + ((off_g + c * chunk_drift) & 15);
 #pragma unroll
@@ -131,7 +137,7 @@ __device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int 
 constexpr size_t STEP2_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 32 * sizeof(int) + 16;
 
 template <int ACT>
-__global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_constant__ StepProgram P) {
+__global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_constant__ StepProgram P) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* ring = smem;
     uint64_t* full = (uint64_t*)(smem + TS_RING_BYTES);
@@ -153,7 +159,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
     if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < TS_NSLOT; s++) {
-            mbar_init(&full[s], P.n_prod == 2 ? 2 : 1);   // one arrival per producer warp
+            mbar_init(&full[s], 1);
             mbar_init(&empty[s], NCW);
         }
         mbar_init(&part_full[0], NCW);
@@ -169,16 +175,14 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
     cluster_sync_all();
     volatile unsigned int* cta_stage = (volatile unsigned int*)&ss.aux[2];
 
-    if (warp == W_PRODUCER || warp == W_PRODUCER2) {
-        // ===== producers: stream every mat-vec stage's weights in program order, never wait for a stage to start.
-        // Two warps, four rows of every step each: the SM's copy engine takes ~46 cycles per bulk copy, and a warp's
-        // copies are issued lane after lane.  The slot of a step is not waited for by itself: eight barrier slots
+    if (warp == W_PROD) {
+        // ===== producer: streams every mat-vec stage's weights in program order, never waits for a stage to start.
+        // (A second producer warp taking half of the rows was measured: no gain, and the tenth warp's registers are
+        // worth more to the compute warps.)  The slot of a step is not waited for by itself: eight barrier slots
         // cover more bytes than the ring holds, so its previous use was released before some younger allocation
         // overwrote it (static_assert below); only the allocations the new bytes overlap are waited for.
         static_assert(TS_NSLOT * TILE_ROWS * (MT_CHUNK * 144 + 16) > TS_RING_BYTES, "a slot's previous use must be out of the ring");
-        const int half = warp - W_PRODUCER;
-        const int rows_mine = P.n_prod == 2 ? 4 : TILE_ROWS;
-        if (half >= (P.n_prod == 2 ? 2 : 1)) return;
+        constexpr int half = 0, rows_mine = TILE_ROWS;
         RingPos2 rp;
         uint32_t my_off = 0, my_end = 0;   // lane j < TS_NSLOT: the latest allocation placed in slot j
         const uint64_t stream_policy = l2_policy_evict_first();
@@ -230,7 +234,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
                         }
                         __syncwarp();
                         if (fine && fine_k < STEP_FINE_STEPS) fine[8 * fine_k + 4] = (unsigned long long)clock64();
-                        // every copying lane announces its own bytes; the phase cannot complete before the two producers' arrivals
+                        // every copying lane announces its own bytes; the phase cannot complete before lane 0's arrival below
                         if (sz) {
                             mbar_expect_tx(&full[sl], sz);
                             bulk_g2s_hint(ring + o + rslot * pitch, src, sz, &full[sl], stream_policy);
@@ -246,7 +250,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) step2_kernel(const __grid_con
         return;
     }
 
-    if (warp == W_EPILOGUE) {
+    if (warp == W_EPI) {
         // ===== epilogue: finish row pairs; after the CTA's last tile of a stage, arrive on the grid barrier =====
         int parity = 0, ph = 0;
         int pos = 0;
@@ -403,7 +407,7 @@ int step2_config(int act, int max_k, size_t* smem_out, int* cluster_out, int* gr
     }
     cudaLaunchConfig_t q{};
     q.gridDim = dim3(sms * ctas_per_sm / cluster * cluster);
-    q.blockDim = dim3(GEMV_THREADS);
+    q.blockDim = dim3(STEP2_THREADS);
     q.dynamicSmemBytes = smem;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -450,7 +454,7 @@ int launch_step2(const StepProgram& p, int act, cudaStream_t st) {
     auto kern = act == ACT_Q8K ? step2_kernel<ACT_Q8K> : step2_kernel<ACT_Q80>;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(GEMV_THREADS);
+    cfg.blockDim = dim3(STEP2_THREADS);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];

@@ -22,7 +22,7 @@ using namespace b2::teamdev;
 constexpr int NSLOT = 4;
 constexpr uint32_t PITCH = 16 * 144 + 16, STEP = 8 * PITCH, ROW = 16 * 144;
 
-template <int LEVEL>
+template <int LEVEL, int PROD>
 __global__ void __launch_bounds__(352, 2) pipe(const uint8_t* w, size_t n_tiles, float* out, size_t wrap_tiles) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* ring = smem;
@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(352, 2) pipe(const uint8_t* w, size_t n_tiles,
     int16_t* bs32 = (int16_t*)(xd + 16);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
-        for (int s = 0; s < NSLOT; s++) { mbar_init(&full[s], 2); mbar_init(&empty[s], 8); }
+        for (int s = 0; s < NSLOT; s++) { mbar_init(&full[s], PROD == 0 ? 2 : 1); mbar_init(&empty[s], 8); }
         mbar_init(&part_full[0], 8); mbar_init(&part_full[1], 8);
         mbar_init(&part_free[0], 1); mbar_init(&part_free[1], 1);
         mbar_fence_init();
@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(352, 2) pipe(const uint8_t* w, size_t n_tiles,
     __syncthreads();
     if (warp == 8 || warp == 9) {
         const int half = warp - 8;
+        if (PROD != 0 && half == 1) return;
         uint64_t pol = l2_policy_evict_first();
         if (wrap_tiles < n_tiles) asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
         int s = 0;
@@ -56,10 +57,29 @@ __global__ void __launch_bounds__(352, 2) pipe(const uint8_t* w, size_t n_tiles,
             if (tw >= wrap_tiles) tw -= wrap_tiles;
             if (lane == 0) mbar_wait(&empty[s], ph ^ 1);
             __syncwarp();
-            if (lane < 4) {
-                const int r = 4 * half + lane;
-                mbar_expect_tx(&full[s], ROW);
-                bulk_g2s_hint(ring + s * STEP + r * PITCH, w + (tw * 8 + r) * (size_t)ROW, ROW, &full[s], pol);
+            if (PROD == 0) {
+                if (lane < 4) {
+                    const int r = 4 * half + lane;
+                    mbar_expect_tx(&full[s], ROW);
+                    bulk_g2s_hint(ring + s * STEP + r * PITCH, w + (tw * 8 + r) * (size_t)ROW, ROW, &full[s], pol);
+                }
+            } else if (PROD == 1) {
+                if (lane < 8) {
+                    mbar_expect_tx(&full[s], ROW);
+                    bulk_g2s_hint(ring + s * STEP + lane * PITCH, w + (tw * 8 + lane) * (size_t)ROW, ROW, &full[s], pol);
+                }
+            } else if (PROD == 2) {
+                if (lane == 0) {
+                    mbar_expect_tx(&full[s], 8 * ROW);
+#pragma unroll
+                    for (int r = 0; r < 8; r++) bulk_g2s_hint(ring + s * STEP + r * PITCH, w + (tw * 8 + r) * (size_t)ROW, ROW, &full[s], pol);
+                }
+            } else {
+                // one copy of the tile's 8 contiguous rows (no padding between the rows: ldmatrix bank conflicts)
+                if (lane == 0) {
+                    mbar_expect_tx(&full[s], 8 * ROW);
+                    bulk_g2s_hint(ring + s * STEP, w + (tw * 8) * (size_t)ROW, 8 * ROW, &full[s], pol);
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&full[s]);
@@ -112,7 +132,9 @@ __global__ void __launch_bounds__(352, 2) pipe(const uint8_t* w, size_t n_tiles,
             const uint4 hd = *(const uint4*)(base + hdr_off);
             acc = __uint_as_float((uint32_t)(ra[0] + ra[2] + ha[1] + ha[3] + hd.x + hd.y) & 0x3fffffffu);
         } else if (LEVEL >= 3) {
-            acc = q4k_rows8_blocks2_mma(smem_u32(base) + lm_off, base + hdr_off, ml, xq_s, bs32_s, xd_s, 2 * warp, 2);
+            XMma xm;
+            load_x_mma(xm, ml, xq_s, bs32_s, xd_s, 2 * warp, 2);
+            acc = q4k_rows8_blocks2_mma(smem_u32(base) + lm_off, base + hdr_off, ml, xm);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);
@@ -133,10 +155,10 @@ __global__ void __launch_bounds__(352, 2) pipe(const uint8_t* w, size_t n_tiles,
     if (LEVEL < 4 && sink == 1.2345f) out[0] = sink;
 }
 
-template <int LEVEL>
+template <int LEVEL, int PROD>
 int run(const uint8_t* buf, size_t total, float* out, int sms, size_t wrap_bytes) {
     const size_t smem = NSLOT * STEP + 12 * 8 + 2 * 64 * 4 + 4096 + 64 + 256 + 128;
-    CHECK(cudaFuncSetAttribute(pipe<LEVEL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CHECK(cudaFuncSetAttribute(pipe<LEVEL, PROD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaEvent_t e0, e1;
     CHECK(cudaEventCreate(&e0));
     CHECK(cudaEventCreate(&e1));
@@ -144,12 +166,12 @@ int run(const uint8_t* buf, size_t total, float* out, int sms, size_t wrap_bytes
     float ms = 0;
     for (int rep = 0; rep < 2; rep++) {
         CHECK(cudaEventRecord(e0));
-        pipe<LEVEL><<<sms * 2, 352, smem>>>(buf, n_tiles, out, wrap_bytes / (8 * ROW));
+        pipe<LEVEL, PROD><<<sms * 2, 352, smem>>>(buf, n_tiles, out, wrap_bytes / (8 * ROW));
         CHECK(cudaEventRecord(e1));
         CHECK(cudaEventSynchronize(e1));
         CHECK(cudaEventElapsedTime(&ms, e0, e1));
     }
-    printf("level %d, source wraps every %zu MB: %.2f TB/s\n", LEVEL, wrap_bytes >> 20, total / (ms * 1e-3) / 1e12);
+    printf("level %d, producer mode %d, source wraps every %zu MB: %.2f TB/s\n", LEVEL, PROD, wrap_bytes >> 20, total / (ms * 1e-3) / 1e12);
     return 0;
 }
 
@@ -164,11 +186,14 @@ int main() {
     int sms = 0;
     CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
     for (size_t wrap : {total, (size_t)48 << 20}) {
-        if (run<0>(buf, total, out, sms, wrap)) return 1;
-        if (run<1>(buf, total, out, sms, wrap)) return 1;
-        if (run<2>(buf, total, out, sms, wrap)) return 1;
-        if (run<3>(buf, total, out, sms, wrap)) return 1;
-        if (run<4>(buf, total, out, sms, wrap)) return 1;
+        if (run<0, 0>(buf, total, out, sms, wrap)) return 1;
+        if (run<0, 1>(buf, total, out, sms, wrap)) return 1;
+        if (run<0, 2>(buf, total, out, sms, wrap)) return 1;
+        if (run<0, 3>(buf, total, out, sms, wrap)) return 1;
+        if (run<4, 0>(buf, total, out, sms, wrap)) return 1;
+        if (run<4, 1>(buf, total, out, sms, wrap)) return 1;
+        if (run<4, 2>(buf, total, out, sms, wrap)) return 1;
+        if (run<4, 3>(buf, total, out, sms, wrap)) return 1;
     }
     return 0;
 }
