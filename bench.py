@@ -101,6 +101,64 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def load_synth_without_package():
+    """synth_gguf.py by file path: importing the package would map libb2.so into the CPU arm's process."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("b2_synth_gguf", os.path.join(ROOT, PKG, "synth_gguf.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["b2_synth_gguf"] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def host_threads() -> int:
+    """Threads the CPU arm uses: every core this process may run on (B2_REF_THREADS overrides).  torch.distributed.run
+    exports OMP_NUM_THREADS=1 to its workers, so the inherited value is not used."""
+    if os.environ.get("B2_REF_THREADS"):
+        return max(1, int(os.environ["B2_REF_THREADS"]))
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def bench_config(workload: str, world: int, tp: bool) -> dict:
+    """The `config` object of the JSON line: identical for the B200 arm and the CPU arm of the same command line."""
+    return {"workload": workload,
+            "parallelism": (f"tensor parallel x{world}: Q/K/V by heads, gate/up by rows, O/down along K, all-reduce per half-layer; "
+                            "roofline.achieved is ONE rank's weight stream") if tp
+            else f"replicas x{world}" if world > 1 else "single GPU",
+            "l2": "inputs exceed L2 (4.6 GB of weights streamed per step vs 126 MB)", "graph": True}
+
+
+def find_llama_bench():
+    """SURVEY 8c tier T4: a real llama.cpp on the box ($PATH or baseline/_ref/) is the ground-truth CPU baseline."""
+    import shutil
+    for name in ("llama-bench",):
+        p = shutil.which(name)
+        if p:
+            return p
+    base = os.path.join(ROOT, "baseline", "_ref")
+    for dirpath, _, files in os.walk(base):
+        if "llama-bench" in files:
+            return os.path.join(dirpath, "llama-bench")
+    return None
+
+
+def llama_bench_decode(exe: str, path: str, n_tokens: int, threads: int):
+    """tok/s of `llama-bench -p 0 -n n_tokens -ngl 0` on the same GGUF, or None if the run or its output is unusable."""
+    try:
+        out = subprocess.run([exe, "-m", path, "-p", "0", "-n", str(n_tokens), "-t", str(threads), "-ngl", "0", "-o", "json"],
+                             capture_output=True, text=True, timeout=240)
+        rows = json.loads(out.stdout)
+        for r in rows:
+            if int(r.get("n_gen", 0)) > 0 and float(r.get("avg_ts", 0)) > 0:
+                return float(r["avg_ts"])
+    except Exception:
+        return None
+    return None
+
+
 def ensure_model(synth, spec_name: str, seed: int, rank: int, barrier) -> str:
     d = os.environ.get("B2_BENCH_DIR", "/tmp")
     path = os.path.join(d, f"b2_synth_{spec_name}_s{seed}.gguf")
@@ -115,6 +173,7 @@ def ensure_model(synth, spec_name: str, seed: int, rank: int, barrier) -> str:
 def cpu_decode_sample(path: str, n_tokens: int, warm: int):
     """Oracle port (oracle/ggml_ref.c, all host threads): decode n_tokens from an empty KV cache."""
     from oracle import ref_model as rm
+    rm.lib().ref_set_num_threads(host_threads())
     ref = rm.RefGGUFModel(path, n_ctx=max(64, n_tokens + warm + 1))
     tok, pos = 1, 0
     for _ in range(warm):
@@ -125,6 +184,30 @@ def cpu_decode_sample(path: str, n_tokens: int, warm: int):
     dt = time.perf_counter() - t0
     ref.close()
     return n_tokens / dt, dt, rm.lib().ref_num_threads()
+
+
+def parity_check(b2, model, path: str, seed: int, n_prompt: int = 16, n_new: int = 8) -> dict:
+    """Outside the timed region: the timed path (one persistent-kernel launch per token, through b2_ctx_decode) against the
+    oracle on a short prompt of the benchmarked model -- logits after the prompt and the greedy ids that follow."""
+    from oracle import parity as par
+    from oracle import ref_model as rm
+    rm.lib().ref_set_num_threads(host_threads())
+    rng = np.random.default_rng(seed + 1000)
+    prompt = rng.integers(3, model.info.vocab, size=n_prompt).tolist()
+    ref = rm.RefGGUFModel(path, n_ctx=n_prompt + n_new + 8)
+    want_ids, want_logits = par.oracle_greedy_trace(ref, prompt, n_new)
+    floor = par.sensitivity_floor(ref, rm.lib(), prompt, want_ids, want_logits)   # the oracle against itself, one ulp apart
+    ref.close()
+    ctx = b2.Context(model, max(64, n_prompt + n_new + 8))
+    tok, logits = None, None
+    for pos, t in enumerate(prompt):          # token by token: every position runs the decode kernel that is timed below
+        tok, logits = ctx.decode([t], pos, want_logits=(pos == n_prompt - 1))
+    got = [tok] + (ctx.generate_greedy(n_new - 1) if n_new > 1 else [])
+    ctx.free()
+    res = par.compare_greedy(want_ids, want_logits, got, logits, floor)
+    res.update({"prompt_tokens": n_prompt, "new_tokens": n_new, "oracle": "oracle/ggml_ref.c",
+                "tolerance": "max(3 % of the logit range, 3 x the oracle's own drift under a one-ulp perturbation); KL: max(1e-3, 5 x)"})
+    return res
 
 
 def bench_batched(b2, synth, spec, model, args, world, barrier, max_over_ranks, gpu_index):
@@ -194,9 +277,11 @@ def bench_batched(b2, synth, spec, model, args, world, barrier, max_over_ranks, 
     value = world * B * args.steps / dt
     step_bytes = info.stream_bytes + B * (args.prompt + args.warmup + args.steps // 2) * synth.kv_bytes_per_token(spec)
     gbs = step_bytes * args.steps / dt / 1e9
+    tc = B >= 24   # from 24 columns b2_ctx_decode_batch takes the tensor-core pass when the fp16 copy is resident (tc_min_rows)
     return {"metric": f"decode tok/s at batch {B}", "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int8 x int4..6 mma.sync (u8.s8 -> s32), fp32 scales", "data": "synthetic",
+            "dtype": "fp16 x fp16 tcgen05.mma, fp32 accumulate (weights dequantised to fp16 tiles, activations quantised as the reference does)" if tc
+                     else "int8 x int4..6 mma.sync (u8.s8 -> s32), fp32 scales", "data": "synthetic",
             "config": {"workload": f"{spec.name} {spec.ftype} synthetic GGUF, batch-{B} greedy decode at ctx {args.prompt}",
                        "parallelism": f"replicas x{world}" if world > 1 else "single GPU",
                        "l2": "inputs exceed L2 (4.6 GB of weights streamed per step vs 126 MB)"},
@@ -216,6 +301,7 @@ def main():
     ap.add_argument("--prompt", type=int, default=128, help="tokens in the KV cache when the timed decode starts")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of the timed path (16-token prompt, 8 greedy ids) before timing")
     ap.add_argument("--dist-selftest", action="store_true", help="CPU-only check of the multi-rank aggregation (gloo)")
     ap.add_argument("--batch", type=int, default=1, help="> 1: batched decode of this many sequences (SURVEY 8d config 3: 8, 32)")
     ap.add_argument("--prefill", type=int, default=0, help="> 0: time the prefill of a prompt of this many tokens instead")
@@ -227,7 +313,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    synth = importlib.import_module(PKG + ".synth_gguf")
+    # the CPU arm must not map the product library: synth_gguf.py is loaded by path there
+    synth = load_synth_without_package() if args.impl == "reference" else importlib.import_module(PKG + ".synth_gguf")
     spec = synth.SPECS[args.model]
     workload = f"{spec.name} {spec.ftype} synthetic GGUF, batch-1 greedy decode at ctx {args.prompt}"
 
@@ -235,23 +322,35 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
+        os.environ["OMP_NUM_THREADS"] = str(host_threads())   # before the OpenMP runtime starts (the oracle library loads lazily)
         path = ensure_model(synth, args.model, args.seed, 0, lambda: None)
+        tp = (args.tp or "70b" in args.model) and world > 1
         # bounded: one CPU token of the 8B model is ~0.1-1 s; cap the run near two minutes
         tps1, dt1, cores = cpu_decode_sample(path, 1, 1)
         budget = 120.0
         steps = max(1, min(args.steps, int(budget / max(dt1, 1e-3)) - args.warmup))
         warm = min(args.warmup, max(1, int(10.0 / max(dt1, 1e-3))))
         tps, dt, cores = cpu_decode_sample(path, steps, warm)
+        kind = "port"
         sample = (f"{steps} decode steps from an empty KV cache after {warm} warm-up steps (KV read is <1% of step bytes), "
-                  f"oracle/ggml_ref.c restatement of the ggml CPU path, OpenMP {cores} threads")
-        print(json.dumps({
+                  f"oracle/ggml_ref.c restatement of the ggml CPU path (llama.cpp itself is not on this machine), OpenMP {cores} threads")
+        exe = find_llama_bench()
+        if exe:
+            real = llama_bench_decode(exe, path, min(steps, 64), host_threads())
+            if real:
+                tps, kind = real, "llama.cpp"
+                sample = f"{exe} -p 0 -n {min(steps, 64)} -t {host_threads()} -ngl 0 on the same GGUF"
+        line = {
             "impl": "reference", "metric": METRIC, "value": tps, "unit": "tok/s", "n_gpus": args.gpus, "steps": steps,
-            "warmup": warm, "ms_per_step": 1000.0 / tps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": warm, "ms_per_step": 1000.0 / tps, "higher_is_better": True, "scaling": "strong" if tp else "weak", "vs_baseline": None,
             "dtype": "int8 x int4..8 dot, fp32 accumulate", "data": "synthetic",
-            "config": {"workload": workload, "note": "llama.cpp itself is not available offline: CPU restatement (llama.cpp-equivalent algorithm)"},
-            "cpu_baseline": {"value": tps, "unit": "tok/s", "cores": cores, "kind": "port", "sample": sample},
+            "config": bench_config(workload, world, tp),
+            "cpu_baseline": {"value": tps, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": tps, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        }))
+        }
+        if cores <= 1 and host_threads() > 1:
+            line["note"] = "the OpenMP team is one thread although more cores are available: do not form a ratio from this line"
+        print(json.dumps(line))
         return
 
     # ------------------------------------------------------------------ B200 arm
@@ -266,7 +365,10 @@ def main():
             red_device = "cpu"
             dist.init_process_group("gloo")
         else:
-            os.environ["NCCL_DEBUG"] = "WARN"   # NCCL's version banner goes to stdout; rank 0 prints exactly one line
+            # NCCL's log (communicator ranks, transports) goes to stderr: stdout carries exactly one JSON line
+            os.environ.setdefault("NCCL_DEBUG", "INFO")
+            os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
             torch.cuda.set_device(local_rank)
             dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -295,7 +397,7 @@ def main():
 
     b2 = importlib.import_module(PKG)  # raises if libb2.so is missing: no fallback
     path = ensure_model(synth, args.model, args.seed, rank, barrier)
-    tp = args.tp and world > 1
+    tp = (args.tp or "70b" in args.model) and world > 1   # BASELINE config 5: the 70B model is tensor parallel over the ranks
     model = b2.Model(path, device=local_rank, tp_rank=rank if tp else 0, tp_size=world if tp else 1)
     jobs = 1 if tp else world          # sequences decoded at once over the whole job
     if tp and (args.batch > 1 or args.prefill > 0):
@@ -308,6 +410,11 @@ def main():
         if dist is not None:
             dist.destroy_process_group()
         return
+    parity = None
+    if rank == 0 and world == 1 and not args.no_parity:
+        parity = parity_check(b2, model, path, args.seed)
+        if not parity["ok"]:
+            raise SystemExit("bench.py: the decode path does not match the oracle: " + json.dumps(parity))
     n_ctx = max(512, args.prompt + 2 * (args.steps + args.warmup) + 64)
     ctx = b2.Context(model, n_ctx)
     if tp:
@@ -373,15 +480,12 @@ def main():
         "metric": METRIC if not tp else f"decode tok/s, {spec.name} {spec.ftype} tensor-parallel", "value": value, "unit": "tok/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong" if tp else "weak", "vs_baseline": None,
-        "dtype": "int8 x int4..8 dot (dp4a), fp32 accumulate", "data": "synthetic",
-        "config": {"workload": workload,
-                   "parallelism": (f"tensor parallel x{world}: Q/K/V by heads, gate/up by rows, O/down along K, NCCL all-reduce per half-layer; "
-                                   "roofline.achieved is ONE rank's weight stream") if tp
-                   else f"replicas x{world}" if world > 1 else "single GPU",
-                   "l2": "inputs exceed L2 (4.6 GB of weights streamed per step vs 126 MB)", "graph": True},
+        "dtype": "int8 x int4..8 dot (mma.sync u8.s8 / dp4a -> s32), fp32 accumulate", "data": "synthetic",
+        "config": bench_config(workload, world, tp),
         "e2e": {"value": e2e, "unit": "tok/s", "h2d_bytes_per_step": 8, "d2h_bytes_per_step": 4},
         "gpu_launches": ctx.launches_per_step * args.steps,
         "clocks": clocks, "roofline": roofline,
+        "parity_checked": bool(parity and parity["ok"]), "parity": parity,
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:

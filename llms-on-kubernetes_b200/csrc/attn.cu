@@ -400,7 +400,6 @@ constexpr size_t STATIC_PART_BYTES = ((size_t)STATIC_MAX_HEADS * STATIC_MAX_SPLI
 constexpr size_t STATIC_SCRATCH_BYTES = STATIC_PART_BYTES + 256;   // + arrival counters (one per kv head)
 static __device__ __align__(256) unsigned char g_attn_static_scratch[STATIC_SCRATCH_BYTES];
 
-constexpr int MAX_DEVICES = 64;
 void* g_static_ptr[MAX_DEVICES];   // device address of the array, per device, filled on first use
 std::mutex g_static_mu;
 }  // namespace

@@ -3,6 +3,7 @@
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
+#include <mutex>
 #include <string>
 
 #include "../../include/b2.h"
@@ -26,6 +27,27 @@ inline int64_t row_bytes(int type, int64_t k) {
     if (!t || k % t->block_elems) return -1;
     return k / t->block_elems * t->block_bytes;
 }
+
+// One process may drive several GPUs (b2_model_load takes a device ordinal), and what is set up once -- a kernel's
+// opt-in dynamic shared-memory size (cudaFuncSetAttribute), the SM count -- is per DEVICE: this keeps the largest
+// value configured so far for each device ordinal.
+constexpr int MAX_DEVICES = 64;
+struct PerDeviceSize {
+    std::mutex mu;
+    size_t v[MAX_DEVICES] = {};
+    // true if device `dev` is not yet configured for `want` (an ordinal outside the table is configured every time)
+    bool below(int dev, size_t want) {
+        std::lock_guard<std::mutex> l(mu);
+        return dev < 0 || dev >= MAX_DEVICES || v[dev] < want;
+    }
+    void set(int dev, size_t want) {
+        std::lock_guard<std::mutex> l(mu);
+        if (dev >= 0 && dev < MAX_DEVICES && v[dev] < want) v[dev] = want;
+    }
+};
+// SMs of the current device (looked up once per device); 0 and the error slot set on failure
+int device_sm_count();
+int current_device();   // ordinal of the current device, -1 on failure
 
 }  // namespace b2
 

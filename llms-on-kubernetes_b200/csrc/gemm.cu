@@ -742,17 +742,18 @@ size_t gemm_smem_bytes() {
            (3 * G::STAGES + 4) * sizeof(uint64_t);
 }
 
-int g_gemm_sms = 0;
-
 template <int NG, int FMT>
 int launch_gemm_ng(const GemmArgs& a, cudaStream_t st) {
-    static bool configured = false;
+    static PerDeviceSize configured;   // the opt-in shared-memory size is a per-device attribute of the kernel
     const size_t smem = gemm_smem_bytes<NG, FMT>();
-    if (!configured) {
+    const int dev = current_device();
+    if (configured.below(dev, smem)) {
         B2_CUDA_CHECK(cudaFuncSetAttribute(gemm_kernel<NG, FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        configured.set(dev, smem);
     }
-    const int ctas = g_gemm_sms * (NG == 1 ? 2 : 1);
+    const int sms = device_sm_count();
+    if (sms <= 0) return B2_ECUDA;
+    const int ctas = sms * (NG == 1 ? 2 : 1);
     const int grid = a.n_tiles < ctas ? a.n_tiles : ctas;
     gemm_kernel<NG, FMT><<<grid, Geo<NG, FMT>::THREADS, smem, st>>>(a);
     B2_CUDA_CHECK(cudaGetLastError());
@@ -832,11 +833,6 @@ int launch_act_quant(const float* x, int64_t x_stride, const float* norm_w, floa
 }
 
 int launch_gemm(const GemmArgs& a, cudaStream_t st) {
-    if (!g_gemm_sms) {
-        int dev = 0;
-        B2_CUDA_CHECK(cudaGetDevice(&dev));
-        B2_CUDA_CHECK(cudaDeviceGetAttribute(&g_gemm_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
     const int nb = gemm_nb(a.cols.n);
     if (a.act_fmt == ACT_Q80) {
         if (nb == 8) return launch_gemm_ng<1, ACT_Q80>(a, st);

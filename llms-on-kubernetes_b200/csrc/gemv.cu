@@ -264,24 +264,21 @@ int gemv_finalize(GemvArgs& a, int act) {
     return 0;
 }
 
-static int g_num_sms = 0;
 
 int launch_gemv(const GemvArgs& a, int act, cudaStream_t st, bool pdl) {
-    if (!g_num_sms) {
-        int dev = 0;
-        B2_CUDA_CHECK(cudaGetDevice(&dev));
-        B2_CUDA_CHECK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    const int g_num_sms = device_sm_count();
+    if (g_num_sms <= 0) return B2_ECUDA;
+    const int dev = current_device();
     const size_t smem = gemv_smem_bytes(act, a.K);
     if (smem > 227 * 1024) {
         set_error("gemv: K=%d needs %zu bytes of shared memory (limit 227 KiB)", a.K, smem);
         return B2_ERANGE;
     }
     auto kern = act == ACT_Q8K ? gemv_kernel<ACT_Q8K> : gemv_kernel<ACT_Q80>;
-    static size_t configured[2] = {0, 0};
-    if (smem > configured[act]) {
+    static PerDeviceSize configured[2];   // per activation format and device
+    if (configured[act].below(dev, smem)) {
         B2_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured[act] = smem;
+        configured[act].set(dev, smem);
     }
     int ctas_per_sm = (int)((227 * 1024) / (smem + 1024));
     if (ctas_per_sm > 2) ctas_per_sm = 2;
@@ -315,6 +312,7 @@ int launch_gemv(const GemvArgs& a, int act, cudaStream_t st, bool pdl) {
     int max_clusters = want / cluster;
     if (cluster > 1) {
         // cached per (activation format, cluster size, shared-memory size)
+        // (every GPU of a box is the same part: the cache is not keyed by device, the attribute above is)
         static int cached[2][9] = {};
         static size_t cached_smem[2][9] = {};
         if (!cached[act][cluster] || cached_smem[act][cluster] != smem) {

@@ -177,3 +177,32 @@ int launch_rope(float* x, int n_heads, int head_dim, int n_dims, int mode, int p
 }
 
 }  // namespace b2
+
+namespace b2 {
+
+int current_device() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+    return dev;
+}
+
+int device_sm_count() {
+    static std::mutex mu;
+    static int sms[MAX_DEVICES] = {};
+    const int dev = current_device();
+    if (dev < 0) {
+        set_error("no current CUDA device");
+        return 0;
+    }
+    std::lock_guard<std::mutex> l(mu);
+    if (dev < MAX_DEVICES && sms[dev] > 0) return sms[dev];
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
+        set_error("cannot read the SM count of device %d", dev);
+        return 0;
+    }
+    if (dev < MAX_DEVICES) sms[dev] = n;
+    return n;
+}
+
+}  // namespace b2

@@ -776,6 +776,21 @@ int kv_map(b2_ctx* c, int slot, int p0, int p1) {
     return 0;
 }
 
+// Attention walks pages 0 .. pos / KV_PAGE of a slot: on an on-demand pool every one of them must have been mapped by
+// an earlier pass (the server fills positions contiguously; a direct caller that jumps to position p of an empty slot
+// would make the kernels address page -1, in front of the pool).
+int kv_check_prefix(const b2_ctx* c, int slot, int p0) {
+    if (!c->kv_dynamic || slot == 0) return 0;
+    const int32_t* row = c->kv_table.data() + (size_t)slot * c->pages_per_seq;
+    for (int i = 0; i < p0 / KV_PAGE; i++)
+        if (row[i] < 0) {
+            set_error("slot %d: position %d needs positions %d..%d in the KV cache, but that page was never written (paged KV pool: "
+                      "fill a sequence from position 0 upwards)", slot, p0, i * KV_PAGE, (i + 1) * KV_PAGE - 1);
+            return B2_ERANGE;
+        }
+    return 0;
+}
+
 // the device copy of the table follows the host's before the next pass is enqueued (stream order)
 int kv_sync_table(b2_ctx* c) {
     if (!c->kv_table_dirty) return 0;
@@ -961,8 +976,10 @@ int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int3
         set_error("b2_ctx_decode_batch: %d columns need the tensor-core pass with a resident fp16 copy of the model (b2_ctx_max_batch)", n);
         return B2_EUNSUP;
     }
-    for (int j = 0; j < n; j++)
+    for (int j = 0; j < n; j++) {
+        if ((rc = kv_check_prefix(c, slots ? slots[j] : 0, pos[j]))) return rc;
         if ((rc = kv_map(c, slots ? slots[j] : 0, pos[j], pos[j]))) return rc;
+    }
     if ((rc = kv_sync_table(c))) return rc;
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // staging buffer reuse
     for (int j = 0; j < n; j++) {
@@ -1266,6 +1283,7 @@ int prefill_tc(b2_ctx* c, int slot, const int32_t* tokens, int n, int pos0, bool
     if ((rc = ensure_batch(c))) return rc;
     if ((rc = ensure_prefill(c))) return rc;
     const b2_model_info& I = c->m->info;
+    if ((rc = kv_check_prefix(c, slot, pos0))) return rc;
     if ((rc = kv_map(c, slot, pos0, pos0 + n - 1))) return rc;
     if ((rc = kv_sync_table(c))) return rc;
     for (int done = 0; done < n;) {
@@ -1357,8 +1375,10 @@ extern "C" int b2_ctx_prefill_multi(b2_ctx* c, int n_seq, const int32_t* slots, 
             set_error("b2_ctx_prefill_multi: token %d at row %d is outside the vocabulary (%d)", tokens[r], r, I.vocab);
             return B2_ERANGE;
         }
-    for (const PromptSeg& sg : segs)
+    for (const PromptSeg& sg : segs) {
+        if ((rc = kv_check_prefix(c, sg.slot, sg.pos0))) return rc;
         if ((rc = kv_map(c, sg.slot, sg.pos0, sg.pos0 + sg.T - 1))) return rc;
+    }
     if ((rc = kv_sync_table(c))) return rc;
     std::vector<int32_t> rpos(rows), rslot(rows);
     for (const PromptSeg& sg : segs)

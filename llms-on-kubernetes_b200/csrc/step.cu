@@ -403,14 +403,9 @@ size_t step_smem_bytes(int act, int max_k) {
     return (n + 127) & ~(size_t)127;
 }
 
-int g_step_sms = 0;
-
 int step_config(int act, int max_k, size_t* smem_out, int* cluster_out, int* grid_out) {
-    if (!g_step_sms) {
-        int dev = 0;
-        B2_CUDA_CHECK(cudaGetDevice(&dev));
-        B2_CUDA_CHECK(cudaDeviceGetAttribute(&g_step_sms, cudaDevAttrMultiProcessorCount, dev));
-    }
+    const int g_step_sms = device_sm_count();
+    if (g_step_sms <= 0) return B2_ECUDA;
     const size_t smem = step_smem_bytes(act, max_k);
     if (smem > 227 * 1024) {
         set_error("step kernel: K=%d needs %zu bytes of shared memory", max_k, smem);

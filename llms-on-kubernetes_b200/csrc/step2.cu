@@ -387,9 +387,8 @@ size_t step2_smem_bytes(int act, int max_k) {
 }
 
 int step2_config(int act, int max_k, size_t* smem_out, int* cluster_out, int* grid_out) {
-    int dev = 0, sms = 0;
-    B2_CUDA_CHECK(cudaGetDevice(&dev));
-    B2_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int sms = device_sm_count();
+    if (sms <= 0) return B2_ECUDA;
     const size_t smem = step2_smem_bytes(act, max_k);
     if (smem > 227 * 1024) {
         set_error("step kernel: K=%d needs %zu bytes of shared memory", max_k, smem);

@@ -502,12 +502,8 @@ int encode_f16_rows(CUtensorMap* map, const void* base, int64_t rows, int64_t K,
 }
 
 int sm_count() {
-    static int n = 0;
-    if (!n) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-    }
-    return n;
+    const int n = device_sm_count();   // per device
+    return n > 0 ? n : 148;
 }
 
 template <int BN>
@@ -517,10 +513,11 @@ int launch_tc(const TcGemmArgs& a, cudaStream_t st) {
     int rc;
     if ((rc = encode_f16_rows(&mw, a.w, a.N, a.K, TC_BM))) return rc;
     if ((rc = encode_f16_rows(&mx, a.x, a.T, a.K, BN))) return rc;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static PerDeviceSize attr_set;   // per device: a second GPU in the same process needs its own opt-in
+    const int dev = current_device();
+    if (attr_set.below(dev, G::SMEM)) {
         B2_CUDA_CHECK(cudaFuncSetAttribute(tc_gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::SMEM));
-        attr_set = true;
+        attr_set.set(dev, G::SMEM);
     }
     const int tiles = ((a.N + TC_BM - 1) / TC_BM) * ((a.T + BN - 1) / BN) * (a.splits > 1 ? a.splits : 1);
     const int grid = tiles < sm_count() ? tiles : sm_count();

@@ -568,6 +568,23 @@ static void ref_attention(ref_ctx* c, int il, int pos) {
 
 /* One token through the decoder (llama.cpp build_llama / build_qwen2 graph for n_tokens = 1).
  * logits_out may be NULL.  Returns the greedy token (argmax of logits, lowest index on ties). */
+/* Sensitivity probe (tests only): with eps > 0 every residual-stream update and every SwiGLU output is multiplied by
+ * (1 + eps * r), r uniform in [-0.5, 0.5) from a hash -- the size of change a different but equally valid fp32
+ * summation order makes.  Comparing a perturbed run with the plain one measures how far two CORRECT implementations of
+ * this model can drift apart (int8 re-quantisation of activations turns a last-bit change into a rounding flip that
+ * the following layers amplify); the parity tests state their tolerance relative to that measured floor. */
+static float g_perturb_eps = 0.0f;
+static uint32_t g_perturb_seed = 0;
+void ref_set_perturb(float eps, uint32_t seed) { g_perturb_eps = eps; g_perturb_seed = seed; }
+static void perturb(float* v, int n, uint32_t salt) {
+    if (g_perturb_eps <= 0.0f) return;
+    for (int i = 0; i < n; i++) {
+        uint32_t h = ((uint32_t)i * 2654435761u) ^ (salt * 40503u) ^ g_perturb_seed;
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        v[i] *= 1.0f + g_perturb_eps * ((float)(h & 0xffff) / 65536.0f - 0.5f);
+    }
+}
+
 int32_t ref_decode(ref_ctx* c, int32_t token, int32_t pos, float* logits_out) {
     const ref_model* m = c->m;
     const int d = m->d_model, hd = m->head_dim;
@@ -594,10 +611,12 @@ int32_t ref_decode(ref_ctx* c, int32_t token, int32_t pos, float* logits_out) {
         ref_attention(c, il, pos);
         ref_gemv(L->wo.type, L->wo.data, c->attn_out, c->proj, d, qd);
         for (int i = 0; i < d; i++) c->x[i] += c->proj[i];
+        perturb(c->x, d, 4u * (uint32_t)il + 1u);
         ref_rmsnorm(c->x, (const float*)L->ffn_norm.data, c->xn, d, m->eps);
         ref_gemv(L->w_gate.type, L->w_gate.data, c->xn, c->gate, m->d_ff, d);
         ref_gemv(L->w_up.type, L->w_up.data, c->xn, c->up, m->d_ff, d);
         for (int i = 0; i < m->d_ff; i++) c->h[i] = silu_f(c->gate[i]) * c->up[i];
+        perturb(c->h, m->d_ff, 4u * (uint32_t)il + 2u);
         ref_gemv(L->w_down.type, L->w_down.data, c->h, c->proj, d, m->d_ff);
         for (int i = 0; i < d; i++) c->x[i] += c->proj[i];
     }
@@ -643,5 +662,14 @@ int ref_num_threads(void) {
     return omp_get_max_threads();
 #else
     return 1;
+#endif
+}
+
+/* bench.py's CPU arm under torch.distributed.run inherits OMP_NUM_THREADS=1: it sets the team size itself */
+void ref_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
 #endif
 }

@@ -69,6 +69,8 @@ def lib() -> C.CDLL:
         L.ref_row_bytes.argtypes = [C.c_int, C.c_int64]
         L.ref_row_bytes.restype = C.c_int64
         L.ref_num_threads.restype = C.c_int
+        L.ref_set_num_threads.argtypes = [C.c_int]
+        L.ref_set_perturb.argtypes = [C.c_float, C.c_uint32]
     return _LIB
 
 

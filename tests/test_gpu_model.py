@@ -38,38 +38,28 @@ KL_TOL = 1e-3
 
 
 @pytest.mark.parametrize("name", MODELS)
-def test_logits_and_greedy_match_oracle(b2, tiny_models, name):
+def test_logits_and_greedy_match_oracle(b2, tiny_models, name, capsys):
+    """Logits after the prompt within the stated tolerance; greedy ids IDENTICAL to the oracle's up to the first step
+    where the oracle's own top-1 / top-2 margin is inside that tolerance (reported per prompt: index and margin) --
+    there both candidates are legitimate argmaxes and the sequences legitimately part ways (oracle/parity.py)."""
+    from oracle import parity as par
     path = tiny_models[name]
     ref = rm.RefGGUFModel(path, n_ctx=512)
     m = b2.Model(path)
     ctx = b2.Context(m, 512)
     rng = np.random.default_rng(11)
-    agree, total = 0, 0
+    report = []
     for trial in range(3):
         prompt = rng.integers(3, m.info.vocab, size=[5, 33, 128][trial]).tolist()
         n_new = 32
         got_ids, got_logits = ctx.greedy(prompt, n_new)
-        # oracle: prompt, then follow its own greedy path recording the top-1/top-2 margin at every step
-        pos = 0
-        for t in prompt:
-            tok, lg = ref.decode(t, pos); pos += 1
-        want_logits = lg
-        scale = np.abs(want_logits).max()
-        assert np.abs(got_logits - want_logits).max() <= LOGIT_TOL * scale
-        assert kl(want_logits, got_logits) < KL_TOL
-        for i in range(n_new):
-            top2 = np.partition(lg, -2)[-2:]
-            margin = float(top2.max() - top2.min())
-            total += 1
-            if got_ids[i] != tok:
-                # a divergence is only legitimate where the oracle's own decision is inside the tolerance
-                assert margin <= 2 * LOGIT_TOL * np.abs(lg).max(), \
-                    f"{name}: greedy diverged at generated token {i} although the oracle margin is {margin:.3e}"
-                break
-            agree += 1
-            tok, lg = ref.decode(tok, pos); pos += 1
-    # most of the compared tokens must be identical (divergences only at near-ties)
-    assert agree >= 0.5 * total, (agree, total)
+        want_ids, want_logits = par.oracle_greedy_trace(ref, prompt, n_new)
+        res = par.compare_greedy(want_ids, want_logits, got_ids, got_logits)
+        report.append((len(prompt), res["first_divergence"], res["margin_at_divergence"], res["logits_err_over_range"], res["kl"]))
+        assert res["logits_err_over_range"] <= LOGIT_TOL and res["kl"] < KL_TOL, (name, trial, res)
+        assert res["ok"], f"{name}: prompt of {len(prompt)}: greedy ids differ from the oracle's at a step that is not a near-tie: {res}"
+    with capsys.disabled():
+        print(f"\n  {name}: (prompt tokens, first divergence, oracle margin there, logit err / range, KL) = {report}")
     ctx.free(); m.free(); ref.close()
 
 
