@@ -90,6 +90,12 @@ __device__ __forceinline__ void dsmem_st_async_v2(uint32_t addr, uint32_t a, uin
     asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(addr), "r"(a), "r"(b), "r"(mbar)
                  : "memory");
 }
+// the same store under a predicate (no branch around it: the activation exchange issues sixteen per lane)
+__device__ __forceinline__ void dsmem_st_async_b32_if(bool p, uint32_t addr, uint32_t v, uint32_t mbar) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %3, 0;\n\t@q st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];\n\t}" ::"r"(addr), "r"(v),
+                 "r"(mbar), "r"((uint32_t)p)
+                 : "memory");
+}
 __device__ __forceinline__ void fence_cluster() { asm volatile("fence.acq_rel.cluster;" ::: "memory"); }
 // arrive on an mbarrier that lives in another CTA of the cluster, releasing this thread's prior writes
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
@@ -167,6 +173,15 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
+}
+
+// Time stamps of the in-kernel traces: the SM's cycle counter scaled to ns at the boost clock (1965 MHz).  All marks of
+// a trace come from one CTA, hence one SM, so they are comparable -- and unlike %globaltimer (updated every ~32 ns, and
+// slow to read: a handful of reads per stage visibly stretched the traced CTA's stages) the read costs a few cycles.
+__device__ __forceinline__ unsigned long long trace_ns() { return (unsigned long long)clock64() * 1000ull / 1965ull; }
+__device__ __forceinline__ unsigned long long trace_after(uint32_t dep) {
+    if (dep == 0x7fc0dead) asm volatile("trap;");
+    return trace_ns();
 }
 
 // same, but not before `dep` has been computed (to time the arrival of loaded data)

@@ -315,17 +315,20 @@ __device__ __forceinline__ void quantise_span(const float (&v)[8], int base, int
         const uint32_t o_16 = (uint32_t)((const uint8_t*)(sm.bs16 + (i0 >> 4)) - smem_base);
         const uint32_t o_32 = (uint32_t)((const uint8_t*)(sm.bs32 + (i0 >> 5)) - smem_base);
         const uint32_t o_bar = (uint32_t)((const uint8_t*)sm.xbar - smem_base);
-        // every byte is reported to the receiving CTA's barrier (activation_bytes() of them complete its phase)
+        // every byte is reported to the receiving CTA's barrier (activation_bytes() of them complete its phase);
+        // straight-line, predicated stores: this runs on the critical path of every stage hand-off
+        const bool q4 = (lane & 3) == 0, q8 = (lane & 7) == 0, q32 = lane == 0;
+#pragma unroll 4
         for (uint32_t r = 0; r < csize; r++) {
             const uint32_t pb = dsmem_addr(smem_base, r);
             const uint32_t bar = pb + o_bar;
             dsmem_st_async_v2(pb + o_q, pk0, pk1, bar);
             if (ACT == ACT_Q8K) {
-                if ((lane & 3) == 0) dsmem_st_async_b32(pb + o_16, p16, bar);
-                if ((lane & 7) == 0) dsmem_st_async_b32(pb + o_32, p32, bar);
-                if (lane == 0) dsmem_st_async_b32(pb + o_d, __float_as_uint(d), bar);
+                dsmem_st_async_b32_if(q4, pb + o_16, p16, bar);
+                dsmem_st_async_b32_if(q8, pb + o_32, p32, bar);
+                dsmem_st_async_b32_if(q32, pb + o_d, __float_as_uint(d), bar);
             } else {
-                if ((lane & 3) == 0) dsmem_st_async_b32(pb + o_d, __float_as_uint(d), bar);
+                dsmem_st_async_b32_if(q4, pb + o_d, __float_as_uint(d), bar);
             }
         }
     }
@@ -340,7 +343,7 @@ __device__ __forceinline__ uint32_t activation_bytes(int K) {
 // parity: phase of xbar to wait for (0 for a kernel that builds one activation vector).
 // Called by all NCT compute threads (uses named barrier 1).
 template <int ACT>
-__device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uint8_t* smem_base, int tid, uint32_t rank, uint32_t csize,
+__device__ __forceinline__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uint8_t* smem_base, int tid, uint32_t rank, uint32_t csize,
                                  uint32_t parity = 0, unsigned long long* tr = nullptr) {
     const int K = a.K;
     const int lane = tid & 31, warp = tid >> 5;
@@ -374,8 +377,8 @@ __device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uin
         const float mean = (float)(tot / (double)K);
         scale = 1.0f / sqrtf(mean + a.eps);
         if (tr && tid == 0) {
-            tr[4] = globaltimer_after(__float_as_uint(v0[0]));
-            tr[5] = globaltimer_after(__float_as_uint(scale));
+            tr[4] = trace_after(__float_as_uint(v0[0]));
+            tr[5] = trace_after(__float_as_uint(scale));
         }
     }
     if (a.prologue == PRO_NORM) {
@@ -397,7 +400,7 @@ __device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uin
         // issue the loads of two spans before the first use
         if (first < nspans) load8(a.x, (first << 8) + lane * 8, K, v0);
         if (first + stride < nspans) load8(a.x, ((first + stride) << 8) + lane * 8, K, v1);
-        if (tr && tid == 0) tr[4] = globaltimer_after(__float_as_uint(v0[0]));
+        if (tr && tid == 0) tr[4] = trace_after(__float_as_uint(v0[0]));
         if (first < nspans) quantise_span<ACT>(v0, first << 8, lane, K, sm, smem_base, csize);
         if (first + stride < nspans) quantise_span<ACT>(v1, (first + stride) << 8, lane, K, sm, smem_base, csize);
         for (int s = first + 2 * stride; s < nspans; s += stride) {
@@ -406,11 +409,11 @@ __device__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uin
             quantise_span<ACT>(t, s << 8, lane, K, sm, smem_base, csize);
         }
     }
-    if (tr && tid == 0) tr[6] = globaltimer_ns();
+    if (tr && tid == 0) tr[6] = trace_ns();
     // the barrier's phase completes when this CTA's copy is whole: one local arrival that announces the byte count
     // (stores of faster peers may already have been counted: the transaction count is signed)
     if (tid == 0) mbar_arrive_expect_tx(sm.xbar, activation_bytes<ACT>(K));
-    if (tr && tid == 0) tr[7] = globaltimer_ns();
+    if (tr && tid == 0) tr[7] = trace_ns();
     mbar_wait(sm.xbar, parity);
 }
 

@@ -28,7 +28,7 @@ namespace teamdev {
 using namespace gemvdev;
 
 constexpr int TS_NSLOT = 8;                                            // ring allocations in flight (barrier pairs)
-constexpr uint32_t TS_RING_BYTES = 3 * TILE_ROWS * (16 * 210 + 16);   // 81 024 B: three Q6_K steps
+constexpr uint32_t TS_RING_BYTES = 5 * TILE_ROWS * (16 * 144 + 16);   // 92 800 B: five Q4_K steps, three Q6_K steps (two CTAs per SM with the K = 14336 activations)
 constexpr int MT_CHUNK = 16;      // 256-element blocks of K per ring step: two per compute warp
 
 // bytes of one 256-element block / of one row's share of a ring step (16 blocks + 16 bytes of alignment slack).

@@ -624,7 +624,7 @@ int build_step_program(b2_ctx* c) {
         const size_t words = ops.size() * STEP_TRACE_SLOTS + 8 * STEP_FINE_STEPS;
         B2_CUDA_CHECK(cudaMalloc((void**)&c->step_trace, words * sizeof(unsigned long long)));
         B2_CUDA_CHECK(cudaMemset(c->step_trace, 0, words * sizeof(unsigned long long)));
-        if (const char* e = getenv("B2_STEP_FINE")) c->step_fine_op = atoi(e);
+        if (const char* e = getenv("B2_STEP_FINE")) c->step_fine_op = atoi(e);   // -2: the compute warps skip the arithmetic (wrong results)
         for (auto& op : ops) {
             c->step_desc.push_back(op.kind);
             c->step_desc.push_back(op.kind == OP_GEMV ? op.g.K : 0);
@@ -672,6 +672,18 @@ void dump_step_trace(b2_ctx* c) {
     if (c->step_fine_op >= 0 && c->step_fine_op < c->n_ops) {
         std::vector<unsigned long long> f(8 * STEP_FINE_STEPS);
         if (cudaMemcpy(f.data(), c->step_trace + (size_t)c->n_ops * S, f.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return;
+        {
+            // arrival of every CTA on the traced stage's barrier and the moment it saw the barrier complete
+            unsigned long long first = ~0ull, last = 0, pfirst = ~0ull, plast = 0;
+            int n = 0;
+            for (int b = 0; b < 1024 && f[1024 + b]; b++, n++) {
+                first = std::min(first, f[1024 + b]); last = std::max(last, f[1024 + b]);
+                if (f[2048 + b]) { pfirst = std::min(pfirst, f[2048 + b]); plast = std::max(plast, f[2048 + b]); }
+            }
+            if (n)
+                fprintf(stderr, "b2 step trace, stage %d barrier: %d CTAs arrive over %lld ns (CTA 0 at +%lld); the barrier is seen complete %lld .. %lld ns after the last arrival\n",
+                        c->step_fine_op, n, (long long)(last - first), (long long)(f[1024] - first), (long long)(pfirst - last), (long long)(plast - last));
+        }
         const long long t0 = (long long)f[6];   // SM clock when CTA 0's compute warps passed the stage's barrier
         fprintf(stderr, "b2 step trace, stage %d, ring steps of CTA 0 (SM cycles after the stage began): producer at step, slot free, copies issued | wait begin  data there  step done\n", c->step_fine_op);
         for (int k = 0; k < STEP_FINE_STEPS && f[8 * k + 2]; k++)

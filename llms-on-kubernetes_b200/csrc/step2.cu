@@ -55,6 +55,7 @@ struct TileWalk2 {
     long long cyc_ready, cyc_dot, cyc_free;   // B2_STEP_TRACE
     unsigned long long* fine;                 // B2_STEP_FINE: this stage's per-step stamps, or nullptr
     int fine_k;
+    bool skip_math;                           // B2_STEP_FINE=-2: release every step unread (how fast can the producer alone go?)
 };
 
 // The tiles of one segment that belong to this CTA, for a weight type known at compile time.
@@ -93,7 +94,7 @@ __device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int 
             if (fine) w.fine[8 * w.fine_k + 1] = (unsigned long long)clock64();
             const long long c1 = tracing ? clock64() : 0;
             const int kb0 = c * MT_CHUNK + 2 * warp;
-            if (kb0 < nblk) {
+            if (kb0 < nblk && !w.skip_math) {
                 const uint8_t* base = w.ring + o;
                 if (TYPE == B2_TYPE_Q4_K) {
                     if (n_chunks > 1) load_x_mma(xm, ml, xq_s, bs32_s, xd_s, kb0, min(2, nblk - kb0));
@@ -279,6 +280,7 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
             __threadfence();
             __syncwarp();
             if (lane == 0) {
+                if (P.trace && P.fine_op == oi) P.trace[(size_t)P.n_ops * STEP_TRACE_SLOTS + 1024 + blockIdx.x] = globaltimer_ns();
                 grid_arrive(P.sync_counter, (unsigned int)oi + 1u);
                 stamp(P, oi, 3);
             }
@@ -319,6 +321,7 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
         }
         named_bar_sync(1, NCT);
         if (tid == 0) stamp(P, oi, 0);
+        if (tid == 0 && P.trace && P.fine_op >= 0 && P.fine_op + 1 == oi) P.trace[(size_t)P.n_ops * STEP_TRACE_SLOTS + 2048 + blockIdx.x] = globaltimer_ns();
         if (tid == 0 && blockIdx.x == 0 && P.trace && P.fine_op == oi) P.trace[(size_t)P.n_ops * STEP_TRACE_SLOTS + 6] = (unsigned long long)clock64();
         const StepOp& op = *cs;
         if (op.kind == OP_GEMV) {
@@ -335,7 +338,7 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
             const int nblk = K >> 8;
             // this CTA's tiles, segment by segment (a segment has one weight type: the tile loop is specialised for it)
             TileWalk2 tw{ring, red, full, empty, part_full, part_free, rpos, parity, fph, 0, 0, 0,
-                         (P.trace && P.fine_op == oi) ? P.trace + (size_t)P.n_ops * STEP_TRACE_SLOTS : nullptr, 0};
+                         (P.trace && P.fine_op == oi) ? P.trace + (size_t)P.n_ops * STEP_TRACE_SLOTS : nullptr, 0, P.fine_op == -2};
             const bool tracing = P.trace && blockIdx.x == 0 && tid == 0;
             int tile = blockIdx.x;
             for (int si = 0; si < a.n_seg; si++) {

@@ -77,7 +77,7 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
     const int tk = lane >> 2, c = lane & 3;
     const int vcol = (HD / 4) * c + 2 * TPWV * warp;   // first dim of this lane's V words / outputs
 
-    if (tr && tid == 0) tr[4] = globaltimer_ns();
+    if (tr && tid == 0) tr[4] = trace_ns();
     uint32_t vpre[V_PRE_KS][2][TPWV];
 
     // ---- scores on the tensor cores: S[head][token] = q[head] . k[token] ----
@@ -102,7 +102,7 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
 #pragma unroll
             for (int j = 0; j < NMMA; j++) qa[j][0] = qa[j][1] = 0u;
         }
-        if (tr && tid == 0) tr[5] = globaltimer_after(qa[0][0]);   // q arrived
+        if (tr && tid == 0) tr[5] = trace_after(qa[0][0]);   // q arrived
         // the V words of the first 32 tokens are requested once q is here, so that they travel while the scores are
         // computed without standing between the score phase and its own operands
 #pragma unroll
@@ -119,7 +119,7 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
                 const uint4 v = t < n ? *(const uint4*)(kbase + (size_t)t * HD + DPT * c + 8 * i) : make_uint4(0, 0, 0, 0);
                 kw[4 * i] = v.x; kw[4 * i + 1] = v.y; kw[4 * i + 2] = v.z; kw[4 * i + 3] = v.w;
             }
-            if (tr && tid == 0 && tg == 0) tr[6] = globaltimer_after(kw[0]);   // first K rows arrived
+            if (tr && tid == 0 && tg == 0) tr[6] = trace_after(kw[0]);   // first K rows arrived
             float s4[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
             for (int j = 0; j < NMMA; j++)
@@ -134,9 +134,9 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
             }
         }
     }
-    if (tr && tid == 0) tr[7] = globaltimer_ns();   // this warp's scores done
+    if (tr && tid == 0) tr[7] = trace_ns();   // this warp's scores done
     named_bar_sync(1, NCT);
-    if (tr && tid == 0) tr[1] = globaltimer_ns();
+    if (tr && tid == 0) tr[1] = trace_ns();
 
     // ---- softmax: warps 2h and 2h+1 own head h (both compute the same max and sum) ----
     const bool exact = n_chunks == 1;
@@ -249,7 +249,7 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
         }
         named_bar_sync(1, NCT);
         if (chunk == 0 && tid == 0) *sm.apar ^= 1;   // the barrier's next phase
-        if (tr && tid == 0) tr[2] = globaltimer_ns();
+        if (tr && tid == 0) tr[2] = trace_ns();
         return;
     }
     if (tk < g) {
@@ -265,13 +265,13 @@ __device__ void attn_item(const StepOp& op, int kvh, int h0, int g, int chunk, i
     }
     if (exact) {
         named_bar_sync(1, NCT);   // the next item reuses the shared buffers
-        if (tr && tid == 0) tr[2] = globaltimer_ns();
+        if (tr && tid == 0) tr[2] = trace_ns();
         return;
     }
     // the last chunk of the (kv head, batch) to arrive merges the records by log-sum-exp
     __threadfence();
     named_bar_sync(1, NCT);
-    if (tr && tid == 0) tr[2] = globaltimer_ns();
+    if (tr && tid == 0) tr[2] = trace_ns();
     if (tid == 0) {
         // one arrival counter per (kv head, head batch): at most n_head of them
         unsigned int* ctr = &op.a_counters[kvh * ((gq + A_MAXG - 1) / A_MAXG) + h0 / A_MAXG];

@@ -61,7 +61,7 @@ __device__ __forceinline__ void grid_wait_local(volatile unsigned int* cta_stage
 }
 // profiling stamp of CTA 0 (no-op unless the program carries a trace buffer)
 __device__ __forceinline__ void stamp(const StepProgram& P, int oi, int slot) {
-    if (P.trace && blockIdx.x == 0) P.trace[oi * STEP_TRACE_SLOTS + slot] = globaltimer_ns();
+    if (P.trace && blockIdx.x == 0) P.trace[oi * STEP_TRACE_SLOTS + slot] = trace_ns();
 }
 
 // copy `words` 32-bit words of static program data from global into shared memory with one warp
