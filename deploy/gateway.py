@@ -39,6 +39,22 @@ def load_backends():
     return table
 
 
+def pick_backend(backends, default, body):
+    """The reference's routing rule (api-gateway.yaml:67-77; the nginx gateway's Lua block, model-gateway.yaml:53-75, is
+    the same rule): the backend named by the JSON body's `model`, else the default; a body that is not a JSON object, or
+    whose `model` is not a known name, stays on the default."""
+    if body:
+        try:
+            doc = json.loads(body.decode())
+        except (ValueError, UnicodeDecodeError):
+            return default
+        if isinstance(doc, dict):
+            name = doc.get("model")
+            if isinstance(name, str) and name in backends:
+                return backends[name]
+    return default
+
+
 def make_handler(backends):
     names = list(backends)
     default = backends[names[0]]
@@ -72,14 +88,7 @@ def make_handler(backends):
         def forward(self):
             n = int(self.headers.get("Content-Length") or 0)
             body = self.rfile.read(n) if n > 0 else b""
-            target = default
-            if body:
-                try:
-                    doc = json.loads(body.decode())
-                    if isinstance(doc, dict) and doc.get("model") in backends:
-                        target = backends[doc["model"]]
-                except (ValueError, UnicodeDecodeError):
-                    pass
+            target = pick_backend(backends, default, body)
             u = urllib.parse.urlsplit(target)
             headers = {k: v for k, v in self.headers.items() if k.lower() not in HOP_BY_HOP}
             if body:

@@ -24,6 +24,19 @@ import urllib.error
 import urllib.request
 
 
+def pick_backend(backends: dict[str, str], default: str, body: bytes) -> str:
+    """api-gateway.yaml:67-77: the backend of the JSON body's `model`, else the default; any parse error keeps the default."""
+    target = default
+    if body:
+        try:
+            wanted = json.loads(body.decode()).get("model", "")
+            if wanted in backends:
+                target = backends[wanted]
+        except Exception:
+            pass
+    return target
+
+
 def make_gateway(backends: dict[str, str], port: int = 0):
     """backends: ordered {modelName: base_url}.  Returns (server, port); call serve_forever in a thread."""
     names = list(backends)
@@ -52,14 +65,7 @@ def make_gateway(backends: dict[str, str], port: int = 0):
         def _forward(self):
             n = int(self.headers.get("Content-Length", 0))
             body = self.rfile.read(n) if n > 0 else b""
-            target = default
-            if body:
-                try:
-                    wanted = json.loads(body.decode()).get("model", "")
-                    if wanted in backends:
-                        target = backends[wanted]
-                except Exception:
-                    pass
+            target = pick_backend(backends, default, body)
             req = urllib.request.Request(target.rstrip("/") + self.path, data=body if body else None)
             for k, v in self.headers.items():
                 if k.lower() not in ("host", "connection"):
@@ -88,3 +94,38 @@ def start(backends: dict[str, str]):
     t = threading.Thread(target=srv.serve_forever, daemon=True)
     t.start()
     return srv, port
+
+
+# ---- the vLLM chart's nginx gateway (vllm-models/helm-chart/templates/model-gateway.yaml:51-82), restated ----
+# nginx / OpenResty / Lua are not on this machine, so the routing block is restated as a table-driven function and
+# checked against the template's text in tests/test_gateway_nginx_table.py.
+def nginx_upstream_for(models: list[str], body: bytes | None) -> str:
+    """access_by_lua_block, model-gateway.yaml:53-75: the upstream a request goes to.  `default_backend` is the first
+    model's server (:20-22); a body that is absent, not JSON, not an object, without `model`, or naming an unknown
+    model stays on it (cjson.decode under pcall: errors leave the default)."""
+    import json
+    upstream = "default_backend"
+    if body:
+        try:
+            data = json.loads(body)
+        except Exception:
+            return upstream
+        # Lua: `json_data and json_data.model` -- indexing a non-table raises inside the block only for non-indexable
+        # values; cjson arrays are tables without a `model` key.  Only an object with a truthy `model` matches.
+        if isinstance(data, dict) and data.get("model"):
+            name = data["model"]
+            for m in models:                      # one `if model_name == "<m>"` per model, in values order (:66-70)
+                if name == m:
+                    upstream = "vllm-" + m
+    return upstream
+
+
+def nginx_backend_host(models: list[str], upstream: str) -> str:
+    """upstream blocks, model-gateway.yaml:14-22: every upstream is one server `vllm-<model>:8080`."""
+    if upstream == "default_backend":
+        return f"vllm-{models[0]}:8080"
+    assert upstream.startswith("vllm-") and upstream[5:] in models
+    return f"{upstream}:8080"
+
+
+NGINX_FORWARDED_HEADERS = ("Host", "X-Real-IP", "X-Forwarded-For", "X-Forwarded-Proto")   # proxy_set_header, :78-81
