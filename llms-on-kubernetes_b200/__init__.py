@@ -16,7 +16,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb2.so")
-SERVER_PATH = os.path.join(_HERE, "bin", "llama-server")
+SERVER_PATH = os.environ.get("B2_SERVER_BIN") or os.path.join(_HERE, "bin", "llama-server")   # B2_SERVER_BIN: an instrumented build (bin/llama-server-tsan)
 
 F32, F16, Q8_0, Q4_K, Q5_K, Q6_K, BF16 = 0, 1, 8, 12, 13, 14, 30
 
