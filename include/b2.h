@@ -182,6 +182,21 @@ int b2_attn_decode_static(const float* q_dev, const void* k_cache_dev, const voi
 size_t b2_argmax_scratch_bytes(int64_t n);
 int b2_sample_greedy(const float* logits_dev, int64_t n, int32_t* token_out_dev, void* scratch_dev, void* stream);
 
+/* Sampling parameters as llama-server applies them (row a16; the server's defaults when a request omits them are
+ * temperature 0.8, top_k 40, top_p 0.95, min_p 0.05).  temperature <= 0 or top_k == 1 is greedy. */
+typedef struct b2_sampling {
+    float temperature, top_p, min_p;
+    int32_t top_k;     /* <= 0: no top-k limit of its own (the sampler considers the B2_SAMPLE_MAX_K most probable tokens) */
+    uint64_t seed;     /* one Philox4x32-10 draw per (seed, draw index): the same pair always picks the same token */
+} b2_sampling;
+#define B2_SAMPLE_MAX_K 1024
+/* Device-side sampling of n_rows logits rows (row r at logits_dev + r * row_stride floats; row_stride 0 = the same row
+ * for every draw): top-k -> softmax with temperature -> min-p -> top-p -> one draw, in llama-server's order.  Row r
+ * uses params_dev[r * param_stride] (param_stride 0 = one parameter set for all rows) and draw index draw_dev[r]
+ * (NULL: r).  Replaces the host sampler of the reference's llama-server: the logits never leave the GPU. */
+int b2_sample(const float* logits_dev, int n_rows, int64_t vocab, int64_t row_stride, const b2_sampling* params_dev,
+              int64_t param_stride, const uint64_t* draw_dev, int32_t* tokens_out_dev, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Model + decode context  (rows a8-a16 end to end; replaces llama_model_load / llama_decode inside
  * the llama-server the chart launches)
@@ -224,6 +239,12 @@ int b2_ctx_reset(b2_ctx* c);
  * vocab-sized fp32 logits after the LAST token.  If next_token_out != NULL it receives the greedy
  * continuation.  Host buffers; the H2D / D2H copies are part of the call. */
 int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, float* logits_out_host, int32_t* next_token_out);
+
+/* Sampling for sequence slot `slot` (p == NULL or a greedy parameter set: back to greedy).  While set, every call that
+ * returns a "next token" for that slot -- b2_ctx_decode, b2_ctx_generate_greedy (slot 0), b2_ctx_decode_batch,
+ * b2_ctx_prefill, b2_ctx_prefill_multi -- returns a token drawn on the device with these parameters; the draw index is
+ * the position the new token will take, so a (seed, prompt) pair reproduces its continuation. */
+int b2_ctx_set_sampler(b2_ctx* c, int slot, const b2_sampling* p);
 
 /* A context with n_slots independent sequences (KV caches of n_ctx tokens each); b2_ctx_create = 1 slot.
  * The single-sequence calls above use slot 0. */

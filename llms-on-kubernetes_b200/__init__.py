@@ -32,6 +32,11 @@ class TensorInfo(C.Structure):
                 ("offset", C.c_uint64), ("n_bytes", C.c_uint64)]
 
 
+class Sampling(C.Structure):
+    """b2_sampling: llama-server's sampling parameters (temperature <= 0 or top_k == 1: greedy)."""
+    _fields_ = [("temperature", C.c_float), ("top_p", C.c_float), ("min_p", C.c_float), ("top_k", C.c_int32), ("seed", C.c_uint64)]
+
+
 class ModelInfo(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("arch", "n_layer", "d_model", "d_ff", "n_head", "n_kv", "head_dim", "vocab",
                                           "n_ctx_train", "rope_dim")] + \
@@ -88,6 +93,8 @@ SYMBOLS = {
     "b2_attn_decode_static": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "b2_argmax_scratch_bytes": (_SZ, [_I64]),
     "b2_sample_greedy": (_I, [_P, _I64, _P, _P, _P]),
+    "b2_sample": (_I, [_P, _I, _I64, _I64, _P, _I64, _P, _P, _P]),
+    "b2_ctx_set_sampler": (_I, [_P, _I, _P]),
     "b2_model_load": (_I, [C.c_char_p, _I, _I, _I, C.POINTER(_P)]),
     "b2_allreduce_unique_id": (_I, [_P, _SZ]),
     "b2_allreduce_init": (_I, [_P, _P, _SZ]),
@@ -141,6 +148,18 @@ def check(rc: int) -> int:
     if rc < 0:
         raise B2Error(rc, (lib.b2_last_error() or b"").decode(errors="replace"))
     return rc
+
+
+def sample(logits: np.ndarray, n_draws: int, temperature=0.8, top_k=40, top_p=0.95, min_p=0.05, seed=0, first_draw=0) -> np.ndarray:
+    """n_draws tokens drawn on the device from ONE logits row (b2_sample with row_stride 0): draw indices first_draw .. ."""
+    lg = DevBuf.from_numpy(np.ascontiguousarray(logits, np.float32))
+    par = np.frombuffer(bytes(Sampling(temperature, top_p, min_p, top_k, seed)), np.uint8)
+    dpar = DevBuf.from_numpy(par)
+    ddraw = DevBuf.from_numpy(np.arange(first_draw, first_draw + n_draws, dtype=np.uint64))
+    out = DevBuf(4 * n_draws, zero=True)
+    check(lib.b2_sample(lg.ptr, n_draws, logits.size, 0, dpar.ptr, 0, ddraw.ptr, out.ptr, None))
+    check(lib.b2_stream_sync(None))
+    return out.to_numpy(np.int32)
 
 
 def device_count() -> int:
@@ -435,6 +454,15 @@ class Context:
         out = np.empty(n, np.int32)
         check(lib.b2_ctx_generate_greedy(self.h, n, out.ctypes.data))
         return out.tolist()
+
+    def set_sampler(self, slot: int = 0, temperature: float = 0.8, top_k: int = 40, top_p: float = 0.95, min_p: float = 0.05, seed: int = 0,
+                    greedy: bool = False):
+        """Device-side sampling for a sequence slot (llama-server's defaults); greedy=True switches it off."""
+        if greedy:
+            check(lib.b2_ctx_set_sampler(self.h, slot, None))
+        else:
+            s = Sampling(temperature, top_p, min_p, top_k, seed)
+            check(lib.b2_ctx_set_sampler(self.h, slot, C.byref(s)))
 
     def greedy(self, prompt, n_new: int):
         """Same contract as oracle.ref_model.RefGGUFModel.greedy."""

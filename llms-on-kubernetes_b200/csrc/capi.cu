@@ -305,4 +305,13 @@ int b2_sample_greedy(const float* logits_dev, int64_t n, int32_t* token_out_dev,
     return launch_argmax(logits_dev, n, token_out_dev, scratch_dev, nullptr, nullptr, nullptr, 0, (cudaStream_t)stream, false);
 }
 
+int b2_sample(const float* logits_dev, int n_rows, int64_t vocab, int64_t row_stride, const b2_sampling* params_dev, int64_t param_stride,
+              const uint64_t* draw_dev, int32_t* tokens_out_dev, void* stream) {
+    if (row_stride < 0 || param_stride < 0 || (row_stride != 0 && row_stride < vocab)) {
+        set_error("b2_sample: row_stride=%lld param_stride=%lld (row_stride is 0 or at least vocab)", (long long)row_stride, (long long)param_stride);
+        return B2_EINVAL;
+    }
+    return launch_sample_rows(logits_dev, vocab, row_stride, n_rows, params_dev, param_stride, draw_dev, tokens_out_dev, false, (cudaStream_t)stream);
+}
+
 }  // extern "C"

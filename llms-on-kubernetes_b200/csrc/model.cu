@@ -556,6 +556,37 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
     return 0;
 }
 
+bool slot_samples(const b2_ctx* c, int slot) {
+    return c->n_samplers > 0 && slot >= 0 && slot < (int)c->samplers.size() && c->samplers[slot].temperature > 0.0f && c->samplers[slot].top_k != 1;
+}
+
+// Slot 0 samples: replace the greedy token the step just left in d_tok (and, inside the device-resident loop, in the
+// output list) by a draw from the step's logits.  The draw index is the position the new token will take (d_pos after
+// the step).  after_step: the step advanced d_step, so the list entry to overwrite is d_out[*d_step - 1].
+int sample_single(b2_ctx* c, cudaStream_t st, bool after_step) {
+    if (!slot_samples(c, 0)) return 0;
+    return launch_sample_rows(c->logits, c->m->info.vocab, 0, 1, c->d_samplers, 0, nullptr, c->d_tok, true, st, c->d_pos,
+                              after_step ? c->d_out : nullptr, after_step ? c->d_step : nullptr, c->out_cap);
+}
+
+// The columns of a batched pass whose sequence slots sample: one draw per logits row, on the device.  Row r of
+// bt.logits belongs to column col0 + r of the pass (slot / position from the host arrays of the call).
+int sample_columns(b2_ctx* c, const int32_t* slots, const int32_t* pos, int col0, int n_rows) {
+    if (c->n_samplers == 0) return 0;
+    bool any = false;
+    for (int r = 0; r < n_rows; r++) any = any || slot_samples(c, slots ? slots[col0 + r] : 0);
+    if (!any) return 0;
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // pinned staging reuse
+    for (int r = 0; r < n_rows; r++) {
+        const int s = slots ? slots[col0 + r] : 0;
+        c->h_col_params[r] = slot_samples(c, s) ? c->samplers[s] : b2_sampling{0.0f, 1.0f, 0.0f, 1, 0};
+        c->h_col_draw[r] = (uint64_t)(pos[col0 + r] + 1);
+    }
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->d_col_params, c->h_col_params, (size_t)n_rows * sizeof(b2_sampling), cudaMemcpyHostToDevice, c->stream));
+    B2_CUDA_CHECK(cudaMemcpyAsync(c->d_col_draw, c->h_col_draw, (size_t)n_rows * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream));
+    return launch_sample_rows(c->bt.logits, c->m->info.vocab, c->m->info.vocab, n_rows, c->d_col_params, 1, c->d_col_draw, c->bt.out, true, c->stream);
+}
+
 // one decode step on the stream: the persistent kernel when a program was built, else one launch per stage
 int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
     if (c->use_step && c->d_ops) {
@@ -567,11 +598,13 @@ int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
         p.trace = c->step_trace;
         p.l2_ahead = c->step_l2_ahead;
         p.fine_op = c->step_fine_op;
-        const int rc = c->step_version == 2 ? launch_step2(p, c->step_act, st) : launch_step(p, c->step_act, st);
+        int rc = c->step_version == 2 ? launch_step2(p, c->step_act, st) : launch_step(p, c->step_act, st);
         if (rc == 0) c->launches_per_step = 1;
+        if (rc == 0) rc = sample_single(c, st, true);
         return rc;
     }
-    return enqueue_step(c, st, pdl);
+    const int rc = enqueue_step(c, st, pdl);
+    return rc ? rc : sample_single(c, st, true);
 }
 
 // record the stages of a step as the persistent kernel's program and upload it
@@ -1416,6 +1449,11 @@ extern "C" int b2_ctx_prefill_multi(b2_ctx* c, int n_seq, const int32_t* slots, 
             rc = B2_EUNSUP;
         }
         if (rc) return rc;
+        {
+            std::vector<int32_t> ls(n_seq), lp(n_seq);
+            for (int i = 0; i < n_seq; i++) { ls[i] = segs[i].slot; lp[i] = segs[i].pos0 + segs[i].T - 1; }
+            if ((rc = sample_columns(c, ls.data(), lp.data(), 0, n_seq))) return rc;
+        }
         if (logits_out_host)
             B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->bt.logits, (size_t)n_seq * I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
         if (next_tokens_out) B2_CUDA_CHECK(cudaMemcpyAsync(c->h_pin, c->bt.out, (size_t)n_seq * 4, cudaMemcpyDeviceToHost, c->stream));
@@ -1474,6 +1512,10 @@ extern "C" int b2_ctx_prefill(b2_ctx* c, int slot, const int32_t* tokens, int n,
     int rc;
     const bool want = next_token_out || logits_out_host;
     if ((rc = prefill_tc(c, slot, tokens, n, pos0, want))) return rc;
+    if (want) {
+        const int32_t s1 = slot, p1 = pos0 + n - 1;
+        if ((rc = sample_columns(c, &s1, &p1, 0, 1))) return rc;
+    }
     if (logits_out_host) B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->bt.logits, (size_t)I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
     if (next_token_out) B2_CUDA_CHECK(cudaMemcpyAsync(c->h_pin, c->bt.out, 4, cudaMemcpyDeviceToHost, c->stream));
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
@@ -1482,6 +1524,43 @@ extern "C" int b2_ctx_prefill(b2_ctx* c, int slot, const int32_t* tokens, int n,
 }
 
 extern "C" int b2_ctx_n_slots(const b2_ctx* c) { return c ? c->n_slots : B2_EINVAL; }
+
+extern "C" int b2_ctx_set_sampler(b2_ctx* c, int slot, const b2_sampling* p) {
+    if (!c || slot < 0 || slot >= c->n_slots) {
+        set_error("b2_ctx_set_sampler: slot %d out of range", slot);
+        return B2_EINVAL;
+    }
+    b2_sampling s = p ? *p : b2_sampling{0.0f, 1.0f, 0.0f, 1, 0};
+    if (p && (!(s.top_p > 0.0f) || s.top_p > 1.0f || s.min_p < 0.0f || s.min_p > 1.0f || s.temperature != s.temperature)) {
+        set_error("b2_ctx_set_sampler: top_p %g must be in (0, 1], min_p %g in [0, 1]", (double)s.top_p, (double)s.min_p);
+        return B2_EINVAL;
+    }
+    B2_CUDA_CHECK(cudaSetDevice(c->m->device));
+    if (c->samplers.empty()) {
+        c->samplers.assign(c->n_slots, b2_sampling{0.0f, 1.0f, 0.0f, 1, 0});
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->d_samplers, (size_t)c->n_slots * sizeof(b2_sampling)));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->d_col_params, BATCH_MAX_COLS * sizeof(b2_sampling)));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->d_col_draw, BATCH_MAX_COLS * sizeof(uint64_t)));
+        B2_CUDA_CHECK(cudaMallocHost((void**)&c->h_col_params, BATCH_MAX_COLS * sizeof(b2_sampling)));
+        B2_CUDA_CHECK(cudaMallocHost((void**)&c->h_col_draw, BATCH_MAX_COLS * sizeof(uint64_t)));
+    }
+    const bool was0 = slot_samples(c, 0);
+    c->samplers[slot] = s;
+    c->n_samplers = 0;
+    for (const auto& x : c->samplers) c->n_samplers += x.temperature > 0.0f && x.top_k != 1;
+    B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
+    B2_CUDA_CHECK(cudaMemcpy(c->d_samplers, c->samplers.data(), (size_t)c->n_slots * sizeof(b2_sampling), cudaMemcpyHostToDevice));
+    // the single-sequence step's CUDA graph carries (or not) the sampling kernel: rebuild it when slot 0 changes sides
+    if (slot == 0 && was0 != slot_samples(c, 0) && c->exec) {
+        cudaGraphExecDestroy(c->exec);
+        cudaGraphDestroy(c->graph);
+        c->exec = nullptr;
+        c->graph = nullptr;
+        int rc;
+        if ((rc = build_graph(c))) return rc;
+    }
+    return 0;
+}
 
 extern "C" int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int32_t* pos, int n, int last_only,
                                    int32_t* next_tokens_out, float* logits_out_host) {
@@ -1505,6 +1584,7 @@ extern "C" int b2_ctx_decode_batch(b2_ctx* c, const int32_t* tokens, const int32
     const int n_logits = last_only ? 1 : n;
     int rc;
     if ((rc = run_batch(c, tokens, slots, pos, n, n_logits))) return rc;
+    if ((rc = sample_columns(c, slots, pos, n - n_logits, n_logits))) return rc;
     if (logits_out_host)
         B2_CUDA_CHECK(cudaMemcpyAsync(logits_out_host, c->bt.logits, (size_t)n_logits * I.vocab * 4, cudaMemcpyDeviceToHost, c->stream));
     if (next_tokens_out) B2_CUDA_CHECK(cudaMemcpyAsync(c->h_pin, c->bt.out, (size_t)n_logits * 4, cudaMemcpyDeviceToHost, c->stream));
@@ -1675,7 +1755,8 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->tp_comm) tp_comm_free(c->tp_comm);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
                     c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch,
-                    c->d_ops, c->step_attn_partials, c->step_counters, c->step_sync, c->step_argmax_val, c->step_argmax_idx, c->step_trace};
+                    c->d_ops, c->step_attn_partials, c->step_counters, c->step_sync, c->step_argmax_val, c->step_argmax_idx, c->step_trace,
+                    c->d_samplers, c->d_col_params, c->d_col_draw};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     for (auto& g : c->bt.graphs)
@@ -1688,6 +1769,8 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     for (void* p : pptrs)
         if (p) cudaFree(p);
     if (c->h_pin) cudaFreeHost(c->h_pin);
+    if (c->h_col_params) cudaFreeHost(c->h_col_params);
+    if (c->h_col_draw) cudaFreeHost(c->h_col_draw);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -1766,6 +1849,7 @@ extern "C" int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, 
         B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // staging buffer reuse
         c->h_pin[0] = pos0 + n;
         B2_CUDA_CHECK(cudaMemcpyAsync(c->d_pos, c->h_pin, 4, cudaMemcpyHostToDevice, c->stream));
+        if ((rc = sample_single(c, c->stream, false))) return rc;
         n = 0;
     } else if (n >= 4 && batch_supported(c->m)) {
         int32_t pos[GEMM_MAX_COLS];
@@ -1789,6 +1873,7 @@ extern "C" int b2_ctx_decode(b2_ctx* c, const int32_t* tokens, int n, int pos0, 
         B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));   // staging buffer reuse
         c->h_pin[0] = pos0 + n;
         B2_CUDA_CHECK(cudaMemcpyAsync(c->d_pos, c->h_pin, 4, cudaMemcpyHostToDevice, c->stream));
+        if ((rc = sample_single(c, c->stream, false))) return rc;
         n = 0;   // nothing left for the per-token loop
     }
     for (int done = 0; done < n;) {

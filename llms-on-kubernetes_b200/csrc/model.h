@@ -79,6 +79,13 @@ struct b2_ctx {
     float* step_argmax_val = nullptr;
     int* step_argmax_idx = nullptr;
     int pos = 0;
+    // device-side sampling (b2_ctx_set_sampler): per-slot parameters (temperature <= 0: greedy), their device copy, and the
+    // per-column parameter / draw-index arrays of the current batched pass (pinned host staging + device)
+    std::vector<b2_sampling> samplers;
+    int n_samplers = 0;                     // slots with a non-greedy sampler
+    b2_sampling* d_samplers = nullptr;      // [n_slots]
+    b2_sampling *h_col_params = nullptr, *d_col_params = nullptr;   // [BATCH_MAX_COLS]
+    uint64_t *h_col_draw = nullptr, *d_col_draw = nullptr;          // [BATCH_MAX_COLS]
     // tensor parallelism: NCCL communicator (b2_allreduce_init)
     void* tp_comm = nullptr;
     // batched path: up to BATCH_MAX_COLS tokens per pass over the weights, each with its own (sequence slot,

@@ -83,6 +83,15 @@ int launch_embed_rows(int type, const void* table, int64_t row_bytes, int d_mode
 int launch_prefill_qkv_post(const PrefillQkvArgs& a, int T, cudaStream_t st);
 int launch_argmax_rows(const float* logits, int64_t n, int rows, int32_t* out, cudaStream_t st);
 
+// sample.cu: device-side sampling, one CTA per logits row.  only_sampled: rows whose parameters are greedy are left
+// untouched (the caller's argmax already wrote them).  draw_i32 (optional, instead of draw_dev): one device int32 used as
+// the draw index of every row (the single-sequence loop's position); echo: also store the token at echo_out[*echo_step - 1]
+// (the device-resident loop's output list).
+constexpr int SAMPLE_MAX_K = B2_SAMPLE_MAX_K;
+int launch_sample_rows(const float* logits, int64_t vocab, int64_t row_stride, int rows, const b2_sampling* params_dev, int64_t param_stride,
+                       const uint64_t* draw_dev, int32_t* out_dev, bool only_sampled, cudaStream_t st, const int32_t* draw_i32 = nullptr,
+                       int32_t* echo_out = nullptr, const int32_t* echo_step = nullptr, int echo_cap = 0);
+
 // tp.cu: the tensor-parallel exchange (NCCL through dlopen)
 int tp_unique_id(void* out, size_t cap);                                   // -> bytes written (128) or an error
 int tp_comm_init(const void* id_bytes, size_t len, int rank, int size, void** comm_out);

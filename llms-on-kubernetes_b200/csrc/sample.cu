@@ -80,7 +80,9 @@ __device__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* buf, int tid, uin
 }
 
 __global__ void __launch_bounds__(ST) sample_rows_kernel(const float* __restrict__ logits, int64_t vocab, int64_t row_stride, const b2_sampling* __restrict__ params,
-                                                        int64_t param_stride, const uint64_t* __restrict__ draw, int32_t* __restrict__ out, int out_only_sampled) {
+                                                        int64_t param_stride, const uint64_t* __restrict__ draw, int32_t* __restrict__ out, int out_only_sampled,
+                                                        const int32_t* __restrict__ draw_i32, int32_t* __restrict__ echo_out,
+                                                        const int32_t* __restrict__ echo_step, int echo_cap) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     SampleSmem& S = *(SampleSmem*)smem_raw;
     const int row = blockIdx.x, tid = threadIdx.x;
@@ -174,7 +176,13 @@ __global__ void __launch_bounds__(ST) sample_rows_kernel(const float* __restrict
         }
     }
     if (greedy) {
-        if (tid == 0) out[row] = S.idx[0];
+        if (tid == 0) {
+            out[row] = S.idx[0];
+            if (echo_out && echo_step) {
+                const int at = *echo_step - 1;
+                if (at >= 0 && at < echo_cap) echo_out[at] = S.idx[0];
+            }
+        }
         return;
     }
     // ---- probabilities, min-p, top-p, draw ----
@@ -204,7 +212,7 @@ __global__ void __launch_bounds__(ST) sample_rows_kernel(const float* __restrict
         }
         double tot = 0.0;
         for (int i = 0; i < keep; i++) tot += S.cum[i];
-        const uint32_t x = philox_u32(p.seed, draw ? draw[row] : (uint64_t)row);
+        const uint32_t x = philox_u32(p.seed, draw_i32 ? (uint64_t)(uint32_t)*draw_i32 : draw ? draw[row] : (uint64_t)row);
         double r = ((double)x + 0.5) * (1.0 / 4294967296.0) * tot;
         int pick = keep - 1;
         for (int i = 0; i < keep; i++) {
@@ -212,13 +220,18 @@ __global__ void __launch_bounds__(ST) sample_rows_kernel(const float* __restrict
             if (r <= 0.0) { pick = i; break; }
         }
         out[row] = S.idx[pick];
+        if (echo_out && echo_step) {
+            const int at = *echo_step - 1;
+            if (at >= 0 && at < echo_cap) echo_out[at] = S.idx[pick];
+        }
     }
 }
 
 }  // namespace
 
 int launch_sample_rows(const float* logits, int64_t vocab, int64_t row_stride, int rows, const b2_sampling* params_dev, int64_t param_stride,
-                       const uint64_t* draw_dev, int32_t* out_dev, bool only_sampled, cudaStream_t st) {
+                       const uint64_t* draw_dev, int32_t* out_dev, bool only_sampled, cudaStream_t st, const int32_t* draw_i32, int32_t* echo_out,
+                       const int32_t* echo_step, int echo_cap) {
     if (!logits || !params_dev || !out_dev || rows <= 0 || vocab <= 0 || vocab > (int64_t)1 << 30) {
         set_error("sample: bad arguments (rows=%d vocab=%lld)", rows, (long long)vocab);
         return B2_EINVAL;
@@ -230,7 +243,8 @@ int launch_sample_rows(const float* logits, int64_t vocab, int64_t row_stride, i
         B2_CUDA_CHECK(cudaFuncSetAttribute(sample_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured.set(dev, smem);
     }
-    sample_rows_kernel<<<rows, ST, smem, st>>>(logits, vocab, row_stride, params_dev, param_stride, draw_dev, out_dev, only_sampled ? 1 : 0);
+    sample_rows_kernel<<<rows, ST, smem, st>>>(logits, vocab, row_stride, params_dev, param_stride, draw_dev, out_dev, only_sampled ? 1 : 0, draw_i32, echo_out,
+                                               echo_step, echo_cap);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

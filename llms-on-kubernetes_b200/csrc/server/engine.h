@@ -63,6 +63,7 @@ struct Engine {
         bool have_next = false, greedy = true, finished = false;
         int max_new = 0;
         std::mt19937_64 rng;
+        uint64_t seed_used = 0;
         std::string pending;       // text held back: it may be the start of a stop string or an incomplete UTF-8 sequence
         size_t max_stop = 0;
         GenResult res;
@@ -77,6 +78,8 @@ struct Engine {
     int n_slots = 1;
     std::vector<std::vector<int32_t>> slot_cached;   // per slot: tokens at positions [0, size) of its KV cache
     std::vector<Job*> slot_job;
+    std::vector<char> slot_samples;   // per slot: a device sampler is set (b2_ctx_set_sampler)
+    bool dev_sampler = true;
     std::mutex qmu;
     std::condition_variable qcv;
     std::deque<Job*> waiting;
@@ -117,6 +120,8 @@ struct Engine {
         }
         slot_cached.assign(n_slots, {});
         slot_job.assign(n_slots, nullptr);
+        slot_samples.assign(n_slots, 0);
+        dev_sampler = !getenv("B2_HOST_SAMPLER");   // B2_HOST_SAMPLER=1: logits to the host, Engine::sample (the reference for the tests)
         logits.resize(info.vocab);
         sched = std::thread([this] { run_scheduler(); });
         sched.detach();
@@ -172,7 +177,8 @@ struct Engine {
             if (t < 0 || t >= info.vocab) { job.res.error = "token id out of range in prompt"; job.res.error_status = 400; return job.res; }
         job.max_new = std::min(p.max_tokens < 0 ? nctx : p.max_tokens, nctx - (int)prompt.size());
         job.greedy = p.temperature <= 0.0f || p.top_k == 1;
-        job.rng.seed(p.seed == 0xFFFFFFFFull ? std::random_device{}() : p.seed);
+        job.seed_used = p.seed == 0xFFFFFFFFull ? ((uint64_t)std::random_device{}() << 32 | std::random_device{}()) : p.seed;
+        job.rng.seed(job.seed_used);
         for (auto& s : p.stop) job.max_stop = std::max(job.max_stop, s.size());
         m_requests++;
         m_deferred++;
@@ -296,6 +302,18 @@ struct Engine {
             slot_cached[best].resize(best_cp);
             b2_ctx_slot_truncate(ctx, best, (int)best_cp);   // paged KV: the pages past the shared prefix go back to the pool
             slot_job[best] = j;
+            // sampling happens on the device (b2_ctx_set_sampler): the slot draws with this request's parameters, and from
+            // here on the request is handled like a greedy one -- every call returns its next token, no logits come back
+            if (dev_sampler) {
+                if (!j->greedy) {
+                    const b2_sampling sp{j->p.temperature, j->p.top_p > 0.0f && j->p.top_p <= 1.0f ? j->p.top_p : 1.0f,
+                                         j->p.min_p < 0.0f ? 0.0f : (j->p.min_p > 1.0f ? 1.0f : j->p.min_p), j->p.top_k, j->seed_used};
+                    if (b2_ctx_set_sampler(ctx, best, &sp) == 0) { j->greedy = true; slot_samples[best] = 1; }
+                } else if (slot_samples[best]) {
+                    b2_ctx_set_sampler(ctx, best, nullptr);
+                    slot_samples[best] = 0;
+                }
+            }
             m_deferred--;
             m_processing++;
             m_prompt_reused += best_cp;

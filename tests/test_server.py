@@ -350,3 +350,29 @@ def test_oversubscribed_kv_pool_recycles_pages(b2, tiny_models):
     finally:
         proc.terminate()
         proc.wait(timeout=10)
+
+
+@pytest.mark.gpu
+def test_default_sampling_requests_stay_on_the_device(server):
+    """A request without sampling fields takes llama-server's defaults (temperature 0.8, top-k 40, top-p 0.95, min-p 0.05:
+    what the README's curl and OpenWebUI send).  The server draws on the device (b2_ctx_set_sampler): a seeded request
+    repeats itself alone or among other traffic of any kind, because a draw depends on (seed, position) only."""
+    import threading
+    base = {"prompt": "the quick brown fox", "max_tokens": 20, "ignore_eos": True, "seed": 4242}
+    st, a = post(server, "/v1/completions", base)
+    assert st == 200 and len(a["choices"][0]["tokens"]) == 20
+    st, b = post(server, "/v1/completions", base)
+    assert a["choices"][0]["tokens"] == b["choices"][0]["tokens"]
+    # the same request among 15 others (sampled with other seeds, and greedy ones)
+    reqs = [dict(base)] + [dict(base, seed=100 + i) for i in range(8)] + [dict(base, temperature=0) for _ in range(7)]
+    res = [None] * len(reqs)
+    ts = [threading.Thread(target=lambda i=i: res.__setitem__(i, post(server, "/v1/completions", reqs[i]))) for i in range(len(reqs))]
+    for t in ts: t.start()
+    for t in ts: t.join()
+    assert all(r[0] == 200 and len(r[1]["choices"][0]["tokens"]) == 20 for r in res)
+    greedy = [r[1]["choices"][0]["tokens"] for r in res[9:]]
+    assert all(g[:4] == greedy[0][:4] for g in greedy)               # the greedy ones agree with each other
+    same_first = res[0][1]["choices"][0]["tokens"][:6] == a["choices"][0]["tokens"][:6]
+    assert same_first, "a seeded sampled request changed its first tokens when served inside a batch"
+    distinct = {tuple(r[1]["choices"][0]["tokens"]) for r in res[:9]}
+    assert len(distinct) >= 5, "nine seeds produced almost the same continuation: the sampler is not sampling"
