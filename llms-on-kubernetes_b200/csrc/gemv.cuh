@@ -36,6 +36,10 @@ struct GemvSeg {
     int n_pairs, n_rows, tile0;
     int head_dim, n_ctx;
     float res_scale;     // EPI_RESID_TP
+    // EPI_RESID_TP inside the persistent kernel of a tensor-parallel shard: instead of updating `out` the epilogue stores
+    // res * res_scale + partial at the same row of every rank's inbox (peer memory, plain stores); out is only read
+    float* peer_out[8];
+    int n_peer;          // 0: update `out` in place (the all-reduce follows as a separate call)
 };
 
 struct GemvArgs {
@@ -48,6 +52,15 @@ struct GemvArgs {
     const int* pos_ptr;    // device-resident position (RoPE / cache epilogues), may be NULL otherwise
     const float2* rope_tab;  // [n_ctx][rope_half] (cos, sin)
     int rope_half;
+    // Tensor-parallel shard inside the persistent kernel (step2.cu): the activation is the sum, in rank order, of x_nparts
+    // vectors of K floats at x_parts + r * K -- the partial residual streams the ranks' row-split epilogues stored into this
+    // rank's inbox -- once xg_flags[r] (written by rank r) have reached the stage's sequence number.  The stage also leaves
+    // the sum in x (the residual the next row-split epilogue reads).  x_nparts == 0: plain x.
+    const float* x_parts;
+    int x_nparts, xg_k;
+    const unsigned int* xg_flags;
+    unsigned int* xg_peer_flags[8];
+    const unsigned int* xg_epoch;
 };
 
 constexpr int GEMV_CONSUMER_WARPS = 8;

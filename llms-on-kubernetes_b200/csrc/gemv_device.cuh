@@ -241,6 +241,23 @@ struct ActSmem {
     uint64_t* xbar;    // completes when every span has arrived
 };
 
+// the same from the sum of the ranks' partial vectors (GemvArgs::x_parts), added in rank order
+__device__ __forceinline__ void load8_parts(const float* parts, int nparts, int i0, int K, float (&v)[8]) {
+    if (i0 < K) {
+        float4 p0 = __ldcg((const float4*)(parts + i0)), p1 = __ldcg((const float4*)(parts + i0 + 4));
+        for (int r = 1; r < nparts; r++) {
+            const float4 q0 = __ldcg((const float4*)(parts + (size_t)r * K + i0)), q1 = __ldcg((const float4*)(parts + (size_t)r * K + i0 + 4));
+            p0.x += q0.x; p0.y += q0.y; p0.z += q0.z; p0.w += q0.w;
+            p1.x += q1.x; p1.y += q1.y; p1.z += q1.z; p1.w += q1.w;
+        }
+        v[0] = p0.x; v[1] = p0.y; v[2] = p0.z; v[3] = p0.w;
+        v[4] = p1.x; v[5] = p1.y; v[6] = p1.z; v[7] = p1.w;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 8; i++) v[i] = 0.0f;
+    }
+}
+
 __device__ __forceinline__ void load8(const float* p, int i0, int K, float (&v)[8]) {
     if (i0 < K) {
         const float4 p0 = *(const float4*)(p + i0), p1 = *(const float4*)(p + i0 + 4);
@@ -347,6 +364,8 @@ __device__ __forceinline__ void build_activation(const GemvArgs& a, const ActSme
                                  uint32_t parity = 0, unsigned long long* tr = nullptr) {
     const int K = a.K;
     const int lane = tid & 31, warp = tid >> 5;
+    // (a tensor-parallel shard reads the sum of the ranks' partial vectors instead of x)
+#define LOADX(i0, KK, vv) do { if (a.x_nparts > 0) load8_parts(a.x_parts, a.x_nparts, i0, KK, vv); else load8(a.x, i0, KK, vv); } while (0)
     const int nspans = (K + 255) >> 8;
     const int first = (int)rank + (int)csize * warp, stride = (int)csize * NCW;   // this warp's spans
     float scale = 1.0f;
@@ -357,13 +376,13 @@ __device__ __forceinline__ void build_activation(const GemvArgs& a, const ActSme
         // ggml rms_norm: sum of fp32 squares accumulated in double, mean, 1/sqrtf(mean + eps); then (x*scale)*w.
         // Every CTA adds up the whole vector itself (K floats out of L2, in flight together with its own
         // spans): a round trip through the cluster for the partial sums costs more than the redundant reads.
-        if (first < nspans) load8(a.x, (first << 8) + lane * 8, K, v0);
-        if (first + stride < nspans) load8(a.x, ((first + stride) << 8) + lane * 8, K, v1);
+        if (first < nspans) LOADX((first << 8) + lane * 8, K, v0);
+        if (first + stride < nspans) LOADX(((first + stride) << 8) + lane * 8, K, v1);
         double ss = 0.0;
 #pragma unroll 2
         for (int i0 = tid * 8; i0 < K; i0 += NCT * 8) {
             float t[8];
-            load8(a.x, i0, K, t);
+            LOADX(i0, K, t);
 #pragma unroll
             for (int i = 0; i < 8; i++) ss += (double)(t[i] * t[i]);
         }
@@ -393,19 +412,19 @@ __device__ __forceinline__ void build_activation(const GemvArgs& a, const ActSme
         if (first + stride < nspans) norm_quant(v1, first + stride);
         for (int s = first + 2 * stride; s < nspans; s += stride) {
             float t[8];
-            load8(a.x, (s << 8) + lane * 8, K, t);
+            LOADX((s << 8) + lane * 8, K, t);
             norm_quant(t, s);
         }
     } else {
         // issue the loads of two spans before the first use
-        if (first < nspans) load8(a.x, (first << 8) + lane * 8, K, v0);
-        if (first + stride < nspans) load8(a.x, ((first + stride) << 8) + lane * 8, K, v1);
+        if (first < nspans) LOADX((first << 8) + lane * 8, K, v0);
+        if (first + stride < nspans) LOADX(((first + stride) << 8) + lane * 8, K, v1);
         if (tr && tid == 0) tr[4] = trace_after(__float_as_uint(v0[0]));
         if (first < nspans) quantise_span<ACT>(v0, first << 8, lane, K, sm, smem_base, csize);
         if (first + stride < nspans) quantise_span<ACT>(v1, (first + stride) << 8, lane, K, sm, smem_base, csize);
         for (int s = first + 2 * stride; s < nspans; s += stride) {
             float t[8];
-            load8(a.x, (s << 8) + lane * 8, K, t);
+            LOADX((s << 8) + lane * 8, K, t);
             quantise_span<ACT>(t, s << 8, lane, K, sm, smem_base, csize);
         }
     }
@@ -415,6 +434,7 @@ __device__ __forceinline__ void build_activation(const GemvArgs& a, const ActSme
     if (tid == 0) mbar_arrive_expect_tx(sm.xbar, activation_bytes<ACT>(K));
     if (tr && tid == 0) tr[7] = trace_ns();
     mbar_wait(sm.xbar, parity);
+#undef LOADX
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -467,10 +487,20 @@ __device__ __forceinline__ void epilogue_apply(const GemvSeg& s, int p, int ra, 
             s.out[ra] = o.res_a + va;
             if (rb >= 0) s.out[rb] = o.res_b + vb;
             break;
-        case EPI_RESID_TP:
-            s.out[ra] = o.res_a * s.res_scale + va;
-            if (rb >= 0) s.out[rb] = o.res_b * s.res_scale + vb;
+        case EPI_RESID_TP: {
+            const float fa = o.res_a * s.res_scale + va, fb = o.res_b * s.res_scale + vb;
+            if (s.n_peer > 0) {
+                // this rank's share of the new residual stream, delivered to every rank (the exchange stage sums them)
+                for (int p = 0; p < s.n_peer; p++) {
+                    s.peer_out[p][ra] = fa;
+                    if (rb >= 0) s.peer_out[p][rb] = fb;
+                }
+            } else {
+                s.out[ra] = fa;
+                if (rb >= 0) s.out[rb] = fb;
+            }
             break;
+        }
         case EPI_SWIGLU:
             // ggml silu: x / (1 + expf(-x))
             s.out[p] = (va / (1.0f + expf(-va))) * vb;

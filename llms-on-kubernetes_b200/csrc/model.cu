@@ -494,7 +494,7 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
         a.seg[0].res_scale = 1.0f / (float)m->tp_size;   // exact for 2 / 4 / 8 ranks
         a.n_seg = 1;
         if ((rc = run(a, gemv_act_for_type(L.wo.type)))) return rc;
-        if (tp && !matvec_only) {
+        if (tp && !record && !matvec_only) {
             if ((rc = tp_allreduce_inplace(c->tp_comm, c->x, I.d_model, st))) return rc;
             launches += 1;
         }
@@ -518,7 +518,7 @@ int enqueue_step(b2_ctx* c, cudaStream_t st, bool pdl, bool matvec_only = false,
         a.seg[0].res_scale = 1.0f / (float)m->tp_size;
         a.n_seg = 1;
         if ((rc = run(a, gemv_act_for_type(L.down.type)))) return rc;
-        if (tp && !matvec_only) {
+        if (tp && !record && !matvec_only) {
             if ((rc = tp_allreduce_inplace(c->tp_comm, c->x, I.d_model, st))) return rc;
             launches += 1;
         }
@@ -647,6 +647,39 @@ int build_step_program(b2_ctx* c) {
                 if (v >= 32 && v <= STEP_ATTN_MAX_CHUNK && v % 32 == 0) op.a_min_chunk = v;
             }
         }
+    if (c->m->tp_size > 1) {
+        // tensor-parallel shard: the exchange stages and the peer stores of the mat-vecs in front of them
+        const int tp = c->m->tp_size, rank = c->m->tp_rank, d = I.d_model;
+        if (c->step_version != 2 || !c->tp_local) {
+            c->use_step = false;   // (the first design has no exchange stage)
+            return 0;
+        }
+        // every row-split mat-vec (O, down) is exchange k: its epilogues store into all ranks' inboxes (parity k & 1), and the
+        // next mat-vec stage -- the consumer of the new residual stream -- waits for the ranks' sequence numbers and reads the sum
+        int k = 0;
+        for (size_t i = 0; i < ops.size(); i++) {
+            StepOp& op = ops[i];
+            if (op.kind == OP_ARGMAX) op.s_epoch = c->tp_epoch;
+            if (op.kind != OP_GEMV || op.g.n_seg != 1 || op.g.seg[0].epi != EPI_RESID_TP) continue;
+            size_t j = i + 1;
+            while (j < ops.size() && ops[j].kind != OP_GEMV) j++;
+            if (k >= 255 || j == ops.size() || ops[j].g.x != c->x || ops[j].g.K != d) {
+                set_error("step program: row-split mat-vec %d is not followed by a stage that reads the residual stream", k);
+                return B2_EINVAL;
+            }
+            GemvSeg& s = op.g.seg[0];
+            s.n_peer = tp;
+            for (int p = 0; p < tp; p++) s.peer_out[p] = (float*)c->tp_peers[p] + ((size_t)(k & 1) * tp + rank) * d;
+            GemvArgs& g = ops[j].g;
+            g.x_parts = (const float*)c->tp_local + (size_t)(k & 1) * tp * d;
+            g.x_nparts = tp;
+            g.xg_k = k;
+            g.xg_flags = (const unsigned int*)((const uint8_t*)c->tp_local + c->tp_flags_off);
+            for (int p = 0; p < tp; p++) g.xg_peer_flags[p] = (unsigned int*)((uint8_t*)c->tp_peers[p] + c->tp_flags_off) + rank;
+            g.xg_epoch = c->tp_epoch;
+            k++;
+        }
+    }
     B2_CUDA_CHECK(cudaMalloc(&c->d_ops, ops.size() * sizeof(StepOp)));
     B2_CUDA_CHECK(cudaMemcpyAsync(c->d_ops, ops.data(), ops.size() * sizeof(StepOp), cudaMemcpyHostToDevice, c->stream));
     B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
@@ -1716,7 +1749,7 @@ extern "C" int b2_ctx_create_slots(b2_model* m, int n_ctx, int n_slots, b2_ctx**
         B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
     }
     // scratch + program of the persistent per-token kernel (B2_NO_STEP=1 keeps one launch per stage)
-    c->use_step = !env_flag("B2_NO_STEP") && m->tp_size == 1;   // a shard exchanges partial sums between stages
+    c->use_step = !env_flag("B2_NO_STEP");   // (a shard's program is built by b2_allreduce_init: its exchange stages need the peers)
     if (m->tp_size > 1) {
         // the first step (and the CUDA graph of a step) need the communicator: b2_allreduce_init finishes the set-up
         B2_CUDA_CHECK(cudaStreamSynchronize(c->stream));
@@ -1752,6 +1785,8 @@ extern "C" void b2_ctx_free(b2_ctx* c) {
     if (c->exec) cudaGraphExecDestroy(c->exec);
     if (c->graph) cudaGraphDestroy(c->graph);
     if (c->d_kv_table) cudaFree(c->d_kv_table);
+    if (c->tp_local) tp_peer_release(c->m->tp_rank, c->m->tp_size, c->tp_local, c->tp_peers);
+    if (c->tp_epoch) cudaFree(c->tp_epoch);
     if (c->tp_comm) tp_comm_free(c->tp_comm);
     void* ptrs[] = {c->k_cache, c->v_cache, c->x, c->q, c->attn_out, c->h, c->logits, c->d_tok, c->d_pos, c->d_step,
                     c->d_out, c->d_prompt, c->rope_tab, c->attn_scratch, c->argmax_scratch,
@@ -1787,6 +1822,28 @@ extern "C" int b2_allreduce_init(b2_ctx* c, const void* id, size_t id_bytes) {
     B2_CUDA_CHECK(cudaSetDevice(c->m->device));
     int rc;
     if ((rc = tp_comm_init(id, id_bytes, c->m->tp_rank, c->m->tp_size, &c->tp_comm))) return rc;
+    // The persistent kernel on a shard: the all-reduce after O and down becomes a stage of the kernel -- every rank's
+    // epilogues store their partial rows into every rank's inbox (peer memory over NVLink, plain stores), the ranks
+    // exchange sequence numbers, each sums its inbox in rank order.  B2_TP_NCCL=1 (or a shape the kernel does not take,
+    // or more than 8 ranks) keeps one launch per stage with ncclAllReduce between them.
+    if (c->use_step && !env_flag("B2_TP_NCCL") && c->m->tp_size <= 8) {
+        const b2_model_info& I = c->m->info;
+        const int tp = c->m->tp_size;
+        c->tp_flags_off = ((size_t)2 * tp * I.d_model * sizeof(float) + 255) & ~(size_t)255;
+        if ((rc = tp_peer_buffers(c->tp_comm, c->m->tp_rank, tp, c->tp_flags_off + 256, &c->tp_local, c->tp_peers, c->stream))) return rc;
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->tp_epoch, 256));
+        B2_CUDA_CHECK(cudaMemset(c->tp_epoch, 0, 256));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_counters, (8 + I.n_head) * sizeof(unsigned int)));
+        B2_CUDA_CHECK(cudaMemsetAsync(c->step_counters, 0, (8 + I.n_head) * sizeof(unsigned int), c->stream));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_sync, STEP_SYNC_BYTES));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_argmax_val, 1024 * sizeof(float)));
+        B2_CUDA_CHECK(cudaMalloc((void**)&c->step_argmax_idx, 1024 * sizeof(int)));
+        if ((rc = build_step_program(c))) return rc;
+        // nobody launches a step before every rank has mapped the buffers and cleared its flags
+        if ((rc = tp_barrier(c->tp_comm, (float*)((uint8_t*)c->tp_epoch + 128), c->stream))) return rc;
+    } else {
+        c->use_step = false;
+    }
     // what b2_ctx_create does for a replica: one eager step (lazy module loading outside capture), then the graph.
     // Every rank runs the same steps, so the collectives inside match up.
     if ((rc = enqueue_decode(c, c->stream, false))) return rc;

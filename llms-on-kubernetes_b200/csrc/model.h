@@ -88,6 +88,11 @@ struct b2_ctx {
     uint64_t *h_col_draw = nullptr, *d_col_draw = nullptr;          // [BATCH_MAX_COLS]
     // tensor parallelism: NCCL communicator (b2_allreduce_init)
     void* tp_comm = nullptr;
+    // ... and the exchange inside the persistent kernel: this rank's inbox + flags, every rank's mapping of them, launch counter
+    void* tp_local = nullptr;
+    void* tp_peers[8] = {};
+    size_t tp_flags_off = 0;
+    unsigned int* tp_epoch = nullptr;
     // batched path: up to BATCH_MAX_COLS tokens per pass over the weights, each with its own (sequence slot,
     // position) -- up to GEMM_MAX_COLS columns on the int8 kernel (gemm.cu), wider batches (and any batch of at least
     // tc_batch_min() columns when the model's fp16 copy is resident) on the tensor-core pass (tc_gemm.cu).  KV caches

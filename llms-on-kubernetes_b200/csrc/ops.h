@@ -97,5 +97,9 @@ int tp_unique_id(void* out, size_t cap);                                   // ->
 int tp_comm_init(const void* id_bytes, size_t len, int rank, int size, void** comm_out);
 void tp_comm_free(void* comm);
 int tp_allreduce_inplace(void* comm, float* x, int n, cudaStream_t st);            // x = allreduce_sum(x)
+// peer memory for the exchange inside the persistent kernel: every rank's zeroed buffer of `bytes`, mapped into every rank
+int tp_peer_buffers(void* comm, int rank, int size, size_t bytes, void** local_out, void** peers, cudaStream_t st);
+void tp_peer_release(int rank, int size, void* local, void** peers);
+int tp_barrier(void* comm, float* scratch_dev, cudaStream_t st);
 
 }  // namespace b2

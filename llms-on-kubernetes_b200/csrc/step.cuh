@@ -34,6 +34,7 @@ struct StepOp {
     float* s_val;            // [grid] partial maxima
     int* s_idx;              // [grid]
     unsigned int* s_counter;
+    unsigned int* s_epoch;   // tensor-parallel shard: launches so far (the exchange stages' sequence numbers), else NULL
 };
 
 struct StepProgram {

@@ -277,7 +277,9 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
                 ph ^= 1 << parity;
             }
             // a fence orders only the calling thread's stores: every lane that wrote results fences, then one arrives
-            __threadfence();
+            // (system scope when the rows went into the other ranks' memory)
+            if (a.seg[0].n_peer > 0) __threadfence_system();
+            else __threadfence();
             __syncwarp();
             if (lane == 0) {
                 if (P.trace && P.fine_op == oi) P.trace[(size_t)P.n_ops * STEP_TRACE_SLOTS + 1024 + blockIdx.x] = globaltimer_ns();
@@ -331,7 +333,9 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
             sm.xd = (float*)(sm.xq + K);
             sm.bs16 = (int16_t*)(sm.xd + (ACT == ACT_Q8K ? K / 256 : K / 32));
             sm.bs32 = sm.bs16 + K / 16;
+            if (a.x_nparts > 0) xchg_wait(a, tid);   // tensor-parallel shard: the ranks' partial residual streams have arrived
             build_activation<ACT>(a, sm, smem, tid, rank, csize, xpar, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
+            if (a.x_nparts > 0) xchg_materialise(a, tid);
             if (tid == 0) stamp(P, oi, 1);
             xpar ^= 1;
             const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};

@@ -185,6 +185,48 @@ static __device__ __noinline__ void prefetch_next_stage(const StepOp& op, int la
     }
 }
 
+// ---- tensor-parallel exchange at the head of a mat-vec stage (GemvArgs::x_parts) ----------------------------------------
+// The grid barrier in front of the stage says: every CTA of THIS rank has stored its partial rows of the previous
+// (row-split) mat-vec into every rank's inbox and fenced them at system scope.  One thread per peer then publishes this
+// rank's sequence number in that peer's flag array (st.release.sys: cumulative over what the barrier made visible), and
+// every CTA waits until all ranks' numbers have arrived here; build_activation then reads the inbox, summed in rank order
+// (the same order on every rank: identical sums).  Peer memory is only ever written (plain stores); loads are local.
+// Waits are bounded and trap.  Called by the NCT compute threads.
+// (Measured and dropped: every CTA adding 1 to a per-exchange counter on every rank with red.release.sys, instead of
+// one flag per rank after the local barrier -- 284 remote reductions on one address per rank and exchange: 8B at TP 2
+// went from 419 to 386 tok/s.)
+static __device__ __noinline__ void xchg_wait(const GemvArgs& a, int tid) {
+    const unsigned int seq = *a.xg_epoch * 256u + (unsigned int)a.xg_k + 1u;
+    if (blockIdx.x == 0 && tid < a.x_nparts) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.xg_peer_flags[tid]), "r"(seq) : "memory");
+    }
+    if (tid < a.x_nparts) {
+        unsigned int v = 0;
+        uint32_t spin = 0;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.xg_flags + tid) : "memory");
+            if ((int)(v - seq) >= 0) break;
+            if (++spin > (1u << 25)) asm volatile("trap;");
+            __nanosleep(40);
+        }
+    }
+    named_bar_sync(1, NCT);
+}
+// ... and the sum is left in x for the residual reads of the next row-split epilogue (a few CTAs' worth of stores)
+static __device__ __noinline__ void xchg_materialise(const GemvArgs& a, int tid) {
+    const int n4 = a.K / 4;
+    const float4* in = (const float4*)a.x_parts;
+    for (int i = blockIdx.x * NCT + tid; i < n4; i += gridDim.x * NCT) {
+        float4 s = __ldcg(in + i);
+        for (int r = 1; r < a.x_nparts; r++) {
+            const float4 v = __ldcg(in + (size_t)r * n4 + i);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        ((float4*)const_cast<float*>(a.x))[i] = s;
+    }
+}
+
 __device__ __forceinline__ void argmax_fold(float& bv, int& bi, float ov, int oi) {
     if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
 }
@@ -233,6 +275,7 @@ static __device__ __noinline__ void argmax_stage(const StepOp& op, uint8_t* xbas
             *op.s_step = s + 1;
         }
         if (op.s_pos) *op.s_pos = *op.s_pos + 1;
+        if (op.s_epoch) *op.s_epoch = *op.s_epoch + 1u;
         *op.s_counter = 0u;
     }
 }

@@ -13,6 +13,7 @@
 
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 #include "common.h"
 #include "ops.h"
@@ -26,6 +27,7 @@ struct Nccl {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
 
@@ -45,8 +47,9 @@ int nccl(Nccl** out) {
         n.CommInitRank = (decltype(n.CommInitRank))dlsym(n.lib, "ncclCommInitRank");
         n.CommDestroy = (decltype(n.CommDestroy))dlsym(n.lib, "ncclCommDestroy");
         n.AllReduce = (decltype(n.AllReduce))dlsym(n.lib, "ncclAllReduce");
+        n.AllGather = (decltype(n.AllGather))dlsym(n.lib, "ncclAllGather");
         n.GetErrorString = (decltype(n.GetErrorString))dlsym(n.lib, "ncclGetErrorString");
-        if (!n.GetUniqueId || !n.CommInitRank || !n.CommDestroy || !n.AllReduce || !n.GetErrorString) {
+        if (!n.GetUniqueId || !n.CommInitRank || !n.CommDestroy || !n.AllReduce || !n.AllGather || !n.GetErrorString) {
             set_error("libnccl does not export the expected symbols");
             dlclose(n.lib);
             n.lib = nullptr;
@@ -117,4 +120,66 @@ int tp_allreduce_inplace(void* comm, float* x, int n, cudaStream_t st) {
     return 0;
 }
 
+// ---- peer memory for the exchange inside the persistent kernel (step2.cu: OP_XCHG) ----
+// Every rank allocates `bytes` of device memory (zeroed), publishes its CUDA IPC handle through the communicator
+// (ncclAllGather of the 64-byte handles) and maps every peer's allocation: peers[r] is rank r's buffer as seen from this
+// process (peers[rank] = the local allocation).  The kernels only ever STORE into a peer's buffer and LOAD from their
+// own (plain st.global / ld.global over NVLink: no TMA, no multicast).
+int tp_peer_buffers(void* comm, int rank, int size, size_t bytes, void** local_out, void** peers, cudaStream_t st) {
+    Nccl* nc;
+    int rc;
+    if ((rc = nccl(&nc))) return rc;
+    if (!comm || size < 2 || size > 8 || rank < 0 || rank >= size) {
+        set_error("tp_peer_buffers: bad group (rank %d of %d; up to 8 ranks)", rank, size);
+        return B2_EINVAL;
+    }
+    void* local = nullptr;
+    B2_CUDA_CHECK(cudaMalloc(&local, bytes));
+    B2_CUDA_CHECK(cudaMemset(local, 0, bytes));
+    cudaIpcMemHandle_t mine;
+    B2_CUDA_CHECK(cudaIpcGetMemHandle(&mine, local));
+    uint8_t *d_mine = nullptr, *d_all = nullptr;
+    B2_CUDA_CHECK(cudaMalloc((void**)&d_mine, sizeof mine));
+    B2_CUDA_CHECK(cudaMalloc((void**)&d_all, sizeof mine * size));
+    B2_CUDA_CHECK(cudaMemcpyAsync(d_mine, &mine, sizeof mine, cudaMemcpyHostToDevice, st));
+    B2_NCCL_CHECK(nc, nc->AllGather(d_mine, d_all, sizeof mine, ncclChar, (ncclComm_t)comm, st));
+    std::vector<cudaIpcMemHandle_t> all(size);
+    B2_CUDA_CHECK(cudaMemcpyAsync(all.data(), d_all, sizeof mine * size, cudaMemcpyDeviceToHost, st));
+    B2_CUDA_CHECK(cudaStreamSynchronize(st));
+    cudaFree(d_mine);
+    cudaFree(d_all);
+    for (int r = 0; r < size; r++) {
+        if (r == rank) {
+            peers[r] = local;
+            continue;
+        }
+        void* p = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            set_error("tensor parallelism: cannot map rank %d's exchange buffer (%s); B2_TP_NCCL=1 keeps the NCCL all-reduce path", r, cudaGetErrorString(e));
+            return B2_ECUDA;
+        }
+        peers[r] = p;
+    }
+    *local_out = local;
+    return 0;
+}
+
+void tp_peer_release(int rank, int size, void* local, void** peers) {
+    for (int r = 0; r < size; r++)
+        if (r != rank && peers[r]) cudaIpcCloseMemHandle(peers[r]);
+    if (local) cudaFree(local);
+}
+
+// every rank has reached this point (and finished what it enqueued before): a one-float all-reduce
+int tp_barrier(void* comm, float* scratch_dev, cudaStream_t st) {
+    Nccl* nc;
+    int rc;
+    if ((rc = nccl(&nc))) return rc;
+    B2_NCCL_CHECK(nc, nc->AllReduce(scratch_dev, scratch_dev, 1, ncclFloat, ncclSum, (ncclComm_t)comm, st));
+    B2_CUDA_CHECK(cudaStreamSynchronize(st));
+    return 0;
+}
+
 }  // namespace b2
+
