@@ -291,6 +291,19 @@ def bench_batched(b2, synth, spec, model, args, world, barrier, max_over_ranks, 
                          "peak_source": peak_src, "bytes_per_step": step_bytes}}
 
 
+_real_stdout = [None]
+
+
+def emit(obj: dict):
+    """The one JSON line of the run, on the process's original stdout."""
+    line = json.dumps(obj)
+    if _real_stdout[0] is not None:
+        _real_stdout[0].write(line + "\n")
+        _real_stdout[0].flush()
+    else:
+        print(line, flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -365,10 +378,14 @@ def main():
             red_device = "cpu"
             dist.init_process_group("gloo")
         else:
-            # NCCL's log (communicator ranks, transports) goes to stderr: stdout carries exactly one JSON line
+            # NCCL's log (communicator ranks, transports) is wanted, but it goes to stdout, which must carry exactly one
+            # JSON line: file descriptor 1 is pointed at stderr for the rest of the process and the line is written to a
+            # duplicate of the original stdout (emit() below)
             os.environ.setdefault("NCCL_DEBUG", "INFO")
             os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
-            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+            sys.stdout.flush()
+            _real_stdout[0] = os.fdopen(os.dup(1), "w")
+            os.dup2(2, 1)
             torch.cuda.set_device(local_rank)
             dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -390,7 +407,7 @@ def main():
         barrier()
         ms = max_over_ranks(10.0 * (rank + 1))
         if rank == 0:
-            print(json.dumps({"selftest": True, "n_gpus": world, "ms": ms, "value": world * args.steps / (ms / 1e3), "scaling": "weak"}))
+            emit({"selftest": True, "n_gpus": world, "ms": ms, "value": world * args.steps / (ms / 1e3), "scaling": "weak"})
         if dist is not None:
             dist.destroy_process_group()
         return
@@ -406,7 +423,7 @@ def main():
         out = bench_batched(b2, synth, spec, model, args, world, barrier, max_over_ranks, local_rank)
         model.free()
         if rank == 0:
-            print(json.dumps(out))
+            emit(out)
         if dist is not None:
             dist.destroy_process_group()
         return
@@ -499,7 +516,7 @@ def main():
     ctx.free()
     model.free()
     if rank == 0:
-        print(json.dumps(out))
+        emit(out)
     if dist is not None:
         dist.destroy_process_group()
 
