@@ -359,13 +359,14 @@ __device__ __forceinline__ uint32_t activation_bytes(int K) {
 
 // parity: phase of xbar to wait for (0 for a kernel that builds one activation vector).
 // Called by all NCT compute threads (uses named barrier 1).
-template <int ACT>
+// TP = false compiles the tensor-parallel input (x_parts) out: the single-GPU step kernel keeps its registers.
+template <int ACT, bool TP = true>
 __device__ __forceinline__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uint8_t* smem_base, int tid, uint32_t rank, uint32_t csize,
                                  uint32_t parity = 0, unsigned long long* tr = nullptr) {
     const int K = a.K;
     const int lane = tid & 31, warp = tid >> 5;
     // (a tensor-parallel shard reads the sum of the ranks' partial vectors instead of x)
-#define LOADX(i0, KK, vv) do { if (a.x_nparts > 0) load8_parts(a.x_parts, a.x_nparts, i0, KK, vv); else load8(a.x, i0, KK, vv); } while (0)
+#define LOADX(i0, KK, vv) do { if (TP && a.x_nparts > 0) load8_parts(a.x_parts, a.x_nparts, i0, KK, vv); else load8(a.x, i0, KK, vv); } while (0)
     const int nspans = (K + 255) >> 8;
     const int first = (int)rank + (int)csize * warp, stride = (int)csize * NCW;   // this warp's spans
     float scale = 1.0f;
@@ -473,6 +474,7 @@ __device__ __forceinline__ EpiOperands epilogue_operands(const GemvArgs& a, cons
     return o;
 }
 
+template <bool TP = true>
 __device__ __forceinline__ void epilogue_apply(const GemvSeg& s, int p, int ra, int rb, float va, float vb, const EpiOperands& o, int pos) {
     if (s.bias) {
         va += o.bias_a;
@@ -489,7 +491,7 @@ __device__ __forceinline__ void epilogue_apply(const GemvSeg& s, int p, int ra, 
             break;
         case EPI_RESID_TP: {
             const float fa = o.res_a * s.res_scale + va, fb = o.res_b * s.res_scale + vb;
-            if (s.n_peer > 0) {
+            if (TP && s.n_peer > 0) {
                 // this rank's share of the new residual stream, delivered to every rank (the exchange stage sums them)
                 for (int p = 0; p < s.n_peer; p++) {
                     s.peer_out[p][ra] = fa;
@@ -537,6 +539,7 @@ __device__ __forceinline__ void epilogue_apply(const GemvSeg& s, int p, int ra, 
 
 // epilogue warp, one tile: lanes 0, 2, 4, 6 own the tile's row pairs.  Fetch the operands, wait for the eight
 // compute warps' shares, add them in a fixed order, release the buffer, finish the pair.
+template <bool TP = true>
 __device__ __forceinline__ void epilogue_tile(const GemvArgs& a, const GemvSeg& s, int ptile, int pos, const float* rp,
                                               uint64_t* part_full, uint64_t* part_free, uint32_t full_phase, int lane) {
     const int p = ptile * GEMV_TILE_PAIRS + (lane >> 1);
@@ -556,7 +559,7 @@ __device__ __forceinline__ void epilogue_tile(const GemvArgs& a, const GemvSeg& 
     __syncwarp();
     if (lane == 0) mbar_arrive(part_free);
     const float vo = __shfl_xor_sync(0xffffffffu, v, 1);
-    if (owner) epilogue_apply(s, p, ra, rb, v, vo, o, pos);
+    if (owner) epilogue_apply<TP>(s, p, ra, rb, v, vo, o, pos);
 }
 
 

@@ -598,6 +598,7 @@ int enqueue_decode(b2_ctx* c, cudaStream_t st, bool pdl) {
         p.trace = c->step_trace;
         p.l2_ahead = c->step_l2_ahead;
         p.fine_op = c->step_fine_op;
+        p.tp = c->tp_local ? c->m->tp_size : 0;
         int rc = c->step_version == 2 ? launch_step2(p, c->step_act, st) : launch_step(p, c->step_act, st);
         if (rc == 0) c->launches_per_step = 1;
         if (rc == 0) rc = sample_single(c, st, true);
@@ -627,7 +628,7 @@ int build_step_program(b2_ctx* c) {
         if (op.kind == OP_GEMV && !step2_supports(act, op.g.K)) c->step_version = 1;
     c->step_l2_ahead = 0;
     if (const char* e = getenv("B2_STEP_L2_AHEAD")) c->step_l2_ahead = atoi(e) < 0 ? 0 : atoi(e);
-    const int grid = c->step_version == 2 ? step2_grid_size(act, max_k) : step_grid_size(act, max_k);
+    const int grid = c->step_version == 2 ? step2_grid_size(act, max_k, c->tp_local != nullptr) : step_grid_size(act, max_k);
     if (grid < 0) return grid;
     if (grid > 1024) {
         set_error("step kernel: grid of %d CTAs exceeds the argmax scratch", grid);

@@ -89,6 +89,7 @@ struct Engine {
     // counters behind GET /metrics (Prometheus text; llama.cpp's metric names where it has one)
     std::atomic<uint64_t> m_requests{0}, m_prompt_tokens{0}, m_prompt_reused{0}, m_predicted{0}, m_passes{0}, m_pass_cols{0};
     std::atomic<int> m_processing{0}, m_deferred{0};
+    std::atomic<uint64_t> m_host_sampled{0}, m_dev_sampler_requests{0};   // tokens drawn on the host from copied logits; requests whose slot draws on the device
     int max_cols = 32;      // widest batch per pass (b2_ctx_max_batch: 32 on the int8 kernel, 256 on the tcgen05 pass)
     bool tc_prefill = false;   // long prompts go through b2_ctx_prefill (whole chunks on the tensor-core prompt path)
 
@@ -130,6 +131,7 @@ struct Engine {
     }
 
     int32_t sample(const GenParams& p, std::mt19937_64& rng) {
+        m_host_sampled++;
         const int V = info.vocab;
         std::vector<std::pair<float, int32_t>> c(V);
         for (int i = 0; i < V; i++) c[i] = {logits[i], i};
@@ -308,7 +310,7 @@ struct Engine {
                 if (!j->greedy) {
                     const b2_sampling sp{j->p.temperature, j->p.top_p > 0.0f && j->p.top_p <= 1.0f ? j->p.top_p : 1.0f,
                                          j->p.min_p < 0.0f ? 0.0f : (j->p.min_p > 1.0f ? 1.0f : j->p.min_p), j->p.top_k, j->seed_used};
-                    if (b2_ctx_set_sampler(ctx, best, &sp) == 0) { j->greedy = true; slot_samples[best] = 1; }
+                    if (b2_ctx_set_sampler(ctx, best, &sp) == 0) { j->greedy = true; slot_samples[best] = 1; m_dev_sampler_requests++; }
                 } else if (slot_samples[best]) {
                     b2_ctx_set_sampler(ctx, best, nullptr);
                     slot_samples[best] = 0;

@@ -331,7 +331,7 @@ bool handle(int fd, const Request& rq, bool keep_alive) {
     if (path == "/metrics") {
         // Prometheus text format; llama.cpp's server exports the same names behind --metrics
         if (rq.method != "GET") return respond(fd, rq, 405, "application/json", error_json(405, "use GET", "invalid_request_error"), keep_alive);
-        char buf[2048];
+        char buf[3072];
         const unsigned long long passes = E.m_passes.load(), cols = E.m_pass_cols.load();
         snprintf(buf, sizeof buf,
                  "# HELP llamacpp:prompt_tokens_total Number of prompt tokens processed.\n# TYPE llamacpp:prompt_tokens_total counter\n"
@@ -348,9 +348,14 @@ bool handle(int fd, const Request& rq, bool keep_alive) {
                  "# HELP b2:batch_passes_total Batched passes over the weights.\n# TYPE b2:batch_passes_total counter\nb2:batch_passes_total %llu\n"
                  "# HELP b2:batch_columns_total Columns (tokens) in those passes.\n# TYPE b2:batch_columns_total counter\nb2:batch_columns_total %llu\n"
                  "# HELP b2:slots Sequence slots of the context.\n# TYPE b2:slots gauge\nb2:slots %d\n"
-                 "# HELP b2:max_batch_columns Widest batch per pass.\n# TYPE b2:max_batch_columns gauge\nb2:max_batch_columns %d\n",
+                 "# HELP b2:max_batch_columns Widest batch per pass.\n# TYPE b2:max_batch_columns gauge\nb2:max_batch_columns %d\n"
+                 "# HELP b2:device_sampled_requests_total Requests whose tokens are drawn on the GPU.\n# TYPE b2:device_sampled_requests_total counter\n"
+                 "b2:device_sampled_requests_total %llu\n"
+                 "# HELP b2:host_sampled_tokens_total Tokens drawn on the host from a copied logits row.\n# TYPE b2:host_sampled_tokens_total counter\n"
+                 "b2:host_sampled_tokens_total %llu\n",
                  (unsigned long long)E.m_prompt_tokens.load(), (unsigned long long)E.m_predicted.load(), E.m_processing.load(), E.m_deferred.load(),
-                 (unsigned long long)E.m_requests.load(), (unsigned long long)E.m_prompt_reused.load(), passes, cols, E.n_slots, E.max_cols);
+                 (unsigned long long)E.m_requests.load(), (unsigned long long)E.m_prompt_reused.load(), passes, cols, E.n_slots, E.max_cols,
+                 (unsigned long long)E.m_dev_sampler_requests.load(), (unsigned long long)E.m_host_sampled.load());
         return respond(fd, rq, 200, "text/plain; version=0.0.4", buf, keep_alive);
     }
     const bool chat = path == "/v1/chat/completions" || path == "/chat/completions";

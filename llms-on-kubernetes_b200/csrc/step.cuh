@@ -52,6 +52,8 @@ struct StepProgram {
     // B2_STEP_FINE=<stage index>: per ring step of that stage, CTA 0 stamps {wait begin, data there, step done, copy issued}
     // into trace[n_ops * STEP_TRACE_SLOTS + 4 k ..] (STEP_FINE_STEPS steps at most); -1 = off
     int fine_op;
+    // ranks of the tensor-parallel group this program exchanges with (0: one GPU; selects the kernel instantiation)
+    int tp;
 };
 
 // tokens one CTA handles per attention work item: chosen per step from the sequence length so that the
@@ -70,7 +72,7 @@ int step_grid_size(int act, int max_k);
 int launch_step(const StepProgram& p, int act, cudaStream_t st);
 // second design (step2.cu, the default; B2_STEP_V=1 keeps the first): needs every mat-vec K to be a multiple of 256
 bool step2_supports(int act, int K);
-int step2_grid_size(int act, int max_k);
+int step2_grid_size(int act, int max_k, bool tp);
 int launch_step2(const StepProgram& p, int act, cudaStream_t st);
 
 }  // namespace b2

@@ -137,7 +137,9 @@ __device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int 
 
 constexpr size_t STEP2_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 32 * sizeof(int) + 16;
 
-template <int ACT>
+// TP: the instantiation a tensor-parallel shard runs (partial residual rows stored to the peers, inputs summed over the
+// ranks); the single-GPU instantiation carries none of it
+template <int ACT, bool TP>
 __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_constant__ StepProgram P) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint8_t* ring = smem;
@@ -272,13 +274,13 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, parity ^= 1) {
                 while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
                 const GemvSeg& s = a.seg[si];
-                epilogue_tile(a, s, tile - s.tile0, pos, red + parity * NCW * TILE_ROWS, &part_full[parity], &part_free[parity],
+                epilogue_tile<TP>(a, s, tile - s.tile0, pos, red + parity * NCW * TILE_ROWS, &part_full[parity], &part_free[parity],
                               (ph >> parity) & 1, lane);
                 ph ^= 1 << parity;
             }
             // a fence orders only the calling thread's stores: every lane that wrote results fences, then one arrives
             // (system scope when the rows went into the other ranks' memory)
-            if (a.seg[0].n_peer > 0) __threadfence_system();
+            if (TP && a.seg[0].n_peer > 0) __threadfence_system();
             else __threadfence();
             __syncwarp();
             if (lane == 0) {
@@ -333,9 +335,9 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
             sm.xd = (float*)(sm.xq + K);
             sm.bs16 = (int16_t*)(sm.xd + (ACT == ACT_Q8K ? K / 256 : K / 32));
             sm.bs32 = sm.bs16 + K / 16;
-            if (a.x_nparts > 0) xchg_wait(a, tid);   // tensor-parallel shard: the ranks' partial residual streams have arrived
-            build_activation<ACT>(a, sm, smem, tid, rank, csize, xpar, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
-            if (a.x_nparts > 0) xchg_materialise(a, tid);
+            if (TP && a.x_nparts > 0) xchg_wait(a, tid);   // tensor-parallel shard: the ranks' partial residual streams have arrived
+            build_activation<ACT, TP>(a, sm, smem, tid, rank, csize, xpar, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
+            if (TP && a.x_nparts > 0) xchg_materialise(a, tid);
             if (tid == 0) stamp(P, oi, 1);
             xpar ^= 1;
             const ActView xv{sm.xq, sm.xd, sm.bs16, sm.bs32};
@@ -393,7 +395,13 @@ size_t step2_smem_bytes(int act, int max_k) {
     return (n + 127) & ~(size_t)127;
 }
 
-int step2_config(int act, int max_k, size_t* smem_out, int* cluster_out, int* grid_out) {
+using Step2Kernel = void (*)(const StepProgram);
+Step2Kernel step2_entry(int act, bool tp) {
+    if (tp) return act == ACT_Q8K ? step2_kernel<ACT_Q8K, true> : step2_kernel<ACT_Q80, true>;
+    return act == ACT_Q8K ? step2_kernel<ACT_Q8K, false> : step2_kernel<ACT_Q80, false>;
+}
+
+int step2_config(int act, bool tp, int max_k, size_t* smem_out, int* cluster_out, int* grid_out) {
     const int sms = device_sm_count();
     if (sms <= 0) return B2_ECUDA;
     const size_t smem = step2_smem_bytes(act, max_k);
@@ -401,7 +409,7 @@ int step2_config(int act, int max_k, size_t* smem_out, int* cluster_out, int* gr
         set_error("step kernel: K=%d needs %zu bytes of shared memory", max_k, smem);
         return B2_ERANGE;
     }
-    auto kern = act == ACT_Q8K ? step2_kernel<ACT_Q8K> : step2_kernel<ACT_Q80>;
+    auto kern = step2_entry(act, tp);
     B2_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int ctas_per_sm = (int)((228 * 1024) / (smem + 1024));
     if (ctas_per_sm > 2) ctas_per_sm = 2;
@@ -444,20 +452,20 @@ bool step2_supports(int act, int K) {
     return K > 0 && (K & 255) == 0;
 }
 
-int step2_grid_size(int act, int max_k) {
+int step2_grid_size(int act, int max_k, bool tp) {
     size_t smem;
     int cluster, grid;
-    const int rc = step2_config(act, max_k, &smem, &cluster, &grid);
+    const int rc = step2_config(act, tp, max_k, &smem, &cluster, &grid);
     return rc ? rc : grid;
 }
 
 int launch_step2(const StepProgram& p, int act, cudaStream_t st) {
     size_t smem;
     int cluster, grid;
-    int rc = step2_config(act, p.max_k, &smem, &cluster, &grid);
+    int rc = step2_config(act, p.tp > 0, p.max_k, &smem, &cluster, &grid);
     if (rc) return rc;
     B2_CUDA_CHECK(cudaMemsetAsync(p.sync_counter, 0, STEP_SYNC_BYTES, st));
-    auto kern = act == ACT_Q8K ? step2_kernel<ACT_Q8K> : step2_kernel<ACT_Q80>;
+    auto kern = step2_entry(act, p.tp > 0);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(STEP2_THREADS);

@@ -80,14 +80,14 @@ def test_default_pool_is_statically_mapped(b2, tiny_models):
 
 def test_position_beyond_an_unwritten_page_is_refused(b2, tiny_models, monkeypatch):
     """On an on-demand pool a pass maps only the page of the position it writes; attention then walks every page below
-    it.  Decoding at position 600 of an empty slot must be turned away on the host (B2_ERANGE), not read page -1."""
+    it.  Decoding at position 300 of an empty slot must be turned away on the host (B2_ERANGE), not read page -1."""
     monkeypatch.setenv("B2_KV_POOL_TOKENS", str(6 * 256))
     m = b2.Model(tiny_models["tiny-llama-q4_k_m"])
-    ctx = b2.Context(m, 1024, n_slots=3)
+    ctx = b2.Context(m, 512, n_slots=4)                              # the model's trained context is 512: 2 pages per slot
     assert ctx.kv_pages()[3]
     free_before = ctx.kv_pages()[1]
     with pytest.raises(b2.B2Error) as e:
-        ctx.decode_batch([5], [600], slots=[1])
+        ctx.decode_batch([5], [300], slots=[1])
     assert e.value.code == -6 and "never written" in str(e.value)
     with pytest.raises(b2.B2Error):
         ctx.prefill([5, 6, 7], slot=2, pos0=300)
