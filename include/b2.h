@@ -228,7 +228,12 @@ const b2_gguf* b2_model_gguf(const b2_model* m);
 /* device pointer + info of a named tensor (for tests that check the upload is byte-identical) */
 int b2_model_tensor(const b2_model* m, const char* name, const void** dev_ptr, b2_tensor_info* info);
 
-/* n_ctx: KV-cache capacity in tokens (0 = min(model training context, 8192)). */
+/* n_ctx: KV-cache capacity in tokens (0 = min(model training context, 8192)).
+ * One DECODING context per GPU at a time: the per-token kernel is persistent (a grid barrier between its stages), all
+ * of its CTAs must be resident together (two per SM).  Another context decoding concurrently on the same GPU -- a second
+ * process under MPS, or an overlapping stream of this process -- can keep CTAs off the SMs; every wait in the kernel is
+ * bounded, so the call then fails with B2_ECUDA instead of hanging, but the step is lost.  Contexts whose calls do not
+ * overlap may share a GPU. */
 int b2_ctx_create(b2_model* m, int n_ctx, b2_ctx** out);
 void b2_ctx_free(b2_ctx* c);
 int b2_ctx_n_ctx(const b2_ctx* c);

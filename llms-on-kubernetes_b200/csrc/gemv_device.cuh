@@ -325,28 +325,34 @@ __device__ __forceinline__ void quantise_span(const float (&v)[8], int base, int
     // the 16-bit sums travel in pairs (asynchronous stores are 4 bytes at least): sums of 16 of lanes l, l+2; sums of 32 of lanes l, l+4
     const uint32_t p16 = ((uint32_t)s16 & 0xffffu) | ((uint32_t)__shfl_down_sync(0xffffffffu, s16, 2) << 16);
     const uint32_t p32 = ((uint32_t)s32 & 0xffffu) | ((uint32_t)__shfl_down_sync(0xffffffffu, s32, 4) << 16);
+    const uint32_t p32n = __shfl_up_sync(0xffffffffu, p32, 1);
     if (i0 < K) {
         const int qpos = ACT == ACT_Q8K ? base + 16 * xswz(lane >> 1) + 8 * (lane & 1) : i0;
         const uint32_t o_q = (uint32_t)((const uint8_t*)(sm.xq + qpos) - smem_base);
         const uint32_t o_d = (uint32_t)((const uint8_t*)(sm.xd + (ACT == ACT_Q8K ? (base >> 8) : (i0 >> 5))) - smem_base);
         const uint32_t o_16 = (uint32_t)((const uint8_t*)(sm.bs16 + (i0 >> 4)) - smem_base);
-        const uint32_t o_32 = (uint32_t)((const uint8_t*)(sm.bs32 + (i0 >> 5)) - smem_base);
+        const uint32_t o_32n = (uint32_t)((const uint8_t*)(sm.bs32 + ((i0 - 8) >> 5)) - smem_base);   // of the lane below (lanes 1, 9, ..)
         const uint32_t o_bar = (uint32_t)((const uint8_t*)sm.xbar - smem_base);
         // every byte is reported to the receiving CTA's barrier (activation_bytes() of them complete its phase);
         // straight-line, predicated stores: this runs on the critical path of every stage hand-off
-        const bool q4 = (lane & 3) == 0, q8 = (lane & 7) == 0, q32 = lane == 0;
+        // (an asynchronous store costs the warp ~90 cycles of issue whatever its lanes carry: the three small items
+        // of a Q8_K span share one instruction -- lanes 0, 4, .. the 16-sums, lanes 1, 9, .. the 32-sums of the
+        // lane below, lane 2 the scale)
+        const bool q4 = (lane & 3) == 0;
+        uint32_t o_side = o_16, v_side = p16;
+        bool side = q4;
+        if (ACT == ACT_Q8K) {
+            if ((lane & 7) == 1) { o_side = o_32n; v_side = p32n; side = true; }
+            if (lane == 2) { o_side = o_d; v_side = __float_as_uint(d); side = true; }
+        } else {
+            o_side = o_d; v_side = __float_as_uint(d);
+        }
 #pragma unroll 4
         for (uint32_t r = 0; r < csize; r++) {
             const uint32_t pb = dsmem_addr(smem_base, r);
             const uint32_t bar = pb + o_bar;
             dsmem_st_async_v2(pb + o_q, pk0, pk1, bar);
-            if (ACT == ACT_Q8K) {
-                dsmem_st_async_b32_if(q4, pb + o_16, p16, bar);
-                dsmem_st_async_b32_if(q8, pb + o_32, p32, bar);
-                dsmem_st_async_b32_if(q32, pb + o_d, __float_as_uint(d), bar);
-            } else {
-                dsmem_st_async_b32_if(q4, pb + o_d, __float_as_uint(d), bar);
-            }
+            dsmem_st_async_b32_if(side, pb + o_side, v_side, bar);
         }
     }
 }
@@ -360,11 +366,63 @@ __device__ __forceinline__ uint32_t activation_bytes(int K) {
 // parity: phase of xbar to wait for (0 for a kernel that builds one activation vector).
 // Called by all NCT compute threads (uses named barrier 1).
 // TP = false compiles the tensor-parallel input (x_parts) out: the single-GPU step kernel keeps its registers.
-template <int ACT, bool TP = true>
+// DEFER (Q8_K activations only): the RMS factor r is a scalar, so it commutes with the quantiser -- q(x r w) = q(x w) and
+// d(x r w) = r d(x w) up to fp32 rounding -- and with the whole mat-vec: y = r * sum_b d_w d_x' (q_w . q_x).  The spans are
+// then quantised from x * w as soon as they arrive, the sum of squares is added up by the warps that own no span (or
+// afterwards) while the exchange is in flight, and r goes to *scale_out for the epilogue warp to apply to the row sums.
+template <int ACT, bool TP = true, bool DEFER = false>
 __device__ __forceinline__ void build_activation(const GemvArgs& a, const ActSmem& sm, const uint8_t* smem_base, int tid, uint32_t rank, uint32_t csize,
-                                 uint32_t parity = 0, unsigned long long* tr = nullptr) {
+                                 uint32_t parity = 0, unsigned long long* tr = nullptr, float* scale_out = nullptr) {
     const int K = a.K;
     const int lane = tid & 31, warp = tid >> 5;
+    if (DEFER && ACT == ACT_Q8K && !(TP && a.x_nparts > 0) && a.prologue == PRO_NORM) {
+        const int nspans = (K + 255) >> 8;
+        const int first = (int)rank + (int)csize * warp, stride = (int)csize * NCW;
+        // warps with a span quantise; when at least half of the warps have none, those add up the squares meanwhile
+        const int owners = min(NCW, (nspans - (int)rank + (int)csize - 1) / (int)csize);   // warps 0 .. owners-1 own a span
+        const bool split = owners <= NCW / 2;
+        double ss = 0.0;
+        auto add_squares = [&](int t0, int nt) {
+#pragma unroll 4
+            for (int i0 = t0 * 8; i0 < K; i0 += nt * 8) {
+                float t[8];
+                load8(a.x, i0, K, t);
+#pragma unroll
+                for (int i = 0; i < 8; i++) ss += (double)(t[i] * t[i]);
+            }
+        };
+        if (split && warp >= owners) {
+            add_squares(tid - owners * 32, (NCW - owners) * 32);
+        } else {
+            for (int s0 = first; s0 < nspans; s0 += stride) {
+                float t[8], w[8];
+                load8(a.x, (s0 << 8) + lane * 8, K, t);
+                load8(a.norm_w, (s0 << 8) + lane * 8, K, w);
+#pragma unroll
+                for (int i = 0; i < 8; i++) t[i] *= w[i];
+                quantise_span<ACT>(t, s0 << 8, lane, K, sm, smem_base, csize);
+            }
+            if (!split) add_squares(tid, NCT);
+        }
+        // the exchange's byte count does not wait for the norm: announce it, then finish the sum while the stores land
+        if (tid == 0) mbar_arrive_expect_tx(sm.xbar, activation_bytes<ACT>(K));
+        if (tr && tid == 0) tr[4] = trace_ns();
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+        if (lane == 0) sm.ss_warp[warp] = ss;
+        named_bar_sync(1, NCT);
+        if (tid == 0) {
+            double tot = 0.0;
+#pragma unroll
+            for (int w = 0; w < NCW; w++) tot += sm.ss_warp[w];
+            const float mean = (float)(tot / (double)K);
+            *scale_out = 1.0f / sqrtf(mean + a.eps);
+            if (tr) tr[5] = trace_ns();
+        }
+        mbar_wait(sm.xbar, parity);
+        if (tr && tid == 0) tr[6] = trace_ns();
+        return;
+    }
     // (a tensor-parallel shard reads the sum of the ranks' partial vectors instead of x)
 #define LOADX(i0, KK, vv) do { if (TP && a.x_nparts > 0) load8_parts(a.x_parts, a.x_nparts, i0, KK, vv); else load8(a.x, i0, KK, vv); } while (0)
     const int nspans = (K + 255) >> 8;
@@ -541,7 +599,8 @@ __device__ __forceinline__ void epilogue_apply(const GemvSeg& s, int p, int ra, 
 // compute warps' shares, add them in a fixed order, release the buffer, finish the pair.
 template <bool TP = true>
 __device__ __forceinline__ void epilogue_tile(const GemvArgs& a, const GemvSeg& s, int ptile, int pos, const float* rp,
-                                              uint64_t* part_full, uint64_t* part_free, uint32_t full_phase, int lane) {
+                                              uint64_t* part_full, uint64_t* part_free, uint32_t full_phase, int lane,
+                                              const float* row_scale = nullptr) {
     const int p = ptile * GEMV_TILE_PAIRS + (lane >> 1);
     const bool owner = lane < TILE_ROWS && (lane & 1) == 0 && p < s.n_pairs;
     int ra = 0, rb = -1;
@@ -555,6 +614,7 @@ __device__ __forceinline__ void epilogue_tile(const GemvArgs& a, const GemvSeg& 
     if (lane < TILE_ROWS) {
 #pragma unroll
         for (int w = 0; w < NCW; w++) v += rp[w * TILE_ROWS + lane];
+        if (row_scale) v *= *row_scale;   // the RMS factor of a normalising stage whose prologue deferred it (build_activation DEFER)
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(part_free);

@@ -747,6 +747,21 @@ void dump_step_trace(b2_ctx* c) {
                 first = std::min(first, f[1024 + b]); last = std::max(last, f[1024 + b]);
                 if (f[2048 + b]) { pfirst = std::min(pfirst, f[2048 + b]); plast = std::max(plast, f[2048 + b]); }
             }
+            if (n) {
+                // deciles of both distributions (ns after the first arrival / after the last arrival)
+                std::vector<long long> arr, det;
+                for (int b = 0; b < n; b++) {
+                    arr.push_back((long long)(f[1024 + b] - first));
+                    if (f[2048 + b]) det.push_back((long long)f[2048 + b] - (long long)last);
+                }
+                std::sort(arr.begin(), arr.end());
+                std::sort(det.begin(), det.end());
+                fprintf(stderr, "b2 step trace, stage %d barrier, arrival deciles:", c->step_fine_op);
+                for (int q = 0; q <= 10; q++) fprintf(stderr, " %lld", arr[(size_t)q * (arr.size() - 1) / 10]);
+                fprintf(stderr, "\nb2 step trace, stage %d barrier, seen-complete deciles:", c->step_fine_op);
+                for (int q = 0; q <= 10 && !det.empty(); q++) fprintf(stderr, " %lld", det[(size_t)q * (det.size() - 1) / 10]);
+                fprintf(stderr, "\n");
+            }
             if (n)
                 fprintf(stderr, "b2 step trace, stage %d barrier: %d CTAs arrive over %lld ns (CTA 0 at +%lld); the barrier is seen complete %lld .. %lld ns after the last arrival\n",
                         c->step_fine_op, n, (long long)(last - first), (long long)(f[1024] - first), (long long)(pfirst - last), (long long)(plast - last));

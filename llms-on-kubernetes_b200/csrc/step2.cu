@@ -137,6 +137,12 @@ __device__ __forceinline__ void segment_tiles2(const GemvSeg& s, int& tile, int 
 
 constexpr size_t STEP2_EXTRA_SMEM = 3 * sizeof(GemvArgs) + 2 * sizeof(StepOp) + 32 * sizeof(int) + 16;
 
+// does this stage's prologue leave the RMS factor to the epilogue warp?  (the condition of build_activation's DEFER branch)
+template <int ACT, bool TP>
+__device__ __forceinline__ bool deferred_scale_of(const GemvArgs& a) {
+    return ACT == ACT_Q8K && a.prologue == PRO_NORM && !(TP && a.x_nparts > 0);
+}
+
 // TP: the instantiation a tensor-parallel shard runs (partial residual rows stored to the peers, inputs summed over the
 // ranks); the single-GPU instantiation carries none of it
 template <int ACT, bool TP>
@@ -177,6 +183,7 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
     }
     cluster_sync_all();
     volatile unsigned int* cta_stage = (volatile unsigned int*)&ss.aux[2];
+    float* rms_scale = (float*)&ss.aux[28];   // RMS factor of the current normalising stage (written by the prologue, applied by the epilogue warp)
 
     if (warp == W_PROD) {
         // ===== producer: streams every mat-vec stage's weights in program order, never waits for a stage to start.
@@ -275,7 +282,7 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
                 while (si + 1 < a.n_seg && tile >= a.seg[si + 1].tile0) si++;
                 const GemvSeg& s = a.seg[si];
                 epilogue_tile<TP>(a, s, tile - s.tile0, pos, red + parity * NCW * TILE_ROWS, &part_full[parity], &part_free[parity],
-                              (ph >> parity) & 1, lane);
+                              (ph >> parity) & 1, lane, deferred_scale_of<ACT, TP>(a) ? rms_scale : nullptr);
                 ph ^= 1 << parity;
             }
             // a fence orders only the calling thread's stores: every lane that wrote results fences, then one arrives
@@ -336,7 +343,8 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
             sm.bs16 = (int16_t*)(sm.xd + (ACT == ACT_Q8K ? K / 256 : K / 32));
             sm.bs32 = sm.bs16 + K / 16;
             if (TP && a.x_nparts > 0) xchg_wait(a, tid);   // tensor-parallel shard: the ranks' partial residual streams have arrived
-            build_activation<ACT, TP>(a, sm, smem, tid, rank, csize, xpar, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
+            build_activation<ACT, TP, true>(a, sm, smem, tid, rank, csize, xpar, (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr,
+                                            rms_scale);
             if (TP && a.x_nparts > 0) xchg_materialise(a, tid);
             if (tid == 0) stamp(P, oi, 1);
             xpar ^= 1;
