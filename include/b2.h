@@ -149,6 +149,16 @@ size_t b2_tc_gemm_scratch_bytes(int64_t N, int64_t K, int T);
 int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int T, int accumulate, void* scratch_dev,
                void* stream);
 
+/* The same product for a decode batch (T <= 128 rows) with the dequantisation FUSED into the kernel's producer: the
+ * quantised blocks go HBM -> TMA -> shared memory as they are, dequantising warps write the fp16 tiles tcgen05.mma
+ * reads, so W crosses HBM once per call in its 4.5 / 6.56-bit form and no fp16 copy of it exists (row a12 with
+ * 2 <= n_tokens <= 128; north_star "dequant fused into the TMA -> smem -> tcgen05 producer").  Same operand values as
+ * b2_tc_gemm, so the results differ only by fp32 summation order.  Q4_K with K a multiple of 256, Q6_K with K a multiple
+ * of 2048 (rows of 210-byte blocks then keep the 16-byte stride a tensor map needs), N a multiple of 4; B2_EUNSUP otherwise.  scratch_dev: b2_tcq_gemm_scratch_bytes(N, K, T) bytes, 256-byte aligned. */
+size_t b2_tcq_gemm_scratch_bytes(int64_t N, int64_t K, int T);
+int b2_tcq_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int T, int accumulate, void* scratch_dev,
+                void* stream);
+
 /* y = x * rsqrt(mean(x^2) + eps) * w  over rows of length n   (row a11, ggml rms_norm + mul) */
 int b2_rmsnorm(const float* x_dev, const float* w_dev, float* y_dev, int64_t n, int64_t rows, float eps, void* stream);
 

@@ -86,6 +86,8 @@ SYMBOLS = {
     "b2_gemm": (_I, [_I, _P, _P, _P, _I64, _I64, _I, _P, _P]),
     "b2_tc_gemm_scratch_bytes": (_SZ, [_I64, _I64, _I]),
     "b2_tc_gemm": (_I, [_I, _P, _P, _P, _I64, _I64, _I, _I, _P, _P]),
+    "b2_tcq_gemm_scratch_bytes": (_SZ, [_I64, _I64, _I]),
+    "b2_tcq_gemm": (_I, [_I, _P, _P, _P, _I64, _I64, _I, _I, _P, _P]),
     "b2_rmsnorm": (_I, [_P, _P, _P, _I64, _I64, C.c_float, _P]),
     "b2_rope": (_I, [_P, _I, _I, _I, _I, _I, C.c_float, _P, _P]),
     "b2_attn_scratch_bytes": (_SZ, [_I, _I, _I]),
@@ -257,6 +259,19 @@ def tc_gemm(qtype: int, W: np.ndarray, x: np.ndarray, N: int, K: int, y0: np.nda
     dy = DevBuf(4 * N * T) if y0 is None else DevBuf.from_numpy(np.ascontiguousarray(y0, np.float32))
     scratch = DevBuf(lib.b2_tc_gemm_scratch_bytes(N, K, T))
     check(lib.b2_tc_gemm(qtype, dW.ptr, dx.ptr, dy.ptr, N, K, T, 0 if y0 is None else 1, scratch.ptr, None))
+    check(lib.b2_stream_sync(None))
+    return dy.to_numpy(np.float32).reshape(T, N)
+
+
+def tcq_gemm(qtype: int, W: np.ndarray, x: np.ndarray, N: int, K: int, y0: np.ndarray | None = None) -> np.ndarray:
+    """Y[T, N] (= y0 +) X[T, K] . W^T for a decode batch: quantised blocks dequantised inside the tcgen05 kernel's producer."""
+    x = np.ascontiguousarray(x, np.float32)
+    assert x.ndim == 2
+    T = x.shape[0]
+    dW, dx = DevBuf.from_numpy(np.ascontiguousarray(W, np.uint8)), DevBuf.from_numpy(x)
+    dy = DevBuf(4 * N * T) if y0 is None else DevBuf.from_numpy(np.ascontiguousarray(y0, np.float32))
+    scratch = DevBuf(lib.b2_tcq_gemm_scratch_bytes(N, K, T))
+    check(lib.b2_tcq_gemm(qtype, dW.ptr, dx.ptr, dy.ptr, N, K, T, 0 if y0 is None else 1, scratch.ptr, None))
     check(lib.b2_stream_sync(None))
     return dy.to_numpy(np.float32).reshape(T, N)
 

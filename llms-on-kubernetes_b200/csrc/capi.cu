@@ -9,6 +9,7 @@
 #include "gguf.h"
 #include "ops.h"
 #include "tc_gemm.cuh"
+#include "tcq_gemm.cuh"
 
 using namespace b2;
 
@@ -259,6 +260,40 @@ int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, in
     a.ldo = N;
     a.epi = accumulate ? TC_EPI_ADD : TC_EPI_STORE;
     return launch_tc_gemm(a, (cudaStream_t)stream);
+}
+
+size_t b2_tcq_gemm_scratch_bytes(int64_t N, int64_t K, int T) {
+    if (N <= 0 || K <= 0 || T <= 0) return 0;
+    return ((size_t)T * K * 2 + 255) / 256 * 256 + tcq_ws_bytes((int)N, (int)K, T);
+}
+
+int b2_tcq_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, int64_t N, int64_t K, int T, int accumulate, void* scratch_dev,
+                void* stream) {
+    if (!W_dev || !x_dev || !y_dev || !scratch_dev || N <= 0 || K <= 0 || T <= 0 || N > 0x3fffffff || K > 0x3fffffff || N % 4 ||
+        ((uintptr_t)scratch_dev & 255)) {
+        set_error("b2_tcq_gemm: bad arguments (N=%lld K=%lld T=%d; N a multiple of 4, scratch 256-byte aligned)", (long long)N, (long long)K, T);
+        return B2_EINVAL;
+    }
+    if (!tcq_supported(type, (int)K) || T > TCQ_MAX_T) {
+        set_error("b2_tcq_gemm: type %d, K=%lld, T=%d is outside the fused path (Q4_K / Q6_K, K a multiple of 256, T <= %d)", type, (long long)K, T,
+                  TCQ_MAX_T);
+        return B2_EUNSUP;
+    }
+    __half* xb = (__half*)scratch_dev;
+    float* ws = (float*)((uint8_t*)scratch_dev + ((size_t)T * K * 2 + 255) / 256 * 256);
+    int rc;
+    if ((rc = launch_rows_to_f16(const_cast<float*>(x_dev), K, nullptr, 0.0f, (int)K, T, ACT_Q8K, xb, (cudaStream_t)stream))) return rc;
+    TcqGemmArgs a{};
+    a.seg[0] = TcqSeg{W_dev, type, (int)N};
+    a.n_seg = 1;
+    a.x = xb;
+    a.K = (int)K;
+    a.T = T;
+    a.ws = ws;
+    a.ws_bytes = tcq_ws_bytes((int)N, (int)K, T);
+    TcParts parts;
+    if ((rc = launch_tcq_gemm(a, (cudaStream_t)stream, &parts))) return rc;
+    return launch_tcq_reduce(parts, T, (int)N, y_dev, N, nullptr, accumulate ? TC_EPI_ADD : TC_EPI_STORE, (cudaStream_t)stream);
 }
 
 int b2_rmsnorm(const float* x_dev, const float* w_dev, float* y_dev, int64_t n, int64_t rows, float eps, void* stream) {

@@ -1,0 +1,45 @@
+// tcq_gemm.cuh -- mat-mul of QUANTISED weights on the 5th-generation tensor cores with the dequantisation fused
+// into the producer (tcq_gemm.cu): raw GGUF blocks -> TMA -> shared memory -> dequantising warps -> 128-byte-swizzled
+// fp16 tiles in shared memory -> tcgen05.mma -> tensor memory.
+//
+// Y[T][N] = X[T][K] . W[N][K]^T for T of a decode batch (2 .. 128 rows; SURVEY 8a row a12 with n_tokens = T), W a stack
+// of up to three GGUF tensors of types Q4_K / Q6_K (the Q | K | V or gate | up matrices of a layer), read from HBM once
+// per pass in their quantised form.  The values the tensor cores see are the ones tc_gemm.cu's resident fp16 copy
+// holds (ggml's dequantised value rounded once to fp16), so both paths give the same sums.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "tc_gemm.cuh"
+
+namespace b2 {
+
+constexpr int TCQ_MAX_SEGS = 3;
+constexpr int TCQ_MAX_T = 128;
+
+struct TcqSeg {
+    const void* w;   // [rows][K] blocks of `type`
+    int type;        // B2_TYPE_Q4_K or B2_TYPE_Q6_K
+    int rows;
+};
+
+struct TcqGemmArgs {
+    TcqSeg seg[TCQ_MAX_SEGS];   // stacked along N in this order
+    int n_seg;
+    const __half* x;            // [T][K] activations (launch_rows_to_f16 / launch_swiglu_to_f16)
+    int K, T;
+    // The result is always left as slices: out(t, n) = sum over s < splits of ws[s * T * N + t * N + n] (N = the stacked
+    // rows), to be added up in slice order by the consumer (TcParts) or by tcq_reduce.  Slices a tile does not need hold zeros.
+    float* ws;
+    size_t ws_bytes;
+};
+
+bool tcq_supported(int type, int K);                                // Q4_K: K a multiple of 256; Q6_K: of 2048 (16-byte row stride)
+size_t tcq_ws_bytes(int N, int K, int T);                           // upper bound of the slices' size for this shape
+// runs the mat-mul; *parts describes the slices (splits >= 1)
+int launch_tcq_gemm(const TcqGemmArgs& a, cudaStream_t st, TcParts* parts);
+// out[t * ldo + n] (+)= sum of the slices (+ bias[n]): for outputs no consumer kernel adds up itself
+int launch_tcq_reduce(const TcParts& parts, int T, int N, float* out, int64_t ldo, const float* bias, int epi, cudaStream_t st);
+
+}  // namespace b2
