@@ -32,6 +32,7 @@
 #include "step.cuh"
 #include "ops.h"
 #include "tc_gemm.cuh"
+#include "tcq_gemm.cuh"
 
 using namespace b2;
 
@@ -953,6 +954,8 @@ int enqueue_logits(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t st
 bool prefill_tc_supported(const b2_model* m);
 int ensure_prefill(b2_ctx* c);
 int tc_min_rows(const b2_model* m);
+int tcq_min_rows();
+bool tcq_pass_ok(const b2_model* m, int T);
 struct PromptSeg { int row0, T, pos0, slot; };   // rows [row0, row0 + T) of a pass = positions [pos0, pos0 + T) of `slot`
 int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0, const int32_t* col_pos, const int32_t* col_slot,
                     cudaStream_t st, const std::vector<PromptSeg>* segs = nullptr);
@@ -962,6 +965,7 @@ int enqueue_logits_tc(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t
 // caller has checked that the pass exists); otherwise from tc_min_rows() columns when the fp16 copy is resident.
 bool batch_uses_tc(const b2_ctx* c, int n) {
     if (n > GEMM_MAX_COLS) return true;
+    if (c->pf.cap && n >= tcq_min_rows() && tcq_pass_ok(c->m, n)) return true;   // raw blocks dequantised inside the tcgen05 kernel
     return c->pf.cap && c->m->f16_cache && n >= tc_min_rows(c->m);
 }
 
@@ -976,7 +980,9 @@ int enqueue_batch(b2_ctx* c, int n, int n_logits, cudaStream_t st) {
         if ((rc = enqueue_tc_pass(c, b.tok, n, 0, 0, b.pos, b.slot, st))) return rc;
         if (n_logits <= 0) return 0;
         const float* rows = c->pf.x + (size_t)(n - n_logits) * I.d_model;
-        return n_logits >= tc_min_rows(m) ? enqueue_logits_tc(c, rows, n_logits, st) : enqueue_logits(c, rows, n_logits, st);
+        const bool lm_tc = (m->f16_cache && n_logits >= tc_min_rows(m)) ||
+                           (n_logits >= tcq_min_rows() && tcq_pass_ok(m, n_logits) && tcq_supported(m->output.type, I.d_model));
+        return lm_tc ? enqueue_logits_tc(c, rows, n_logits, st) : enqueue_logits(c, rows, n_logits, st);
     }
     const int64_t kv_layer = (int64_t)I.n_kv * c->kv_tokens * I.head_dim;
     const int rope_pairing = I.arch == 1 ? PAIR_NEOX : PAIR_ADJ;
@@ -1066,8 +1072,9 @@ int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int3
     int rc;
     if ((rc = ensure_batch(c))) return rc;
     if (n >= 16 && !c->pf.cap && prefill_tc_supported(c->m) && (rc = ensure_prefill(c))) return rc;
-    if (n > GEMM_MAX_COLS && !(c->pf.cap && c->m->f16_cache)) {
-        set_error("b2_ctx_decode_batch: %d columns need the tensor-core pass with a resident fp16 copy of the model (b2_ctx_max_batch)", n);
+    if (n > GEMM_MAX_COLS && !(c->pf.cap && (c->m->f16_cache || tcq_pass_ok(c->m, n)))) {
+        set_error("b2_ctx_decode_batch: %d columns need the tensor-core pass: a resident fp16 copy of the model, or at most 128 columns of Q4_K / "
+                  "Q6_K tensors (b2_ctx_max_batch)", n);
         return B2_EUNSUP;
     }
     for (int j = 0; j < n; j++) {
@@ -1123,6 +1130,38 @@ int tc_min_rows(const b2_model* m) {
     }();
     if (v > 0) return v;
     return m->f16_cache ? 24 : 48;   // with the fp16 copy resident a pass is one HBM sweep: measured faster than the int8 kernel beyond ~20 rows
+}
+
+// Can a pass of T rows run every layer mat-mul on the fused-dequantisation kernel?  (Q4_K / Q6_K tensors with row strides a
+// tensor map accepts; B2_NO_TCQ=1 switches it off)
+bool tcq_model_ok(const b2_model* m) {
+    if (env_flag("B2_NO_TCQ")) return false;
+    const b2_model_info& I = m->info;
+    const int qdim = I.n_head * I.head_dim;
+    for (const auto& L : m->layers) {
+        if (!tcq_supported(L.wq.type, I.d_model) || !tcq_supported(L.wk.type, I.d_model) || !tcq_supported(L.wv.type, I.d_model) ||
+            !tcq_supported(L.wo.type, qdim) || !tcq_supported(L.gate.type, I.d_model) || !tcq_supported(L.up.type, I.d_model) ||
+            !tcq_supported(L.down.type, I.d_ff))
+            return false;
+        if ((L.wq.rows | L.wk.rows | L.wv.rows | L.gate.rows) & 3) return false;   // stacked segments start on multiples of 4 rows
+    }
+    return true;
+}
+// Which passes take it: measured on the 8B shape, the fused kernel beats the int8 kernel from ~24 columns (5.06 vs 5.91 ms
+// at 32) and is within 4 % of the pass over the resident fp16 copy (5.59 vs 5.35 ms at 64 columns) while reading 3.2 x
+// fewer bytes; so by default it serves the models whose fp16 copy is not resident (it does not fit, or B2_NO_F16_CACHE=1)
+// -- those used to dequantise every matrix again per pass -- and B2_TCQ=1 makes it the path of every pass of <= 128 rows.
+bool tcq_pass_ok(const b2_model* m, int T) {
+    const bool force = env_flag("B2_TCQ");   // read per call: the tests switch it inside one process
+    return T <= TCQ_MAX_T && tcq_model_ok(m) && (force || !m->f16_cache);
+}
+// columns from which a decode batch takes the fused tensor-core pass instead of the int8 kernel
+int tcq_min_rows() {
+    static const int v = [] {
+        const char* e = getenv("B2_TCQ_MIN_ROWS");
+        return e ? atoi(e) : 0;
+    }();
+    return v > 0 ? v : 24;
 }
 
 int prefill_tc_chunk(const b2_ctx* c) {
@@ -1226,6 +1265,9 @@ int ensure_prefill(b2_ctx* c) {
     const int shapes[5][2] = {{(int)(qdim + 2 * kvdim), I.d_model}, {I.d_model, (int)qdim}, {2 * I.d_ff, I.d_model}, {I.d_model, I.d_ff}, {I.vocab, I.d_model}};
     for (const auto& s : shapes)
         for (size_t T = 128; T < 2 * cap; T *= 2) p.ws_bytes = std::max(p.ws_bytes, tc_gemm_ws_bytes(s[0], s[1], (int)std::min(T, cap)));
+    if (tcq_model_ok(c->m))
+        for (const auto& s : shapes)
+            if (s[0] % 4 == 0) p.ws_bytes = std::max(p.ws_bytes, tcq_ws_bytes(s[0], s[1], TCQ_MAX_T));
     if (p.ws_bytes) B2_CUDA_CHECK(cudaMalloc(&p.ws, p.ws_bytes));
     p.cap = (int)cap;
     return 0;
@@ -1280,6 +1322,30 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         mark(0);
         return r;
     };
+    // Decode batches (T <= 128 rows): the mat-mul whose producer dequantises the raw blocks (tcq_gemm.cu) -- the quantised
+    // tensors cross HBM once, no fp16 copy is read.  The result is always left as slices; a caller that wants it in `out`
+    // (defer == nullptr) gets a reduction kernel.
+    const bool fused = tcq_pass_ok(m, T);
+    auto mmq = [&](std::initializer_list<const b2_model::W*> ws, int K, float* out, int64_t ldo, int epi, TcParts* defer) {
+        TcqGemmArgs a{};
+        int N = 0;
+        for (const b2_model::W* w : ws) {
+            a.seg[a.n_seg++] = TcqSeg{w->p, w->type, (int)w->rows};
+            N += (int)w->rows;
+        }
+        a.x = xb;
+        a.K = K;
+        a.T = T;
+        a.ws = p.ws;
+        a.ws_bytes = p.ws_bytes;
+        mark(1);
+        TcParts parts;
+        int r = launch_tcq_gemm(a, st, &parts);
+        if (r == 0 && defer) *defer = parts;
+        if (r == 0 && !defer) r = launch_tcq_reduce(parts, T, N, out, ldo, nullptr, epi, st);
+        mark(0);
+        return r;
+    };
     TcParts pend{nullptr, 1, 0};   // residual mat-mul (O, down) whose slices the next norm kernel adds into x
     if ((rc = launch_embed_rows(m->tok_embd.type, m->tok_embd.p, row_bytes(m->tok_embd.type, I.d_model), I.d_model, I.vocab, tok_dev, T, p.x, st))) return rc;
     for (int il = 0; il < I.n_layer; il++) {
@@ -1290,13 +1356,15 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         // RMSNorm -> one mat-mul over the stacked Q | K | V matrices -> bias, RoPE, KV cache
         if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.wq.type), xb, st, pend)))
             return rc;
-        if (!cache) {
+        if (!cache && !fused) {
             if ((rc = dq(L.wq, wb))) return rc;
             if ((rc = dq(L.wk, wb + (size_t)qdim * I.d_model))) return rc;
             if ((rc = dq(L.wv, wb + (size_t)(qdim + kvdim) * I.d_model))) return rc;
         }
         TcParts parts;
-        if ((rc = mm(cache ? cache + m->f16_off[il].qkv : wb, qdim + 2 * kvdim, I.d_model, p.qkv, qdim + 2 * kvdim, TC_EPI_STORE, &parts))) return rc;
+        if (fused) rc = mmq({&L.wq, &L.wk, &L.wv}, I.d_model, p.qkv, qdim + 2 * kvdim, TC_EPI_STORE, &parts);
+        else rc = mm(cache ? cache + m->f16_off[il].qkv : wb, qdim + 2 * kvdim, I.d_model, p.qkv, qdim + 2 * kvdim, TC_EPI_STORE, &parts);
+        if (rc) return rc;
         PrefillQkvArgs qa{};
         qa.qkv = p.qkv;
         qa.parts_ws = parts.ws;
@@ -1339,21 +1407,27 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         mark(2);
         // output projection + residual
         if ((rc = launch_rows_to_f16(p.attn_out, qdim, nullptr, 0.0f, qdim, T, gemm_act_for_type(L.wo.type), xb, st))) return rc;
-        if (!cache && (rc = dq(L.wo, wb))) return rc;
-        if ((rc = mm(cache ? cache + m->f16_off[il].o : wb, I.d_model, qdim, p.x, I.d_model, TC_EPI_ADD, &pend))) return rc;
+        if (!cache && !fused && (rc = dq(L.wo, wb))) return rc;
+        if (fused) rc = mmq({&L.wo}, qdim, p.x, I.d_model, TC_EPI_ADD, &pend);
+        else rc = mm(cache ? cache + m->f16_off[il].o : wb, I.d_model, qdim, p.x, I.d_model, TC_EPI_ADD, &pend);
+        if (rc) return rc;
         // (+ the O slices) RMSNorm -> stacked gate | up -> SwiGLU -> down + residual
         if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.gate.type), xb, st, pend)))
             return rc;
-        if (!cache) {
+        if (!cache && !fused) {
             if ((rc = dq(L.gate, wb))) return rc;
             if ((rc = dq(L.up, wb + (size_t)I.d_ff * I.d_model))) return rc;
         }
-        if ((rc = mm(cache ? cache + m->f16_off[il].gate_up : wb, 2 * I.d_ff, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE, &parts))) return rc;
+        if (fused) rc = mmq({&L.gate, &L.up}, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE, &parts);
+        else rc = mm(cache ? cache + m->f16_off[il].gate_up : wb, 2 * I.d_ff, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE, &parts);
+        if (rc) return rc;
         if ((rc = launch_swiglu_to_f16(p.gu, parts, I.d_ff, T, gemm_act_for_type(L.down.type), xb, il == I.n_layer - 1 ? c->h : nullptr, st))) return rc;
-        if (!cache && (rc = dq(L.down, wb))) return rc;
+        if (!cache && !fused && (rc = dq(L.down, wb))) return rc;
         // the last layer's down projection reduces its own slices: nothing after it in this pass reads x through a norm kernel
         const bool last = il == I.n_layer - 1;
-        if ((rc = mm(cache ? cache + m->f16_off[il].down : wb, I.d_model, I.d_ff, p.x, I.d_model, TC_EPI_ADD, last ? nullptr : &pend))) return rc;
+        if (fused) rc = mmq({&L.down}, I.d_ff, p.x, I.d_model, TC_EPI_ADD, last ? nullptr : &pend);
+        else rc = mm(cache ? cache + m->f16_off[il].down : wb, I.d_model, I.d_ff, p.x, I.d_model, TC_EPI_ADD, last ? nullptr : &pend);
+        if (rc) return rc;
     }
     if (trace && ev.size() > 1) {
         cudaStreamSynchronize(st);
@@ -1407,6 +1481,23 @@ int enqueue_logits_tc(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t
     if ((rc = launch_rows_to_f16(const_cast<float*>(x_rows), I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits,
                                  gemm_act_for_type(m->output.type), xb, st)))
         return rc;
+    const bool no_tcq = env_flag("B2_NO_TCQ") || (m->f16_cache && !env_flag("B2_TCQ"));
+    if (!no_tcq && n_logits <= TCQ_MAX_T && tcq_supported(m->output.type, I.d_model) && I.vocab % 4 == 0 &&
+        tcq_ws_bytes(I.vocab, I.d_model, n_logits) <= c->pf.ws_bytes) {
+        // the lm_head's quantised rows dequantised inside the tcgen05 kernel (tcq_gemm.cu)
+        TcqGemmArgs q{};
+        q.seg[0] = TcqSeg{m->output.p, m->output.type, I.vocab};
+        q.n_seg = 1;
+        q.x = xb;
+        q.K = I.d_model;
+        q.T = n_logits;
+        q.ws = c->pf.ws;
+        q.ws_bytes = c->pf.ws_bytes;
+        TcParts parts;
+        if ((rc = launch_tcq_gemm(q, st, &parts))) return rc;
+        if ((rc = launch_tcq_reduce(parts, n_logits, I.vocab, c->bt.logits, I.vocab, nullptr, TC_EPI_STORE, st))) return rc;
+        return launch_argmax_rows(c->bt.logits, I.vocab, n_logits, c->bt.out, st);
+    }
     TcGemmArgs a{};
     a.w = (const __half*)m->f16_cache + m->f16_output;
     a.x = xb;
@@ -1424,7 +1515,10 @@ extern "C" int b2_ctx_max_batch(b2_ctx* c) {
     if (!c) return B2_EINVAL;
     if (!batch_supported(c->m)) return 0;
     if (cudaSetDevice(c->m->device) != cudaSuccess) return GEMM_MAX_COLS;
-    if (prefill_tc_supported(c->m) && !ensure_batch(c) && !ensure_prefill(c) && c->m->f16_cache) return BATCH_MAX_COLS;
+    if (prefill_tc_supported(c->m) && !ensure_batch(c) && !ensure_prefill(c)) {
+        if (c->m->f16_cache) return BATCH_MAX_COLS;
+        if (tcq_pass_ok(c->m, TCQ_MAX_T)) return TCQ_MAX_T;   // no fp16 copy: the fused-dequantisation pass, up to 128 columns
+    }
     return GEMM_MAX_COLS;
 }
 

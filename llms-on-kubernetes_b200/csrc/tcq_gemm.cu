@@ -1,17 +1,21 @@
-// tcq_gemm.cu -- quantised-weight mat-mul for decode batches: TMA (raw blocks) -> dequantising warps -> swizzled fp16
-// tiles -> tcgen05.mma -> tensor memory (SURVEY 8a row a12, 2 <= n_tokens <= 128; north_star's "dequant fused into the
-// TMA -> smem -> tcgen05 producer").
+// tcq_gemm.cu -- quantised-weight mat-mul for decode batches: TMA (raw blocks) -> dequantising warps -> tensor memory
+// -> tcgen05.mma (SURVEY 8a row a12, 2 <= n_tokens <= 128; north_star's "dequant fused into the TMA -> smem -> tcgen05
+// producer").
 //
-// One persistent CTA per SM, fifteen warps with fixed roles:
+// One persistent CTA per SM, 23 warps with fixed roles:
 //   warp 0      weight producer: per 256-element block column one TMA box of 128 rows x (144 | 224) raw bytes of the
-//               quantised tensor into a ring of 3 stages (the tensor map's element type is a byte; a box starts on a
-//               16-byte boundary of the row, so a 210-byte Q6_K block sits 0 .. 14 bytes into its 224-byte slot and
-//               is read with 4-byte loads and funnel shifts)
+//               quantised tensor into a ring of shared-memory stages (the tensor map's element type is a byte; a box
+//               starts on a 16-byte boundary of the row, so a 210-byte Q6_K block sits 0 .. 14 bytes into its
+//               224-byte slot and is read with 4-byte loads and funnel shifts)
 //   warp 2      activation producer: per 64-element K step one BN x 64 fp16 tile (TMA, 128-byte swizzle)
-//   warps 7-14  dequantise: thread (row, half) turns 32 weights of its row per K step into fp16 -- exactly the value
-//               dequant.cuh gives, rounded once -- and stores them as 16-byte chunks into the K-major 128-byte-swizzled
-//               tile the UMMA descriptor expects (chunk c of row r at 128 r + 16 (c ^ (r & 7)))
-//   warp 1      tcgen05.mma 128 x BN x 16, four per K step, accumulators in tensor memory (two, alternating)
+//   warps 7-22  dequantise: a thread owns one weight row (lane 32 (warp % 4) + lane of tensor memory) and one of the
+//               block's four K steps (warp group (warp - 7) / 4): 64 weights -> fp16, exactly the value dequant.cuh
+//               gives rounded once -> 32 packed registers -> tcgen05.st into the A-operand ring in TENSOR memory.
+//               The fp16 weights never touch shared memory: at 3.5 x the size of the raw blocks, writing them there
+//               and having the tensor core read them back cost more shared-memory bandwidth than the SM's share of
+//               the HBM stream leaves time for (first version of this kernel: 1.25 TB/s).
+//   warp 1      tcgen05.mma 128 x BN x 16, A from tensor memory, B (activations) from shared memory, four per K step,
+//               accumulators in tensor memory (two, alternating)
 //   warps 3-6   epilogue: tcgen05.ld, fp32 partial sums to the output slices
 // Work is cut stream-K fashion: the (tile, block column) pairs of the whole matrix are numbered tile-major and every
 // CTA takes an equal contiguous share, so each SM streams the same number of bytes whatever the matrix's shape;
@@ -27,6 +31,9 @@
 #include <cuda.h>
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
 
 #include "common.h"
 #include "dequant.cuh"
@@ -41,21 +48,29 @@ using namespace tcptx;
 constexpr int TQ_BM = 128, TQ_BK = 64;
 constexpr int TQ_RAW_PITCH_MAX = 224;                      // bytes per row of a raw stage: 144 (Q4_K) or 224 (Q6_K: 210 -> next multiple of 16)
 constexpr int TQ_RAW_BYTES = TQ_BM * TQ_RAW_PITCH_MAX;     // 28 672
-constexpr int TQ_RSTAGES = 3;
-constexpr int TQ_DQ_WARPS = 8, TQ_DQ_WARP0 = 7;
-constexpr int TQ_THREADS = (TQ_DQ_WARP0 + TQ_DQ_WARPS) * 32;   // 480
+constexpr int TQ_DQ_WARPS = 16, TQ_DQ_WARP0 = 7;           // warp 7 + 4 g + q: K step g of the block, lane quarter (7 + q) % 4
+constexpr int TQ_THREADS = (TQ_DQ_WARP0 + TQ_DQ_WARPS) * 32;   // 736
+constexpr int TQ_NA = 2;                                   // A-operand ring in tensor memory: block columns of 128 columns (4 K steps)
+constexpr int TQ_A_COL0 = 256;                             // columns 0 .. 255: the two accumulators; 256 .. 511: the A ring
+constexpr int TQ_TMEM_COLS = 512;
 
+// Hand-offs are per 256-element block column, not per K step: the one thread that issues the MMAs needs ~80 cycles per
+// tcgen05 instruction and ~100 per barrier wait, and at 4 MMAs + 2 commits + 2 waits per K step it was the bottleneck of
+// the first versions (950 cycles per K step, 1.2 TB/s).
 template <int BN>
 struct TqGeo {
-    static constexpr int NSLOT = BN <= 32 ? 6 : (BN == 64 ? 5 : 4);
-    static constexpr int A_BYTES = TQ_BM * TQ_BK * 2;
-    static constexpr int X_BYTES = BN * TQ_BK * 2;
-    static constexpr int SLOT_BYTES = A_BYTES + X_BYTES;
-    static constexpr int N_BARS = 2 * NSLOT + 2 * TQ_RSTAGES + 4;
-    static constexpr int SMEM = NSLOT * SLOT_BYTES + TQ_RSTAGES * TQ_RAW_BYTES + 1024 + 8 * N_BARS + 16;
-    static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+    static constexpr int RSTAGES = BN <= 32 ? 5 : (BN == 64 ? 4 : 3);   // raw weight stages
+    static constexpr int NX = BN <= 32 ? 4 : (BN == 64 ? 3 : 2);        // activation stages: BN x 256 fp16 = four swizzled BN x 64 tiles
+    static constexpr int XT_BYTES = BN * TQ_BK * 2;                     // one tile
+    static constexpr int X_BYTES = 4 * XT_BYTES;
+    static constexpr int N_BARS = 2 * TQ_NA + 2 * NX + 2 * RSTAGES + 4;
+    static constexpr int SMEM = NX * X_BYTES + RSTAGES * TQ_RAW_BYTES + 1024 + 8 * N_BARS + 16;
     static constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TQ_BM >> 4) << 24);
+    // MMAs into one accumulator execute one after the other at the pipeline's latency (~130 cycles for these narrow
+    // shapes): consecutive K = 16 slices go to NACC accumulators in turn, the epilogue adds them in a fixed order
+    static constexpr int NACC = 128 / BN;
 };
+static_assert(TqGeo<32>::SMEM <= 227 * 1024 && TqGeo<64>::SMEM <= 227 * 1024 && TqGeo<128>::SMEM <= 227 * 1024, "shared memory budget");
 
 struct TcqParams {
     int n_seg;
@@ -64,7 +79,9 @@ struct TcqParams {
     int seg_rows[TCQ_MAX_SEGS];
     int seg_type[TCQ_MAX_SEGS];
     int N, K, T, nblk, tiles_m, splits;
+    int dbg;   // B2_TCQ_DBG (experiments): 1 = no MMAs, 2 = no dequantisation arithmetic, 4 = no tensor-memory stores
     float* ws;
+    long long* trace;   // B2_TCQ_TRACE=1: clock64 stamps of CTA 0 ([0..]: MMA thread, 2 per K step; [4096..]: dequantising warp of group 0, 4 per block)
 };
 
 // the CTA's share of the tile-major (tile, block column) sequence, one tile segment at a time
@@ -76,12 +93,12 @@ struct Walk {
         step = total * blockIdx.x / gridDim.x;
         hi = total * (blockIdx.x + 1) / gridDim.x;
     }
-    __device__ bool next(int* tile, int* kb0, int* kb1) {
+    __device__ __forceinline__ bool next(int& tile, int& kb0, int& kb1) {
         if (step >= hi) return false;
-        *tile = (int)(step / nblk);
-        *kb0 = (int)(step - (long long)*tile * nblk);
-        const long long n = min((long long)(nblk - *kb0), hi - step);
-        *kb1 = *kb0 + (int)n;
+        tile = (int)(step / nblk);
+        kb0 = (int)(step - (long long)tile * nblk);
+        const long long n = min((long long)(nblk - kb0), hi - step);
+        kb1 = kb0 + (int)n;
         step += n;
         return true;
     }
@@ -103,23 +120,20 @@ __device__ __forceinline__ uint32_t pack_sat(float lo, float hi) {
 __device__ __forceinline__ float lo_f(uint32_t x) { return __low2float(*(const __half2*)&x); }
 __device__ __forceinline__ float hi_f(uint32_t x) { return __high2float(*(const __half2*)&x); }
 
-__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
     uint4 v;
     asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
     return v;
 }
 
-// ---- 32 weights of one row and one 64-element K step -> 64 bytes of the swizzled fp16 tile --------------------------------
-// Q4_K, K step g of the block: bytes qs[32 g + 16 h ..+16) hold elements 16 h .. 16 h + 15 of sub-block 2 g (low nibbles)
-// and of sub-block 2 g + 1 (high nibbles): chunks 2 h, 2 h + 1 and 4 + 2 h, 5 + 2 h of the row.
-__device__ __forceinline__ void dequant_q4k(uint32_t raw_row, uint32_t a_row, int sw, int g, int h) {
-    const uint4 hd = lds128(raw_row);   // d | dmin, scales[12]
+// ---- the 64 weights of one row and one 64-element K step -> 32 registers of packed fp16 pairs (K order) -----------------
+// Q4_K, K step g of the block: bytes qs[32 g ..+32) hold sub-block 2 g in their low nibbles (elements 0 .. 31 of the
+// step) and sub-block 2 g + 1 in their high nibbles (elements 32 .. 63).
+__device__ __forceinline__ void dequant_q4k(uint32_t blk, int g, uint32_t (&o)[32]) {
+    const uint4 hd = lds128(blk);   // d | dmin, scales[12]
     const __half2 dd = *(const __half2*)&hd.x;
     const float d = __low2float(dd), dmin = __high2float(dd);
-    // get_scale_min_k4 for sub-blocks 2 g and 2 g + 1 from the three words of packed 6-bit scales (no byte array: registers only)
+    // get_scale_min_k4 for sub-blocks 2 g and 2 g + 1 from the three words of packed 6-bit scales
     int s0, m0, s1, m1;
     if (g < 2) {
         const int sh = 16 * g;
@@ -134,22 +148,17 @@ __device__ __forceinline__ void dequant_q4k(uint32_t raw_row, uint32_t a_row, in
     }
     const float ds0 = (d * (float)s0) * 16777216.0f, dm0 = -(dmin * (float)m0);
     const float ds1 = (d * (float)s1) * 16777216.0f, dm1 = -(dmin * (float)m1);
-    const uint4 q = lds128(raw_row + 16 + 32 * g + 16 * h);
-    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-    uint32_t lo[8], hi[8];
+    const uint4 qa = lds128(blk + 16 + 32 * g), qb = lds128(blk + 32 + 32 * g);
+    const uint32_t w[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
+    for (int i = 0; i < 8; i++) {
         const uint32_t a = w[i] & 0x000F000Fu, b = (w[i] >> 8) & 0x000F000Fu;     // elements (0, 2), (1, 3) of the word, low nibbles
         const uint32_t c = (w[i] >> 4) & 0x000F000Fu, e = (w[i] >> 12) & 0x000F000Fu;
-        lo[2 * i] = pack_sat(fmaf(lo_f(a), ds0, dm0), fmaf(lo_f(b), ds0, dm0));
-        lo[2 * i + 1] = pack_sat(fmaf(hi_f(a), ds0, dm0), fmaf(hi_f(b), ds0, dm0));
-        hi[2 * i] = pack_sat(fmaf(lo_f(c), ds1, dm1), fmaf(lo_f(e), ds1, dm1));
-        hi[2 * i + 1] = pack_sat(fmaf(hi_f(c), ds1, dm1), fmaf(hi_f(e), ds1, dm1));
+        o[2 * i] = pack_sat(fmaf(lo_f(a), ds0, dm0), fmaf(lo_f(b), ds0, dm0));
+        o[2 * i + 1] = pack_sat(fmaf(hi_f(a), ds0, dm0), fmaf(hi_f(b), ds0, dm0));
+        o[16 + 2 * i] = pack_sat(fmaf(lo_f(c), ds1, dm1), fmaf(lo_f(e), ds1, dm1));
+        o[16 + 2 * i + 1] = pack_sat(fmaf(hi_f(c), ds1, dm1), fmaf(hi_f(e), ds1, dm1));
     }
-    sts128(a_row + (uint32_t)(((2 * h) ^ sw) << 4), lo[0], lo[1], lo[2], lo[3]);
-    sts128(a_row + (uint32_t)(((2 * h + 1) ^ sw) << 4), lo[4], lo[5], lo[6], lo[7]);
-    sts128(a_row + (uint32_t)(((4 + 2 * h) ^ sw) << 4), hi[0], hi[1], hi[2], hi[3]);
-    sts128(a_row + (uint32_t)(((5 + 2 * h) ^ sw) << 4), hi[4], hi[5], hi[6], hi[7]);
 }
 
 // NW 32-bit words starting at a 2-byte-aligned shared-memory address
@@ -163,33 +172,36 @@ __device__ __forceinline__ void lds_words_even(uint32_t addr, uint32_t (&out)[NW
     for (int i = 0; i < NW; i++) out[i] = __funnelshift_r(w[i], w[i + 1], sh);
 }
 
-// Q6_K, K step g = 2 n + u of the block: elements 128 n + 64 u + 32 h + l (l < 32) = quarter qi = 2 u + h of half n:
-// ql[64 n + 32 h + l] nibble u, qh[32 n + l] bits 2 qi .. 2 qi + 1, scale[8 n + 2 qi + l / 16], minus 32.
-// blk: the block's first byte in shared memory, 2-byte aligned only (210-byte blocks; a TMA box starts on a 16-byte
-// boundary of the row, so the block sits 0 .. 14 bytes into its slot).
-__device__ __forceinline__ void dequant_q6k(uint32_t blk, uint32_t a_row, int sw, int g, int h) {
-    const int n = g >> 1, u = g & 1, qi = 2 * u + h;
-    uint32_t tail;   // scales[8 n + 2 qi], [.. + 1]
-    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(tail) : "r"(blk + 192 + 8 * n + 2 * qi) : "memory");
-    uint32_t dbits;
+// Q6_K, K step g = 2 n + u of the block: element 32 j + l of the step (j < 2, l < 32) is quarter qi = 2 u + j of half n:
+// ql[64 n + 32 j + l] nibble u, qh[32 n + l] bits 2 qi .. 2 qi + 1, scale[8 n + 2 qi + l / 16], minus 32.
+// blk: the block's first byte in shared memory, 2-byte aligned only.
+__device__ __forceinline__ void dequant_q6k(uint32_t blk, int g, uint32_t (&o)[32]) {
+    const int n = g >> 1, u = g & 1;
+    uint32_t dbits, sc4[1];
     asm volatile("ld.shared.u16 %0, [%1];" : "=r"(dbits) : "r"(blk + 208) : "memory");
+    lds_words_even<1>(blk + 192 + 8 * n + 4 * u, sc4);   // scales[8 n + 4 u ..+4): quarters 2 u (two scales) and 2 u + 1
     const float d = __half2float(__ushort_as_half((unsigned short)dbits));
-    const float dsA = d * (float)(int8_t)(tail & 0xff), dsB = d * (float)(int8_t)(tail >> 8);
-    const float ds[2] = {dsA * 16777216.0f, dsB * 16777216.0f}, off[2] = {-32.0f * dsA, -32.0f * dsB};
-    uint32_t ql[8], qh[8];
-    lds_words_even<8>(blk + 64 * n + 32 * h, ql);
-    lds_words_even<8>(blk + 128 + 32 * n, qh);
-    uint32_t o[16];
+    float ds[4], off[4];
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-        const uint32_t q = ((ql[i] >> (4 * u)) & 0x0F0F0F0Fu) | (((qh[i] >> (2 * qi)) & 0x03030303u) << 4);
-        const uint32_t p01 = __byte_perm(q, 0u, 0x4140), p23 = __byte_perm(q, 0u, 0x4342);
-        const float s = ds[i >> 2], f = off[i >> 2];
-        o[2 * i] = pack_sat(fmaf(lo_f(p01), s, f), fmaf(hi_f(p01), s, f));
-        o[2 * i + 1] = pack_sat(fmaf(lo_f(p23), s, f), fmaf(hi_f(p23), s, f));
+    for (int k = 0; k < 4; k++) {
+        const float t = d * (float)(int8_t)(sc4[0] >> (8 * k));
+        ds[k] = t * 16777216.0f;
+        off[k] = -32.0f * t;
     }
+    uint32_t ql[16], qh[8];
+    lds_words_even<16>(blk + 64 * n, ql);
+    lds_words_even<8>(blk + 128 + 32 * n, qh);
 #pragma unroll
-    for (int c = 0; c < 4; c++) sts128(a_row + (uint32_t)(((4 * h + c) ^ sw) << 4), o[4 * c], o[4 * c + 1], o[4 * c + 2], o[4 * c + 3]);
+    for (int j = 0; j < 2; j++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const uint32_t q = ((ql[8 * j + i] >> (4 * u)) & 0x0F0F0F0Fu) | (((qh[i] >> (2 * (2 * u + j))) & 0x03030303u) << 4);
+            const uint32_t p01 = __byte_perm(q, 0u, 0x4140), p23 = __byte_perm(q, 0u, 0x4342);
+            const float s = ds[2 * j + (i >> 2)], f = off[2 * j + (i >> 2)];
+            o[16 * j + 2 * i] = pack_sat(fmaf(lo_f(p01), s, f), fmaf(hi_f(p01), s, f));
+            o[16 * j + 2 * i + 1] = pack_sat(fmaf(lo_f(p23), s, f), fmaf(hi_f(p23), s, f));
+        }
+    }
 }
 
 // 32 lanes x 16 consecutive fp32 columns of tensor memory
@@ -203,6 +215,20 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// one lane polls, the warp follows: 700 threads spinning on mbarriers starve the one thread that issues the MMAs
+__device__ __forceinline__ void bar_wait_warp(uint32_t bar, uint32_t parity, int lane) {
+    if (lane == 0) bar_wait(bar, parity);
+    __syncwarp();
+}
+
+// one lane of a converged warp (the warp runs the surrounding loop as a whole: its variables stay warp-uniform, and the
+// tcgen05 instructions get their operands from uniform registers without a per-instruction broadcast loop)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(pred));
+    return pred != 0;
+}
+
 struct TcqMaps {
     CUtensorMap w[TCQ_MAX_SEGS];
     CUtensorMap x;
@@ -212,24 +238,32 @@ template <int BN>
 __global__ void __launch_bounds__(TQ_THREADS, 1) tcq_gemm_kernel(const __grid_constant__ TcqMaps maps, const TcqParams p) {
     using G = TqGeo<BN>;
     extern __shared__ uint8_t tq_smem[];
-    const uint32_t slots0 = (smem_u32(tq_smem) + 1023u) & ~1023u;
-    const uint32_t raw0 = slots0 + G::NSLOT * G::SLOT_BYTES;
-    const uint32_t bars = raw0 + TQ_RSTAGES * TQ_RAW_BYTES;
-    auto ab_full = [&](int s) { return bars + 8u * s; };
-    auto ab_empty = [&](int s) { return bars + 8u * (G::NSLOT + s); };
-    auto raw_full = [&](int s) { return bars + 8u * (2 * G::NSLOT + s); };
-    auto raw_empty = [&](int s) { return bars + 8u * (2 * G::NSLOT + TQ_RSTAGES + s); };
-    auto acc_full = [&](int i) { return bars + 8u * (2 * G::NSLOT + 2 * TQ_RSTAGES + i); };
-    auto acc_empty = [&](int i) { return bars + 8u * (2 * G::NSLOT + 2 * TQ_RSTAGES + 2 + i); };
+    if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) p.trace[8000] = clock64();
+    const uint32_t x0 = (smem_u32(tq_smem) + 1023u) & ~1023u;
+    const uint32_t raw0 = x0 + G::NX * G::X_BYTES;
+    const uint32_t bars = raw0 + G::RSTAGES * TQ_RAW_BYTES;
+    auto a_full = [&](int s) { return bars + 8u * s; };
+    auto a_empty = [&](int s) { return bars + 8u * (TQ_NA + s); };
+    auto x_full = [&](int s) { return bars + 8u * (2 * TQ_NA + s); };
+    auto x_empty = [&](int s) { return bars + 8u * (2 * TQ_NA + G::NX + s); };
+    constexpr int RB = 2 * TQ_NA + 2 * G::NX;
+    auto raw_full = [&](int s) { return bars + 8u * (RB + s); };
+    auto raw_empty = [&](int s) { return bars + 8u * (RB + G::RSTAGES + s); };
+    auto acc_full = [&](int i) { return bars + 8u * (RB + 2 * G::RSTAGES + i); };
+    auto acc_empty = [&](int i) { return bars + 8u * (RB + 2 * G::RSTAGES + 2 + i); };
     const uint32_t tmem_slot = bars + 8u * G::N_BARS;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (warp == 0 && lane == 0) {
-        for (int s = 0; s < G::NSLOT; s++) {
-            bar_init(ab_full(s), TQ_DQ_WARPS + 1);   // the dequantising warps and the activation tile's byte count
-            bar_init(ab_empty(s), 1);                // tcgen05.commit
+        for (int s = 0; s < TQ_NA; s++) {
+            bar_init(a_full(s), TQ_DQ_WARPS);   // every dequantising warp has stored its part of the block column
+            bar_init(a_empty(s), 1);            // tcgen05.commit
         }
-        for (int s = 0; s < TQ_RSTAGES; s++) {
+        for (int s = 0; s < G::NX; s++) {
+            bar_init(x_full(s), 1);
+            bar_init(x_empty(s), 1);
+        }
+        for (int s = 0; s < G::RSTAGES; s++) {
             bar_init(raw_full(s), 1);
             bar_init(raw_empty(s), TQ_DQ_WARPS);
         }
@@ -242,7 +276,7 @@ __global__ void __launch_bounds__(TQ_THREADS, 1) tcq_gemm_kernel(const __grid_co
         asm volatile("prefetch.tensormap [%0];" :: "l"(&maps.x) : "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "n"(G::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "n"(TQ_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
@@ -251,6 +285,7 @@ __global__ void __launch_bounds__(TQ_THREADS, 1) tcq_gemm_kernel(const __grid_co
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
 
+    if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) p.trace[8001] = clock64();
     Walk walk(p);
     int tile, kb0, kb1;
     if (warp == 0) {
@@ -258,7 +293,7 @@ __global__ void __launch_bounds__(TQ_THREADS, 1) tcq_gemm_kernel(const __grid_co
         if (lane == 0) {
             int rs = 0;
             uint32_t ph = 0;
-            while (walk.next(&tile, &kb0, &kb1)) {
+            while (walk.next(tile, kb0, kb1)) {
                 const int si = seg_of_tile(p, tile);
                 const int q4 = p.seg_type[si] == B2_TYPE_Q4_K;
                 const int bb = q4 ? 144 : 210;
@@ -268,78 +303,101 @@ __global__ void __launch_bounds__(TQ_THREADS, 1) tcq_gemm_kernel(const __grid_co
                     bar_wait(raw_empty(rs), ph ^ 1);
                     bar_expect_tx(raw_full(rs), box);
                     tma_load_2d(raw0 + rs * TQ_RAW_BYTES, &maps.w[si], raw_full(rs), (kb * bb) & ~15, m0);   // a box starts on 16 bytes
-                    if (++rs == TQ_RSTAGES) { rs = 0; ph ^= 1; }
+                    if (++rs == G::RSTAGES) { rs = 0; ph ^= 1; }
                 }
             }
         }
         __syncwarp();
     } else if (warp == 2) {
-        // ===== activation tiles =====
+        // ===== activations: the block column's BN x 256 values as four swizzled BN x 64 tiles =====
         if (lane == 0) {
             int s = 0;
             uint32_t ph = 0;
-            while (walk.next(&tile, &kb0, &kb1)) {
-                for (int ks = 4 * kb0; ks < 4 * kb1; ks++) {
-                    bar_wait(ab_empty(s), ph ^ 1);
-                    bar_expect_tx(ab_full(s), G::X_BYTES);
-                    tma_load_2d(slots0 + s * G::SLOT_BYTES + G::A_BYTES, &maps.x, ab_full(s), ks * TQ_BK, 0);
-                    if (++s == G::NSLOT) { s = 0; ph ^= 1; }
+            while (walk.next(tile, kb0, kb1)) {
+                for (int kb = kb0; kb < kb1; kb++) {
+                    bar_wait(x_empty(s), ph ^ 1);
+                    bar_expect_tx(x_full(s), G::X_BYTES);
+#pragma unroll
+                    for (int g = 0; g < 4; g++) tma_load_2d(x0 + s * G::X_BYTES + g * G::XT_BYTES, &maps.x, x_full(s), (4 * kb + g) * TQ_BK, 0);
+                    if (++s == G::NX) { s = 0; ph ^= 1; }
                 }
             }
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ===== tensor cores =====
-        if (lane == 0) {
-            int s = 0, j = 0;
-            uint32_t ph = 0;
-            for (; walk.next(&tile, &kb0, &kb1); j++) {
+        // ===== tensor cores: D[128 rows][BN] += A (tensor memory) . B (activation tile), 16 MMAs per block column =====
+        {
+            int xs = 0, j = 0, nb = 0, tn = 0;
+            uint32_t xph = 0;
+            for (; walk.next(tile, kb0, kb1); j++) {
                 const int as = j & 1;
                 bar_wait(acc_empty(as), ((j >> 1) & 1) ^ 1);   // the epilogue has drained this accumulator
                 tc_fence_after();
-                const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
-                const int n_ks = 4 * (kb1 - kb0);
-                for (int ks = 0; ks < n_ks; ks++) {
-                    bar_wait(ab_full(s), ph);
+                const uint32_t tmem_d = tmem_base + (uint32_t)(as * 128);
+                for (int kb = kb0; kb < kb1; kb++, nb++) {
+                    const int s = nb & 1;
+                    bar_wait(x_full(xs), xph);
+                    bar_wait(a_full(s), (nb >> 1) & 1);
                     tc_fence_after();
-                    const uint32_t sa = slots0 + s * G::SLOT_BYTES;
-                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + G::A_BYTES);
+                    const uint32_t ta = tmem_base + (uint32_t)(TQ_A_COL0 + 128 * s);
+                    const uint64_t db = umma_desc_sw128(x0 + xs * G::X_BYTES);
+                    if (elect_one()) {
+                        if (p.trace && blockIdx.x == 0 && tn < 2000) p.trace[2 * tn] = clock64();
+                        if (!(p.dbg & 1)) {
 #pragma unroll
-                    for (int k = 0; k < TQ_BK / 16; k++) umma_f16(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), G::IDESC, (ks | k) != 0);
-                    umma_commit(ab_empty(s));
-                    if (++s == G::NSLOT) { s = 0; ph ^= 1; }
+                            for (int k = 0; k < 16; k++)
+                                umma_f16_ta(tmem_d + (uint32_t)((k & (G::NACC - 1)) * BN), ta + 8u * k,
+                                            db + (uint64_t)((k >> 2) * (G::XT_BYTES >> 4) + 2 * (k & 3)), G::IDESC, (kb > kb0) | (k >= G::NACC));
+                        }
+                        const long long tm = (p.trace && blockIdx.x == 0) ? clock64() : 0;
+                        umma_commit(a_empty(s));
+                        umma_commit(x_empty(xs));
+                        if (p.trace && blockIdx.x == 0 && tn < 2000) p.trace[2 * tn + 1] = clock64() | ((clock64() - tm) << 48);
+                    }
+                    tn++;
+                    __syncwarp();
+                    if (++xs == G::NX) { xs = 0; xph ^= 1; }
                 }
-                umma_commit(acc_full(as));
+                if (elect_one()) umma_commit(acc_full(as));
+                __syncwarp();
             }
         }
-        __syncwarp();
     } else if (warp >= TQ_DQ_WARP0) {
-        // ===== dequantisation: two threads per weight row =====
-        const int td = threadIdx.x - TQ_DQ_WARP0 * 32;
-        const int row = td >> 1, h = td & 1;
-        const int sw = row & 7;
-        int s = 0, rs = 0;
-        uint32_t ph = 0, rph = 0;
-        while (walk.next(&tile, &kb0, &kb1)) {
+        // ===== dequantisation: thread = weight row 32 (warp % 4) + lane, K step g of every block =====
+        const int g = (warp - TQ_DQ_WARP0) >> 2;
+        const int row = 32 * (warp & 3) + lane;
+        const uint32_t ta = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)(TQ_A_COL0 + 32 * g);
+        int tb = 0;
+        int rs = 0, nb = 0;
+        uint32_t rph = 0;
+        while (walk.next(tile, kb0, kb1)) {
             const int q4 = p.seg_type[seg_of_tile(p, tile)] == B2_TYPE_Q4_K;
             const uint32_t pitch = q4 ? 144u : 224u;
-            for (int kb = kb0; kb < kb1; kb++) {
-                bar_wait(raw_full(rs), rph);
-                const uint32_t raw_row = raw0 + rs * TQ_RAW_BYTES + row * pitch;
+            for (int kb = kb0; kb < kb1; kb++, nb++) {
+                const bool tr = p.trace && blockIdx.x == 0 && warp == TQ_DQ_WARP0 && lane == 0 && tb < 500;
+                if (tr) p.trace[4096 + 5 * tb] = clock64();
+                bar_wait_warp(raw_full(rs), rph, lane);
+                if (tr) p.trace[4096 + 5 * tb + 1] = clock64();
+                const uint32_t blk = raw0 + rs * TQ_RAW_BYTES + row * pitch;
+                uint32_t o[32];
+                if (p.dbg & 2) {
 #pragma unroll
-                for (int g = 0; g < 4; g++) {
-                    bar_wait(ab_empty(s), ph ^ 1);
-                    const uint32_t a_row = slots0 + s * G::SLOT_BYTES + row * 128;
-                    if (q4) dequant_q4k(raw_row, a_row, sw, g, h);
-                    else dequant_q6k(raw_row + (uint32_t)((kb * 210) & 15), a_row, sw, g, h);
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores, read by the tensor cores
-                    __syncwarp();
-                    if (lane == 0) bar_arrive(ab_full(s));
-                    if (++s == G::NSLOT) { s = 0; ph ^= 1; }
-                }
+                    for (int i = 0; i < 32; i++) o[i] = 0u;
+                } else if (q4) dequant_q4k(blk, g, o);
+                else dequant_q6k(blk + (uint32_t)((kb * 210) & 15), g, o);
                 __syncwarp();
-                if (lane == 0) bar_arrive(raw_empty(rs));
-                if (++rs == TQ_RSTAGES) { rs = 0; rph ^= 1; }
+                if (lane == 0) bar_arrive(raw_empty(rs));   // the stage's bytes are in registers
+                if (++rs == G::RSTAGES) { rs = 0; rph ^= 1; }
+                const int s = nb & 1;
+                if (tr) p.trace[4096 + 5 * tb + 2] = clock64() + (o[0] == 0x12345678u);
+                bar_wait_warp(a_empty(s), ((nb >> 1) & 1) ^ 1, lane);
+                tc_fence_after();
+                if (tr) p.trace[4096 + 5 * tb + 3] = clock64();
+                if (!(p.dbg & 4)) tmem_st_32x32(ta + 128u * s, o);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) bar_arrive(a_full(s));
+                if (tr) p.trace[4096 + 5 * tb++ + 4] = clock64();
             }
         }
     } else {
@@ -347,25 +405,34 @@ __global__ void __launch_bounds__(TQ_THREADS, 1) tcq_gemm_kernel(const __grid_co
         const int q = warp & 3;   // the quarter of the 128 tensor-memory lanes this warp may read
         const long long total = (long long)p.tiles_m * p.nblk;
         const size_t slice = (size_t)p.T * p.N;
-        for (int j = 0; walk.next(&tile, &kb0, &kb1); j++) {
+        for (int j = 0; walk.next(tile, kb0, kb1); j++) {
             const int as = j & 1;
             const int si = seg_of_tile(p, tile);
             const int r = (tile - p.seg_tile0[si]) * TQ_BM + q * 32 + lane;   // row inside the segment
             const bool row_ok = r < p.seg_rows[si];
             const int n = p.seg_row0[si] + r;
             const int sl = (int)blockIdx.x - cta_of_step((long long)tile * p.nblk, total, (int)gridDim.x);
-            bar_wait(acc_full(as), (j >> 1) & 1);
+            bar_wait_warp(acc_full(as), (j >> 1) & 1, lane);
             tc_fence_after();
             float* const o = p.ws + (size_t)sl * slice + n;
 #pragma unroll 1
             for (int c = 0; c < BN / 16; c++) {
                 if (c * 16 >= p.T) break;
                 uint32_t v[16];
-                tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN + c * 16), v);
+                tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 128 + c * 16), v);
+                float f[16];
+#pragma unroll
+                for (int i = 0; i < 16; i++) f[i] = __uint_as_float(v[i]);
+#pragma unroll
+                for (int a = 1; a < G::NACC; a++) {
+                    tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * 128 + a * BN + c * 16), v);
+#pragma unroll
+                    for (int i = 0; i < 16; i++) f[i] += __uint_as_float(v[i]);
+                }
                 if (row_ok) {
 #pragma unroll
                     for (int i = 0; i < 16; i++)
-                        if (c * 16 + i < p.T) o[(size_t)(c * 16 + i) * p.N] = __uint_as_float(v[i]);
+                        if (c * 16 + i < p.T) o[(size_t)(c * 16 + i) * p.N] = f[i];
                 }
             }
             tc_fence_before();
@@ -377,11 +444,13 @@ __global__ void __launch_bounds__(TQ_THREADS, 1) tcq_gemm_kernel(const __grid_co
             }
         }
     }
+    if (p.trace && blockIdx.x == 0 && threadIdx.x == 96) p.trace[8003] = clock64();   // an epilogue warp is through
     tc_fence_before();
     __syncthreads();
+    if (p.trace && blockIdx.x == 0 && threadIdx.x == 0) p.trace[8002] = clock64();
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(G::TMEM_COLS) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(TQ_TMEM_COLS) : "memory");
     }
 }
 
@@ -570,7 +639,31 @@ int launch_tcq_gemm(const TcqGemmArgs& a, cudaStream_t st, TcParts* parts) {
         return B2_EINVAL;
     }
     p.ws = a.ws;
+    if (const char* e = getenv("B2_TCQ_DBG")) p.dbg = atoi(e);
     *parts = TcParts{a.ws, p.splits, (size_t)a.T * p.N};
+    static const bool want_trace = getenv("B2_TCQ_TRACE") != nullptr;
+    if (want_trace) {
+        static long long* tbuf = nullptr;
+        if (!tbuf) cudaMalloc(&tbuf, 8192 * sizeof(long long));
+        cudaMemsetAsync(tbuf, 0, 8192 * sizeof(long long), st);
+        p.trace = tbuf;
+        rc = bn == 32 ? launch_tq<32>(maps, p, grid, st) : bn == 64 ? launch_tq<64>(maps, p, grid, st) : launch_tq<128>(maps, p, grid, st);
+        cudaStreamSynchronize(st);
+        std::vector<long long> h(8192);
+        cudaMemcpy(h.data(), tbuf, h.size() * 8, cudaMemcpyDeviceToHost);
+        fprintf(stderr, "tcq trace: N=%d K=%d T=%d grid=%d slices=%d\n", p.N, p.K, p.T, grid, p.splits);
+        const long long t0 = h[4096];
+        fprintf(stderr, "  kernel entry %lld, set-up done %lld, epilogue warp done %lld, all warps done %lld (cycles relative to the first dequantising wait)\n",
+                h[8000] - t0, h[8001] - t0, h[8003] - t0, h[8002] - t0);
+        for (int b = 0; b < 40 && h[4096 + 5 * b]; b++)
+            fprintf(stderr, "  dq block %2d: start %7lld raw_full +%5lld dequant +%5lld a_empty +%5lld st+arrive +%5lld\n", b, h[4096 + 5 * b] - t0,
+                    h[4096 + 5 * b + 1] - h[4096 + 5 * b], h[4096 + 5 * b + 2] - h[4096 + 5 * b + 1], h[4096 + 5 * b + 3] - h[4096 + 5 * b + 2],
+                    h[4096 + 5 * b + 4] - h[4096 + 5 * b + 3]);
+        for (int k = 0; k < 40 && h[2 * k]; k++)
+            fprintf(stderr, "  mma block %2d: ready at %7lld, issue+commit %4lld (the two commits %lld)\n", k, h[2 * k] - t0,
+                    (h[2 * k + 1] & 0xffffffffffffll) - (h[2 * k] & 0xffffffffffffll), (long long)((unsigned long long)h[2 * k + 1] >> 48));
+        return rc;
+    }
     if (bn == 32) return launch_tq<32>(maps, p, grid, st);
     if (bn == 64) return launch_tq<64>(maps, p, grid, st);
     return launch_tq<128>(maps, p, grid, st);

@@ -105,6 +105,23 @@ def test_real_shape_parity(b2, synth, name, n_prompts, capsys):
             bat.append({"err": st["err"], "kl": st["kl"]})
             assert st["err"] <= tol_err and st["kl"] <= tol_kl, (name, f"batch {cols}", j, st)
         rep[f"decode_batch_{cols}"] = {"max_err": max(b["err"] for b in bat), "max_kl": max(b["kl"] for b in bat)}
+        if cols == 32 and name == "llama-3.1-8b-q4_k_m":
+            # (iv) the same 32 columns through the pass whose tcgen05 kernels dequantise the raw blocks themselves
+            # (tcq_gemm.cu; B2_TCQ=1 prefers it although the fp16 copy is resident): same operand values, so the logits
+            # differ from the fp16-copy pass by summation order only
+            os.environ["B2_TCQ"] = "1"
+            try:
+                ids_q, lg_q = ctx.decode_batch(toks, [N_PROMPT] * cols, slots=list(range(cols)))
+            finally:
+                del os.environ["B2_TCQ"]
+            worst = 0.0
+            for j in range(cols):
+                st = par.logit_stats(oracle[j % n_prompts][1][1], lg_q[j])
+                assert st["err"] <= tol_err and st["kl"] <= tol_kl, (name, "fused-dequantisation batch", j, st)
+                rng_j = float(lg[j].max() - lg[j].min())
+                worst = max(worst, float(np.abs(lg_q[j] - lg[j]).max()) / rng_j)
+            rep["decode_batch_32_fused_dequant"] = {"max_diff_vs_fp16_copy_pass_over_range": worst}
+            assert worst <= tol_err
         ctx.free()
     m.free()
     save_report()
