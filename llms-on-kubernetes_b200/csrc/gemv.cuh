@@ -40,6 +40,7 @@ struct GemvSeg {
     // res * res_scale + partial at the same row of every rank's inbox (peer memory, plain stores); out is only read
     float* peer_out[8];
     int n_peer;          // 0: update `out` in place (the all-reduce follows as a separate call)
+    int peer_local;      // 1: peer_out[0] is this GPU's own memory (the peers fetch the row: a device-scope fence is enough)
 };
 
 struct GemvArgs {
@@ -60,6 +61,9 @@ struct GemvArgs {
     int x_nparts, xg_k;
     const unsigned int* xg_flags;
     unsigned int* xg_peer_flags[8];
+    // pull form of the exchange (OP_XCHG): rank r's partial row is read from x_part_ptr[r] -- this rank's own buffer or the
+    // peer-mapped address of rank r's -- instead of from x_parts + r * K (the inbox the ranks stored into); NULL: inbox form
+    const float* x_part_ptr[8];
     const unsigned int* xg_epoch;
 };
 

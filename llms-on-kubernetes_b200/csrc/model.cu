@@ -658,11 +658,21 @@ int build_step_program(b2_ctx* c) {
         }
         // every row-split mat-vec (O, down) is exchange k: its epilogues store into all ranks' inboxes (parity k & 1), and the
         // next mat-vec stage -- the consumer of the new residual stream -- waits for the ranks' sequence numbers and reads the sum
+        // B2_TP_GATHER=1: no reduce stage -- the consuming mat-vec's prologue adds up the ranks' rows itself (first version)
+        const bool gather = env_flag("B2_TP_GATHER");
+        // B2_TP_PUSH=1: the epilogues store their partial rows into every rank's inbox (system-scope fence per CTA); default:
+        // the rows stay local and the reduce stage of every rank fetches its slice of them over NVLink
+        const bool pull = !gather && !env_flag("B2_TP_PUSH");
         int k = 0;
+        std::vector<StepOp> out;
+        out.reserve(ops.size() + 2 * I.n_layer);
         for (size_t i = 0; i < ops.size(); i++) {
             StepOp& op = ops[i];
             if (op.kind == OP_ARGMAX) op.s_epoch = c->tp_epoch;
-            if (op.kind != OP_GEMV || op.g.n_seg != 1 || op.g.seg[0].epi != EPI_RESID_TP) continue;
+            if (op.kind != OP_GEMV || op.g.n_seg != 1 || op.g.seg[0].epi != EPI_RESID_TP) {
+                out.push_back(op);
+                continue;
+            }
             size_t j = i + 1;
             while (j < ops.size() && ops[j].kind != OP_GEMV) j++;
             if (k >= 255 || j == ops.size() || ops[j].g.x != c->x || ops[j].g.K != d) {
@@ -670,17 +680,33 @@ int build_step_program(b2_ctx* c) {
                 return B2_EINVAL;
             }
             GemvSeg& s = op.g.seg[0];
-            s.n_peer = tp;
-            for (int p = 0; p < tp; p++) s.peer_out[p] = (float*)c->tp_peers[p] + ((size_t)(k & 1) * tp + rank) * d;
-            GemvArgs& g = ops[j].g;
+            if (pull) {
+                // the partial row stays in this rank's buffer (slot `rank` of parity k & 1); the peers' reduce stages fetch it
+                s.n_peer = 1;
+                s.peer_local = 1;
+                s.peer_out[0] = (float*)c->tp_local + ((size_t)(k & 1) * tp + rank) * d;
+            } else {
+                s.n_peer = tp;
+                for (int p = 0; p < tp; p++) s.peer_out[p] = (float*)c->tp_peers[p] + ((size_t)(k & 1) * tp + rank) * d;
+            }
+            out.push_back(op);
+            StepOp xr{};
+            xr.kind = OP_XCHG;
+            GemvArgs& g = gather ? ops[j].g : xr.g;
+            g.x = c->x;
+            g.K = d;
             g.x_parts = (const float*)c->tp_local + (size_t)(k & 1) * tp * d;
             g.x_nparts = tp;
             g.xg_k = k;
             g.xg_flags = (const unsigned int*)((const uint8_t*)c->tp_local + c->tp_flags_off);
             for (int p = 0; p < tp; p++) g.xg_peer_flags[p] = (unsigned int*)((uint8_t*)c->tp_peers[p] + c->tp_flags_off) + rank;
             g.xg_epoch = c->tp_epoch;
+            if (pull)
+                for (int p = 0; p < tp; p++) g.x_part_ptr[p] = (const float*)c->tp_peers[p] + ((size_t)(k & 1) * tp + p) * d;
+            if (!gather) out.push_back(xr);
             k++;
         }
+        ops.swap(out);
     }
     B2_CUDA_CHECK(cudaMalloc(&c->d_ops, ops.size() * sizeof(StepOp)));
     B2_CUDA_CHECK(cudaMemcpyAsync(c->d_ops, ops.data(), ops.size() * sizeof(StepOp), cudaMemcpyHostToDevice, c->stream));
@@ -708,7 +734,7 @@ void dump_step_trace(b2_ctx* c) {
     const int S = STEP_TRACE_SLOTS;
     std::vector<unsigned long long> t((size_t)c->n_ops * S);
     if (cudaMemcpy(t.data(), c->step_trace, t.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return;
-    const char* kinds[] = {"embed", "gemv", "attn", "argmax"};
+    const char* kinds[] = {"embed", "gemv", "attn", "argmax", "xchg"};
     struct Acc { double wait = 0, pro = 0, tiles = 0, epi = 0, mark[7] = {0, 0, 0, 0, 0, 0, 0}; int n = 0; };
     std::map<std::string, Acc> by;
     unsigned long long prev_arrive = 0;

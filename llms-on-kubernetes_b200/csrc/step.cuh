@@ -4,12 +4,12 @@
 
 namespace b2 {
 
-enum { OP_EMBED = 0, OP_GEMV = 1, OP_ATTN = 2, OP_ARGMAX = 3 };
+enum { OP_EMBED = 0, OP_GEMV = 1, OP_ATTN = 2, OP_ARGMAX = 3, OP_XCHG = 4 };
 
 // One stage of a decode step.  Stages run in order with a grid-wide barrier between them.
 struct StepOp {
     int kind;
-    GemvArgs g;   // OP_GEMV
+    GemvArgs g;   // OP_GEMV; OP_XCHG (tensor-parallel shard: wait for the ranks' partial rows and add them into x) uses x, K and the x_* / xg_* fields
     // OP_EMBED: x = dequantise(table[*token])
     int e_type, e_d_model, e_vocab;
     const uint8_t* e_table;

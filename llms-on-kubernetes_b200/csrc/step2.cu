@@ -287,7 +287,7 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
             }
             // a fence orders only the calling thread's stores: every lane that wrote results fences, then one arrives
             // (system scope when the rows went into the other ranks' memory)
-            if (TP && a.seg[0].n_peer > 0) __threadfence_system();
+            if (TP && a.seg[0].n_peer > 0 && !a.seg[0].peer_local) __threadfence_system();
             else __threadfence();
             __syncwarp();
             if (lane == 0) {
@@ -383,6 +383,10 @@ __global__ void __launch_bounds__(STEP2_THREADS, 2) step2_kernel(const __grid_co
                 attn_stage(op, ss.xbase, ss.aux[oi & 1], ss.aux + 4 + 12 * (oi & 1), sm.xbar + 1, ss.aux + 3, tid,
                            (P.trace && blockIdx.x == 0) ? P.trace + oi * STEP_TRACE_SLOTS : nullptr);
             else if (op.kind == OP_ARGMAX) argmax_stage(op, ss.xbase, tid);
+            else if (TP && op.kind == OP_XCHG) {
+                xchg_wait(op.g, tid);
+                xchg_materialise(op.g, tid);
+            }
             __threadfence();   // every thread's stores of this stage, before the CTA's single arrival
             named_bar_sync(1, NCT);
             if (tid == 0) {

@@ -213,9 +213,28 @@ static __device__ __noinline__ void xchg_wait(const GemvArgs& a, int tid) {
     }
     named_bar_sync(1, NCT);
 }
-// ... and the sum is left in x for the residual reads of the next row-split epilogue (a few CTAs' worth of stores)
+// ... and the sum, every CTA a slice, is written to x: as a stage of its own (OP_XCHG) in front of the consuming
+// mat-vec, so that its prologue reads one vector instead of every CTA adding up all the ranks' rows itself (at TP 8 that
+// was 256 KB out of L2 per CTA and exchange).
 static __device__ __noinline__ void xchg_materialise(const GemvArgs& a, int tid) {
     const int n4 = a.K / 4;
+    if (a.x_part_ptr[0]) {
+        // pull form: every rank left its partial row in its own memory; this CTA's slice of each is fetched over NVLink
+        // (loads that bypass L1: a parity buffer is rewritten two exchanges later) and added in rank order
+        for (int i = blockIdx.x * NCT + tid; i < n4; i += gridDim.x * NCT) {
+            float4 v[8];
+#pragma unroll
+            for (int r = 0; r < 8; r++)
+                if (r < a.x_nparts) asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[r].x), "=f"(v[r].y), "=f"(v[r].z), "=f"(v[r].w)
+                                                 : "l"((const float4*)a.x_part_ptr[r] + i) : "memory");
+            float4 s = v[0];
+#pragma unroll
+            for (int r = 1; r < 8; r++)
+                if (r < a.x_nparts) { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+            ((float4*)const_cast<float*>(a.x))[i] = s;
+        }
+        return;
+    }
     const float4* in = (const float4*)a.x_parts;
     for (int i = blockIdx.x * NCT + tid; i < n4; i += gridDim.x * NCT) {
         float4 s = __ldcg(in + i);

@@ -123,7 +123,7 @@ int tp_allreduce_inplace(void* comm, float* x, int n, cudaStream_t st) {
 // ---- peer memory for the exchange inside the persistent kernel (step2.cu: OP_XCHG) ----
 // Every rank allocates `bytes` of device memory (zeroed), publishes its CUDA IPC handle through the communicator
 // (ncclAllGather of the 64-byte handles) and maps every peer's allocation: peers[r] is rank r's buffer as seen from this
-// process (peers[rank] = the local allocation).  The kernels only ever STORE into a peer's buffer and LOAD from their
+// process (peers[rank] = the local allocation).  The kernels STORE flags into a peer's buffer and, in the pull form of the exchange, LOAD partial rows from it (plain loads over NVLink, no multicast); everything else they read is their
 // own (plain st.global / ld.global over NVLink: no TMA, no multicast).
 int tp_peer_buffers(void* comm, int rank, int size, size_t bytes, void** local_out, void** peers, cudaStream_t st) {
     Nccl* nc;
