@@ -381,8 +381,10 @@ def main():
             # NCCL's log (communicator ranks, transports) is wanted, but it goes to stdout, which must carry exactly one
             # JSON line: file descriptor 1 is pointed at stderr for the rest of the process and the line is written to a
             # duplicate of the original stdout (emit() below)
-            os.environ.setdefault("NCCL_DEBUG", "INFO")
+            if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+                os.environ["NCCL_DEBUG"] = "INFO"      # (a WARN / VERSION left in the environment would hide the communicator lines)
             os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+            os.environ.pop("NCCL_DEBUG_FILE", None)
             sys.stdout.flush()
             _real_stdout[0] = os.fdopen(os.dup(1), "w")
             os.dup2(2, 1)
