@@ -3,14 +3,20 @@
 // Same program of stages, grid barrier, attention / embedding / sampling stages and epilogues as step.cu; what changed
 // is how the weight stream reaches the arithmetic (matvec_team.cuh: the first design was bound by instruction issue):
 //   * tile = 8 weight rows (4 row pairs); ring allocation = one STEP = the tile's rows x 16 blocks of K, copied by the
-//     producer warp with one bulk copy per row; up to 8 steps in flight in an 81 KB byte ring;
+//     producer warp with one bulk copy per row (lanes 0..7 each announce and issue their row's copy); five Q4_K steps
+//     fit the 92.8 KB byte ring;
 //   * compute warp w owns blocks 2w, 2w + 1 of the step for all 8 rows: Q4_K through ldmatrix + mma.sync (u8 x s8), the
 //     other types through dp4a quarters; a lane keeps one fp32 row sum over the tile's whole K loop; the 6-bit scales
 //     are unpacked in the lane: no decoder warp, one barrier per step;
-//   * the warp that used to decode headers is a second producer (measured: a look-ahead warp that asked L2 to fetch the
-//     rows some steps ahead, cp.async.bulk.prefetch.L2, bought nothing: the stream is limited by how fast copies are
-//     issued and slots released, not by DRAM latency -- tools/ubench_stream.cu reaches 7.2 TB/s with 108 KB in flight
-//     per SM, and prefetching on top of a ring that deep lowers it).
+//   * ten warps (8 compute, producer, epilogue): 320 threads x 2 CTAs per SM leave 96 registers per thread, enough to keep
+//     the activation fragments of a single-chunk row in registers for the whole stage.  Measured and left out: a second
+//     producer warp (the eleventh warp caps the kernel at 80 registers: 461 -> 417 tok/s) and a look-ahead warp that
+//     asked L2 to fetch rows some steps ahead (cp.async.bulk.prefetch.L2: -1 .. +0.3 %; the stream is limited by how
+//     fast copies are issued and slots released, not by DRAM latency -- tools/ubench_stream.cu reaches 7.2 TB/s with
+//     108 KB in flight per SM, and prefetching on top of a ring that deep lowers it);
+//   * a normalising stage's RMS factor is applied by the epilogue warp to the finished row sums (build_activation DEFER):
+//     the quantiser does not wait for the sum of squares;
+//   * TP instantiation: row-split stages leave partial rows for the other ranks, OP_XCHG stages add the ranks' rows.
 // B2_STEP_V=1 selects the first design (step.cu) for comparison.
 #include <cstdlib>
 
