@@ -282,8 +282,11 @@ int b2_tcq_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, i
     __half* xb = (__half*)scratch_dev;
     float* ws = (float*)((uint8_t*)scratch_dev + ((size_t)T * K * 2 + 255) / 256 * 256);
     int rc;
-    if ((rc = launch_rows_to_f16(const_cast<float*>(x_dev), K, nullptr, 0.0f, (int)K, T, ACT_Q8K, xb, (cudaStream_t)stream))) return rc;
+    const bool perm = tcq_fast_conversion();
+    if ((rc = launch_rows_to_f16(const_cast<float*>(x_dev), K, nullptr, 0.0f, (int)K, T, ACT_Q8K, xb, (cudaStream_t)stream, TcParts{nullptr, 1, 0}, perm)))
+        return rc;
     TcqGemmArgs a{};
+    a.x_perm = perm ? 1 : 0;
     a.seg[0] = TcqSeg{W_dev, type, (int)N};
     a.n_seg = 1;
     a.x = xb;

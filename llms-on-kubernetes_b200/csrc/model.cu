@@ -1352,6 +1352,7 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
     // tensors cross HBM once, no fp16 copy is read.  The result is always left as slices; a caller that wants it in `out`
     // (defer == nullptr) gets a reduction kernel.
     const bool fused = tcq_pass_ok(m, T);
+    const bool perm = fused && tcq_fast_conversion();   // the fused kernel's fp16 conversion wants the activations' K order permuted
     auto mmq = [&](std::initializer_list<const b2_model::W*> ws, int K, float* out, int64_t ldo, int epi, TcParts* defer) {
         TcqGemmArgs a{};
         int N = 0;
@@ -1360,6 +1361,7 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
             N += (int)w->rows;
         }
         a.x = xb;
+        a.x_perm = perm ? 1 : 0;
         a.K = K;
         a.T = T;
         a.ws = p.ws;
@@ -1380,7 +1382,7 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         __half* kc = c->k_cache + il * kv_layer;
         __half* vc = c->v_cache + il * kv_layer;
         // RMSNorm -> one mat-mul over the stacked Q | K | V matrices -> bias, RoPE, KV cache
-        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.wq.type), xb, st, pend)))
+        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.attn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.wq.type), xb, st, pend, perm)))
             return rc;
         if (!cache && !fused) {
             if ((rc = dq(L.wq, wb))) return rc;
@@ -1432,13 +1434,13 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         }
         mark(2);
         // output projection + residual
-        if ((rc = launch_rows_to_f16(p.attn_out, qdim, nullptr, 0.0f, qdim, T, gemm_act_for_type(L.wo.type), xb, st))) return rc;
+        if ((rc = launch_rows_to_f16(p.attn_out, qdim, nullptr, 0.0f, qdim, T, gemm_act_for_type(L.wo.type), xb, st, TcParts{nullptr, 1, 0}, perm))) return rc;
         if (!cache && !fused && (rc = dq(L.wo, wb))) return rc;
         if (fused) rc = mmq({&L.wo}, qdim, p.x, I.d_model, TC_EPI_ADD, &pend);
         else rc = mm(cache ? cache + m->f16_off[il].o : wb, I.d_model, qdim, p.x, I.d_model, TC_EPI_ADD, &pend);
         if (rc) return rc;
         // (+ the O slices) RMSNorm -> stacked gate | up -> SwiGLU -> down + residual
-        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.gate.type), xb, st, pend)))
+        if ((rc = launch_rows_to_f16(p.x, I.d_model, (const float*)L.ffn_norm.p, I.eps, I.d_model, T, gemm_act_for_type(L.gate.type), xb, st, pend, perm)))
             return rc;
         if (!cache && !fused) {
             if ((rc = dq(L.gate, wb))) return rc;
@@ -1447,7 +1449,7 @@ int enqueue_tc_pass(b2_ctx* c, const int32_t* tok_dev, int T, int slot, int pos0
         if (fused) rc = mmq({&L.gate, &L.up}, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE, &parts);
         else rc = mm(cache ? cache + m->f16_off[il].gate_up : wb, 2 * I.d_ff, I.d_model, p.gu, 2 * (int64_t)I.d_ff, TC_EPI_STORE, &parts);
         if (rc) return rc;
-        if ((rc = launch_swiglu_to_f16(p.gu, parts, I.d_ff, T, gemm_act_for_type(L.down.type), xb, il == I.n_layer - 1 ? c->h : nullptr, st))) return rc;
+        if ((rc = launch_swiglu_to_f16(p.gu, parts, I.d_ff, T, gemm_act_for_type(L.down.type), xb, il == I.n_layer - 1 ? c->h : nullptr, st, perm))) return rc;
         if (!cache && !fused && (rc = dq(L.down, wb))) return rc;
         // the last layer's down projection reduces its own slices: nothing after it in this pass reads x through a norm kernel
         const bool last = il == I.n_layer - 1;
@@ -1504,17 +1506,20 @@ int enqueue_logits_tc(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t
     const b2_model_info& I = m->info;
     int rc;
     __half* xb = (__half*)c->pf.xb;
-    if ((rc = launch_rows_to_f16(const_cast<float*>(x_rows), I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits,
-                                 gemm_act_for_type(m->output.type), xb, st)))
-        return rc;
     const bool no_tcq = env_flag("B2_NO_TCQ") || (m->f16_cache && !env_flag("B2_TCQ"));
-    if (!no_tcq && n_logits <= TCQ_MAX_T && tcq_supported(m->output.type, I.d_model) && I.vocab % 4 == 0 &&
-        tcq_ws_bytes(I.vocab, I.d_model, n_logits) <= c->pf.ws_bytes) {
+    const bool fused = !no_tcq && n_logits <= TCQ_MAX_T && tcq_supported(m->output.type, I.d_model) && I.vocab % 4 == 0 &&
+                       tcq_ws_bytes(I.vocab, I.d_model, n_logits) <= c->pf.ws_bytes;
+    const bool perm = fused && tcq_fast_conversion();
+    if ((rc = launch_rows_to_f16(const_cast<float*>(x_rows), I.d_model, (const float*)m->output_norm.p, I.eps, I.d_model, n_logits,
+                                 gemm_act_for_type(m->output.type), xb, st, TcParts{nullptr, 1, 0}, perm)))
+        return rc;
+    if (fused) {
         // the lm_head's quantised rows dequantised inside the tcgen05 kernel (tcq_gemm.cu)
         TcqGemmArgs q{};
         q.seg[0] = TcqSeg{m->output.p, m->output.type, I.vocab};
         q.n_seg = 1;
         q.x = xb;
+        q.x_perm = perm ? 1 : 0;
         q.K = I.d_model;
         q.T = n_logits;
         q.ws = c->pf.ws;

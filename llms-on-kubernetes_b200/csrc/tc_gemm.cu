@@ -236,6 +236,13 @@ __device__ __forceinline__ uint32_t pack_h2s(float a, float b) {
     return *(const uint32_t*)&h;
 }
 
+// eight consecutive values as fp16; perm: elements 1 and 2 of each group of four swapped (the K order tcq_gemm.cu's fp16
+// conversion produces its weight pairs in)
+__device__ __forceinline__ uint4 store8(const float (&v)[8], int perm) {
+    if (perm) return make_uint4(pack_h2s(v[0], v[2]), pack_h2s(v[1], v[3]), pack_h2s(v[4], v[6]), pack_h2s(v[5], v[7]));
+    return make_uint4(pack_h2s(v[0], v[1]), pack_h2s(v[2], v[3]), pack_h2s(v[4], v[5]), pack_h2s(v[6], v[7]));
+}
+
 template <int TYPE>
 __global__ void dequant_f16_kernel(const uint8_t* __restrict__ src, uint4* __restrict__ dst, int64_t n8) {
     for (int64_t g = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; g < n8; g += (int64_t)gridDim.x * blockDim.x) {
@@ -309,7 +316,7 @@ __device__ __forceinline__ void load8_parts(const float* __restrict__ direct, co
 // (2) the activation quantisation of the mat-mul that follows (act_requantise8) and the rounding to fp16.
 template <int FMT>
 __global__ void __launch_bounds__(256) rows_to_f16_kernel(float* __restrict__ x, int64_t ldx, const float* __restrict__ w, float eps, int n,
-                                                          __half* __restrict__ y, const TcParts pend) {
+                                                          __half* __restrict__ y, const TcParts pend, int perm) {
     __shared__ double ss_warp[8];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     float* xr = x + (int64_t)blockIdx.x * ldx;
@@ -362,7 +369,7 @@ __global__ void __launch_bounds__(256) rows_to_f16_kernel(float* __restrict__ x,
             for (int i = 0; i < 8; i++) v[i] = 0.0f;
         }
         act_requantise8<FMT>(v);
-        if (in) *(uint4*)(yr + i0) = make_uint4(pack_h2s(v[0], v[1]), pack_h2s(v[2], v[3]), pack_h2s(v[4], v[5]), pack_h2s(v[6], v[7]));
+        if (in) *(uint4*)(yr + i0) = store8(v, perm);
     }
 }
 
@@ -371,7 +378,7 @@ __global__ void __launch_bounds__(256) rows_to_f16_kernel(float* __restrict__ x,
 // last row's h also in fp32 (h_last, b2_ctx_get_activation)
 template <int FMT>
 __global__ void __launch_bounds__(256) swiglu_to_f16_kernel(const float* __restrict__ gu, const TcParts parts, int d_ff, int T,
-                                                            __half* __restrict__ y, float* __restrict__ h_last) {
+                                                            __half* __restrict__ y, float* __restrict__ h_last, int perm) {
     const int t = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t row = (size_t)t * 2 * d_ff;
     for (int s = warp; s < (d_ff + 255) / 256; s += 8) {
@@ -393,7 +400,7 @@ __global__ void __launch_bounds__(256) swiglu_to_f16_kernel(const float* __restr
             for (int i = 0; i < 8; i++) v[i] = 0.0f;
         }
         act_requantise8<FMT>(v);
-        if (in) *(uint4*)(y + (size_t)t * d_ff + i0) = make_uint4(pack_h2s(v[0], v[1]), pack_h2s(v[2], v[3]), pack_h2s(v[4], v[5]), pack_h2s(v[6], v[7]));
+        if (in) *(uint4*)(y + (size_t)t * d_ff + i0) = store8(v, perm);
     }
 }
 
@@ -529,7 +536,7 @@ int launch_dequant_f16(int type, const void* src, __half* dst, int64_t n, cudaSt
     return 0;
 }
 
-int launch_rows_to_f16(float* x, int64_t ldx, const float* norm_w, float eps, int n, int rows, int act_fmt, __half* y, cudaStream_t st, TcParts pend) {
+int launch_rows_to_f16(float* x, int64_t ldx, const float* norm_w, float eps, int n, int rows, int act_fmt, __half* y, cudaStream_t st, TcParts pend, bool perm) {
     if (!x || !y || n <= 0 || rows <= 0 || n % 8 || ldx % 4 || ((uintptr_t)x & 15) || ((uintptr_t)y & 15) || (norm_w && ((uintptr_t)norm_w & 15))) {
         set_error("rows_to_f16: bad arguments (n=%d rows=%d)", n, rows);
         return B2_EINVAL;
@@ -538,21 +545,21 @@ int launch_rows_to_f16(float* x, int64_t ldx, const float* norm_w, float eps, in
         set_error("rows_to_f16: row length %d is not a whole number of activation blocks", n);
         return B2_EINVAL;
     }
-    if (act_fmt == ACT_Q8K) rows_to_f16_kernel<ACT_Q8K><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend);
-    else if (act_fmt == ACT_Q80) rows_to_f16_kernel<ACT_Q80><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend);
-    else rows_to_f16_kernel<-1><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend);
+    if (act_fmt == ACT_Q8K) rows_to_f16_kernel<ACT_Q8K><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend, perm ? 1 : 0);
+    else if (act_fmt == ACT_Q80) rows_to_f16_kernel<ACT_Q80><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend, perm ? 1 : 0);
+    else rows_to_f16_kernel<-1><<<rows, 256, 0, st>>>(x, ldx, norm_w, eps, n, y, pend, perm ? 1 : 0);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
 
-int launch_swiglu_to_f16(const float* gu, TcParts parts, int d_ff, int T, int act_fmt, __half* y, float* h_last, cudaStream_t st) {
+int launch_swiglu_to_f16(const float* gu, TcParts parts, int d_ff, int T, int act_fmt, __half* y, float* h_last, cudaStream_t st, bool perm) {
     if (!gu || !y || d_ff <= 0 || T <= 0 || d_ff % 8 || (act_fmt == ACT_Q8K && d_ff % 256) || (act_fmt == ACT_Q80 && d_ff % 32)) {
         set_error("swiglu_to_f16: bad arguments (d_ff=%d T=%d)", d_ff, T);
         return B2_EINVAL;
     }
-    if (act_fmt == ACT_Q8K) swiglu_to_f16_kernel<ACT_Q8K><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last);
-    else if (act_fmt == ACT_Q80) swiglu_to_f16_kernel<ACT_Q80><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last);
-    else swiglu_to_f16_kernel<-1><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last);
+    if (act_fmt == ACT_Q8K) swiglu_to_f16_kernel<ACT_Q8K><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
+    else if (act_fmt == ACT_Q80) swiglu_to_f16_kernel<ACT_Q80><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
+    else swiglu_to_f16_kernel<-1><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

@@ -57,9 +57,9 @@ int launch_dequant_f16(int type, const void* src, __half* dst, int64_t n, cudaSt
 // ACT_Q80 (Q8_0 weights: 32-element Q8_0 blocks), or < 0 for no quantisation (plain rounding).  pend: a deferred
 // residual mat-mul (out += ...) into x: its slices are added to x[t][:] first (x is written back)
 int launch_rows_to_f16(float* x, int64_t ldx, const float* norm_w, float eps, int n, int rows, int act_fmt, __half* y, cudaStream_t st,
-                       TcParts pend = TcParts{nullptr, 1, 0});
+                       TcParts pend = TcParts{nullptr, 1, 0}, bool perm = false);   // perm: see TcqGemmArgs::x_perm
 
 // y[t][:] = fp16(Q(silu(gate) * up)) of the stacked gate | up output gu[T][2 d_ff] (or its deferred slices)
-int launch_swiglu_to_f16(const float* gu, TcParts parts, int d_ff, int T, int act_fmt, __half* y, float* h_last, cudaStream_t st);
+int launch_swiglu_to_f16(const float* gu, TcParts parts, int d_ff, int T, int act_fmt, __half* y, float* h_last, cudaStream_t st, bool perm = false);
 
 }  // namespace b2

@@ -79,6 +79,7 @@ struct TcqParams {
     int seg_rows[TCQ_MAX_SEGS];
     int seg_type[TCQ_MAX_SEGS];
     int N, K, T, nblk, tiles_m, splits;
+    int fast;  // fp16 conversion, activations stored with the middle two of every four elements swapped (TcqGemmArgs::x_perm)
     int dbg;   // B2_TCQ_DBG (experiments): 1 = no MMAs, 2 = no dequantisation arithmetic, 4 = no tensor-memory stores
     float* ws;
     long long* trace;   // B2_TCQ_TRACE=1: clock64 stamps of CTA 0 ([0..]: MMA thread, 2 per K step; [4096..]: dequantising warp of group 0, 4 per block)
@@ -200,6 +201,75 @@ __device__ __forceinline__ void dequant_q6k(uint32_t blk, int g, uint32_t (&o)[3
             const float s = ds[2 * j + (i >> 2)], f = off[2 * j + (i >> 2)];
             o[16 * j + 2 * i] = pack_sat(fmaf(lo_f(p01), s, f), fmaf(hi_f(p01), s, f));
             o[16 * j + 2 * i + 1] = pack_sat(fmaf(lo_f(p23), s, f), fmaf(hi_f(p23), s, f));
+        }
+    }
+}
+
+// ---- the same in fp16 arithmetic (TcqGemmArgs::x_perm): 1.6 instead of 3.4 instructions per weight -----------------------
+// The code bits are OR-ed into the mantissa of a half whose ulp is the code's unit -- 0x6400 (1024, ulp 1) for a low
+// nibble or a byte, 0x5400 (64, ulp 1/16) for a high nibble in place -- the offset is subtracted exactly, and one HFMA2
+// applies scale and minimum, both rounded to fp16 first (2^-11 relative each; the exact path rounds once at the end).
+// A word's four codes come out as the pairs (0, 2) and (1, 3): the activations are stored with elements 1 and 2 of every
+// group of four swapped (launch_rows_to_f16 / launch_swiglu_to_f16 `perm`), so no shuffle is needed.
+__device__ __forceinline__ __half2 h2_of(uint32_t x) { return *(const __half2*)&x; }
+__device__ __forceinline__ uint32_t u_of(__half2 h) { return *(const uint32_t*)&h; }
+__device__ __forceinline__ __half2 h2_clamped(float v) { return __float2half2_rn(fminf(fmaxf(v, -65504.0f), 65504.0f)); }
+
+__device__ __forceinline__ void dequant_q4k_fast(uint32_t blk, int g, uint32_t (&o)[32]) {
+    const uint4 hd = lds128(blk);
+    const __half2 dd = *(const __half2*)&hd.x;
+    const float d = __low2float(dd), dmin = __high2float(dd);
+    int s0, m0, s1, m1;
+    if (g < 2) {
+        const int sh = 16 * g;
+        s0 = (hd.y >> sh) & 63; m0 = (hd.z >> sh) & 63;
+        s1 = (hd.y >> (sh + 8)) & 63; m1 = (hd.z >> (sh + 8)) & 63;
+    } else {
+        const int sh = 16 * (g - 2);
+        s0 = ((hd.w >> sh) & 0xF) | (((hd.y >> (sh + 6)) & 3) << 4);
+        m0 = ((hd.w >> (sh + 4)) & 0xF) | (((hd.z >> (sh + 6)) & 3) << 4);
+        s1 = ((hd.w >> (sh + 8)) & 0xF) | (((hd.y >> (sh + 14)) & 3) << 4);
+        m1 = ((hd.w >> (sh + 12)) & 0xF) | (((hd.z >> (sh + 14)) & 3) << 4);
+    }
+    const __half2 ds0 = h2_clamped(d * (float)s0), dm0 = h2_clamped(-(dmin * (float)m0));
+    const __half2 ds1 = h2_clamped(d * (float)s1), dm1 = h2_clamped(-(dmin * (float)m1));
+    const __half2 k1024 = __float2half2_rn(1024.0f), k64 = __float2half2_rn(64.0f);
+    const uint4 qa = lds128(blk + 16 + 32 * g), qb = lds128(blk + 32 + 32 * g);
+    const uint32_t w[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const uint32_t w8 = w[i] >> 8;
+        const uint32_t a = (w[i] & 0x000F000Fu) | 0x64006400u, b = (w8 & 0x000F000Fu) | 0x64006400u;   // codes (0, 2), (1, 3), low nibbles
+        const uint32_t c = (w[i] & 0x00F000F0u) | 0x54005400u, e = (w8 & 0x00F000F0u) | 0x54005400u;   // high nibbles in place: bits 4..7 of a half in [64, 128) count units of 16 x 1/16 = 1
+        o[2 * i] = u_of(__hfma2(__hsub2(h2_of(a), k1024), ds0, dm0));
+        o[2 * i + 1] = u_of(__hfma2(__hsub2(h2_of(b), k1024), ds0, dm0));
+        o[16 + 2 * i] = u_of(__hfma2(__hsub2(h2_of(c), k64), ds1, dm1));
+        o[16 + 2 * i + 1] = u_of(__hfma2(__hsub2(h2_of(e), k64), ds1, dm1));
+    }
+}
+
+__device__ __forceinline__ void dequant_q6k_fast(uint32_t blk, int g, uint32_t (&o)[32]) {
+    const int n = g >> 1, u = g & 1;
+    uint32_t dbits, sc4[1];
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(dbits) : "r"(blk + 208) : "memory");
+    lds_words_even<1>(blk + 192 + 8 * n + 4 * u, sc4);
+    const float d = __half2float(__ushort_as_half((unsigned short)dbits));
+    __half2 ds[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) ds[k] = h2_clamped(d * (float)(int8_t)(sc4[0] >> (8 * k)));
+    const __half2 k1056 = __float2half2_rn(1056.0f);   // 1024 (the magic) + 32 (the code's bias)
+    uint32_t ql[16], qh[8];
+    lds_words_even<16>(blk + 64 * n, ql);
+    lds_words_even<8>(blk + 128 + 32 * n, qh);
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const uint32_t q = ((ql[8 * j + i] >> (4 * u)) & 0x0F0F0F0Fu) | (((qh[i] >> (2 * (2 * u + j))) & 0x03030303u) << 4);
+            const uint32_t p02 = __byte_perm(q, 0x64646464u, 0x4240), p13 = __byte_perm(q, 0x64646464u, 0x4341);
+            const __half2 s = ds[2 * j + (i >> 2)];
+            o[16 * j + 2 * i] = u_of(__hmul2(__hsub2(h2_of(p02), k1056), s));
+            o[16 * j + 2 * i + 1] = u_of(__hmul2(__hsub2(h2_of(p13), k1056), s));
         }
     }
 }
@@ -383,6 +453,9 @@ __global__ void __launch_bounds__(TQ_THREADS, 1) tcq_gemm_kernel(const __grid_co
                 if (p.dbg & 2) {
 #pragma unroll
                     for (int i = 0; i < 32; i++) o[i] = 0u;
+                } else if (p.fast) {
+                    if (q4) dequant_q4k_fast(blk, g, o);
+                    else dequant_q6k_fast(blk + (uint32_t)((kb * 210) & 15), g, o);
                 } else if (q4) dequant_q4k(blk, g, o);
                 else dequant_q6k(blk + (uint32_t)((kb * 210) & 15), g, o);
                 __syncwarp();
@@ -572,6 +645,8 @@ int tq_tiles(const TcqGemmArgs& a) {
 }  // namespace
 
 // (a tensor map's row stride is a multiple of 16 bytes: rows of 210-byte Q6_K blocks qualify when K is a multiple of 2048)
+bool tcq_fast_conversion() { return getenv("B2_TCQ_EXACT") == nullptr; }
+
 bool tcq_supported(int type, int K) {
     if (K <= 0 || K % 256) return false;
     return type == B2_TYPE_Q4_K || (type == B2_TYPE_Q6_K && (K / 256) % 8 == 0);
@@ -639,6 +714,7 @@ int launch_tcq_gemm(const TcqGemmArgs& a, cudaStream_t st, TcParts* parts) {
         return B2_EINVAL;
     }
     p.ws = a.ws;
+    p.fast = a.x_perm;
     if (const char* e = getenv("B2_TCQ_DBG")) p.dbg = atoi(e);
     *parts = TcParts{a.ws, p.splits, (size_t)a.T * p.N};
     static const bool want_trace = getenv("B2_TCQ_TRACE") != nullptr;

@@ -29,12 +29,17 @@ struct TcqGemmArgs {
     int n_seg;
     const __half* x;            // [T][K] activations (launch_rows_to_f16 / launch_swiglu_to_f16)
     int K, T;
+    // 1: x was written with `perm` (elements 1 and 2 of every group of four swapped) and the kernel converts the codes in
+    // fp16 arithmetic (scale and minimum rounded to fp16 before the multiply-add: <= 2 ulp of the fp16 weight instead of the
+    // exact path's 1/2 ulp; 1.6 instead of 3.4 instructions per weight).  0: natural order, exact conversion.
+    int x_perm;
     // The result is always left as slices: out(t, n) = sum over s < splits of ws[s * T * N + t * N + n] (N = the stacked
     // rows), to be added up in slice order by the consumer (TcParts) or by tcq_reduce.  Slices a tile does not need hold zeros.
     float* ws;
     size_t ws_bytes;
 };
 
+bool tcq_fast_conversion();                                         // the default; B2_TCQ_EXACT=1: exact conversion, natural K order
 bool tcq_supported(int type, int K);                                // Q4_K: K a multiple of 256; Q6_K: of 2048 (16-byte row stride)
 size_t tcq_ws_bytes(int N, int K, int T);                           // upper bound of the slices' size for this shape
 // runs the mat-mul; *parts describes the slices (splits >= 1)
