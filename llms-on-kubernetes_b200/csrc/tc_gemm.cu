@@ -321,6 +321,62 @@ __global__ void __launch_bounds__(256) rows_to_f16_kernel(float* __restrict__ x,
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     float* xr = x + (int64_t)blockIdx.x * ldx;
     __half* yr = y + (int64_t)blockIdx.x * n;
+    constexpr int RC = 4;   // chunks of 2048 elements a thread keeps in registers: rows up to 8192 make ONE pass over global memory
+    if (n <= RC * 2048) {
+        // thread tid owns elements tid * 8 + 2048 k ..+8 = lane `lane` of span warp + 8 k: the mapping of all three phases
+        float v[RC][8];
+        double ss = 0.0;
+#pragma unroll
+        for (int k = 0; k < RC; k++) {
+            const int i0 = tid * 8 + k * 2048;
+            if (i0 < n) {
+                const float4 p0 = *(const float4*)(xr + i0), p1 = *(const float4*)(xr + i0 + 4);
+                v[k][0] = p0.x; v[k][1] = p0.y; v[k][2] = p0.z; v[k][3] = p0.w; v[k][4] = p1.x; v[k][5] = p1.y; v[k][6] = p1.z; v[k][7] = p1.w;
+                if (pend.splits > 1) {
+                    float d[8];
+                    load8_parts(nullptr, pend, (size_t)blockIdx.x * n + i0, d);
+#pragma unroll
+                    for (int i = 0; i < 8; i++) v[k][i] += d[i];
+                    *(float4*)(xr + i0) = make_float4(v[k][0], v[k][1], v[k][2], v[k][3]);
+                    *(float4*)(xr + i0 + 4) = make_float4(v[k][4], v[k][5], v[k][6], v[k][7]);
+                }
+#pragma unroll
+                for (int i = 0; i < 8; i++) ss += (double)(v[k][i] * v[k][i]);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[k][i] = 0.0f;
+            }
+        }
+        float scale = 1.0f;
+        if (w) {
+            // (the double sum is reduced in another order than the re-reading path below: within fp32 rounding of the mean)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+            if (lane == 0) ss_warp[warp] = ss;
+            __syncthreads();
+            double tot = 0.0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) tot += ss_warp[i];
+            scale = 1.0f / sqrtf((float)(tot / (double)n) + eps);
+        }
+#pragma unroll
+        for (int k = 0; k < RC; k++) {
+            const int i0 = tid * 8 + k * 2048;
+            if (k * 2048 >= n) break;                 // whole spans only beyond this point (warp-uniform)
+            const bool in = i0 < n;
+            if (in && w) {
+                const float4 w0 = *(const float4*)(w + i0), w1 = *(const float4*)(w + i0 + 4);
+                const float g[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+                for (int i = 0; i < 8; i++) v[k][i] = (v[k][i] * scale) * g[i];
+            }
+            if ((warp + 8 * k) * 256 < n) {           // the warp's span exists (its tail lanes may be past the row end)
+                act_requantise8<FMT>(v[k]);
+                if (in) *(uint4*)(yr + i0) = store8(v[k], perm);
+            }
+        }
+        return;
+    }
     if (pend.splits > 1) {
         for (int i0 = tid * 8; i0 < n; i0 += 256 * 8) {
             float v[8];
@@ -381,7 +437,8 @@ __global__ void __launch_bounds__(256) swiglu_to_f16_kernel(const float* __restr
                                                             __half* __restrict__ y, float* __restrict__ h_last, int perm) {
     const int t = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t row = (size_t)t * 2 * d_ff;
-    for (int s = warp; s < (d_ff + 255) / 256; s += 8) {
+    // (the spans are independent: gridDim.y CTAs share a row, so that a 32-row decode batch is more than 32 CTAs)
+    for (int s = blockIdx.y * 8 + warp; s < (d_ff + 255) / 256; s += 8 * gridDim.y) {
         const int i0 = (s << 8) + lane * 8;
         const bool in = i0 < d_ff;
         float v[8];
@@ -557,9 +614,13 @@ int launch_swiglu_to_f16(const float* gu, TcParts parts, int d_ff, int T, int ac
         set_error("swiglu_to_f16: bad arguments (d_ff=%d T=%d)", d_ff, T);
         return B2_EINVAL;
     }
-    if (act_fmt == ACT_Q8K) swiglu_to_f16_kernel<ACT_Q8K><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
-    else if (act_fmt == ACT_Q80) swiglu_to_f16_kernel<ACT_Q80><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
-    else swiglu_to_f16_kernel<-1><<<T, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
+    // CTAs per row: enough to fill the GPU with a narrow batch, never fewer than one span per warp
+    const int spans = (d_ff + 255) / 256;
+    int per_row = std::max(1, std::min((spans + 7) / 8, (2 * 148 + T - 1) / T));
+    const dim3 grid(T, per_row);
+    if (act_fmt == ACT_Q8K) swiglu_to_f16_kernel<ACT_Q8K><<<grid, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
+    else if (act_fmt == ACT_Q80) swiglu_to_f16_kernel<ACT_Q80><<<grid, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
+    else swiglu_to_f16_kernel<-1><<<grid, 256, 0, st>>>(gu, parts, d_ff, T, y, h_last, perm ? 1 : 0);
     B2_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
