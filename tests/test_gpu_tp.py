@@ -11,18 +11,22 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def test_two_way_tensor_parallel_decode_matches_oracle_and_replica(b2, tmp_path):
+# every form of the exchange that was built: the default (reduce stage, partial rows pulled over NVLink),
+# rows pushed into every rank's inbox, the consumer adding the rows up itself, and round 1's NCCL all-reduce path
+# (captured in the step's CUDA graph, and eager)
+FORMS = [{}, {"B2_TP_PUSH": "1"}, {"B2_TP_GATHER": "1"}, {"B2_TP_NCCL": "1"}, {"B2_TP_NCCL": "1", "B2_TP_NO_GRAPH": "1"}]
+
+
+@pytest.mark.parametrize("form", FORMS, ids=lambda f: "+".join(sorted(f)) or "default")
+def test_two_way_tensor_parallel_decode_matches_oracle_and_replica(b2, tmp_path, form):
     if b2.device_count() < 2:
         pytest.skip("needs two GPUs")
-    for graph in ("", "1"):                      # the all-reduces captured in the step's CUDA graph, and eager
-        env = dict(os.environ, B2_TP_PARITY_ONLY="1", B2_BENCH_DIR=str(tmp_path))
-        if graph:
-            env["B2_TP_NO_GRAPH"] = "1"
-        r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-                            "--master-port", "29517", os.path.join(ROOT, "tools", "tp_check.py")], env=env, capture_output=True, text=True,
-                           timeout=600)
-        lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
-        assert r.returncode == 0 and len(lines) == 3, r.stdout[-2000:] + r.stderr[-2000:]
+    env = dict(os.environ, B2_TP_PARITY_ONLY="1", B2_BENCH_DIR=str(tmp_path), **form)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29517", os.path.join(ROOT, "tools", "tp_check.py")], env=env, capture_output=True, text=True,
+                       timeout=600)
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    assert r.returncode == 0 and len(lines) == 3, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 def test_shard_arguments_are_checked(b2, tiny_models):
