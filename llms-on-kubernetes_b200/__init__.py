@@ -87,6 +87,7 @@ SYMBOLS = {
     "b2_tc_gemm_scratch_bytes": (_SZ, [_I64, _I64, _I]),
     "b2_tc_gemm": (_I, [_I, _P, _P, _P, _I64, _I64, _I, _I, _P, _P]),
     "b2_tcq_gemm_scratch_bytes": (_SZ, [_I64, _I64, _I]),
+    "b2_tcq_plan": (_I, [_P, _I, _I64, _I, _P, _P, _P, _P, _P]),
     "b2_tcq_gemm": (_I, [_I, _P, _P, _P, _I64, _I64, _I, _I, _P, _P]),
     "b2_rmsnorm": (_I, [_P, _P, _P, _I64, _I64, C.c_float, _P]),
     "b2_rope": (_I, [_P, _I, _I, _I, _I, _I, C.c_float, _P, _P]),
@@ -261,6 +262,17 @@ def tc_gemm(qtype: int, W: np.ndarray, x: np.ndarray, N: int, K: int, y0: np.nda
     check(lib.b2_tc_gemm(qtype, dW.ptr, dx.ptr, dy.ptr, N, K, T, 0 if y0 is None else 1, scratch.ptr, None))
     check(lib.b2_stream_sync(None))
     return dy.to_numpy(np.float32).reshape(T, N)
+
+
+def tcq_plan(seg_rows, K: int, n_sms: int = 148) -> dict:
+    """The stream-K decomposition b2_tcq_gemm uses for a stack of tensors (host arithmetic; works without a GPU)."""
+    rows = np.ascontiguousarray(seg_rows, np.int32)
+    tiles, grid, slices = C.c_int32(), C.c_int32(), C.c_int32()
+    check(lib.b2_tcq_plan(rows.ctypes.data, rows.size, K, n_sms, C.byref(tiles), C.byref(grid), C.byref(slices), None, None))
+    shares = np.zeros(2 * grid.value, np.int64)
+    first = np.zeros(tiles.value, np.int32)
+    check(lib.b2_tcq_plan(rows.ctypes.data, rows.size, K, n_sms, None, None, None, shares.ctypes.data, first.ctypes.data))
+    return {"tiles": tiles.value, "grid": grid.value, "slices": slices.value, "shares": shares.reshape(-1, 2), "first_cta": first}
 
 
 def tcq_gemm(qtype: int, W: np.ndarray, x: np.ndarray, N: int, K: int, y0: np.ndarray | None = None) -> np.ndarray:

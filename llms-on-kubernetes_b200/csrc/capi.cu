@@ -262,6 +262,31 @@ int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, in
     return launch_tc_gemm(a, (cudaStream_t)stream);
 }
 
+int b2_tcq_plan(const int32_t* seg_rows, int n_seg, int64_t K, int n_sms, int32_t* tiles_out, int32_t* grid_out, int32_t* slices_out,
+                int64_t* shares_out, int32_t* first_cta_out) {
+    if (K <= 0 || K > 0x3fffffff) return B2_EINVAL;
+    int tiles = 0, grid = 0, slices = 0;
+    const int rc = tcq_plan(seg_rows, n_seg, (int)K, n_sms, &tiles, &grid, &slices);
+    if (rc) {
+        set_error("b2_tcq_plan: bad arguments");
+        return rc;
+    }
+    if (tiles_out) *tiles_out = tiles;
+    if (grid_out) *grid_out = grid;
+    if (slices_out) *slices_out = slices;
+    const int nblk = (int)(K / 256);
+    if (shares_out)
+        for (int c = 0; c < grid; c++) {
+            long long lo, hi;
+            tcq_share(tiles, nblk, grid, c, &lo, &hi);
+            shares_out[2 * c] = lo;
+            shares_out[2 * c + 1] = hi;
+        }
+    if (first_cta_out)
+        for (int t = 0; t < tiles; t++) first_cta_out[t] = tcq_first_cta_of_tile(tiles, nblk, grid, t);
+    return 0;
+}
+
 size_t b2_tcq_gemm_scratch_bytes(int64_t N, int64_t K, int T) {
     if (N <= 0 || K <= 0 || T <= 0) return 0;
     return ((size_t)T * K * 2 + 255) / 256 * 256 + tcq_ws_bytes((int)N, (int)K, T);

@@ -636,30 +636,48 @@ int launch_tq(const TcqMaps& maps, const TcqParams& p, int grid, cudaStream_t st
     return 0;
 }
 
-int tq_tiles(const TcqGemmArgs& a) {
-    int t = 0;
-    for (int i = 0; i < a.n_seg; i++) t += (a.seg[i].rows + TQ_BM - 1) / TQ_BM;
-    return t;
-}
-
 }  // namespace
-
-// (a tensor map's row stride is a multiple of 16 bytes: rows of 210-byte Q6_K blocks qualify when K is a multiple of 2048)
-bool tcq_fast_conversion() { return getenv("B2_TCQ_EXACT") == nullptr; }
-
-bool tcq_supported(int type, int K) {
-    if (K <= 0 || K % 256) return false;
-    return type == B2_TYPE_Q4_K || (type == B2_TYPE_Q6_K && (K / 256) % 8 == 0);
-}
 
 // CTAs for `tiles` tiles of `nblk` block columns: one per SM, fewer when a tile would otherwise be cut into more than
 // TQ_MAX_SLICES partial sums (skinny matrices with a long K: the consumer reads every slice)
 constexpr int TQ_MAX_SLICES = 8;
-static int tq_grid(int tiles, int nblk) {
+static int tq_grid_for(int tiles, int nblk, int n_sms) {
     const long long total = (long long)tiles * nblk;
-    int grid = (int)std::min<long long>(tq_sm_count(), total);
+    int grid = (int)std::min<long long>(n_sms, total);
     while (grid > 1 && tq_slices(tiles, nblk, grid) > TQ_MAX_SLICES) grid = grid * 7 / 8;
     return grid;
+}
+static int tq_grid(int tiles, int nblk) { return tq_grid_for(tiles, nblk, tq_sm_count()); }
+
+// The stream-K plan of a launch as host arithmetic (tests/test_tcq_plan.py checks it without a GPU): tiles of 128 rows per
+// segment, K / 256 block columns each, shared out over `grid` CTAs; *slices_out = the most CTAs any tile meets.
+int tcq_plan(const int* seg_rows, int n_seg, int K, int n_sms, int* tiles_out, int* grid_out, int* slices_out) {
+    if (!seg_rows || n_seg < 1 || n_seg > TCQ_MAX_SEGS || K <= 0 || K % 256 || n_sms < 1) return B2_EINVAL;
+    int tiles = 0;
+    for (int i = 0; i < n_seg; i++) {
+        if (seg_rows[i] < 1) return B2_EINVAL;
+        tiles += (seg_rows[i] + TQ_BM - 1) / TQ_BM;
+    }
+    const int nblk = K / 256, grid = tq_grid_for(tiles, nblk, n_sms);
+    if (tiles_out) *tiles_out = tiles;
+    if (grid_out) *grid_out = grid;
+    if (slices_out) *slices_out = tq_slices(tiles, nblk, grid);
+    return 0;
+}
+// the share of CTA c: steps [lo, hi) of the tile-major sequence (step = tile * nblk + block column), as Walk computes it
+void tcq_share(int tiles, int nblk, int grid, int c, long long* lo, long long* hi) {
+    const long long total = (long long)tiles * nblk;
+    *lo = total * c / grid;
+    *hi = total * (c + 1) / grid;
+}
+int tcq_first_cta_of_tile(int tiles, int nblk, int grid, int tile) { return cta_of_step((long long)tile * nblk, (long long)tiles * nblk, grid); }
+
+bool tcq_fast_conversion() { return getenv("B2_TCQ_EXACT") == nullptr; }
+
+// (a tensor map's row stride is a multiple of 16 bytes: rows of 210-byte Q6_K blocks qualify when K is a multiple of 2048)
+bool tcq_supported(int type, int K) {
+    if (K <= 0 || K % 256) return false;
+    return type == B2_TYPE_Q4_K || (type == B2_TYPE_Q6_K && (K / 256) % 8 == 0);
 }
 
 size_t tcq_ws_bytes(int N, int K, int T) {

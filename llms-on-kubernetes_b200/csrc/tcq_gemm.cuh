@@ -41,6 +41,10 @@ struct TcqGemmArgs {
 
 bool tcq_fast_conversion();                                         // the default; B2_TCQ_EXACT=1: exact conversion, natural K order
 bool tcq_supported(int type, int K);                                // Q4_K: K a multiple of 256; Q6_K: of 2048 (16-byte row stride)
+// host arithmetic of the stream-K decomposition (no GPU needed): see tcq_gemm.cu
+int tcq_plan(const int* seg_rows, int n_seg, int K, int n_sms, int* tiles_out, int* grid_out, int* slices_out);
+void tcq_share(int tiles, int nblk, int grid, int c, long long* lo, long long* hi);
+int tcq_first_cta_of_tile(int tiles, int nblk, int grid, int tile);
 size_t tcq_ws_bytes(int N, int K, int T);                           // upper bound of the slices' size for this shape
 // runs the mat-mul; *parts describes the slices (splits >= 1)
 int launch_tcq_gemm(const TcqGemmArgs& a, cudaStream_t st, TcParts* parts);
