@@ -1119,8 +1119,10 @@ int run_batch(b2_ctx* c, const int32_t* tokens, const int32_t* slots, const int3
     B2_CUDA_CHECK(cudaMemcpyAsync(c->bt.slot, c->h_pin + 2 * BATCH_MAX_COLS, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
     if (!c->use_graph) return enqueue_batch(c, n, n_logits, c->stream);
     auto& graphs = c->bt.graphs;
-    if (graphs.empty()) graphs.resize((size_t)(BATCH_MAX_COLS + 1) * (BATCH_MAX_COLS + 1));
-    auto& g = graphs[(size_t)n * (BATCH_MAX_COLS + 1) + n_logits];
+    if (graphs.empty()) graphs.resize((size_t)2 * (BATCH_MAX_COLS + 1) * (BATCH_MAX_COLS + 1));
+    // one graph per (columns, logits rows) and per mat-mul path: B2_TCQ can be switched between calls
+    const size_t variant = (c->pf.cap && tcq_pass_ok(c->m, n)) ? 1 : 0;
+    auto& g = graphs[(variant * (BATCH_MAX_COLS + 1) + (size_t)n) * (BATCH_MAX_COLS + 1) + n_logits];
     if (g.exec) {
         B2_CUDA_CHECK(cudaGraphLaunch(g.exec, c->stream));
         return 0;
@@ -1529,6 +1531,7 @@ int enqueue_logits_tc(b2_ctx* c, const float* x_rows, int n_logits, cudaStream_t
         if ((rc = launch_tcq_reduce(parts, n_logits, I.vocab, c->bt.logits, I.vocab, nullptr, TC_EPI_STORE, st))) return rc;
         return launch_argmax_rows(c->bt.logits, I.vocab, n_logits, c->bt.out, st);
     }
+    if (!m->f16_cache) return enqueue_logits(c, x_rows, n_logits, st);   // neither path applies: the int8 kernel
     TcGemmArgs a{};
     a.w = (const __half*)m->f16_cache + m->f16_output;
     a.x = xb;

@@ -121,7 +121,7 @@ struct b2_ctx {
         // one CUDA graph per (columns, logit columns): ~310 launches per pass replayed as one; an entry is
         // captured the second time its shape is used (the first use runs eagerly)
         struct G { cudaGraphExec_t exec = nullptr; bool seen = false; };
-        std::vector<G> graphs;   // index = n * (cap + 1) + n_logits
+        std::vector<G> graphs;   // index = (path * (cap + 1) + n) * (cap + 1) + n_logits  (path 1: the fused-dequantisation mat-mul)
     } bt;
     // prompt-phase path (tc_gemm.cu, prefill_attn.cu): whole chunks of a prompt per pass over fp16 copies of the
     // weights, allocated on the first long prompt
