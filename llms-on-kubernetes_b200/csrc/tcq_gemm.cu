@@ -66,8 +66,10 @@ struct TqGeo {
     static constexpr int N_BARS = 2 * TQ_NA + 2 * NX + 2 * RSTAGES + 4;
     static constexpr int SMEM = NX * X_BYTES + RSTAGES * TQ_RAW_BYTES + 1024 + 8 * N_BARS + 16;
     static constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TQ_BM >> 4) << 24);
-    // MMAs into one accumulator execute one after the other at the pipeline's latency (~130 cycles for these narrow
-    // shapes): consecutive K = 16 slices go to NACC accumulators in turn, the epilogue adds them in a fixed order
+    // consecutive K = 16 slices go to NACC accumulators in turn and the epilogue adds them in a fixed order.  (Built on the
+    // suspicion that MMAs into ONE accumulator serialise at the pipeline's latency; measured, they do not -- dependent
+    // M = 128, N = 32 MMAs issue every 26 cycles, tools/ubench_umma.cu; the ~130 cycles per MMA seen before were the
+    // divergent issuing thread.  Kept: it is free and shortens each accumulator's fp32 summation chain.)
     static constexpr int NACC = 128 / BN;
 };
 static_assert(TqGeo<32>::SMEM <= 227 * 1024 && TqGeo<64>::SMEM <= 227 * 1024 && TqGeo<128>::SMEM <= 227 * 1024, "shared memory budget");
