@@ -156,7 +156,7 @@ int b2_tc_gemm(int type, const void* W_dev, const float* x_dev, float* y_dev, in
  * b2_tc_gemm, so the results differ only by fp32 summation order.  Q4_K with K a multiple of 256, Q6_K with K a multiple
  * of 2048 (rows of 210-byte blocks then keep the 16-byte stride a tensor map needs), N a multiple of 4; B2_EUNSUP otherwise.  scratch_dev: b2_tcq_gemm_scratch_bytes(N, K, T) bytes, 256-byte aligned. */
 size_t b2_tcq_gemm_scratch_bytes(int64_t N, int64_t K, int T);
-/* How b2_tcq_gemm cuts a stack of n_seg tensors (seg_rows[i] rows each, K columns) over n_sms CTAs: host arithmetic, no GPU
+/* (row a12, host side) How b2_tcq_gemm cuts a stack of n_seg tensors (seg_rows[i] rows each, K columns) over n_sms CTAs: host arithmetic, no GPU
  * needed.  The (128-row tile, 256-column block) pairs are numbered tile-major and every CTA takes an equal contiguous
  * share; a tile that several CTAs touch is summed from that many slices.  *tiles_out, *grid_out (CTAs), *slices_out (the
  * most CTAs any tile meets), shares_out[2 c], [2 c + 1] = CTA c's first step and end (room for 2 n_sms values),
